@@ -1,0 +1,208 @@
+/*
+ * orfx.h — C-ABI of the B200-native ORFanage hot path.
+ *
+ * The reference (alevar/ORFanage v1.2.0) has no plugin / FFI interface: its hot path is a code
+ * region, the body of the bundle loop in orfanage.cpp:376-817 and the SEGTP/CHAIN/TX/SEQ methods
+ * it calls (src/Transcriptome.{h,cpp}, src/common.hpp).  This header is the seam a maintainer
+ * would cut there: everything upstream (GTF/FASTA loading, template preparation, bundling —
+ * orfanage.cpp:313-367) packs an orfx_batch; everything downstream (attribute maps, GTF / stats
+ * formatting — orfanage.cpp:662-815) consumes orfx_results.  INTEGRATION.md shows the binding.
+ *
+ * Conventions: plain C, plain pointers and sizes, no exceptions across the boundary.  Every call
+ * returns 0 on success or a negative ORFX_E_* code; orfx_last_error() gives the message.  There is
+ * no CPU fallback: orfx_create fails when no sm_100 device / CUDA runtime is usable.
+ */
+#ifndef ORFX_H
+#define ORFX_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define ORFX_ABI_VERSION 1
+
+/* error codes */
+#define ORFX_OK            0
+#define ORFX_E_INVALID    -1   /* bad argument / malformed batch */
+#define ORFX_E_CUDA       -2   /* CUDA runtime or kernel failure */
+#define ORFX_E_NODEVICE   -3   /* no usable GPU: the product path never computes on the CPU */
+#define ORFX_E_UNSUPPORTED -4  /* option outside this build's scope (e.g. --overhang > 0) */
+#define ORFX_E_STATE      -5   /* call sequence error (wait without submit, ...) */
+
+/* --mode selector entries; replaces enum FindMode, orfanage.cpp:29-39 */
+#define ORFX_MODE_START_MATCH   0
+#define ORFX_MODE_ALL           1
+#define ORFX_MODE_LONGEST       2
+#define ORFX_MODE_LONGEST_MATCH 3
+#define ORFX_MODE_BEST          4
+#define ORFX_MODE_FIRST         5
+
+/* candidate-row status; replaces the `notes` strings written at orfanage.cpp:510-627 */
+#define ORFX_ST_OK             0   /* "-" (reached scoring; see `pass`)        */
+#define ORFX_ST_NO_OVERLAP     1   /* "no-overlap"      orfanage.cpp:509-514   */
+#define ORFX_ST_SEGMENT_LT3    2   /* "segment_len<3"   orfanage.cpp:538-542   */
+#define ORFX_ST_CDS_LT3        3   /* "cds_len<3"       orfanage.cpp:549-561   */
+#define ORFX_ST_NOT_RESCUED    4   /* "not_rescued"     orfanage.cpp:578-582   */
+#define ORFX_ST_MISSING_STOP   5   /* "missing_stop"    orfanage.cpp:584-598   */
+#define ORFX_ST_MISSING_START  6   /* "missing_start"   orfanage.cpp:584-598   */
+#define ORFX_ST_MINLEN         7   /* "minlen"          orfanage.cpp:607-611   */
+#define ORFX_ST_DUP            8   /* "dup"             orfanage.cpp:622-627   */
+
+/* transcript kinds inside a batch */
+#define ORFX_TX_QUERY     0
+#define ORFX_TX_TEMPLATE  1
+#define ORFX_TX_SKIP      2   /* present in the bundle but not evaluated (e.g. --keep_all_cds) */
+
+/* Hot-path parameters; replaces the fields of GlobalParameters (orfanage.cpp:99-142) that the
+ * bundle loop reads. */
+typedef struct orfx_params {
+    int32_t n_modes;
+    int32_t mode_array[8];      /* ORFX_MODE_*, priority order (orfanage.cpp:120-122)          */
+    int32_t lpi, ilpi, mlpi;    /* int thresholds, -1 = off (orfanage.cpp:615-617)             */
+    int32_t cds_minlen;         /* -1 = off (orfanage.cpp:607)                                 */
+    int32_t non_aug;            /* --non_aug                                                   */
+    int32_t overhang;           /* --overhang (must be 0 in this build)                        */
+    int32_t spliced_overhang;
+    int32_t has_reference;      /* 0: no FASTA, candidates are scored as seeded (orfanage.cpp:564) */
+    int32_t want_rows;          /* 1: return every candidate row (needed by --stats and mode ALL) */
+    int32_t reserved[4];
+} orfx_params;
+
+/* 1-based inclusive genomic interval; replaces SEGTP (Transcriptome.h:23-169) */
+typedef struct orfx_seg { int32_t start, end; } orfx_seg;
+
+/* A packed set of locus bundles; replaces the bundled Transcriptome handed to the loop at
+ * orfanage.cpp:376 (Bundle: Transcriptome.h:840-891).  All arrays are caller-owned host memory
+ * (pinned memory makes the upload asynchronous) and must stay valid until orfx_wait returns.
+ * Only bundles that hold at least one template and one query belong here (orfanage.cpp:383). */
+typedef struct orfx_batch {
+    int32_t n_bundles;
+    int32_t n_tx;
+    int64_t n_segs;
+    int64_t seq_bytes;
+    /* per bundle */
+    const uint8_t* seq;            /* concatenated bundle windows, raw FASTA bytes, case preserved;
+                                      may be NULL when params.has_reference == 0                  */
+    const int64_t* seq_off;        /* [n_bundles+1] byte offsets into seq                          */
+    const int32_t* bundle_start;   /* [n_bundles] genomic coordinate of the first window byte      */
+    const int32_t* bundle_tx_off;  /* [n_bundles+1] transcripts of a bundle are contiguous, in the
+                                      reference's sorted bundle order                              */
+    /* per transcript */
+    const uint8_t* tx_kind;        /* [n_tx] ORFX_TX_*                                             */
+    const uint8_t* tx_strand;      /* [n_tx] '+', '-' or '.'                                       */
+    const int32_t* tx_seg_off;     /* [n_tx+1] CSR into segs                                       */
+    const int32_t* tx_cds_start;   /* [n_tx] templates: TX::cds_start member; others 0             */
+    const int32_t* tx_cds_end;     /* [n_tx] templates: TX::cds_end member; others 0               */
+    const int32_t* tx_tid_class;   /* [n_tx] equal transcript_id strings <=> equal value           */
+    /* per segment: query -> exon chain; template -> CDS chain (== its exon chain after
+     * set_cds_as_exons, orfanage.cpp:351) with the phase column of each CDS segment */
+    const orfx_seg* segs;          /* [n_segs] ascending, disjoint                                 */
+    const int8_t*   seg_phase;     /* [n_segs] templates: SEGTP::phase of the CDS chain; else 0    */
+} orfx_batch;
+
+/* One chosen ORF per query transcript; what orfanage.cpp:753-791 needs to write the GTF. */
+typedef struct orfx_best {
+    int32_t q_tx;          /* transcript index in the batch                                   */
+    int32_t t_tx;          /* template index of the winning row, -1 = no ORF found            */
+    int32_t cds_start;     /* genomic, 1-based inclusive                                      */
+    int32_t cds_end;
+    int32_t duplicity;     /* TX::num_dups() of the emitted transcript (orfanage_duplicity)   */
+    int32_t n_rows;        /* candidate rows of this query                                    */
+    int64_t row_off;       /* first row of this query in the row arrays                       */
+    int64_t best_row;      /* absolute row index of the winner, -1 = none                     */
+    float   lpi, ilpi, mlpi;
+    int32_t start_match;
+} orfx_best;
+
+/* Results of one batch.  Library-owned pinned host buffers, valid until orfx_release / the next
+ * orfx_submit on the same context.  Row arrays are filled only when params.want_rows != 0. */
+typedef struct orfx_results {
+    int32_t n_queries;
+    int64_t n_rows;
+    const orfx_best* best;         /* [n_queries] in bundle order, then query order inside the bundle */
+    /* candidate rows, SoA, in the reference's (query, template, segment) order */
+    const int32_t* row_q_tx;
+    const int32_t* row_t_tx;
+    const int32_t* row_seg_start;  /* original intersection segment (orfanage.cpp:522)           */
+    const int32_t* row_seg_end;
+    const int32_t* row_cds_start;  /* flatten() key (orfanage.cpp:265-267)                       */
+    const int32_t* row_cds_end;
+    const uint8_t* row_status;     /* ORFX_ST_*                                                  */
+    const uint8_t* row_pass;
+    const uint8_t* row_start_match;
+    const int32_t* row_n_dup;      /* TX::num_dups() of the row's query copy (stats column 5 - 1) */
+    const int32_t* row_qlen;       /* Score (common.hpp:32-65)                                   */
+    const int32_t* row_tlen;
+    const int32_t* row_ulen;
+    const int32_t* row_query_start;
+    const int32_t* row_extra;
+    const int32_t* row_missing;
+    const int32_t* row_match;
+    const int32_t* row_outframe;
+    const int32_t* row_inframe;
+    const float*   row_lpi;
+    const float*   row_ilpi;
+    const float*   row_mlpi;
+    const int64_t* print_order;    /* [n_rows] absolute row indices in the stats print order:
+                                      per query, keys ascending, inside a key the std::sort by
+                                      score_gt (orfanage.cpp:250-283)                            */
+    /* device-side timing of the last batch, milliseconds (CUDA events on the launch stream) */
+    float ms_h2d, ms_kernels, ms_d2h;
+} orfx_results;
+
+typedef struct orfx_ctx orfx_ctx;
+
+const char* orfx_last_error(void);
+int  orfx_abi_version(void);
+
+/* device = CUDA ordinal. */
+int  orfx_create(orfx_ctx** out, int device, const orfx_params* params);
+int  orfx_set_params(orfx_ctx* ctx, const orfx_params* params);
+/* Asynchronous: uploads the batch and enqueues every kernel of the path on the context's stream. */
+int  orfx_submit(orfx_ctx* ctx, const orfx_batch* batch);
+/* Blocks until the batch is done and the results are in host memory. */
+int  orfx_wait(orfx_ctx* ctx, orfx_results* out);
+int  orfx_release(orfx_ctx* ctx);
+void orfx_destroy(orfx_ctx* ctx);
+
+/* ---- device-resident variant used by the benchmark's kernel-only timing ------------------- */
+/* Uploads a batch once and keeps it in HBM. */
+int  orfx_upload(orfx_ctx* ctx, const orfx_batch* batch);
+/* Runs the whole path on the resident batch; no host<->device copies.  Returns the number of
+ * kernels launched in *n_launches (may be NULL). */
+int  orfx_run_resident(orfx_ctx* ctx, int* n_launches);
+/* Copies the results of the last resident run to the host (same buffers as orfx_wait). */
+int  orfx_fetch(orfx_ctx* ctx, orfx_results* out);
+/* Per-kernel device times of the last run, in launch order.  names[i] are static strings. */
+int  orfx_kernel_times(orfx_ctx* ctx, int max_n, const char** names, float* ms, int* n);
+/* Sum of spliced query nucleotides in the resident batch (codon-scan roofline numerator). */
+int64_t orfx_resident_query_nt(orfx_ctx* ctx);
+
+/* ---- per-stage access for differential tests (SURVEY.md §4 iii) --------------------------- */
+/* Codon-scan masks of the resident batch after a run: for query transcript tx, bit p of
+ * stop/start says whether the codon starting at spliced position p (5'->3') is a stop / ATG.
+ * Buffers must hold ceil(L/32) words, L = spliced length.  Returns L or a negative error. */
+int64_t orfx_get_masks(orfx_ctx* ctx, int32_t tx, uint32_t* stop_bits, uint32_t* start_bits, int64_t max_words);
+
+/* ---- protein alignment (src/aln.hpp:27-41 with the build definition) ---- */
+typedef struct orfx_aln_out {
+    int32_t* max;      /* ez.max  : max(0, best H over all cells) */
+    int32_t* score;    /* ez.score: H(tlen-1, qlen-1)             */
+    int32_t* mqe;      /* ez.mqe  : best H in the last query column */
+    int32_t* mte;      /* ez.mte  : best H in the last target row   */
+} orfx_aln_out;
+
+/* aa: concatenated residues already encoded 0..23 through aa_table (common.hpp:268-277);
+ * off[n_seq+1]; pair_q / pair_t index sequences.  Substitution matrix mat50 (common.hpp:239-265),
+ * gap open gapo, gap extend gape (aln.hpp:146: 12 / 2).  Output arrays are caller-owned host memory
+ * of n_pairs entries.  cells (optional) receives sum of qlen*tlen; ms (optional) the device time. */
+int  orfx_align_batch(orfx_ctx* ctx, const uint8_t* aa, const int64_t* off, int64_t n_seq,
+                      const int32_t* pair_q, const int32_t* pair_t, int64_t n_pairs,
+                      int gapo, int gape, orfx_aln_out* out, double* cells, float* ms);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* ORFX_H */

@@ -1,0 +1,169 @@
+// Host side of the B200-native ORFanage hot path: the reference's surface (CLI flags, GTF/FASTA
+// loading, template preparation, locus bundling, GTF / stats emission) around the C-ABI in
+// include/orfx.h.  Nothing here scores or rescues an ORF: that is the device library's job.
+#pragma once
+#include <cstdint>
+#include <cstdio>
+#include <map>
+#include <string>
+#include <vector>
+#include <stdexcept>
+#include "orfx.h"
+
+namespace orfx {
+
+// --- interval chains (host mirror of SEGTP/CHAIN, Transcriptome.h:23-563) -------------------
+struct Seg {
+    int32_t s = 0, e = 0;
+    int8_t phase = 0;
+    int32_t len() const { return e + 1 - s; }
+};
+typedef std::vector<Seg> Chain;
+
+int chain_len(const Chain& c);
+// transcript-order offset (5'->3') of genomic position g, -1 when g is intronic/outside
+// (CHAIN::genome2nt, Transcriptome.h:447-462)
+int genome2nt(const Chain& c, int g, char strand);
+// genomic position of transcript-order offset; clamps to the 3' end (CHAIN::nt2genome, h:463-481)
+int nt2genome(const Chain& c, int off, char strand);
+// GTF phase column for every segment, 5'->3' (CHAIN::assign_phase, h:432-446)
+void assign_phase(Chain& c, char strand, int start_phase);
+// keep the part of c inside [lo,hi] (CHAIN::cut, h:268-289)
+void cut_chain(Chain& c, int lo, int hi);
+
+// --- transcripts -----------------------------------------------------------------------------
+struct Tx {
+    bool is_templ = false;
+    int id = -1;
+    std::string tid, gid;
+    int seqid = -1;
+    char strand = '.';
+    int cds_start = 0, cds_end = 0, cds_phase = 0;
+    bool is_coding = false;
+    std::string source, cds_source;
+    std::map<std::string, std::string> attrs;
+    Chain exons, cds;
+
+    int start() const { return exons.front().s; }
+    int end() const { return exons.back().e; }
+    void build_cds();            // TX::build_cds, Transcriptome.cpp:92-122
+    void correct_chain_len();    // TX::correct_chain_len, cpp:123-130
+    void remove_cds();           // TX::remove_cds, cpp:131-138
+    bool add_attribute(const std::string& k, const std::string& v) { return attrs.insert(std::make_pair(k, v)).second; }
+    std::string gtf(const std::string& seqname) const;   // TX::str, Transcriptome.h:734-783
+};
+bool tx_less(const Tx& a, const Tx& b);    // TX::operator<, Transcriptome.h:668-684
+bool tx_same(const Tx& a, const Tx& b);    // TX::operator==, Transcriptome.h:703-722
+
+struct GtfRecord {   // one transcript as read from a GTF (what the reference gets from gclib's GffObj)
+    std::string seqname, source, tid, gid;
+    bool has_gid = false, has_cds = false;
+    char strand = '.';
+    std::vector<std::pair<uint32_t, uint32_t>> exons;   // ascending
+    uint32_t cd_start = 0, cd_end = 0;
+    char cd_phase = '.';
+    std::vector<std::pair<std::string, std::string>> attrs;   // transcript-line attributes, file order
+};
+void read_gtf(const std::string& path, std::vector<GtfRecord>& out);
+
+// --- FASTA ------------------------------------------------------------------------------------
+class Fasta {
+public:
+    void load(const std::string& path);
+    const std::string* get(const std::string& name) const;
+    bool write_fai_if_missing(const std::string& path) const;
+private:
+    struct Rec { std::string name; std::string seq; int64_t file_off = 0; int line_bases = 0, line_bytes = 0; };
+    std::vector<Rec> recs_;
+    std::map<std::string, size_t> idx_;
+};
+
+struct Bundle {
+    int first = 0, count = 0;        // range in Transcriptome::txs
+    int seqid = -1;
+    char strand = 0;
+    int bstart = INT32_MAX, bend = 0;
+    std::string gid;
+    bool has_template = false, has_query = false;
+};
+
+class Transcriptome {
+public:
+    std::vector<Tx> txs;
+    std::vector<Bundle> bundles;
+    std::vector<std::string> seqnames;
+    const Fasta* fasta = nullptr;
+
+    void add(const std::string& gtf_path, bool is_templ, bool coding_only);   // Transcriptome::add, cpp:866-894
+    void build_cds_chains();          // cpp:1033-1044
+    void correct_chain_len();         // cpp:1045-1051
+    void sort(bool use_id);           // Transcriptome.h:904-924
+    void set_cds_as_exons();          // cpp:1141-1145
+    void remove_non_coding();         // cpp:1146-1150
+    size_t deduplicate(bool use_id);  // cpp:1124-1140
+    size_t bundleup(bool use_id, uint32_t overhang);   // cpp:920-1032
+private:
+    std::map<std::string, int> seqids_;
+};
+
+// --- options (GlobalParameters, orfanage.cpp:99-142) -------------------------------------------
+struct Options {
+    bool clean_query = false, clean_templ = false, rescue = false, use_id = false, non_aug = false;
+    bool keep_all_cds = false, keep_cds_if_not_found = false, spliced_overhang = false;
+    int lpi = -1, ilpi = -1, mlpi = -1, minlen = -1, overhang = 0, threads = 1;
+    std::vector<int> modes{ORFX_MODE_LONGEST_MATCH, ORFX_MODE_BEST, ORFX_MODE_START_MATCH,
+                           ORFX_MODE_LONGEST, ORFX_MODE_FIRST, ORFX_MODE_ALL};
+    std::string reference, query, output, stats;
+    std::vector<std::string> templates;
+    bool stats_set = false;
+    // build-specific
+    std::vector<int> devices{0};
+    bool timing = false;
+};
+// Parses argv with the reference's rules (arg_parse.hpp:101-209; orfanage.cpp:835-1098).
+// Returns false when the program should exit 0 (help).
+bool parse_cli(int argc, char** argv, Options& opt);
+void fill_params(const Options& opt, bool want_rows, orfx_params& p);
+
+// --- batcher: bundles -> flat arrays ------------------------------------------
+struct PackedBatch {
+    std::vector<int> bundle_ids;            // index into Transcriptome::bundles
+    std::vector<int> tx_global;             // batch tx index -> Transcriptome::txs index
+    std::vector<uint8_t> seq;
+    std::vector<int64_t> seq_off;
+    std::vector<int32_t> bundle_start, bundle_tx_off;
+    std::vector<uint8_t> tx_kind, tx_strand;
+    std::vector<int32_t> tx_seg_off, tx_cds_start, tx_cds_end, tx_tid_class;
+    std::vector<orfx_seg> segs;
+    std::vector<int8_t> seg_phase;
+    orfx_batch view() const;
+};
+// Packs the listed bundles (each must hold a template and a query).
+void pack_bundles(const Transcriptome& tr, const std::vector<int>& bundle_ids, const Options& opt,
+                  const std::map<std::string, int>& tid_classes, PackedBatch& out);
+void build_tid_classes(const Transcriptome& tr, std::map<std::string, int>& out);
+// greedy longest-processing-time split of active bundles over n shards
+void shard_bundles(const Transcriptome& tr, const std::vector<int>& active, int n, std::vector<std::vector<int>>& shards);
+
+// --- backend: the five C-ABI entry points the runner drives -----------------------------------
+struct Backend {
+    int (*create)(orfx_ctx**, int, const orfx_params*);
+    int (*submit)(orfx_ctx*, const orfx_batch*);
+    int (*wait)(orfx_ctx*, orfx_results*);
+    int (*release)(orfx_ctx*);
+    void (*destroy)(orfx_ctx*);
+    const char* (*last_error)();
+};
+
+// replaces run() (orfanage.cpp:307-822): prepares, bundles, evaluates through `be`, writes outputs
+int run_orfanage(const Options& opt, const Backend& be);
+
+// emission helpers (orfanage.cpp:662-815)
+struct Emitter {
+    FILE* gtf = nullptr;
+    FILE* stats = nullptr;
+};
+std::string float_to_string(float v);     // std::to_string(float)
+std::string float_ostream(float v);       // operator<<(ostream&, float) at default precision
+
+}  // namespace orfx

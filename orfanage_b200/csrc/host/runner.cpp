@@ -1,0 +1,378 @@
+// Batcher, multi-GPU locus sharding and GTF / stats emission around the C-ABI.
+// Replaces run() of the reference (orfanage.cpp:307-822); the evaluation itself (the body of the
+// bundle loop) happens behind Backend::submit / wait.
+#include "orfx_host.h"
+#include <algorithm>
+#include <chrono>
+#include <cstring>
+#include <thread>
+
+namespace orfx {
+
+std::string float_to_string(float v) { char b[64]; snprintf(b, sizeof b, "%f", (double)v); return b; }
+std::string float_ostream(float v) { char b[64]; snprintf(b, sizeof b, "%g", (double)v); return b; }
+
+orfx_batch PackedBatch::view() const {
+    orfx_batch b;
+    memset(&b, 0, sizeof b);
+    b.n_bundles = (int32_t)bundle_ids.size();
+    b.n_tx = (int32_t)tx_kind.size();
+    b.n_segs = (int64_t)segs.size();
+    b.seq_bytes = (int64_t)seq.size();
+    b.seq = seq.empty() ? nullptr : seq.data();
+    b.seq_off = seq_off.data();
+    b.bundle_start = bundle_start.data();
+    b.bundle_tx_off = bundle_tx_off.data();
+    b.tx_kind = tx_kind.data();
+    b.tx_strand = tx_strand.data();
+    b.tx_seg_off = tx_seg_off.data();
+    b.tx_cds_start = tx_cds_start.data();
+    b.tx_cds_end = tx_cds_end.data();
+    b.tx_tid_class = tx_tid_class.data();
+    b.segs = segs.data();
+    b.seg_phase = seg_phase.data();
+    return b;
+}
+
+void build_tid_classes(const Transcriptome& tr, std::map<std::string, int>& out) {
+    for (const Tx& t : tr.txs) out.insert(std::make_pair(t.tid, (int)out.size()));
+}
+
+void pack_bundles(const Transcriptome& tr, const std::vector<int>& bundle_ids, const Options& opt,
+                  const std::map<std::string, int>& tid_classes, PackedBatch& out) {
+    out = PackedBatch();
+    out.bundle_ids = bundle_ids;
+    size_t total_seq = 0, total_tx = 0, total_segs = 0;
+    for (int bi : bundle_ids) {
+        const Bundle& b = tr.bundles[bi];
+        if (tr.fasta) total_seq += (size_t)(b.bend - b.bstart + 1);
+        total_tx += (size_t)b.count;
+        for (int i = 0; i < b.count; i++) { const Tx& t = tr.txs[b.first + i]; total_segs += t.is_templ ? t.cds.size() : t.exons.size(); }
+    }
+    out.seq.reserve(total_seq + 16);
+    out.segs.reserve(total_segs);
+    out.seg_phase.reserve(total_segs);
+    out.tx_kind.reserve(total_tx);
+    out.seq_off.push_back(0);
+    out.bundle_tx_off.push_back(0);
+    out.tx_seg_off.push_back(0);
+    for (int bi : bundle_ids) {
+        const Bundle& b = tr.bundles[bi];
+        if (tr.fasta) {
+            const std::string* s = tr.fasta->get(tr.seqnames[b.seqid]);
+            out.seq.insert(out.seq.end(), s->begin() + (b.bstart - 1), s->begin() + b.bend);   // Bundle::load_seq, cpp:821-830
+        }
+        out.seq_off.push_back((int64_t)out.seq.size());
+        out.bundle_start.push_back(b.bstart);
+        for (int i = 0; i < b.count; i++) {
+            const Tx& t = tr.txs[b.first + i];
+            out.tx_global.push_back(b.first + i);
+            uint8_t kind = t.is_templ ? ORFX_TX_TEMPLATE : ((opt.keep_all_cds && t.is_coding) ? ORFX_TX_SKIP : ORFX_TX_QUERY);
+            out.tx_kind.push_back(kind);
+            out.tx_strand.push_back((uint8_t)t.strand);
+            const Chain& c = t.is_templ ? t.cds : t.exons;
+            for (const Seg& s : c) { out.segs.push_back(orfx_seg{s.s, s.e}); out.seg_phase.push_back(t.is_templ ? s.phase : 0); }
+            out.tx_seg_off.push_back((int32_t)out.segs.size());
+            out.tx_cds_start.push_back(t.is_templ ? t.cds_start : 0);
+            out.tx_cds_end.push_back(t.is_templ ? t.cds_end : 0);
+            out.tx_tid_class.push_back(tid_classes.at(t.tid));
+        }
+        out.bundle_tx_off.push_back((int32_t)out.tx_kind.size());
+    }
+}
+
+void shard_bundles(const Transcriptome& tr, const std::vector<int>& active, int n, std::vector<std::vector<int>>& shards) {
+    shards.assign((size_t)n, std::vector<int>());
+    if (n == 1) { shards[0] = active; return; }
+    // cost ~ (#queries x #templates) pair tests + spliced query bases
+    std::vector<std::pair<double, int>> cost;
+    cost.reserve(active.size());
+    for (int bi : active) {
+        const Bundle& b = tr.bundles[bi];
+        double nq = 0, nt = 0, nts = 0;
+        for (int i = 0; i < b.count; i++) { const Tx& t = tr.txs[b.first + i]; if (t.is_templ) nt++; else { nq++; nts += chain_len(t.exons); } }
+        cost.emplace_back(nq * nt * 64.0 + nts + (double)(b.bend - b.bstart + 1) * 0.05, bi);
+    }
+    std::sort(cost.begin(), cost.end(), [](const std::pair<double, int>& a, const std::pair<double, int>& b) { return a.first != b.first ? a.first > b.first : a.second < b.second; });
+    std::vector<double> load((size_t)n, 0.0);
+    for (auto& c : cost) {
+        int best = 0;
+        for (int k = 1; k < n; k++) if (load[k] < load[best]) best = k;
+        load[best] += c.first;
+        shards[best].push_back(c.second);
+    }
+    for (auto& s : shards) std::sort(s.begin(), s.end());   // keep bundle order inside a shard
+}
+
+namespace {
+const char* status_note(int st) {
+    switch (st) {
+        case ORFX_ST_OK: return "-";
+        case ORFX_ST_NO_OVERLAP: return "no-overlap";
+        case ORFX_ST_SEGMENT_LT3: return "segment_len<3";
+        case ORFX_ST_CDS_LT3: return "cds_len<3";
+        case ORFX_ST_NOT_RESCUED: return "not_rescued";
+        case ORFX_ST_MISSING_STOP: return "missing_stop";
+        case ORFX_ST_MISSING_START: return "missing_start";
+        case ORFX_ST_MINLEN: return "minlen";
+        case ORFX_ST_DUP: return "dup";
+    }
+    return "?";
+}
+const char* DASH19 = "-\t-\t-\t-\t-\t-\t-\t-\t-\t-\t-\t-\t-\t-\t-\t-\t-\t-\t-";
+const char* KEEP19 = "-\t-\tkeep_cds\t-\t-\t-\t-\t-\t-\t-\t-\t-\t-\t-\t-\t-\t-\t-\t-";
+
+// The CDS chain of an emitted ORF: the query's exon chain clipped to [cs,ce] with GTF phases
+// (what build_cds / trim_to_pos / extend leave behind; Transcriptome.cpp:92-122, 675-681).
+void set_orf(Tx& q, int cs, int ce) {
+    q.cds.clear();
+    q.cds_start = cs;
+    q.cds_end = ce;
+    for (const Seg& e : q.exons) {
+        if (e.e < cs || e.s > ce) continue;
+        Seg c;
+        c.s = std::max(e.s, cs);
+        c.e = std::min(e.e, ce);
+        q.cds.push_back(c);
+    }
+    assign_phase(q.cds, q.strand, 0);
+}
+
+struct Shard {
+    PackedBatch batch;
+    orfx_ctx* ctx = nullptr;
+    orfx_results res;
+    int rc = 0;
+    std::string err;
+    double ms_pack = 0, ms_eval = 0;
+};
+}  // namespace
+
+int run_orfanage(const Options& opt, const Backend& be) {
+    typedef std::chrono::steady_clock clk;
+    auto t0 = clk::now();
+    if (opt.overhang != 0) throw std::runtime_error("--overhang is not supported by this build (SURVEY.md §8f row 2)");
+    if (opt.clean_templ || opt.rescue) throw std::runtime_error("--cleant / --rescue are not supported by this build (SURVEY.md §8f row 1)");
+    fprintf(stderr, "loading reference genome\n");
+    Fasta fasta;
+    Transcriptome tr;
+    if (!opt.reference.empty()) {
+        fasta.load(opt.reference);
+        if (fasta.write_fai_if_missing(opt.reference)) fprintf(stderr, "FASTA index rebuilt.\n");
+        tr.fasta = &fasta;
+    }
+    fprintf(stderr, "loading reference transcriptomes\n");
+    for (const std::string& k : opt.templates) tr.add(k, true, true);
+    tr.build_cds_chains();
+    if (opt.clean_templ || !opt.reference.empty()) tr.correct_chain_len();
+    fprintf(stderr, "sorting reference transcriptome\n");
+    tr.sort(false);
+    tr.set_cds_as_exons();
+    tr.remove_non_coding();
+    tr.sort(false);
+    fprintf(stderr, "start removing duplicates\n");
+    tr.deduplicate(opt.use_id);
+    fprintf(stderr, "loading query transcriptome\n");
+    tr.add(opt.query, false, false);
+    fprintf(stderr, "bundling transcriptome\n");
+    tr.bundleup(opt.use_id, (uint32_t)opt.overhang);
+    auto t1 = clk::now();
+
+    FILE* gtf = fopen(opt.output.c_str(), "w");
+    if (!gtf) throw std::runtime_error("Cannot open output file: " + opt.output);
+    FILE* stats = nullptr;
+    if (opt.stats_set) {
+        stats = fopen(opt.stats.c_str(), "w");
+        if (!stats) throw std::runtime_error("Cannot open stats file: " + opt.stats);
+        fputs("query_id\ttemplate_id\tsegment\tnotes\tnum_templates\tquery_len\ttemplate_len\tunion_len\tpass\tlen_match\tlen_inframe\t"
+              "len_outframe\tlen_extra\tlen_missing\tlength_pi\tmatch_length_pi\tinframe_length_pi\talignment_match\tstart_match\tstop_match\tpi\n", stats);
+    }
+    static std::vector<char> gtf_buf(1 << 22), stats_buf(1 << 22);
+    setvbuf(gtf, gtf_buf.data(), _IOFBF, gtf_buf.size());
+    if (stats) setvbuf(stats, stats_buf.data(), _IOFBF, stats_buf.size());
+
+    fprintf(stderr, "starting main evaluation\n");
+    const bool mode_all = !opt.modes.empty() && opt.modes[0] == ORFX_MODE_ALL;
+    const bool want_rows = stats != nullptr || mode_all;
+    orfx_params params;
+    fill_params(opt, want_rows, params);
+
+    std::vector<int> active;
+    for (int bi = 0; bi < (int)tr.bundles.size(); bi++) if (tr.bundles[bi].has_template && tr.bundles[bi].has_query) active.push_back(bi);
+    std::map<std::string, int> tid_classes;
+    build_tid_classes(tr, tid_classes);
+
+    const int n_shards = (int)opt.devices.size();
+    std::vector<std::vector<int>> shard_ids;
+    shard_bundles(tr, active, n_shards, shard_ids);
+    std::vector<Shard> shards((size_t)n_shards);
+    auto work = [&](int k) {
+        Shard& s = shards[k];
+        try {
+            auto a = clk::now();
+            pack_bundles(tr, shard_ids[k], opt, tid_classes, s.batch);
+            auto b = clk::now();
+            s.ms_pack = std::chrono::duration<double, std::milli>(b - a).count();
+            memset(&s.res, 0, sizeof s.res);
+            if (s.batch.bundle_ids.empty()) return;
+            s.rc = be.create(&s.ctx, opt.devices[k], &params);
+            if (s.rc) { s.err = be.last_error(); return; }
+            orfx_batch v = s.batch.view();
+            s.rc = be.submit(s.ctx, &v);
+            if (s.rc) { s.err = be.last_error(); return; }
+            s.rc = be.wait(s.ctx, &s.res);
+            if (s.rc) { s.err = be.last_error(); return; }
+            s.ms_eval = std::chrono::duration<double, std::milli>(clk::now() - b).count();
+        } catch (const std::exception& e) { s.rc = -100; s.err = e.what(); }
+    };
+    if (n_shards == 1) work(0);
+    else {
+        std::vector<std::thread> th;
+        for (int k = 0; k < n_shards; k++) th.emplace_back(work, k);
+        for (auto& t : th) t.join();
+    }
+    for (Shard& s : shards) if (s.rc) {
+        for (Shard& z : shards) if (z.ctx) be.destroy(z.ctx);
+        throw std::runtime_error("device evaluation failed: " + s.err);
+    }
+    auto t2 = clk::now();
+
+    // bundle -> (shard, index of its first query among the shard's results)
+    std::vector<int> b_shard(tr.bundles.size(), -1);
+    std::vector<int> b_firstq(tr.bundles.size(), 0);
+    for (int k = 0; k < n_shards; k++) {
+        int qi = 0;
+        const PackedBatch& pb = shards[k].batch;
+        for (size_t j = 0; j < pb.bundle_ids.size(); j++) {
+            b_shard[pb.bundle_ids[j]] = k;
+            b_firstq[pb.bundle_ids[j]] = qi;
+            for (int x = pb.bundle_tx_off[j]; x < pb.bundle_tx_off[j + 1]; x++) if (pb.tx_kind[x] == ORFX_TX_QUERY) qi++;
+        }
+    }
+
+    std::string line;
+    auto stats_score = [&](const orfx_results& r, int64_t row) {
+        fprintf(stats, "%d\t%d\t%d\t%d\t%d\t%d\t%d\t%d\t%d\t%s\t%s\t%s\t0\t%d\t0\t0\n", r.row_qlen[row], r.row_tlen[row], r.row_ulen[row],
+                (int)r.row_pass[row], r.row_match[row], r.row_inframe[row], r.row_outframe[row], r.row_extra[row], r.row_missing[row],
+                float_ostream(r.row_lpi[row]).c_str(), float_ostream(r.row_mlpi[row]).c_str(), float_ostream(r.row_ilpi[row]).c_str(),
+                (int)r.row_start_match[row]);
+    };
+    auto add_found_attrs = [&](Tx& fq, const Tx& t, int duplicity, float ilpi, float lpi, float mlpi, int start_match) {
+        fq.add_attribute("orfanage_status", "1");
+        fq.add_attribute("orfanage_template_source", t.source);
+        fq.add_attribute("orfanage_template", t.tid);
+        fq.add_attribute("orfanage_duplicity", std::to_string(duplicity));
+        fq.add_attribute("orfanage_ilpi", float_to_string(ilpi));
+        fq.add_attribute("orfanage_lpi", float_to_string(lpi));
+        fq.add_attribute("orfanage_mlpi", float_to_string(mlpi));
+        fq.add_attribute("orfanage_start_match", start_match ? "1" : "0");
+        bool stop_match = fq.strand == '+' ? fq.cds_end == t.cds_end : fq.cds_start == t.cds_start;
+        fq.add_attribute("orfanage_stop_match", stop_match ? "1" : "0");
+    };
+
+    for (int bi = 0; bi < (int)tr.bundles.size(); bi++) {
+        const Bundle& b = tr.bundles[bi];
+        const std::string& seqname = tr.seqnames[b.seqid];
+        if (!(b.has_template && b.has_query)) {   // orfanage.cpp:383-432
+            for (int i = 0; i < b.count; i++) {
+                Tx& q = tr.txs[b.first + i];
+                if (q.is_templ) continue;
+                if ((opt.keep_all_cds || opt.keep_cds_if_not_found) && q.is_coding) q.build_cds();
+                line = q.gtf(seqname);
+                fputs(line.c_str(), gtf); fputc('\n', gtf);
+                if (stats) fprintf(stats, "%s\t%s\n", q.tid.c_str(), DASH19);
+            }
+            continue;
+        }
+        const Shard& sh = shards[b_shard[bi]];
+        const orfx_results& r = sh.res;
+        const std::vector<int>& txg = sh.batch.tx_global;
+        int qi = b_firstq[bi];
+        for (int i = 0; i < b.count; i++) {
+            Tx& q = tr.txs[b.first + i];
+            if (q.is_templ) continue;
+            Tx og_q;
+            bool use_og = false;
+            if (opt.keep_cds_if_not_found && q.is_coding) { og_q = q; og_q.build_cds(); use_og = true; }
+            if (opt.keep_all_cds && q.is_coding) {   // orfanage.cpp:458-491
+                q.build_cds();
+                line = q.gtf(seqname);
+                fputs(line.c_str(), gtf); fputc('\n', gtf);
+                if (stats) fprintf(stats, "%s\t%s\n", q.tid.c_str(), KEEP19);
+                continue;
+            }
+            q.remove_cds();
+            q.cds_source = "ORFanage";
+            const orfx_best& best = r.best[qi++];
+            if (best.t_tx < 0) {   // orfanage.cpp:662-691
+                Tx* out = &q;
+                if (use_og) { out = &og_q; out->build_cds(); }
+                out->add_attribute("orfanage_status", "0");
+                line = out->gtf(seqname);
+                fputs(line.c_str(), gtf); fputc('\n', gtf);
+                if (stats) fprintf(stats, "%s\t%s\n", out->tid.c_str(), KEEP19);
+                continue;
+            }
+            if (!mode_all) {   // orfanage.cpp:753-791
+                Tx fq = q;
+                set_orf(fq, best.cds_start, best.cds_end);
+                const Tx& t = tr.txs[txg[best.t_tx]];
+                add_found_attrs(fq, t, best.duplicity, best.ilpi, best.lpi, best.mlpi, best.start_match);
+                line = fq.gtf(seqname);
+                fputs(line.c_str(), gtf); fputc('\n', gtf);
+            }
+            if (!want_rows) continue;
+            // walk the key groups in print order (orfanage.cpp:693-752, 793-814)
+            int64_t o0 = best.row_off, o1 = best.row_off + best.n_rows;
+            for (int64_t o = o0; o < o1;) {
+                int64_t front = r.print_order[o];
+                int ks = r.row_cds_start[front], ke = r.row_cds_end[front];
+                int64_t oe = o;
+                while (oe < o1 && r.row_cds_start[r.print_order[oe]] == ks && r.row_cds_end[r.print_order[oe]] == ke) oe++;
+                std::string tid = q.tid;
+                if (mode_all) tid += "." + std::to_string(ks) + "-" + std::to_string(ke);
+                const char* front_note = nullptr;
+                if (mode_all) {
+                    if (r.row_pass[front]) {
+                        Tx fq = q;
+                        set_orf(fq, ks, ke);
+                        fq.tid = tid;
+                        const Tx& t = tr.txs[txg[r.row_t_tx[front]]];
+                        add_found_attrs(fq, t, r.row_n_dup[front], r.row_ilpi[front], r.row_lpi[front], r.row_mlpi[front], r.row_start_match[front]);
+                        front_note = front == best.best_row ? "best_gtf" : "gtf";
+                        line = fq.gtf(seqname);
+                        fputs(line.c_str(), gtf); fputc('\n', gtf);
+                    }
+                } else if (front == best.best_row) front_note = "best_gtf";
+                if (stats) {
+                    for (int64_t k = o; k < oe; k++) {
+                        int64_t row = r.print_order[k];
+                        const Tx& t = tr.txs[txg[r.row_t_tx[row]]];
+                        const char* note = (k == o && front_note) ? front_note : status_note(r.row_status[row]);
+                        if (r.row_status[row] == ORFX_ST_NO_OVERLAP)
+                            fprintf(stats, "%s\t%s\t4294967295-4294967295\t%s\t%d\t", tid.c_str(), t.tid.c_str(), note, r.row_n_dup[row] + 1);
+                        else
+                            fprintf(stats, "%s\t%s\t%u-%u\t%s\t%d\t", tid.c_str(), t.tid.c_str(), (uint32_t)r.row_seg_start[row], (uint32_t)r.row_seg_end[row], note, r.row_n_dup[row] + 1);
+                        stats_score(r, row);
+                    }
+                }
+                o = oe;
+            }
+        }
+    }
+    fclose(gtf);
+    if (stats) fclose(stats);
+    for (Shard& s : shards) if (s.ctx) { be.release(s.ctx); be.destroy(s.ctx); }
+    fprintf(stderr, "Done\n");
+    if (opt.timing) {
+        auto t3 = clk::now();
+        auto ms = [](clk::time_point a, clk::time_point b) { return std::chrono::duration<double, std::milli>(b - a).count(); };
+        fprintf(stderr, "[timing] load+prep %.1f ms, evaluate %.1f ms, emit %.1f ms\n", ms(t0, t1), ms(t1, t2), ms(t2, t3));
+        for (int k = 0; k < n_shards; k++)
+            fprintf(stderr, "[timing] shard %d: %zu bundles, pack %.1f ms, submit+wait %.1f ms (h2d %.2f, kernels %.2f, d2h %.2f)\n", k,
+                    shards[k].batch.bundle_ids.size(), shards[k].ms_pack, shards[k].ms_eval, shards[k].res.ms_h2d, shards[k].res.ms_kernels, shards[k].res.ms_d2h);
+    }
+    return 0;
+}
+
+}  // namespace orfx

@@ -1,0 +1,440 @@
+// Interval chains, transcripts, GTF loading, template preparation and locus bundling.
+// Host mirror of the reference's Transcriptome layer; each function cites what it replaces.
+#include "orfx_host.h"
+#include <algorithm>
+#include <cstring>
+#include <fcntl.h>
+#include <sys/mman.h>
+#include <sys/stat.h>
+#include <unistd.h>
+
+namespace orfx {
+
+int chain_len(const Chain& c) {
+    int l = 0;
+    for (const Seg& s : c) l += (int)(uint32_t)(s.e + 1 - s.s);
+    return l;
+}
+
+int genome2nt(const Chain& c, int g, char strand) {
+    int acc = 0;
+    bool found = false;
+    for (const Seg& s : c) {
+        if (g >= s.s && g <= s.e) { acc += g - s.s; found = true; break; }
+        acc += s.len();
+    }
+    if (!found) return -1;
+    return strand == '+' ? acc : (chain_len(c) - acc) - 1;
+}
+
+int nt2genome(const Chain& c, int off, char strand) {
+    const int n = (int)c.size();
+    if (off >= 0) {
+        if (strand == '+') {
+            for (int i = 0; i < n; i++) { int l = c[i].len(); if (off < l) return c[i].s + off; off -= l; }
+        } else {
+            for (int i = n - 1; i >= 0; i--) { int l = c[i].len(); if (off < l) return c[i].e - off; off -= l; }
+        }
+    }
+    // over-requested (or negative, which the reference compares as unsigned): last position
+    return strand == '+' ? c.back().e : c.front().s;
+}
+
+void assign_phase(Chain& c, char strand, int start_phase) {
+    int acc = start_phase;
+    if (strand == '-') {
+        for (int i = (int)c.size() - 1; i >= 0; i--) { c[i].phase = (int8_t)((3 - acc % 3) % 3); acc += c[i].e - c[i].s + 1; }
+    } else {
+        for (Seg& s : c) { s.phase = (int8_t)((3 - acc % 3) % 3); acc += s.e - s.s + 1; }
+    }
+}
+
+void cut_chain(Chain& c, int lo, int hi) {
+    if (c.empty()) return;
+    if (lo <= c.front().s && hi >= c.back().e) return;
+    Chain tmp;
+    for (Seg s : c) {
+        if (s.s <= lo && s.e >= lo) { s.s = lo; s.phase = -1; }
+        if (s.e >= hi) { s.e = hi; s.phase = -1; tmp.push_back(s); break; }
+        if (s.e < lo || s.s > hi) continue;
+        tmp.push_back(s);
+    }
+    c.swap(tmp);
+}
+
+// ---- Tx -------------------------------------------------------------------------------------
+void Tx::build_cds() {
+    cds.clear();
+    if (cds_start == 0 && cds_end == 0) return;
+    if (cds_phase != 0) {
+        if (strand == '+') cds_start = nt2genome(exons, genome2nt(exons, cds_start, strand) + cds_phase, strand);
+        else cds_end = nt2genome(exons, genome2nt(exons, cds_end, strand) + cds_phase, strand);
+        cds_phase = 0;
+    }
+    for (Seg e : exons) {
+        if (cds_end < e.s || cds_start > e.e) continue;
+        if (cds_start >= e.s && cds_start <= e.e) e.s = cds_start;
+        if (cds_end >= e.s && cds_end <= e.e) e.e = cds_end;
+        e.phase = 0;
+        cds.push_back(e);
+    }
+    assign_phase(cds, strand, 0);
+}
+
+void Tx::correct_chain_len() {
+    int clen = chain_len(cds);
+    int num_trim = clen % 3;
+    if (num_trim > 0) {
+        int a = nt2genome(cds, 0, strand);
+        int b = nt2genome(cds, clen - num_trim - 1, strand);
+        cut_chain(cds, std::min(a, b), std::max(a, b));
+        assign_phase(cds, strand, 0);
+        cds_start = cds.front().s;
+        cds_end = cds.back().e;
+    }
+}
+
+void Tx::remove_cds() {
+    cds.clear();
+    cds_start = cds_end = cds_phase = 0;
+    is_coding = false;
+}
+
+std::string Tx::gtf(const std::string& seqname) const {
+    std::string o;
+    o.reserve(256 + 96 * (exons.size() + cds.size()));
+    char num[64];
+    auto coords = [&](int s, int e) { snprintf(num, sizeof num, "%d\t%d", s, e); o += num; };
+    o += seqname; o += '\t'; o += source; o += "\ttranscript\t";
+    coords(start(), end());
+    o += "\t.\t"; o += strand; o += "\t.\ttranscript_id \""; o += tid; o += "\"; gene_id \""; o += gid; o += "\"; ";
+    {
+        std::string a;
+        for (const auto& kv : attrs) { a += kv.first; a += " \""; a += kv.second; a += "\"; "; }
+        if (!a.empty()) a.pop_back();
+        o += a;
+    }
+    o += '\n';
+    for (const Seg& e : exons) {
+        o += seqname; o += '\t'; o += source; o += "\texon\t";
+        coords(e.s, e.e);
+        o += "\t.\t"; o += strand; o += "\t.\ttranscript_id \""; o += tid; o += "\";\n";
+    }
+    for (const Seg& c : cds) {
+        o += seqname; o += '\t'; o += cds_source; o += "\tCDS\t";
+        coords(c.s, c.e);
+        o += "\t.\t"; o += strand; o += '\t';
+        snprintf(num, sizeof num, "%u", (uint32_t)(int32_t)c.phase);
+        o += num;
+        o += "\ttranscript_id \""; o += tid; o += "\";\n";
+    }
+    o.pop_back();   // the caller appends the record-terminating newline (std::endl in the reference)
+    return o;
+}
+
+bool tx_less(const Tx& a, const Tx& b) {
+    if (a.seqid != b.seqid) return a.seqid < b.seqid;
+    if (a.strand != b.strand) return a.strand < b.strand;
+    if (a.start() != b.start()) return a.start() < b.start();
+    if (a.end() != b.end()) return a.end() < b.end();
+    return false;
+}
+
+bool tx_same(const Tx& a, const Tx& b) {
+    if (a.seqid != b.seqid || a.strand != b.strand || a.start() != b.start() || a.end() != b.end()) return false;
+    if (a.exons.size() != b.exons.size()) return false;
+    for (size_t i = 0; i < a.exons.size(); i++)
+        if (a.exons[i].s != b.exons[i].s || a.exons[i].e != b.exons[i].e || a.exons[i].phase != b.exons[i].phase) return false;
+    return true;
+}
+
+// ---- GTF reader --------------------------------------------------------------------------------
+// Accepts `transcript`/`mRNA`, `exon` and `CDS` rows keyed by transcript_id; transcripts come out
+// in order of first appearance, exons ascending.  CDS-only records use their CDS rows as exons.
+namespace {
+struct Span { const char* p; size_t n; };
+inline bool eq(const Span& s, const char* lit) { size_t l = strlen(lit); return s.n == l && memcmp(s.p, lit, l) == 0; }
+
+void parse_attr_column(const char* p, const char* end, std::vector<std::pair<Span, Span>>& out) {
+    out.clear();
+    while (p < end) {
+        while (p < end && (*p == ' ' || *p == ';' || *p == '\t')) p++;
+        if (p >= end) break;
+        const char* k0 = p;
+        while (p < end && *p != ' ' && *p != '\t' && *p != ';') p++;
+        Span key{k0, (size_t)(p - k0)};
+        while (p < end && (*p == ' ' || *p == '\t')) p++;
+        Span val{p, 0};
+        if (p < end && *p == '"') {
+            p++;
+            const char* v0 = p;
+            while (p < end && *p != '"') p++;
+            val = Span{v0, (size_t)(p - v0)};
+            if (p < end) p++;
+        } else {
+            const char* v0 = p;
+            while (p < end && *p != ';') p++;
+            const char* v1 = p;
+            while (v1 > v0 && v1[-1] == ' ') v1--;
+            val = Span{v0, (size_t)(v1 - v0)};
+        }
+        out.push_back(std::make_pair(key, val));
+    }
+}
+}  // namespace
+
+void read_gtf(const std::string& path, std::vector<GtfRecord>& out) {
+    int fd = open(path.c_str(), O_RDONLY);
+    if (fd < 0) throw std::runtime_error("Couldn't open the GTF file: " + path);
+    struct stat st;
+    fstat(fd, &st);
+    size_t size = (size_t)st.st_size;
+    const char* data = size ? (const char*)mmap(nullptr, size, PROT_READ, MAP_PRIVATE, fd, 0) : nullptr;
+    if (size && data == MAP_FAILED) { close(fd); throw std::runtime_error("Couldn't map the GTF file: " + path); }
+
+    struct Work { std::vector<std::pair<uint32_t, uint32_t>> cds; std::vector<char> frames; };
+    std::vector<Work> work;
+    std::map<std::string, size_t> by_id;
+    std::vector<std::pair<Span, Span>> av;
+    size_t base = out.size();
+    const char* p = data;
+    const char* fend = data + size;
+    std::string tid;
+    size_t last = (size_t)-1;   // rows of one transcript are usually consecutive
+    while (p < fend) {
+        const char* eol = (const char*)memchr(p, '\n', (size_t)(fend - p));
+        if (!eol) eol = fend;
+        const char* le = eol;
+        while (le > p && (le[-1] == '\r')) le--;
+        if (le > p && *p != '#') {
+            Span col[9];
+            int nc = 0;
+            const char* q = p;
+            while (nc < 9) {
+                const char* t = nc < 8 ? (const char*)memchr(q, '\t', (size_t)(le - q)) : nullptr;
+                if (!t) { col[nc++] = Span{q, (size_t)(le - q)}; break; }
+                col[nc++] = Span{q, (size_t)(t - q)};
+                q = t + 1;
+            }
+            if (nc == 9) {
+                bool is_tx = eq(col[2], "transcript") || eq(col[2], "mRNA");
+                bool is_exon = eq(col[2], "exon");
+                bool is_cds = eq(col[2], "CDS");
+                if (is_tx || is_exon || is_cds) {
+                    parse_attr_column(col[8].p, col[8].p + col[8].n, av);
+                    const Span* tspan = nullptr;
+                    const Span* gspan = nullptr;
+                    for (auto& kv : av) {
+                        if (!tspan && eq(kv.first, "transcript_id")) tspan = &kv.second;
+                        else if (!gspan && eq(kv.first, "gene_id")) gspan = &kv.second;
+                    }
+                    if (tspan && tspan->n) {
+                        size_t ri;
+                        if (last != (size_t)-1 && out[last].tid.size() == tspan->n && memcmp(out[last].tid.data(), tspan->p, tspan->n) == 0) ri = last;
+                        else {
+                            tid.assign(tspan->p, tspan->n);
+                            auto it = by_id.find(tid);
+                            if (it == by_id.end()) {
+                                ri = out.size();
+                                by_id[tid] = ri;
+                                out.emplace_back();
+                                work.emplace_back();
+                                GtfRecord& r = out.back();
+                                r.tid = tid;
+                                r.seqname.assign(col[0].p, col[0].n);
+                                r.source.assign(col[1].p, col[1].n);
+                                r.strand = col[6].n ? col[6].p[0] : '.';
+                            } else ri = it->second;
+                            last = ri;
+                        }
+                        GtfRecord& r = out[ri];
+                        Work& w = work[ri - base];
+                        if (gspan && !r.has_gid) { r.has_gid = true; r.gid.assign(gspan->p, gspan->n); }
+                        uint32_t s = (uint32_t)strtoul(col[3].p, nullptr, 10);
+                        uint32_t e = (uint32_t)strtoul(col[4].p, nullptr, 10);
+                        if (s > e) std::swap(s, e);
+                        if (is_tx) {
+                            r.source.assign(col[1].p, col[1].n);
+                            for (auto& kv : av) {
+                                if (eq(kv.first, "transcript_id")) continue;
+                                r.attrs.emplace_back(std::string(kv.first.p, kv.first.n), std::string(kv.second.p, kv.second.n));
+                            }
+                        } else if (is_exon) {
+                            r.exons.emplace_back(s, e);
+                        } else {
+                            r.has_cds = true;
+                            w.cds.emplace_back(s, e);
+                            w.frames.push_back(col[7].n ? col[7].p[0] : '.');
+                        }
+                    }
+                }
+            }
+        }
+        p = eol + 1;
+    }
+    if (data) munmap((void*)data, size);
+    close(fd);
+    for (size_t i = base; i < out.size(); i++) {
+        GtfRecord& r = out[i];
+        Work& w = work[i - base];
+        if (r.exons.empty()) r.exons = w.cds;
+        std::sort(r.exons.begin(), r.exons.end());
+        if (r.has_cds) {
+            uint32_t mn = UINT32_MAX, mx = 0;
+            size_t imn = 0, imx = 0;
+            for (size_t k = 0; k < w.cds.size(); k++) {
+                if (w.cds[k].first < mn) { mn = w.cds[k].first; imn = k; }
+                if (w.cds[k].second > mx) { mx = w.cds[k].second; imx = k; }
+            }
+            r.cd_start = mn;
+            r.cd_end = mx;
+            r.cd_phase = r.strand == '-' ? w.frames[imx] : w.frames[imn];
+        }
+    }
+}
+
+// ---- Transcriptome -----------------------------------------------------------------------------
+void Transcriptome::add(const std::string& gtf_path, bool is_templ, bool coding_only) {
+    bundles.clear();
+    std::vector<GtfRecord> recs;
+    read_gtf(gtf_path, recs);
+    for (const GtfRecord& r : recs) {   // Transcriptome::load_seqids, cpp:855-865
+        auto ins = seqids_.insert(std::make_pair(r.seqname, (int)seqnames.size()));
+        if (ins.second) seqnames.push_back(r.seqname);
+    }
+    for (const GtfRecord& r : recs) {
+        if (coding_only && !r.has_cds) continue;
+        if (r.exons.empty()) continue;
+        Tx t;   // TX::TX(GffObj*), cpp:11-82
+        if (r.has_cds) {
+            t.is_coding = true;
+            t.cds_start = (int)r.cd_start;
+            t.cds_end = (int)r.cd_end;
+            switch (r.cd_phase) {
+                case '0': t.cds_phase = 0; break;
+                case '1': t.cds_phase = 1; break;
+                case '2': t.cds_phase = 2; break;
+                case '3': t.cds_phase = 3; break;
+                case '.': t.cds_phase = 0; break;
+                default: throw std::runtime_error("Unknown CDS phase for the initial segment");
+            }
+        }
+        t.is_templ = is_templ;
+        t.id = (int)txs.size();
+        t.tid = r.tid;
+        t.gid = r.has_gid ? r.gid : r.tid;
+        t.seqid = seqids_[r.seqname];
+        t.strand = r.strand;
+        t.source = r.source;
+        t.cds_source = r.source;
+        for (auto& e : r.exons) { Seg s; s.s = (int)e.first; s.e = (int)e.second; s.phase = 0; t.exons.push_back(s); }
+        bool tr_id = false;
+        for (const auto& kv : r.attrs) {
+            if (kv.second.empty()) continue;
+            std::string name = kv.first;
+            if (name == "transcriptID") { if (tr_id) continue; tr_id = true; }
+            if (name == "transcript_id" && !tr_id) { name = "transcriptID"; tr_id = true; }
+            if (name == "geneID" || name == "gene_id") continue;
+            if (!t.attrs.insert(std::make_pair(name, kv.second)).second)
+                throw std::runtime_error("Attribute: " + name + " already exists");
+        }
+        txs.push_back(std::move(t));
+    }
+}
+
+void Transcriptome::build_cds_chains() {
+    for (Tx& t : txs) if (t.is_coding && t.is_templ) t.build_cds();
+}
+void Transcriptome::correct_chain_len() {
+    for (Tx& t : txs) if (t.is_coding && t.is_templ) t.correct_chain_len();
+}
+void Transcriptome::sort(bool use_id) {
+    // std::sort on purpose: the reference sorts with libstdc++'s introsort, whose order among
+    // equal keys decides the bundle-internal transcript order (SURVEY.md §7 hard parts).
+    if (use_id) {
+        std::sort(txs.begin(), txs.end(), [](const Tx& a, const Tx& b) {
+            if (a.seqid != b.seqid) return a.seqid < b.seqid;
+            if (a.strand != b.strand) return a.strand < b.strand;
+            if (a.gid != b.gid) return a.gid < b.gid;
+            return tx_less(a, b);
+        });
+    } else {
+        std::sort(txs.begin(), txs.end(), tx_less);
+    }
+}
+void Transcriptome::set_cds_as_exons() {
+    for (Tx& t : txs) {
+        if (t.is_coding && !t.cds.empty()) {
+            t.exons = t.cds;
+            for (Seg& s : t.exons) s.phase = 0;
+        }
+    }
+}
+void Transcriptome::remove_non_coding() {
+    txs.erase(std::remove_if(txs.begin(), txs.end(), [](const Tx& t) { return !t.is_coding; }), txs.end());
+}
+size_t Transcriptome::deduplicate(bool use_id) {
+    size_t before = txs.size();
+    if (use_id) txs.erase(std::unique(txs.begin(), txs.end(), [](const Tx& a, const Tx& b) { return a.gid == b.gid && tx_same(a, b); }), txs.end());
+    else txs.erase(std::unique(txs.begin(), txs.end(), tx_same), txs.end());
+    return before - txs.size();
+}
+
+size_t Transcriptome::bundleup(bool use_id, uint32_t overhang) {
+    sort(use_id);
+    if (fasta) {
+        std::vector<Tx> valid;
+        valid.reserve(txs.size());
+        int cur = -1;
+        bool ok = false;
+        for (Tx& t : txs) {
+            if (t.seqid != cur) { cur = t.seqid; ok = fasta->get(seqnames[cur]) != nullptr; }
+            if (!ok) {
+                if (!t.is_templ) throw std::runtime_error("Reference FASTA is missing sequence for query: " + seqnames[cur]);
+            } else valid.push_back(std::move(t));
+        }
+        txs.swap(valid);
+    }
+    bundles.clear();
+    if (txs.empty()) return 0;
+    auto close_bundle = [&](Bundle& b) {
+        if (!fasta) return;
+        const std::string* seq = fasta->get(seqnames[b.seqid]);
+        int seqlen = seq ? (int)seq->size() : 0;
+        int ns = std::max(b.bstart - (int)overhang, 1);
+        uint32_t ne = std::min((uint32_t)b.bend + overhang, (uint32_t)seqlen);
+        b.bstart = std::min(b.bstart, ns); b.bend = std::max(b.bend, ns);
+        b.bstart = std::min(b.bstart, (int)ne); b.bend = std::max(b.bend, (int)ne);
+        uint32_t blen = (uint32_t)(b.bend + 1) - (uint32_t)b.bstart;
+        if ((int64_t)b.bstart + (int64_t)blen - 1 > (int64_t)seqlen || b.bstart < 0)
+            throw std::runtime_error("Bundle + stop codon extends past the end of the reference sequence");
+    };
+    Bundle cur;
+    cur.first = 0;
+    for (int i = 0; i < (int)txs.size(); i++) {
+        const Tx& t = txs[i];
+        bool can = cur.count == 0;
+        if (!can) {
+            if (use_id) can = cur.gid == t.gid;
+            else can = cur.seqid == t.seqid && cur.strand == t.strand && (t.start() <= cur.bend && t.end() >= cur.bstart);
+        }
+        if (!can) {
+            close_bundle(cur);
+            bundles.push_back(cur);
+            cur = Bundle();
+            cur.first = i;
+        }
+        cur.count++;
+        cur.seqid = t.seqid;
+        cur.strand = t.strand;
+        cur.bstart = std::min(cur.bstart, t.start());
+        cur.bend = std::max(cur.bend, t.end());
+        cur.gid = use_id ? t.gid : std::string();
+        if (t.is_templ) cur.has_template = true; else cur.has_query = true;
+    }
+    close_bundle(cur);
+    bundles.push_back(cur);
+    return bundles.size();
+}
+
+}  // namespace orfx
