@@ -1,0 +1,93 @@
+// Device helpers on CSR interval chains and on the codon-scan bit masks.
+#pragma once
+#include "orfx_device.cuh"
+
+namespace orfx {
+
+// One transcript's chain: segments ascending by genomic coordinate, `cum` = bases before each segment.
+struct TxView {
+    const orfx_seg* segs;
+    const int32_t* cum;
+    int n;        // segments
+    int L;        // spliced length
+    bool plus;    // strand == '+'; every other strand byte is handled as the reverse strand, as the
+                  // reference does (`strand == '+' ? ... : ...` throughout Transcriptome.cpp)
+};
+
+__device__ __forceinline__ TxView tx_view(const DevBatch& B, int tx) {
+    TxView v;
+    int s0 = B.tx_seg_off[tx];
+    v.segs = B.segs + s0;
+    v.cum = B.seg_cum + s0;
+    v.n = B.tx_seg_off[tx + 1] - s0;
+    v.L = B.tx_len[tx];
+    v.plus = B.tx_strand[tx] == '+';
+    return v;
+}
+
+// index of the segment containing genomic position g, or -1
+__device__ __forceinline__ int seg_of_genomic(const TxView& v, int g) {
+    int lo = 0, hi = v.n - 1;
+    if (hi < 0 || g < v.segs[0].start) return -1;
+    while (lo < hi) {
+        int mid = (lo + hi + 1) >> 1;
+        if (v.segs[mid].start <= g) lo = mid; else hi = mid - 1;
+    }
+    return g <= v.segs[lo].end ? lo : -1;
+}
+// genomic -> transcript-order offset (CHAIN::genome2nt, Transcriptome.h:447-462); -1 when not exonic
+__device__ __forceinline__ int g2t(const TxView& v, int g) {
+    int k = seg_of_genomic(v, g);
+    if (k < 0) return -1;
+    int u = v.cum[k] + (g - v.segs[k].start);
+    return v.plus ? u : v.L - 1 - u;
+}
+// index of the segment holding genomic-order spliced offset u (0 <= u < L)
+__device__ __forceinline__ int seg_of_offset(const TxView& v, int u) {
+    int lo = 0, hi = v.n - 1;
+    while (lo < hi) {
+        int mid = (lo + hi + 1) >> 1;
+        if (v.cum[mid] <= u) lo = mid; else hi = mid - 1;
+    }
+    return lo;
+}
+// transcript-order offset -> genomic (CHAIN::nt2genome, Transcriptome.h:463-481); p must be in [0,L)
+__device__ __forceinline__ int t2g(const TxView& v, int p) {
+    int u = v.plus ? p : v.L - 1 - p;
+    int k = seg_of_offset(v, u);
+    return v.segs[k].start + (u - v.cum[k]);
+}
+
+// ---- in-frame scans over a transcript's bit mask (bit p = codon starting at spliced position p) ----
+__device__ __forceinline__ uint32_t frame_pattern(int word, int residue) {
+    // bits b of word `word` with (32*word + b) % 3 == residue
+    int s = (residue - (word * 2) % 3 + 3) % 3;   // 32 == 2 (mod 3)
+    return s == 0 ? 0x49249249u : (s == 1 ? 0x92492492u : 0x24924924u);
+}
+__device__ __forceinline__ bool mask_bit(const uint32_t* m, int p) { return (m[p >> 5] >> (p & 31)) & 1u; }
+// smallest q >= p with q == p (mod 3), q < L and bit set; -1 when none
+__device__ __forceinline__ int next_inframe(const uint32_t* m, int p, int L) {
+    if (p < 0 || p >= L) return -1;
+    const int r = p % 3, nw = (L + 31) >> 5;
+    int w = p >> 5;
+    uint32_t x = m[w] & frame_pattern(w, r) & (0xFFFFFFFFu << (p & 31));
+    while (true) {
+        if (x) { int q = (w << 5) + __ffs(x) - 1; return q < L ? q : -1; }
+        if (++w >= nw) return -1;
+        x = m[w] & frame_pattern(w, r);
+    }
+}
+// largest q <= p with q == p (mod 3), q >= 0 and bit set; -1 when none
+__device__ __forceinline__ int prev_inframe(const uint32_t* m, int p) {
+    if (p < 0) return -1;
+    const int r = p % 3;
+    int w = p >> 5;
+    uint32_t x = m[w] & frame_pattern(w, r) & (0xFFFFFFFFu >> (31 - (p & 31)));
+    while (true) {
+        if (x) return (w << 5) + 31 - __clz(x);
+        if (--w < 0) return -1;
+        x = m[w] & frame_pattern(w, r);
+    }
+}
+
+}  // namespace orfx

@@ -1,0 +1,459 @@
+// C-ABI of the device library (include/orfx.h): context, buffers, stream orchestration.
+// One context = one GPU, one stream.  No CPU fallback: every entry point that computes needs a
+// CUDA device, and orfx_create fails without one.
+#include "orfx_device.cuh"
+
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+
+namespace orfx {
+int launch_exclusive_scan(const int64_t* in, int64_t* out, int64_t* tmp, int64_t n, cudaStream_t s);
+int64_t scan_tmp_elems(int64_t n);
+int launch_prep(const DevBatch& B, int64_t* cnt_q, int64_t* cnt_words, int64_t* cnt_tiles, int64_t* scan_tmp, cudaStream_t s);
+int launch_fill_tiles(const DevBatch& B, cudaStream_t s);
+int launch_count_rows(const DevBatch& B, int64_t* cnt, int64_t* scan_tmp, cudaStream_t s);
+int launch_fill_rows(const DevBatch& B, const DevRows& R, int n_queries, cudaStream_t s);
+int launch_rescue_score(const DevBatch& B, const DevRows& R, const orfx_params& P, cudaStream_t s);
+int launch_select(const DevBatch& B, const DevRows& R, const orfx_params& P, int n_queries, orfx_best* best_out, int32_t* ord_scratch, cudaStream_t s);
+void launch_codon_scan(const DevBatch& B, int64_t n_tiles, int n_sm, cudaStream_t stream);
+int align_batch_device(int device, cudaStream_t stream, const uint8_t* aa, const int64_t* off, int64_t n_seq, const int32_t* pair_q,
+                       const int32_t* pair_t, int64_t n_pairs, int gapo, int gape, orfx_aln_out* out, double* cells, float* ms, std::string& err);
+}  // namespace orfx
+
+using namespace orfx;
+
+namespace {
+
+thread_local std::string g_err;
+
+int fail(int code, const std::string& msg) { g_err = msg; return code; }
+#define CU(call)                                                                                   \
+    do {                                                                                           \
+        cudaError_t e_ = (call);                                                                   \
+        if (e_ != cudaSuccess) return fail(ORFX_E_CUDA, std::string(#call) + ": " + cudaGetErrorString(e_)); \
+    } while (0)
+
+// grow-only device buffer
+struct DBuf {
+    void* p = nullptr;
+    size_t cap = 0;
+    cudaError_t ensure(size_t bytes) {
+        if (bytes <= cap) return cudaSuccess;
+        if (p) cudaFree(p);
+        p = nullptr; cap = 0;
+        size_t want = bytes + bytes / 8 + 256;
+        cudaError_t e = cudaMalloc(&p, want);
+        if (e == cudaSuccess) cap = want;
+        return e;
+    }
+    void free_() { if (p) cudaFree(p); p = nullptr; cap = 0; }
+    template <class T> T* as() const { return reinterpret_cast<T*>(p); }
+};
+// grow-only pinned host buffer
+struct HBuf {
+    void* p = nullptr;
+    size_t cap = 0;
+    cudaError_t ensure(size_t bytes) {
+        if (bytes <= cap) return cudaSuccess;
+        if (p) cudaFreeHost(p);
+        p = nullptr; cap = 0;
+        size_t want = bytes + bytes / 8 + 256;
+        cudaError_t e = cudaMallocHost(&p, want);
+        if (e == cudaSuccess) cap = want;
+        return e;
+    }
+    void free_() { if (p) cudaFreeHost(p); p = nullptr; cap = 0; }
+    template <class T> T* as() const { return reinterpret_cast<T*>(p); }
+};
+
+enum { ST_PREP = 0, ST_COUNT, ST_SCAN, ST_FILL, ST_RESCUE, ST_SELECT, ST_N };
+const char* STAGE_NAME[ST_N] = {"prep", "count_rows", "codon_scan", "fill_rows", "rescue_score", "select"};
+
+}  // namespace
+
+struct orfx_ctx {
+    int device = 0;
+    int n_sm = 148;
+    cudaStream_t stream = nullptr;
+    orfx_params P;
+    // inputs
+    DBuf d_seq, d_seq_off, d_bstart, d_btx_off, d_kind, d_strand, d_seg_off, d_cds_s, d_cds_e, d_tid, d_segs, d_phase;
+    // derived
+    DBuf d_seg_cum, d_tx_len, d_tx_bundle, d_mask_off, d_tile_off, d_q_off, d_q_list, d_row_off, d_tile_tx, d_stop, d_start;
+    DBuf d_cnt_q, d_cnt_words, d_cnt_tiles, d_cnt_rows, d_scan_tmp, d_ord;
+    // rows
+    DBuf r_i32[16], r_f32[3], r_u8[3], r_order, d_best;
+    HBuf h_totals, h_best, h_i32[16], h_f32[3], h_u8[3], h_order;
+    DevBatch B;
+    DevRows R;
+    bool resident = false, pending = false, have_results = false;
+    int64_t n_queries = 0, n_rows = 0, n_tiles = 0, n_words = 0;
+    cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};
+    cudaEvent_t st_ev[ST_N][2];
+    float st_ms[ST_N];
+    int n_launches = 0;
+};
+
+namespace {
+
+int upload_batch(orfx_ctx* c, const orfx_batch* b) {
+    if (!b) return fail(ORFX_E_INVALID, "null batch");
+    if (b->n_bundles < 0 || b->n_tx < 0 || b->n_segs < 0) return fail(ORFX_E_INVALID, "negative batch size");
+    if (c->P.has_reference && b->n_bundles > 0 && !b->seq) return fail(ORFX_E_INVALID, "params.has_reference set but batch.seq is NULL");
+    cudaStream_t s = c->stream;
+    const size_t nb = (size_t)b->n_bundles, nt = (size_t)b->n_tx, ns = (size_t)b->n_segs;
+    const size_t seqb = c->P.has_reference ? (size_t)b->seq_bytes : 0;
+    CU(c->d_seq.ensure(seqb + 64));
+    CU(c->d_seq_off.ensure((nb + 1) * 8));
+    CU(c->d_bstart.ensure(nb * 4 + 4));
+    CU(c->d_btx_off.ensure((nb + 1) * 4));
+    CU(c->d_kind.ensure(nt + 4));
+    CU(c->d_strand.ensure(nt + 4));
+    CU(c->d_seg_off.ensure((nt + 1) * 4));
+    CU(c->d_cds_s.ensure(nt * 4 + 4));
+    CU(c->d_cds_e.ensure(nt * 4 + 4));
+    CU(c->d_tid.ensure(nt * 4 + 4));
+    CU(c->d_segs.ensure(ns * 8 + 8));
+    CU(c->d_phase.ensure(ns + 4));
+    auto cp = [&](DBuf& d, const void* src, size_t bytes) -> cudaError_t {
+        if (bytes == 0) return cudaSuccess;
+        return cudaMemcpyAsync(d.p, src, bytes, cudaMemcpyHostToDevice, s);
+    };
+    if (seqb) {
+        CU(cp(c->d_seq, b->seq, seqb));
+        CU(cudaMemsetAsync((char*)c->d_seq.p + seqb, 0, 64, s));   // the last aligned 16-byte chunk may read past the end
+    }
+    CU(cp(c->d_seq_off, b->seq_off, (nb + 1) * 8));
+    CU(cp(c->d_bstart, b->bundle_start, nb * 4));
+    CU(cp(c->d_btx_off, b->bundle_tx_off, (nb + 1) * 4));
+    CU(cp(c->d_kind, b->tx_kind, nt));
+    CU(cp(c->d_strand, b->tx_strand, nt));
+    CU(cp(c->d_seg_off, b->tx_seg_off, (nt + 1) * 4));
+    CU(cp(c->d_cds_s, b->tx_cds_start, nt * 4));
+    CU(cp(c->d_cds_e, b->tx_cds_end, nt * 4));
+    CU(cp(c->d_tid, b->tx_tid_class, nt * 4));
+    CU(cp(c->d_segs, b->segs, ns * 8));
+    CU(cp(c->d_phase, b->seg_phase, ns));
+    // derived buffers whose size is known now
+    CU(c->d_seg_cum.ensure(ns * 4 + 4));
+    CU(c->d_tx_len.ensure(nt * 4 + 4));
+    CU(c->d_tx_bundle.ensure(nt * 4 + 4));
+    CU(c->d_mask_off.ensure((nt + 1) * 8));
+    CU(c->d_tile_off.ensure((nt + 1) * 8));
+    CU(c->d_q_off.ensure((nt + 1) * 8));
+    CU(c->d_q_list.ensure(nt * 4 + 4));
+    CU(c->d_row_off.ensure((nt + 1) * 8));
+    CU(c->d_cnt_q.ensure(nt * 8 + 8));
+    CU(c->d_cnt_words.ensure(nt * 8 + 8));
+    CU(c->d_cnt_tiles.ensure(nt * 8 + 8));
+    CU(c->d_cnt_rows.ensure(nt * 8 + 8));
+    CU(c->d_scan_tmp.ensure((size_t)scan_tmp_elems((int64_t)nt) * 8 + 8));
+    CU(c->h_totals.ensure(64));
+    DevBatch& B = c->B;
+    memset(&B, 0, sizeof B);
+    B.n_bundles = b->n_bundles; B.n_tx = b->n_tx; B.n_segs = b->n_segs; B.seq_bytes = (int64_t)seqb;
+    B.seq = c->d_seq.as<uint8_t>(); B.seq_off = c->d_seq_off.as<int64_t>(); B.bundle_start = c->d_bstart.as<int32_t>();
+    B.bundle_tx_off = c->d_btx_off.as<int32_t>(); B.tx_kind = c->d_kind.as<uint8_t>(); B.tx_strand = c->d_strand.as<uint8_t>();
+    B.tx_seg_off = c->d_seg_off.as<int32_t>(); B.tx_cds_start = c->d_cds_s.as<int32_t>(); B.tx_cds_end = c->d_cds_e.as<int32_t>();
+    B.tx_tid_class = c->d_tid.as<int32_t>(); B.segs = c->d_segs.as<orfx_seg>(); B.seg_phase = c->d_phase.as<int8_t>();
+    B.seg_cum = c->d_seg_cum.as<int32_t>(); B.tx_len = c->d_tx_len.as<int32_t>(); B.tx_bundle = c->d_tx_bundle.as<int32_t>();
+    B.tx_mask_off = c->d_mask_off.as<int64_t>(); B.tx_tile_off = c->d_tile_off.as<int64_t>(); B.tx_q_off = c->d_q_off.as<int64_t>();
+    B.q_list = c->d_q_list.as<int32_t>(); B.q_row_off = c->d_row_off.as<int64_t>();
+    c->resident = true;
+    c->have_results = false;
+    return ORFX_OK;
+}
+
+void stage_begin(orfx_ctx* c, int st) { cudaEventRecord(c->st_ev[st][0], c->stream); }
+void stage_end(orfx_ctx* c, int st) { cudaEventRecord(c->st_ev[st][1], c->stream); }
+
+// the whole path on the resident batch; leaves results in device memory
+int run_path(orfx_ctx* c) {
+    cudaStream_t s = c->stream;
+    DevBatch& B = c->B;
+    c->n_launches = 0;
+    c->n_queries = c->n_rows = c->n_tiles = c->n_words = 0;
+    if (B.n_tx == 0) return ORFX_OK;
+    stage_begin(c, ST_PREP);
+    c->n_launches += launch_prep(B, c->d_cnt_q.as<int64_t>(), c->d_cnt_words.as<int64_t>(), c->d_cnt_tiles.as<int64_t>(), c->d_scan_tmp.as<int64_t>(), s);
+    stage_end(c, ST_PREP);
+    stage_begin(c, ST_COUNT);
+    c->n_launches += launch_count_rows(B, c->d_cnt_rows.as<int64_t>(), c->d_scan_tmp.as<int64_t>(), s);
+    stage_end(c, ST_COUNT);
+    // the only host round trip of the path: four totals that size the remaining buffers
+    int64_t* tot = c->h_totals.as<int64_t>();
+    CU(cudaMemcpyAsync(tot + 0, B.tx_q_off + B.n_tx, 8, cudaMemcpyDeviceToHost, s));
+    CU(cudaMemcpyAsync(tot + 1, B.tx_mask_off + B.n_tx, 8, cudaMemcpyDeviceToHost, s));
+    CU(cudaMemcpyAsync(tot + 2, B.tx_tile_off + B.n_tx, 8, cudaMemcpyDeviceToHost, s));
+    CU(cudaMemcpyAsync(tot + 3, B.q_row_off + B.n_tx, 8, cudaMemcpyDeviceToHost, s));
+    CU(cudaStreamSynchronize(s));
+    const int64_t nq = tot[0], words = tot[1], tiles = tot[2], nrows = tot[3];
+    c->n_queries = nq; c->n_words = words; c->n_tiles = tiles; c->n_rows = nrows;
+    if (c->P.has_reference) {
+        CU(c->d_tile_tx.ensure((size_t)tiles * 4 + 4));
+        CU(c->d_stop.ensure((size_t)words * 4 + 16));
+        CU(c->d_start.ensure((size_t)words * 4 + 16));
+        B.tile_tx = c->d_tile_tx.as<int32_t>(); B.stop_mask = c->d_stop.as<uint32_t>(); B.start_mask = c->d_start.as<uint32_t>();
+    }
+    for (int i = 0; i < 16; i++) CU(c->r_i32[i].ensure((size_t)nrows * 4 + 4));
+    for (int i = 0; i < 3; i++) CU(c->r_f32[i].ensure((size_t)nrows * 4 + 4));
+    for (int i = 0; i < 3; i++) CU(c->r_u8[i].ensure((size_t)nrows + 4));
+    CU(c->r_order.ensure((size_t)nrows * 8 + 8));
+    CU(c->d_ord.ensure((size_t)nrows * 4 + 4));
+    CU(c->d_best.ensure((size_t)nq * sizeof(orfx_best) + 8));
+    DevRows& R = c->R;
+    R.n_rows = nrows;
+    int32_t** i32[16] = {&R.q_tx, &R.t_tx, &R.seg_start, &R.seg_end, &R.cds_start, &R.cds_end, &R.n_dup, &R.qlen, &R.tlen, &R.ulen,
+                         &R.query_start, &R.extra, &R.missing, &R.match, &R.outframe, &R.inframe};
+    for (int i = 0; i < 16; i++) *i32[i] = c->r_i32[i].as<int32_t>();
+    R.lpi = c->r_f32[0].as<float>(); R.ilpi = c->r_f32[1].as<float>(); R.mlpi = c->r_f32[2].as<float>();
+    R.status = c->r_u8[0].as<uint8_t>(); R.pass = c->r_u8[1].as<uint8_t>(); R.start_match = c->r_u8[2].as<uint8_t>();
+    R.print_order = c->r_order.as<int64_t>();
+
+    stage_begin(c, ST_SCAN);
+    if (c->P.has_reference) {
+        c->n_launches += launch_fill_tiles(B, s);
+        launch_codon_scan(B, tiles, c->n_sm, s);
+        if (tiles > 0) c->n_launches++;
+    }
+    stage_end(c, ST_SCAN);
+    stage_begin(c, ST_FILL);
+    c->n_launches += launch_fill_rows(B, R, (int)nq, s);
+    stage_end(c, ST_FILL);
+    stage_begin(c, ST_RESCUE);
+    c->n_launches += launch_rescue_score(B, R, c->P, s);
+    stage_end(c, ST_RESCUE);
+    stage_begin(c, ST_SELECT);
+    c->n_launches += launch_select(B, R, c->P, (int)nq, c->d_best.as<orfx_best>(), c->d_ord.as<int32_t>(), s);
+    stage_end(c, ST_SELECT);
+    CU(cudaGetLastError());
+    return ORFX_OK;
+}
+
+int download_results(orfx_ctx* c) {
+    cudaStream_t s = c->stream;
+    const size_t nq = (size_t)c->n_queries, nr = (size_t)c->n_rows;
+    CU(c->h_best.ensure(nq * sizeof(orfx_best) + 8));
+    if (nq) CU(cudaMemcpyAsync(c->h_best.p, c->d_best.p, nq * sizeof(orfx_best), cudaMemcpyDeviceToHost, s));
+    if (c->P.want_rows && nr) {
+        for (int i = 0; i < 16; i++) { CU(c->h_i32[i].ensure(nr * 4)); CU(cudaMemcpyAsync(c->h_i32[i].p, c->r_i32[i].p, nr * 4, cudaMemcpyDeviceToHost, s)); }
+        for (int i = 0; i < 3; i++) { CU(c->h_f32[i].ensure(nr * 4)); CU(cudaMemcpyAsync(c->h_f32[i].p, c->r_f32[i].p, nr * 4, cudaMemcpyDeviceToHost, s)); }
+        for (int i = 0; i < 3; i++) { CU(c->h_u8[i].ensure(nr)); CU(cudaMemcpyAsync(c->h_u8[i].p, c->r_u8[i].p, nr, cudaMemcpyDeviceToHost, s)); }
+        CU(c->h_order.ensure(nr * 8));
+        CU(cudaMemcpyAsync(c->h_order.p, c->r_order.p, nr * 8, cudaMemcpyDeviceToHost, s));
+    }
+    return ORFX_OK;
+}
+
+void fill_results(orfx_ctx* c, orfx_results* r) {
+    memset(r, 0, sizeof *r);
+    r->n_queries = (int32_t)c->n_queries;
+    r->n_rows = c->n_rows;
+    r->best = c->h_best.as<orfx_best>();
+    if (c->P.want_rows) {
+        const int32_t** i32[16] = {&r->row_q_tx, &r->row_t_tx, &r->row_seg_start, &r->row_seg_end, &r->row_cds_start, &r->row_cds_end, &r->row_n_dup,
+                                   &r->row_qlen, &r->row_tlen, &r->row_ulen, &r->row_query_start, &r->row_extra, &r->row_missing, &r->row_match,
+                                   &r->row_outframe, &r->row_inframe};
+        for (int i = 0; i < 16; i++) *i32[i] = c->h_i32[i].as<int32_t>();
+        r->row_lpi = c->h_f32[0].as<float>(); r->row_ilpi = c->h_f32[1].as<float>(); r->row_mlpi = c->h_f32[2].as<float>();
+        r->row_status = c->h_u8[0].as<uint8_t>(); r->row_pass = c->h_u8[1].as<uint8_t>(); r->row_start_match = c->h_u8[2].as<uint8_t>();
+        r->print_order = c->h_order.as<int64_t>();
+    }
+}
+
+int check_params(const orfx_params* p) {
+    if (!p) return fail(ORFX_E_INVALID, "null params");
+    if (p->n_modes < 0 || p->n_modes > 8) return fail(ORFX_E_INVALID, "n_modes out of range");
+    for (int i = 0; i < p->n_modes; i++) if (p->mode_array[i] < 0 || p->mode_array[i] > ORFX_MODE_FIRST) return fail(ORFX_E_INVALID, "invalid mode");
+    if (p->overhang != 0) return fail(ORFX_E_UNSUPPORTED, "--overhang > 0 is not implemented in this build");
+    return ORFX_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+const char* orfx_last_error(void) { return g_err.c_str(); }
+int orfx_abi_version(void) { return ORFX_ABI_VERSION; }
+
+int orfx_create(orfx_ctx** out, int device, const orfx_params* params) {
+    if (!out) return fail(ORFX_E_INVALID, "null out");
+    int rc = check_params(params);
+    if (rc) return rc;
+    int ndev = 0;
+    cudaError_t e = cudaGetDeviceCount(&ndev);
+    if (e != cudaSuccess || ndev == 0)
+        return fail(ORFX_E_NODEVICE, std::string("no CUDA device available (") + (e == cudaSuccess ? "device count 0" : cudaGetErrorString(e)) +
+                                         "); this library has no CPU path");
+    if (device < 0 || device >= ndev) return fail(ORFX_E_NODEVICE, "device ordinal out of range");
+    CU(cudaSetDevice(device));
+    cudaDeviceProp prop;
+    CU(cudaGetDeviceProperties(&prop, device));
+    if (prop.major < 10) return fail(ORFX_E_NODEVICE, std::string("device ") + prop.name + " is not sm_100-class; this library is built for sm_100a only");
+    orfx_ctx* c = new orfx_ctx();
+    c->device = device;
+    c->n_sm = prop.multiProcessorCount;
+    c->P = *params;
+    if (cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking) != cudaSuccess) { delete c; return fail(ORFX_E_CUDA, "cudaStreamCreate failed"); }
+    for (auto& ev : c->ev) cudaEventCreate(&ev);
+    for (int i = 0; i < ST_N; i++) { cudaEventCreate(&c->st_ev[i][0]); cudaEventCreate(&c->st_ev[i][1]); c->st_ms[i] = 0; }
+    *out = c;
+    return ORFX_OK;
+}
+
+int orfx_set_params(orfx_ctx* c, const orfx_params* params) {
+    if (!c) return fail(ORFX_E_INVALID, "null ctx");
+    int rc = check_params(params);
+    if (rc) return rc;
+    c->P = *params;
+    return ORFX_OK;
+}
+
+int orfx_submit(orfx_ctx* c, const orfx_batch* batch) {
+    if (!c) return fail(ORFX_E_INVALID, "null ctx");
+    CU(cudaSetDevice(c->device));
+    CU(cudaEventRecord(c->ev[0], c->stream));
+    int rc = upload_batch(c, batch);
+    if (rc) return rc;
+    CU(cudaEventRecord(c->ev[1], c->stream));
+    rc = run_path(c);
+    if (rc) return rc;
+    CU(cudaEventRecord(c->ev[2], c->stream));
+    rc = download_results(c);
+    if (rc) return rc;
+    CU(cudaEventRecord(c->ev[3], c->stream));
+    c->pending = true;
+    return ORFX_OK;
+}
+
+int orfx_wait(orfx_ctx* c, orfx_results* out) {
+    if (!c || !out) return fail(ORFX_E_INVALID, "null argument");
+    if (!c->pending) return fail(ORFX_E_STATE, "orfx_wait without a pending orfx_submit");
+    CU(cudaSetDevice(c->device));
+    CU(cudaStreamSynchronize(c->stream));
+    CU(cudaGetLastError());
+    c->pending = false;
+    c->have_results = true;
+    fill_results(c, out);
+    cudaEventElapsedTime(&out->ms_h2d, c->ev[0], c->ev[1]);
+    cudaEventElapsedTime(&out->ms_kernels, c->ev[1], c->ev[2]);
+    cudaEventElapsedTime(&out->ms_d2h, c->ev[2], c->ev[3]);
+    return ORFX_OK;
+}
+
+int orfx_release(orfx_ctx* c) {
+    if (!c) return fail(ORFX_E_INVALID, "null ctx");
+    c->have_results = false;
+    return ORFX_OK;
+}
+
+void orfx_destroy(orfx_ctx* c) {
+    if (!c) return;
+    cudaSetDevice(c->device);
+    cudaStreamSynchronize(c->stream);
+    DBuf* d[] = {&c->d_seq, &c->d_seq_off, &c->d_bstart, &c->d_btx_off, &c->d_kind, &c->d_strand, &c->d_seg_off, &c->d_cds_s, &c->d_cds_e, &c->d_tid,
+                 &c->d_segs, &c->d_phase, &c->d_seg_cum, &c->d_tx_len, &c->d_tx_bundle, &c->d_mask_off, &c->d_tile_off, &c->d_q_off, &c->d_q_list,
+                 &c->d_row_off, &c->d_tile_tx, &c->d_stop, &c->d_start, &c->d_cnt_q, &c->d_cnt_words, &c->d_cnt_tiles, &c->d_cnt_rows, &c->d_scan_tmp,
+                 &c->d_ord, &c->r_order, &c->d_best};
+    for (DBuf* b : d) b->free_();
+    for (auto& b : c->r_i32) b.free_();
+    for (auto& b : c->r_f32) b.free_();
+    for (auto& b : c->r_u8) b.free_();
+    c->h_totals.free_(); c->h_best.free_(); c->h_order.free_();
+    for (auto& b : c->h_i32) b.free_();
+    for (auto& b : c->h_f32) b.free_();
+    for (auto& b : c->h_u8) b.free_();
+    for (auto& ev : c->ev) if (ev) cudaEventDestroy(ev);
+    for (int i = 0; i < ST_N; i++) { cudaEventDestroy(c->st_ev[i][0]); cudaEventDestroy(c->st_ev[i][1]); }
+    cudaStreamDestroy(c->stream);
+    delete c;
+}
+
+int orfx_upload(orfx_ctx* c, const orfx_batch* batch) {
+    if (!c) return fail(ORFX_E_INVALID, "null ctx");
+    CU(cudaSetDevice(c->device));
+    int rc = upload_batch(c, batch);
+    if (rc) return rc;
+    CU(cudaStreamSynchronize(c->stream));
+    return ORFX_OK;
+}
+
+int orfx_run_resident(orfx_ctx* c, int* n_launches) {
+    if (!c) return fail(ORFX_E_INVALID, "null ctx");
+    if (!c->resident) return fail(ORFX_E_STATE, "no resident batch: call orfx_upload first");
+    CU(cudaSetDevice(c->device));
+    int rc = run_path(c);
+    if (rc) return rc;
+    CU(cudaStreamSynchronize(c->stream));
+    CU(cudaGetLastError());
+    for (int i = 0; i < ST_N; i++) cudaEventElapsedTime(&c->st_ms[i], c->st_ev[i][0], c->st_ev[i][1]);
+    if (n_launches) *n_launches = c->n_launches;
+    return ORFX_OK;
+}
+
+int orfx_fetch(orfx_ctx* c, orfx_results* out) {
+    if (!c || !out) return fail(ORFX_E_INVALID, "null argument");
+    if (!c->resident) return fail(ORFX_E_STATE, "nothing to fetch");
+    CU(cudaSetDevice(c->device));
+    int rc = download_results(c);
+    if (rc) return rc;
+    CU(cudaStreamSynchronize(c->stream));
+    fill_results(c, out);
+    return ORFX_OK;
+}
+
+int orfx_kernel_times(orfx_ctx* c, int max_n, const char** names, float* ms, int* n) {
+    if (!c || !n) return fail(ORFX_E_INVALID, "null argument");
+    int k = 0;
+    for (; k < ST_N && k < max_n; k++) { if (names) names[k] = STAGE_NAME[k]; if (ms) ms[k] = c->st_ms[k]; }
+    *n = k;
+    return ORFX_OK;
+}
+
+int64_t orfx_resident_query_nt(orfx_ctx* c) {
+    if (!c || !c->resident) return fail(ORFX_E_STATE, "no resident batch");
+    if (cudaSetDevice(c->device) != cudaSuccess) return ORFX_E_CUDA;
+    const size_t nt = (size_t)c->B.n_tx;
+    std::vector<int32_t> len(nt);
+    std::vector<uint8_t> kind(nt);
+    if (nt) {
+        if (cudaMemcpy(len.data(), c->B.tx_len, nt * 4, cudaMemcpyDeviceToHost) != cudaSuccess) return fail(ORFX_E_CUDA, "copy tx_len");
+        if (cudaMemcpy(kind.data(), c->B.tx_kind, nt, cudaMemcpyDeviceToHost) != cudaSuccess) return fail(ORFX_E_CUDA, "copy tx_kind");
+    }
+    int64_t sum = 0;
+    for (size_t i = 0; i < nt; i++) if (kind[i] == ORFX_TX_QUERY) sum += len[i];
+    return sum;
+}
+
+int64_t orfx_get_masks(orfx_ctx* c, int32_t tx, uint32_t* stop_bits, uint32_t* start_bits, int64_t max_words) {
+    if (!c || !c->resident || !c->P.has_reference) return fail(ORFX_E_STATE, "no resident masks");
+    if (tx < 0 || tx >= c->B.n_tx) return fail(ORFX_E_INVALID, "tx out of range");
+    if (cudaSetDevice(c->device) != cudaSuccess) return ORFX_E_CUDA;
+    int64_t off[2];
+    int32_t L;
+    uint8_t kind;
+    if (cudaMemcpy(off, c->B.tx_mask_off + tx, 16, cudaMemcpyDeviceToHost) != cudaSuccess) return fail(ORFX_E_CUDA, "copy mask_off");
+    if (cudaMemcpy(&L, c->B.tx_len + tx, 4, cudaMemcpyDeviceToHost) != cudaSuccess) return fail(ORFX_E_CUDA, "copy len");
+    if (cudaMemcpy(&kind, c->B.tx_kind + tx, 1, cudaMemcpyDeviceToHost) != cudaSuccess) return fail(ORFX_E_CUDA, "copy kind");
+    if (kind != ORFX_TX_QUERY) return fail(ORFX_E_INVALID, "not a query transcript");
+    int64_t words = ((int64_t)L + 31) / 32;
+    if (words > max_words || words > off[1] - off[0]) return fail(ORFX_E_INVALID, "mask buffer too small");
+    if (cudaMemcpy(stop_bits, c->B.stop_mask + off[0], (size_t)words * 4, cudaMemcpyDeviceToHost) != cudaSuccess) return fail(ORFX_E_CUDA, "copy stop mask");
+    if (cudaMemcpy(start_bits, c->B.start_mask + off[0], (size_t)words * 4, cudaMemcpyDeviceToHost) != cudaSuccess) return fail(ORFX_E_CUDA, "copy start mask");
+    return L;
+}
+
+int orfx_align_batch(orfx_ctx* c, const uint8_t* aa, const int64_t* off, int64_t n_seq, const int32_t* pair_q, const int32_t* pair_t,
+                     int64_t n_pairs, int gapo, int gape, orfx_aln_out* out, double* cells, float* ms) {
+    if (!c) return fail(ORFX_E_INVALID, "null ctx");
+    if (!aa || !off || !pair_q || !pair_t || !out || n_pairs < 0 || n_seq < 0) return fail(ORFX_E_INVALID, "null or negative argument");
+    CU(cudaSetDevice(c->device));
+    std::string err;
+    int rc = align_batch_device(c->device, c->stream, aa, off, n_seq, pair_q, pair_t, n_pairs, gapo, gape, out, cells, ms, err);
+    if (rc) return fail(rc, err);
+    return ORFX_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,55 @@
+// Device-side data layout shared by the kernels of the path (see DESIGN.md "Data layout in HBM").
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include "orfx.h"
+
+namespace orfx {
+
+// Flat view of one resident batch.  Arrays marked [in] are uploaded as given by the caller
+// (orfx_batch); the others are derived on the device by prep kernels.
+struct DevBatch {
+    int32_t n_bundles, n_tx;
+    int64_t n_segs, seq_bytes;
+    // [in]
+    const uint8_t* seq;
+    const int64_t* seq_off;
+    const int32_t* bundle_start;
+    const int32_t* bundle_tx_off;
+    const uint8_t* tx_kind;
+    const uint8_t* tx_strand;
+    const int32_t* tx_seg_off;
+    const int32_t* tx_cds_start;
+    const int32_t* tx_cds_end;
+    const int32_t* tx_tid_class;
+    const orfx_seg* segs;
+    const int8_t* seg_phase;
+    // derived
+    int32_t* seg_cum;        // [n_segs] bases of the transcript before this segment (genomic order)
+    int32_t* tx_len;         // [n_tx] spliced length
+    int32_t* tx_bundle;      // [n_tx]
+    int64_t* tx_mask_off;    // [n_tx+1] word offset of the transcript's masks (queries only; 4-word aligned)
+    int64_t* tx_tile_off;    // [n_tx+1] first codon-scan tile of the transcript (queries only)
+    int64_t* tx_q_off;       // [n_tx+1] query ordinal (exclusive scan of is_query)
+    int32_t* q_list;         // [n_tx capacity] transcript index of each query
+    int64_t* q_row_off;      // [n_tx+1] first candidate row of each query (entries past n_queries = total)
+    int32_t* tile_tx;        // [n_tiles] transcript of each codon-scan tile
+    // codon-scan output: bit p of a transcript's region = codon starting at spliced position p (5'->3')
+    uint32_t* stop_mask;
+    uint32_t* start_mask;
+};
+
+// Candidate rows, SoA (orfx_results row_* arrays mirror these)
+struct DevRows {
+    int64_t n_rows;
+    int32_t *q_tx, *t_tx, *seg_start, *seg_end, *cds_start, *cds_end, *n_dup;
+    int32_t *qlen, *tlen, *ulen, *query_start, *extra, *missing, *match, *outframe, *inframe;
+    float *lpi, *ilpi, *mlpi;
+    uint8_t *status, *pass, *start_match;
+    int64_t* print_order;
+};
+
+static constexpr int SCAN_TILE = 512;          // spliced positions per codon-scan tile (one warp)
+static constexpr int SCAN_WARPS_PER_CTA = 4;
+
+}  // namespace orfx

@@ -1,0 +1,467 @@
+// Batch preparation, candidate enumeration, ORF rescue and pair scoring kernels.
+//
+//   prep        per-transcript spliced length / per-segment prefix, query list, codon-scan tile list
+//   rows        for every query, every template of its bundle that passes the bounding-box test
+//               (orfanage.cpp:500-503) -> CHAIN::intersection(..., segments=true) (Transcriptome.h:321-361)
+//               -> one candidate row per intersection segment (or one "no-overlap" row)
+//   rescue      per row: template phase at the segment's 5' end, seed CDS, stop trim / stop extension,
+//               template-guided start choice, start trim (orfanage.cpp:532-599; TX::rescue_cds and
+//               callees, Transcriptome.cpp:182-227, 400-677) restated in transcript coordinates as
+//               in-frame bit scans over the codon-scan masks
+//   score       TX::score (Transcriptome.cpp:699-762): lossy union, sweep classification, lpi/ilpi/mlpi
+#include "chain_ops.cuh"
+
+namespace orfx {
+
+// ------------------------------------------------------------------------------------------------
+// exclusive scan of int64 (small hand-written three-phase scan; sizes here are n_tx / n_queries)
+// ------------------------------------------------------------------------------------------------
+namespace {
+constexpr int SCAN_THREADS = 256;
+constexpr int SCAN_ITEMS = 8;
+constexpr int SCAN_BLOCK = SCAN_THREADS * SCAN_ITEMS;
+
+__device__ __forceinline__ int64_t block_exclusive_scan(int64_t v, int64_t* total) {
+    __shared__ int64_t warp_sums[SCAN_THREADS / 32];
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    int64_t incl = v;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) { int64_t t = __shfl_up_sync(0xffffffffu, incl, d); if (lane >= d) incl += t; }
+    if (lane == 31) warp_sums[wid] = incl;
+    __syncthreads();
+    if (wid == 0) {
+        int64_t s = lane < SCAN_THREADS / 32 ? warp_sums[lane] : 0;
+#pragma unroll
+        for (int d = 1; d < SCAN_THREADS / 32; d <<= 1) { int64_t t = __shfl_up_sync(0xffffffffu, s, d); if (lane >= d) s += t; }
+        if (lane < SCAN_THREADS / 32) warp_sums[lane] = s;
+    }
+    __syncthreads();
+    int64_t base = wid > 0 ? warp_sums[wid - 1] : 0;
+    *total = warp_sums[SCAN_THREADS / 32 - 1];
+    __syncthreads();
+    return base + incl - v;
+}
+
+__global__ void __launch_bounds__(SCAN_THREADS) scan_local_kernel(const int64_t* in, int64_t* out, int64_t* block_sums, int64_t n) {
+    const int64_t base = (int64_t)blockIdx.x * SCAN_BLOCK + (int64_t)threadIdx.x * SCAN_ITEMS;
+    int64_t v[SCAN_ITEMS], sum = 0;
+#pragma unroll
+    for (int i = 0; i < SCAN_ITEMS; i++) { v[i] = base + i < n ? in[base + i] : 0; sum += v[i]; }
+    int64_t total;
+    int64_t ex = block_exclusive_scan(sum, &total);
+#pragma unroll
+    for (int i = 0; i < SCAN_ITEMS; i++) { if (base + i < n) out[base + i] = ex; ex += v[i]; }
+    if (threadIdx.x == 0) block_sums[blockIdx.x] = total;
+}
+__global__ void __launch_bounds__(SCAN_THREADS) scan_tops_kernel(int64_t* block_sums, int64_t n_blocks, int64_t* grand_total) {
+    int64_t carry = 0;
+    for (int64_t c = 0; c < n_blocks; c += SCAN_THREADS) {
+        int64_t i = c + threadIdx.x;
+        int64_t v = i < n_blocks ? block_sums[i] : 0, total;
+        int64_t ex = block_exclusive_scan(v, &total);
+        if (i < n_blocks) block_sums[i] = carry + ex;
+        carry += total;
+    }
+    if (threadIdx.x == 0) *grand_total = carry;
+}
+__global__ void __launch_bounds__(SCAN_THREADS) scan_add_kernel(int64_t* out, const int64_t* block_sums, int64_t n) {
+    const int64_t base = (int64_t)blockIdx.x * SCAN_BLOCK + (int64_t)threadIdx.x * SCAN_ITEMS;
+    const int64_t add = block_sums[blockIdx.x];
+#pragma unroll
+    for (int i = 0; i < SCAN_ITEMS; i++) if (base + i < n) out[base + i] += add;
+}
+}  // namespace
+
+// out[0..n) = exclusive prefix of in[0..n); out[n] = total.  tmp must hold ceil(n / SCAN_BLOCK) int64.
+int launch_exclusive_scan(const int64_t* in, int64_t* out, int64_t* tmp, int64_t n, cudaStream_t s) {
+    if (n <= 0) { cudaMemsetAsync(out, 0, sizeof(int64_t), s); return 0; }
+    int64_t nb = (n + SCAN_BLOCK - 1) / SCAN_BLOCK;
+    scan_local_kernel<<<(unsigned)nb, SCAN_THREADS, 0, s>>>(in, out, tmp, n);
+    scan_tops_kernel<<<1, SCAN_THREADS, 0, s>>>(tmp, nb, out + n);
+    scan_add_kernel<<<(unsigned)nb, SCAN_THREADS, 0, s>>>(out, tmp, n);
+    return 3;
+}
+int64_t scan_tmp_elems(int64_t n) { return (n + SCAN_BLOCK - 1) / SCAN_BLOCK + 1; }
+
+// ------------------------------------------------------------------------------------------------
+// prep
+// ------------------------------------------------------------------------------------------------
+__global__ void tx_prep_kernel(DevBatch B, int64_t* cnt_q, int64_t* cnt_words, int64_t* cnt_tiles) {
+    int tx = blockIdx.x * blockDim.x + threadIdx.x;
+    if (tx >= B.n_tx) return;
+    int s0 = B.tx_seg_off[tx], s1 = B.tx_seg_off[tx + 1];
+    int acc = 0;
+    for (int k = s0; k < s1; k++) { B.seg_cum[k] = acc; orfx_seg sg = B.segs[k]; acc += sg.end - sg.start + 1; }
+    B.tx_len[tx] = acc;
+    bool isq = B.tx_kind[tx] == ORFX_TX_QUERY;
+    int64_t tiles = isq ? (acc + SCAN_TILE - 1) / SCAN_TILE : 0;
+    if (isq && tiles == 0) tiles = 1;
+    cnt_q[tx] = isq ? 1 : 0;
+    cnt_tiles[tx] = tiles;
+    cnt_words[tx] = tiles * (SCAN_TILE / 32);
+}
+__global__ void bundle_prep_kernel(DevBatch B) {
+    int b = blockIdx.x * blockDim.x + threadIdx.x;
+    if (b >= B.n_bundles) return;
+    for (int x = B.bundle_tx_off[b]; x < B.bundle_tx_off[b + 1]; x++) B.tx_bundle[x] = b;
+}
+__global__ void fill_q_list_kernel(DevBatch B) {
+    int tx = blockIdx.x * blockDim.x + threadIdx.x;
+    if (tx >= B.n_tx) return;
+    if (B.tx_kind[tx] == ORFX_TX_QUERY) B.q_list[B.tx_q_off[tx]] = tx;
+}
+__global__ void fill_tile_list_kernel(DevBatch B) {
+    int tx = blockIdx.x * blockDim.x + threadIdx.x;
+    if (tx >= B.n_tx) return;
+    if (B.tx_kind[tx] != ORFX_TX_QUERY) return;
+    for (int64_t t = B.tx_tile_off[tx]; t < B.tx_tile_off[tx + 1]; t++) B.tile_tx[t] = tx;
+}
+// Everything that needs no host-side size: lengths, prefixes, the three per-transcript scans, the
+// query list (capacity n_tx).  The totals land in tx_q_off[n_tx], tx_mask_off[n_tx], tx_tile_off[n_tx].
+int launch_prep(const DevBatch& B, int64_t* cnt_q, int64_t* cnt_words, int64_t* cnt_tiles, int64_t* scan_tmp, cudaStream_t s) {
+    int n = 0;
+    if (B.n_tx == 0) return 0;
+    tx_prep_kernel<<<(B.n_tx + 255) / 256, 256, 0, s>>>(B, cnt_q, cnt_words, cnt_tiles); n++;
+    bundle_prep_kernel<<<(B.n_bundles + 127) / 128, 128, 0, s>>>(B); n++;
+    n += launch_exclusive_scan(cnt_q, B.tx_q_off, scan_tmp, B.n_tx, s);
+    n += launch_exclusive_scan(cnt_words, B.tx_mask_off, scan_tmp, B.n_tx, s);
+    n += launch_exclusive_scan(cnt_tiles, B.tx_tile_off, scan_tmp, B.n_tx, s);
+    fill_q_list_kernel<<<(B.n_tx + 255) / 256, 256, 0, s>>>(B); n++;
+    return n;
+}
+int launch_fill_tiles(const DevBatch& B, cudaStream_t s) {
+    if (B.n_tx == 0) return 0;
+    fill_tile_list_kernel<<<(B.n_tx + 255) / 256, 256, 0, s>>>(B);
+    return 1;
+}
+
+// ------------------------------------------------------------------------------------------------
+// rows: bounding box + intersection segments
+// ------------------------------------------------------------------------------------------------
+namespace {
+// Enumerates the candidate rows of query transcript qx in the reference's order.  FILL = false only counts.
+template <bool FILL>
+__device__ int64_t enumerate_rows(const DevBatch& B, const DevRows& R, int qx, int64_t out) {
+    const int b = B.tx_bundle[qx];
+    const int x0 = B.bundle_tx_off[b], x1 = B.bundle_tx_off[b + 1];
+    const int q0 = B.tx_seg_off[qx], q1 = B.tx_seg_off[qx + 1];
+    const int qstart = B.segs[q0].start, qend = B.segs[q1 - 1].end;
+    int64_t n = 0;
+    for (int t = x0; t < x1; t++) {
+        if (B.tx_kind[t] != ORFX_TX_TEMPLATE) continue;
+        if (qstart > B.tx_cds_end[t] || qend < B.tx_cds_start[t]) continue;   // orfanage.cpp:501-503
+        const int t0 = B.tx_seg_off[t], t1 = B.tx_seg_off[t + 1];
+        int start = t0, nseg = 0, cur_s = 0, cur_e = 0;
+        bool continue_prev = false;
+        for (int i = q0; i < q1; i++) {
+            const orfx_seg s1 = B.segs[i];
+            bool found_yet = false;
+            for (int j = start; j < t1; j++) {
+                const orfx_seg c2 = B.segs[j];
+                const int is = max(s1.start, c2.start), ie = min(s1.end, c2.end);
+                if (is <= ie) {
+                    found_yet = true;
+                    start = j;
+                    if (ie == c2.end) start++;
+                    const bool ends_match = ie == s1.end && s1.end == c2.end;
+                    const bool starts_match = is == s1.start && s1.start == c2.start;
+                    if (!continue_prev || !starts_match) {
+                        if (nseg > 0) {
+                            if (FILL) { R.q_tx[out + n] = qx; R.t_tx[out + n] = t; R.seg_start[out + n] = cur_s; R.seg_end[out + n] = cur_e; R.status[out + n] = ORFX_ST_OK; }
+                            n++;
+                        }
+                        nseg++;
+                        cur_s = is; cur_e = ie;
+                    } else {
+                        cur_s = min(cur_s, is); cur_e = max(cur_e, ie);
+                    }
+                    continue_prev = ends_match;
+                } else {
+                    if (found_yet) break;
+                    continue_prev = false;
+                }
+            }
+            if (!found_yet && continue_prev) continue_prev = false;
+        }
+        if (nseg > 0) {
+            if (FILL) { R.q_tx[out + n] = qx; R.t_tx[out + n] = t; R.seg_start[out + n] = cur_s; R.seg_end[out + n] = cur_e; R.status[out + n] = ORFX_ST_OK; }
+            n++;
+        } else {
+            if (FILL) { R.q_tx[out + n] = qx; R.t_tx[out + n] = t; R.seg_start[out + n] = -1; R.seg_end[out + n] = -1; R.status[out + n] = ORFX_ST_NO_OVERLAP; }
+            n++;
+        }
+    }
+    return n;
+}
+}  // namespace
+
+// The query count is still on the device here: one thread per transcript slot, slots past the last
+// query count zero, so that q_row_off[n_queries .. n_tx] all hold the total.
+__global__ void count_rows_kernel(DevBatch B, int64_t* cnt) {
+    int qi = blockIdx.x * blockDim.x + threadIdx.x;
+    if (qi >= B.n_tx) return;
+    const int64_t nq = B.tx_q_off[B.n_tx];
+    DevRows dummy{};
+    cnt[qi] = qi < nq ? enumerate_rows<false>(B, dummy, B.q_list[qi], 0) : 0;
+}
+__global__ void fill_rows_kernel(DevBatch B, DevRows R, int n_queries) {
+    int qi = blockIdx.x * blockDim.x + threadIdx.x;
+    if (qi >= n_queries) return;
+    enumerate_rows<true>(B, R, B.q_list[qi], B.q_row_off[qi]);
+}
+int launch_count_rows(const DevBatch& B, int64_t* cnt, int64_t* scan_tmp, cudaStream_t s) {
+    if (B.n_tx == 0) { cudaMemsetAsync(B.q_row_off, 0, sizeof(int64_t), s); return 0; }
+    count_rows_kernel<<<(B.n_tx + 127) / 128, 128, 0, s>>>(B, cnt);
+    return 1 + launch_exclusive_scan(cnt, B.q_row_off, scan_tmp, B.n_tx, s);
+}
+int launch_fill_rows(const DevBatch& B, const DevRows& R, int n_queries, cudaStream_t s) {
+    if (n_queries == 0) return 0;
+    fill_rows_kernel<<<(n_queries + 127) / 128, 128, 0, s>>>(B, R, n_queries);
+    return 1;
+}
+
+// ------------------------------------------------------------------------------------------------
+// rescue + score, one thread per candidate row
+// ------------------------------------------------------------------------------------------------
+namespace {
+
+// Template-guided choice among the in-frame ATGs upstream of `a` (TX::extend_to_start(TX*,bool),
+// Transcriptome.cpp:564-619): the pieces of (query CDS extended to the farthest ATG) x (template CDS)
+// are walked 5'->3' until the first piece where both CDSs are in the same frame; the start is the
+// nearest ATG whose transcript position does not exceed that piece's CDS-relative position (mixed
+// coordinate systems exactly as written, cpp:581-590), else the farthest ATG.
+__device__ int guided_start(const TxView& q, const TxView& t, const uint32_t* start_mask, int far, int a, int e, int lb) {
+    const int g_far = t2g(q, far), g_e = t2g(q, e);
+    const int glo = min(g_far, g_e), ghi = max(g_far, g_e);
+    const bool plus = q.plus;
+    bool seen = false, done = false;
+    uint32_t Q = 0;
+    int qi = seg_of_genomic(q, plus ? glo : ghi);
+    for (; qi >= 0 && qi < q.n && !done; qi += plus ? 1 : -1) {
+        const orfx_seg qs = q.segs[qi];
+        if (qs.end < glo || qs.start > ghi) break;
+        const int s = max(qs.start, glo), en = min(qs.end, ghi);
+        if (plus) {
+            int lo = 0, hi = t.n;   // first template segment with end >= s
+            while (lo < hi) { int mid = (lo + hi) >> 1; if (t.segs[mid].end < s) lo = mid + 1; else hi = mid; }
+            for (int tj = lo; tj < t.n; tj++) {
+                const orfx_seg ts = t.segs[tj];
+                if (ts.start > en) break;
+                const int pos5 = max(s, ts.start);
+                const uint32_t q_tpos = (uint32_t)(q.cum[qi] + (pos5 - qs.start) - far);
+                const uint32_t t_tpos = (uint32_t)(t.cum[tj] + (pos5 - ts.start));
+                seen = true; Q = q_tpos;
+                if (t_tpos % 3 == q_tpos % 3) { done = true; break; }
+            }
+        } else {
+            int lo = -1, hi = t.n - 1;   // last template segment with start <= en
+            while (lo < hi) { int mid = (lo + hi + 1) >> 1; if (t.segs[mid].start <= en) lo = mid; else hi = mid - 1; }
+            for (int tj = lo; tj >= 0; tj--) {
+                const orfx_seg ts = t.segs[tj];
+                if (ts.end < s) break;
+                const int pos5 = min(en, ts.end);
+                const uint32_t q_tpos = (uint32_t)(q.L - 1 - (q.cum[qi] + (pos5 - qs.start)) - far);
+                const uint32_t t_tpos = (uint32_t)(t.L - 1 - (t.cum[tj] + (pos5 - ts.start)));
+                seen = true; Q = q_tpos;
+                if (t_tpos % 3 == q_tpos % 3) { done = true; break; }
+            }
+        }
+    }
+    if (!seen) return far;
+    const uint32_t lim = Q < (uint32_t)a ? Q : (uint32_t)a;
+    const uint32_t r = (uint32_t)(a % 3);
+    if (lim < r) return far;
+    const int p = (int)(lim - ((lim - r) % 3));
+    const int m = prev_inframe(start_mask, p);
+    return m >= lb ? m : far;
+}
+
+__device__ __forceinline__ float pct(int num, int den) {
+    // 100.0 * ((float)num / (float)den) narrowed to float (Transcriptome.cpp:748-750)
+    return __double2float_rn(__dmul_rn(100.0, (double)__fdiv_rn((float)num, (float)den)));
+}
+
+}  // namespace
+
+__global__ void __launch_bounds__(128) rescue_score_kernel(DevBatch B, DevRows R, orfx_params P) {
+    const int64_t row = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (row >= R.n_rows) return;
+    // defaults: an all-zero Score that does not pass
+    int status = R.status[row];
+    int key_s = 0, key_e = 0;
+    int qlen = 0, tlen = 0, ulen = 0, query_start = 0, extra = 0, missing = 0, match = 0, outframe = 0, inframe = 0;
+    float lpi = 0.f, ilpi = 0.f, mlpi = 0.f;
+    int pass = 0, start_match = 0;
+
+    const int qx = R.q_tx[row], tx = R.t_tx[row];
+    const int seg_s = R.seg_start[row], seg_e = R.seg_end[row];
+    const TxView q = tx_view(B, qx), t = tx_view(B, tx);
+    const bool plus = q.plus;
+    const int t_cds_start = B.tx_cds_start[tx], t_cds_end = B.tx_cds_end[tx];
+    const int t5 = plus ? t_cds_start : t_cds_end;
+    int start = 0, e = 0;   // final ORF, transcript coordinates
+
+    do {
+        if (status != ORFX_ST_OK) break;   // no-overlap
+        // template phase at the segment's 5' end (orfanage.cpp:532-534; SEGTP::get_phase, Transcriptome.h:80-89)
+        const int pos5_t = t.plus ? seg_s : seg_e;
+        int tk = seg_of_genomic(t, pos5_t);
+        uint32_t phase;
+        if (tk >= 0) {
+            const uint32_t off = t.plus ? (uint32_t)(pos5_t - t.segs[tk].start) : (uint32_t)(t.segs[tk].end - pos5_t);
+            phase = ((uint32_t)(int)B.seg_phase[B.tx_seg_off[tx] + tk] + (3u - off % 3u) % 3u) % 3u;
+        } else {
+            phase = (uint32_t)(int)B.seg_phase[B.tx_seg_off[tx] + (t.plus ? 0 : t.n - 1)];
+        }
+        if ((uint32_t)(seg_e + 1 - seg_s) < 3u) { status = ORFX_ST_SEGMENT_LT3; break; }
+        // seed CDS: TX::build_cds + correct_chain_len on the query copy (orfanage.cpp:543-561)
+        const int a0 = g2t(q, plus ? seg_s : seg_e);
+        const int b0 = g2t(q, plus ? seg_e : seg_s);
+        int a = a0;
+        if (phase != 0) { a = a0 + (int)phase; if (a > q.L - 1) a = q.L - 1; }
+        const int g_a = t2g(q, a);
+        if (a > b0 || b0 - a + 1 < 3) {
+            status = ORFX_ST_CDS_LT3;
+            key_s = plus ? g_a : seg_s;
+            key_e = plus ? seg_e : g_a;
+            break;
+        }
+        const int b = a + ((b0 - a + 1) / 3) * 3 - 1;
+        start = a; e = b;
+        if (P.has_reference) {
+            const uint32_t* stopm = B.stop_mask + B.tx_mask_off[qx];
+            const uint32_t* startm = B.start_mask + B.tx_mask_off[qx];
+            // adjust_stop + extend_to_stop (Transcriptome.cpp:182-201, 400-442): first in-frame stop at or after a
+            const int p0 = next_inframe(stopm, a, q.L);
+            if (p0 == a) { status = ORFX_ST_NOT_RESCUED; break; }
+            const bool has_stop = p0 >= 0;
+            e = has_stop ? p0 + 2 : b;
+            // extend_to_start(TX*, non_aug) (Transcriptome.cpp:496-620)
+            const bool m_at_a = mask_bit(startm, a);
+            bool found_start = false;
+            if ((m_at_a || P.non_aug) && g_a == t5) found_start = true;
+            if (!found_start && P.non_aug) {
+                const int ref = g2t(q, t5);
+                if (ref >= 0 && ref % 3 == a % 3) {
+                    bool stop_between = false;
+                    for (int i = a;; i -= 3) {   // SEQ::find_inframe_codon('.',';',...,backward,first), common.hpp:420-450
+                        if (mask_bit(stopm, i)) { stop_between = true; break; }
+                        if (i < ref) break;
+                        if (i < 3) break;
+                    }
+                    if (!stop_between) { if (ref < a) start = ref; found_start = true; }
+                }
+            }
+            if (!found_start) {
+                // all in-frame ATG walking back from a until a stop codon or the transcript start
+                const int prev_stop = a >= 3 ? prev_inframe(stopm, a - 3) : -1;
+                const int lb = prev_stop >= 0 ? prev_stop + 3 : a % 3;
+                int far = next_inframe(startm, lb, q.L);
+                if (far > a) far = -1;
+                if (far >= 0) {
+                    const int ref = g2t(q, t5);
+                    if (ref >= lb && ref <= a && ref % 3 == a % 3 && mask_bit(startm, ref)) start = ref;
+                    else start = guided_start(q, t, startm, far, a, e, lb);
+                }
+                // no upstream ATG: extend_to_start(-1,...) finds nothing either (cpp:446-492)
+            }
+            // adjust_start (Transcriptome.cpp:202-227) unless --non_aug kept the template's start
+            const bool at_t5 = t2g(q, start) == t5;
+            if (!(P.non_aug && at_t5) && !mask_bit(startm, start)) {
+                const int m = next_inframe(startm, start, q.L);
+                if (m >= 0 && m + 2 <= e) start = m;
+            }
+        }
+        const int gs = t2g(q, start), ge = t2g(q, e);
+        const int cs = min(gs, ge), ce = max(gs, ge);
+        if (P.has_reference) {
+            key_s = cs; key_e = ce;
+            const uint32_t* stopm = B.stop_mask + B.tx_mask_off[qx];
+            const uint32_t* startm = B.start_mask + B.tx_mask_off[qx];
+            const bool ends_in_stop = e >= 2 && mask_bit(stopm, e - 2) && ((e - 2 - start) % 3 == 0);
+            const bool front_m = mask_bit(startm, start);
+            const bool at_t5 = (plus ? cs : ce) == t5;
+            if (!ends_in_stop) { status = ORFX_ST_MISSING_STOP; break; }
+            if ((!P.non_aug && !front_m) || (P.non_aug && !front_m && !at_t5)) { status = ORFX_ST_MISSING_START; break; }
+        }
+        qlen = e - start + 1;
+        if (qlen < P.cds_minlen) { status = ORFX_ST_MINLEN; qlen = 0; break; }
+
+        // ---- TX::score (Transcriptome.cpp:699-762) ----
+        tlen = t.L;
+        // query CDS segments = exons clipped to [cs,ce]
+        const int qk0 = seg_of_genomic(q, cs), qk1 = seg_of_genomic(q, ce);
+        // lossy union (CHAIN::get_union, Transcriptome.h:291-319)
+        {
+            int i = qk0, j = 0;
+            while (i <= qk1 && j < t.n) {
+                const int c1s = max(q.segs[i].start, cs), c1e = min(q.segs[i].end, ce);
+                const int c2s = t.segs[j].start, c2e = t.segs[j].end;
+                if (c1e < c2s) { ulen += c1e - c1s + 1; i++; }
+                else if (c2e < c1s) { ulen += c2e - c2s + 1; j++; }
+                else { ulen += max(c1e, c2e) - min(c1s, c2s) + 1; i++; j++; }
+            }
+        }
+        // sweep classification (CHAIN::compare + the frame walk, Transcriptome.h:514-558, cpp:719-745):
+        // match pieces are binned by (extra - missing) mod 3 seen so far on the genomic-left side
+        {
+            int bin[3] = {0, 0, 0};
+            int i = qk0, j = 0;
+            int qs = max(q.segs[i].start, cs), qe = min(q.segs[i].end, ce);
+            int ts = 0, te = -1;
+            if (t.n > 0) { ts = t.segs[0].start; te = t.segs[0].end; }
+            bool hq = true, ht = t.n > 0;
+            while (hq || ht) {
+                if (hq && (!ht || qe < ts)) {          // query-only remainder
+                    extra += qe - qs + 1;
+                    i++; hq = i <= qk1;
+                    if (hq) { qs = max(q.segs[i].start, cs); qe = min(q.segs[i].end, ce); }
+                } else if (ht && (!hq || te < qs)) {   // template-only remainder
+                    missing += te - ts + 1;
+                    j++; ht = j < t.n;
+                    if (ht) { ts = t.segs[j].start; te = t.segs[j].end; }
+                } else {
+                    const int lo = max(qs, ts), hi = min(qe, te);
+                    if (qs < lo) extra += lo - qs;
+                    if (ts < lo) missing += lo - ts;
+                    int d = (extra - missing) % 3; if (d < 0) d += 3;
+                    bin[d] += hi - lo + 1;
+                    match += hi - lo + 1;
+                    qs = hi + 1; ts = hi + 1;
+                    if (qs > qe) { i++; hq = i <= qk1; if (hq) { qs = max(q.segs[i].start, cs); qe = min(q.segs[i].end, ce); } }
+                    if (ts > te) { j++; ht = j < t.n; if (ht) { ts = t.segs[j].start; te = t.segs[j].end; } }
+                }
+            }
+            // 5'->3' on '+' is genomic-left to right: in frame when (extra-missing) so far == 0 (mod 3);
+            // on the reverse strand the 5' side is the genomic-right side: totals minus the left part
+            int want = 0;
+            if (!plus) { want = (extra - missing) % 3; if (want < 0) want += 3; }
+            inframe = bin[want];
+            outframe = match - inframe;
+        }
+        lpi = pct(qlen, ulen); ilpi = pct(inframe, ulen); mlpi = pct(match, ulen);
+        query_start = plus ? cs - q.segs[0].start : q.segs[q.n - 1].end - ce;
+        start_match = (B.tx_strand[qx] == B.tx_strand[tx]) && ((plus ? cs : ce) == t5);
+        pass = 1;
+        if (lpi < (float)P.lpi || ilpi < (float)P.ilpi || mlpi < (float)P.mlpi) pass = 0;
+        // with a reference the row's query copy already carries the rescued coordinates; without one
+        // they are stored only for rows that survive the duplicate check (orfanage.cpp:577 vs 634)
+        key_s = cs; key_e = ce;
+    } while (false);
+
+    R.status[row] = (uint8_t)status;
+    R.cds_start[row] = key_s; R.cds_end[row] = key_e;
+    R.qlen[row] = qlen; R.tlen[row] = tlen; R.ulen[row] = ulen; R.query_start[row] = query_start;
+    R.extra[row] = extra; R.missing[row] = missing; R.match[row] = match; R.outframe[row] = outframe; R.inframe[row] = inframe;
+    R.lpi[row] = lpi; R.ilpi[row] = ilpi; R.mlpi[row] = mlpi;
+    R.pass[row] = (uint8_t)pass; R.start_match[row] = (uint8_t)start_match;
+    R.n_dup[row] = 0;
+}
+
+int launch_rescue_score(const DevBatch& B, const DevRows& R, const orfx_params& P, cudaStream_t s) {
+    if (R.n_rows == 0) return 0;
+    rescue_score_kernel<<<(unsigned)((R.n_rows + 127) / 128), 128, 0, s>>>(B, R, P);
+    return 1;
+}
+
+}  // namespace orfx
