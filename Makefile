@@ -16,11 +16,14 @@ CU_HDR := $(wildcard orfanage_b200/csrc/*.cuh) include/orfx.h include/orfx_codon
 all: tools host oracle cuda
 
 host: $(HOST_OBJ)
-build/host/%.o: orfanage_b200/csrc/host/%.cpp orfanage_b200/csrc/host/orfx_host.h include/orfx.h
+build/host/%.o: orfanage_b200/csrc/host/%.cpp orfanage_b200/csrc/host/orfx_host.h include/orfx.h include/orfx_pack.h
 	@mkdir -p build/host
 	$(CXX) $(CXXFLAGS) -c $< -o $@
 
 cuda: orfanage_b200/liborfx.so orfanage_b200/bin/orfanage
+host: orfanage_b200/liborfx_host.so
+orfanage_b200/liborfx_host.so: $(HOST_OBJ)
+	$(CXX) -shared -o $@ $(HOST_OBJ) -lpthread
 orfanage_b200/liborfx.so: $(CU_SRC) $(CU_HDR)
 	$(NVCC) $(NVFLAGS) -shared $(CU_SRC) -o $@ 2> build/ptxas.log || (cat build/ptxas.log; false)
 	@grep -E "registers|spill|error" build/ptxas.log | sort | uniq -c | sort -rn | head -40 || true
@@ -43,5 +46,5 @@ tools/orfx_synth: tools/orfx_synth.cpp
 	$(CXX) -O2 -std=c++17 -o $@ $<
 
 clean:
-	rm -rf build orfanage_b200/liborfx.so orfanage_b200/bin oracle/liborfx_oracle.so oracle/orfanage_oracle_cli tools/orfx_synth
+	rm -rf build orfanage_b200/liborfx.so orfanage_b200/liborfx_host.so orfanage_b200/bin oracle/liborfx_oracle.so oracle/orfanage_oracle_cli tools/orfx_synth
 .PHONY: all host cuda oracle tools clean

@@ -15,6 +15,7 @@
 #ifndef ORFX_H
 #define ORFX_H
 
+#include <stddef.h>
 #include <stdint.h>
 
 #ifdef __cplusplus
@@ -166,6 +167,11 @@ int  orfx_submit(orfx_ctx* ctx, const orfx_batch* batch);
 int  orfx_wait(orfx_ctx* ctx, orfx_results* out);
 int  orfx_release(orfx_ctx* ctx);
 void orfx_destroy(orfx_ctx* ctx);
+
+/* Pinned (page-locked, portable) host memory for batch arrays: makes the uploads of orfx_submit
+ * asynchronous and full-speed.  Optional — any host memory is accepted by orfx_submit. */
+void* orfx_host_alloc(size_t bytes);
+void  orfx_host_free(void* p);
 
 /* ---- device-resident variant used by the benchmark's kernel-only timing ------------------- */
 /* Uploads a batch once and keeps it in HBM. */

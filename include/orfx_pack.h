@@ -1,0 +1,52 @@
+/*
+ * orfx_pack.h — C-ABI of the host-side locus-bundle batcher.
+ *
+ * The reference has no such interface: loading, template preparation and bundling are the first
+ * sixty lines of run() (orfanage.cpp:313-367; Transcriptome::add / build_cds_chains / sort /
+ * set_cds_as_exons / remove_non_coding / deduplicate / bundleup, Transcriptome.cpp:866-1150).
+ * This header exposes that prefix plus the batcher so that callers that are not
+ * the `orfanage` binary — the benchmark, the parity tests, a binding in another language — can
+ * obtain the flat orfx_batch that orfx_submit / orfx_upload (orfx.h) consume.
+ *
+ * The library behind it (orfanage_b200/liborfx_host.so) is plain C++ and has no CUDA dependency;
+ * it never evaluates anything.
+ */
+#ifndef ORFX_PACK_H
+#define ORFX_PACK_H
+
+#include "orfx.h"
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct orfxh_workload orfxh_workload;
+
+const char* orfxh_last_error(void);
+
+/* Loads the template GTF/GFFs, the query GTF and (optionally, may be NULL) the genome FASTA,
+ * prepares the templates and bundles everything exactly as orfanage.cpp:313-367 does.
+ * use_id / keep_all_cds are the CLI flags of the same names. */
+int orfxh_load(orfxh_workload** out, const char* query_gtf, const char* const* template_gtfs, int n_templates,
+               const char* reference_fasta, int use_id, int keep_all_cds);
+
+/* Counts over the whole workload.  what: 0 = bundles, 1 = bundles holding a template and a query
+ * ("active"), 2 = query transcripts in active bundles, 3 = template transcripts, 4 = all query
+ * transcripts, 5 = spliced query nucleotides in active bundles. */
+int64_t orfxh_count(const orfxh_workload* w, int what);
+
+/* Splits the active bundles over n_shards (longest-processing-time greedy) and packs
+ * shard `shard`.  The arrays behind *out are owned by the workload and stay valid until the next
+ * orfxh_pack with the same shard index or orfxh_free.  alloc/dealloc (both NULL = malloc/free) let
+ * the caller place the arrays in pinned memory (orfx_host_alloc / orfx_host_free of orfx.h). */
+int orfxh_pack(orfxh_workload* w, int shard, int n_shards, void* (*alloc)(size_t), void (*dealloc)(void*), orfx_batch* out);
+
+/* Keeps only the first n active bundles of the workload (bounded samples for CPU baselines). */
+int orfxh_truncate(orfxh_workload* w, int64_t n_active_bundles);
+
+void orfxh_free(orfxh_workload* w);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* ORFX_PACK_H */

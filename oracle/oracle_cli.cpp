@@ -20,7 +20,7 @@ int main(int argc, char** argv) {
         orfx::Options opt;
         if (!orfx::parse_cli(argc, argv, opt)) return 0;
         opt.devices.assign(1, 0);
-        orfx::Backend be{orfx_oracle_create, orfx_oracle_submit, orfx_oracle_wait, orfx_oracle_release, orfx_oracle_destroy, orfx_oracle_last_error};
+        orfx::Backend be{orfx_oracle_create, orfx_oracle_submit, orfx_oracle_wait, orfx_oracle_release, orfx_oracle_destroy, orfx_oracle_last_error, nullptr, nullptr};
         return orfx::run_orfanage(opt, be);
     } catch (const std::exception& e) {
         fprintf(stderr, "Error: %s\n", e.what());

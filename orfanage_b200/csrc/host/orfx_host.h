@@ -129,18 +129,30 @@ void fill_params(const Options& opt, bool want_rows, orfx_params& p);
 struct PackedBatch {
     std::vector<int> bundle_ids;            // index into Transcriptome::bundles
     std::vector<int> tx_global;             // batch tx index -> Transcriptome::txs index
-    std::vector<uint8_t> seq;
-    std::vector<int64_t> seq_off;
-    std::vector<int32_t> bundle_start, bundle_tx_off;
-    std::vector<uint8_t> tx_kind, tx_strand;
-    std::vector<int32_t> tx_seg_off, tx_cds_start, tx_cds_end, tx_tid_class;
-    std::vector<orfx_seg> segs;
-    std::vector<int8_t> seg_phase;
+    // the flat arrays live in one arena obtained from `alloc` (pinned when the backend offers it)
+    void* arena = nullptr;
+    size_t arena_bytes = 0;
+    void (*dealloc)(void*) = nullptr;
+    uint8_t* seq = nullptr;
+    int64_t* seq_off = nullptr;
+    int32_t *bundle_start = nullptr, *bundle_tx_off = nullptr;
+    uint8_t *tx_kind = nullptr, *tx_strand = nullptr;
+    int32_t *tx_seg_off = nullptr, *tx_cds_start = nullptr, *tx_cds_end = nullptr, *tx_tid_class = nullptr;
+    orfx_seg* segs = nullptr;
+    int8_t* seg_phase = nullptr;
+    int32_t n_tx = 0;
+    int64_t n_segs = 0, seq_bytes = 0, n_queries = 0;
+    PackedBatch() {}
+    PackedBatch(const PackedBatch&) = delete;
+    PackedBatch& operator=(const PackedBatch&) = delete;
+    ~PackedBatch() { reset(); }
+    void reset();
     orfx_batch view() const;
 };
 // Packs the listed bundles (each must hold a template and a query).
-void pack_bundles(const Transcriptome& tr, const std::vector<int>& bundle_ids, const Options& opt,
-                  const std::map<std::string, int>& tid_classes, PackedBatch& out);
+void pack_bundles(const Transcriptome& tr, const std::vector<int>& bundle_ids, bool keep_all_cds,
+                  const std::map<std::string, int>& tid_classes, PackedBatch& out,
+                  void* (*alloc)(size_t) = nullptr, void (*dealloc)(void*) = nullptr);
 void build_tid_classes(const Transcriptome& tr, std::map<std::string, int>& out);
 // greedy longest-processing-time split of active bundles over n shards
 void shard_bundles(const Transcriptome& tr, const std::vector<int>& active, int n, std::vector<std::vector<int>>& shards);
@@ -153,8 +165,12 @@ struct Backend {
     int (*release)(orfx_ctx*);
     void (*destroy)(orfx_ctx*);
     const char* (*last_error)();
+    void* (*host_alloc)(size_t);      // optional (may be NULL): pinned host memory for the packed arrays
+    void (*host_free)(void*);
 };
 
+// load + template preparation + bundling (orfanage.cpp:313-367)
+void prepare_transcriptome(const Options& opt, Fasta& fasta, Transcriptome& tr, bool verbose);
 // replaces run() (orfanage.cpp:307-822): prepares, bundles, evaluates through `be`, writes outputs
 int run_orfanage(const Options& opt, const Backend& be);
 

@@ -12,25 +12,32 @@ namespace orfx {
 std::string float_to_string(float v) { char b[64]; snprintf(b, sizeof b, "%f", (double)v); return b; }
 std::string float_ostream(float v) { char b[64]; snprintf(b, sizeof b, "%g", (double)v); return b; }
 
+void PackedBatch::reset() {
+    if (arena) { if (dealloc) dealloc(arena); else free(arena); }
+    arena = nullptr; arena_bytes = 0; dealloc = nullptr;
+    bundle_ids.clear(); tx_global.clear();
+    n_tx = 0; n_segs = 0; seq_bytes = 0; n_queries = 0;
+}
+
 orfx_batch PackedBatch::view() const {
     orfx_batch b;
     memset(&b, 0, sizeof b);
     b.n_bundles = (int32_t)bundle_ids.size();
-    b.n_tx = (int32_t)tx_kind.size();
-    b.n_segs = (int64_t)segs.size();
-    b.seq_bytes = (int64_t)seq.size();
-    b.seq = seq.empty() ? nullptr : seq.data();
-    b.seq_off = seq_off.data();
-    b.bundle_start = bundle_start.data();
-    b.bundle_tx_off = bundle_tx_off.data();
-    b.tx_kind = tx_kind.data();
-    b.tx_strand = tx_strand.data();
-    b.tx_seg_off = tx_seg_off.data();
-    b.tx_cds_start = tx_cds_start.data();
-    b.tx_cds_end = tx_cds_end.data();
-    b.tx_tid_class = tx_tid_class.data();
-    b.segs = segs.data();
-    b.seg_phase = seg_phase.data();
+    b.n_tx = n_tx;
+    b.n_segs = n_segs;
+    b.seq_bytes = seq_bytes;
+    b.seq = seq_bytes ? seq : nullptr;
+    b.seq_off = seq_off;
+    b.bundle_start = bundle_start;
+    b.bundle_tx_off = bundle_tx_off;
+    b.tx_kind = tx_kind;
+    b.tx_strand = tx_strand;
+    b.tx_seg_off = tx_seg_off;
+    b.tx_cds_start = tx_cds_start;
+    b.tx_cds_end = tx_cds_end;
+    b.tx_tid_class = tx_tid_class;
+    b.segs = segs;
+    b.seg_phase = seg_phase;
     return b;
 }
 
@@ -38,10 +45,14 @@ void build_tid_classes(const Transcriptome& tr, std::map<std::string, int>& out)
     for (const Tx& t : tr.txs) out.insert(std::make_pair(t.tid, (int)out.size()));
 }
 
-void pack_bundles(const Transcriptome& tr, const std::vector<int>& bundle_ids, const Options& opt,
-                  const std::map<std::string, int>& tid_classes, PackedBatch& out) {
-    out = PackedBatch();
+// Two passes: size everything, take one arena from the allocator, fill.  The bundle windows (the
+// bulk of the bytes) are copied by several threads.
+void pack_bundles(const Transcriptome& tr, const std::vector<int>& bundle_ids, bool keep_all_cds,
+                  const std::map<std::string, int>& tid_classes, PackedBatch& out,
+                  void* (*alloc)(size_t), void (*dealloc)(void*)) {
+    out.reset();
     out.bundle_ids = bundle_ids;
+    const size_t nb = bundle_ids.size();
     size_t total_seq = 0, total_tx = 0, total_segs = 0;
     for (int bi : bundle_ids) {
         const Bundle& b = tr.bundles[bi];
@@ -49,35 +60,73 @@ void pack_bundles(const Transcriptome& tr, const std::vector<int>& bundle_ids, c
         total_tx += (size_t)b.count;
         for (int i = 0; i < b.count; i++) { const Tx& t = tr.txs[b.first + i]; total_segs += t.is_templ ? t.cds.size() : t.exons.size(); }
     }
-    out.seq.reserve(total_seq + 16);
-    out.segs.reserve(total_segs);
-    out.seg_phase.reserve(total_segs);
-    out.tx_kind.reserve(total_tx);
-    out.seq_off.push_back(0);
-    out.bundle_tx_off.push_back(0);
-    out.tx_seg_off.push_back(0);
-    for (int bi : bundle_ids) {
-        const Bundle& b = tr.bundles[bi];
-        if (tr.fasta) {
-            const std::string* s = tr.fasta->get(tr.seqnames[b.seqid]);
-            out.seq.insert(out.seq.end(), s->begin() + (b.bstart - 1), s->begin() + b.bend);   // Bundle::load_seq, cpp:821-830
-        }
-        out.seq_off.push_back((int64_t)out.seq.size());
-        out.bundle_start.push_back(b.bstart);
-        for (int i = 0; i < b.count; i++) {
+    if (total_tx > (size_t)INT32_MAX || total_segs > (size_t)INT32_MAX) throw std::runtime_error("batch too large for 32-bit transcript / segment indices: shard it");
+    auto up = [](size_t x) { return (x + 255) & ~(size_t)255; };
+    size_t o_seq = 0, o_seq_off = o_seq + up(total_seq + 64), o_bstart = o_seq_off + up((nb + 1) * 8), o_btx = o_bstart + up(nb * 4 + 4),
+           o_kind = o_btx + up((nb + 1) * 4), o_strand = o_kind + up(total_tx + 4), o_segoff = o_strand + up(total_tx + 4),
+           o_cs = o_segoff + up((total_tx + 1) * 4), o_ce = o_cs + up(total_tx * 4 + 4), o_tid = o_ce + up(total_tx * 4 + 4),
+           o_segs = o_tid + up(total_tx * 4 + 4), o_phase = o_segs + up(total_segs * 8 + 8), o_end = o_phase + up(total_segs + 4);
+    out.arena = alloc ? alloc(o_end) : malloc(o_end);
+    if (!out.arena) throw std::runtime_error("cannot allocate " + std::to_string(o_end) + " bytes for the packed batch");
+    out.arena_bytes = o_end;
+    out.dealloc = alloc ? dealloc : nullptr;
+    char* base = (char*)out.arena;
+    out.seq = (uint8_t*)(base + o_seq); out.seq_off = (int64_t*)(base + o_seq_off); out.bundle_start = (int32_t*)(base + o_bstart);
+    out.bundle_tx_off = (int32_t*)(base + o_btx); out.tx_kind = (uint8_t*)(base + o_kind); out.tx_strand = (uint8_t*)(base + o_strand);
+    out.tx_seg_off = (int32_t*)(base + o_segoff); out.tx_cds_start = (int32_t*)(base + o_cs); out.tx_cds_end = (int32_t*)(base + o_ce);
+    out.tx_tid_class = (int32_t*)(base + o_tid); out.segs = (orfx_seg*)(base + o_segs); out.seg_phase = (int8_t*)(base + o_phase);
+    out.n_tx = (int32_t)total_tx; out.n_segs = (int64_t)total_segs; out.seq_bytes = (int64_t)total_seq;
+    out.tx_global.resize(total_tx);
+
+    int64_t so = 0;
+    int32_t x = 0, sg = 0;
+    out.seq_off[0] = 0; out.bundle_tx_off[0] = 0; out.tx_seg_off[0] = 0;
+    for (size_t j = 0; j < nb; j++) {
+        const Bundle& b = tr.bundles[bundle_ids[j]];
+        if (tr.fasta) so += (int64_t)(b.bend - b.bstart + 1);
+        out.seq_off[j + 1] = so;
+        out.bundle_start[j] = b.bstart;
+        for (int i = 0; i < b.count; i++, x++) {
             const Tx& t = tr.txs[b.first + i];
-            out.tx_global.push_back(b.first + i);
-            uint8_t kind = t.is_templ ? ORFX_TX_TEMPLATE : ((opt.keep_all_cds && t.is_coding) ? ORFX_TX_SKIP : ORFX_TX_QUERY);
-            out.tx_kind.push_back(kind);
-            out.tx_strand.push_back((uint8_t)t.strand);
+            out.tx_global[(size_t)x] = b.first + i;
+            const uint8_t kind = t.is_templ ? ORFX_TX_TEMPLATE : ((keep_all_cds && t.is_coding) ? ORFX_TX_SKIP : ORFX_TX_QUERY);
+            if (kind == ORFX_TX_QUERY) out.n_queries++;
+            out.tx_kind[x] = kind;
+            out.tx_strand[x] = (uint8_t)t.strand;
             const Chain& c = t.is_templ ? t.cds : t.exons;
-            for (const Seg& s : c) { out.segs.push_back(orfx_seg{s.s, s.e}); out.seg_phase.push_back(t.is_templ ? s.phase : 0); }
-            out.tx_seg_off.push_back((int32_t)out.segs.size());
-            out.tx_cds_start.push_back(t.is_templ ? t.cds_start : 0);
-            out.tx_cds_end.push_back(t.is_templ ? t.cds_end : 0);
-            out.tx_tid_class.push_back(tid_classes.at(t.tid));
+            for (const Seg& s : c) { out.segs[sg] = orfx_seg{s.s, s.e}; out.seg_phase[sg] = t.is_templ ? s.phase : 0; sg++; }
+            out.tx_seg_off[x + 1] = sg;
+            out.tx_cds_start[x] = t.is_templ ? t.cds_start : 0;
+            out.tx_cds_end[x] = t.is_templ ? t.cds_end : 0;
+            out.tx_tid_class[x] = tid_classes.at(t.tid);
         }
-        out.bundle_tx_off.push_back((int32_t)out.tx_kind.size());
+        out.bundle_tx_off[j + 1] = x;
+    }
+    if (tr.fasta && total_seq) {   // Bundle::load_seq, cpp:821-830
+        std::vector<const std::string*> chrom(tr.seqnames.size(), nullptr);
+        for (size_t k = 0; k < chrom.size(); k++) chrom[k] = tr.fasta->get(tr.seqnames[k]);
+        auto copy_range = [&](size_t j0, size_t j1) {
+            for (size_t j = j0; j < j1; j++) {
+                const Bundle& b = tr.bundles[bundle_ids[j]];
+                memcpy(out.seq + out.seq_off[j], chrom[(size_t)b.seqid]->data() + (b.bstart - 1), (size_t)(b.bend - b.bstart + 1));
+            }
+        };
+        unsigned nthr = total_seq > (64u << 20) ? std::min(8u, std::max(1u, std::thread::hardware_concurrency())) : 1u;
+        if (nthr <= 1) copy_range(0, nb);
+        else {
+            std::vector<std::thread> th;
+            size_t j0 = 0;
+            for (unsigned k = 0; k < nthr; k++) {   // equal byte shares
+                const int64_t want = (int64_t)(total_seq * (k + 1) / nthr);
+                size_t j1 = j0;
+                while (j1 < nb && out.seq_off[j1 + 1] <= want) j1++;
+                if (k == nthr - 1) j1 = nb;
+                th.emplace_back(copy_range, j0, j1);
+                j0 = j1;
+            }
+            for (auto& t : th) t.join();
+        }
+        memset(out.seq + total_seq, 0, 64);
     }
 }
 
@@ -144,38 +193,44 @@ struct Shard {
     orfx_results res;
     int rc = 0;
     std::string err;
-    double ms_pack = 0, ms_eval = 0;
+    double ms_create = 0, ms_pack = 0, ms_eval = 0;
 };
 }  // namespace
 
-int run_orfanage(const Options& opt, const Backend& be) {
-    typedef std::chrono::steady_clock clk;
-    auto t0 = clk::now();
+// Everything upstream of the bundle loop (orfanage.cpp:313-367): load, prepare templates, bundle.
+void prepare_transcriptome(const Options& opt, Fasta& fasta, Transcriptome& tr, bool verbose) {
     if (opt.overhang != 0) throw std::runtime_error("--overhang is not supported by this build (SURVEY.md §8f row 2)");
     if (opt.clean_templ || opt.rescue) throw std::runtime_error("--cleant / --rescue are not supported by this build (SURVEY.md §8f row 1)");
-    fprintf(stderr, "loading reference genome\n");
-    Fasta fasta;
-    Transcriptome tr;
+    auto say = [&](const char* m) { if (verbose) fprintf(stderr, "%s\n", m); };
+    say("loading reference genome");
     if (!opt.reference.empty()) {
         fasta.load(opt.reference);
-        if (fasta.write_fai_if_missing(opt.reference)) fprintf(stderr, "FASTA index rebuilt.\n");
+        if (fasta.write_fai_if_missing(opt.reference)) say("FASTA index rebuilt.");
         tr.fasta = &fasta;
     }
-    fprintf(stderr, "loading reference transcriptomes\n");
+    say("loading reference transcriptomes");
     for (const std::string& k : opt.templates) tr.add(k, true, true);
     tr.build_cds_chains();
     if (opt.clean_templ || !opt.reference.empty()) tr.correct_chain_len();
-    fprintf(stderr, "sorting reference transcriptome\n");
+    say("sorting reference transcriptome");
     tr.sort(false);
     tr.set_cds_as_exons();
     tr.remove_non_coding();
     tr.sort(false);
-    fprintf(stderr, "start removing duplicates\n");
+    say("start removing duplicates");
     tr.deduplicate(opt.use_id);
-    fprintf(stderr, "loading query transcriptome\n");
+    say("loading query transcriptome");
     tr.add(opt.query, false, false);
-    fprintf(stderr, "bundling transcriptome\n");
+    say("bundling transcriptome");
     tr.bundleup(opt.use_id, (uint32_t)opt.overhang);
+}
+
+int run_orfanage(const Options& opt, const Backend& be) {
+    typedef std::chrono::steady_clock clk;
+    auto t0 = clk::now();
+    Fasta fasta;
+    Transcriptome tr;
+    prepare_transcriptome(opt, fasta, tr, true);
     auto t1 = clk::now();
 
     FILE* gtf = fopen(opt.output.c_str(), "w");
@@ -205,18 +260,20 @@ int run_orfanage(const Options& opt, const Backend& be) {
     const int n_shards = (int)opt.devices.size();
     std::vector<std::vector<int>> shard_ids;
     shard_bundles(tr, active, n_shards, shard_ids);
-    std::vector<Shard> shards((size_t)n_shards);
+    std::vector<Shard> shards((size_t)n_shards);   // Shard is not copyable (PackedBatch owns an arena)
     auto work = [&](int k) {
         Shard& s = shards[k];
         try {
-            auto a = clk::now();
-            pack_bundles(tr, shard_ids[k], opt, tid_classes, s.batch);
-            auto b = clk::now();
-            s.ms_pack = std::chrono::duration<double, std::milli>(b - a).count();
             memset(&s.res, 0, sizeof s.res);
-            if (s.batch.bundle_ids.empty()) return;
+            if (shard_ids[k].empty()) return;
+            auto c0 = clk::now();
             s.rc = be.create(&s.ctx, opt.devices[k], &params);
             if (s.rc) { s.err = be.last_error(); return; }
+            auto a = clk::now();
+            s.ms_create = std::chrono::duration<double, std::milli>(a - c0).count();
+            pack_bundles(tr, shard_ids[k], opt.keep_all_cds, tid_classes, s.batch, be.host_alloc, be.host_free);
+            auto b = clk::now();
+            s.ms_pack = std::chrono::duration<double, std::milli>(b - a).count();
             orfx_batch v = s.batch.view();
             s.rc = be.submit(s.ctx, &v);
             if (s.rc) { s.err = be.last_error(); return; }
@@ -369,8 +426,8 @@ int run_orfanage(const Options& opt, const Backend& be) {
         auto ms = [](clk::time_point a, clk::time_point b) { return std::chrono::duration<double, std::milli>(b - a).count(); };
         fprintf(stderr, "[timing] load+prep %.1f ms, evaluate %.1f ms, emit %.1f ms\n", ms(t0, t1), ms(t1, t2), ms(t2, t3));
         for (int k = 0; k < n_shards; k++)
-            fprintf(stderr, "[timing] shard %d: %zu bundles, pack %.1f ms, submit+wait %.1f ms (h2d %.2f, kernels %.2f, d2h %.2f)\n", k,
-                    shards[k].batch.bundle_ids.size(), shards[k].ms_pack, shards[k].ms_eval, shards[k].res.ms_h2d, shards[k].res.ms_kernels, shards[k].res.ms_d2h);
+            fprintf(stderr, "[timing] shard %d: %zu bundles, context %.1f ms, pack %.1f ms, submit+wait %.1f ms (h2d %.2f, kernels %.2f, d2h %.2f)\n", k,
+                    shards[k].batch.bundle_ids.size(), shards[k].ms_create, shards[k].ms_pack, shards[k].ms_eval, shards[k].res.ms_h2d, shards[k].res.ms_kernels, shards[k].res.ms_d2h);
     }
     return 0;
 }

@@ -278,6 +278,14 @@ extern "C" {
 const char* orfx_last_error(void) { return g_err.c_str(); }
 int orfx_abi_version(void) { return ORFX_ABI_VERSION; }
 
+void* orfx_host_alloc(size_t bytes) {
+    void* p = nullptr;
+    cudaError_t e = cudaHostAlloc(&p, bytes ? bytes : 1, cudaHostAllocPortable);
+    if (e != cudaSuccess) { g_err = std::string("cudaHostAlloc: ") + cudaGetErrorString(e); return nullptr; }
+    return p;
+}
+void orfx_host_free(void* p) { if (p) cudaFreeHost(p); }
+
 int orfx_create(orfx_ctx** out, int device, const orfx_params* params) {
     if (!out) return fail(ORFX_E_INVALID, "null out");
     int rc = check_params(params);
