@@ -1,0 +1,465 @@
+"""ctypes bindings for include/orfx.h (device library) and include/orfx_pack.h (host batcher)."""
+import ctypes as C
+import os
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+
+MODES = {"START_MATCH": 0, "ALL": 1, "LONGEST": 2, "LONGEST_MATCH": 3, "BEST": 4, "FIRST": 5}
+STATUS_NOTES = ["-", "no-overlap", "segment_len<3", "cds_len<3", "not_rescued", "missing_stop",
+                "missing_start", "minlen", "dup"]
+
+# aa_table of the reference (common.hpp:268-277): order ARNDCQEGHILKMFPSTWYVBZX*, unknown -> 23
+_AA_ORDER = "ARNDCQEGHILKMFPSTWYVBZX*"
+
+
+def encode_protein(s):
+    """ASCII protein -> 0..23 codes through the reference's aa_table."""
+    lut = np.full(256, 23, dtype=np.uint8)
+    for i, ch in enumerate(_AA_ORDER):
+        lut[ord(ch)] = i
+        lut[ord(ch.lower())] = i
+    return lut[np.frombuffer(s.encode("ascii") if isinstance(s, str) else bytes(s), dtype=np.uint8)]
+
+
+class OrfxError(RuntimeError):
+    def __init__(self, code, msg):
+        super().__init__("orfx error %d: %s" % (code, msg))
+        self.code = code
+
+
+def device_library_path():
+    return os.path.join(_HERE, "liborfx.so")
+
+
+def host_library_path():
+    return os.path.join(_HERE, "liborfx_host.so")
+
+
+def cli_path():
+    return os.path.join(_HERE, "bin", "orfanage")
+
+
+class Params(C.Structure):
+    """orfx_params (include/orfx.h); replaces GlobalParameters, orfanage.cpp:99-142."""
+    _fields_ = [("n_modes", C.c_int32), ("mode_array", C.c_int32 * 8), ("lpi", C.c_int32), ("ilpi", C.c_int32),
+                ("mlpi", C.c_int32), ("cds_minlen", C.c_int32), ("non_aug", C.c_int32), ("overhang", C.c_int32),
+                ("spliced_overhang", C.c_int32), ("has_reference", C.c_int32), ("want_rows", C.c_int32),
+                ("reserved", C.c_int32 * 4)]
+
+    @classmethod
+    def make(cls, mode="LONGEST_MATCH,BEST,START_MATCH,LONGEST,FIRST,ALL", lpi=-1, ilpi=-1, mlpi=-1, minlen=-1,
+             non_aug=False, has_reference=True, want_rows=True, overhang=0, spliced_overhang=False):
+        p = cls()
+        names = [m.strip().upper() for m in mode.split(",")] if isinstance(mode, str) else list(mode)
+        p.n_modes = len(names)
+        for i, m in enumerate(names):
+            p.mode_array[i] = MODES[m] if isinstance(m, str) else int(m)
+        p.lpi, p.ilpi, p.mlpi, p.cds_minlen = lpi, ilpi, mlpi, minlen
+        p.non_aug = int(non_aug)
+        p.overhang = overhang
+        p.spliced_overhang = int(spliced_overhang)
+        p.has_reference = int(has_reference)
+        p.want_rows = int(want_rows)
+        return p
+
+
+class _Seg(C.Structure):
+    _fields_ = [("start", C.c_int32), ("end", C.c_int32)]
+
+
+class _Batch(C.Structure):
+    _fields_ = [("n_bundles", C.c_int32), ("n_tx", C.c_int32), ("n_segs", C.c_int64), ("seq_bytes", C.c_int64),
+                ("seq", C.c_void_p), ("seq_off", C.c_void_p), ("bundle_start", C.c_void_p), ("bundle_tx_off", C.c_void_p),
+                ("tx_kind", C.c_void_p), ("tx_strand", C.c_void_p), ("tx_seg_off", C.c_void_p), ("tx_cds_start", C.c_void_p),
+                ("tx_cds_end", C.c_void_p), ("tx_tid_class", C.c_void_p), ("segs", C.c_void_p), ("seg_phase", C.c_void_p)]
+
+
+class _Best(C.Structure):
+    _fields_ = [("q_tx", C.c_int32), ("t_tx", C.c_int32), ("cds_start", C.c_int32), ("cds_end", C.c_int32),
+                ("duplicity", C.c_int32), ("n_rows", C.c_int32), ("row_off", C.c_int64), ("best_row", C.c_int64),
+                ("lpi", C.c_float), ("ilpi", C.c_float), ("mlpi", C.c_float), ("start_match", C.c_int32)]
+
+
+BEST_DTYPE = np.dtype([("q_tx", "<i4"), ("t_tx", "<i4"), ("cds_start", "<i4"), ("cds_end", "<i4"), ("duplicity", "<i4"),
+                       ("n_rows", "<i4"), ("row_off", "<i8"), ("best_row", "<i8"), ("lpi", "<f4"), ("ilpi", "<f4"),
+                       ("mlpi", "<f4"), ("start_match", "<i4")])
+assert BEST_DTYPE.itemsize == C.sizeof(_Best)
+
+_ROW_I32 = ["row_q_tx", "row_t_tx", "row_seg_start", "row_seg_end", "row_cds_start", "row_cds_end"]
+_ROW_U8 = ["row_status", "row_pass", "row_start_match"]
+_ROW_I32B = ["row_n_dup", "row_qlen", "row_tlen", "row_ulen", "row_query_start", "row_extra", "row_missing", "row_match",
+             "row_outframe", "row_inframe"]
+_ROW_F32 = ["row_lpi", "row_ilpi", "row_mlpi"]
+
+
+class _Results(C.Structure):
+    _fields_ = ([("n_queries", C.c_int32), ("n_rows", C.c_int64), ("best", C.c_void_p)]
+                + [(n, C.c_void_p) for n in _ROW_I32] + [(n, C.c_void_p) for n in _ROW_U8]
+                + [(n, C.c_void_p) for n in _ROW_I32B] + [(n, C.c_void_p) for n in _ROW_F32]
+                + [("print_order", C.c_void_p), ("ms_h2d", C.c_float), ("ms_kernels", C.c_float), ("ms_d2h", C.c_float)])
+
+
+class _AlnOut(C.Structure):
+    _fields_ = [("max", C.c_void_p), ("score", C.c_void_p), ("mqe", C.c_void_p), ("mte", C.c_void_p)]
+
+
+_BATCH_ARRAYS = [("seq", np.uint8), ("seq_off", np.int64), ("bundle_start", np.int32), ("bundle_tx_off", np.int32),
+                 ("tx_kind", np.uint8), ("tx_strand", np.uint8), ("tx_seg_off", np.int32), ("tx_cds_start", np.int32),
+                 ("tx_cds_end", np.int32), ("tx_tid_class", np.int32), ("segs", np.int32), ("seg_phase", np.int8)]
+
+
+def _view(ptr, n, dtype):
+    """numpy view (no copy) of n elements at a raw address."""
+    if not ptr or n <= 0:
+        return np.zeros(0, dtype=dtype)
+    nbytes = int(n) * np.dtype(dtype).itemsize
+    buf = (C.c_char * nbytes).from_address(ptr)
+    return np.frombuffer(buf, dtype=dtype, count=int(n))
+
+
+class Batch:
+    """A packed set of locus bundles (orfx_batch).  Holds numpy arrays (or views of library-owned
+    memory) and the ctypes struct that points at them."""
+
+    def __init__(self, **arrays):
+        self.arrays = {}
+        for name, dt in _BATCH_ARRAYS:
+            a = arrays.get(name)
+            if a is None:
+                a = np.zeros(0, dtype=dt)
+            a = np.ascontiguousarray(a, dtype=dt)
+            self.arrays[name] = a
+        self.owner = arrays.get("owner")
+        a = self.arrays
+        if a["segs"].ndim == 1:
+            a["segs"] = a["segs"].reshape(-1, 2)
+        s = _Batch()
+        s.n_bundles = max(len(a["bundle_tx_off"]) - 1, 0)
+        s.n_tx = len(a["tx_kind"])
+        s.n_segs = a["segs"].shape[0]
+        s.seq_bytes = a["seq"].size
+        for name, _ in _BATCH_ARRAYS:
+            arr = a[name]
+            setattr(s, name, arr.ctypes.data if arr.size else None)
+        # offset arrays must exist even for an empty batch
+        if a["seq_off"].size == 0:
+            self.arrays["seq_off"] = np.zeros(1, dtype=np.int64)
+            s.seq_off = self.arrays["seq_off"].ctypes.data
+        if a["bundle_tx_off"].size == 0:
+            self.arrays["bundle_tx_off"] = np.zeros(1, dtype=np.int32)
+            s.bundle_tx_off = self.arrays["bundle_tx_off"].ctypes.data
+        if a["tx_seg_off"].size == 0:
+            self.arrays["tx_seg_off"] = np.zeros(1, dtype=np.int32)
+            s.tx_seg_off = self.arrays["tx_seg_off"].ctypes.data
+        self.struct = s
+
+    @classmethod
+    def from_struct(cls, s, owner=None):
+        nb, nt, ns = s.n_bundles, s.n_tx, s.n_segs
+        arrays = dict(
+            seq=_view(s.seq, s.seq_bytes, np.uint8), seq_off=_view(s.seq_off, nb + 1, np.int64),
+            bundle_start=_view(s.bundle_start, nb, np.int32), bundle_tx_off=_view(s.bundle_tx_off, nb + 1, np.int32),
+            tx_kind=_view(s.tx_kind, nt, np.uint8), tx_strand=_view(s.tx_strand, nt, np.uint8),
+            tx_seg_off=_view(s.tx_seg_off, nt + 1, np.int32), tx_cds_start=_view(s.tx_cds_start, nt, np.int32),
+            tx_cds_end=_view(s.tx_cds_end, nt, np.int32), tx_tid_class=_view(s.tx_tid_class, nt, np.int32),
+            segs=_view(s.segs, ns * 2, np.int32), seg_phase=_view(s.seg_phase, ns, np.int8))
+        b = cls.__new__(cls)
+        b.arrays = arrays
+        b.arrays["segs"] = b.arrays["segs"].reshape(-1, 2)
+        b.owner = owner
+        cp = _Batch()
+        C.memmove(C.byref(cp), C.byref(s), C.sizeof(_Batch))
+        b.struct = cp
+        return b
+
+    @property
+    def n_queries(self):
+        return int((self.arrays["tx_kind"] == 0).sum())
+
+    @property
+    def h2d_bytes(self):
+        return int(sum(a.nbytes for a in self.arrays.values()))
+
+    def query_nt(self):
+        a = self.arrays
+        seg_len = (a["segs"][:, 1] - a["segs"][:, 0] + 1).astype(np.int64)
+        cum = np.concatenate([[0], np.cumsum(seg_len)])
+        tx_len = cum[a["tx_seg_off"][1:]] - cum[a["tx_seg_off"][:-1]]
+        return int(tx_len[a["tx_kind"] == 0].sum())
+
+    def save(self, path):
+        np.savez_compressed(path, **self.arrays)
+
+    @classmethod
+    def load(cls, path):
+        with np.load(path) as z:
+            return cls(**{k: z[k] for k in z.files})
+
+
+class Results:
+    """Copies of one orfx_results (the library's buffers are only valid until the next submit)."""
+
+    def __init__(self, r, want_rows=True):
+        self.n_queries = int(r.n_queries)
+        self.n_rows = int(r.n_rows)
+        self.best = _view(r.best, self.n_queries, BEST_DTYPE).copy()
+        self.rows = {}
+        if want_rows and r.row_q_tx:
+            n = self.n_rows
+            for name in _ROW_I32 + _ROW_I32B:
+                self.rows[name[4:]] = _view(getattr(r, name), n, np.int32).copy()
+            for name in _ROW_U8:
+                self.rows[name[4:]] = _view(getattr(r, name), n, np.uint8).copy()
+            for name in _ROW_F32:
+                self.rows[name[4:]] = _view(getattr(r, name), n, np.float32).copy()
+            self.rows["print_order"] = _view(r.print_order, n, np.int64).copy()
+        self.ms_h2d, self.ms_kernels, self.ms_d2h = float(r.ms_h2d), float(r.ms_kernels), float(r.ms_d2h)
+
+    def d2h_bytes(self):
+        return int(self.best.nbytes + sum(a.nbytes for a in self.rows.values()))
+
+
+# ---- library loading ---------------------------------------------------------------------------
+_DEVICE_LIB = None
+_HOST_LIB = None
+
+_SUFFIXES = ["last_error", "create", "submit", "wait", "release", "destroy"]
+
+
+def _bind_backend(lib, prefix):
+    """argtypes/restypes of the five backend entry points + last_error under a symbol prefix."""
+    f = lambda n: getattr(lib, prefix + n)  # noqa: E731
+    f("last_error").restype = C.c_char_p
+    f("last_error").argtypes = []
+    f("create").restype = C.c_int
+    f("create").argtypes = [C.POINTER(C.c_void_p), C.c_int, C.POINTER(Params)]
+    f("submit").restype = C.c_int
+    f("submit").argtypes = [C.c_void_p, C.POINTER(_Batch)]
+    f("wait").restype = C.c_int
+    f("wait").argtypes = [C.c_void_p, C.POINTER(_Results)]
+    f("release").restype = C.c_int
+    f("release").argtypes = [C.c_void_p]
+    f("destroy").restype = None
+    f("destroy").argtypes = [C.c_void_p]
+
+
+def load_device_library(path=None):
+    """Loads liborfx.so.  Raises when it is missing: there is no CPU path to fall back to."""
+    global _DEVICE_LIB
+    if _DEVICE_LIB is not None and path is None:
+        return _DEVICE_LIB
+    p = path or device_library_path()
+    if not os.path.exists(p):
+        raise OrfxError(-3, "CUDA library %s is not built (run `make cuda` / __graft_entry__.build()); "
+                            "this package has no CPU fallback" % p)
+    lib = C.CDLL(p)
+    _bind_backend(lib, "orfx_")
+    lib.orfx_abi_version.restype = C.c_int
+    lib.orfx_set_params.restype = C.c_int
+    lib.orfx_set_params.argtypes = [C.c_void_p, C.POINTER(Params)]
+    lib.orfx_host_alloc.restype = C.c_void_p
+    lib.orfx_host_alloc.argtypes = [C.c_size_t]
+    lib.orfx_host_free.restype = None
+    lib.orfx_host_free.argtypes = [C.c_void_p]
+    lib.orfx_upload.restype = C.c_int
+    lib.orfx_upload.argtypes = [C.c_void_p, C.POINTER(_Batch)]
+    lib.orfx_run_resident.restype = C.c_int
+    lib.orfx_run_resident.argtypes = [C.c_void_p, C.POINTER(C.c_int)]
+    lib.orfx_fetch.restype = C.c_int
+    lib.orfx_fetch.argtypes = [C.c_void_p, C.POINTER(_Results)]
+    lib.orfx_kernel_times.restype = C.c_int
+    lib.orfx_kernel_times.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_char_p), C.POINTER(C.c_float), C.POINTER(C.c_int)]
+    lib.orfx_resident_query_nt.restype = C.c_int64
+    lib.orfx_resident_query_nt.argtypes = [C.c_void_p]
+    lib.orfx_get_masks.restype = C.c_int64
+    lib.orfx_get_masks.argtypes = [C.c_void_p, C.c_int32, C.c_void_p, C.c_void_p, C.c_int64]
+    lib.orfx_align_batch.restype = C.c_int
+    lib.orfx_align_batch.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_int64,
+                                     C.c_int, C.c_int, C.POINTER(_AlnOut), C.POINTER(C.c_double), C.POINTER(C.c_float)]
+    if path is None:
+        _DEVICE_LIB = lib
+    return lib
+
+
+def load_host_library(path=None):
+    global _HOST_LIB
+    if _HOST_LIB is not None and path is None:
+        return _HOST_LIB
+    p = path or host_library_path()
+    if not os.path.exists(p):
+        raise OrfxError(-1, "host library %s is not built (run `make host`)" % p)
+    lib = C.CDLL(p)
+    lib.orfxh_last_error.restype = C.c_char_p
+    lib.orfxh_load.restype = C.c_int
+    lib.orfxh_load.argtypes = [C.POINTER(C.c_void_p), C.c_char_p, C.POINTER(C.c_char_p), C.c_int, C.c_char_p, C.c_int, C.c_int]
+    lib.orfxh_count.restype = C.c_int64
+    lib.orfxh_count.argtypes = [C.c_void_p, C.c_int]
+    lib.orfxh_pack.restype = C.c_int
+    lib.orfxh_pack.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.POINTER(_Batch)]
+    lib.orfxh_truncate.restype = C.c_int
+    lib.orfxh_truncate.argtypes = [C.c_void_p, C.c_int64]
+    lib.orfxh_free.restype = None
+    lib.orfxh_free.argtypes = [C.c_void_p]
+    if path is None:
+        _HOST_LIB = lib
+    return lib
+
+
+class Context:
+    """One GPU, one stream (orfx_ctx).  `lib`/`prefix` exist so that the test-suite can drive a
+    second implementation of the same five entry points (the CPU oracle) through this wrapper."""
+
+    def __init__(self, params=None, device=0, lib=None, prefix="orfx_"):
+        self.lib = lib if lib is not None else load_device_library()
+        self.prefix = prefix
+        if lib is not None:
+            _bind_backend(self.lib, prefix)
+        self.params = params if params is not None else Params.make()
+        self.handle = C.c_void_p()
+        self._keep = None
+        self._check(self._f("create")(C.byref(self.handle), device, C.byref(self.params)))
+
+    def _f(self, name):
+        return getattr(self.lib, self.prefix + name)
+
+    def _check(self, rc):
+        if rc != 0:
+            msg = self._f("last_error")()
+            raise OrfxError(rc, msg.decode() if msg else "")
+        return rc
+
+    def set_params(self, params):
+        self.params = params
+        self._check(self.lib.orfx_set_params(self.handle, C.byref(params)))
+
+    def submit(self, batch):
+        self._keep = batch
+        self._check(self._f("submit")(self.handle, C.byref(batch.struct)))
+
+    def wait(self, copy=True):
+        r = _Results()
+        self._check(self._f("wait")(self.handle, C.byref(r)))
+        return Results(r, bool(self.params.want_rows)) if copy else r
+
+    def run(self, batch):
+        """orfx_submit + orfx_wait: the whole path on host buffers."""
+        self.submit(batch)
+        return self.wait()
+
+    # device-resident variant
+    def upload(self, batch):
+        self._keep = batch
+        self._check(self.lib.orfx_upload(self.handle, C.byref(batch.struct)))
+
+    def run_resident(self):
+        n = C.c_int(0)
+        self._check(self.lib.orfx_run_resident(self.handle, C.byref(n)))
+        return n.value
+
+    def fetch(self):
+        r = _Results()
+        self._check(self.lib.orfx_fetch(self.handle, C.byref(r)))
+        return Results(r, bool(self.params.want_rows))
+
+    def kernel_times(self):
+        names = (C.c_char_p * 32)()
+        ms = (C.c_float * 32)()
+        n = C.c_int(0)
+        self._check(self.lib.orfx_kernel_times(self.handle, 32, names, ms, C.byref(n)))
+        return {names[i].decode(): float(ms[i]) for i in range(n.value)}
+
+    def resident_query_nt(self):
+        v = self.lib.orfx_resident_query_nt(self.handle)
+        if v < 0:
+            self._check(int(v))
+        return int(v)
+
+    def masks(self, tx, max_len):
+        words = (max_len + 31) // 32 + 1
+        stop = np.zeros(words, dtype=np.uint32)
+        start = np.zeros(words, dtype=np.uint32)
+        L = self.lib.orfx_get_masks(self.handle, tx, stop.ctypes.data, start.ctypes.data, words)
+        if L < 0:
+            self._check(int(L))
+        nw = (L + 31) // 32
+        return int(L), stop[:nw], start[:nw]
+
+    def align(self, aa, off, pair_q, pair_t, gapo=12, gape=2):
+        """orfx_align_batch: returns dict(max, score, mqe, mte), cells, device ms."""
+        aa = np.ascontiguousarray(aa, dtype=np.uint8)
+        off = np.ascontiguousarray(off, dtype=np.int64)
+        pq = np.ascontiguousarray(pair_q, dtype=np.int32)
+        pt = np.ascontiguousarray(pair_t, dtype=np.int32)
+        n = len(pq)
+        out = {k: np.zeros(max(n, 1), dtype=np.int32) for k in ("max", "score", "mqe", "mte")}
+        o = _AlnOut(out["max"].ctypes.data, out["score"].ctypes.data, out["mqe"].ctypes.data, out["mte"].ctypes.data)
+        cells = C.c_double(0)
+        ms = C.c_float(0)
+        self._check(self.lib.orfx_align_batch(self.handle, aa.ctypes.data, off.ctypes.data, len(off) - 1, pq.ctypes.data,
+                                              pt.ctypes.data, n, gapo, gape, C.byref(o), C.byref(cells), C.byref(ms)))
+        return {k: v[:n] for k, v in out.items()}, cells.value, ms.value
+
+    def close(self):
+        if self.handle:
+            self._f("release")(self.handle)
+            self._f("destroy")(self.handle)
+            self.handle = C.c_void_p()
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+class Workload:
+    """Loaded + prepared + bundled transcriptome (orfxh_workload): orfanage.cpp:313-367."""
+
+    def __init__(self, query, templates, reference=None, use_id=False, keep_all_cds=False):
+        self.lib = load_host_library()
+        self.handle = C.c_void_p()
+        arr = (C.c_char_p * len(templates))(*[t.encode() for t in templates])
+        rc = self.lib.orfxh_load(C.byref(self.handle), query.encode(), arr, len(templates),
+                                 reference.encode() if reference else None, int(use_id), int(keep_all_cds))
+        if rc != 0:
+            raise OrfxError(rc, self.lib.orfxh_last_error().decode())
+
+    def count(self, what):
+        return int(self.lib.orfxh_count(self.handle, {"bundles": 0, "active_bundles": 1, "queries": 2, "templates": 3,
+                                                      "all_queries": 4, "query_nt": 5}[what]))
+
+    def truncate(self, n_active):
+        self.lib.orfxh_truncate(self.handle, int(n_active))
+
+    def pack(self, shard=0, n_shards=1, pinned=False):
+        """Returns a Batch viewing arrays owned by this workload (valid until the next pack of the
+        same shard or close())."""
+        s = _Batch()
+        alloc = dealloc = None
+        if pinned:
+            dev = load_device_library()
+            alloc = C.cast(dev.orfx_host_alloc, C.c_void_p)
+            dealloc = C.cast(dev.orfx_host_free, C.c_void_p)
+        rc = self.lib.orfxh_pack(self.handle, shard, n_shards, alloc, dealloc, C.byref(s))
+        if rc != 0:
+            raise OrfxError(rc, self.lib.orfxh_last_error().decode())
+        return Batch.from_struct(s, owner=self)
+
+    def close(self):
+        if self.handle:
+            self.lib.orfxh_free(self.handle)
+            self.handle = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
