@@ -44,6 +44,9 @@ int orfxh_pack(orfxh_workload* w, int shard, int n_shards, void* (*alloc)(size_t
 /* Keeps only the first n active bundles of the workload (bounded samples for CPU baselines). */
 int orfxh_truncate(orfxh_workload* w, int64_t n_active_bundles);
 
+/* transcript_id of transcript `tx` of the batch last packed for `shard`; NULL when out of range. */
+const char* orfxh_tx_id(const orfxh_workload* w, int shard, int32_t tx);
+
 void orfxh_free(orfxh_workload* w);
 
 #ifdef __cplusplus

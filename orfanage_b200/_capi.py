@@ -300,6 +300,8 @@ def load_host_library(path=None):
     lib.orfxh_pack.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.POINTER(_Batch)]
     lib.orfxh_truncate.restype = C.c_int
     lib.orfxh_truncate.argtypes = [C.c_void_p, C.c_int64]
+    lib.orfxh_tx_id.restype = C.c_char_p
+    lib.orfxh_tx_id.argtypes = [C.c_void_p, C.c_int, C.c_int32]
     lib.orfxh_free.restype = None
     lib.orfxh_free.argtypes = [C.c_void_p]
     if path is None:
@@ -452,6 +454,10 @@ class Workload:
         if rc != 0:
             raise OrfxError(rc, self.lib.orfxh_last_error().decode())
         return Batch.from_struct(s, owner=self)
+
+    def tx_id(self, tx, shard=0):
+        v = self.lib.orfxh_tx_id(self.handle, shard, tx)
+        return v.decode() if v is not None else None
 
     def close(self):
         if self.handle:

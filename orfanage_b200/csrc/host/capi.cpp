@@ -91,6 +91,13 @@ int orfxh_truncate(orfxh_workload* w, int64_t n_active_bundles) {
     return ORFX_OK;
 }
 
+const char* orfxh_tx_id(const orfxh_workload* w, int shard, int32_t tx) {
+    if (!w || shard < 0 || (size_t)shard >= w->packed.size() || !w->packed[(size_t)shard]) return nullptr;
+    const PackedBatch& pb = *w->packed[(size_t)shard];
+    if (tx < 0 || (size_t)tx >= pb.tx_global.size()) return nullptr;
+    return w->tr.txs[(size_t)pb.tx_global[(size_t)tx]].tid.c_str();
+}
+
 void orfxh_free(orfxh_workload* w) { delete w; }
 
 }  // extern "C"

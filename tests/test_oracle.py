@@ -1,0 +1,134 @@
+"""CPU suite, part 1: the oracle (CPU restatement) is pinned against the reference.
+
+  * byte parity of oracle/orfanage_oracle_cli with oracle/_ref/orfanage_ref (the reference's own sources
+    compiled against the gclib stand-in) on seeded synthetic inputs over an option grid;
+  * byte parity with the committed goldens (tests/golden/, written by make_golden.py from the reference);
+  * config 1 at the C-ABI level: committed packed batch -> oracle library -> the reference's stats rows;
+  * constants: codon table, mat50, aa_table against the literals parsed from src/common.hpp;
+  * the docs' worked orfcompare rows reproduce from the reference build (pins the gclib stand-in).
+"""
+import json
+import os
+import re
+import subprocess
+
+import numpy as np
+import pytest
+
+import orfanage_b200 as ob
+from conftest import GOLDEN, ORACLE_CLI, REF_BIN, ROOT, run_cli, template_files
+from fmt import stats_lines
+from golden.make_golden import SYNTH_ARGS, SYNTH_RUNS, SYNTH_SEEDS
+
+OPTION_GRID = [
+    ["--reference", "genome.fa", "--query", "query.gtf"],
+    ["--reference", "genome.fa", "--query", "query.gtf", "--mode", "BEST", "--cleanq"],
+    ["--reference", "genome.fa", "--query", "query.gtf", "--mode", "ALL"],
+    ["--reference", "genome.fa", "--query", "query.gtf", "--mode", "START_MATCH,FIRST"],
+    ["--reference", "genome.fa", "--query", "query.gtf", "--mode", "LONGEST", "--non_aug"],
+    ["--reference", "genome.fa", "--query", "query.gtf", "--mode", "LONGEST_MATCH,BEST", "--lpi", "50", "--ilpi", "60",
+     "--mlpi", "70", "--minlen", "300"],
+    ["--query", "query.gtf", "--mode", "LONGEST_MATCH,BEST"],
+    ["--query", "query.gtf", "--mode", "ALL", "--lpi", "80"],
+    ["--reference", "genome.fa", "--query", "query.gtf", "--use_id"],
+]
+SELF_GRID = [   # query file = a template file (queries that carry a CDS)
+    (["--reference", "genome.fa", "--query", "template2.gtf", "--keep_all_cds"], ["template1.gtf"]),
+    (["--reference", "genome.fa", "--query", "template3.gtf", "--keep_cds_if_not_found", "--mode", "FIRST"], ["template1.gtf"]),
+    (["--reference", "genome.fa", "--query", "template3.gtf", "--mode", "BEST"], ["template1.gtf"]),
+]
+
+needs_ref_bin = pytest.mark.skipif(not os.path.exists(REF_BIN), reason="oracle/_ref/orfanage_ref not built")
+
+
+def compare_clis(cand, d, args, templates=None):
+    rc_r, gtf_r, tsv_r, err_r = run_cli(REF_BIN, d, args + ["--threads", "1"], "ref", templates)
+    rc_o, gtf_o, tsv_o, err_o = run_cli(cand, d, args, "cand", templates)
+    assert rc_o == rc_r, (args, err_o[-400:], err_r[-400:])
+    assert gtf_o == gtf_r, "GTF differs for %s" % args
+    assert tsv_o == tsv_r, "stats TSV differs for %s" % args
+    return len(gtf_r)
+
+
+@needs_ref_bin
+@pytest.mark.parametrize("seed", [1, 2])
+def test_oracle_cli_matches_reference_binary(synth, seed):
+    d = synth(seed, loci=60, template_files=3)
+    total = 0
+    for args in OPTION_GRID:
+        total += compare_clis(ORACLE_CLI, d, args)
+    for args, tpl in SELF_GRID:
+        total += compare_clis(ORACLE_CLI, d, args, tpl)
+    assert total > 100000   # the runs produced real output
+
+
+@pytest.mark.parametrize("seed", SYNTH_SEEDS)
+def test_oracle_cli_matches_goldens(tmp_path, seed):
+    d = str(tmp_path)
+    subprocess.run([os.path.join(ROOT, "tools", "orfx_synth"), "--out", d, "--seed", str(seed)] + SYNTH_ARGS, check=True,
+                   capture_output=True)
+    for tag, args in SYNTH_RUNS:
+        rc, gtf, tsv, err = run_cli(ORACLE_CLI, d, args, "o_" + tag, ["template1.gtf", "template2.gtf"])
+        assert rc == 0, err
+        base = os.path.join(GOLDEN, "synth_s%d_%s" % (seed, tag))
+        assert gtf == open(base + ".gtf", "rb").read(), tag
+        assert tsv == open(base + ".tsv", "rb").read(), tag
+
+
+def test_config1_oracle_library_matches_reference_rows(oracle_lib):
+    batch = ob.Batch.load(os.path.join(GOLDEN, "c1_batch.npz"))
+    names = json.load(open(os.path.join(GOLDEN, "c1_names.json")))["tx_id"]
+    with ob.Context(ob.Params.make(mode="BEST"), lib=oracle_lib, prefix="orfx_oracle_") as cx:
+        res = cx.run(batch)
+    want = open(os.path.join(GOLDEN, "c1_ref.tsv")).read().splitlines()[1:]
+    assert stats_lines(res, names) == want
+    # the chosen ORFs are the CDS rows of the reference's GTF
+    gtf = open(os.path.join(GOLDEN, "c1_ref.gtf")).read()
+    for b in res.best:
+        tid = names[b["q_tx"]]
+        cds = [(int(m.group(1)), int(m.group(2))) for m in
+               re.finditer(r"\tCDS\t(\d+)\t(\d+)\t[^\n]*transcript_id \"%s\";" % re.escape(tid), gtf)]
+        if b["t_tx"] < 0:
+            assert not cds
+        else:
+            assert (min(c[0] for c in cds), max(c[1] for c in cds)) == (b["cds_start"], b["cds_end"])
+
+
+def test_codon_table_matches_reference_literal():
+    want = open(os.path.join(GOLDEN, "codon_map.txt")).read().split()
+    hdr = open(os.path.join(ROOT, "include", "orfx_codon_table.h")).read()
+    got = re.findall(r"\"([A-Z]{3}[A-Z.])\"", hdr)
+    assert sorted(got) == sorted(want) and len(got) == 180
+    if os.path.exists("/root/reference/src/common.hpp"):   # the golden itself is current
+        src = open("/root/reference/src/common.hpp").read()
+        pairs = re.findall(r"\{\s*\"([A-Z]{3})\"\s*,\s*'(.)'\s*\}", src)
+        assert sorted(c + a for c, a in pairs) == sorted(want)
+
+
+def test_mat50_and_aa_table_match_reference_literals():
+    mat = np.load(os.path.join(GOLDEN, "mat50.npy"))
+    cu = open(os.path.join(ROOT, "orfanage_b200", "csrc", "align.cu")).read()
+    body = cu[cu.index("c_mat50[24 * 24] = {"):]
+    body = body[body.index("{") + 1:body.index("};")]
+    got = np.array([int(x) for x in re.findall(r"-?\d+", body)], dtype=np.int8).reshape(24, 24)
+    assert (got == mat).all()
+    assert (mat == mat.T).all()
+    table = np.load(os.path.join(GOLDEN, "aa_table.npy"))
+    all_bytes = bytes(range(128))
+    assert (ob.encode_protein(all_bytes) == table).all()
+
+
+def test_orfcompare_known_answers():
+    rows = [l.rstrip("\n").split("\t") for l in open(os.path.join(GOLDEN, "orfcompare_kat.tsv"))]
+    # docs/content/csvs/orfcompare_stats.csv, Examples 1 and 2
+    assert rows[1][:12] == ["CHS.8812.2", "ENST00000300146.10", "1566", "2313", "1566", "1566", "0", "0", "747", "92.5532",
+                            "92.5532", "92.5532"]
+    assert rows[2][:12] == ["CHS.8812.5", "ENST00000300146.10", "2310", "2313", "2310", "2310", "0", "0", "3", "99.8703",
+                            "99.8703", "99.8703"]
+    cmp_bin = os.path.join(ROOT, "oracle", "_ref", "orfcompare_ref")
+    if os.path.exists(cmp_bin) and os.path.exists("/root/reference/example/patl.chess3.gtf"):
+        out = "/tmp/orfx_kat.tsv"
+        subprocess.run([cmp_bin, "--query", "/root/reference/example/patl.chess3.gtf", "--template",
+                        "/root/reference/example/patl.gencode.gtf", "--output", out, "--threads", "1"], check=True,
+                       capture_output=True)
+        assert open(out).read() == open(os.path.join(GOLDEN, "orfcompare_kat.tsv")).read()
