@@ -183,6 +183,11 @@ int  orfx_run_resident(orfx_ctx* ctx, int* n_launches);
 int  orfx_fetch(orfx_ctx* ctx, orfx_results* out);
 /* Per-kernel device times of the last run, in launch order.  names[i] are static strings. */
 int  orfx_kernel_times(orfx_ctx* ctx, int max_n, const char** names, float* ms, int* n);
+/* Device time of the last run of the path (first to last kernel, CUDA events on the launch stream;
+ * includes the one host round trip that sizes the row buffers), and its number of kernel launches.
+ * Valid after orfx_wait or orfx_run_resident. */
+float orfx_last_run_ms(orfx_ctx* ctx);
+int   orfx_last_run_launches(orfx_ctx* ctx);
 /* Sum of spliced query nucleotides in the resident batch (codon-scan roofline numerator). */
 int64_t orfx_resident_query_nt(orfx_ctx* ctx);
 

@@ -271,6 +271,10 @@ def load_device_library(path=None):
     lib.orfx_fetch.argtypes = [C.c_void_p, C.POINTER(_Results)]
     lib.orfx_kernel_times.restype = C.c_int
     lib.orfx_kernel_times.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_char_p), C.POINTER(C.c_float), C.POINTER(C.c_int)]
+    lib.orfx_last_run_ms.restype = C.c_float
+    lib.orfx_last_run_ms.argtypes = [C.c_void_p]
+    lib.orfx_last_run_launches.restype = C.c_int
+    lib.orfx_last_run_launches.argtypes = [C.c_void_p]
     lib.orfx_resident_query_nt.restype = C.c_int64
     lib.orfx_resident_query_nt.argtypes = [C.c_void_p]
     lib.orfx_get_masks.restype = C.c_int64
@@ -371,6 +375,12 @@ class Context:
         n = C.c_int(0)
         self._check(self.lib.orfx_kernel_times(self.handle, 32, names, ms, C.byref(n)))
         return {names[i].decode(): float(ms[i]) for i in range(n.value)}
+
+    def last_run_ms(self):
+        return float(self.lib.orfx_last_run_ms(self.handle))
+
+    def last_run_launches(self):
+        return int(self.lib.orfx_last_run_launches(self.handle))
 
     def resident_query_nt(self):
         v = self.lib.orfx_resident_query_nt(self.handle)

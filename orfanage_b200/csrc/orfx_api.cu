@@ -92,6 +92,8 @@ struct orfx_ctx {
     int64_t n_queries = 0, n_rows = 0, n_tiles = 0, n_words = 0;
     cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};
     cudaEvent_t st_ev[ST_N][2];
+    cudaEvent_t run_ev[2] = {nullptr, nullptr};
+    float run_ms = 0;
     float st_ms[ST_N];
     int n_launches = 0;
 };
@@ -175,7 +177,8 @@ int run_path(orfx_ctx* c) {
     DevBatch& B = c->B;
     c->n_launches = 0;
     c->n_queries = c->n_rows = c->n_tiles = c->n_words = 0;
-    if (B.n_tx == 0) return ORFX_OK;
+    cudaEventRecord(c->run_ev[0], s);
+    if (B.n_tx == 0) { cudaEventRecord(c->run_ev[1], s); return ORFX_OK; }
     stage_begin(c, ST_PREP);
     c->n_launches += launch_prep(B, c->d_cnt_q.as<int64_t>(), c->d_cnt_words.as<int64_t>(), c->d_cnt_tiles.as<int64_t>(), c->d_scan_tmp.as<int64_t>(), s);
     stage_end(c, ST_PREP);
@@ -228,8 +231,17 @@ int run_path(orfx_ctx* c) {
     stage_begin(c, ST_SELECT);
     c->n_launches += launch_select(B, R, c->P, (int)nq, c->d_best.as<orfx_best>(), c->d_ord.as<int32_t>(), s);
     stage_end(c, ST_SELECT);
+    cudaEventRecord(c->run_ev[1], s);
     CU(cudaGetLastError());
     return ORFX_OK;
+}
+
+void collect_times(orfx_ctx* c) {
+    c->run_ms = 0;
+    for (int i = 0; i < ST_N; i++) c->st_ms[i] = 0;
+    if (c->B.n_tx == 0) return;
+    cudaEventElapsedTime(&c->run_ms, c->run_ev[0], c->run_ev[1]);
+    for (int i = 0; i < ST_N; i++) cudaEventElapsedTime(&c->st_ms[i], c->st_ev[i][0], c->st_ev[i][1]);
 }
 
 int download_results(orfx_ctx* c) {
@@ -307,6 +319,7 @@ int orfx_create(orfx_ctx** out, int device, const orfx_params* params) {
     if (cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking) != cudaSuccess) { delete c; return fail(ORFX_E_CUDA, "cudaStreamCreate failed"); }
     for (auto& ev : c->ev) cudaEventCreate(&ev);
     for (int i = 0; i < ST_N; i++) { cudaEventCreate(&c->st_ev[i][0]); cudaEventCreate(&c->st_ev[i][1]); c->st_ms[i] = 0; }
+    cudaEventCreate(&c->run_ev[0]); cudaEventCreate(&c->run_ev[1]);
     *out = c;
     return ORFX_OK;
 }
@@ -344,6 +357,7 @@ int orfx_wait(orfx_ctx* c, orfx_results* out) {
     CU(cudaGetLastError());
     c->pending = false;
     c->have_results = true;
+    collect_times(c);
     fill_results(c, out);
     cudaEventElapsedTime(&out->ms_h2d, c->ev[0], c->ev[1]);
     cudaEventElapsedTime(&out->ms_kernels, c->ev[1], c->ev[2]);
@@ -375,6 +389,7 @@ void orfx_destroy(orfx_ctx* c) {
     for (auto& b : c->h_u8) b.free_();
     for (auto& ev : c->ev) if (ev) cudaEventDestroy(ev);
     for (int i = 0; i < ST_N; i++) { cudaEventDestroy(c->st_ev[i][0]); cudaEventDestroy(c->st_ev[i][1]); }
+    cudaEventDestroy(c->run_ev[0]); cudaEventDestroy(c->run_ev[1]);
     cudaStreamDestroy(c->stream);
     delete c;
 }
@@ -396,7 +411,7 @@ int orfx_run_resident(orfx_ctx* c, int* n_launches) {
     if (rc) return rc;
     CU(cudaStreamSynchronize(c->stream));
     CU(cudaGetLastError());
-    for (int i = 0; i < ST_N; i++) cudaEventElapsedTime(&c->st_ms[i], c->st_ev[i][0], c->st_ev[i][1]);
+    collect_times(c);
     if (n_launches) *n_launches = c->n_launches;
     return ORFX_OK;
 }
@@ -419,6 +434,9 @@ int orfx_kernel_times(orfx_ctx* c, int max_n, const char** names, float* ms, int
     *n = k;
     return ORFX_OK;
 }
+
+float orfx_last_run_ms(orfx_ctx* c) { return c ? c->run_ms : -1.f; }
+int orfx_last_run_launches(orfx_ctx* c) { return c ? c->n_launches : -1; }
 
 int64_t orfx_resident_query_nt(orfx_ctx* c) {
     if (!c || !c->resident) return fail(ORFX_E_STATE, "no resident batch");

@@ -1,0 +1,119 @@
+"""GPU suite: protein alignment kernel (orfx_align_batch) against the scalar CPU restatement of the
+ksw2 extension recurrence (oracle/orfx_oracle.cpp: orfx_oracle_align — parity UNPINNED against ksw2
+itself) and against hand-computable cases."""
+import ctypes as C
+import os
+
+import numpy as np
+import pytest
+
+import orfanage_b200 as ob
+from conftest import GOLDEN
+
+pytestmark = pytest.mark.gpu
+
+MAT = np.load(os.path.join(GOLDEN, "mat50.npy"))
+# background amino-acid frequencies (order ARNDCQEGHILKMFPSTWYV), proteome-like
+FREQ = np.array([8.25, 5.53, 4.06, 5.45, 1.37, 3.93, 6.75, 7.07, 2.27, 5.96, 9.66, 5.84, 2.42, 3.86, 4.70, 6.56, 5.34, 1.08,
+                 2.92, 6.87])
+FREQ = FREQ / FREQ.sum()
+
+
+def oracle_align(lib, q, t, gapo=12, gape=2):
+    lib.orfx_oracle_align.restype = C.c_int
+    lib.orfx_oracle_align.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_int, C.c_int,
+                                      C.POINTER(C.c_int32), C.POINTER(C.c_int32), C.POINTER(C.c_int32), C.POINTER(C.c_int32)]
+    o = [C.c_int32() for _ in range(4)]
+    q = np.ascontiguousarray(q, dtype=np.uint8)
+    t = np.ascontiguousarray(t, dtype=np.uint8)
+    mat = np.ascontiguousarray(MAT, dtype=np.int8)
+    lib.orfx_oracle_align(q.ctypes.data, len(q), t.ctypes.data, len(t), mat.ctypes.data, 24, gapo, gape, *[C.byref(x) for x in o])
+    return tuple(x.value for x in o)
+
+
+def mutate(rng, s, sub, n_indel):
+    s = s.copy()
+    m = rng.random(len(s)) < sub
+    s[m] = rng.choice(20, size=int(m.sum()), p=FREQ)
+    for _ in range(n_indel):
+        p = int(rng.integers(0, max(len(s), 1)))
+        k = int(rng.integers(1, 12))
+        if rng.random() < 0.5:
+            s = np.concatenate([s[:p], s[p + k:]])
+        else:
+            s = np.concatenate([s[:p], rng.choice(20, size=k, p=FREQ).astype(np.uint8), s[p:]])
+    return s if len(s) else np.array([0], dtype=np.uint8)
+
+
+def make_pairs(rng, lengths):
+    seqs, pq, pt = [], [], []
+    for L in lengths:
+        a = rng.choice(20, size=int(L), p=FREQ).astype(np.uint8)
+        b = mutate(rng, a, rng.uniform(0.05, 0.4), int(rng.integers(0, 4))).astype(np.uint8)
+        pq.append(len(seqs)); seqs.append(a)
+        pt.append(len(seqs)); seqs.append(b)
+    off = np.concatenate([[0], np.cumsum([len(s) for s in seqs])]).astype(np.int64)
+    return seqs, np.concatenate(seqs), off, np.array(pq, dtype=np.int32), np.array(pt, dtype=np.int32)
+
+
+@pytest.fixture(scope="module")
+def gpu():
+    cx = ob.Context(ob.Params.make(), device=0)
+    yield cx
+    cx.close()
+
+
+def test_alignment_matches_scalar_restatement(gpu, oracle_lib):
+    rng = np.random.default_rng(2026)
+    lengths = list(rng.integers(1, 40, size=40)) + list(np.exp(rng.normal(np.log(400), 0.9, size=150)).clip(50, 4000).astype(int)) \
+        + [255, 256, 257, 511, 512, 513, 1024, 2048, 3000]
+    seqs, aa, off, pq, pt = make_pairs(rng, lengths)
+    out, cells, ms = gpu.align(aa, off, pq, pt)
+    assert cells == sum(len(seqs[q]) * len(seqs[t]) for q, t in zip(pq, pt))
+    for i, (q, t) in enumerate(zip(pq, pt)):
+        want = oracle_align(oracle_lib, seqs[q], seqs[t])
+        got = (int(out["max"][i]), int(out["score"][i]), int(out["mqe"][i]), int(out["mte"][i]))
+        assert got == want, "pair %d (qlen %d, tlen %d): %s != %s" % (i, len(seqs[q]), len(seqs[t]), got, want)
+
+
+def test_alignment_other_gap_costs_and_wildcards(gpu, oracle_lib):
+    rng = np.random.default_rng(7)
+    seqs, aa, off, pq, pt = make_pairs(rng, [30, 333, 700, 1500])
+    aa = aa.copy()
+    aa[rng.integers(0, len(aa), size=40)] = rng.integers(20, 24, size=40)   # B Z X *
+    seqs = [aa[off[i]:off[i + 1]] for i in range(len(off) - 1)]
+    for gapo, gape in [(12, 2), (10, 1), (5, 3), (0, 1)]:
+        out, _, _ = gpu.align(aa, off, pq, pt, gapo, gape)
+        for i, (q, t) in enumerate(zip(pq, pt)):
+            want = oracle_align(oracle_lib, seqs[q], seqs[t], gapo, gape)
+            assert (int(out["max"][i]), int(out["score"][i]), int(out["mqe"][i]), int(out["mte"][i])) == want
+
+
+def test_alignment_hand_computable_cases(gpu):
+    # identical strings: score = sum of the diagonal entries; a single k-residue gap costs gapo + k*gape
+    s = ob.encode_protein("MKTAYIAKQRQISFVKSHFSRQLEERLGLIEVQAPILSRVGDGTQDNLSGAEKAVQVKVKALPDAQFEVVHSLAKWKR")
+    diag = int(MAT[s, s].sum())
+    gapped = np.concatenate([s[:30], s[35:]])   # 5 residues deleted from the target
+    aa = np.concatenate([s, s, gapped])
+    off = np.array([0, len(s), 2 * len(s), 2 * len(s) + len(gapped)], dtype=np.int64)
+    out, _, _ = gpu.align(aa, off, [0, 0], [1, 2])
+    assert out["score"][0] == diag and out["max"][0] == diag and out["mqe"][0] == diag and out["mte"][0] == diag
+    assert out["score"][1] == diag - int(MAT[s[30:35], s[30:35]].sum()) - (12 + 5 * 2)
+
+
+def test_alignment_titin_class_pair(gpu, oracle_lib):
+    """One long pair (block-striped path, int32 scores beyond the int16 range)."""
+    rng = np.random.default_rng(99)
+    seqs, aa, off, pq, pt = make_pairs(rng, [9000])
+    out, cells, ms = gpu.align(aa, off, pq, pt)
+    want = oracle_align(oracle_lib, seqs[0], seqs[1])
+    assert (int(out["max"][0]), int(out["score"][0]), int(out["mqe"][0]), int(out["mte"][0])) == want
+    assert want[0] > 32767
+
+
+def test_alignment_empty_inputs(gpu):
+    out, cells, _ = gpu.align(np.zeros(0, dtype=np.uint8), np.array([0], dtype=np.int64), [], [])
+    assert cells == 0 and len(out["max"]) == 0
+    aa = np.array([3, 4, 5], dtype=np.uint8)
+    out, _, _ = gpu.align(aa, np.array([0, 3, 3], dtype=np.int64), [0], [1])   # empty target
+    assert out["max"][0] == 0

@@ -1,0 +1,149 @@
+"""GPU suite: the CUDA path, called through the C-ABI, against the CPU oracle — bit-exact.
+
+Everything here needs a B200 (`-m gpu`); the oracle and the reference binary are only the checkers.
+"""
+import json
+import os
+import subprocess
+
+import numpy as np
+import pytest
+
+import orfanage_b200 as ob
+from conftest import GOLDEN, REF_BIN, ROOT, run_cli, template_files
+from fmt import stats_lines
+from golden.make_golden import SYNTH_ARGS, SYNTH_RUNS, SYNTH_SEEDS
+from test_oracle import OPTION_GRID, SELF_GRID, compare_clis
+
+pytestmark = pytest.mark.gpu
+
+PARAM_GRID = [
+    dict(mode="LONGEST_MATCH,BEST"),
+    dict(),   # the default cascade
+    dict(mode="ALL"),
+    dict(mode="START_MATCH,FIRST"),
+    dict(mode="LONGEST", non_aug=True),
+    dict(mode="BEST", lpi=50, ilpi=60, mlpi=70, minlen=300),
+    dict(mode="LONGEST_MATCH,BEST", has_reference=False),
+    dict(mode="FIRST,LONGEST", want_rows=False),
+]
+
+
+def assert_same_results(got, want, what=""):
+    assert got.n_queries == want.n_queries and got.n_rows == want.n_rows, what
+    for f in want.best.dtype.names:
+        assert (got.best[f].view(np.uint32 if want.best[f].dtype == np.float32 else want.best[f].dtype)
+                == want.best[f].view(np.uint32 if want.best[f].dtype == np.float32 else want.best[f].dtype)).all(), (what, "best." + f)
+    assert set(got.rows) == set(want.rows), what
+    for k in want.rows:
+        assert got.rows[k].tobytes() == want.rows[k].tobytes(), (what, "row field " + k)
+
+
+@pytest.fixture(scope="module")
+def gpu():
+    cx = ob.Context(ob.Params.make(), device=0)
+    yield cx
+    cx.close()
+
+
+@pytest.mark.parametrize("seed,kw", [(21, dict(loci=80)), (22, dict(loci=60, titin=0.15, iupac=0.002)),
+                                     (23, dict(loci=120, queries=14, templates=5, template_files=3))])
+def test_results_match_oracle_bit_for_bit(synth, oracle_lib, gpu, seed, kw):
+    d = synth(seed, **kw)
+    w = ob.Workload(os.path.join(d, "query.gtf"), template_files(d), os.path.join(d, "genome.fa"))
+    batch = w.pack()
+    assert batch.n_queries > 200
+    for pk in PARAM_GRID:
+        params = ob.Params.make(**pk)
+        gpu.set_params(params)
+        got = gpu.run(batch)
+        with ob.Context(params, lib=oracle_lib, prefix="orfx_oracle_") as ox:
+            want = ox.run(batch)
+        assert_same_results(got, want, "seed %d params %s" % (seed, pk))
+        # the device-resident variant gives the same answers as submit/wait
+        gpu.upload(batch)
+        assert gpu.run_resident() > 0
+        assert_same_results(gpu.fetch(), want, "resident, seed %d params %s" % (seed, pk))
+    w.close()
+
+
+def test_codon_scan_masks_match_oracle(synth, oracle_lib, gpu):
+    """Per-stage check (SURVEY.md §4 iii): stop / ATG masks of every query transcript, soft-masked and
+    IUPAC bases included, both strands, against SEQ::translate semantics restated in the oracle."""
+    import ctypes as C
+    d = synth(24, loci=60, lower=0.5, iupac=0.01, titin=0.1)
+    w = ob.Workload(os.path.join(d, "query.gtf"), template_files(d), os.path.join(d, "genome.fa"))
+    batch = w.pack()
+    gpu.set_params(ob.Params.make(mode="BEST"))
+    gpu.upload(batch)
+    gpu.run_resident()
+    oracle_lib.orfx_oracle_masks.restype = C.c_int64
+    oracle_lib.orfx_oracle_masks.argtypes = [C.c_void_p, C.c_int32, C.c_void_p, C.c_void_p, C.c_int64]
+    a = batch.arrays
+    seg_len = a["segs"][:, 1] - a["segs"][:, 0] + 1
+    n_checked = strands = 0
+    seen = set()
+    for tx in np.nonzero(a["tx_kind"] == 0)[0]:
+        L = int(seg_len[a["tx_seg_off"][tx]:a["tx_seg_off"][tx + 1]].sum())
+        gl, gstop, gstart = gpu.masks(int(tx), L)
+        words = (L + 31) // 32
+        ostop = np.zeros(words, dtype=np.uint32)
+        ostart = np.zeros(words, dtype=np.uint32)
+        ol = oracle_lib.orfx_oracle_masks(C.byref(batch.struct), int(tx), ostop.ctypes.data, ostart.ctypes.data, words)
+        assert gl == ol == L
+        assert (gstop == ostop).all() and (gstart == ostart).all(), "masks differ for transcript %d" % tx
+        assert ostop.any()
+        n_checked += 1
+        seen.add(int(a["tx_strand"][tx]))
+    assert n_checked > 200 and seen == {ord("+"), ord("-")}
+    w.close()
+
+
+def test_config1_golden_batch(gpu):
+    """Config 1 (example/query.gtf x example/template.gtf, random chr19, --mode BEST): committed packed
+    batch -> CUDA path -> the reference's own stats rows."""
+    batch = ob.Batch.load(os.path.join(GOLDEN, "c1_batch.npz"))
+    names = json.load(open(os.path.join(GOLDEN, "c1_names.json")))["tx_id"]
+    gpu.set_params(ob.Params.make(mode="BEST"))
+    res = gpu.run(batch)
+    want = open(os.path.join(GOLDEN, "c1_ref.tsv")).read().splitlines()[1:]
+    assert stats_lines(res, names) == want
+
+
+@pytest.mark.parametrize("seed", SYNTH_SEEDS)
+def test_cli_matches_goldens(tmp_path, seed):
+    d = str(tmp_path)
+    subprocess.run([os.path.join(ROOT, "tools", "orfx_synth"), "--out", d, "--seed", str(seed)] + SYNTH_ARGS, check=True,
+                   capture_output=True)
+    for tag, args in SYNTH_RUNS:
+        rc, gtf, tsv, err = run_cli(ob.cli_path(), d, args, "g_" + tag, ["template1.gtf", "template2.gtf"])
+        assert rc == 0, err
+        base = os.path.join(GOLDEN, "synth_s%d_%s" % (seed, tag))
+        assert gtf == open(base + ".gtf", "rb").read(), tag
+        assert tsv == open(base + ".tsv", "rb").read(), tag
+
+
+@pytest.mark.skipif(not os.path.exists(REF_BIN), reason="oracle/_ref/orfanage_ref not shipped")
+@pytest.mark.parametrize("seed", [1, 2, 3])
+def test_cli_byte_identical_to_reference_binary(synth, seed):
+    d = synth(seed, loci=150, template_files=3, queries=8)
+    for args in OPTION_GRID:
+        compare_clis(ob.cli_path(), d, args)
+    for args, tpl in SELF_GRID:
+        compare_clis(ob.cli_path(), d, args, tpl)
+
+
+def test_empty_and_degenerate_batches(gpu, oracle_lib):
+    gpu.set_params(ob.Params.make(mode="BEST"))
+    r = gpu.run(ob.Batch())
+    assert r.n_queries == 0 and r.n_rows == 0
+    # one bundle, a query with a 1-base exon and a template that does not overlap it -> "no-overlap"
+    seq = np.frombuffer(b"ACGTACGTATGAAATAGACGT" * 5, dtype=np.uint8)
+    b = ob.Batch(seq=seq, seq_off=[0, len(seq)], bundle_start=[100], bundle_tx_off=[0, 3], tx_kind=[1, 0, 0],
+                 tx_strand=[ord("+")] * 3, tx_seg_off=[0, 1, 2, 4], tx_cds_start=[150, 0, 0], tx_cds_end=[170, 0, 0],
+                 tx_tid_class=[0, 1, 2], segs=[[150, 170], [100, 100], [101, 120], [140, 180]], seg_phase=[0, 0, 0, 0])
+    got = gpu.run(b)
+    with ob.Context(ob.Params.make(mode="BEST"), lib=oracle_lib, prefix="orfx_oracle_") as ox:
+        want = ox.run(b)
+    assert_same_results(got, want, "degenerate")
+    assert got.n_queries == 2

@@ -1,0 +1,168 @@
+"""CPU suite, part 2: host logic and the C-ABI surface (no compute calls on the CUDA library)."""
+import ctypes
+import os
+import re
+import subprocess
+import sys
+
+import numpy as np
+import pytest
+
+import orfanage_b200 as ob
+from conftest import ORACLE_LIB, ROOT, template_files
+
+
+def declared_functions(header):
+    src = open(os.path.join(ROOT, "include", header)).read()
+    src = re.sub(r"/\*.*?\*/", "", src, flags=re.S)
+    return sorted(set(re.findall(r"\b(orfxh?_[a-z_0-9]+)\s*\(", src)))
+
+
+def test_device_library_exports_every_declared_symbol():
+    lib = ctypes.CDLL(ob.device_library_path())
+    names = declared_functions("orfx.h")
+    assert len(names) >= 15
+    for n in names:
+        assert hasattr(lib, n), "liborfx.so does not export %s" % n
+    ob.load_device_library()
+    assert lib.orfx_abi_version() == 1
+
+
+def test_host_library_exports_every_declared_symbol():
+    lib = ctypes.CDLL(ob.host_library_path())
+    names = [n for n in declared_functions("orfx_pack.h") if n.startswith("orfxh_")]
+    assert len(names) >= 7
+    for n in names:
+        assert hasattr(lib, n), "liborfx_host.so does not export %s" % n
+
+
+def test_no_cpu_fallback_without_a_gpu(synth):
+    """The product must fail loudly, not compute on the CPU, when no CUDA device is usable."""
+    try:
+        import torch
+        if torch.cuda.is_available():
+            pytest.skip("a GPU is present")
+    except ImportError:
+        pass
+    with pytest.raises(ob.OrfxError) as e:
+        ob.Context(ob.Params.make())
+    assert e.value.code == -3 and "no CPU path" in str(e.value)
+    d = synth(5, loci=40)
+    p = subprocess.run([ob.cli_path(), "--reference", "genome.fa", "--query", "query.gtf", "--output", "nogpu.gtf", "template.gtf"],
+                       cwd=d, capture_output=True, text=True)
+    assert p.returncode == 1 and "no CPU path" in p.stderr
+
+
+def test_product_does_not_link_or_import_the_oracle():
+    for lib in (ob.device_library_path(), ob.host_library_path(), ob.cli_path()):
+        out = subprocess.run(["ldd", lib], capture_output=True, text=True).stdout
+        assert "oracle" not in out
+        syms = subprocess.run(["nm", "-D", lib], capture_output=True, text=True).stdout
+        assert "orfx_oracle" not in syms
+    for root, _, files in os.walk(os.path.join(ROOT, "orfanage_b200")):
+        for f in files:
+            if f.endswith((".py", ".cpp", ".cu", ".cuh", ".h")):
+                text = open(os.path.join(root, f), errors="replace").read()
+                assert "orfx_oracle" not in text and "liborfx_oracle" not in text, f
+
+
+def test_workload_counts_and_batch_layout(synth):
+    d = synth(5, loci=40)
+    w = ob.Workload(os.path.join(d, "query.gtf"), template_files(d), os.path.join(d, "genome.fa"))
+    b = w.pack()
+    a = b.arrays
+    assert w.count("active_bundles") == len(a["bundle_start"]) <= w.count("bundles")
+    assert w.count("queries") == b.n_queries
+    assert w.count("query_nt") == b.query_nt()
+    # CSR invariants
+    assert a["bundle_tx_off"][0] == 0 and a["bundle_tx_off"][-1] == len(a["tx_kind"])
+    assert a["tx_seg_off"][0] == 0 and a["tx_seg_off"][-1] == a["segs"].shape[0]
+    assert (np.diff(a["seq_off"]) > 0).all()
+    segs = a["segs"]
+    assert (segs[:, 0] <= segs[:, 1]).all()
+    for x in range(len(a["tx_kind"])):
+        s = segs[a["tx_seg_off"][x]:a["tx_seg_off"][x + 1]]
+        assert (s[1:, 0] > s[:-1, 1]).all()   # ascending, disjoint
+    # every transcript lies inside its bundle window
+    for j in range(len(a["bundle_start"])):
+        lo = a["bundle_start"][j]
+        hi = lo + (a["seq_off"][j + 1] - a["seq_off"][j]) - 1
+        for x in range(a["bundle_tx_off"][j], a["bundle_tx_off"][j + 1]):
+            s = segs[a["tx_seg_off"][x]:a["tx_seg_off"][x + 1]]
+            assert s[0, 0] >= lo and s[-1, 1] <= hi
+    # window bytes are the FASTA bytes, case preserved
+    fa = "".join(l.strip() for l in open(os.path.join(d, "genome.fa")) if not l.startswith(">"))
+    j = 0
+    lo = int(a["bundle_start"][j])
+    n = int(a["seq_off"][1])
+    win = bytes(a["seq"][:n]).decode()
+    assert win in fa and any(c.islower() for c in fa)
+    w.close()
+
+
+def test_sharding_is_a_partition(synth, oracle_lib):
+    """Shards are disjoint, cover every active bundle, and evaluating them separately gives the same
+    per-query answers as one batch (loci are independent: SURVEY.md §8e)."""
+    d = synth(6, loci=50)
+    w = ob.Workload(os.path.join(d, "query.gtf"), template_files(d), os.path.join(d, "genome.fa"))
+    params = ob.Params.make(mode="LONGEST_MATCH,BEST")
+    with ob.Context(params, lib=oracle_lib, prefix="orfx_oracle_") as cx:
+        whole = w.pack(0, 1)
+        ids_whole = [w.tx_id(int(q)) for q in np.nonzero(whole.arrays["tx_kind"] == 0)[0]]
+        res = cx.run(whole)
+        want = {ids_whole[i]: (int(b["cds_start"]), int(b["cds_end"]), int(b["t_tx"] >= 0)) for i, b in enumerate(res.best)}
+        got = {}
+        starts = []
+        for k in range(3):
+            part = w.pack(k, 3)
+            starts += list(part.arrays["bundle_start"])
+            ids = {int(q): w.tx_id(int(q), k) for q in np.nonzero(part.arrays["tx_kind"] == 0)[0]}
+            r = cx.run(part)
+            for b in r.best:
+                key = ids[int(b["q_tx"])]
+                assert key not in got
+                got[key] = (int(b["cds_start"]), int(b["cds_end"]), int(b["t_tx"] >= 0))
+    assert len(starts) == len(whole.arrays["bundle_start"])
+    assert got == want and len(got) > 100
+    w.close()
+
+
+WORKER = r'''
+import os, sys, ctypes, json
+sys.path.insert(0, {root!r})
+import numpy as np, torch, torch.distributed as dist
+import orfanage_b200 as ob
+rank, world = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"])
+dist.init_process_group("gloo", rank=rank, world_size=world)
+d = {d!r}
+w = ob.Workload(d + "/query.gtf", [d + "/template.gtf"], d + "/genome.fa")
+part = w.pack(rank, world)
+lib = ctypes.CDLL({oracle!r})
+with ob.Context(ob.Params.make(mode="LONGEST_MATCH,BEST"), lib=lib, prefix="orfx_oracle_") as cx:
+    r = cx.run(part)
+found = torch.tensor([int((r.best["t_tx"] >= 0).sum()), r.n_queries, int(r.best["cds_start"].astype(np.int64).sum())])
+dist.all_reduce(found)          # results are gathered on the host; no collective on the data path
+if rank == 0:
+    json.dump(found.tolist(), open({out!r}, "w"))
+dist.destroy_process_group()
+'''
+
+
+def test_two_rank_sharding_over_gloo(synth, tmp_path, oracle_lib):
+    """The N>1 launch shape of bench.py (one process per shard, torch.distributed rendezvous, results
+    reduced on the host) on world_size 2 / gloo."""
+    d = synth(6, loci=50)
+    out = str(tmp_path / "found.json")
+    script = tmp_path / "worker.py"
+    script.write_text(WORKER.format(root=ROOT, d=d, oracle=ORACLE_LIB, out=out))
+    env = dict(os.environ, MASTER_ADDR="127.0.0.1", MASTER_PORT="29531")
+    p = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2", "--master-addr",
+                        "127.0.0.1", "--master-port", "29531", str(script)], env=env, capture_output=True, text=True, timeout=600)
+    assert p.returncode == 0, p.stderr[-2000:]
+    import json
+    found, nq, cs = json.load(open(out))
+    w = ob.Workload(os.path.join(d, "query.gtf"), template_files(d), os.path.join(d, "genome.fa"))
+    with ob.Context(ob.Params.make(mode="LONGEST_MATCH,BEST"), lib=oracle_lib, prefix="orfx_oracle_") as cx:
+        r = cx.run(w.pack())
+    assert (found, nq, cs) == (int((r.best["t_tx"] >= 0).sum()), r.n_queries, int(r.best["cds_start"].astype(np.int64).sum()))
+    w.close()
