@@ -1,0 +1,352 @@
+#!/usr/bin/env python
+"""Benchmark of the ORFanage hot path on B200 (contract: see DESIGN.md "Measurement").
+
+  python bench.py [--gpus N] [--steps K] [--warmup W]            our arm (CUDA path through the C-ABI)
+  python bench.py --impl reference [--gpus N] [--steps K] ...     the reference's own CPU code (oracle/_ref)
+
+A "step" is one pass of the whole hot path (prep, candidate rows, codon scan, rescue + score, --mode
+reduction) over one batch: the GENCODE-scale synthetic configuration (BASELINE.json configs[1]:
+~250k query transcripts vs ~90k template CDSs on a 3 Gb random genome, --mode LONGEST_MATCH,BEST),
+generated on the box by the seeded generator tools/orfx_synth.  At N > 1 every rank evaluates its own
+configs[1]-sized locus shard (weak scaling; loci are independent, no collective on the data path).
+
+One JSON line on stdout (rank 0).  `value` = query transcripts/s with the batch resident in HBM (device
+time, CUDA events on the library's stream, max over ranks); `e2e` = the same through orfx_submit /
+orfx_wait with the batch in pinned HOST memory, uploads and result downloads inside the timed region.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+C2 = dict(seed=20261104, loci=20000, chroms=24, chrom_len=125000000, queries=13, templates=8, template_files=1)
+MODE = "LONGEST_MATCH,BEST"
+ALG_BYTES_PER_NT = 1.25      # codon scan: 1 B read per spliced nucleotide + 2 mask bits written
+
+
+def log(*a):
+    print("[bench]", *a, file=sys.stderr, flush=True)
+
+
+def workload_dir(cfg, tag):
+    base = os.environ.get("ORFX_BENCH_DIR", "/tmp/orfx_bench")
+    return os.path.join(base, "%s_s%d_l%d_c%dx%d_q%d_t%d" % (tag, cfg["seed"], cfg["loci"], cfg["chroms"], cfg["chrom_len"],
+                                                           cfg["queries"], cfg["templates"]))
+
+
+def generate(cfg, tag):
+    """Seeded synthetic workload (tools/orfx_synth); reused when already on disk."""
+    d = workload_dir(cfg, tag)
+    done = os.path.join(d, ".done")
+    if os.path.exists(done):
+        return d
+    os.makedirs(d, exist_ok=True)
+    t = time.time()
+    subprocess.run([os.path.join(ROOT, "tools", "orfx_synth"), "--out", d, "--seed", str(cfg["seed"]), "--loci", str(cfg["loci"]),
+                    "--chroms", str(cfg["chroms"]), "--chrom-len", str(cfg["chrom_len"]), "--queries", str(cfg["queries"]),
+                    "--templates", str(cfg["templates"]), "--template-files", str(cfg["template_files"])], check=True,
+                   stderr=subprocess.DEVNULL)
+    open(done, "w").write("ok\n")
+    log("generated %s in %.1f s" % (d, time.time() - t))
+    return d
+
+
+class ClockSampler(threading.Thread):
+    """Samples SM clock and throttle reasons of one GPU through NVML while the timed region runs."""
+
+    def __init__(self, index):
+        super().__init__(daemon=True)
+        self.index, self.samples, self.reasons, self.stop_flag, self.max_mhz = index, [], set(), False, None
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self.nv = pynvml
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.max_mhz = pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM)
+        except Exception as e:   # NVML missing: report that, never invent clocks
+            self.nv, self.err = None, str(e)
+
+    def run(self):
+        if not self.nv:
+            return
+        nv = self.nv
+        names = {nv.nvmlClocksThrottleReasonHwSlowdown: "hw_slowdown", nv.nvmlClocksThrottleReasonHwThermalSlowdown:
+                 "hw_thermal_slowdown", nv.nvmlClocksThrottleReasonSwThermalSlowdown: "sw_thermal_slowdown",
+                 nv.nvmlClocksThrottleReasonSwPowerCap: "sw_power_cap"}
+        while not self.stop_flag:
+            try:
+                self.samples.append(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM))
+                r = nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
+                for bit, name in names.items():
+                    if r & bit:
+                        self.reasons.add(name)
+            except Exception:
+                pass
+            time.sleep(0.005)
+
+    def result(self):
+        self.stop_flag = True
+        if self.is_alive():
+            self.join(timeout=2)
+        if not self.samples:
+            return {"sm_mhz": None, "sm_max_mhz": self.max_mhz, "reasons": [], "note": "no NVML samples"}
+        s = sorted(self.samples)
+        return {"sm_mhz": s[len(s) // 2], "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons), "samples": len(s)}
+
+
+# ---- the reference's CPU implementation of the path (oracle/_ref) -----------------------------------
+SAMPLE = dict(C2, loci=3336, chroms=4)     # same generator law and locus spacing as configs[1], 1/6 of the loci
+
+
+def evaluated_queries(d):
+    """Query transcripts in bundles that hold a template (the ones the hot path evaluates; the rest are
+    copied through unchanged by both implementations, orfanage.cpp:383-432)."""
+    import orfanage_b200 as ob
+    w = ob.Workload(os.path.join(d, "query.gtf"), [os.path.join(d, "template.gtf")], None)
+    n = w.count("queries")
+    w.close()
+    return n
+
+
+def time_reference_once(d, threads):
+    """One run of the reference binary on the workload in d.  Returns seconds spent in its main evaluation
+    loop (between its own 'starting main evaluation' and 'Done' stderr lines, orfanage.cpp:369,819) and
+    whole-process seconds."""
+    ref = os.path.join(ROOT, "oracle", "_ref", "orfanage_ref")
+    if not os.path.exists(ref):
+        raise RuntimeError("oracle/_ref/orfanage_ref is not built (make oracle, in the container that has /root/reference)")
+    out = os.path.join(d, "ref_out.gtf")
+    t0 = time.time()
+    p = subprocess.Popen([ref, "--reference", "genome.fa", "--query", "query.gtf", "--output", out, "--mode", MODE, "--threads",
+                          str(threads), "template.gtf"], cwd=d, stderr=subprocess.PIPE, stdout=subprocess.DEVNULL, text=True, bufsize=1)
+    t_start = t_done = None
+    for line in p.stderr:
+        if "starting main evaluation" in line:
+            t_start = time.time()
+        elif line.startswith("Done"):
+            t_done = time.time()
+    rc = p.wait()
+    t1 = time.time()
+    if rc != 0 or t_start is None or t_done is None:
+        raise RuntimeError("reference run failed (rc %d)" % rc)
+    return t_done - t_start, t1 - t0
+
+
+def reference_arm(args):
+    """bench.py --impl reference: the reference's own sources (compiled against the gclib stand-in) on the
+    host cores, all threads, on a bounded sample of the workload.  Rank 0 only."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    threads = os.cpu_count() or 1
+    d = generate(SAMPLE, "sample")
+    nq = evaluated_queries(d)
+    for _ in range(args.warmup):
+        time_reference_once(d, threads)
+    evals, wholes = [], []
+    for _ in range(args.steps):
+        e, w = time_reference_once(d, threads)
+        evals.append(e)
+        wholes.append(w)
+    ms = 1e3 * sum(evals) / len(evals)
+    value = nq / (ms / 1e3)
+    sample = "%d loci / %d query transcripts of the configs[1] generator (1/6 of the loci, same locus spacing)" % (SAMPLE["loci"], nq)
+    line = {"impl": "reference", "metric": "query transcripts/sec", "value": value, "unit": "transcripts/s", "n_gpus": args.gpus,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "int32", "data": "synthetic",
+            "config": {"workload": "GENCODE-scale synthetic (configs[1]) — bounded sample", "mode": MODE, "sample": sample,
+                       "timed": "reference main evaluation loop (orfanage.cpp:369-819), mean of %d runs" % args.steps,
+                       "whole_process_s": sum(wholes) / len(wholes)},
+            "cpu_baseline": {"value": value, "unit": "transcripts/s", "cores": threads, "kind": "reference", "sample": sample},
+            "e2e": {"value": value, "unit": "transcripts/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0}
+    print(json.dumps(line), flush=True)
+
+
+# ---- our arm -------------------------------------------------------------------------------------------
+def cpu_baseline_leg():
+    """Reference binary on the bounded sample, all host threads, one warm-up + two timed runs."""
+    threads = os.cpu_count() or 1
+    d = generate(SAMPLE, "sample")
+    nq = evaluated_queries(d)
+    time_reference_once(d, threads)
+    ev = [time_reference_once(d, threads)[0] for _ in range(2)]
+    e1 = time_reference_once(d, 1)[0]
+    sample = "%d loci / %d query transcripts of the configs[1] generator; main evaluation loop only" % (SAMPLE["loci"], nq)
+    return {"value": nq / (sum(ev) / len(ev)), "unit": "transcripts/s", "cores": threads, "kind": "reference", "sample": sample,
+            "single_thread_value": nq / e1}
+
+
+def ours(args):
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+    import orfanage_b200 as ob
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; the product has no CPU path (use --impl reference for the CPU arm)")
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    cfg = dict(C2)
+    if args.loci:
+        cfg["loci"] = args.loci
+        cfg["chroms"] = max(1, min(24, args.loci // 834 + 1))
+    # every rank evaluates a configs[1]-sized locus shard of its own (distinct seed => distinct loci)
+    # (when the scratch disk cannot hold one genome per rank, all ranks read rank 0's)
+    import shutil
+    base = os.environ.get("ORFX_BENCH_DIR", "/tmp/orfx_bench")
+    os.makedirs(base, exist_ok=True)
+    need = world * (cfg["chroms"] * cfg["chrom_len"] * 1.2 + 1e9)
+    shared = world > 1 and shutil.disk_usage(base).free < need
+    cfg["seed"] = C2["seed"] + (0 if shared else rank)
+    if shared:
+        if rank == 0:
+            generate(cfg, "c2")
+        barrier()
+    d = generate(cfg, "c2")
+    t = time.time()
+    w = ob.Workload(os.path.join(d, "query.gtf"), [os.path.join(d, "template.gtf")], os.path.join(d, "genome.fa"))
+    batch = w.pack(0, 1, pinned=True)
+    nq, nt_sum = batch.n_queries, w.count("query_nt")
+    log("rank %d: loaded + packed in %.1f s: %d queries, %d templates, %d bundles, %.1f MB windows, %.1f M spliced nt"
+        % (rank, time.time() - t, nq, w.count("templates"), w.count("active_bundles"), batch.arrays["seq"].nbytes / 1e6, nt_sum / 1e6))
+    params = ob.Params.make(mode=MODE, want_rows=False)
+    cx = ob.Context(params, device=local)
+
+    # ---- leg 1: batch resident in HBM -------------------------------------------------------------
+    cx.upload(batch)
+    for _ in range(args.warmup):
+        cx.run_resident()
+    stage_ms = {}
+    launches = 0
+    barrier()
+    sampler = ClockSampler(local)
+    sampler.start()
+    dev_ms = 0.0
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        launches += cx.run_resident()
+        dev_ms += cx.last_run_ms()
+        for k, v in cx.kernel_times().items():
+            stage_ms[k] = stage_ms.get(k, 0.0) + v
+    barrier()
+    wall_ms = (time.perf_counter() - t0) * 1e3
+    clocks = sampler.result()
+    res = cx.fetch()
+    found = int((res.best["t_tx"] >= 0).sum())
+
+    # ---- leg 2: end to end through orfx_submit / orfx_wait, batch in pinned host memory -----------
+    for _ in range(max(1, args.warmup // 2)):
+        cx.run(batch)
+    barrier()
+    t0 = time.perf_counter()
+    e2e_dev = [0.0, 0.0, 0.0]
+    for _ in range(args.steps):
+        cx.submit(batch)
+        r = cx.wait(copy=False)
+        launches += cx.last_run_launches()
+        e2e_dev = [e2e_dev[0] + r.ms_h2d, e2e_dev[1] + r.ms_kernels, e2e_dev[2] + r.ms_d2h]
+    barrier()
+    e2e_ms = (time.perf_counter() - t0) * 1e3
+    d2h_bytes = int(nq * ob._capi.BEST_DTYPE.itemsize + 32)
+
+    # max over ranks of the timed regions, sum of the units
+    tt = torch.tensor([dev_ms, wall_ms, e2e_ms], dtype=torch.float64, device="cuda")
+    cnt = torch.tensor([nq, launches, found, nt_sum], dtype=torch.int64, device="cuda")
+    if world > 1:
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+        dist.all_reduce(cnt)
+    dev_ms, wall_ms, e2e_ms = [float(x) for x in tt.tolist()]
+    nq_all, launches_all, found_all, nt_all = [int(x) for x in cnt.tolist()]
+    return dict(rank=rank, world=world, cfg=cfg, nq=nq, nq_all=nq_all, nt_sum=nt_sum, dev_ms=dev_ms, wall_ms=wall_ms, e2e_ms=e2e_ms,
+                e2e_dev=e2e_dev, stage_ms=stage_ms, launches=launches_all, found=found_all, clocks=clocks, h2d=batch.h2d_bytes,
+                d2h=d2h_bytes, windows=int(batch.arrays["seq"].nbytes), n_templates=w.count("templates"),
+                n_bundles=w.count("active_bundles"))
+
+
+def measured_peak():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        try:
+            return float(json.load(open(p))["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+        except Exception:
+            pass
+    return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--loci", type=int, default=0, help="override the number of loci (development only; 0 = configs[1])")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
+    if args.impl == "reference":
+        reference_arm(args)
+        return
+    m = ours(args)
+    if m["rank"] != 0:
+        return
+    K = args.steps
+    ms_per_step = m["dev_ms"] / K
+    value = m["nq_all"] / (ms_per_step / 1e3)
+    e2e_value = m["nq_all"] / (m["e2e_ms"] / K / 1e3)
+    peak, peak_src = measured_peak()
+    scan_ms = m["stage_ms"].get("codon_scan", 0.0) / K
+    alg_bytes = ALG_BYTES_PER_NT * m["nt_sum"]
+    achieved = alg_bytes / (scan_ms / 1e3) / 1e9 if scan_ms > 0 else 0.0
+    dominant = max(m["stage_ms"], key=lambda k: m["stage_ms"][k]) if m["stage_ms"] else None
+    line = {
+        "metric": "query transcripts/sec", "value": value, "unit": "transcripts/s", "n_gpus": m["world"], "steps": K,
+        "warmup": args.warmup, "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "int32", "data": "synthetic",
+        "config": {"workload": "GENCODE-scale synthetic (BASELINE.json configs[1])", "mode": MODE,
+                   "query_transcripts_per_gpu": m["nq"], "templates_after_dedup": m["n_templates"], "bundles": m["n_bundles"],
+                   "genome": "%d x %d bp random, planted ORFs, seed %d+rank" % (m["cfg"]["chroms"], m["cfg"]["chrom_len"], C2["seed"]),
+                   "spliced_query_nt_per_gpu": m["nt_sum"], "bundle_window_bytes_per_gpu": m["windows"],
+                   "parallelism": "locus shards, one per GPU, no collective", "orfs_found": m["found"],
+                   "l2": "inputs larger than L2 (windows + chains + masks > 126 MB); no explicit flush",
+                   "timing": "CUDA events on the library stream around the whole path, summed over steps, max over ranks",
+                   "wall_ms_per_step": m["wall_ms"] / K},
+        "e2e": {"value": e2e_value, "unit": "transcripts/s", "h2d_bytes_per_step": m["h2d"], "d2h_bytes_per_step": m["d2h"],
+                "ms_per_step": m["e2e_ms"] / K, "device_ms_per_step": {"h2d": m["e2e_dev"][0] / K, "kernels": m["e2e_dev"][1] / K,
+                                                                      "d2h": m["e2e_dev"][2] / K},
+                "api": "orfx_submit + orfx_wait on a pinned host batch (include/orfx.h)"},
+        "gpu_launches": m["launches"],
+        "clocks": m["clocks"],
+        "roofline": {"bound": "hbm", "kernel": "codon_scan_kernel", "achieved": achieved, "peak": peak, "unit": "GB/s",
+                     "frac": achieved / peak if peak else None, "traffic": None, "peak_source": peak_src,
+                     "algorithmic_bytes_per_launch": alg_bytes, "kernel_ms": scan_ms,
+                     "share_of_step": scan_ms / ms_per_step if ms_per_step else None, "dominant_stage": dominant},
+        "stages_ms": {k: v / K for k, v in m["stage_ms"].items()},
+    }
+    if m["world"] == 1 and not args.no_cpu_baseline:
+        try:
+            line["cpu_baseline"] = cpu_baseline_leg()
+        except Exception as e:   # the checker being absent must not hide the GPU number
+            line["cpu_baseline"] = {"value": None, "unit": "transcripts/s", "cores": os.cpu_count(), "kind": "reference",
+                                    "sample": "unavailable: %s" % e}
+    print(json.dumps(line), flush=True)
+
+
+if __name__ == "__main__":
+    main()
