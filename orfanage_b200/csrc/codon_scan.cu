@@ -1,21 +1,30 @@
-// Codon scan: for every query transcript, one pass over its spliced sequence (gathered exon by exon
-// from the locus window, complemented and reversed for non-'+' strands, case-folded) that emits two
-// bit masks in transcript order: bit p of `stop` = the codon starting at spliced position p is a stop
-// codon (TAA TAG TGA TAR TRA), bit p of `start` = it is ATG.  All three frames are covered at once
-// (frame = p mod 3); every later question of the rescue step ("first in-frame stop at or after a",
-// "all in-frame ATG between the previous stop and a") becomes a bit scan over these masks.
+// Codon scan: stop / ATG bit masks of every query transcript, all three frames at once.
+//
+//   bit p of `stop`  = the codon starting at spliced position p (5'->3') is a stop codon
+//                      (TAA TAG TGA TAR TRA — the '.' entries of codon_map, common.hpp:279)
+//   bit p of `start` = it is ATG
+// Every later question of the rescue step ("first in-frame stop at or after a", "all in-frame ATG
+// between the previous stop and a") becomes a bit scan over these masks (chain_ops.cuh).
 //
 // Replaces, for the whole batch at once, what the reference recomputes ~2.4x per candidate:
-// TX::_get_nt_seq (Transcriptome.cpp:155-171), SEQ::SEQ toupper (common.hpp:303-308),
-// SEQ::translate and SEQ::find_inframe_codon's codon_map lookups (common.hpp:420-450, 477-495).
+// TX::_get_nt_seq (Transcriptome.cpp:155-171), SEQ::SEQ toupper (common.hpp:303-308), SEQ::translate
+// and SEQ::find_inframe_codon's codon_map lookups (common.hpp:420-450, 477-495).
 //
-// Shape: one warp per tile of SCAN_TILE spliced positions.  Lanes read source-aligned 16-byte chunks
-// of the window (LDG.128, coalesced along each exon), classify the 16 bytes with SWAR byte compares,
-// squeeze each class to a 16-bit plane (multiply-gather), and OR the valid bits into four per-warp
-// bit planes (T, A, G, R in transcript orientation) in shared memory at their transcript offset.
-// Re-aligning *bits* instead of bytes is what makes arbitrary exon alignment and exon junctions free:
-// the codon logic then runs on aligned 32-position words of the planes.
-// HBM-bound by design: 1 B read per spliced nucleotide + 2 bits written (roofline).
+// Two kernels, both HBM/L2-streaming, no shared memory needed:
+//
+//  1. base_planes_kernel — once per WINDOW byte (not per spliced base: a locus window is shared by all
+//     its isoforms).  Each thread reads 32 bytes with two 128-bit loads, classifies them with SWAR byte
+//     compares (case folded, exact for all 256 byte values) and writes one 32-bit word into each of
+//     the base planes the window's strand needs:  '+' : T A G R;  other strands (transcript base =
+//     complement of the genomic byte, gclib ntComplement): A (->T)  T|U (->A)  C (->G)  Y (->R).
+//  2. codon_scan_kernel — one warp per tile of 31 mask words of one transcript.  A lane assembles the
+//     four plane words of its 32 spliced positions by funnel-shifting bit runs out of the window
+//     planes exon piece by exon piece (reversed with brev for the reverse strand), takes the next
+//     word's low bits from its neighbour lane (shuffle; lane 31 only supplies the halo), evaluates the
+//     codon logic on whole words and stores the two mask words, coalesced.
+//
+// Roofline accounting: algorithmic bytes = 1 B per spliced nucleotide read + 2 bits
+// written; the planes make the real DRAM traffic smaller than that (window bytes once + bits).
 #include "orfx_device.cuh"
 
 namespace orfx {
@@ -24,8 +33,8 @@ namespace {
 
 __device__ __forceinline__ uint32_t eq_flags(uint32_t w, uint32_t fold, uint32_t lit) {
     // 0x80 in every byte of w that equals lit after masking with fold; exact for all 256 byte values
-    uint32_t y = (w & fold) ^ lit;
-    uint32_t t = ((y & 0x7F7F7F7Fu) + 0x7F7F7F7Fu) | y;
+    const uint32_t y = (w & fold) ^ lit;
+    const uint32_t t = ((y & 0x7F7F7F7Fu) + 0x7F7F7F7Fu) | y;
     return ~t & 0x80808080u;
 }
 __device__ __forceinline__ uint32_t gather4(uint32_t flags) {
@@ -33,179 +42,138 @@ __device__ __forceinline__ uint32_t gather4(uint32_t flags) {
     return (flags * 0x00204081u) >> 28;
 }
 
-struct Planes { uint32_t t, a, g, r; };   // 16 valid bits each, bit i = byte i of the chunk
+constexpr uint32_t FOLD = 0xDFDFDFDFu;      // clear the ASCII case bit
+constexpr uint32_t FOLD_TU = 0xDEDEDEDEu;   // ... and bit 0: 'T' (0x54) and 'U' (0x55) coincide
 
-template <bool PLUS>
-__device__ __forceinline__ Planes classify16(const uint4& v) {
-    const uint32_t w[4] = {v.x, v.y, v.z, v.w};
-    Planes p{0, 0, 0, 0};
+template <uint32_t FOLDM, uint32_t LIT>
+__device__ __forceinline__ uint32_t plane_word(const uint32_t (&w)[8]) {
+    uint32_t r = 0;
 #pragma unroll
-    for (int k = 0; k < 4; k++) {
-        uint32_t ft, fa, fg, fr;
-        if (PLUS) {
-            ft = eq_flags(w[k], 0xDFDFDFDFu, 0x54545454u);   // T
-            fa = eq_flags(w[k], 0xDFDFDFDFu, 0x41414141u);   // A
-            fg = eq_flags(w[k], 0xDFDFDFDFu, 0x47474747u);   // G
-            fr = eq_flags(w[k], 0xDFDFDFDFu, 0x52525252u);   // R
-        } else {   // transcript base = complement of the genomic byte (ntComplement)
-            ft = eq_flags(w[k], 0xDFDFDFDFu, 0x41414141u);   // A -> T
-            fa = eq_flags(w[k], 0xDEDEDEDEu, 0x54545454u);   // T or U -> A
-            fg = eq_flags(w[k], 0xDFDFDFDFu, 0x43434343u);   // C -> G
-            fr = eq_flags(w[k], 0xDFDFDFDFu, 0x59595959u);   // Y -> R
-        }
-        p.t |= gather4(ft) << (4 * k);
-        p.a |= gather4(fa) << (4 * k);
-        p.g |= gather4(fg) << (4 * k);
-        p.r |= gather4(fr) << (4 * k);
-    }
-    return p;
+    for (int k = 0; k < 8; k++) r |= gather4(eq_flags(w[k], FOLDM, LIT)) << (4 * k);
+    return r;
 }
-
-__device__ __forceinline__ void or_bits(uint32_t* plane, int dest, uint32_t val, int n) {
-    // OR n (<=16) bits of val into the bit array at bit offset dest
-    if (val == 0) return;
-    int wi = dest >> 5, sh = dest & 31;
-    atomicOr(&plane[wi], val << sh);
-    if (sh + n > 32) atomicOr(&plane[wi + 1], val >> (32 - sh));
-}
-
-constexpr int PLANE_WORDS = SCAN_TILE / 32 + 2;   // tile + halo
 
 }  // namespace
 
-__global__ void __launch_bounds__(SCAN_WARPS_PER_CTA * 32)
-codon_scan_kernel(DevBatch B, int64_t n_tiles) {
-    __shared__ uint32_t s_plane[SCAN_WARPS_PER_CTA][4][PLANE_WORDS];
-    __shared__ int64_t s_blo[SCAN_WARPS_PER_CTA][32];
-    __shared__ int32_t s_nbytes[SCAN_WARPS_PER_CTA][32];
-    __shared__ int32_t s_tfirst[SCAN_WARPS_PER_CTA][32];
-    __shared__ int32_t s_cpre[SCAN_WARPS_PER_CTA][33];
-
-    const int lane = threadIdx.x & 31;
-    const int wib = threadIdx.x >> 5;
-    const int64_t warp0 = (int64_t)blockIdx.x * SCAN_WARPS_PER_CTA + wib;
-    const int64_t n_warps = (int64_t)gridDim.x * SCAN_WARPS_PER_CTA;
-    uint32_t(*plane)[PLANE_WORDS] = s_plane[wib];
-
-    for (int64_t tile = warp0; tile < n_tiles; tile += n_warps) {
-        const int tx = B.tile_tx[tile];
-        const int tidx = (int)(tile - B.tx_tile_off[tx]);
-        const int L = B.tx_len[tx];
-        const bool plus = B.tx_strand[tx] == '+';
-        const int p0 = tidx * SCAN_TILE;
-        const int p1 = min(L, p0 + SCAN_TILE + 2);
-        const int s0 = B.tx_seg_off[tx], s1 = B.tx_seg_off[tx + 1];
-        const int bundle = B.tx_bundle[tx];
-        const int64_t win = B.seq_off[bundle];
-        const int bstart = B.bundle_start[bundle];
-        // spliced range in genomic order
-        const int u0 = plus ? p0 : L - p1;
-        const int u1 = plus ? p1 : L - p0;
-
-        for (int i = lane; i < 4 * PLANE_WORDS; i += 32) (&plane[0][0])[i] = 0;
-        // first exon overlapping u0: last k with cum[k] <= u0
-        int lo = s0, hi = s1 - 1;
-        while (lo < hi) {
-            int mid = (lo + hi + 1) >> 1;
-            if (B.seg_cum[mid] <= u0) lo = mid; else hi = mid - 1;
-        }
-        __syncwarp();
-        for (int kbase = lo; kbase < s1; kbase += 32) {
-            // lane i describes piece kbase+i
-            int k = kbase + lane;
-            int nchunks = 0;
-            bool live = false;
-            if (k < s1) {
-                int cum = B.seg_cum[k];
-                if (cum < u1) {
-                    orfx_seg sg = B.segs[k];
-                    int len = sg.end - sg.start + 1;
-                    int ulo = max(cum, u0), uhi = min(cum + len, u1);
-                    if (uhi > ulo) {
-                        live = true;
-                        int64_t blo = win + (int64_t)(sg.start - bstart) + (ulo - cum);
-                        int nb = uhi - ulo;
-                        s_blo[wib][lane] = blo;
-                        s_nbytes[wib][lane] = nb;
-                        s_tfirst[wib][lane] = plus ? (ulo - p0) : (L - 1 - ulo - p0);
-                        nchunks = (int)(((blo + nb - 1) >> 4) - (blo >> 4)) + 1;
-                    }
-                }
-            }
-            // exclusive prefix of chunk counts
-            int incl = nchunks;
-#pragma unroll
-            for (int d = 1; d < 32; d <<= 1) { int v = __shfl_up_sync(0xffffffffu, incl, d); if (lane >= d) incl += v; }
-            s_cpre[wib][lane + 1] = incl;
-            if (lane == 0) s_cpre[wib][0] = 0;
-            const int total = __shfl_sync(0xffffffffu, incl, 31);
-            const unsigned live_mask = __ballot_sync(0xffffffffu, live);
-            __syncwarp();
-            for (int j = lane; j < total; j += 32) {
-                // piece of chunk j: largest i with cpre[i] <= j
-                int a = 0, b = 31;
-                while (a < b) { int m = (a + b + 1) >> 1; if (s_cpre[wib][m] <= j) a = m; else b = m - 1; }
-                const int64_t blo = s_blo[wib][a];
-                const int nb = s_nbytes[wib][a];
-                const int tfirst = s_tfirst[wib][a];
-                const int64_t c = (blo >> 4) + (j - s_cpre[wib][a]);
-                const uint4 v = __ldg(reinterpret_cast<const uint4*>(B.seq) + c);
-                const int v0 = (int)max((int64_t)0, blo - (c << 4));
-                const int v1 = (int)min((int64_t)16, blo + nb - (c << 4));
-                const int n = v1 - v0;
-                const uint32_t keep = ((1u << v1) - 1u) & ~((1u << v0) - 1u);
-                const int off = (int)((c << 4) + v0 - blo);   // byte offset of the first valid byte inside the piece
-                if (plus) {
-                    Planes p = classify16<true>(v);
-                    const int dest = tfirst + off;
-                    or_bits(plane[0], dest, (p.t & keep) >> v0, n);
-                    or_bits(plane[1], dest, (p.a & keep) >> v0, n);
-                    or_bits(plane[2], dest, (p.g & keep) >> v0, n);
-                    or_bits(plane[3], dest, (p.r & keep) >> v0, n);
-                } else {
-                    Planes p = classify16<false>(v);
-                    // bytes v0..v1-1 run 3'->5': the last valid byte has the smallest transcript position
-                    const int dest = tfirst - (off + n - 1);
-                    const int sh = 16 - v1;
-                    or_bits(plane[0], dest, (__brev(p.t & keep) >> 16) >> sh, n);
-                    or_bits(plane[1], dest, (__brev(p.a & keep) >> 16) >> sh, n);
-                    or_bits(plane[2], dest, (__brev(p.g & keep) >> 16) >> sh, n);
-                    or_bits(plane[3], dest, (__brev(p.r & keep) >> 16) >> sh, n);
-                }
-            }
-            __syncwarp();
-            // all pieces of this batch were inside the range and the batch was full: there may be more
-            if (!(live_mask == 0xffffffffu)) break;
-        }
-        __syncwarp();
-        // codon logic on aligned words: lanes 0..15 -> stop word, lanes 16..31 -> start word
-        {
-            const int w = lane & 15;
-            const uint32_t T0 = plane[0][w], T1w = plane[0][w + 1];
-            const uint32_t A0 = plane[1][w], A1w = plane[1][w + 1];
-            const uint32_t G0 = plane[2][w], G1w = plane[2][w + 1];
-            const uint32_t R0 = plane[3][w], R1w = plane[3][w + 1];
-            const uint32_t A1 = __funnelshift_r(A0, A1w, 1), A2 = __funnelshift_r(A0, A1w, 2);
-            const uint32_t G1 = __funnelshift_r(G0, G1w, 1), G2 = __funnelshift_r(G0, G1w, 2);
-            const uint32_t R1 = __funnelshift_r(R0, R1w, 1), R2 = __funnelshift_r(R0, R1w, 2);
-            const uint32_t T1 = __funnelshift_r(T0, T1w, 1);
-            // TAA TAG TAR | TGA TRA ; ATG
-            const uint32_t stop = T0 & ((A1 & (A2 | G2 | R2)) | ((G1 | R1) & A2));
-            const uint32_t start = A0 & T1 & G2;
-            const int64_t base = B.tx_mask_off[tx] + (int64_t)tidx * (SCAN_TILE / 32) + w;
-            if (lane < 16) B.stop_mask[base] = stop; else B.start_mask[base] = start;
-        }
-        __syncwarp();
+// ---- 1. window bytes -> base planes -------------------------------------------------------------------
+__global__ void __launch_bounds__(256) base_planes_kernel(DevBatch B, int64_t n_chunks) {
+    const int64_t chunk = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;   // 32 bytes each
+    // which strands do the windows under this warp's 1 KB need?  (warp-uniform)
+    const int64_t warp_lo = (chunk & ~(int64_t)31) * 32;
+    if (warp_lo >= B.seq_bytes) return;
+    const int64_t warp_hi = min(warp_lo + 1024, B.seq_bytes);
+    int lo = 0, hi = B.n_bundles - 1;
+    while (lo < hi) {   // last bundle with seq_off <= warp_lo
+        const int mid = (lo + hi + 1) >> 1;
+        if (B.seq_off[mid] <= warp_lo) lo = mid; else hi = mid - 1;
+    }
+    uint32_t need = 0;
+    for (int b = lo; b < B.n_bundles && B.seq_off[b] < warp_hi; b++) need |= B.bundle_need[b];
+    if (chunk >= n_chunks || need == 0) return;
+    const uint4* src = reinterpret_cast<const uint4*>(B.seq) + 2 * chunk;
+    const uint4 v0 = __ldg(src), v1 = __ldg(src + 1);
+    const uint32_t w[8] = {v0.x, v0.y, v0.z, v0.w, v1.x, v1.y, v1.z, v1.w};
+    uint32_t* out = B.planes + chunk;
+    const int64_t ps = B.plane_words;
+    const uint32_t a = plane_word<FOLD, 0x41414141u>(w);   // A: '+' A plane and reverse-strand T plane
+    out[1 * ps] = a;
+    if (need & 1u) {
+        out[0 * ps] = plane_word<FOLD, 0x54545454u>(w);    // T
+        out[2 * ps] = plane_word<FOLD, 0x47474747u>(w);    // G
+        out[3 * ps] = plane_word<FOLD, 0x52525252u>(w);    // R
+    }
+    if (need & 2u) {
+        out[4 * ps] = plane_word<FOLD_TU, 0x54545454u>(w); // T or U -> A
+        out[5 * ps] = plane_word<FOLD, 0x43434343u>(w);    // C -> G
+        out[6 * ps] = plane_word<FOLD, 0x59595959u>(w);    // Y -> R
     }
 }
 
+// ---- 2. planes -> per-transcript stop / start masks ---------------------------------------------------
+namespace {
+// n (1..32) bits of a plane starting at absolute bit position `pos`
+__device__ __forceinline__ uint32_t plane_bits(const uint32_t* __restrict__ plane, int64_t pos, int n) {
+    const int64_t wi = pos >> 5;
+    const uint32_t lo = __ldg(plane + wi), hi = __ldg(plane + wi + 1);
+    const uint32_t v = __funnelshift_r(lo, hi, (uint32_t)(pos & 31));
+    return n >= 32 ? v : (v & ((1u << n) - 1u));
+}
+}  // namespace
+
+__global__ void __launch_bounds__(SCAN_WARPS_PER_CTA * 32) codon_scan_kernel(DevBatch B, int64_t n_tiles) {
+    const int lane = threadIdx.x & 31;
+    const int64_t tile = (int64_t)blockIdx.x * SCAN_WARPS_PER_CTA + (threadIdx.x >> 5);
+    if (tile >= n_tiles) return;
+    const int tx = B.tile_tx[tile];
+    const int tidx = (int)(tile - B.tx_tile_off[tx]);
+    const int L = B.tx_len[tx];
+    const bool plus = B.tx_strand[tx] == '+';
+    const int w = tidx * SCAN_TILE_WORDS + lane;   // mask word of this lane (lane 31: halo for lane 30)
+    const int p0 = w * 32;
+    uint32_t T0 = 0, A0 = 0, G0 = 0, R0 = 0;
+    if (p0 < L) {
+        const int n = min(32, L - p0);
+        const int s0 = B.tx_seg_off[tx], s1 = B.tx_seg_off[tx + 1];
+        const int bundle = B.tx_bundle[tx];
+        const int64_t win = B.seq_off[bundle] - (int64_t)B.bundle_start[bundle];   // byte offset of genomic coordinate 0
+        const int64_t ps = B.plane_words;
+        const uint32_t* pT = B.planes + (plus ? 0 : 1) * ps;
+        const uint32_t* pA = B.planes + (plus ? 1 : 4) * ps;
+        const uint32_t* pG = B.planes + (plus ? 2 : 5) * ps;
+        const uint32_t* pR = B.planes + (plus ? 3 : 6) * ps;
+        // spliced offsets in genomic order covered by this word
+        const int u0 = plus ? p0 : L - p0 - n;
+        int lo = s0, hi = s1 - 1;
+        while (lo < hi) {   // exon holding u0: last k with cum[k] <= u0
+            const int mid = (lo + hi + 1) >> 1;
+            if (B.seg_cum[mid] <= u0) lo = mid; else hi = mid - 1;
+        }
+        int filled = 0;
+        for (int k = lo; filled < n && k < s1; k++) {
+            const orfx_seg sg = B.segs[k];
+            const int offs = u0 + filled - B.seg_cum[k];
+            const int take = min(n - filled, sg.end - sg.start + 1 - offs);
+            const int64_t pos = win + sg.start + offs;
+            T0 |= plane_bits(pT, pos, take) << filled;
+            A0 |= plane_bits(pA, pos, take) << filled;
+            G0 |= plane_bits(pG, pos, take) << filled;
+            R0 |= plane_bits(pR, pos, take) << filled;
+            filled += take;
+        }
+        if (!plus) {   // genomic order -> transcript order: bit j <- bit n-1-j
+            const int sh = 32 - n;
+            T0 = __brev(T0) >> sh; A0 = __brev(A0) >> sh; G0 = __brev(G0) >> sh; R0 = __brev(R0) >> sh;
+        }
+    }
+    // the next word's planes live in the neighbour lane
+    const uint32_t T1w = __shfl_down_sync(0xffffffffu, T0, 1), A1w = __shfl_down_sync(0xffffffffu, A0, 1);
+    const uint32_t G1w = __shfl_down_sync(0xffffffffu, G0, 1), R1w = __shfl_down_sync(0xffffffffu, R0, 1);
+    if (lane == 31 || p0 >= L) return;
+    const uint32_t A1 = __funnelshift_r(A0, A1w, 1), A2 = __funnelshift_r(A0, A1w, 2);
+    const uint32_t G1 = __funnelshift_r(G0, G1w, 1), G2 = __funnelshift_r(G0, G1w, 2);
+    const uint32_t R1 = __funnelshift_r(R0, R1w, 1), R2 = __funnelshift_r(R0, R1w, 2);
+    const uint32_t T1 = __funnelshift_r(T0, T1w, 1);
+    // TAA TAG TAR | TGA TRA ; ATG
+    const uint32_t stop = T0 & ((A1 & (A2 | G2 | R2)) | ((G1 | R1) & A2));
+    const uint32_t start = A0 & T1 & G2;
+    const int64_t base = B.tx_mask_off[tx] + w;
+    B.stop_mask[base] = stop;
+    B.start_mask[base] = start;
+}
+
+int launch_base_planes(const DevBatch& B, cudaStream_t stream) {
+    if (B.seq_bytes <= 0 || B.n_bundles <= 0) return 0;
+    const int64_t n_chunks = (B.seq_bytes + 31) / 32;
+    const int64_t threads = (n_chunks + 31) / 32 * 32;
+    base_planes_kernel<<<(unsigned)((threads + 255) / 256), 256, 0, stream>>>(B, n_chunks);
+    return 1;
+}
+
 void launch_codon_scan(const DevBatch& B, int64_t n_tiles, int n_sm, cudaStream_t stream) {
+    (void)n_sm;
     if (n_tiles <= 0) return;
-    // resident CTAs: 16 per SM at 128 threads (64 warps/SM); grid = multiple of the SM count
-    int64_t want = (n_tiles + SCAN_WARPS_PER_CTA - 1) / SCAN_WARPS_PER_CTA;
-    int64_t cap = (int64_t)n_sm * 16;
-    int grid = (int)(want < cap ? want : cap);
-    codon_scan_kernel<<<grid, SCAN_WARPS_PER_CTA * 32, 0, stream>>>(B, n_tiles);
+    const int64_t grid = (n_tiles + SCAN_WARPS_PER_CTA - 1) / SCAN_WARPS_PER_CTA;
+    codon_scan_kernel<<<(unsigned)grid, SCAN_WARPS_PER_CTA * 32, 0, stream>>>(B, n_tiles);
 }
 
 }  // namespace orfx

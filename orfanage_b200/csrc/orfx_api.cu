@@ -18,6 +18,7 @@ int launch_fill_rows(const DevBatch& B, const DevRows& R, int n_queries, cudaStr
 int launch_rescue_score(const DevBatch& B, const DevRows& R, const orfx_params& P, cudaStream_t s);
 int launch_select(const DevBatch& B, const DevRows& R, const orfx_params& P, int n_queries, orfx_best* best_out, int32_t* ord_scratch, cudaStream_t s);
 void launch_codon_scan(const DevBatch& B, int64_t n_tiles, int n_sm, cudaStream_t stream);
+int launch_base_planes(const DevBatch& B, cudaStream_t stream);
 int align_batch_device(int device, cudaStream_t stream, const uint8_t* aa, const int64_t* off, int64_t n_seq, const int32_t* pair_q,
                        const int32_t* pair_t, int64_t n_pairs, int gapo, int gape, orfx_aln_out* out, double* cells, float* ms, std::string& err);
 }  // namespace orfx
@@ -82,6 +83,7 @@ struct orfx_ctx {
     DBuf d_seq, d_seq_off, d_bstart, d_btx_off, d_kind, d_strand, d_seg_off, d_cds_s, d_cds_e, d_tid, d_segs, d_phase;
     // derived
     DBuf d_seg_cum, d_tx_len, d_tx_bundle, d_mask_off, d_tile_off, d_q_off, d_q_list, d_row_off, d_tile_tx, d_stop, d_start;
+    DBuf d_need, d_planes;
     DBuf d_cnt_q, d_cnt_words, d_cnt_tiles, d_cnt_rows, d_scan_tmp, d_ord;
     // rows
     DBuf r_i32[16], r_f32[3], r_u8[3], r_order, d_best;
@@ -152,6 +154,9 @@ int upload_batch(orfx_ctx* c, const orfx_batch* b) {
     CU(c->d_cnt_tiles.ensure(nt * 8 + 8));
     CU(c->d_cnt_rows.ensure(nt * 8 + 8));
     CU(c->d_scan_tmp.ensure((size_t)scan_tmp_elems((int64_t)nt) * 8 + 8));
+    CU(c->d_need.ensure(nb + 4));
+    const size_t plane_words = (seqb + 31) / 32 + 4;
+    if (seqb) CU(c->d_planes.ensure(7 * plane_words * 4));
     CU(c->h_totals.ensure(64));
     DevBatch& B = c->B;
     memset(&B, 0, sizeof B);
@@ -163,6 +168,7 @@ int upload_batch(orfx_ctx* c, const orfx_batch* b) {
     B.seg_cum = c->d_seg_cum.as<int32_t>(); B.tx_len = c->d_tx_len.as<int32_t>(); B.tx_bundle = c->d_tx_bundle.as<int32_t>();
     B.tx_mask_off = c->d_mask_off.as<int64_t>(); B.tx_tile_off = c->d_tile_off.as<int64_t>(); B.tx_q_off = c->d_q_off.as<int64_t>();
     B.q_list = c->d_q_list.as<int32_t>(); B.q_row_off = c->d_row_off.as<int64_t>();
+    B.bundle_need = c->d_need.as<uint8_t>(); B.planes = c->d_planes.as<uint32_t>(); B.plane_words = (int64_t)plane_words;
     c->resident = true;
     c->have_results = false;
     return ORFX_OK;
@@ -218,6 +224,7 @@ int run_path(orfx_ctx* c) {
     stage_begin(c, ST_SCAN);
     if (c->P.has_reference) {
         c->n_launches += launch_fill_tiles(B, s);
+        c->n_launches += launch_base_planes(B, s);
         launch_codon_scan(B, tiles, c->n_sm, s);
         if (tiles > 0) c->n_launches++;
     }
@@ -377,7 +384,7 @@ void orfx_destroy(orfx_ctx* c) {
     cudaStreamSynchronize(c->stream);
     DBuf* d[] = {&c->d_seq, &c->d_seq_off, &c->d_bstart, &c->d_btx_off, &c->d_kind, &c->d_strand, &c->d_seg_off, &c->d_cds_s, &c->d_cds_e, &c->d_tid,
                  &c->d_segs, &c->d_phase, &c->d_seg_cum, &c->d_tx_len, &c->d_tx_bundle, &c->d_mask_off, &c->d_tile_off, &c->d_q_off, &c->d_q_list,
-                 &c->d_row_off, &c->d_tile_tx, &c->d_stop, &c->d_start, &c->d_cnt_q, &c->d_cnt_words, &c->d_cnt_tiles, &c->d_cnt_rows, &c->d_scan_tmp,
+                 &c->d_row_off, &c->d_tile_tx, &c->d_stop, &c->d_start, &c->d_need, &c->d_planes, &c->d_cnt_q, &c->d_cnt_words, &c->d_cnt_tiles, &c->d_cnt_rows, &c->d_scan_tmp,
                  &c->d_ord, &c->r_order, &c->d_best};
     for (DBuf* b : d) b->free_();
     for (auto& b : c->r_i32) b.free_();

@@ -94,16 +94,20 @@ __global__ void tx_prep_kernel(DevBatch B, int64_t* cnt_q, int64_t* cnt_words, i
     for (int k = s0; k < s1; k++) { B.seg_cum[k] = acc; orfx_seg sg = B.segs[k]; acc += sg.end - sg.start + 1; }
     B.tx_len[tx] = acc;
     bool isq = B.tx_kind[tx] == ORFX_TX_QUERY;
-    int64_t tiles = isq ? (acc + SCAN_TILE - 1) / SCAN_TILE : 0;
-    if (isq && tiles == 0) tiles = 1;
+    const int64_t words = acc > 0 ? (acc + 31) / 32 : 1;
     cnt_q[tx] = isq ? 1 : 0;
-    cnt_tiles[tx] = tiles;
-    cnt_words[tx] = tiles * (SCAN_TILE / 32);
+    cnt_tiles[tx] = isq ? (words + SCAN_TILE_WORDS - 1) / SCAN_TILE_WORDS : 0;
+    cnt_words[tx] = isq ? ((words + 3) & ~(int64_t)3) : 0;   // 16-byte aligned mask regions
 }
 __global__ void bundle_prep_kernel(DevBatch B) {
     int b = blockIdx.x * blockDim.x + threadIdx.x;
     if (b >= B.n_bundles) return;
-    for (int x = B.bundle_tx_off[b]; x < B.bundle_tx_off[b + 1]; x++) B.tx_bundle[x] = b;
+    uint32_t need = 0;
+    for (int x = B.bundle_tx_off[b]; x < B.bundle_tx_off[b + 1]; x++) {
+        B.tx_bundle[x] = b;
+        if (B.tx_kind[x] == ORFX_TX_QUERY) need |= B.tx_strand[x] == '+' ? 1u : 2u;
+    }
+    B.bundle_need[b] = (uint8_t)need;
 }
 __global__ void fill_q_list_kernel(DevBatch B) {
     int tx = blockIdx.x * blockDim.x + threadIdx.x;
@@ -139,84 +143,119 @@ int launch_fill_tiles(const DevBatch& B, cudaStream_t s) {
 // rows: bounding box + intersection segments
 // ------------------------------------------------------------------------------------------------
 namespace {
-// Enumerates the candidate rows of query transcript qx in the reference's order.  FILL = false only counts.
+__device__ __forceinline__ void put_row(const DevRows& R, int64_t at, int qx, int t, int s, int e, int status) {
+    R.q_tx[at] = qx; R.t_tx[at] = t; R.seg_start[at] = s; R.seg_end[at] = e; R.status[at] = (uint8_t)status;
+}
+
+// Candidate rows of one (query, template) pair in the reference's order: CHAIN::intersection(...,
+// segments = true) (Transcriptome.h:321-361) merges consecutive pieces into one genomic span while they
+// share intron boundaries; one row per span, or one "no-overlap" row.  FILL = false only counts.
+// Same visiting order and state as the reference's double loop, but template segments that can no
+// longer / not yet overlap are skipped with a persistent pointer, so a pair costs O(exons + segments).
 template <bool FILL>
-__device__ int64_t enumerate_rows(const DevBatch& B, const DevRows& R, int qx, int64_t out) {
+__device__ int pair_rows(const DevBatch& B, const DevRows& R, int qx, int t, int64_t out) {
+    const int q0 = B.tx_seg_off[qx], q1 = B.tx_seg_off[qx + 1];
+    const int t0 = B.tx_seg_off[t], t1 = B.tx_seg_off[t + 1];
+    int start = t0, low = t0, nseg = 0, cur_s = 0, cur_e = 0, n = 0;
+    bool continue_prev = false;
+    for (int i = q0; i < q1; i++) {
+        const orfx_seg s1 = B.segs[i];
+        bool found_yet = false;
+        // segments wholly left of this exon: the reference walks over them (resetting continue_prev)
+        if (low < start) low = start;
+        while (low < t1 && B.segs[low].end < s1.start) low++;
+        if (low > start) continue_prev = false;
+        for (int j = low; j < t1; j++) {
+            const orfx_seg c2 = B.segs[j];
+            const int is = max(s1.start, c2.start), ie = min(s1.end, c2.end);
+            if (is <= ie) {
+                found_yet = true;
+                start = j;
+                if (ie == c2.end) start++;
+                const bool ends_match = ie == s1.end && s1.end == c2.end;
+                const bool starts_match = is == s1.start && s1.start == c2.start;
+                if (!continue_prev || !starts_match) {
+                    if (nseg > 0) { if (FILL) put_row(R, out + n, qx, t, cur_s, cur_e, ORFX_ST_OK); n++; }
+                    nseg++;
+                    cur_s = is; cur_e = ie;
+                } else {
+                    cur_s = min(cur_s, is); cur_e = max(cur_e, ie);
+                }
+                continue_prev = ends_match;
+            } else {
+                // every later segment lies right of this exon as well: the reference visits them all
+                // (or stops at the first one once it has found an overlap) with this same effect
+                if (!found_yet) continue_prev = false;
+                break;
+            }
+        }
+        if (!found_yet && continue_prev) continue_prev = false;
+    }
+    if (nseg > 0) { if (FILL) put_row(R, out + n, qx, t, cur_s, cur_e, ORFX_ST_OK); n++; }
+    else { if (FILL) put_row(R, out + n, qx, t, -1, -1, ORFX_ST_NO_OVERLAP); n++; }
+    return n;
+}
+
+// does template slot t of the query's bundle take part?  (bounding box, orfanage.cpp:500-503)
+__device__ __forceinline__ bool pair_live(const DevBatch& B, int t, int x1, int qstart, int qend) {
+    return t < x1 && B.tx_kind[t] == ORFX_TX_TEMPLATE && !(qstart > B.tx_cds_end[t] || qend < B.tx_cds_start[t]);
+}
+}  // namespace
+
+// One warp per query slot; lanes take the transcripts of the query's bundle 32 at a time.  The query
+// count is still on the device here: slots past the last query count zero, so that
+// q_row_off[n_queries .. n_tx] all hold the total.
+__global__ void __launch_bounds__(256) count_rows_kernel(DevBatch B, int64_t* cnt) {
+    const int qi = (int)(((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5);
+    const int lane = threadIdx.x & 31;
+    if (qi >= B.n_tx) return;
+    const int64_t nq = B.tx_q_off[B.n_tx];
+    int total = 0;
+    if (qi < nq) {
+        const int qx = B.q_list[qi];
+        const int b = B.tx_bundle[qx];
+        const int x0 = B.bundle_tx_off[b], x1 = B.bundle_tx_off[b + 1];
+        const int q0 = B.tx_seg_off[qx], q1 = B.tx_seg_off[qx + 1];
+        const int qstart = B.segs[q0].start, qend = B.segs[q1 - 1].end;
+        DevRows dummy{};
+        for (int base = x0; base < x1; base += 32) {
+            const int t = base + lane;
+            if (pair_live(B, t, x1, qstart, qend)) total += pair_rows<false>(B, dummy, qx, t, 0);
+        }
+#pragma unroll
+        for (int d = 16; d > 0; d >>= 1) total += __shfl_xor_sync(0xffffffffu, total, d);
+    }
+    if (lane == 0) cnt[qi] = total;
+}
+__global__ void __launch_bounds__(256) fill_rows_kernel(DevBatch B, DevRows R, int n_queries) {
+    const int qi = (int)(((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5);
+    const int lane = threadIdx.x & 31;
+    if (qi >= n_queries) return;
+    const int qx = B.q_list[qi];
     const int b = B.tx_bundle[qx];
     const int x0 = B.bundle_tx_off[b], x1 = B.bundle_tx_off[b + 1];
     const int q0 = B.tx_seg_off[qx], q1 = B.tx_seg_off[qx + 1];
     const int qstart = B.segs[q0].start, qend = B.segs[q1 - 1].end;
-    int64_t n = 0;
-    for (int t = x0; t < x1; t++) {
-        if (B.tx_kind[t] != ORFX_TX_TEMPLATE) continue;
-        if (qstart > B.tx_cds_end[t] || qend < B.tx_cds_start[t]) continue;   // orfanage.cpp:501-503
-        const int t0 = B.tx_seg_off[t], t1 = B.tx_seg_off[t + 1];
-        int start = t0, nseg = 0, cur_s = 0, cur_e = 0;
-        bool continue_prev = false;
-        for (int i = q0; i < q1; i++) {
-            const orfx_seg s1 = B.segs[i];
-            bool found_yet = false;
-            for (int j = start; j < t1; j++) {
-                const orfx_seg c2 = B.segs[j];
-                const int is = max(s1.start, c2.start), ie = min(s1.end, c2.end);
-                if (is <= ie) {
-                    found_yet = true;
-                    start = j;
-                    if (ie == c2.end) start++;
-                    const bool ends_match = ie == s1.end && s1.end == c2.end;
-                    const bool starts_match = is == s1.start && s1.start == c2.start;
-                    if (!continue_prev || !starts_match) {
-                        if (nseg > 0) {
-                            if (FILL) { R.q_tx[out + n] = qx; R.t_tx[out + n] = t; R.seg_start[out + n] = cur_s; R.seg_end[out + n] = cur_e; R.status[out + n] = ORFX_ST_OK; }
-                            n++;
-                        }
-                        nseg++;
-                        cur_s = is; cur_e = ie;
-                    } else {
-                        cur_s = min(cur_s, is); cur_e = max(cur_e, ie);
-                    }
-                    continue_prev = ends_match;
-                } else {
-                    if (found_yet) break;
-                    continue_prev = false;
-                }
-            }
-            if (!found_yet && continue_prev) continue_prev = false;
-        }
-        if (nseg > 0) {
-            if (FILL) { R.q_tx[out + n] = qx; R.t_tx[out + n] = t; R.seg_start[out + n] = cur_s; R.seg_end[out + n] = cur_e; R.status[out + n] = ORFX_ST_OK; }
-            n++;
-        } else {
-            if (FILL) { R.q_tx[out + n] = qx; R.t_tx[out + n] = t; R.seg_start[out + n] = -1; R.seg_end[out + n] = -1; R.status[out + n] = ORFX_ST_NO_OVERLAP; }
-            n++;
-        }
+    int64_t out = B.q_row_off[qi];
+    for (int base = x0; base < x1; base += 32) {
+        const int t = base + lane;
+        const bool live = pair_live(B, t, x1, qstart, qend);
+        const int n = live ? pair_rows<false>(B, R, qx, t, 0) : 0;
+        int incl = n;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) { const int v = __shfl_up_sync(0xffffffffu, incl, d); if (lane >= d) incl += v; }
+        if (live) pair_rows<true>(B, R, qx, t, out + incl - n);
+        out += __shfl_sync(0xffffffffu, incl, 31);
     }
-    return n;
-}
-}  // namespace
-
-// The query count is still on the device here: one thread per transcript slot, slots past the last
-// query count zero, so that q_row_off[n_queries .. n_tx] all hold the total.
-__global__ void count_rows_kernel(DevBatch B, int64_t* cnt) {
-    int qi = blockIdx.x * blockDim.x + threadIdx.x;
-    if (qi >= B.n_tx) return;
-    const int64_t nq = B.tx_q_off[B.n_tx];
-    DevRows dummy{};
-    cnt[qi] = qi < nq ? enumerate_rows<false>(B, dummy, B.q_list[qi], 0) : 0;
-}
-__global__ void fill_rows_kernel(DevBatch B, DevRows R, int n_queries) {
-    int qi = blockIdx.x * blockDim.x + threadIdx.x;
-    if (qi >= n_queries) return;
-    enumerate_rows<true>(B, R, B.q_list[qi], B.q_row_off[qi]);
 }
 int launch_count_rows(const DevBatch& B, int64_t* cnt, int64_t* scan_tmp, cudaStream_t s) {
     if (B.n_tx == 0) { cudaMemsetAsync(B.q_row_off, 0, sizeof(int64_t), s); return 0; }
-    count_rows_kernel<<<(B.n_tx + 127) / 128, 128, 0, s>>>(B, cnt);
+    count_rows_kernel<<<(unsigned)(((int64_t)B.n_tx * 32 + 255) / 256), 256, 0, s>>>(B, cnt);
     return 1 + launch_exclusive_scan(cnt, B.q_row_off, scan_tmp, B.n_tx, s);
 }
 int launch_fill_rows(const DevBatch& B, const DevRows& R, int n_queries, cudaStream_t s) {
     if (n_queries == 0) return 0;
-    fill_rows_kernel<<<(n_queries + 127) / 128, 128, 0, s>>>(B, R, n_queries);
+    fill_rows_kernel<<<(unsigned)(((int64_t)n_queries * 32 + 255) / 256), 256, 0, s>>>(B, R, n_queries);
     return 1;
 }
 
