@@ -65,16 +65,38 @@ __device__ __forceinline__ uint32_t frame_pattern(int word, int residue) {
     return s == 0 ? 0x49249249u : (s == 1 ? 0x92492492u : 0x24924924u);
 }
 __device__ __forceinline__ bool mask_bit(const uint32_t* m, int p) { return (m[p >> 5] >> (p & 31)) & 1u; }
+// The mask region of a transcript starts 16-byte aligned and is padded to a multiple of 4 words
+// (tx_prep_kernel), so long scans move 4 words per load with the next load already in flight.
 // smallest q >= p with q == p (mod 3), q < L and bit set; -1 when none
 __device__ __forceinline__ int next_inframe(const uint32_t* m, int p, int L) {
     if (p < 0 || p >= L) return -1;
     const int r = p % 3, nw = (L + 31) >> 5;
     int w = p >> 5;
     uint32_t x = m[w] & frame_pattern(w, r) & (0xFFFFFFFFu << (p & 31));
-    while (true) {
-        if (x) { int q = (w << 5) + __ffs(x) - 1; return q < L ? q : -1; }
+    while (true) {   // head: up to the next 4-word boundary
+        if (x) { const int q = (w << 5) + __ffs(x) - 1; return q < L ? q : -1; }
         if (++w >= nw) return -1;
+        if ((w & 3) == 0) break;
         x = m[w] & frame_pattern(w, r);
+    }
+    uint32_t pa = frame_pattern(w, r), pb = frame_pattern(w + 1, r), pc = frame_pattern(w + 2, r);
+    uint4 v = *reinterpret_cast<const uint4*>(m + w);
+    while (true) {
+        const int wn = w + 4;
+        uint4 nx = make_uint4(0, 0, 0, 0);
+        if (wn < nw) nx = *reinterpret_cast<const uint4*>(m + wn);
+        const uint32_t x0 = v.x & pa, x1 = v.y & pb, x2 = v.z & pc, x3 = v.w & pa;
+        if (x0 | x1 | x2 | x3) {
+            int q;
+            if (x0) q = (w << 5) + __ffs(x0) - 1;
+            else if (x1) q = ((w + 1) << 5) + __ffs(x1) - 1;
+            else if (x2) q = ((w + 2) << 5) + __ffs(x2) - 1;
+            else q = ((w + 3) << 5) + __ffs(x3) - 1;
+            return q < L ? q : -1;   // words past the last real one are padding: any bit there is >= L
+        }
+        if (wn >= nw) return -1;
+        w = wn; v = nx;
+        const uint32_t t = pa; pa = pb; pb = pc; pc = t;   // 4 words on: the frame pattern advances by one
     }
 }
 // largest q <= p with q == p (mod 3), q >= 0 and bit set; -1 when none
@@ -83,10 +105,29 @@ __device__ __forceinline__ int prev_inframe(const uint32_t* m, int p) {
     const int r = p % 3;
     int w = p >> 5;
     uint32_t x = m[w] & frame_pattern(w, r) & (0xFFFFFFFFu >> (31 - (p & 31)));
-    while (true) {
+    while (true) {   // head: down to a 4-word boundary
         if (x) return (w << 5) + 31 - __clz(x);
-        if (--w < 0) return -1;
+        if (w == 0) return -1;
+        if ((w & 3) == 0) break;
+        --w;
         x = m[w] & frame_pattern(w, r);
+    }
+    w -= 4;   // block [w, w+4)
+    uint32_t pa = frame_pattern(w, r), pb = frame_pattern(w + 1, r), pc = frame_pattern(w + 2, r);
+    uint4 v = *reinterpret_cast<const uint4*>(m + w);
+    while (true) {
+        uint4 nx = make_uint4(0, 0, 0, 0);
+        if (w >= 4) nx = *reinterpret_cast<const uint4*>(m + w - 4);
+        const uint32_t x0 = v.x & pa, x1 = v.y & pb, x2 = v.z & pc, x3 = v.w & pa;
+        if (x0 | x1 | x2 | x3) {
+            if (x3) return ((w + 3) << 5) + 31 - __clz(x3);
+            if (x2) return ((w + 2) << 5) + 31 - __clz(x2);
+            if (x1) return ((w + 1) << 5) + 31 - __clz(x1);
+            return (w << 5) + 31 - __clz(x0);
+        }
+        if (w < 4) return -1;
+        w -= 4; v = nx;
+        const uint32_t t = pc; pc = pb; pb = pa; pa = t;   // 4 words back: the pattern steps the other way
     }
 }
 

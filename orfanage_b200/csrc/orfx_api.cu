@@ -3,6 +3,7 @@
 // CUDA device, and orfx_create fails without one.
 #include "orfx_device.cuh"
 
+#include <climits>
 #include <cstdio>
 #include <cstring>
 #include <string>
@@ -15,7 +16,7 @@ int launch_prep(const DevBatch& B, int64_t* cnt_q, int64_t* cnt_words, int64_t* 
 int launch_fill_tiles(const DevBatch& B, cudaStream_t s);
 int launch_count_rows(const DevBatch& B, int64_t* cnt, int64_t* scan_tmp, cudaStream_t s);
 int launch_fill_rows(const DevBatch& B, const DevRows& R, int n_queries, cudaStream_t s);
-int launch_rescue_score(const DevBatch& B, const DevRows& R, const orfx_params& P, cudaStream_t s);
+int launch_rescue_score(const DevBatch& B, const DevRows& R, const orfx_params& P, int32_t* heavy_list, unsigned* heavy_count, int n_sm, cudaStream_t s);
 int launch_select(const DevBatch& B, const DevRows& R, const orfx_params& P, int n_queries, orfx_best* best_out, int32_t* ord_scratch, cudaStream_t s);
 void launch_codon_scan(const DevBatch& B, int64_t n_tiles, int n_sm, cudaStream_t stream);
 int launch_base_planes(const DevBatch& B, cudaStream_t stream);
@@ -83,7 +84,7 @@ struct orfx_ctx {
     DBuf d_seq, d_seq_off, d_bstart, d_btx_off, d_kind, d_strand, d_seg_off, d_cds_s, d_cds_e, d_tid, d_segs, d_phase;
     // derived
     DBuf d_seg_cum, d_tx_len, d_tx_bundle, d_mask_off, d_tile_off, d_q_off, d_q_list, d_row_off, d_tile_tx, d_stop, d_start;
-    DBuf d_need, d_planes;
+    DBuf d_need, d_planes, d_heavy, d_heavy_count;
     DBuf d_cnt_q, d_cnt_words, d_cnt_tiles, d_cnt_rows, d_scan_tmp, d_ord;
     // rows
     DBuf r_i32[16], r_f32[3], r_u8[3], r_order, d_best;
@@ -210,7 +211,10 @@ int run_path(orfx_ctx* c) {
     for (int i = 0; i < 3; i++) CU(c->r_f32[i].ensure((size_t)nrows * 4 + 4));
     for (int i = 0; i < 3; i++) CU(c->r_u8[i].ensure((size_t)nrows + 4));
     CU(c->r_order.ensure((size_t)nrows * 8 + 8));
+    if (nrows > (int64_t)INT32_MAX) return fail(ORFX_E_INVALID, "more than 2^31 candidate rows in one batch: shard it");
     CU(c->d_ord.ensure((size_t)nrows * 4 + 4));
+    CU(c->d_heavy.ensure((size_t)nrows * 4 + 4));
+    CU(c->d_heavy_count.ensure(16));
     CU(c->d_best.ensure((size_t)nq * sizeof(orfx_best) + 8));
     DevRows& R = c->R;
     R.n_rows = nrows;
@@ -233,7 +237,7 @@ int run_path(orfx_ctx* c) {
     c->n_launches += launch_fill_rows(B, R, (int)nq, s);
     stage_end(c, ST_FILL);
     stage_begin(c, ST_RESCUE);
-    c->n_launches += launch_rescue_score(B, R, c->P, s);
+    c->n_launches += launch_rescue_score(B, R, c->P, c->d_heavy.as<int32_t>(), c->d_heavy_count.as<unsigned>(), c->n_sm, s);
     stage_end(c, ST_RESCUE);
     stage_begin(c, ST_SELECT);
     c->n_launches += launch_select(B, R, c->P, (int)nq, c->d_best.as<orfx_best>(), c->d_ord.as<int32_t>(), s);
@@ -384,7 +388,7 @@ void orfx_destroy(orfx_ctx* c) {
     cudaStreamSynchronize(c->stream);
     DBuf* d[] = {&c->d_seq, &c->d_seq_off, &c->d_bstart, &c->d_btx_off, &c->d_kind, &c->d_strand, &c->d_seg_off, &c->d_cds_s, &c->d_cds_e, &c->d_tid,
                  &c->d_segs, &c->d_phase, &c->d_seg_cum, &c->d_tx_len, &c->d_tx_bundle, &c->d_mask_off, &c->d_tile_off, &c->d_q_off, &c->d_q_list,
-                 &c->d_row_off, &c->d_tile_tx, &c->d_stop, &c->d_start, &c->d_need, &c->d_planes, &c->d_cnt_q, &c->d_cnt_words, &c->d_cnt_tiles, &c->d_cnt_rows, &c->d_scan_tmp,
+                 &c->d_row_off, &c->d_tile_tx, &c->d_stop, &c->d_start, &c->d_need, &c->d_planes, &c->d_heavy, &c->d_heavy_count, &c->d_cnt_q, &c->d_cnt_words, &c->d_cnt_tiles, &c->d_cnt_rows, &c->d_scan_tmp,
                  &c->d_ord, &c->r_order, &c->d_best};
     for (DBuf* b : d) b->free_();
     for (auto& b : c->r_i32) b.free_();

@@ -202,13 +202,14 @@ __device__ __forceinline__ bool pair_live(const DevBatch& B, int t, int x1, int 
 }
 }  // namespace
 
-// One warp per query slot; lanes take the transcripts of the query's bundle 32 at a time.  The query
-// count is still on the device here: slots past the last query count zero, so that
-// q_row_off[n_queries .. n_tx] all hold the total.
+// ROWS_GROUP lanes per query slot (8 queries per warp); the lanes of a group take the transcripts of
+// the query's bundle ROWS_GROUP at a time.  The query count is still on the device here: slots past
+// the last query count zero, so that q_row_off[n_queries .. n_tx] all hold the total.
+constexpr int ROWS_GROUP = 4;
+
 __global__ void __launch_bounds__(256) count_rows_kernel(DevBatch B, int64_t* cnt) {
-    const int qi = (int)(((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5);
-    const int lane = threadIdx.x & 31;
-    if (qi >= B.n_tx) return;
+    const int64_t gt = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int qi = (int)(gt / ROWS_GROUP), sub = (int)(gt % ROWS_GROUP);
     const int64_t nq = B.tx_q_off[B.n_tx];
     int total = 0;
     if (qi < nq) {
@@ -218,44 +219,49 @@ __global__ void __launch_bounds__(256) count_rows_kernel(DevBatch B, int64_t* cn
         const int q0 = B.tx_seg_off[qx], q1 = B.tx_seg_off[qx + 1];
         const int qstart = B.segs[q0].start, qend = B.segs[q1 - 1].end;
         DevRows dummy{};
-        for (int base = x0; base < x1; base += 32) {
-            const int t = base + lane;
+        for (int t = x0 + sub; t < x1; t += ROWS_GROUP)
             if (pair_live(B, t, x1, qstart, qend)) total += pair_rows<false>(B, dummy, qx, t, 0);
-        }
-#pragma unroll
-        for (int d = 16; d > 0; d >>= 1) total += __shfl_xor_sync(0xffffffffu, total, d);
     }
-    if (lane == 0) cnt[qi] = total;
+#pragma unroll
+    for (int d = ROWS_GROUP / 2; d > 0; d >>= 1) total += __shfl_xor_sync(0xffffffffu, total, d);
+    if (sub == 0 && qi < B.n_tx) cnt[qi] = total;
 }
 __global__ void __launch_bounds__(256) fill_rows_kernel(DevBatch B, DevRows R, int n_queries) {
-    const int qi = (int)(((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5);
-    const int lane = threadIdx.x & 31;
-    if (qi >= n_queries) return;
-    const int qx = B.q_list[qi];
-    const int b = B.tx_bundle[qx];
-    const int x0 = B.bundle_tx_off[b], x1 = B.bundle_tx_off[b + 1];
-    const int q0 = B.tx_seg_off[qx], q1 = B.tx_seg_off[qx + 1];
-    const int qstart = B.segs[q0].start, qend = B.segs[q1 - 1].end;
-    int64_t out = B.q_row_off[qi];
-    for (int base = x0; base < x1; base += 32) {
-        const int t = base + lane;
-        const bool live = pair_live(B, t, x1, qstart, qend);
+    const int64_t gt = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int qi = (int)(gt / ROWS_GROUP), sub = (int)(gt % ROWS_GROUP);
+    const bool valid = qi < n_queries;
+    const int qx = valid ? B.q_list[qi] : 0;
+    int x0 = 0, x1 = 0, qstart = 0, qend = 0;
+    int64_t out = 0;
+    if (valid) {
+        const int b = B.tx_bundle[qx];
+        x0 = B.bundle_tx_off[b]; x1 = B.bundle_tx_off[b + 1];
+        qstart = B.segs[B.tx_seg_off[qx]].start; qend = B.segs[B.tx_seg_off[qx + 1] - 1].end;
+        out = B.q_row_off[qi];
+    }
+    // the groups of a warp iterate together (shuffles are warp-wide): as many rounds as the largest bundle
+    int rounds = (x1 - x0 + ROWS_GROUP - 1) / ROWS_GROUP;
+#pragma unroll
+    for (int d = 16; d > 0; d >>= 1) rounds = max(rounds, __shfl_xor_sync(0xffffffffu, rounds, d));
+    for (int it = 0; it < rounds; it++) {
+        const int t = x0 + it * ROWS_GROUP + sub;
+        const bool live = valid && pair_live(B, t, x1, qstart, qend);
         const int n = live ? pair_rows<false>(B, R, qx, t, 0) : 0;
         int incl = n;
 #pragma unroll
-        for (int d = 1; d < 32; d <<= 1) { const int v = __shfl_up_sync(0xffffffffu, incl, d); if (lane >= d) incl += v; }
+        for (int d = 1; d < ROWS_GROUP; d <<= 1) { const int v = __shfl_up_sync(0xffffffffu, incl, d, ROWS_GROUP); if (sub >= d) incl += v; }
         if (live) pair_rows<true>(B, R, qx, t, out + incl - n);
-        out += __shfl_sync(0xffffffffu, incl, 31);
+        out += __shfl_sync(0xffffffffu, incl, ROWS_GROUP - 1, ROWS_GROUP);
     }
 }
 int launch_count_rows(const DevBatch& B, int64_t* cnt, int64_t* scan_tmp, cudaStream_t s) {
     if (B.n_tx == 0) { cudaMemsetAsync(B.q_row_off, 0, sizeof(int64_t), s); return 0; }
-    count_rows_kernel<<<(unsigned)(((int64_t)B.n_tx * 32 + 255) / 256), 256, 0, s>>>(B, cnt);
+    count_rows_kernel<<<(unsigned)(((int64_t)B.n_tx * ROWS_GROUP + 255) / 256), 256, 0, s>>>(B, cnt);
     return 1 + launch_exclusive_scan(cnt, B.q_row_off, scan_tmp, B.n_tx, s);
 }
 int launch_fill_rows(const DevBatch& B, const DevRows& R, int n_queries, cudaStream_t s) {
     if (n_queries == 0) return 0;
-    fill_rows_kernel<<<(unsigned)(((int64_t)n_queries * 32 + 255) / 256), 256, 0, s>>>(B, R, n_queries);
+    fill_rows_kernel<<<(unsigned)(((int64_t)n_queries * ROWS_GROUP + 255) / 256), 256, 0, s>>>(B, R, n_queries);
     return 1;
 }
 
@@ -322,9 +328,9 @@ __device__ __forceinline__ float pct(int num, int den) {
 
 }  // namespace
 
-__global__ void __launch_bounds__(128) rescue_score_kernel(DevBatch B, DevRows R, orfx_params P) {
-    const int64_t row = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (row >= R.n_rows) return;
+// One candidate row: rescue (when a genome is loaded) + TX::score.  q / t may view the chains in
+// global or in shared memory.
+__device__ void process_row(const DevBatch& B, const DevRows& R, const orfx_params& P, const int64_t row, const TxView& q, const TxView& t) {
     // defaults: an all-zero Score that does not pass
     int status = R.status[row];
     int key_s = 0, key_e = 0;
@@ -334,7 +340,6 @@ __global__ void __launch_bounds__(128) rescue_score_kernel(DevBatch B, DevRows R
 
     const int qx = R.q_tx[row], tx = R.t_tx[row];
     const int seg_s = R.seg_start[row], seg_e = R.seg_end[row];
-    const TxView q = tx_view(B, qx), t = tx_view(B, tx);
     const bool plus = q.plus;
     const int t_cds_start = B.tx_cds_start[tx], t_cds_end = B.tx_cds_end[tx];
     const int t5 = plus ? t_cds_start : t_cds_end;
@@ -497,10 +502,54 @@ __global__ void __launch_bounds__(128) rescue_score_kernel(DevBatch B, DevRows R
     R.n_dup[row] = 0;
 }
 
-int launch_rescue_score(const DevBatch& B, const DevRows& R, const orfx_params& P, cudaStream_t s) {
+// Rows whose two chains together hold more than HEAVY_SEGS segments (titin-class loci) would make
+// their thread the tail of the whole launch: chain walks are dependent-load chains.  The light kernel
+// defers them to a list; the heavy kernel gives each a warp, stages both chains in shared memory with
+// coalesced loads and lets one lane walk them at shared-memory latency.
+constexpr int HEAVY_SEGS = 64;
+constexpr int HEAVY_CAP = 384;      // segments per chain that fit the per-warp stage
+constexpr int HEAVY_WARPS = 4;
+
+__global__ void __launch_bounds__(128) rescue_score_kernel(DevBatch B, DevRows R, orfx_params P, int32_t* heavy_list, unsigned* heavy_count) {
+    const int64_t row = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (row >= R.n_rows) return;
+    const TxView q = tx_view(B, R.q_tx[row]), t = tx_view(B, R.t_tx[row]);
+    if (q.n + t.n > HEAVY_SEGS && R.status[row] == ORFX_ST_OK) {
+        heavy_list[atomicAdd(heavy_count, 1u)] = (int32_t)row;
+        return;
+    }
+    process_row(B, R, P, row, q, t);
+}
+
+__global__ void __launch_bounds__(HEAVY_WARPS * 32) rescue_score_heavy_kernel(DevBatch B, DevRows R, orfx_params P, const int32_t* heavy_list,
+                                                                             const unsigned* heavy_count) {
+    __shared__ orfx_seg s_seg[HEAVY_WARPS][2][HEAVY_CAP];
+    __shared__ int32_t s_cum[HEAVY_WARPS][2][HEAVY_CAP];
+    const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
+    const unsigned n = *heavy_count;
+    for (unsigned h = blockIdx.x * HEAVY_WARPS + wib; h < n; h += gridDim.x * HEAVY_WARPS) {
+        const int64_t row = heavy_list[h];
+        TxView q = tx_view(B, R.q_tx[row]), t = tx_view(B, R.t_tx[row]);
+        if (q.n <= HEAVY_CAP) {
+            for (int i = lane; i < q.n; i += 32) { s_seg[wib][0][i] = q.segs[i]; s_cum[wib][0][i] = q.cum[i]; }
+            q.segs = s_seg[wib][0]; q.cum = s_cum[wib][0];
+        }
+        if (t.n <= HEAVY_CAP) {
+            for (int i = lane; i < t.n; i += 32) { s_seg[wib][1][i] = t.segs[i]; s_cum[wib][1][i] = t.cum[i]; }
+            t.segs = s_seg[wib][1]; t.cum = s_cum[wib][1];
+        }
+        __syncwarp();
+        if (lane == 0) process_row(B, R, P, row, q, t);
+        __syncwarp();
+    }
+}
+
+int launch_rescue_score(const DevBatch& B, const DevRows& R, const orfx_params& P, int32_t* heavy_list, unsigned* heavy_count, int n_sm, cudaStream_t s) {
     if (R.n_rows == 0) return 0;
-    rescue_score_kernel<<<(unsigned)((R.n_rows + 127) / 128), 128, 0, s>>>(B, R, P);
-    return 1;
+    cudaMemsetAsync(heavy_count, 0, sizeof(unsigned), s);
+    rescue_score_kernel<<<(unsigned)((R.n_rows + 127) / 128), 128, 0, s>>>(B, R, P, heavy_list, heavy_count);
+    rescue_score_heavy_kernel<<<n_sm * 4, HEAVY_WARPS * 32, 0, s>>>(B, R, P, heavy_list, heavy_count);
+    return 2;
 }
 
 }  // namespace orfx
