@@ -22,7 +22,7 @@
 extern "C" {
 #endif
 
-#define ORFX_ABI_VERSION 1
+#define ORFX_ABI_VERSION 2
 
 /* error codes */
 #define ORFX_OK            0
@@ -84,8 +84,13 @@ typedef struct orfx_batch {
     int64_t n_segs;
     int64_t seq_bytes;
     /* per bundle */
-    const uint8_t* seq;            /* concatenated bundle windows, raw FASTA bytes, case preserved;
-                                      may be NULL when params.has_reference == 0                  */
+    const uint8_t* seq;            /* per bundle, raw FASTA bytes, case preserved; may be NULL when
+                                      params.has_reference == 0.  Two layouts:
+                                      windows (seg_seq_off == NULL): the whole locus window
+                                        [bundle_start, bundle end], as Bundle::bundle_seq;
+                                      islands (seg_seq_off != NULL): only the bases under the query
+                                        exons of the bundle (overlapping exons merged), which is all
+                                        the path reads without --overhang; 4-15x fewer bytes to upload */
     const int64_t* seq_off;        /* [n_bundles+1] byte offsets into seq                          */
     const int32_t* bundle_start;   /* [n_bundles] genomic coordinate of the first window byte      */
     const int32_t* bundle_tx_off;  /* [n_bundles+1] transcripts of a bundle are contiguous, in the
@@ -101,6 +106,9 @@ typedef struct orfx_batch {
      * set_cds_as_exons, orfanage.cpp:351) with the phase column of each CDS segment */
     const orfx_seg* segs;          /* [n_segs] ascending, disjoint                                 */
     const int8_t*   seg_phase;     /* [n_segs] templates: SEGTP::phase of the CDS chain; else 0    */
+    const int32_t*  seg_seq_off;   /* [n_segs] or NULL.  Islands layout: for every segment of a QUERY
+                                      transcript, the offset of its first base relative to
+                                      seq_off[bundle]; ignored for other transcripts               */
 } orfx_batch;
 
 /* One chosen ORF per query transcript; what orfanage.cpp:753-791 needs to write the GTF. */

@@ -36,10 +36,11 @@ int orfxh_load(orfxh_workload** out, const char* query_gtf, const char* const* t
 int64_t orfxh_count(const orfxh_workload* w, int what);
 
 /* Splits the active bundles over n_shards (longest-processing-time greedy) and packs
- * shard `shard`.  The arrays behind *out are owned by the workload and stay valid until the next
+ * shard `shard`.  layout: 0 = whole locus windows, 1 = islands (only the bases under query exons; see
+ * orfx_batch.seq in orfx.h).  The arrays behind *out are owned by the workload and stay valid until the next
  * orfxh_pack with the same shard index or orfxh_free.  alloc/dealloc (both NULL = malloc/free) let
  * the caller place the arrays in pinned memory (orfx_host_alloc / orfx_host_free of orfx.h). */
-int orfxh_pack(orfxh_workload* w, int shard, int n_shards, void* (*alloc)(size_t), void (*dealloc)(void*), orfx_batch* out);
+int orfxh_pack(orfxh_workload* w, int shard, int n_shards, int layout, void* (*alloc)(size_t), void (*dealloc)(void*), orfx_batch* out);
 
 /* Keeps only the first n active bundles of the workload (bounded samples for CPU baselines). */
 int orfxh_truncate(orfxh_workload* w, int64_t n_active_bundles);

@@ -527,15 +527,40 @@ T load_tx(const orfx_batch* b, int tx) {
     return t;
 }
 
+// The bundle's sequence as the reference holds it (Bundle::bundle_seq: the whole window).  With the
+// islands layout of orfx_batch only the bases under query exons were packed: the window is rebuilt
+// here with 'N' everywhere else, so that the rest of this file indexes it exactly as the reference
+// does (an access outside the query exons would then show up as a mismatch in the parity tests).
+struct BundleSeq {
+    std::string rebuilt;
+    Bn bn;
+    BundleSeq(const orfx_batch* b, int bi) {
+        bn.bstart = b->bundle_start[bi];
+        if (!b->seq) { bn.seq = nullptr; return; }
+        if (!b->seg_seq_off) { bn.seq = b->seq + b->seq_off[bi]; return; }
+        int hi = bn.bstart;
+        for (int x = b->bundle_tx_off[bi]; x < b->bundle_tx_off[bi + 1]; x++)
+            if (b->tx_seg_off[x + 1] > b->tx_seg_off[x]) hi = std::max(hi, (int)b->segs[b->tx_seg_off[x + 1] - 1].end);
+        rebuilt.assign((size_t)(hi - bn.bstart + 1), 'N');
+        for (int x = b->bundle_tx_off[bi]; x < b->bundle_tx_off[bi + 1]; x++) {
+            if (b->tx_kind[x] != ORFX_TX_QUERY) continue;
+            for (int k = b->tx_seg_off[x]; k < b->tx_seg_off[x + 1]; k++) {
+                const orfx_seg& sg = b->segs[k];
+                memcpy(&rebuilt[(size_t)(sg.start - bn.bstart)], b->seq + b->seq_off[bi] + b->seg_seq_off[k], (size_t)(sg.end - sg.start + 1));
+            }
+        }
+        bn.seq = (const uint8_t*)rebuilt.data();
+    }
+};
+
 void evaluate(Ctx& cx, const orfx_batch* b) {
     const orfx_params& p = cx.p;
     std::vector<Row> rows_all;
     cx.best.clear();
     cx.order.clear();
     for (int bi = 0; bi < b->n_bundles; bi++) {
-        Bn bn;
-        bn.seq = b->seq ? b->seq + b->seq_off[bi] : nullptr;
-        bn.bstart = b->bundle_start[bi];
+        BundleSeq bseq(b, bi);
+        const Bn& bn = bseq.bn;
         int x0 = b->bundle_tx_off[bi], x1 = b->bundle_tx_off[bi + 1];
         std::vector<T> txs;
         for (int x = x0; x < x1; x++) txs.push_back(load_tx(b, x));
@@ -701,7 +726,8 @@ int64_t orfx_oracle_masks(const orfx_batch* b, int32_t tx, uint32_t* stop_bits, 
     int bi = 0;
     while (bi < b->n_bundles && !(tx >= b->bundle_tx_off[bi] && tx < b->bundle_tx_off[bi + 1])) bi++;
     if (bi >= b->n_bundles) return ORFX_E_INVALID;
-    Bn bn; bn.seq = b->seq + b->seq_off[bi]; bn.bstart = b->bundle_start[bi];
+    BundleSeq bseq(b, bi);
+    const Bn& bn = bseq.bn;
     T t = load_tx(b, tx);
     t.bn = &bn;
     std::string nt;

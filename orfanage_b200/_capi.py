@@ -73,7 +73,8 @@ class _Batch(C.Structure):
     _fields_ = [("n_bundles", C.c_int32), ("n_tx", C.c_int32), ("n_segs", C.c_int64), ("seq_bytes", C.c_int64),
                 ("seq", C.c_void_p), ("seq_off", C.c_void_p), ("bundle_start", C.c_void_p), ("bundle_tx_off", C.c_void_p),
                 ("tx_kind", C.c_void_p), ("tx_strand", C.c_void_p), ("tx_seg_off", C.c_void_p), ("tx_cds_start", C.c_void_p),
-                ("tx_cds_end", C.c_void_p), ("tx_tid_class", C.c_void_p), ("segs", C.c_void_p), ("seg_phase", C.c_void_p)]
+                ("tx_cds_end", C.c_void_p), ("tx_tid_class", C.c_void_p), ("segs", C.c_void_p), ("seg_phase", C.c_void_p),
+                ("seg_seq_off", C.c_void_p)]
 
 
 class _Best(C.Structure):
@@ -107,7 +108,8 @@ class _AlnOut(C.Structure):
 
 _BATCH_ARRAYS = [("seq", np.uint8), ("seq_off", np.int64), ("bundle_start", np.int32), ("bundle_tx_off", np.int32),
                  ("tx_kind", np.uint8), ("tx_strand", np.uint8), ("tx_seg_off", np.int32), ("tx_cds_start", np.int32),
-                 ("tx_cds_end", np.int32), ("tx_tid_class", np.int32), ("segs", np.int32), ("seg_phase", np.int8)]
+                 ("tx_cds_end", np.int32), ("tx_tid_class", np.int32), ("segs", np.int32), ("seg_phase", np.int8),
+                 ("seg_seq_off", np.int32)]
 
 
 def _view(ptr, n, dtype):
@@ -164,7 +166,8 @@ class Batch:
             tx_kind=_view(s.tx_kind, nt, np.uint8), tx_strand=_view(s.tx_strand, nt, np.uint8),
             tx_seg_off=_view(s.tx_seg_off, nt + 1, np.int32), tx_cds_start=_view(s.tx_cds_start, nt, np.int32),
             tx_cds_end=_view(s.tx_cds_end, nt, np.int32), tx_tid_class=_view(s.tx_tid_class, nt, np.int32),
-            segs=_view(s.segs, ns * 2, np.int32), seg_phase=_view(s.seg_phase, ns, np.int8))
+            segs=_view(s.segs, ns * 2, np.int32), seg_phase=_view(s.seg_phase, ns, np.int8),
+            seg_seq_off=_view(s.seg_seq_off, ns if s.seg_seq_off else 0, np.int32))
         b = cls.__new__(cls)
         b.arrays = arrays
         b.arrays["segs"] = b.arrays["segs"].reshape(-1, 2)
@@ -301,7 +304,7 @@ def load_host_library(path=None):
     lib.orfxh_count.restype = C.c_int64
     lib.orfxh_count.argtypes = [C.c_void_p, C.c_int]
     lib.orfxh_pack.restype = C.c_int
-    lib.orfxh_pack.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.POINTER(_Batch)]
+    lib.orfxh_pack.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.POINTER(_Batch)]
     lib.orfxh_truncate.restype = C.c_int
     lib.orfxh_truncate.argtypes = [C.c_void_p, C.c_int64]
     lib.orfxh_tx_id.restype = C.c_char_p
@@ -451,7 +454,7 @@ class Workload:
     def truncate(self, n_active):
         self.lib.orfxh_truncate(self.handle, int(n_active))
 
-    def pack(self, shard=0, n_shards=1, pinned=False):
+    def pack(self, shard=0, n_shards=1, pinned=False, layout="islands"):
         """Returns a Batch viewing arrays owned by this workload (valid until the next pack of the
         same shard or close())."""
         s = _Batch()
@@ -460,7 +463,7 @@ class Workload:
             dev = load_device_library()
             alloc = C.cast(dev.orfx_host_alloc, C.c_void_p)
             dealloc = C.cast(dev.orfx_host_free, C.c_void_p)
-        rc = self.lib.orfxh_pack(self.handle, shard, n_shards, alloc, dealloc, C.byref(s))
+        rc = self.lib.orfxh_pack(self.handle, shard, n_shards, 1 if layout == "islands" else 0, alloc, dealloc, C.byref(s))
         if rc != 0:
             raise OrfxError(rc, self.lib.orfxh_last_error().decode())
         return Batch.from_struct(s, owner=self)

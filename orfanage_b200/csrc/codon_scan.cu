@@ -115,7 +115,9 @@ __global__ void __launch_bounds__(SCAN_WARPS_PER_CTA * 32) codon_scan_kernel(Dev
         const int n = min(32, L - p0);
         const int s0 = B.tx_seg_off[tx], s1 = B.tx_seg_off[tx + 1];
         const int bundle = B.tx_bundle[tx];
-        const int64_t win = B.seq_off[bundle] - (int64_t)B.bundle_start[bundle];   // byte offset of genomic coordinate 0
+        const bool isl = B.seg_seq_off != nullptr;
+        // windows: byte offset of genomic coordinate 0; islands: byte offset of the bundle's first island
+        const int64_t win = isl ? B.seq_off[bundle] : B.seq_off[bundle] - (int64_t)B.bundle_start[bundle];
         const int64_t ps = B.plane_words;
         const uint32_t* pT = B.planes + (plus ? 0 : 1) * ps;
         const uint32_t* pA = B.planes + (plus ? 1 : 4) * ps;
@@ -133,7 +135,7 @@ __global__ void __launch_bounds__(SCAN_WARPS_PER_CTA * 32) codon_scan_kernel(Dev
             const orfx_seg sg = B.segs[k];
             const int offs = u0 + filled - B.seg_cum[k];
             const int take = min(n - filled, sg.end - sg.start + 1 - offs);
-            const int64_t pos = win + sg.start + offs;
+            const int64_t pos = win + (isl ? B.seg_seq_off[k] : sg.start) + offs;
             T0 |= plane_bits(pT, pos, take) << filled;
             A0 |= plane_bits(pA, pos, take) << filled;
             G0 |= plane_bits(pG, pos, take) << filled;

@@ -71,7 +71,7 @@ int64_t orfxh_count(const orfxh_workload* w, int what) {
     return ORFX_E_INVALID;
 }
 
-int orfxh_pack(orfxh_workload* w, int shard, int n_shards, void* (*alloc)(size_t), void (*dealloc)(void*), orfx_batch* out) {
+int orfxh_pack(orfxh_workload* w, int shard, int n_shards, int layout, void* (*alloc)(size_t), void (*dealloc)(void*), orfx_batch* out) {
     if (!w || !out || n_shards <= 0 || shard < 0 || shard >= n_shards) { g_err = "bad shard arguments"; return ORFX_E_INVALID; }
     if ((alloc == nullptr) != (dealloc == nullptr)) { g_err = "alloc and dealloc must be given together"; return ORFX_E_INVALID; }
     try {
@@ -79,7 +79,7 @@ int orfxh_pack(orfxh_workload* w, int shard, int n_shards, void* (*alloc)(size_t
         shard_bundles(w->tr, w->active, n_shards, shards);
         if (w->packed.size() <= (size_t)shard) w->packed.resize((size_t)shard + 1);
         w->packed[(size_t)shard].reset(new PackedBatch());
-        pack_bundles(w->tr, shards[(size_t)shard], w->opt.keep_all_cds, w->tid_classes, *w->packed[(size_t)shard], alloc, dealloc);
+        pack_bundles(w->tr, shards[(size_t)shard], w->opt.keep_all_cds, w->tid_classes, *w->packed[(size_t)shard], alloc, dealloc, layout != 0);
         *out = w->packed[(size_t)shard]->view();
         return ORFX_OK;
     } catch (const std::exception& e) { g_err = e.what(); return ORFX_E_INVALID; }

@@ -140,6 +140,7 @@ struct PackedBatch {
     int32_t *tx_seg_off = nullptr, *tx_cds_start = nullptr, *tx_cds_end = nullptr, *tx_tid_class = nullptr;
     orfx_seg* segs = nullptr;
     int8_t* seg_phase = nullptr;
+    int32_t* seg_seq_off = nullptr;         // islands layout only
     int32_t n_tx = 0;
     int64_t n_segs = 0, seq_bytes = 0, n_queries = 0;
     PackedBatch() {}
@@ -152,7 +153,7 @@ struct PackedBatch {
 // Packs the listed bundles (each must hold a template and a query).
 void pack_bundles(const Transcriptome& tr, const std::vector<int>& bundle_ids, bool keep_all_cds,
                   const std::map<std::string, int>& tid_classes, PackedBatch& out,
-                  void* (*alloc)(size_t) = nullptr, void (*dealloc)(void*) = nullptr);
+                  void* (*alloc)(size_t) = nullptr, void (*dealloc)(void*) = nullptr, bool islands = true);
 void build_tid_classes(const Transcriptome& tr, std::map<std::string, int>& out);
 // greedy longest-processing-time split of active bundles over n shards
 void shard_bundles(const Transcriptome& tr, const std::vector<int>& active, int n, std::vector<std::vector<int>>& shards);

@@ -38,6 +38,7 @@ orfx_batch PackedBatch::view() const {
     b.tx_tid_class = tx_tid_class;
     b.segs = segs;
     b.seg_phase = seg_phase;
+    b.seg_seq_off = seq_bytes ? seg_seq_off : nullptr;
     return b;
 }
 
@@ -45,18 +46,48 @@ void build_tid_classes(const Transcriptome& tr, std::map<std::string, int>& out)
     for (const Tx& t : tr.txs) out.insert(std::make_pair(t.tid, (int)out.size()));
 }
 
-// Two passes: size everything, take one arena from the allocator, fill.  The bundle windows (the
-// bulk of the bytes) are copied by several threads.
+namespace {
+// Islands of one bundle: the union of its query exons (what the path reads from the genome when
+// --overhang is 0).  Returns the merged intervals, ascending.
+void bundle_islands(const Transcriptome& tr, const Bundle& b, bool keep_all_cds, std::vector<std::pair<int, int>>& isl) {
+    isl.clear();
+    for (int i = 0; i < b.count; i++) {
+        const Tx& t = tr.txs[b.first + i];
+        if (t.is_templ || (keep_all_cds && t.is_coding)) continue;
+        for (const Seg& s : t.exons) isl.emplace_back(s.s, s.e);
+    }
+    std::sort(isl.begin(), isl.end());
+    size_t k = 0;
+    for (size_t i = 0; i < isl.size(); i++) {
+        if (k > 0 && isl[i].first <= isl[k - 1].second + 1) isl[k - 1].second = std::max(isl[k - 1].second, isl[i].second);
+        else isl[k++] = isl[i];
+    }
+    isl.resize(k);
+}
+}  // namespace
+
+// Two passes: size everything, take one arena from the allocator, fill.  Sequence bytes (the bulk) are
+// copied by several threads.  islands = true uploads only the bases under query exons.
 void pack_bundles(const Transcriptome& tr, const std::vector<int>& bundle_ids, bool keep_all_cds,
                   const std::map<std::string, int>& tid_classes, PackedBatch& out,
-                  void* (*alloc)(size_t), void (*dealloc)(void*)) {
+                  void* (*alloc)(size_t), void (*dealloc)(void*), bool islands) {
     out.reset();
     out.bundle_ids = bundle_ids;
     const size_t nb = bundle_ids.size();
+    const bool has_seq = tr.fasta != nullptr;
+    islands = islands && has_seq;
     size_t total_seq = 0, total_tx = 0, total_segs = 0;
-    for (int bi : bundle_ids) {
-        const Bundle& b = tr.bundles[bi];
-        if (tr.fasta) total_seq += (size_t)(b.bend - b.bstart + 1);
+    std::vector<int64_t> bundle_bytes(nb, 0);
+    std::vector<std::pair<int, int>> isl;
+    for (size_t j = 0; j < nb; j++) {
+        const Bundle& b = tr.bundles[bundle_ids[j]];
+        if (has_seq) {
+            if (islands) {
+                bundle_islands(tr, b, keep_all_cds, isl);
+                for (auto& iv : isl) bundle_bytes[j] += iv.second - iv.first + 1;
+            } else bundle_bytes[j] = b.bend - b.bstart + 1;
+            total_seq += (size_t)bundle_bytes[j];
+        }
         total_tx += (size_t)b.count;
         for (int i = 0; i < b.count; i++) { const Tx& t = tr.txs[b.first + i]; total_segs += t.is_templ ? t.cds.size() : t.exons.size(); }
     }
@@ -65,7 +96,8 @@ void pack_bundles(const Transcriptome& tr, const std::vector<int>& bundle_ids, b
     size_t o_seq = 0, o_seq_off = o_seq + up(total_seq + 64), o_bstart = o_seq_off + up((nb + 1) * 8), o_btx = o_bstart + up(nb * 4 + 4),
            o_kind = o_btx + up((nb + 1) * 4), o_strand = o_kind + up(total_tx + 4), o_segoff = o_strand + up(total_tx + 4),
            o_cs = o_segoff + up((total_tx + 1) * 4), o_ce = o_cs + up(total_tx * 4 + 4), o_tid = o_ce + up(total_tx * 4 + 4),
-           o_segs = o_tid + up(total_tx * 4 + 4), o_phase = o_segs + up(total_segs * 8 + 8), o_end = o_phase + up(total_segs + 4);
+           o_segs = o_tid + up(total_tx * 4 + 4), o_phase = o_segs + up(total_segs * 8 + 8), o_sso = o_phase + up(total_segs + 4),
+           o_end = o_sso + up(islands ? total_segs * 4 + 4 : 4);
     out.arena = alloc ? alloc(o_end) : malloc(o_end);
     if (!out.arena) throw std::runtime_error("cannot allocate " + std::to_string(o_end) + " bytes for the packed batch");
     out.arena_bytes = o_end;
@@ -75,17 +107,20 @@ void pack_bundles(const Transcriptome& tr, const std::vector<int>& bundle_ids, b
     out.bundle_tx_off = (int32_t*)(base + o_btx); out.tx_kind = (uint8_t*)(base + o_kind); out.tx_strand = (uint8_t*)(base + o_strand);
     out.tx_seg_off = (int32_t*)(base + o_segoff); out.tx_cds_start = (int32_t*)(base + o_cs); out.tx_cds_end = (int32_t*)(base + o_ce);
     out.tx_tid_class = (int32_t*)(base + o_tid); out.segs = (orfx_seg*)(base + o_segs); out.seg_phase = (int8_t*)(base + o_phase);
+    out.seg_seq_off = islands ? (int32_t*)(base + o_sso) : nullptr;
     out.n_tx = (int32_t)total_tx; out.n_segs = (int64_t)total_segs; out.seq_bytes = (int64_t)total_seq;
     out.tx_global.resize(total_tx);
 
     int64_t so = 0;
     int32_t x = 0, sg = 0;
+    std::vector<int32_t> first_seg(nb + 1, 0);
     out.seq_off[0] = 0; out.bundle_tx_off[0] = 0; out.tx_seg_off[0] = 0;
     for (size_t j = 0; j < nb; j++) {
         const Bundle& b = tr.bundles[bundle_ids[j]];
-        if (tr.fasta) so += (int64_t)(b.bend - b.bstart + 1);
+        so += bundle_bytes[j];
         out.seq_off[j + 1] = so;
         out.bundle_start[j] = b.bstart;
+        first_seg[j] = sg;
         for (int i = 0; i < b.count; i++, x++) {
             const Tx& t = tr.txs[b.first + i];
             out.tx_global[(size_t)x] = b.first + i;
@@ -102,16 +137,40 @@ void pack_bundles(const Transcriptome& tr, const std::vector<int>& bundle_ids, b
         }
         out.bundle_tx_off[j + 1] = x;
     }
-    if (tr.fasta && total_seq) {   // Bundle::load_seq, cpp:821-830
+    first_seg[nb] = sg;
+    if (has_seq && total_seq) {   // Bundle::load_seq, cpp:821-830
         std::vector<const std::string*> chrom(tr.seqnames.size(), nullptr);
         for (size_t k = 0; k < chrom.size(); k++) chrom[k] = tr.fasta->get(tr.seqnames[k]);
         auto copy_range = [&](size_t j0, size_t j1) {
+            std::vector<std::pair<int, int>> il;
+            std::vector<int32_t> il_off;
             for (size_t j = j0; j < j1; j++) {
                 const Bundle& b = tr.bundles[bundle_ids[j]];
-                memcpy(out.seq + out.seq_off[j], chrom[(size_t)b.seqid]->data() + (b.bstart - 1), (size_t)(b.bend - b.bstart + 1));
+                const char* src = chrom[(size_t)b.seqid]->data();
+                uint8_t* dst = out.seq + out.seq_off[j];
+                if (!islands) { memcpy(dst, src + (b.bstart - 1), (size_t)(b.bend - b.bstart + 1)); continue; }
+                bundle_islands(tr, b, keep_all_cds, il);
+                il_off.resize(il.size());
+                int32_t o = 0;
+                for (size_t k = 0; k < il.size(); k++) {
+                    il_off[k] = o;
+                    memcpy(dst + o, src + (il[k].first - 1), (size_t)(il[k].second - il[k].first + 1));
+                    o += il[k].second - il[k].first + 1;
+                }
+                // offset of every query segment: the island holding its start
+                for (int xx = out.bundle_tx_off[j]; xx < out.bundle_tx_off[j + 1]; xx++) {
+                    const bool isq = out.tx_kind[xx] == ORFX_TX_QUERY;
+                    for (int k = out.tx_seg_off[xx]; k < out.tx_seg_off[xx + 1]; k++) {
+                        if (!isq) { out.seg_seq_off[k] = 0; continue; }
+                        const int st = out.segs[k].start;
+                        size_t lo = 0, hi = il.size() - 1;
+                        while (lo < hi) { size_t mid = (lo + hi + 1) >> 1; if (il[mid].first <= st) lo = mid; else hi = mid - 1; }
+                        out.seg_seq_off[k] = il_off[lo] + (st - il[lo].first);
+                    }
+                }
             }
         };
-        unsigned nthr = total_seq > (64u << 20) ? std::min(8u, std::max(1u, std::thread::hardware_concurrency())) : 1u;
+        unsigned nthr = (total_seq > (32u << 20) || (islands && nb > 2000)) ? std::min(8u, std::max(1u, std::thread::hardware_concurrency())) : 1u;
         if (nthr <= 1) copy_range(0, nb);
         else {
             std::vector<std::thread> th;

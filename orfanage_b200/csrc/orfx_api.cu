@@ -81,6 +81,7 @@ struct orfx_ctx {
     cudaStream_t stream = nullptr;
     orfx_params P;
     // inputs
+    DBuf d_sso;
     DBuf d_seq, d_seq_off, d_bstart, d_btx_off, d_kind, d_strand, d_seg_off, d_cds_s, d_cds_e, d_tid, d_segs, d_phase;
     // derived
     DBuf d_seg_cum, d_tx_len, d_tx_bundle, d_mask_off, d_tile_off, d_q_off, d_q_list, d_row_off, d_tile_tx, d_stop, d_start;
@@ -106,7 +107,7 @@ namespace {
 int upload_batch(orfx_ctx* c, const orfx_batch* b) {
     if (!b) return fail(ORFX_E_INVALID, "null batch");
     if (b->n_bundles < 0 || b->n_tx < 0 || b->n_segs < 0) return fail(ORFX_E_INVALID, "negative batch size");
-    if (c->P.has_reference && b->n_bundles > 0 && !b->seq) return fail(ORFX_E_INVALID, "params.has_reference set but batch.seq is NULL");
+    if (c->P.has_reference && b->seq_bytes > 0 && !b->seq) return fail(ORFX_E_INVALID, "params.has_reference set but batch.seq is NULL");
     cudaStream_t s = c->stream;
     const size_t nb = (size_t)b->n_bundles, nt = (size_t)b->n_tx, ns = (size_t)b->n_segs;
     const size_t seqb = c->P.has_reference ? (size_t)b->seq_bytes : 0;
@@ -141,6 +142,8 @@ int upload_batch(orfx_ctx* c, const orfx_batch* b) {
     CU(cp(c->d_tid, b->tx_tid_class, nt * 4));
     CU(cp(c->d_segs, b->segs, ns * 8));
     CU(cp(c->d_phase, b->seg_phase, ns));
+    const bool islands = seqb && b->seg_seq_off;
+    if (islands) { CU(c->d_sso.ensure(ns * 4 + 4)); CU(cp(c->d_sso, b->seg_seq_off, ns * 4)); }
     // derived buffers whose size is known now
     CU(c->d_seg_cum.ensure(ns * 4 + 4));
     CU(c->d_tx_len.ensure(nt * 4 + 4));
@@ -169,6 +172,7 @@ int upload_batch(orfx_ctx* c, const orfx_batch* b) {
     B.seg_cum = c->d_seg_cum.as<int32_t>(); B.tx_len = c->d_tx_len.as<int32_t>(); B.tx_bundle = c->d_tx_bundle.as<int32_t>();
     B.tx_mask_off = c->d_mask_off.as<int64_t>(); B.tx_tile_off = c->d_tile_off.as<int64_t>(); B.tx_q_off = c->d_q_off.as<int64_t>();
     B.q_list = c->d_q_list.as<int32_t>(); B.q_row_off = c->d_row_off.as<int64_t>();
+    B.seg_seq_off = islands ? c->d_sso.as<int32_t>() : nullptr;
     B.bundle_need = c->d_need.as<uint8_t>(); B.planes = c->d_planes.as<uint32_t>(); B.plane_words = (int64_t)plane_words;
     c->resident = true;
     c->have_results = false;
@@ -386,7 +390,7 @@ void orfx_destroy(orfx_ctx* c) {
     if (!c) return;
     cudaSetDevice(c->device);
     cudaStreamSynchronize(c->stream);
-    DBuf* d[] = {&c->d_seq, &c->d_seq_off, &c->d_bstart, &c->d_btx_off, &c->d_kind, &c->d_strand, &c->d_seg_off, &c->d_cds_s, &c->d_cds_e, &c->d_tid,
+    DBuf* d[] = {&c->d_sso, &c->d_seq, &c->d_seq_off, &c->d_bstart, &c->d_btx_off, &c->d_kind, &c->d_strand, &c->d_seg_off, &c->d_cds_s, &c->d_cds_e, &c->d_tid,
                  &c->d_segs, &c->d_phase, &c->d_seg_cum, &c->d_tx_len, &c->d_tx_bundle, &c->d_mask_off, &c->d_tile_off, &c->d_q_off, &c->d_q_list,
                  &c->d_row_off, &c->d_tile_tx, &c->d_stop, &c->d_start, &c->d_need, &c->d_planes, &c->d_heavy, &c->d_heavy_count, &c->d_cnt_q, &c->d_cnt_words, &c->d_cnt_tiles, &c->d_cnt_rows, &c->d_scan_tmp,
                  &c->d_ord, &c->r_order, &c->d_best};

@@ -24,6 +24,7 @@ struct DevBatch {
     const int32_t* tx_tid_class;
     const orfx_seg* segs;
     const int8_t* seg_phase;
+    const int32_t* seg_seq_off;   // islands layout (else nullptr)
     // derived
     int32_t* seg_cum;        // [n_segs] bases of the transcript before this segment (genomic order)
     int32_t* tx_len;         // [n_tx] spliced length

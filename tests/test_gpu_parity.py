@@ -52,7 +52,15 @@ def test_results_match_oracle_bit_for_bit(synth, oracle_lib, gpu, seed, kw):
     d = synth(seed, **kw)
     w = ob.Workload(os.path.join(d, "query.gtf"), template_files(d), os.path.join(d, "genome.fa"))
     batch = w.pack()
+    windows = w.pack(1, 2, layout="windows") if seed == 21 else None
     assert batch.n_queries > 200
+    if windows is not None:   # the whole-window layout of the batch gives the same answers as the islands layout
+        params = ob.Params.make(mode="BEST")
+        gpu.set_params(params)
+        got = gpu.run(windows)
+        with ob.Context(params, lib=oracle_lib, prefix="orfx_oracle_") as ox:
+            assert_same_results(got, ox.run(windows), "windows layout")
+            assert_same_results(got, ox.run(w.pack(1, 2, layout="islands")), "windows vs islands")
     for pk in PARAM_GRID:
         params = ob.Params.make(**pk)
         gpu.set_params(params)

@@ -25,7 +25,7 @@ def test_device_library_exports_every_declared_symbol():
     for n in names:
         assert hasattr(lib, n), "liborfx.so does not export %s" % n
     ob.load_device_library()
-    assert lib.orfx_abi_version() == 1
+    assert lib.orfx_abi_version() == 2
 
 
 def test_host_library_exports_every_declared_symbol():
@@ -69,8 +69,9 @@ def test_product_does_not_link_or_import_the_oracle():
 def test_workload_counts_and_batch_layout(synth):
     d = synth(5, loci=40)
     w = ob.Workload(os.path.join(d, "query.gtf"), template_files(d), os.path.join(d, "genome.fa"))
-    b = w.pack()
+    b = w.pack(layout="windows")
     a = b.arrays
+    assert a["seg_seq_off"].size == 0
     assert w.count("active_bundles") == len(a["bundle_start"]) <= w.count("bundles")
     assert w.count("queries") == b.n_queries
     assert w.count("query_nt") == b.query_nt()
@@ -97,6 +98,34 @@ def test_workload_counts_and_batch_layout(synth):
     n = int(a["seq_off"][1])
     win = bytes(a["seq"][:n]).decode()
     assert win in fa and any(c.islower() for c in fa)
+    # islands layout: same chains, only the bases under query exons, every query segment finds its bytes
+    chroms = {}
+    name = None
+    for l in open(os.path.join(d, "genome.fa")):
+        if l.startswith(">"):
+            name = l[1:].split()[0]
+            chroms[name] = []
+        else:
+            chroms[name].append(l.strip())
+    chroms = {k: "".join(v) for k, v in chroms.items()}
+    bi = w.pack(layout="islands")
+    ai = bi.arrays
+    for k in ("segs", "tx_kind", "tx_seg_off", "bundle_tx_off", "bundle_start", "tx_cds_start", "seg_phase"):
+        assert (ai[k] == np.array(a[k])).all(), k
+    assert ai["seq"].size < a["seq"].size / 2 and ai["seg_seq_off"].size == ai["segs"].shape[0]
+    n_checked = 0
+    for j in range(len(ai["bundle_start"])):
+        for x in range(ai["bundle_tx_off"][j], ai["bundle_tx_off"][j + 1]):
+            if ai["tx_kind"][x] != 0:
+                continue
+            for k in range(ai["tx_seg_off"][x], ai["tx_seg_off"][x + 1]):
+                s0, e0 = ai["segs"][k]
+                o = int(ai["seq_off"][j]) + int(ai["seg_seq_off"][k])
+                assert o + (e0 - s0 + 1) <= ai["seq_off"][j + 1]
+                got = bytes(ai["seq"][o:o + (e0 - s0 + 1)]).decode()
+                assert any(c[s0 - 1:e0] == got for c in chroms.values())
+                n_checked += 1
+    assert n_checked > 1000
     w.close()
 
 
