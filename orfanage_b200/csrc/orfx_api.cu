@@ -160,7 +160,7 @@ int upload_batch(orfx_ctx* c, const orfx_batch* b) {
     CU(c->d_scan_tmp.ensure((size_t)scan_tmp_elems((int64_t)nt) * 8 + 8));
     CU(c->d_need.ensure(nb + 4));
     const size_t plane_words = (seqb + 31) / 32 + 4;
-    if (seqb) CU(c->d_planes.ensure(7 * plane_words * 4));
+    if (seqb) CU(c->d_planes.ensure(2 * plane_words * 16));
     CU(c->h_totals.ensure(64));
     DevBatch& B = c->B;
     memset(&B, 0, sizeof B);

@@ -36,9 +36,9 @@ struct DevBatch {
     int64_t* q_row_off;      // [n_tx+1] first candidate row of each query (entries past n_queries = total)
     int32_t* tile_tx;        // [n_tiles] transcript of each codon-scan tile
     uint8_t* bundle_need;    // [n_bundles] bit 0: holds a '+' query, bit 1: holds a query on another strand
-    uint32_t* planes;        // 7 base planes of the window bytes, plane k at planes + k * plane_words:
-                             //   0 T  1 A  2 G  3 R  ('+' transcripts)   1 A  4 T|U  5 C  6 Y  (reverse strand: T A G R)
-    int64_t plane_words;     // words per plane (bit i of a plane = byte i of `seq`)
+    uint32_t* planes;        // base planes of the window bytes, one uint4 per 32-byte chunk c and strand class:
+                             //   ((uint4*)planes)[c] = {T,A,G,R} ('+'), [plane_words + c] = {A,T|U,C,Y} (reverse strand: T A G R)
+    int64_t plane_words;     // chunks per strand class (bit i of a plane word = byte 32 c + i of `seq`)
     // codon-scan output: bit p of a transcript's region = codon starting at spliced position p (5'->3')
     uint32_t* stop_mask;
     uint32_t* start_mask;
@@ -54,8 +54,8 @@ struct DevRows {
     int64_t* print_order;
 };
 
-static constexpr int SCAN_TILE_WORDS = 31;     // mask words (32 spliced positions each) per codon-scan tile (one warp;
-                                               // the 32nd lane supplies the halo word)
+static constexpr int SCAN_TILE_WORDS = 256;    // mask words (32 spliced positions each) per codon-scan work item (one warp,
+                                               // 32 words per round)
 static constexpr int SCAN_WARPS_PER_CTA = 8;
 
 }  // namespace orfx

@@ -86,12 +86,23 @@ int64_t scan_tmp_elems(int64_t n) { return (n + SCAN_BLOCK - 1) / SCAN_BLOCK + 1
 // ------------------------------------------------------------------------------------------------
 // prep
 // ------------------------------------------------------------------------------------------------
-__global__ void tx_prep_kernel(DevBatch B, int64_t* cnt_q, int64_t* cnt_words, int64_t* cnt_tiles) {
-    int tx = blockIdx.x * blockDim.x + threadIdx.x;
+// one warp per transcript: coalesced segment loads, warp scan of the segment lengths
+__global__ void __launch_bounds__(256) tx_prep_kernel(DevBatch B, int64_t* cnt_q, int64_t* cnt_words, int64_t* cnt_tiles) {
+    const int tx = (int)(((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5), lane = threadIdx.x & 31;
     if (tx >= B.n_tx) return;
-    int s0 = B.tx_seg_off[tx], s1 = B.tx_seg_off[tx + 1];
+    const int s0 = B.tx_seg_off[tx], s1 = B.tx_seg_off[tx + 1];
     int acc = 0;
-    for (int k = s0; k < s1; k++) { B.seg_cum[k] = acc; orfx_seg sg = B.segs[k]; acc += sg.end - sg.start + 1; }
+    for (int base = s0; base < s1; base += 32) {
+        const int k = base + lane;
+        int len = 0;
+        if (k < s1) { const orfx_seg sg = B.segs[k]; len = sg.end - sg.start + 1; }
+        int incl = len;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) { const int v = __shfl_up_sync(0xffffffffu, incl, d); if (lane >= d) incl += v; }
+        if (k < s1) B.seg_cum[k] = acc + incl - len;
+        acc += __shfl_sync(0xffffffffu, incl, 31);
+    }
+    if (lane != 0) return;
     B.tx_len[tx] = acc;
     bool isq = B.tx_kind[tx] == ORFX_TX_QUERY;
     const int64_t words = acc > 0 ? (acc + 31) / 32 : 1;
@@ -125,7 +136,7 @@ __global__ void fill_tile_list_kernel(DevBatch B) {
 int launch_prep(const DevBatch& B, int64_t* cnt_q, int64_t* cnt_words, int64_t* cnt_tiles, int64_t* scan_tmp, cudaStream_t s) {
     int n = 0;
     if (B.n_tx == 0) return 0;
-    tx_prep_kernel<<<(B.n_tx + 255) / 256, 256, 0, s>>>(B, cnt_q, cnt_words, cnt_tiles); n++;
+    tx_prep_kernel<<<(unsigned)(((int64_t)B.n_tx * 32 + 255) / 256), 256, 0, s>>>(B, cnt_q, cnt_words, cnt_tiles); n++;
     bundle_prep_kernel<<<(B.n_bundles + 127) / 128, 128, 0, s>>>(B); n++;
     n += launch_exclusive_scan(cnt_q, B.tx_q_off, scan_tmp, B.n_tx, s);
     n += launch_exclusive_scan(cnt_words, B.tx_mask_off, scan_tmp, B.n_tx, s);
