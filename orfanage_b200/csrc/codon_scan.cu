@@ -27,6 +27,7 @@
 // Roofline accounting: algorithmic bytes = 1 B per spliced nucleotide read + 2 bits
 // written; the planes make the real DRAM traffic smaller than that (window bytes once + bits).
 #include "orfx_device.cuh"
+#include <climits>
 
 namespace orfx {
 
@@ -87,130 +88,116 @@ __global__ void __launch_bounds__(256) base_planes_kernel(DevBatch B, int64_t n_
 }
 
 // ---- 2. planes -> per-transcript stop / start masks ---------------------------------------------------
-// One warp per work item = up to SCAN_ITEM_WORDS mask words (8192 spliced positions) of one transcript,
-// walked 32 words at a time.  The warp reads the transcript's header once and stages its exon table
-// (spliced offset + bit position in the planes of every exon) in shared memory; a lane then finds the
-// exon piece(s) under its 32 positions with a short walk at shared-memory latency and fetches each
-// piece with two 128-bit plane loads.  The next 32 words are gathered before the current ones are
-// finished (software pipeline), which also supplies lane 31's look-ahead bits without a halo lane.
+// One THREAD per run of SCAN_TILE_WORDS consecutive mask words (128 spliced positions) of one transcript.
+// The thread locates the exon under the run's first position once, then streams: every round appends up
+// to 32 plane bits of the current exon piece to a 64-bit window per plane (one new 128-bit plane load
+// per round while it stays inside an exon) and, once 34 bits are there (32 positions + the two
+// look-ahead bases of the last codons), evaluates the codon logic on whole words and emits one word of
+// each mask.  Per-word costs of a gather formulation (exon search, junction masks, neighbour shuffles)
+// are paid once per run or once per exon junction instead.  The run's words are parked in shared memory
+// (dynamic index) and leave as one 128-bit store per mask.
 namespace {
-constexpr int SCAN_SMEM_EXONS = 128;   // exon tables up to this size are staged per warp; longer chains stay in global memory
+struct Win { uint64_t T, A, G, R; };
 
-struct P4 { uint32_t T, A, G, R; };
-
-struct ExonTable {
-    const int32_t* cum;     // [n+1] spliced offset of each exon (genomic order), cum[n] = L   (shared)   or seg_cum + s0 (global, no sentinel)
-    const int32_t* pos;     // [n]   bit position of the exon's first base relative to the warp's plane base (shared only)
-    const orfx_seg* segs;   // global fallback
-    const int32_t* sso;     // global fallback (islands) or nullptr
-    int n, L, bstart, base_sh;
-    bool staged;
-    __device__ __forceinline__ int cum_at(int k) const { return (staged || k < n) ? cum[k] : L; }
-    __device__ __forceinline__ int pos_at(int k) const {
-        if (staged) return pos[k];
-        return (sso ? sso[k] : segs[k].start - bstart) + base_sh;
+__device__ __forceinline__ void win_append(Win& w, const uint4& lo, const uint4& hi, uint32_t sh, int take, int fill, bool reverse) {
+    const uint32_t m = 0xFFFFFFFFu >> (32 - take);
+    uint32_t t = __funnelshift_r(lo.x, hi.x, sh) & m, a = __funnelshift_r(lo.y, hi.y, sh) & m;
+    uint32_t g = __funnelshift_r(lo.z, hi.z, sh) & m, r = __funnelshift_r(lo.w, hi.w, sh) & m;
+    if (reverse) {   // genomic order -> transcript order
+        const int rs = 32 - take;
+        t = __brev(t) >> rs; a = __brev(a) >> rs; g = __brev(g) >> rs; r = __brev(r) >> rs;
     }
-};
-
-// the four plane words of spliced offsets [u0, u0+n) in genomic order; k = exon holding u0
-__device__ __forceinline__ P4 gather_word(const ExonTable& E, const uint4* __restrict__ pl, int u0, int n, int k) {
-    P4 r{0, 0, 0, 0};
-    int filled = 0;
-    while (filled < n && k < E.n) {
-        const int u = u0 + filled;
-        const int take = min(n - filled, E.cum_at(k + 1) - u);
-        const int bit = E.pos_at(k) + (u - E.cum_at(k));
-        const uint4 lo = __ldg(pl + (bit >> 5)), hi = __ldg(pl + (bit >> 5) + 1);
-        const uint32_t sh = (uint32_t)bit & 31u, m = 0xFFFFFFFFu >> (32 - take);
-        r.T |= (__funnelshift_r(lo.x, hi.x, sh) & m) << filled;
-        r.A |= (__funnelshift_r(lo.y, hi.y, sh) & m) << filled;
-        r.G |= (__funnelshift_r(lo.z, hi.z, sh) & m) << filled;
-        r.R |= (__funnelshift_r(lo.w, hi.w, sh) & m) << filled;
-        filled += take;
-        k++;
-    }
-    return r;
+    w.T |= (uint64_t)t << fill; w.A |= (uint64_t)a << fill; w.G |= (uint64_t)g << fill; w.R |= (uint64_t)r << fill;
 }
 }  // namespace
 
-__global__ void __launch_bounds__(SCAN_WARPS_PER_CTA * 32) codon_scan_kernel(DevBatch B, int64_t n_items) {
-    __shared__ int32_t s_cum[SCAN_WARPS_PER_CTA][SCAN_SMEM_EXONS + 1];
-    __shared__ int32_t s_pos[SCAN_WARPS_PER_CTA][SCAN_SMEM_EXONS];
-    const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
-    const int64_t item = (int64_t)blockIdx.x * SCAN_WARPS_PER_CTA + wib;
-    if (item >= n_items) return;
-    const int tx = B.tile_tx[item];
+__global__ void __launch_bounds__(CSCAN_THREADS) codon_scan_kernel(DevBatch B, int64_t n_tiles) {
+    __shared__ uint32_t s_out[2][SCAN_TILE_WORDS][CSCAN_THREADS];
+    const int tid = threadIdx.x;
+    const int64_t tile = (int64_t)blockIdx.x * CSCAN_THREADS + tid;
+    if (tile >= n_tiles) return;
+    const int tx = B.tile_tx[tile];
     const int L = B.tx_len[tx];
+    const int nwords = (L + 31) >> 5;
+    const int w0 = (int)(tile - B.tx_tile_off[tx]) * SCAN_TILE_WORDS;
+    const int nw = min(SCAN_TILE_WORDS, nwords - w0);
+    if (nw <= 0) return;
     const bool plus = B.tx_strand[tx] == '+';
     const int s0 = B.tx_seg_off[tx], nseg = B.tx_seg_off[tx + 1] - s0;
     const int bundle = B.tx_bundle[tx];
-    const int nwords = (L + 31) >> 5;
-    const int w_begin = (int)(item - B.tx_tile_off[tx]) * SCAN_TILE_WORDS;
-    const int w_end = min(nwords, w_begin + SCAN_TILE_WORDS);
     const bool isl = B.seg_seq_off != nullptr;
     const int64_t base = B.seq_off[bundle];   // byte (= plane bit) offset of the bundle's first base
-    const uint4* pl = reinterpret_cast<const uint4*>(B.planes) + (plus ? 0 : B.plane_words) + (base >> 5);
-    ExonTable E;
-    E.n = nseg; E.L = L; E.bstart = isl ? 0 : B.bundle_start[bundle]; E.base_sh = (int)(base & 31);
-    E.segs = B.segs + s0; E.sso = isl ? B.seg_seq_off + s0 : nullptr;
-    E.staged = nseg <= SCAN_SMEM_EXONS;
-    if (E.staged) {
-        for (int i = lane; i < nseg; i += 32) {
-            s_cum[wib][i] = B.seg_cum[s0 + i];
-            s_pos[wib][i] = (isl ? B.seg_seq_off[s0 + i] : B.segs[s0 + i].start - E.bstart) + E.base_sh;
-        }
-        if (lane == 0) s_cum[wib][nseg] = L;
-        __syncwarp();
-        E.cum = s_cum[wib]; E.pos = s_pos[wib];
-    } else {
-        E.cum = B.seg_cum + s0; E.pos = nullptr;
+    const int base_sh = (int)(base & 31);
+    const int bstart = isl ? 0 : B.bundle_start[bundle];
+    const uint4* __restrict__ pl = reinterpret_cast<const uint4*>(B.planes) + (plus ? 0 : B.plane_words) + (base >> 5);
+    const int32_t* __restrict__ cum = B.seg_cum + s0;
+    const orfx_seg* __restrict__ segs = B.segs + s0;
+    const int32_t* __restrict__ sso = isl ? B.seg_seq_off + s0 : nullptr;
+    auto cum_at = [&](int k) { return k < nseg ? cum[k] : L; };
+    auto pos_at = [&](int k) { return (isl ? sso[k] : segs[k].start - bstart) + base_sh; };
+
+    const int p_lo = w0 << 5;
+    const int nbits = min(L, ((w0 + nw) << 5) + 2) - p_lo;   // spliced positions this run reads, look-ahead included
+    // exon under the first position (genomic-order spliced offset u): last k with cum[k] <= u
+    const int u = plus ? p_lo : L - 1 - p_lo;
+    int k;
+    {
+        int lo = 0, hi = nseg - 1;
+        while (lo < hi) { const int mid = (lo + hi + 1) >> 1; if (cum[mid] <= u) lo = mid; else hi = mid - 1; }
+        k = lo;
     }
-    int k = 0;          // exon under this lane's current offset
-    bool first = true;
-    // planes of mask word w of this transcript, in transcript order (bit j = spliced position 32 w + j)
-    auto word_planes = [&](int w) -> P4 {
-        const int p0 = w << 5, n = min(32, L - p0);
-        const int u0 = plus ? p0 : L - p0 - n;
-        if (first) {   // exon holding u0: last k with cum[k] <= u0
-            int lo = 0, hi = nseg - 1;
-            while (lo < hi) { const int mid = (lo + hi + 1) >> 1; if (E.cum_at(mid) <= u0) lo = mid; else hi = mid - 1; }
-            k = lo; first = false;
-        } else {
-            while (k + 1 < nseg && E.cum_at(k + 1) <= u0) k++;
-            while (k > 0 && E.cum_at(k) > u0) k--;
+    int c0 = cum[k], c1 = cum_at(k + 1);
+    int rem = plus ? c1 - u : u - c0 + 1;     // positions left in the current exon, in reading direction
+    int bit = pos_at(k) + (u - c0);           // plane bit of the next position to read
+    Win w{0, 0, 0, 0};
+    uint4 lo = make_uint4(0, 0, 0, 0), hi = lo;
+    int ci = INT_MIN;                         // plane chunk held in lo (hi = chunk ci + 1)
+    int fill = 0, produced = 0, emitted = 0;
+    while (emitted < nw) {
+        if (fill < 34 && produced < nbits) {
+            const int take = min(min(32, rem), min(nbits - produced, 64 - fill));
+            const int lowbit = plus ? bit : bit - take + 1;
+            const int ni = lowbit >> 5;
+            if (ni != ci) {
+                if (ni == ci + 1) { lo = hi; hi = __ldg(pl + ni + 1); }
+                else if (ni == ci - 1) { hi = lo; lo = __ldg(pl + ni); }
+                else { lo = __ldg(pl + ni); hi = __ldg(pl + ni + 1); }
+                ci = ni;
+            }
+            win_append(w, lo, hi, (uint32_t)lowbit & 31u, take, fill, !plus);
+            fill += take; produced += take; rem -= take;
+            bit += plus ? take : -take;
+            if (rem == 0 && produced < nbits) {   // next exon in reading direction
+                k += plus ? 1 : -1;
+                c0 = cum[k]; c1 = cum_at(k + 1);
+                rem = c1 - c0;
+                bit = pos_at(k) + (plus ? 0 : rem - 1);
+            }
         }
-        P4 r = gather_word(E, pl, u0, n, k);
-        if (!plus) {   // genomic order -> transcript order: bit j <- bit n-1-j
-            const int sh = 32 - n;
-            r.T = __brev(r.T) >> sh; r.A = __brev(r.A) >> sh; r.G = __brev(r.G) >> sh; r.R = __brev(r.R) >> sh;
-        }
-        return r;
-    };
-    const int64_t mbase = B.tx_mask_off[tx];
-    P4 cur{0, 0, 0, 0};
-    if (w_begin + lane < w_end) cur = word_planes(w_begin + lane);
-    for (int wb = w_begin; wb < w_end; wb += 32) {
-        const int wn = wb + 32 + lane;
-        P4 nxt{0, 0, 0, 0};
-        if (wn < nwords && (wn < w_end || lane == 0)) nxt = word_planes(wn);   // past the item only lane 0: the look-ahead word
-        // the next word's planes live in the neighbour lane; lane 31 takes lane 0's of the next round
-        uint32_t T1w = __shfl_down_sync(0xffffffffu, cur.T, 1), A1w = __shfl_down_sync(0xffffffffu, cur.A, 1);
-        uint32_t G1w = __shfl_down_sync(0xffffffffu, cur.G, 1), R1w = __shfl_down_sync(0xffffffffu, cur.R, 1);
-        const uint32_t T1n = __shfl_sync(0xffffffffu, nxt.T, 0), A1n = __shfl_sync(0xffffffffu, nxt.A, 0);
-        const uint32_t G1n = __shfl_sync(0xffffffffu, nxt.G, 0), R1n = __shfl_sync(0xffffffffu, nxt.R, 0);
-        if (lane == 31) { T1w = T1n; A1w = A1n; G1w = G1n; R1w = R1n; }
-        const int w = wb + lane;
-        if (w < w_end) {
-            const uint32_t A1 = __funnelshift_r(cur.A, A1w, 1), A2 = __funnelshift_r(cur.A, A1w, 2);
-            const uint32_t G1 = __funnelshift_r(cur.G, G1w, 1), G2 = __funnelshift_r(cur.G, G1w, 2);
-            const uint32_t R1 = __funnelshift_r(cur.R, R1w, 1), R2 = __funnelshift_r(cur.R, R1w, 2);
-            const uint32_t T1 = __funnelshift_r(cur.T, T1w, 1);
+        if (fill >= 34 || produced >= nbits) {
+            const uint32_t T0 = (uint32_t)w.T, A0 = (uint32_t)w.A;
+            const uint32_t T1 = (uint32_t)(w.T >> 1);
+            const uint32_t A1 = (uint32_t)(w.A >> 1), A2 = (uint32_t)(w.A >> 2);
+            const uint32_t G1 = (uint32_t)(w.G >> 1), G2 = (uint32_t)(w.G >> 2);
+            const uint32_t R1 = (uint32_t)(w.R >> 1), R2 = (uint32_t)(w.R >> 2);
             // TAA TAG TAR | TGA TRA ; ATG
-            B.stop_mask[mbase + w] = cur.T & ((A1 & (A2 | G2 | R2)) | ((G1 | R1) & A2));
-            B.start_mask[mbase + w] = cur.A & T1 & G2;
+            s_out[0][emitted][tid] = T0 & ((A1 & (A2 | G2 | R2)) | ((G1 | R1) & A2));
+            s_out[1][emitted][tid] = A0 & T1 & G2;
+            emitted++;
+            w.T >>= 32; w.A >>= 32; w.G >>= 32; w.R >>= 32;
+            fill = max(fill - 32, 0);
         }
-        cur = nxt;
     }
+    // mask regions are 16-byte aligned and padded to 4 words; a run starts on a 4-word boundary
+    static_assert(SCAN_TILE_WORDS == 4, "the store below writes one uint4 per mask");
+    uint4 so, sa;
+    so.x = s_out[0][0][tid]; sa.x = s_out[1][0][tid];
+    so.y = nw > 1 ? s_out[0][1][tid] : 0u; sa.y = nw > 1 ? s_out[1][1][tid] : 0u;
+    so.z = nw > 2 ? s_out[0][2][tid] : 0u; sa.z = nw > 2 ? s_out[1][2][tid] : 0u;
+    so.w = nw > 3 ? s_out[0][3][tid] : 0u; sa.w = nw > 3 ? s_out[1][3][tid] : 0u;
+    const int64_t at = B.tx_mask_off[tx] + w0;
+    *reinterpret_cast<uint4*>(B.stop_mask + at) = so;
+    *reinterpret_cast<uint4*>(B.start_mask + at) = sa;
 }
 
 int launch_base_planes(const DevBatch& B, cudaStream_t stream) {
@@ -224,8 +211,8 @@ int launch_base_planes(const DevBatch& B, cudaStream_t stream) {
 void launch_codon_scan(const DevBatch& B, int64_t n_items, int n_sm, cudaStream_t stream) {
     (void)n_sm;
     if (n_items <= 0) return;
-    const int64_t grid = (n_items + SCAN_WARPS_PER_CTA - 1) / SCAN_WARPS_PER_CTA;
-    codon_scan_kernel<<<(unsigned)grid, SCAN_WARPS_PER_CTA * 32, 0, stream>>>(B, n_items);
+    const int64_t grid = (n_items + CSCAN_THREADS - 1) / CSCAN_THREADS;
+    codon_scan_kernel<<<(unsigned)grid, CSCAN_THREADS, 0, stream>>>(B, n_items);
 }
 
 }  // namespace orfx

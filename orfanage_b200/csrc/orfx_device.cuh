@@ -54,8 +54,7 @@ struct DevRows {
     int64_t* print_order;
 };
 
-static constexpr int SCAN_TILE_WORDS = 256;    // mask words (32 spliced positions each) per codon-scan work item (one warp,
-                                               // 32 words per round)
-static constexpr int SCAN_WARPS_PER_CTA = 8;
+static constexpr int SCAN_TILE_WORDS = 4;      // mask words (32 spliced positions each) per codon-scan run (one thread)
+static constexpr int CSCAN_THREADS = 256;
 
 }  // namespace orfx
