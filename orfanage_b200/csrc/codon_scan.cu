@@ -88,14 +88,14 @@ __global__ void __launch_bounds__(256) base_planes_kernel(DevBatch B, int64_t n_
 }
 
 // ---- 2. planes -> per-transcript stop / start masks ---------------------------------------------------
-// One THREAD per run of SCAN_TILE_WORDS consecutive mask words (128 spliced positions) of one transcript.
+// One THREAD per run of SCAN_TILE_WORDS consecutive mask words (256 spliced positions) of one transcript.
 // The thread locates the exon under the run's first position once, then streams: every round appends up
 // to 32 plane bits of the current exon piece to a 64-bit window per plane (one new 128-bit plane load
 // per round while it stays inside an exon) and, once 34 bits are there (32 positions + the two
 // look-ahead bases of the last codons), evaluates the codon logic on whole words and emits one word of
 // each mask.  Per-word costs of a gather formulation (exon search, junction masks, neighbour shuffles)
 // are paid once per run or once per exon junction instead.  The run's words are parked in shared memory
-// (dynamic index) and leave as one 128-bit store per mask.
+// (dynamic index) and leave as 128-bit stores.
 namespace {
 struct Win { uint64_t T, A, G, R; };
 
@@ -158,10 +158,11 @@ __global__ void __launch_bounds__(CSCAN_THREADS) codon_scan_kernel(DevBatch B, i
             const int take = min(min(32, rem), min(nbits - produced, 64 - fill));
             const int lowbit = plus ? bit : bit - take + 1;
             const int ni = lowbit >> 5;
-            if (ni != ci) {
-                if (ni == ci + 1) { lo = hi; hi = __ldg(pl + ni + 1); }
-                else if (ni == ci - 1) { hi = lo; lo = __ldg(pl + ni); }
-                else { lo = __ldg(pl + ni); hi = __ldg(pl + ni + 1); }
+            if (ni != ci) {   // steady state inside an exon: one new chunk per round, the other is carried over
+                const bool fwd = ni == ci + 1, bwd = ni == ci - 1;
+                const uint4 keep_lo = lo;
+                if (fwd) lo = hi; else lo = __ldg(pl + ni);
+                if (bwd) hi = keep_lo; else hi = __ldg(pl + ni + 1);
                 ci = ni;
             }
             win_append(w, lo, hi, (uint32_t)lowbit & 31u, take, fill, !plus);
@@ -189,15 +190,18 @@ __global__ void __launch_bounds__(CSCAN_THREADS) codon_scan_kernel(DevBatch B, i
         }
     }
     // mask regions are 16-byte aligned and padded to 4 words; a run starts on a 4-word boundary
-    static_assert(SCAN_TILE_WORDS == 4, "the store below writes one uint4 per mask");
-    uint4 so, sa;
-    so.x = s_out[0][0][tid]; sa.x = s_out[1][0][tid];
-    so.y = nw > 1 ? s_out[0][1][tid] : 0u; sa.y = nw > 1 ? s_out[1][1][tid] : 0u;
-    so.z = nw > 2 ? s_out[0][2][tid] : 0u; sa.z = nw > 2 ? s_out[1][2][tid] : 0u;
-    so.w = nw > 3 ? s_out[0][3][tid] : 0u; sa.w = nw > 3 ? s_out[1][3][tid] : 0u;
     const int64_t at = B.tx_mask_off[tx] + w0;
-    *reinterpret_cast<uint4*>(B.stop_mask + at) = so;
-    *reinterpret_cast<uint4*>(B.start_mask + at) = sa;
+#pragma unroll
+    for (int q = 0; q < SCAN_TILE_WORDS / 4; q++) {
+        if (q * 4 >= nw) break;
+        uint4 so, sa;
+        so.x = s_out[0][q * 4][tid]; sa.x = s_out[1][q * 4][tid];
+        so.y = nw > q * 4 + 1 ? s_out[0][q * 4 + 1][tid] : 0u; sa.y = nw > q * 4 + 1 ? s_out[1][q * 4 + 1][tid] : 0u;
+        so.z = nw > q * 4 + 2 ? s_out[0][q * 4 + 2][tid] : 0u; sa.z = nw > q * 4 + 2 ? s_out[1][q * 4 + 2][tid] : 0u;
+        so.w = nw > q * 4 + 3 ? s_out[0][q * 4 + 3][tid] : 0u; sa.w = nw > q * 4 + 3 ? s_out[1][q * 4 + 3][tid] : 0u;
+        *reinterpret_cast<uint4*>(B.stop_mask + at + q * 4) = so;
+        *reinterpret_cast<uint4*>(B.start_mask + at + q * 4) = sa;
+    }
 }
 
 int launch_base_planes(const DevBatch& B, cudaStream_t stream) {

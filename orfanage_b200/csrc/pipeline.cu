@@ -125,11 +125,12 @@ __global__ void fill_q_list_kernel(DevBatch B) {
     if (tx >= B.n_tx) return;
     if (B.tx_kind[tx] == ORFX_TX_QUERY) B.q_list[B.tx_q_off[tx]] = tx;
 }
-__global__ void __launch_bounds__(256) fill_tile_list_kernel(DevBatch B) {   // one warp per transcript, coalesced
-    const int tx = (int)(((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5), lane = threadIdx.x & 31;
+__global__ void __launch_bounds__(256) fill_tile_list_kernel(DevBatch B) {   // 8 lanes per transcript
+    const int64_t gt = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int tx = (int)(gt >> 3), sub = (int)(gt & 7);
     if (tx >= B.n_tx || B.tx_kind[tx] != ORFX_TX_QUERY) return;
     const int64_t t1 = B.tx_tile_off[tx + 1];
-    for (int64_t t = B.tx_tile_off[tx] + lane; t < t1; t += 32) B.tile_tx[t] = tx;
+    for (int64_t t = B.tx_tile_off[tx] + sub; t < t1; t += 8) B.tile_tx[t] = tx;
 }
 // Everything that needs no host-side size: lengths, prefixes, the three per-transcript scans, the
 // query list (capacity n_tx).  The totals land in tx_q_off[n_tx], tx_mask_off[n_tx], tx_tile_off[n_tx].
@@ -146,7 +147,7 @@ int launch_prep(const DevBatch& B, int64_t* cnt_q, int64_t* cnt_words, int64_t* 
 }
 int launch_fill_tiles(const DevBatch& B, cudaStream_t s) {
     if (B.n_tx == 0) return 0;
-    fill_tile_list_kernel<<<(unsigned)(((int64_t)B.n_tx * 32 + 255) / 256), 256, 0, s>>>(B);
+    fill_tile_list_kernel<<<(unsigned)(((int64_t)B.n_tx * 8 + 255) / 256), 256, 0, s>>>(B);
     return 1;
 }
 
