@@ -79,24 +79,32 @@ __device__ __forceinline__ int next_inframe(const uint32_t* m, int p, int L) {
         if ((w & 3) == 0) break;
         x = m[w] & frame_pattern(w, r);
     }
+    // 16 words per round, four independent 128-bit loads in flight plus the next round's four: an ORF's
+    // stop is typically kilobases away, and one dependent load per 128 positions would make that a
+    // latency chain
     uint32_t pa = frame_pattern(w, r), pb = frame_pattern(w + 1, r), pc = frame_pattern(w + 2, r);
-    uint4 v = *reinterpret_cast<const uint4*>(m + w);
+    const uint4 zero = make_uint4(0, 0, 0, 0);
+    auto load4 = [&](int at) { return at < nw ? *reinterpret_cast<const uint4*>(m + at) : zero; };
+    auto hit4 = [&](const uint4& v, int at, uint32_t a, uint32_t b, uint32_t c) {   // first set in-frame bit of words [at, at+4), or -1
+        const uint32_t x0 = v.x & a, x1 = v.y & b, x2 = v.z & c, x3 = v.w & a;
+        if (!(x0 | x1 | x2 | x3)) return -1;
+        if (x0) return (at << 5) + __ffs(x0) - 1;
+        if (x1) return ((at + 1) << 5) + __ffs(x1) - 1;
+        if (x2) return ((at + 2) << 5) + __ffs(x2) - 1;
+        return ((at + 3) << 5) + __ffs(x3) - 1;
+    };
+    uint4 v0 = load4(w), v1 = load4(w + 4), v2 = load4(w + 8), v3 = load4(w + 12);
     while (true) {
-        const int wn = w + 4;
-        uint4 nx = make_uint4(0, 0, 0, 0);
-        if (wn < nw) nx = *reinterpret_cast<const uint4*>(m + wn);
-        const uint32_t x0 = v.x & pa, x1 = v.y & pb, x2 = v.z & pc, x3 = v.w & pa;
-        if (x0 | x1 | x2 | x3) {
-            int q;
-            if (x0) q = (w << 5) + __ffs(x0) - 1;
-            else if (x1) q = ((w + 1) << 5) + __ffs(x1) - 1;
-            else if (x2) q = ((w + 2) << 5) + __ffs(x2) - 1;
-            else q = ((w + 3) << 5) + __ffs(x3) - 1;
-            return q < L ? q : -1;   // words past the last real one are padding: any bit there is >= L
-        }
+        const int wn = w + 16;
+        const uint4 n0 = load4(wn), n1 = load4(wn + 4), n2 = load4(wn + 8), n3 = load4(wn + 12);
+        int q = hit4(v0, w, pa, pb, pc);                 // 4 words on, the frame pattern advances by one
+        if (q < 0) q = hit4(v1, w + 4, pb, pc, pa);
+        if (q < 0) q = hit4(v2, w + 8, pc, pa, pb);
+        if (q < 0) q = hit4(v3, w + 12, pa, pb, pc);
+        if (q >= 0) return q < L ? q : -1;               // words past the last real one are padding: any bit there is >= L
         if (wn >= nw) return -1;
-        w = wn; v = nx;
-        const uint32_t t = pa; pa = pb; pb = pc; pc = t;   // 4 words on: the frame pattern advances by one
+        w = wn; v0 = n0; v1 = n1; v2 = n2; v3 = n3;
+        const uint32_t t = pa; pa = pb; pb = pc; pc = t;  // 16 words on: one step as well
     }
 }
 // largest q <= p with q == p (mod 3), q >= 0 and bit set; -1 when none

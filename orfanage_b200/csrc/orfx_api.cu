@@ -12,11 +12,14 @@
 namespace orfx {
 int launch_exclusive_scan(const int64_t* in, int64_t* out, int64_t* tmp, int64_t n, cudaStream_t s);
 int64_t scan_tmp_elems(int64_t n);
-int launch_prep(const DevBatch& B, int64_t* cnt_q, int64_t* cnt_words, int64_t* cnt_tiles, int64_t* scan_tmp, cudaStream_t s);
+int launch_prep(const DevBatch& B, int64_t* cnt_q, int64_t* cnt_words, int64_t* cnt_tiles, int64_t* scan_tmp, int32_t* heavy_list, unsigned* heavy_count,
+                cudaStream_t s);
 int launch_fill_tiles(const DevBatch& B, cudaStream_t s);
-int launch_count_rows(const DevBatch& B, int64_t* cnt, int64_t* scan_tmp, cudaStream_t s);
+int launch_count_rows(const DevBatch& B, int64_t* cnt, int64_t* scan_tmp, const int32_t* heavy_list, const unsigned* heavy_count, int n_sm, cudaStream_t s);
 int launch_fill_rows(const DevBatch& B, const DevRows& R, int n_queries, cudaStream_t s);
-int launch_rescue_score(const DevBatch& B, const DevRows& R, const orfx_params& P, int32_t* heavy_list, unsigned* heavy_count, int n_sm, cudaStream_t s);
+int launch_rescue_score(const DevBatch& B, const DevRows& R, const orfx_params& P, cudaStream_t s);
+int launch_heavy_fill_rescue(const DevBatch& B, const DevRows& R, const orfx_params& P, const int32_t* heavy_list, const unsigned* heavy_count, int n_sm,
+                             cudaStream_t s);
 int launch_select(const DevBatch& B, const DevRows& R, const orfx_params& P, int n_queries, orfx_best* best_out, int32_t* ord_scratch, cudaStream_t s);
 void launch_codon_scan(const DevBatch& B, int64_t n_tiles, int n_sm, cudaStream_t stream);
 int launch_base_planes(const DevBatch& B, cudaStream_t stream);
@@ -70,8 +73,8 @@ struct HBuf {
     template <class T> T* as() const { return reinterpret_cast<T*>(p); }
 };
 
-enum { ST_PREP = 0, ST_COUNT, ST_PLANES, ST_SCAN, ST_FILL, ST_RESCUE, ST_SELECT, ST_N };
-const char* STAGE_NAME[ST_N] = {"prep", "count_rows", "base_planes", "codon_scan", "fill_rows", "rescue_score", "select"};
+enum { ST_PREP = 0, ST_COUNT, ST_PLANES, ST_SCAN, ST_FILL, ST_HEAVY, ST_RESCUE, ST_SELECT, ST_N };
+const char* STAGE_NAME[ST_N] = {"prep", "count_rows", "base_planes", "codon_scan", "fill_rows", "heavy_bundles", "rescue_score", "select"};
 
 }  // namespace
 
@@ -159,6 +162,8 @@ int upload_batch(orfx_ctx* c, const orfx_batch* b) {
     CU(c->d_cnt_rows.ensure(nt * 8 + 8));
     CU(c->d_scan_tmp.ensure((size_t)scan_tmp_elems((int64_t)nt) * 8 + 8));
     CU(c->d_need.ensure(nb + 4));
+    CU(c->d_heavy.ensure(nb * 4 + 4));
+    CU(c->d_heavy_count.ensure(16));
     const size_t plane_words = (seqb + 31) / 32 + 4;
     if (seqb) CU(c->d_planes.ensure(2 * plane_words * 16));
     CU(c->h_totals.ensure(64));
@@ -191,10 +196,12 @@ int run_path(orfx_ctx* c) {
     cudaEventRecord(c->run_ev[0], s);
     if (B.n_tx == 0) { cudaEventRecord(c->run_ev[1], s); return ORFX_OK; }
     stage_begin(c, ST_PREP);
-    c->n_launches += launch_prep(B, c->d_cnt_q.as<int64_t>(), c->d_cnt_words.as<int64_t>(), c->d_cnt_tiles.as<int64_t>(), c->d_scan_tmp.as<int64_t>(), s);
+    c->n_launches += launch_prep(B, c->d_cnt_q.as<int64_t>(), c->d_cnt_words.as<int64_t>(), c->d_cnt_tiles.as<int64_t>(), c->d_scan_tmp.as<int64_t>(),
+                                 c->d_heavy.as<int32_t>(), c->d_heavy_count.as<unsigned>(), s);
     stage_end(c, ST_PREP);
     stage_begin(c, ST_COUNT);
-    c->n_launches += launch_count_rows(B, c->d_cnt_rows.as<int64_t>(), c->d_scan_tmp.as<int64_t>(), s);
+    c->n_launches += launch_count_rows(B, c->d_cnt_rows.as<int64_t>(), c->d_scan_tmp.as<int64_t>(), c->d_heavy.as<int32_t>(), c->d_heavy_count.as<unsigned>(),
+                                       c->n_sm, s);
     stage_end(c, ST_COUNT);
     // the only host round trip of the path: four totals that size the remaining buffers
     int64_t* tot = c->h_totals.as<int64_t>();
@@ -217,8 +224,6 @@ int run_path(orfx_ctx* c) {
     CU(c->r_order.ensure((size_t)nrows * 8 + 8));
     if (nrows > (int64_t)INT32_MAX) return fail(ORFX_E_INVALID, "more than 2^31 candidate rows in one batch: shard it");
     CU(c->d_ord.ensure((size_t)nrows * 4 + 4));
-    CU(c->d_heavy.ensure((size_t)nrows * 4 + 4));
-    CU(c->d_heavy_count.ensure(16));
     CU(c->d_best.ensure((size_t)nq * sizeof(orfx_best) + 8));
     DevRows& R = c->R;
     R.n_rows = nrows;
@@ -244,8 +249,11 @@ int run_path(orfx_ctx* c) {
     stage_begin(c, ST_FILL);
     c->n_launches += launch_fill_rows(B, R, (int)nq, s);
     stage_end(c, ST_FILL);
+    stage_begin(c, ST_HEAVY);
+    c->n_launches += launch_heavy_fill_rescue(B, R, c->P, c->d_heavy.as<int32_t>(), c->d_heavy_count.as<unsigned>(), c->n_sm, s);
+    stage_end(c, ST_HEAVY);
     stage_begin(c, ST_RESCUE);
-    c->n_launches += launch_rescue_score(B, R, c->P, c->d_heavy.as<int32_t>(), c->d_heavy_count.as<unsigned>(), c->n_sm, s);
+    c->n_launches += launch_rescue_score(B, R, c->P, s);
     stage_end(c, ST_RESCUE);
     stage_begin(c, ST_SELECT);
     c->n_launches += launch_select(B, R, c->P, (int)nq, c->d_best.as<orfx_best>(), c->d_ord.as<int32_t>(), s);

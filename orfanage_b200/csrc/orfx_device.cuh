@@ -54,7 +54,7 @@ struct DevRows {
     int64_t* print_order;
 };
 
-static constexpr int SCAN_TILE_WORDS = 8;      // mask words (32 spliced positions each) per codon-scan run (one thread)
+static constexpr int SCAN_TILE_WORDS = 16;     // mask words (32 spliced positions each) per codon-scan run (one thread)
 static constexpr int CSCAN_THREADS = 256;
 
 }  // namespace orfx

@@ -110,13 +110,30 @@ __global__ void __launch_bounds__(256) tx_prep_kernel(DevBatch B, int64_t* cnt_q
     cnt_tiles[tx] = isq ? (words + SCAN_TILE_WORDS - 1) / SCAN_TILE_WORDS : 0;
     cnt_words[tx] = isq ? ((words + 3) & ~(int64_t)3) : 0;   // 16-byte aligned mask regions
 }
-__global__ void bundle_prep_kernel(DevBatch B) {
+// A bundle is "heavy" when one of its transcripts has more than HEAVY_TX_SEGS segments (titin-class loci):
+// chain walks over such transcripts are long dependent-load chains that would make single threads the
+// tail of every row kernel.  Heavy bundles are listed here and handled by the CTA-per-bundle kernels
+// below, which stage the bundle's chains in shared memory; the thread-per-query / thread-per-row
+// kernels skip them.
+constexpr int HEAVY_TX_SEGS = 32;
+constexpr uint8_t BUNDLE_HEAVY = 4;
+
+__global__ void bundle_prep_kernel(DevBatch B, int32_t* heavy_list, unsigned* heavy_count) {
     int b = blockIdx.x * blockDim.x + threadIdx.x;
     if (b >= B.n_bundles) return;
     uint32_t need = 0;
+    int max_segs = 0;
+    bool has_q = false, has_t = false;
     for (int x = B.bundle_tx_off[b]; x < B.bundle_tx_off[b + 1]; x++) {
         B.tx_bundle[x] = b;
-        if (B.tx_kind[x] == ORFX_TX_QUERY) need |= B.tx_strand[x] == '+' ? 1u : 2u;
+        const int kind = B.tx_kind[x];
+        if (kind == ORFX_TX_QUERY) { need |= B.tx_strand[x] == '+' ? 1u : 2u; has_q = true; }
+        if (kind == ORFX_TX_TEMPLATE) has_t = true;
+        if (kind != ORFX_TX_SKIP) max_segs = max(max_segs, B.tx_seg_off[x + 1] - B.tx_seg_off[x]);
+    }
+    if (max_segs > HEAVY_TX_SEGS && has_q && has_t) {
+        need |= BUNDLE_HEAVY;
+        heavy_list[atomicAdd(heavy_count, 1u)] = b;
     }
     B.bundle_need[b] = (uint8_t)need;
 }
@@ -134,11 +151,13 @@ __global__ void __launch_bounds__(256) fill_tile_list_kernel(DevBatch B) {   // 
 }
 // Everything that needs no host-side size: lengths, prefixes, the three per-transcript scans, the
 // query list (capacity n_tx).  The totals land in tx_q_off[n_tx], tx_mask_off[n_tx], tx_tile_off[n_tx].
-int launch_prep(const DevBatch& B, int64_t* cnt_q, int64_t* cnt_words, int64_t* cnt_tiles, int64_t* scan_tmp, cudaStream_t s) {
+int launch_prep(const DevBatch& B, int64_t* cnt_q, int64_t* cnt_words, int64_t* cnt_tiles, int64_t* scan_tmp, int32_t* heavy_list, unsigned* heavy_count,
+                cudaStream_t s) {
     int n = 0;
     if (B.n_tx == 0) return 0;
     tx_prep_kernel<<<(unsigned)(((int64_t)B.n_tx * 32 + 255) / 256), 256, 0, s>>>(B, cnt_q, cnt_words, cnt_tiles); n++;
-    bundle_prep_kernel<<<(B.n_bundles + 127) / 128, 128, 0, s>>>(B); n++;
+    cudaMemsetAsync(heavy_count, 0, sizeof(unsigned), s);
+    bundle_prep_kernel<<<(B.n_bundles + 127) / 128, 128, 0, s>>>(B, heavy_list, heavy_count); n++;
     n += launch_exclusive_scan(cnt_q, B.tx_q_off, scan_tmp, B.n_tx, s);
     n += launch_exclusive_scan(cnt_words, B.tx_mask_off, scan_tmp, B.n_tx, s);
     n += launch_exclusive_scan(cnt_tiles, B.tx_tile_off, scan_tmp, B.n_tx, s);
@@ -162,28 +181,31 @@ __device__ __forceinline__ void put_row(const DevRows& R, int64_t at, int qx, in
 // Candidate rows of one (query, template) pair in the reference's order: CHAIN::intersection(...,
 // segments = true) (Transcriptome.h:321-361) merges consecutive pieces into one genomic span while they
 // share intron boundaries; one row per span, or one "no-overlap" row.  FILL = false only counts.
-// Same visiting order and state as the reference's double loop, but template segments that can no
-// longer / not yet overlap are skipped with a persistent pointer, so a pair costs O(exons + segments).
+// `segs` is B.segs or a shared-memory copy of the bundle's segments biased to accept the same absolute
+// indices.  Same visiting order and state as the reference's double loop at O(exons + segments) per pair.
 template <bool FILL>
-__device__ int pair_rows(const DevBatch& B, const DevRows& R, int qx, int t, int64_t out) {
+__device__ int pair_rows(const DevBatch& B, const orfx_seg* segs, const DevRows& R, int qx, int t, int64_t out) {
     const int q0 = B.tx_seg_off[qx], q1 = B.tx_seg_off[qx + 1];
     const int t0 = B.tx_seg_off[t], t1 = B.tx_seg_off[t + 1];
-    int start = t0, low = t0, nseg = 0, cur_s = 0, cur_e = 0, n = 0;
-    bool continue_prev = false;
-    for (int i = q0; i < q1; i++) {
-        const orfx_seg s1 = B.segs[i];
-        bool found_yet = false;
-        // segments wholly left of this exon: the reference walks over them (resetting continue_prev)
-        if (low < start) low = start;
-        while (low < t1 && B.segs[low].end < s1.start) low++;
-        if (low > start) continue_prev = false;
-        for (int j = low; j < t1; j++) {
-            const orfx_seg c2 = B.segs[j];
-            const int is = max(s1.start, c2.start), ie = min(s1.end, c2.end);
-            if (is <= ie) {
+    int nseg = 0, cur_s = 0, cur_e = 0, n = 0;
+    if (q0 < q1 && t0 < t1) {
+        // The reference's double loop, flattened into one merge step per exon or template segment (its
+        // `start` pointer is j here); the next element of either chain is already loaded when it is needed.
+        int i = q0, j = t0;
+        orfx_seg s1 = segs[i], c2 = segs[j];
+        orfx_seg s1n = segs[min(i + 1, q1 - 1)], c2n = segs[min(j + 1, t1 - 1)];
+        bool continue_prev = false, found_yet = false;
+        while (true) {
+            bool next_seg;
+            if (c2.end < s1.start) {            // segment wholly left of the exon: walked over (low > start)
+                continue_prev = false;
+                next_seg = true;
+            } else if (c2.start > s1.end) {     // nothing (more) under this exon
+                if (!found_yet) continue_prev = false;
+                next_seg = false;
+            } else {
+                const int is = max(s1.start, c2.start), ie = min(s1.end, c2.end);
                 found_yet = true;
-                start = j;
-                if (ie == c2.end) start++;
                 const bool ends_match = ie == s1.end && s1.end == c2.end;
                 const bool starts_match = is == s1.start && s1.start == c2.start;
                 if (!continue_prev || !starts_match) {
@@ -194,14 +216,17 @@ __device__ int pair_rows(const DevBatch& B, const DevRows& R, int qx, int t, int
                     cur_s = min(cur_s, is); cur_e = max(cur_e, ie);
                 }
                 continue_prev = ends_match;
+                next_seg = ie == c2.end;        // else the segment reaches past the exon: next exon, same segment
+            }
+            if (next_seg) {
+                if (++j >= t1) break;
+                c2 = c2n; c2n = segs[min(j + 1, t1 - 1)];
             } else {
-                // every later segment lies right of this exon as well: the reference visits them all
-                // (or stops at the first one once it has found an overlap) with this same effect
-                if (!found_yet) continue_prev = false;
-                break;
+                if (++i >= q1) break;
+                s1 = s1n; s1n = segs[min(i + 1, q1 - 1)];
+                found_yet = false;
             }
         }
-        if (!found_yet && continue_prev) continue_prev = false;
     }
     if (nseg > 0) { if (FILL) put_row(R, out + n, qx, t, cur_s, cur_e, ORFX_ST_OK); n++; }
     else { if (FILL) put_row(R, out + n, qx, t, -1, -1, ORFX_ST_NO_OVERLAP); n++; }
@@ -227,12 +252,12 @@ __global__ void __launch_bounds__(256) count_rows_kernel(DevBatch B, int64_t* cn
     if (qi < nq) {
         const int qx = B.q_list[qi];
         const int b = B.tx_bundle[qx];
-        const int x0 = B.bundle_tx_off[b], x1 = B.bundle_tx_off[b + 1];
+        const int x0 = B.bundle_tx_off[b], x1 = (B.bundle_need[b] & BUNDLE_HEAVY) ? x0 : B.bundle_tx_off[b + 1];   // heavy: counted by heavy_count_kernel
         const int q0 = B.tx_seg_off[qx], q1 = B.tx_seg_off[qx + 1];
         const int qstart = B.segs[q0].start, qend = B.segs[q1 - 1].end;
         DevRows dummy{};
         for (int t = x0 + sub; t < x1; t += ROWS_GROUP)
-            if (pair_live(B, t, x1, qstart, qend)) total += pair_rows<false>(B, dummy, qx, t, 0);
+            if (pair_live(B, t, x1, qstart, qend)) total += pair_rows<false>(B, B.segs, dummy, qx, t, 0);
     }
 #pragma unroll
     for (int d = ROWS_GROUP / 2; d > 0; d >>= 1) total += __shfl_xor_sync(0xffffffffu, total, d);
@@ -241,10 +266,11 @@ __global__ void __launch_bounds__(256) count_rows_kernel(DevBatch B, int64_t* cn
 __global__ void __launch_bounds__(256) fill_rows_kernel(DevBatch B, DevRows R, int n_queries) {
     const int64_t gt = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     const int qi = (int)(gt / ROWS_GROUP), sub = (int)(gt % ROWS_GROUP);
-    const bool valid = qi < n_queries;
+    bool valid = qi < n_queries;
     const int qx = valid ? B.q_list[qi] : 0;
     int x0 = 0, x1 = 0, qstart = 0, qend = 0;
     int64_t out = 0;
+    if (valid && (B.bundle_need[B.tx_bundle[qx]] & BUNDLE_HEAVY)) valid = false;   // filled by heavy_fill_rescue_kernel
     if (valid) {
         const int b = B.tx_bundle[qx];
         x0 = B.bundle_tx_off[b]; x1 = B.bundle_tx_off[b + 1];
@@ -258,18 +284,20 @@ __global__ void __launch_bounds__(256) fill_rows_kernel(DevBatch B, DevRows R, i
     for (int it = 0; it < rounds; it++) {
         const int t = x0 + it * ROWS_GROUP + sub;
         const bool live = valid && pair_live(B, t, x1, qstart, qend);
-        const int n = live ? pair_rows<false>(B, R, qx, t, 0) : 0;
+        const int n = live ? pair_rows<false>(B, B.segs, R, qx, t, 0) : 0;
         int incl = n;
 #pragma unroll
         for (int d = 1; d < ROWS_GROUP; d <<= 1) { const int v = __shfl_up_sync(0xffffffffu, incl, d, ROWS_GROUP); if (sub >= d) incl += v; }
-        if (live) pair_rows<true>(B, R, qx, t, out + incl - n);
+        if (live) pair_rows<true>(B, B.segs, R, qx, t, out + incl - n);
         out += __shfl_sync(0xffffffffu, incl, ROWS_GROUP - 1, ROWS_GROUP);
     }
 }
-int launch_count_rows(const DevBatch& B, int64_t* cnt, int64_t* scan_tmp, cudaStream_t s) {
+int launch_heavy_count(const DevBatch& B, int64_t* cnt, const int32_t* heavy_list, const unsigned* heavy_count, int n_sm, cudaStream_t s);
+int launch_count_rows(const DevBatch& B, int64_t* cnt, int64_t* scan_tmp, const int32_t* heavy_list, const unsigned* heavy_count, int n_sm, cudaStream_t s) {
     if (B.n_tx == 0) { cudaMemsetAsync(B.q_row_off, 0, sizeof(int64_t), s); return 0; }
     count_rows_kernel<<<(unsigned)(((int64_t)B.n_tx * ROWS_GROUP + 255) / 256), 256, 0, s>>>(B, cnt);
-    return 1 + launch_exclusive_scan(cnt, B.q_row_off, scan_tmp, B.n_tx, s);
+    int n = 1 + launch_heavy_count(B, cnt, heavy_list, heavy_count, n_sm, s);
+    return n + launch_exclusive_scan(cnt, B.q_row_off, scan_tmp, B.n_tx, s);
 }
 int launch_fill_rows(const DevBatch& B, const DevRows& R, int n_queries, cudaStream_t s) {
     if (n_queries == 0) return 0;
@@ -514,54 +542,143 @@ __device__ void process_row(const DevBatch& B, const DevRows& R, const orfx_para
     R.n_dup[row] = 0;
 }
 
-// Rows whose two chains together hold more than HEAVY_SEGS segments (titin-class loci) would make
-// their thread the tail of the whole launch: chain walks are dependent-load chains.  The light kernel
-// defers them to a list; the heavy kernel gives each a warp, stages both chains in shared memory with
-// coalesced loads and lets one lane walk them at shared-memory latency.
-constexpr int HEAVY_SEGS = 64;
-constexpr int HEAVY_CAP = 384;      // segments per chain that fit the per-warp stage
-constexpr int HEAVY_WARPS = 4;
-
-__global__ void __launch_bounds__(128) rescue_score_kernel(DevBatch B, DevRows R, orfx_params P, int32_t* heavy_list, unsigned* heavy_count) {
+__global__ void __launch_bounds__(128) rescue_score_kernel(DevBatch B, DevRows R, orfx_params P) {
     const int64_t row = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (row >= R.n_rows) return;
-    const TxView q = tx_view(B, R.q_tx[row]), t = tx_view(B, R.t_tx[row]);
-    if (q.n + t.n > HEAVY_SEGS && R.status[row] == ORFX_ST_OK) {
-        heavy_list[atomicAdd(heavy_count, 1u)] = (int32_t)row;
-        return;
-    }
+    const int qx = R.q_tx[row];
+    if (B.bundle_need[B.tx_bundle[qx]] & BUNDLE_HEAVY) return;   // done by heavy_fill_rescue_kernel
+    const TxView q = tx_view(B, qx), t = tx_view(B, R.t_tx[row]);
     process_row(B, R, P, row, q, t);
 }
 
-__global__ void __launch_bounds__(HEAVY_WARPS * 32) rescue_score_heavy_kernel(DevBatch B, DevRows R, orfx_params P, const int32_t* heavy_list,
-                                                                             const unsigned* heavy_count) {
-    __shared__ orfx_seg s_seg[HEAVY_WARPS][2][HEAVY_CAP];
-    __shared__ int32_t s_cum[HEAVY_WARPS][2][HEAVY_CAP];
-    const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
+// ------------------------------------------------------------------------------------------------
+// heavy bundles: one CTA per bundle, the bundle's chains staged in shared memory
+// ------------------------------------------------------------------------------------------------
+constexpr int HB_THREADS = 256;
+constexpr int HB_MAX_SEGS = 8192;     // segments of one bundle that fit the stage (8 B + 4 B each); two CTAs per SM
+constexpr int HB_MAX_PAIRS = 8192;    // (query, transcript slot) pairs whose row counts fit the stage
+constexpr size_t HB_SMEM = (size_t)HB_MAX_SEGS * (sizeof(orfx_seg) + sizeof(int32_t)) + (size_t)HB_MAX_PAIRS * sizeof(uint16_t);
+
+namespace {
+struct HeavyBundle {
+    int b, x0, x1, ntx, qbase, nq, seg_lo, ns;
+    bool staged;
+    const orfx_seg* segs;    // accepts absolute segment indices
+    const int32_t* cum;
+};
+// loads bundle h of the heavy list; stages its segments (and prefixes when `with_cum`) when they fit
+__device__ HeavyBundle hb_load(const DevBatch& B, int b, orfx_seg* s_seg, int32_t* s_cum, bool with_cum) {
+    HeavyBundle H;
+    H.b = b;
+    H.x0 = B.bundle_tx_off[b]; H.x1 = B.bundle_tx_off[b + 1]; H.ntx = H.x1 - H.x0;
+    H.qbase = (int)B.tx_q_off[H.x0]; H.nq = (int)B.tx_q_off[H.x1] - H.qbase;
+    H.seg_lo = B.tx_seg_off[H.x0]; H.ns = B.tx_seg_off[H.x1] - H.seg_lo;
+    H.staged = H.ns <= HB_MAX_SEGS;
+    if (H.staged) {
+        for (int i = threadIdx.x; i < H.ns; i += blockDim.x) {
+            s_seg[i] = B.segs[H.seg_lo + i];
+            if (with_cum) s_cum[i] = B.seg_cum[H.seg_lo + i];
+        }
+        H.segs = s_seg - H.seg_lo; H.cum = s_cum - H.seg_lo;
+    } else {
+        H.segs = B.segs; H.cum = B.seg_cum;
+    }
+    __syncthreads();
+    return H;
+}
+__device__ __forceinline__ TxView hb_view(const DevBatch& B, const HeavyBundle& H, int tx) {
+    TxView v;
+    const int s0 = B.tx_seg_off[tx];
+    v.segs = H.segs + s0; v.cum = H.cum + s0;
+    v.n = B.tx_seg_off[tx + 1] - s0; v.L = B.tx_len[tx]; v.plus = B.tx_strand[tx] == '+';
+    return v;
+}
+}  // namespace
+
+// rows of every query of the heavy bundles, one thread per (query, transcript slot) pair
+__global__ void __launch_bounds__(HB_THREADS) heavy_count_kernel(DevBatch B, int64_t* cnt, const int32_t* heavy_list, const unsigned* heavy_count) {
+    extern __shared__ __align__(16) unsigned char hb_smem[];
+    orfx_seg* s_seg = reinterpret_cast<orfx_seg*>(hb_smem);
     const unsigned n = *heavy_count;
-    for (unsigned h = blockIdx.x * HEAVY_WARPS + wib; h < n; h += gridDim.x * HEAVY_WARPS) {
-        const int64_t row = heavy_list[h];
-        TxView q = tx_view(B, R.q_tx[row]), t = tx_view(B, R.t_tx[row]);
-        if (q.n <= HEAVY_CAP) {
-            for (int i = lane; i < q.n; i += 32) { s_seg[wib][0][i] = q.segs[i]; s_cum[wib][0][i] = q.cum[i]; }
-            q.segs = s_seg[wib][0]; q.cum = s_cum[wib][0];
+    DevRows dummy{};
+    for (unsigned h = blockIdx.x; h < n; h += gridDim.x) {
+        const HeavyBundle H = hb_load(B, heavy_list[h], s_seg, nullptr, false);
+        const int64_t npairs = (int64_t)H.nq * H.ntx;
+        for (int64_t p = threadIdx.x; p < npairs; p += blockDim.x) {
+            const int ql = (int)(p / H.ntx), t = H.x0 + (int)(p % H.ntx);
+            const int qx = B.q_list[H.qbase + ql];
+            const int qstart = H.segs[B.tx_seg_off[qx]].start, qend = H.segs[B.tx_seg_off[qx + 1] - 1].end;
+            if (!pair_live(B, t, H.x1, qstart, qend)) continue;
+            const int r = pair_rows<false>(B, H.segs, dummy, qx, t, 0);
+            atomicAdd(reinterpret_cast<unsigned long long*>(cnt + H.qbase + ql), (unsigned long long)r);   // zeroed by count_rows_kernel
         }
-        if (t.n <= HEAVY_CAP) {
-            for (int i = lane; i < t.n; i += 32) { s_seg[wib][1][i] = t.segs[i]; s_cum[wib][1][i] = t.cum[i]; }
-            t.segs = s_seg[wib][1]; t.cum = s_cum[wib][1];
-        }
-        __syncwarp();
-        if (lane == 0) process_row(B, R, P, row, q, t);
-        __syncwarp();
+        __syncthreads();
     }
 }
 
-int launch_rescue_score(const DevBatch& B, const DevRows& R, const orfx_params& P, int32_t* heavy_list, unsigned* heavy_count, int n_sm, cudaStream_t s) {
+// candidate rows of the heavy bundles (in the reference's order), then rescue + score of those rows,
+// all against the staged chains
+__global__ void __launch_bounds__(HB_THREADS) heavy_fill_rescue_kernel(DevBatch B, DevRows R, orfx_params P, const int32_t* heavy_list,
+                                                                      const unsigned* heavy_count) {
+    extern __shared__ __align__(16) unsigned char hb_smem[];
+    orfx_seg* s_seg = reinterpret_cast<orfx_seg*>(hb_smem);
+    int32_t* s_cum = reinterpret_cast<int32_t*>(hb_smem + (size_t)HB_MAX_SEGS * sizeof(orfx_seg));
+    uint16_t* s_n = reinterpret_cast<uint16_t*>(hb_smem + (size_t)HB_MAX_SEGS * (sizeof(orfx_seg) + sizeof(int32_t)));
+    const unsigned n = *heavy_count;
+    for (unsigned h = blockIdx.x; h < n; h += gridDim.x) {
+        const HeavyBundle H = hb_load(B, heavy_list[h], s_seg, s_cum, true);
+        const int64_t npairs = (int64_t)H.nq * H.ntx;
+        if (H.staged && npairs <= HB_MAX_PAIRS) {
+            // rows of every pair, then each pair fills at (rows of the query's earlier pairs)
+            for (int p = threadIdx.x; p < (int)npairs; p += blockDim.x) {
+                const int ql = p / H.ntx, t = H.x0 + p % H.ntx;
+                const int qx = B.q_list[H.qbase + ql];
+                const int qstart = H.segs[B.tx_seg_off[qx]].start, qend = H.segs[B.tx_seg_off[qx + 1] - 1].end;
+                s_n[p] = pair_live(B, t, H.x1, qstart, qend) ? (uint16_t)pair_rows<false>(B, H.segs, R, qx, t, 0) : (uint16_t)0;
+            }
+            __syncthreads();
+            for (int p = threadIdx.x; p < (int)npairs; p += blockDim.x) {
+                if (s_n[p] == 0) continue;   // a live pair has at least its "no-overlap" row
+                const int ql = p / H.ntx, tl = p % H.ntx;
+                int64_t out = B.q_row_off[H.qbase + ql];
+                for (int k = p - tl; k < p; k++) out += s_n[k];
+                pair_rows<true>(B, H.segs, R, B.q_list[H.qbase + ql], H.x0 + tl, out);
+            }
+        } else {
+            for (int ql = threadIdx.x; ql < H.nq; ql += blockDim.x) {
+                const int qx = B.q_list[H.qbase + ql];
+                const int qstart = H.segs[B.tx_seg_off[qx]].start, qend = H.segs[B.tx_seg_off[qx + 1] - 1].end;
+                int64_t out = B.q_row_off[H.qbase + ql];
+                for (int t = H.x0; t < H.x1; t++)
+                    if (pair_live(B, t, H.x1, qstart, qend)) out += pair_rows<true>(B, H.segs, R, qx, t, out);
+            }
+        }
+        __syncthreads();   // the rows written above are read below by other threads of this CTA
+        const int64_t r0 = B.q_row_off[H.qbase], r1 = B.q_row_off[H.qbase + H.nq];
+        for (int64_t row = r0 + threadIdx.x; row < r1; row += blockDim.x)
+            process_row(B, R, P, row, hb_view(B, H, R.q_tx[row]), hb_view(B, H, R.t_tx[row]));
+        __syncthreads();
+    }
+}
+
+int launch_heavy_count(const DevBatch& B, int64_t* cnt, const int32_t* heavy_list, const unsigned* heavy_count, int n_sm, cudaStream_t s) {
+    if (B.n_bundles == 0) return 0;
+    cudaFuncSetAttribute(heavy_count_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)HB_SMEM);   // per device
+    heavy_count_kernel<<<min(2 * n_sm, B.n_bundles), HB_THREADS, HB_SMEM, s>>>(B, cnt, heavy_list, heavy_count);
+    return 1;
+}
+int launch_heavy_fill_rescue(const DevBatch& B, const DevRows& R, const orfx_params& P, const int32_t* heavy_list, const unsigned* heavy_count, int n_sm,
+                             cudaStream_t s) {
+    if (B.n_bundles == 0 || R.n_rows == 0) return 0;
+    cudaFuncSetAttribute(heavy_fill_rescue_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)HB_SMEM);
+    heavy_fill_rescue_kernel<<<min(2 * n_sm, B.n_bundles), HB_THREADS, HB_SMEM, s>>>(B, R, P, heavy_list, heavy_count);
+    return 1;
+}
+
+int launch_rescue_score(const DevBatch& B, const DevRows& R, const orfx_params& P, cudaStream_t s) {
     if (R.n_rows == 0) return 0;
-    cudaMemsetAsync(heavy_count, 0, sizeof(unsigned), s);
-    rescue_score_kernel<<<(unsigned)((R.n_rows + 127) / 128), 128, 0, s>>>(B, R, P, heavy_list, heavy_count);
-    rescue_score_heavy_kernel<<<n_sm * 4, HEAVY_WARPS * 32, 0, s>>>(B, R, P, heavy_list, heavy_count);
-    return 2;
+    rescue_score_kernel<<<(unsigned)((R.n_rows + 127) / 128), 128, 0, s>>>(B, R, P);
+    return 1;
 }
 
 }  // namespace orfx
