@@ -274,10 +274,118 @@ def ours(args):
         dist.all_reduce(cnt)
     dev_ms, wall_ms, e2e_ms = [float(x) for x in tt.tolist()]
     nq_all, launches_all, found_all, nt_all = [int(x) for x in cnt.tolist()]
-    return dict(rank=rank, world=world, cfg=cfg, nq=nq, nq_all=nq_all, nt_sum=nt_sum, dev_ms=dev_ms, wall_ms=wall_ms, e2e_ms=e2e_ms,
+    align = None
+    if rank == 0 and args.align_pairs > 0:
+        t = time.time()
+        align = alignment_leg(cx, args.align_pairs)
+        log("alignment leg: %.1f s, %.1f GCUPS" % (time.time() - t, align["gcups"]))
+    return dict(align=align, rank=rank, world=world, cfg=cfg, nq=nq, nq_all=nq_all, nt_sum=nt_sum, dev_ms=dev_ms, wall_ms=wall_ms, e2e_ms=e2e_ms,
                 e2e_dev=e2e_dev, stage_ms=stage_ms, launches=launches_all, found=found_all, clocks=clocks, h2d=batch.h2d_bytes,
                 d2h=d2h_bytes, windows=int(batch.arrays["seq"].nbytes), n_templates=w.count("templates"),
                 n_bundles=w.count("active_bundles"))
+
+
+# ---- protein alignment leg (BASELINE.json configs[4]; metric's "alignment GCUPS vs host-CPU ref") ------------
+AA_FREQ = [8.25, 5.53, 4.06, 5.45, 1.37, 3.93, 6.75, 7.07, 2.27, 5.96, 9.66, 5.84, 2.42, 3.86, 4.70, 6.56, 5.34, 1.08, 2.92, 6.87]
+
+
+def c5_pairs(n_pairs, seed):
+    """Seeded C5-law pairs: 99 % of lengths log-normal (median 400 aa, sigma_ln 0.9) clipped to
+    [50, 35000], 1 % log-uniform in [5000, 35000], at least n/10000 titin-class pairs (30-35 k aa); residues
+    i.i.d. with proteome background frequencies; the partner is a mutated copy (5-40 % substitutions, up to two
+    deletions of 1-11 residues).  Returns aa (0..19), off, pair_q, pair_t."""
+    import numpy as np
+    rng = np.random.default_rng(seed)
+    L = np.clip(np.exp(rng.normal(np.log(400.0), 0.9, n_pairs)), 50, 35000).astype(np.int64)
+    tail = rng.random(n_pairs) < 0.01
+    L[tail] = np.exp(rng.uniform(np.log(5000.0), np.log(35000.0), int(tail.sum()))).astype(np.int64)
+    n_titin = max(1, n_pairs // 10000)
+    L[rng.choice(n_pairs, n_titin, replace=False)] = rng.integers(30000, 35001, n_titin)
+    freq = np.array(AA_FREQ) / sum(AA_FREQ)
+    cdf = np.cumsum(freq)
+    total = int(L.sum())
+    q = np.minimum(np.searchsorted(cdf, rng.random(total, dtype=np.float32)), 19).astype(np.uint8)
+    qoff = np.concatenate([[0], np.cumsum(L)])
+    rate = np.repeat(rng.uniform(0.05, 0.4, n_pairs).astype(np.float32), L)
+    sub = rng.random(total, dtype=np.float32) < rate
+    t = q.copy()
+    t[sub] = np.minimum(np.searchsorted(cdf, rng.random(int(sub.sum()), dtype=np.float32)), 19).astype(np.uint8)
+    idx = np.arange(total, dtype=np.int64) - np.repeat(qoff[:-1], L)
+    keep = np.ones(total, dtype=bool)
+    for _ in range(2):
+        p0 = np.repeat((rng.random(n_pairs) * L).astype(np.int64), L)
+        k = np.repeat(rng.integers(0, 12, n_pairs), L)
+        keep &= ~((idx >= p0) & (idx < p0 + k) & (idx > 0))
+    tl = np.add.reduceat(keep.astype(np.int64), qoff[:-1])
+    t = t[keep]
+    aa = np.concatenate([q, t])
+    lens = np.empty(2 * n_pairs, dtype=np.int64)
+    lens[:n_pairs] = L
+    lens[n_pairs:] = tl
+    off = np.concatenate([[0], np.cumsum(lens)]).astype(np.int64)
+    pq = np.arange(n_pairs, dtype=np.int32)
+    return aa, off, pq, pq + np.int32(n_pairs)
+
+
+def alignment_leg(cx, n_pairs, cpu_seconds=12.0):
+    """GCUPS of orfx_align_batch on a C5-law sample, against the measured integer-ALU issue rate; the scalar
+    restatement of the same recurrence (oracle, OpenMP over pairs) on a subsample as the CPU baseline."""
+    import ctypes as C
+    import numpy as np
+    aa, off, pq, pt = c5_pairs(n_pairs, 20261104)
+    ql = (off[pq + 1] - off[pq]).astype(np.float64)
+    tl = (off[pt + 1] - off[pt]).astype(np.float64)
+    cx.align(aa, off, pq[:64], pt[:64])   # warm-up
+    best = None
+    for _ in range(3):
+        out, cells, ms = cx.align(aa, off, pq, pt)
+        if best is None or ms < best[2]:
+            best = (out, cells, ms)
+    out, cells, ms = best
+    peak = cx.int_alu_peak()
+    gcups = cells / (ms * 1e-3) / 1e9
+    # per power-of-two bucket of max(qlen, tlen)
+    buckets = {}
+    mx = np.maximum(ql, tl)
+    for lo in (32, 64, 128, 256, 512, 1024, 2048, 4096, 8192, 16384, 32768):
+        sel = np.nonzero((mx >= lo) & (mx < 2 * lo))[0]
+        if len(sel) == 0:
+            continue
+        _, c, m = cx.align(aa, off, pq[sel], pt[sel])
+        buckets["%d-%d" % (lo, 2 * lo - 1)] = {"pairs": int(len(sel)), "gcups": c / (m * 1e-3) / 1e9 if m > 0 else None}
+    line = {"workload": "C5-law protein pairs (BASELINE.json configs[4]), %d pairs, lengths 50-35000 aa" % n_pairs,
+            "pairs": int(n_pairs), "cells": cells, "kernel_ms": ms, "gcups": gcups,
+            "int_alu_peak_ops_per_s": peak, "ops_per_cell": 10,
+            "roofline": {"bound": "int-alu", "achieved": 10.0 * gcups, "peak": peak["iadd3"] / 1e9, "unit": "Gop/s",
+                         "frac": 10.0 * gcups * 1e9 / peak["iadd3"] if peak["iadd3"] else None,
+                         "peak_source": "measured on this GPU (orfx_int_alu_peak: IADD3 issue rate, all SMs)"},
+            "gcups_by_length": buckets,
+            "checksum": int(np.bitwise_xor.reduce(out["score"].astype(np.int64) * 31 + out["max"]))}
+    # CPU baseline: same recurrence, scalar int32, all cores, bounded subsample
+    try:
+        lib = C.CDLL(os.path.join(ROOT, "oracle", "liborfx_oracle.so"))
+        lib.orfx_oracle_align_batch.restype = C.c_int
+        mat = np.ascontiguousarray(np.load(os.path.join(ROOT, "tests", "golden", "mat50.npy")), dtype=np.int8)
+        order = np.arange(n_pairs)
+        budget_cells = cpu_seconds * 0.25e9 * (os.cpu_count() or 1)   # ~0.25 GCUPS per core, scalar
+        csum = np.cumsum(ql * tl)
+        k = max(8, int(np.searchsorted(csum, budget_cells)))
+        k = min(k, n_pairs)
+        sel = order[:k]
+        res = [np.zeros(k, dtype=np.int32) for _ in range(4)]
+        sq, st = np.ascontiguousarray(pq[sel]), np.ascontiguousarray(pt[sel])
+        t0 = time.perf_counter()
+        used = lib.orfx_oracle_align_batch(C.c_void_p(aa.ctypes.data), C.c_void_p(off.ctypes.data), C.c_void_p(sq.ctypes.data),
+                                           C.c_void_p(st.ctypes.data), C.c_int64(k), C.c_void_p(mat.ctypes.data), 24, 12, 2, 0,
+                                           *[C.c_void_p(r.ctypes.data) for r in res])
+        dt = time.perf_counter() - t0
+        same = all(np.array_equal(res[i], out[n][:k]) for i, n in enumerate(("max", "score", "mqe", "mte")))
+        line["cpu_baseline"] = {"value": float(csum[k - 1]) / dt / 1e9, "unit": "GCUPS", "cores": int(used), "kind": "port",
+                                "sample": "first %d pairs of the same set (%.3g cells); scalar int32 restatement, OpenMP over pairs"
+                                          % (k, float(csum[k - 1])), "identical_to_gpu": bool(same)}
+    except Exception as e:
+        line["cpu_baseline"] = {"value": None, "unit": "GCUPS", "sample": "unavailable: %s" % e}
+    return line
 
 
 def measured_peak():
@@ -298,6 +406,7 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--loci", type=int, default=0, help="override the number of loci (development only; 0 = configs[1])")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--align-pairs", type=int, default=50000, help="protein pairs of the alignment leg (0 = skip; configs[4] = 1000000)")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
     if args.impl == "reference":
@@ -339,6 +448,8 @@ def main():
                      "share_of_step": scan_ms / ms_per_step if ms_per_step else None, "dominant_stage": dominant},
         "stages_ms": {k: v / K for k, v in m["stage_ms"].items()},
     }
+    if m["align"] is not None:
+        line["alignment"] = m["align"]
     if m["world"] == 1 and not args.no_cpu_baseline:
         try:
             line["cpu_baseline"] = cpu_baseline_leg()

@@ -221,6 +221,11 @@ int  orfx_align_batch(orfx_ctx* ctx, const uint8_t* aa, const int64_t* off, int6
                       const int32_t* pair_q, const int32_t* pair_t, int64_t n_pairs,
                       int gapo, int gape, orfx_aln_out* out, double* cells, float* ms);
 
+/* Integer-ALU issue-rate microbenchmark on the context's device: the denominator of the alignment roofline
+ * (SURVEY.md §8d).  ops3[0] = IADD3 operations/s; ops3[1] = IADD + VIMNMX3 pairs (2 operations each)/s;
+ * ops3[2] = VIADDMNMX (add + max, 2 operations each)/s; all SMs, 8 independent chains per thread. */
+int  orfx_int_alu_peak(orfx_ctx* ctx, double* ops3);
+
 #ifdef __cplusplus
 }
 #endif

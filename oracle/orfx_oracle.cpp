@@ -17,6 +17,9 @@
 #include "../include/orfx_codon_table.h"
 
 #include <algorithm>
+#ifdef _OPENMP
+#include <omp.h>
+#endif
 #include <cstring>
 #include <map>
 #include <set>
@@ -788,6 +791,25 @@ int orfx_oracle_align(const uint8_t* query, int qlen, const uint8_t* target, int
     }
     *out_max = (int32_t)ez_max; *out_score = sc; *out_mqe = mqe; *out_mte = mte;
     return 0;
+}
+
+// The same recurrence over a batch of pairs, OpenMP over pairs (CPU baseline of the alignment benchmark;
+// sequences concatenated as in orfx_align_batch).  threads <= 0: all cores.  Returns the threads used.
+int orfx_oracle_align_batch(const uint8_t* aa, const int64_t* off, const int32_t* pair_q, const int32_t* pair_t, int64_t n_pairs,
+                            const int8_t* mat, int m, int gapo, int gape, int threads, int32_t* out_max, int32_t* out_score,
+                            int32_t* out_mqe, int32_t* out_mte) {
+    int used = 1;
+#ifdef _OPENMP
+    if (threads <= 0) threads = omp_get_max_threads();
+    used = threads;
+#pragma omp parallel for schedule(dynamic, 1) num_threads(threads)
+#endif
+    for (int64_t p = 0; p < n_pairs; p++) {
+        const int64_t q0 = off[pair_q[p]], q1 = off[pair_q[p] + 1], t0 = off[pair_t[p]], t1 = off[pair_t[p] + 1];
+        orfx_oracle_align(aa + q0, (int)(q1 - q0), aa + t0, (int)(t1 - t0), mat, m, gapo, gape, out_max + p, out_score + p, out_mqe + p,
+                          out_mte + p);
+    }
+    return used;
 }
 
 }  // extern "C"

@@ -285,6 +285,9 @@ def load_device_library(path=None):
     lib.orfx_align_batch.restype = C.c_int
     lib.orfx_align_batch.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_int64,
                                      C.c_int, C.c_int, C.POINTER(_AlnOut), C.POINTER(C.c_double), C.POINTER(C.c_float)]
+    if hasattr(lib, "orfx_int_alu_peak"):
+        lib.orfx_int_alu_peak.restype = C.c_int
+        lib.orfx_int_alu_peak.argtypes = [C.c_void_p, C.POINTER(C.c_double)]
     if path is None:
         _DEVICE_LIB = lib
     return lib
@@ -415,6 +418,12 @@ class Context:
         self._check(self.lib.orfx_align_batch(self.handle, aa.ctypes.data, off.ctypes.data, len(off) - 1, pq.ctypes.data,
                                               pt.ctypes.data, n, gapo, gape, C.byref(o), C.byref(cells), C.byref(ms)))
         return {k: v[:n] for k, v in out.items()}, cells.value, ms.value
+
+    def int_alu_peak(self):
+        """orfx_int_alu_peak: measured integer issue rates of this GPU, operations/s."""
+        ops = (C.c_double * 3)()
+        self._check(self.lib.orfx_int_alu_peak(self.handle, ops))
+        return {"iadd3": ops[0], "iadd_vimnmx3": ops[1], "viaddmnmx": ops[2]}
 
     def close(self):
         if self.handle:

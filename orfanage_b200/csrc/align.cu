@@ -55,30 +55,210 @@ constexpr int NEG_INF = -0x40000000;
 constexpr int PAD_CODE = 24;        // virtual query column right of the query's end
 constexpr int PAD_SCORE = -4096;    // never wins: padded cells are dominated by H(i,qlen-1)
 constexpr int MAT_STRIDE = 32;
-constexpr int ALN_WARPS = 4;
+constexpr int ALN_WARPS = 16;       // one CTA per SM; its warps work alone on short pairs and as a pipeline on long ones
 
+struct AlnAcc { int gmax, mqe, mte, score; };
+
+// What a stripe reads on its left and writes on its right: H(i, c_base-1) / F(i, c_base) per target row.
+// PIPE: the stripes of one pair run concurrently on the warps of a CTA; a stripe may read row chunk
+// [s, s+32) of its left edge once the warp of the previous stripe has posted that many rows.
+struct StripeIO {
+    const int32_t* h_in; const int32_t* f_in;      // nullptr for the first stripe
+    int32_t* h_out; int32_t* f_out;                // nullptr for the last stripe
+    volatile unsigned long long* wait_flag; unsigned long long wait_base;
+    volatile unsigned long long* post_flag; unsigned long long post_base;
+};
+
+// One stripe of 32*CPL query columns over all target rows.  Lanes own CPL consecutive columns; lane l works on
+// target row (step - l), so only the lane's right edge (H, F) and the target residue move to the next lane.
+template <int CPL, bool PIPE>
+__device__ __forceinline__ void dp_stripe(const int* __restrict__ s_mat, const uint8_t* __restrict__ q, const uint8_t* __restrict__ t, int qlen, int tlen,
+                                          int c_base, bool last_stripe, int gapoe, int gape, const StripeIO& io, AlnAcc& acc, int lane) {
+    const int c0 = c_base + lane * CPL;
+    const bool first_stripe = io.h_in == nullptr, have_next = io.h_out != nullptr;
+    int qoff[CPL];   // column of the query residue in s_mat
+    int hp[CPL], ee[CPL];
+#pragma unroll
+    for (int k = 0; k < CPL; k++) {
+        const int c = c0 + k;
+        qoff[k] = c < qlen ? (int)q[c] : PAD_CODE;
+        hp[k] = -(gapoe + gape * c);                 // H(-1, c)
+        ee[k] = -(gapoe + gapoe + gape * c);         // E(0, c)
+    }
+    // lane-local column of qlen-1 (last stripe only)
+    const int jq_lane = (qlen - 1 - c_base) / CPL, jq = (qlen - 1 - c_base) % CPL;
+    int diag = c0 == 0 ? 0 : -(gapoe + gape * (c0 - 1));   // H(i-1, c0-1), starts at row -1
+    int h_out = 0, f_out = 0, t_out = 0;                   // what this lane hands to lane+1
+    int tcur = 0;                                          // 32 target residues, one per lane
+    int hb_in = 0, fb_in = 0, hb_keep = 0, fb_keep = 0;
+    int gmax = acc.gmax, mqe = acc.mqe, mte = acc.mte, score = acc.score;
+    const int n_steps = tlen + 31;
+    for (int s = 0; s < n_steps; s++) {
+        if ((s & 31) == 0) {
+            const int r = s + lane;
+            tcur = r < tlen ? (int)t[r] : 0;
+            if (!first_stripe) {
+                if (PIPE && s < tlen) {
+                    const unsigned long long need = io.wait_base + (unsigned long long)min(s + 32, tlen);
+                    if (lane == 0) while (*io.wait_flag < need) __nanosleep(20);
+                    __syncwarp();
+                }
+                hb_in = r < tlen ? __ldcg(io.h_in + r) : 0;
+                fb_in = r < tlen ? __ldcg(io.f_in + r) : 0;
+            }
+        }
+        // values arriving from the left neighbour (computed in the previous step)
+        int h_left = __shfl_up_sync(0xffffffffu, h_out, 1);
+        int f_in = __shfl_up_sync(0xffffffffu, f_out, 1);
+        int t_res = __shfl_up_sync(0xffffffffu, t_out, 1);
+        const int t0 = __shfl_sync(0xffffffffu, tcur, s & 31);
+        const int hb0 = __shfl_sync(0xffffffffu, hb_in, s & 31);
+        const int fb0 = __shfl_sync(0xffffffffu, fb_in, s & 31);
+        if (lane == 0) {
+            t_res = t0;
+            if (first_stripe) { h_left = -(gapoe + gape * s); f_in = -(gapoe + gapoe + gape * s); }
+            else { h_left = hb0; f_in = fb0; }
+        }
+        const int i = s - lane;
+        const bool active = i >= 0 && i < tlen;
+        if (active) {
+            const int* mrow = s_mat + t_res * MAT_STRIDE;
+            int f = f_in, d = diag, h = 0, rowmax = NEG_INF;
+#pragma unroll
+            for (int k = 0; k < CPL; k++) {
+                h = d + mrow[qoff[k]];
+                h = __vimax3_s32(h, ee[k], f);
+                d = hp[k];
+                hp[k] = h;
+                rowmax = max(rowmax, h);
+                const int tt = h - gapoe;
+                ee[k] = __viaddmax_s32(ee[k], -gape, tt);
+                f = __viaddmax_s32(f, -gape, tt);
+            }
+            gmax = max(gmax, rowmax);
+            diag = h_left;
+            h_out = h; f_out = f; t_out = t_res;
+            if (i == tlen - 1) mte = max(mte, rowmax);
+            if (last_stripe && lane == jq_lane) {
+                int hq = hp[0];
+#pragma unroll
+                for (int k = 1; k < CPL; k++) hq = jq == k ? hp[k] : hq;
+                mqe = max(mqe, hq);
+                if (i == tlen - 1) score = hq;
+            }
+        }
+        if (have_next) {
+            // lane 31 finished row s-31: collect 32 rows, then store them coalesced
+            const int hr = __shfl_sync(0xffffffffu, h_out, 31);
+            const int fr = __shfl_sync(0xffffffffu, f_out, 31);
+            const int row = s - 31;
+            if (row >= 0 && (row & 31) == lane) { hb_keep = hr; fb_keep = fr; }
+            if (row >= 0 && ((row & 31) == 31 || row == tlen - 1)) {
+                const int r = (row & ~31) + lane;
+                if (r <= row) { __stcg(io.h_out + r, hb_keep); __stcg(io.f_out + r, fb_keep); }
+                if (PIPE) {
+                    __threadfence();
+                    __syncwarp();
+                    if (lane == 0) *io.post_flag = io.post_base + (unsigned long long)(row + 1);
+                }
+            }
+        }
+    }
+    acc.gmax = gmax; acc.mqe = mqe; acc.mte = mte; acc.score = score;
+}
+
+__device__ __forceinline__ void acc_reduce_warp(AlnAcc& a) {
+#pragma unroll
+    for (int d = 16; d > 0; d >>= 1) {
+        a.gmax = max(a.gmax, __shfl_xor_sync(0xffffffffu, a.gmax, d));
+        a.mte = max(a.mte, __shfl_xor_sync(0xffffffffu, a.mte, d));
+        a.mqe = max(a.mqe, __shfl_xor_sync(0xffffffffu, a.mqe, d));
+        a.score = max(a.score, __shfl_xor_sync(0xffffffffu, a.score, d));
+    }
+}
+
+// a whole pair on one warp, stripe after stripe (edges through the warp's global scratch)
 template <int CPL>
-__global__ void __launch_bounds__(ALN_WARPS * 32)
+__device__ __forceinline__ void pair_on_warp(const int* s_mat, const uint8_t* q, const uint8_t* t, int qlen, int tlen, int gapoe, int gape,
+                                             int32_t* hb, int32_t* fb, AlnAcc& acc, int lane) {
+    const int n_stripes = (qlen + 32 * CPL - 1) / (32 * CPL);
+    for (int st = 0; st < n_stripes; st++) {
+        StripeIO io;
+        io.h_in = st > 0 ? hb : nullptr; io.f_in = st > 0 ? fb : nullptr;
+        io.h_out = st < n_stripes - 1 ? hb : nullptr; io.f_out = st < n_stripes - 1 ? fb : nullptr;
+        io.wait_flag = io.post_flag = nullptr; io.wait_base = io.post_base = 0;
+        dp_stripe<CPL, false>(s_mat, q, t, qlen, tlen, st * 32 * CPL, st == n_stripes - 1, gapoe, gape, io, acc, lane);
+        __syncwarp();
+    }
+}
+
+constexpr int LONG_CPL = 8;
+
+// Persistent CTAs.  Phase A: the n_long longest pairs (order[0 .. n_long)) are taken one per CTA; the stripes of
+// a pair go round-robin to the CTA's warps, which run them as a software pipeline (block-cooperative tiles):
+// stripe k starts as soon as stripe k-1 has posted its first 32 rows.  Edges of neighbouring stripes live in two
+// global buffers per CTA (stripe parity), handed over with shared-memory progress counters.  Phase B: every warp
+// takes the remaining pairs on its own from a second counter.
+__global__ void __launch_bounds__(ALN_WARPS * 32, 1)
 align_kernel(const uint8_t* __restrict__ aa, const int64_t* __restrict__ off, const int32_t* __restrict__ pair_q,
-             const int32_t* __restrict__ pair_t, const int32_t* __restrict__ order, long long n_pairs, int gapo, int gape,
+             const int32_t* __restrict__ pair_t, const int32_t* __restrict__ order, long long n_pairs, long long n_long, int gapo, int gape,
              int32_t* __restrict__ out_max, int32_t* __restrict__ out_score, int32_t* __restrict__ out_mqe, int32_t* __restrict__ out_mte,
-             int32_t* __restrict__ scratch, long long scratch_stride, unsigned long long* counter) {
+             int32_t* __restrict__ scratch, long long scratch_stride, int32_t* __restrict__ cta_scratch, long long cta_stride,
+             unsigned long long* counters) {
     __shared__ int s_mat[25 * MAT_STRIDE];
+    __shared__ unsigned long long s_progress[ALN_WARPS];
+    __shared__ unsigned long long s_slot;
+    __shared__ int s_acc[4];
     for (int i = threadIdx.x; i < 25 * MAT_STRIDE; i += blockDim.x) {
         int r = i / MAT_STRIDE, c = i % MAT_STRIDE;
         s_mat[i] = (r < 24 && c < 24) ? (int)c_mat50[r * 24 + c] : PAD_SCORE;
     }
+    const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
+    const int gapoe = gapo + gape;
     __syncthreads();
-    const int lane = threadIdx.x & 31;
-    const long long warp_id = (long long)blockIdx.x * ALN_WARPS + (threadIdx.x >> 5);
+
+    // ---- phase A: long pairs, one per CTA at a time ----
+    int32_t* edge = cta_scratch + (long long)blockIdx.x * 4 * cta_stride;   // [parity][h|f][row]
+    while (n_long > 0) {
+        if (threadIdx.x == 0) { s_slot = atomicAdd(counters, 1ULL); s_acc[0] = 0; s_acc[1] = s_acc[2] = s_acc[3] = NEG_INF; }
+        if (lane == 0) s_progress[wib] = 0;
+        __syncthreads();
+        const unsigned long long slot = s_slot;
+        if (slot >= (unsigned long long)n_long) break;
+        const int pair = order[slot];
+        const int qi = pair_q[pair], ti = pair_t[pair];
+        const uint8_t* q = aa + off[qi];
+        const uint8_t* t = aa + off[ti];
+        const int qlen = (int)(off[qi + 1] - off[qi]), tlen = (int)(off[ti + 1] - off[ti]);
+        const int n_stripes = (qlen + 32 * LONG_CPL - 1) / (32 * LONG_CPL);
+        AlnAcc acc{0, NEG_INF, NEG_INF, NEG_INF};
+        const unsigned long long per = (unsigned long long)tlen + 1ULL;
+        for (int st = wib; st < n_stripes; st += ALN_WARPS) {
+            StripeIO io;
+            int32_t* in = edge + (long long)((st + 1) & 1) * 2 * cta_stride;    // written by stripe st-1
+            int32_t* outb = edge + (long long)(st & 1) * 2 * cta_stride;
+            io.h_in = st > 0 ? in : nullptr; io.f_in = st > 0 ? in + cta_stride : nullptr;
+            io.h_out = st < n_stripes - 1 ? outb : nullptr; io.f_out = st < n_stripes - 1 ? outb + cta_stride : nullptr;
+            io.wait_flag = &s_progress[(wib + ALN_WARPS - 1) % ALN_WARPS]; io.wait_base = (unsigned long long)(st - 1 + 1) * per;
+            io.post_flag = &s_progress[wib]; io.post_base = (unsigned long long)(st + 1) * per;
+            dp_stripe<LONG_CPL, true>(s_mat, q, t, qlen, tlen, st * 32 * LONG_CPL, st == n_stripes - 1, gapoe, gape, io, acc, lane);
+            __syncwarp();
+        }
+        acc_reduce_warp(acc);
+        if (lane == 0) { atomicMax(&s_acc[0], acc.gmax); atomicMax(&s_acc[1], acc.score); atomicMax(&s_acc[2], acc.mqe); atomicMax(&s_acc[3], acc.mte); }
+        __syncthreads();
+        if (threadIdx.x == 0) { out_max[pair] = s_acc[0]; out_score[pair] = s_acc[1]; out_mqe[pair] = s_acc[2]; out_mte[pair] = s_acc[3]; }
+        __syncthreads();
+    }
+
+    // ---- phase B: one warp per pair ----
+    const long long warp_id = (long long)blockIdx.x * ALN_WARPS + wib;
     int32_t* hb = scratch + warp_id * 2 * scratch_stride;   // right edge of the previous stripe: H(i, c_base-1)
     int32_t* fb = hb + scratch_stride;                      //                                    F(i, c_base)
-    const int gapoe = gapo + gape;
-
     while (true) {
         unsigned long long slot = 0;
-        if (lane == 0) slot = atomicAdd(counter, 1ULL);
-        slot = __shfl_sync(0xffffffffu, slot, 0);
+        if (lane == 0) slot = atomicAdd(counters + 1, 1ULL);
+        slot = (unsigned long long)n_long + __shfl_sync(0xffffffffu, slot, 0);
         if (slot >= (unsigned long long)n_pairs) break;
         const int pair = order[slot];
         const int qi = pair_q[pair], ti = pair_t[pair];
@@ -89,135 +269,114 @@ align_kernel(const uint8_t* __restrict__ aa, const int64_t* __restrict__ off, co
             if (lane == 0) { out_max[pair] = 0; out_score[pair] = NEG_INF; out_mqe[pair] = NEG_INF; out_mte[pair] = NEG_INF; }
             continue;
         }
-        int gmax = 0, mqe = NEG_INF, mte = NEG_INF, score = NEG_INF;
-        const int n_stripes = (qlen + 32 * CPL - 1) / (32 * CPL);
-        for (int st = 0; st < n_stripes; st++) {
-            const int c_base = st * 32 * CPL;
-            const int c0 = c_base + lane * CPL;
-            const bool last_stripe = st == n_stripes - 1;
-            const bool have_next = !last_stripe;
-            int qoff[CPL];   // byte offset of the query residue's column in s_mat
-            int hp[CPL], ee[CPL];
-#pragma unroll
-            for (int k = 0; k < CPL; k++) {
-                const int c = c0 + k;
-                qoff[k] = c < qlen ? (int)q[c] : PAD_CODE;
-                hp[k] = -(gapoe + gape * c);                 // H(-1, c)
-                ee[k] = -(gapoe + gapoe + gape * c);         // E(0, c)
-            }
-            // lane-local column of qlen-1 (last stripe only)
-            const int jq_lane = (qlen - 1 - c_base) / CPL, jq = (qlen - 1 - c_base) % CPL;
-            int diag = c0 == 0 ? 0 : -(gapoe + gape * (c0 - 1));   // H(i-1, c0-1), starts at row -1
-            int h_out = 0, f_out = 0, t_out = 0;                   // what this lane hands to lane+1
-            int tcur = 0;                                          // 32 target residues, one per lane
-            int hb_in = 0, fb_in = 0, hb_keep = 0, fb_keep = 0;
-            const int n_steps = tlen + 31;
-            for (int s = 0; s < n_steps; s++) {
-                if ((s & 31) == 0) {
-                    const int r = s + lane;
-                    tcur = r < tlen ? (int)t[r] : 0;
-                    if (st > 0) { hb_in = r < tlen ? hb[r] : 0; fb_in = r < tlen ? fb[r] : 0; }
-                }
-                // values arriving from the left neighbour (computed in the previous step)
-                int h_left = __shfl_up_sync(0xffffffffu, h_out, 1);
-                int f_in = __shfl_up_sync(0xffffffffu, f_out, 1);
-                int t_res = __shfl_up_sync(0xffffffffu, t_out, 1);
-                const int t0 = __shfl_sync(0xffffffffu, tcur, s & 31);
-                const int hb0 = __shfl_sync(0xffffffffu, hb_in, s & 31);
-                const int fb0 = __shfl_sync(0xffffffffu, fb_in, s & 31);
-                if (lane == 0) {
-                    t_res = t0;
-                    if (st == 0) { h_left = -(gapoe + gape * s); f_in = -(gapoe + gapoe + gape * s); }
-                    else { h_left = hb0; f_in = fb0; }
-                }
-                const int i = s - lane;
-                const bool active = i >= 0 && i < tlen;
-                if (active) {
-                    const int* mrow = s_mat + t_res * MAT_STRIDE;
-                    int f = f_in, d = diag, h = 0, rowmax = NEG_INF;
-#pragma unroll
-                    for (int k = 0; k < CPL; k++) {
-                        h = d + mrow[qoff[k]];
-                        h = __vimax3_s32(h, ee[k], f);
-                        d = hp[k];
-                        hp[k] = h;
-                        rowmax = max(rowmax, h);
-                        const int tt = h - gapoe;
-                        ee[k] = __viaddmax_s32(ee[k], -gape, tt);
-                        f = __viaddmax_s32(f, -gape, tt);
-                    }
-                    gmax = max(gmax, rowmax);
-                    diag = h_left;
-                    h_out = h; f_out = f; t_out = t_res;
-                    if (i == tlen - 1) mte = max(mte, rowmax);
-                    if (last_stripe && lane == jq_lane) {
-                        int hq = hp[0];
-#pragma unroll
-                        for (int k = 1; k < CPL; k++) hq = jq == k ? hp[k] : hq;
-                        mqe = max(mqe, hq);
-                        if (i == tlen - 1) score = hq;
-                    }
-                }
-                if (have_next) {
-                    // lane 31 finished row s-31: collect 32 rows, then store them coalesced
-                    const int hr = __shfl_sync(0xffffffffu, h_out, 31);
-                    const int fr = __shfl_sync(0xffffffffu, f_out, 31);
-                    const int row = s - 31;
-                    if (row >= 0 && (row & 31) == lane) { hb_keep = hr; fb_keep = fr; }
-                    if (row >= 0 && ((row & 31) == 31 || row == tlen - 1)) {
-                        const int r = (row & ~31) + lane;
-                        if (r <= row) { hb[r] = hb_keep; fb[r] = fb_keep; }
-                    }
-                }
-            }
-            __syncwarp();
-        }
-#pragma unroll
-        for (int d = 16; d > 0; d >>= 1) {
-            gmax = max(gmax, __shfl_xor_sync(0xffffffffu, gmax, d));
-            mte = max(mte, __shfl_xor_sync(0xffffffffu, mte, d));
-            mqe = max(mqe, __shfl_xor_sync(0xffffffffu, mqe, d));
-            score = max(score, __shfl_xor_sync(0xffffffffu, score, d));
-        }
-        if (lane == 0) { out_max[pair] = gmax; out_score[pair] = score; out_mqe[pair] = mqe; out_mte[pair] = mte; }
+        AlnAcc acc{0, NEG_INF, NEG_INF, NEG_INF};
+        if (qlen <= 64) pair_on_warp<2>(s_mat, q, t, qlen, tlen, gapoe, gape, hb, fb, acc, lane);
+        else if (qlen <= 128) pair_on_warp<4>(s_mat, q, t, qlen, tlen, gapoe, gape, hb, fb, acc, lane);
+        else pair_on_warp<8>(s_mat, q, t, qlen, tlen, gapoe, gape, hb, fb, acc, lane);
+        acc_reduce_warp(acc);
+        if (lane == 0) { out_max[pair] = acc.gmax; out_score[pair] = acc.score; out_mqe[pair] = acc.mqe; out_mte[pair] = acc.mte; }
     }
+}
+
+// Issue-rate microbenchmark behind the alignment roofline: every thread runs 8 independent
+// dependent chains of one integer instruction; ops/s = threads x ops / time.
+template <int KIND>
+__global__ void __launch_bounds__(256) int_alu_peak_kernel(int iters, int seed, int* sink) {
+    int a[8];
+#pragma unroll
+    for (int k = 0; k < 8; k++) a[k] = seed + threadIdx.x * 8 + k;
+    const int b = seed * 3 + 1, c = seed - 7;
+    for (int it = 0; it < iters; it++) {
+#pragma unroll
+        for (int u = 0; u < 8; u++) {
+#pragma unroll
+            for (int k = 0; k < 8; k++) {
+                if (KIND == 0) a[k] = a[k] + a[(k + 1) & 7] + b;     // IADD3 (two live chains per add: not foldable)
+                else if (KIND == 1) a[k] = __vimax3_s32(a[k] - 1, b + u, c);   // IADD + VIMNMX3
+                else a[k] = __viaddmax_s32(a[k], -2, b + u);           // VIADDMNMX
+            }
+        }
+    }
+    int r = 0;
+#pragma unroll
+    for (int k = 0; k < 8; k++) r ^= a[k];
+    if (r == 0x7fffffff) *sink = r;
 }
 
 }  // namespace
 
+// ops[0] IADD3/s, ops[1] (IADD + VIMNMX3 pairs counted as 2 ops)/s, ops[2] VIADDMNMX/s (counted as 2 ops: add + max)
+int int_alu_peak_device(cudaStream_t stream, double* ops, std::string& err) {
+    cudaDeviceProp prop;
+    int dev = 0;
+    cudaGetDevice(&dev);
+    if (cudaGetDeviceProperties(&prop, dev) != cudaSuccess) { err = "cudaGetDeviceProperties"; return ORFX_E_CUDA; }
+    int* sink = nullptr;
+    if (cudaMalloc(&sink, 4) != cudaSuccess) { err = "cudaMalloc"; return ORFX_E_CUDA; }
+    cudaEvent_t e0, e1;
+    cudaEventCreate(&e0); cudaEventCreate(&e1);
+    const int grid = prop.multiProcessorCount * 8, iters = 4096;
+    const double per_thread = (double)iters * 64;
+    for (int kind = 0; kind < 3; kind++) {
+        float best = 1e30f;
+        for (int rep = 0; rep < 4; rep++) {
+            cudaEventRecord(e0, stream);
+            if (kind == 0) int_alu_peak_kernel<0><<<grid, 256, 0, stream>>>(iters, rep + 1, sink);
+            else if (kind == 1) int_alu_peak_kernel<1><<<grid, 256, 0, stream>>>(iters, rep + 1, sink);
+            else int_alu_peak_kernel<2><<<grid, 256, 0, stream>>>(iters, rep + 1, sink);
+            cudaEventRecord(e1, stream);
+            if (cudaStreamSynchronize(stream) != cudaSuccess) { err = "int_alu_peak kernel failed"; cudaFree(sink); return ORFX_E_CUDA; }
+            float ms = 0;
+            cudaEventElapsedTime(&ms, e0, e1);
+            if (rep > 0 && ms < best) best = ms;
+        }
+        const double insts = per_thread * (double)grid * 256.0;
+        ops[kind] = insts * (kind == 0 ? 1.0 : 2.0) / (best * 1e-3);
+    }
+    cudaEventDestroy(e0); cudaEventDestroy(e1);
+    cudaFree(sink);
+    return ORFX_OK;
+}
+
 int align_batch_device(int device, cudaStream_t stream, const uint8_t* aa, const int64_t* off, int64_t n_seq, const int32_t* pair_q,
                        const int32_t* pair_t, int64_t n_pairs, int gapo, int gape, orfx_aln_out* out, double* cells, float* ms, std::string& err) {
     (void)device;
-    constexpr int CPL = 8;
     auto ck = [&](cudaError_t e, const char* what) { if (e != cudaSuccess) { err = std::string(what) + ": " + cudaGetErrorString(e); return false; } return true; };
     if (n_pairs == 0) { if (cells) *cells = 0; if (ms) *ms = 0; return ORFX_OK; }
     const int64_t total = off[n_seq];
-    // longest-first order (cells = qlen * tlen), so the long tail starts early
+    // long pairs first (they take whole CTAs, phase A), then the rest; both longest-first (cells = qlen * tlen),
+    // so the long tail starts early
     std::vector<int32_t> order((size_t)n_pairs);
     std::iota(order.begin(), order.end(), 0);
     std::vector<double> cost((size_t)n_pairs);
+    std::vector<uint8_t> is_long((size_t)n_pairs);
     double sum_cells = 0;
-    int64_t max_tlen = 1;
+    int64_t max_tlen = 1, max_tlen_long = 1, n_long = 0;
     for (int64_t p = 0; p < n_pairs; p++) {
         if (pair_q[p] < 0 || pair_q[p] >= n_seq || pair_t[p] < 0 || pair_t[p] >= n_seq) { err = "pair index out of range"; return ORFX_E_INVALID; }
         const int64_t ql = off[pair_q[p] + 1] - off[pair_q[p]], tl = off[pair_t[p] + 1] - off[pair_t[p]];
         cost[(size_t)p] = (double)ql * (double)tl;
         sum_cells += cost[(size_t)p];
-        if (ql > 32 * CPL) max_tlen = std::max(max_tlen, tl);
+        is_long[(size_t)p] = ql >= 1024 && tl >= 256 && cost[(size_t)p] >= 4194304.0;
+        if (is_long[(size_t)p]) { n_long++; max_tlen_long = std::max(max_tlen_long, tl); }
+        else if (ql > 64) max_tlen = std::max(max_tlen, tl);
     }
-    std::sort(order.begin(), order.end(), [&](int32_t a, int32_t b) { return cost[(size_t)a] != cost[(size_t)b] ? cost[(size_t)a] > cost[(size_t)b] : a < b; });
+    std::sort(order.begin(), order.end(), [&](int32_t a, int32_t b) {
+        if (is_long[(size_t)a] != is_long[(size_t)b]) return is_long[(size_t)a] > is_long[(size_t)b];
+        return cost[(size_t)a] != cost[(size_t)b] ? cost[(size_t)a] > cost[(size_t)b] : a < b;
+    });
     cudaDeviceProp prop;
     int dev = 0;
     cudaGetDevice(&dev);
     if (!ck(cudaGetDeviceProperties(&prop, dev), "cudaGetDeviceProperties")) return ORFX_E_CUDA;
-    const int ctas_per_sm = 4;
-    int grid = prop.multiProcessorCount * ctas_per_sm;
-    const int64_t max_grid = (n_pairs + ALN_WARPS - 1) / ALN_WARPS;
-    if (grid > max_grid) grid = (int)max_grid;
+    int grid = prop.multiProcessorCount;
+    const int64_t max_grid = std::max<int64_t>(n_long, (n_pairs - n_long + ALN_WARPS - 1) / ALN_WARPS);
+    if (grid > max_grid) grid = (int)std::max<int64_t>(1, max_grid);
     const int64_t n_warps = (int64_t)grid * ALN_WARPS;
     const int64_t stride = (max_tlen + 31) / 32 * 32;
+    const int64_t cta_stride = (max_tlen_long + 31) / 32 * 32;
 
-    uint8_t* d_aa = nullptr; int64_t* d_off = nullptr; int32_t *d_pq = nullptr, *d_pt = nullptr, *d_order = nullptr, *d_out = nullptr, *d_scratch = nullptr;
+    uint8_t* d_aa = nullptr; int64_t* d_off = nullptr; int32_t *d_pq = nullptr, *d_pt = nullptr, *d_order = nullptr, *d_out = nullptr, *d_scratch = nullptr, *d_cta = nullptr;
     unsigned long long* d_counter = nullptr;
     cudaEvent_t e0 = nullptr, e1 = nullptr;
     int rc = ORFX_OK;
@@ -229,17 +388,19 @@ int align_batch_device(int device, cudaStream_t stream, const uint8_t* aa, const
         if (!ck(cudaMalloc(&d_order, (size_t)n_pairs * 4), "cudaMalloc order")) { rc = ORFX_E_CUDA; break; }
         if (!ck(cudaMalloc(&d_out, (size_t)n_pairs * 16), "cudaMalloc out")) { rc = ORFX_E_CUDA; break; }
         if (!ck(cudaMalloc(&d_scratch, (size_t)(n_warps * 2 * stride) * 4 + 16), "cudaMalloc scratch")) { rc = ORFX_E_CUDA; break; }
-        if (!ck(cudaMalloc(&d_counter, 8), "cudaMalloc counter")) { rc = ORFX_E_CUDA; break; }
+        if (!ck(cudaMalloc(&d_cta, (size_t)((int64_t)grid * 4 * cta_stride) * 4 + 16), "cudaMalloc cta scratch")) { rc = ORFX_E_CUDA; break; }
+        if (!ck(cudaMalloc(&d_counter, 16), "cudaMalloc counter")) { rc = ORFX_E_CUDA; break; }
         cudaEventCreate(&e0); cudaEventCreate(&e1);
         if (!ck(cudaMemcpyAsync(d_aa, aa, (size_t)total, cudaMemcpyHostToDevice, stream), "H2D aa")) { rc = ORFX_E_CUDA; break; }
         cudaMemcpyAsync(d_off, off, (size_t)(n_seq + 1) * 8, cudaMemcpyHostToDevice, stream);
         cudaMemcpyAsync(d_pq, pair_q, (size_t)n_pairs * 4, cudaMemcpyHostToDevice, stream);
         cudaMemcpyAsync(d_pt, pair_t, (size_t)n_pairs * 4, cudaMemcpyHostToDevice, stream);
         cudaMemcpyAsync(d_order, order.data(), (size_t)n_pairs * 4, cudaMemcpyHostToDevice, stream);
-        cudaMemsetAsync(d_counter, 0, 8, stream);
+        cudaMemsetAsync(d_counter, 0, 16, stream);
         cudaEventRecord(e0, stream);
-        align_kernel<CPL><<<grid, ALN_WARPS * 32, 0, stream>>>(d_aa, d_off, d_pq, d_pt, d_order, (long long)n_pairs, gapo, gape, d_out, d_out + n_pairs,
-                                                             d_out + 2 * n_pairs, d_out + 3 * n_pairs, d_scratch, (long long)stride, d_counter);
+        align_kernel<<<grid, ALN_WARPS * 32, 0, stream>>>(d_aa, d_off, d_pq, d_pt, d_order, (long long)n_pairs, (long long)n_long, gapo, gape, d_out,
+                                                        d_out + n_pairs, d_out + 2 * n_pairs, d_out + 3 * n_pairs, d_scratch, (long long)stride, d_cta,
+                                                        (long long)cta_stride, d_counter);
         cudaEventRecord(e1, stream);
         cudaMemcpyAsync(out->max, d_out, (size_t)n_pairs * 4, cudaMemcpyDeviceToHost, stream);
         cudaMemcpyAsync(out->score, d_out + n_pairs, (size_t)n_pairs * 4, cudaMemcpyDeviceToHost, stream);
@@ -254,7 +415,7 @@ int align_batch_device(int device, cudaStream_t stream, const uint8_t* aa, const
     } while (false);
     if (e0) cudaEventDestroy(e0);
     if (e1) cudaEventDestroy(e1);
-    cudaFree(d_aa); cudaFree(d_off); cudaFree(d_pq); cudaFree(d_pt); cudaFree(d_order); cudaFree(d_out); cudaFree(d_scratch); cudaFree(d_counter);
+    cudaFree(d_aa); cudaFree(d_off); cudaFree(d_pq); cudaFree(d_pt); cudaFree(d_order); cudaFree(d_out); cudaFree(d_scratch); cudaFree(d_cta); cudaFree(d_counter);
     return rc;
 }
 

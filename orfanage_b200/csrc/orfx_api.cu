@@ -25,6 +25,7 @@ void launch_codon_scan(const DevBatch& B, int64_t n_tiles, int n_sm, cudaStream_
 int launch_base_planes(const DevBatch& B, cudaStream_t stream);
 int align_batch_device(int device, cudaStream_t stream, const uint8_t* aa, const int64_t* off, int64_t n_seq, const int32_t* pair_q,
                        const int32_t* pair_t, int64_t n_pairs, int gapo, int gape, orfx_aln_out* out, double* cells, float* ms, std::string& err);
+int int_alu_peak_device(cudaStream_t stream, double* ops, std::string& err);
 }  // namespace orfx
 
 using namespace orfx;
@@ -505,6 +506,15 @@ int orfx_align_batch(orfx_ctx* c, const uint8_t* aa, const int64_t* off, int64_t
     CU(cudaSetDevice(c->device));
     std::string err;
     int rc = align_batch_device(c->device, c->stream, aa, off, n_seq, pair_q, pair_t, n_pairs, gapo, gape, out, cells, ms, err);
+    if (rc) return fail(rc, err);
+    return ORFX_OK;
+}
+
+int orfx_int_alu_peak(orfx_ctx* c, double* ops3) {
+    if (!c || !ops3) return fail(ORFX_E_INVALID, "null argument");
+    CU(cudaSetDevice(c->device));
+    std::string err;
+    int rc = int_alu_peak_device(c->stream, ops3, err);
     if (rc) return fail(rc, err);
     return ORFX_OK;
 }
