@@ -222,9 +222,10 @@ int  orfx_align_batch(orfx_ctx* ctx, const uint8_t* aa, const int64_t* off, int6
                       int gapo, int gape, orfx_aln_out* out, double* cells, float* ms);
 
 /* Integer-ALU issue-rate microbenchmark on the context's device: the denominator of the alignment roofline
- * (SURVEY.md §8d).  ops3[0] = IADD3 operations/s; ops3[1] = IADD + VIMNMX3 pairs (2 operations each)/s;
- * ops3[2] = VIADDMNMX (add + max, 2 operations each)/s; all SMs, 8 independent chains per thread. */
-int  orfx_int_alu_peak(orfx_ctx* ctx, double* ops3);
+ * (SURVEY.md §8d).  ops4[0] = IADD3 instructions/s; ops4[1] = IADD + VIMNMX3 pairs (2 operations each)/s;
+ * ops4[2] = VIADDMNMX (add + max, 2 operations each)/s; ops4[3] = IDP.4A instructions/s; all SMs, 8
+ * independent chains per thread. */
+int  orfx_int_alu_peak(orfx_ctx* ctx, double* ops4);
 
 #ifdef __cplusplus
 }

@@ -421,9 +421,9 @@ class Context:
 
     def int_alu_peak(self):
         """orfx_int_alu_peak: measured integer issue rates of this GPU, operations/s."""
-        ops = (C.c_double * 3)()
+        ops = (C.c_double * 4)()
         self._check(self.lib.orfx_int_alu_peak(self.handle, ops))
-        return {"iadd3": ops[0], "iadd_vimnmx3": ops[1], "viaddmnmx": ops[2]}
+        return {"iadd3": ops[0], "iadd_vimnmx3": ops[1], "viaddmnmx": ops[2], "idp4a": ops[3]}
 
     def close(self):
         if self.handle:

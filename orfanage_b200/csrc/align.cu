@@ -52,8 +52,6 @@ __constant__ int8_t c_mat50[24 * 24] = {
     -5,-5,-5,-5,-5,-5,-5,-5,-5,-5,-5,-5,-5,-5,-5,-5,-5,-5,-5,-5,-5,-5,-5, 1};
 
 constexpr int NEG_INF = -0x40000000;
-constexpr int PAD_CODE = 24;        // virtual query column right of the query's end
-constexpr int PAD_SCORE = -4096;    // never wins: padded cells are dominated by H(i,qlen-1)
 constexpr int MAT_STRIDE = 32;
 constexpr int ALN_WARPS = 16;       // one CTA per SM; its warps work alone on short pairs and as a pipeline on long ones
 
@@ -69,75 +67,97 @@ struct StripeIO {
     volatile unsigned long long* post_flag; unsigned long long post_base;
 };
 
+// Per-warp shared memory of the DP (dynamic shared memory, one WarpSmem per warp).
+struct WarpSmem {
+    uint2 prof[24][32];     // query profile: prof[r][lane] = the lane's CPL scores against target residue r, one int8 each
+    int   t_ring[64];       // target residues of the current and the previous 32-row chunk
+    int2  in_ring[32];      // left edge {H(i, c_base-1), F(i, c_base)} of the current chunk (borders for the first stripe)
+    int2  out_ring[32];     // right edge of the rows lane 31 finished, until the chunk is stored
+};
+constexpr int PAD_SCORE8 = -128;    // score of the virtual columns right of the query's end: padded cells stay below
+                                    // H(i, qlen-1) - (gapo+gape) per column as long as gapo+gape <= 64
+
 // One stripe of 32*CPL query columns over all target rows.  Lanes own CPL consecutive columns; lane l works on
-// target row (step - l), so only the lane's right edge (H, F) and the target residue move to the next lane.
+// target row (step - l), so only the lane's right edge (H, F) moves to the next lane (two shuffles per step).
+// The substitution scores of a step come as ONE shared-memory load of the lane's profile entry and are added to
+// the diagonal with dp4a (one-hot selector) on the FMA pipe, which leaves the ALU pipe to the max/add-max chain:
+//   x = d + s; h = max3(x, E, F); E' = max(E - e, h - (q+e)); F' = max(F - e, h - (q+e))      (4 ALU + 1 FMA per cell)
 template <int CPL, bool PIPE>
-__device__ __forceinline__ void dp_stripe(const int* __restrict__ s_mat, const uint8_t* __restrict__ q, const uint8_t* __restrict__ t, int qlen, int tlen,
-                                          int c_base, bool last_stripe, int gapoe, int gape, const StripeIO& io, AlnAcc& acc, int lane) {
+__device__ __forceinline__ void dp_stripe(const int* __restrict__ s_mat, WarpSmem& ws, const uint8_t* __restrict__ q, const uint8_t* __restrict__ t,
+                                          int qlen, int tlen, int c_base, bool last_stripe, int gapoe, int gape, const StripeIO& io, AlnAcc& acc,
+                                          int lane) {
+    static_assert(CPL <= 8, "a profile entry holds 8 scores");
     const int c0 = c_base + lane * CPL;
     const bool first_stripe = io.h_in == nullptr, have_next = io.h_out != nullptr;
-    int qoff[CPL];   // column of the query residue in s_mat
     int hp[CPL], ee[CPL];
+    {
+        int qcode[CPL];
 #pragma unroll
-    for (int k = 0; k < CPL; k++) {
-        const int c = c0 + k;
-        qoff[k] = c < qlen ? (int)q[c] : PAD_CODE;
-        hp[k] = -(gapoe + gape * c);                 // H(-1, c)
-        ee[k] = -(gapoe + gapoe + gape * c);         // E(0, c)
+        for (int k = 0; k < CPL; k++) {
+            const int c = c0 + k;
+            qcode[k] = c < qlen ? min((int)q[c], 23) : -1;
+            hp[k] = -(gapoe + gape * c);                 // H(-1, c)
+            ee[k] = -(gapoe + gapoe + gape * c);         // E(0, c)
+        }
+        __syncwarp();   // the previous stripe's profile is no longer read
+        for (int r = 0; r < 24; r++) {
+            uint32_t lo = 0, hi = 0;
+#pragma unroll
+            for (int k = 0; k < CPL; k++) {
+                const uint32_t b = (uint32_t)(qcode[k] >= 0 ? s_mat[r * MAT_STRIDE + qcode[k]] : PAD_SCORE8) & 0xFFu;
+                if (k < 4) lo |= b << (8 * k); else hi |= b << (8 * (k - 4));
+            }
+            ws.prof[r][lane] = make_uint2(lo, hi);
+        }
     }
     // lane-local column of qlen-1 (last stripe only)
     const int jq_lane = (qlen - 1 - c_base) / CPL, jq = (qlen - 1 - c_base) % CPL;
     int diag = c0 == 0 ? 0 : -(gapoe + gape * (c0 - 1));   // H(i-1, c0-1), starts at row -1
-    int h_out = 0, f_out = 0, t_out = 0;                   // what this lane hands to lane+1
-    int tcur = 0;                                          // 32 target residues, one per lane
-    int hb_in = 0, fb_in = 0, hb_keep = 0, fb_keep = 0;
+    int h_out = 0, f_out = 0;                              // what this lane hands to lane+1
     int gmax = acc.gmax, mqe = acc.mqe, mte = acc.mte, score = acc.score;
     const int n_steps = tlen + 31;
     for (int s = 0; s < n_steps; s++) {
-        if ((s & 31) == 0) {
+        if ((s & 31) == 0) {   // next 32 target rows: residues and left edge into the rings
             const int r = s + lane;
-            tcur = r < tlen ? (int)t[r] : 0;
+            int2 e = make_int2(-(gapoe + gape * r), -(gapoe + gapoe + gape * r));   // first stripe: H(r, -1), F(r, 0)
             if (!first_stripe) {
                 if (PIPE && s < tlen) {
                     const unsigned long long need = io.wait_base + (unsigned long long)min(s + 32, tlen);
                     if (lane == 0) while (*io.wait_flag < need) __nanosleep(20);
                     __syncwarp();
                 }
-                hb_in = r < tlen ? __ldcg(io.h_in + r) : 0;
-                fb_in = r < tlen ? __ldcg(io.f_in + r) : 0;
+                e.x = r < tlen ? __ldcg(io.h_in + r) : 0;
+                e.y = r < tlen ? __ldcg(io.f_in + r) : 0;
             }
+            __syncwarp();   // every lane is done with the rings' previous contents
+            ws.t_ring[r & 63] = r < tlen ? min((int)t[r], 23) : 0;
+            ws.in_ring[lane] = e;
+            __syncwarp();
         }
-        // values arriving from the left neighbour (computed in the previous step)
+        // values arriving from the left neighbour (computed in the previous step); lane 0 reads the edge ring
         int h_left = __shfl_up_sync(0xffffffffu, h_out, 1);
         int f_in = __shfl_up_sync(0xffffffffu, f_out, 1);
-        int t_res = __shfl_up_sync(0xffffffffu, t_out, 1);
-        const int t0 = __shfl_sync(0xffffffffu, tcur, s & 31);
-        const int hb0 = __shfl_sync(0xffffffffu, hb_in, s & 31);
-        const int fb0 = __shfl_sync(0xffffffffu, fb_in, s & 31);
-        if (lane == 0) {
-            t_res = t0;
-            if (first_stripe) { h_left = -(gapoe + gape * s); f_in = -(gapoe + gapoe + gape * s); }
-            else { h_left = hb0; f_in = fb0; }
-        }
+        const int2 edge = ws.in_ring[s & 31];
+        if (lane == 0) { h_left = edge.x; f_in = edge.y; }
         const int i = s - lane;
-        const bool active = i >= 0 && i < tlen;
-        if (active) {
-            const int* mrow = s_mat + t_res * MAT_STRIDE;
-            int f = f_in, d = diag, h = 0, rowmax = NEG_INF;
+        if (i >= 0 && i < tlen) {
+            const uint2 sc = ws.prof[ws.t_ring[i & 63]][lane];
+            int f = f_in, d = diag, h = 0, m0 = NEG_INF, m1 = NEG_INF;
 #pragma unroll
             for (int k = 0; k < CPL; k++) {
-                h = d + mrow[qoff[k]];
-                h = __vimax3_s32(h, ee[k], f);
+                const int x = __dp4a((int)(k < 4 ? sc.x : sc.y), 1 << (8 * (k & 3)), d);
+                h = __vimax3_s32(x, ee[k], f);
                 d = hp[k];
                 hp[k] = h;
-                rowmax = max(rowmax, h);
+                if (k & 1) m1 = __vimax3_s32(m1, m0, h); else m0 = h;
                 const int tt = h - gapoe;
                 ee[k] = __viaddmax_s32(ee[k], -gape, tt);
                 f = __viaddmax_s32(f, -gape, tt);
             }
+            const int rowmax = (CPL & 1) ? max(m1, m0) : m1;
             gmax = max(gmax, rowmax);
             diag = h_left;
-            h_out = h; f_out = f; t_out = t_res;
+            h_out = h; f_out = f;
             if (i == tlen - 1) mte = max(mte, rowmax);
             if (last_stripe && lane == jq_lane) {
                 int hq = hp[0];
@@ -148,18 +168,21 @@ __device__ __forceinline__ void dp_stripe(const int* __restrict__ s_mat, const u
             }
         }
         if (have_next) {
-            // lane 31 finished row s-31: collect 32 rows, then store them coalesced
-            const int hr = __shfl_sync(0xffffffffu, h_out, 31);
-            const int fr = __shfl_sync(0xffffffffu, f_out, 31);
+            // lane 31 finished row s-31: park its edge, store 32 rows at a time, coalesced
             const int row = s - 31;
-            if (row >= 0 && (row & 31) == lane) { hb_keep = hr; fb_keep = fr; }
-            if (row >= 0 && ((row & 31) == 31 || row == tlen - 1)) {
-                const int r = (row & ~31) + lane;
-                if (r <= row) { __stcg(io.h_out + r, hb_keep); __stcg(io.f_out + r, fb_keep); }
-                if (PIPE) {
-                    __threadfence();
+            if (row >= 0) {
+                if (lane == 31) ws.out_ring[row & 31] = make_int2(h_out, f_out);
+                if ((row & 31) == 31 || row == tlen - 1) {
                     __syncwarp();
-                    if (lane == 0) *io.post_flag = io.post_base + (unsigned long long)(row + 1);
+                    const int r = (row & ~31) + lane;
+                    if (r <= row) { const int2 o = ws.out_ring[lane]; __stcg(io.h_out + r, o.x); __stcg(io.f_out + r, o.y); }
+                    if (PIPE) {
+                        __threadfence();
+                        __syncwarp();
+                        if (lane == 0) *io.post_flag = io.post_base + (unsigned long long)(row + 1);
+                    } else {
+                        __syncwarp();
+                    }
                 }
             }
         }
@@ -179,7 +202,7 @@ __device__ __forceinline__ void acc_reduce_warp(AlnAcc& a) {
 
 // a whole pair on one warp, stripe after stripe (edges through the warp's global scratch)
 template <int CPL>
-__device__ __forceinline__ void pair_on_warp(const int* s_mat, const uint8_t* q, const uint8_t* t, int qlen, int tlen, int gapoe, int gape,
+__device__ __forceinline__ void pair_on_warp(const int* s_mat, WarpSmem& ws, const uint8_t* q, const uint8_t* t, int qlen, int tlen, int gapoe, int gape,
                                              int32_t* hb, int32_t* fb, AlnAcc& acc, int lane) {
     const int n_stripes = (qlen + 32 * CPL - 1) / (32 * CPL);
     for (int st = 0; st < n_stripes; st++) {
@@ -187,7 +210,7 @@ __device__ __forceinline__ void pair_on_warp(const int* s_mat, const uint8_t* q,
         io.h_in = st > 0 ? hb : nullptr; io.f_in = st > 0 ? fb : nullptr;
         io.h_out = st < n_stripes - 1 ? hb : nullptr; io.f_out = st < n_stripes - 1 ? fb : nullptr;
         io.wait_flag = io.post_flag = nullptr; io.wait_base = io.post_base = 0;
-        dp_stripe<CPL, false>(s_mat, q, t, qlen, tlen, st * 32 * CPL, st == n_stripes - 1, gapoe, gape, io, acc, lane);
+        dp_stripe<CPL, false>(s_mat, ws, q, t, qlen, tlen, st * 32 * CPL, st == n_stripes - 1, gapoe, gape, io, acc, lane);
         __syncwarp();
     }
 }
@@ -211,10 +234,12 @@ align_kernel(const uint8_t* __restrict__ aa, const int64_t* __restrict__ off, co
     __shared__ int s_acc[4];
     for (int i = threadIdx.x; i < 25 * MAT_STRIDE; i += blockDim.x) {
         int r = i / MAT_STRIDE, c = i % MAT_STRIDE;
-        s_mat[i] = (r < 24 && c < 24) ? (int)c_mat50[r * 24 + c] : PAD_SCORE;
+        s_mat[i] = (r < 24 && c < 24) ? (int)c_mat50[r * 24 + c] : PAD_SCORE8;
     }
     const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
     const int gapoe = gapo + gape;
+    extern __shared__ __align__(16) unsigned char aln_smem[];
+    WarpSmem& ws = reinterpret_cast<WarpSmem*>(aln_smem)[wib];
     __syncthreads();
 
     // ---- phase A: long pairs, one per CTA at a time ----
@@ -241,7 +266,7 @@ align_kernel(const uint8_t* __restrict__ aa, const int64_t* __restrict__ off, co
             io.h_out = st < n_stripes - 1 ? outb : nullptr; io.f_out = st < n_stripes - 1 ? outb + cta_stride : nullptr;
             io.wait_flag = &s_progress[(wib + ALN_WARPS - 1) % ALN_WARPS]; io.wait_base = (unsigned long long)(st - 1 + 1) * per;
             io.post_flag = &s_progress[wib]; io.post_base = (unsigned long long)(st + 1) * per;
-            dp_stripe<LONG_CPL, true>(s_mat, q, t, qlen, tlen, st * 32 * LONG_CPL, st == n_stripes - 1, gapoe, gape, io, acc, lane);
+            dp_stripe<LONG_CPL, true>(s_mat, ws, q, t, qlen, tlen, st * 32 * LONG_CPL, st == n_stripes - 1, gapoe, gape, io, acc, lane);
             __syncwarp();
         }
         acc_reduce_warp(acc);
@@ -270,9 +295,9 @@ align_kernel(const uint8_t* __restrict__ aa, const int64_t* __restrict__ off, co
             continue;
         }
         AlnAcc acc{0, NEG_INF, NEG_INF, NEG_INF};
-        if (qlen <= 64) pair_on_warp<2>(s_mat, q, t, qlen, tlen, gapoe, gape, hb, fb, acc, lane);
-        else if (qlen <= 128) pair_on_warp<4>(s_mat, q, t, qlen, tlen, gapoe, gape, hb, fb, acc, lane);
-        else pair_on_warp<8>(s_mat, q, t, qlen, tlen, gapoe, gape, hb, fb, acc, lane);
+        if (qlen <= 64) pair_on_warp<2>(s_mat, ws, q, t, qlen, tlen, gapoe, gape, hb, fb, acc, lane);
+        else if (qlen <= 128) pair_on_warp<4>(s_mat, ws, q, t, qlen, tlen, gapoe, gape, hb, fb, acc, lane);
+        else pair_on_warp<8>(s_mat, ws, q, t, qlen, tlen, gapoe, gape, hb, fb, acc, lane);
         acc_reduce_warp(acc);
         if (lane == 0) { out_max[pair] = acc.gmax; out_score[pair] = acc.score; out_mqe[pair] = acc.mqe; out_mte[pair] = acc.mte; }
     }
@@ -293,7 +318,8 @@ __global__ void __launch_bounds__(256) int_alu_peak_kernel(int iters, int seed, 
             for (int k = 0; k < 8; k++) {
                 if (KIND == 0) a[k] = a[k] + a[(k + 1) & 7] + b;     // IADD3 (two live chains per add: not foldable)
                 else if (KIND == 1) a[k] = __vimax3_s32(a[k] - 1, b + u, c);   // IADD + VIMNMX3
-                else a[k] = __viaddmax_s32(a[k], -2, b + u);           // VIADDMNMX
+                else if (KIND == 2) a[k] = __viaddmax_s32(a[k], -2, b + u);           // VIADDMNMX
+                else a[k] = __dp4a(a[(k + 1) & 7], 0x00000100, a[k]);   // IDP.4A
             }
         }
     }
@@ -305,7 +331,8 @@ __global__ void __launch_bounds__(256) int_alu_peak_kernel(int iters, int seed, 
 
 }  // namespace
 
-// ops[0] IADD3/s, ops[1] (IADD + VIMNMX3 pairs counted as 2 ops)/s, ops[2] VIADDMNMX/s (counted as 2 ops: add + max)
+// ops[0] IADD3/s, ops[1] (IADD + VIMNMX3 pairs counted as 2 ops)/s, ops[2] VIADDMNMX/s (counted as 2 ops: add + max),
+// ops[3] IDP.4A instructions/s
 int int_alu_peak_device(cudaStream_t stream, double* ops, std::string& err) {
     cudaDeviceProp prop;
     int dev = 0;
@@ -317,13 +344,14 @@ int int_alu_peak_device(cudaStream_t stream, double* ops, std::string& err) {
     cudaEventCreate(&e0); cudaEventCreate(&e1);
     const int grid = prop.multiProcessorCount * 8, iters = 4096;
     const double per_thread = (double)iters * 64;
-    for (int kind = 0; kind < 3; kind++) {
+    for (int kind = 0; kind < 4; kind++) {
         float best = 1e30f;
         for (int rep = 0; rep < 4; rep++) {
             cudaEventRecord(e0, stream);
             if (kind == 0) int_alu_peak_kernel<0><<<grid, 256, 0, stream>>>(iters, rep + 1, sink);
             else if (kind == 1) int_alu_peak_kernel<1><<<grid, 256, 0, stream>>>(iters, rep + 1, sink);
-            else int_alu_peak_kernel<2><<<grid, 256, 0, stream>>>(iters, rep + 1, sink);
+            else if (kind == 2) int_alu_peak_kernel<2><<<grid, 256, 0, stream>>>(iters, rep + 1, sink);
+            else int_alu_peak_kernel<3><<<grid, 256, 0, stream>>>(iters, rep + 1, sink);
             cudaEventRecord(e1, stream);
             if (cudaStreamSynchronize(stream) != cudaSuccess) { err = "int_alu_peak kernel failed"; cudaFree(sink); return ORFX_E_CUDA; }
             float ms = 0;
@@ -331,7 +359,7 @@ int int_alu_peak_device(cudaStream_t stream, double* ops, std::string& err) {
             if (rep > 0 && ms < best) best = ms;
         }
         const double insts = per_thread * (double)grid * 256.0;
-        ops[kind] = insts * (kind == 0 ? 1.0 : 2.0) / (best * 1e-3);
+        ops[kind] = insts * (kind == 0 || kind == 3 ? 1.0 : 2.0) / (best * 1e-3);
     }
     cudaEventDestroy(e0); cudaEventDestroy(e1);
     cudaFree(sink);
@@ -343,6 +371,7 @@ int align_batch_device(int device, cudaStream_t stream, const uint8_t* aa, const
     (void)device;
     auto ck = [&](cudaError_t e, const char* what) { if (e != cudaSuccess) { err = std::string(what) + ": " + cudaGetErrorString(e); return false; } return true; };
     if (n_pairs == 0) { if (cells) *cells = 0; if (ms) *ms = 0; return ORFX_OK; }
+    if (gapo < 0 || gape < 0 || gapo + gape > 64) { err = "gap costs outside this build's range (0 <= gapo + gape <= 64)"; return ORFX_E_UNSUPPORTED; }
     const int64_t total = off[n_seq];
     // long pairs first (they take whole CTAs, phase A), then the rest; both longest-first (cells = qlen * tlen),
     // so the long tail starts early
@@ -397,8 +426,9 @@ int align_batch_device(int device, cudaStream_t stream, const uint8_t* aa, const
         cudaMemcpyAsync(d_pt, pair_t, (size_t)n_pairs * 4, cudaMemcpyHostToDevice, stream);
         cudaMemcpyAsync(d_order, order.data(), (size_t)n_pairs * 4, cudaMemcpyHostToDevice, stream);
         cudaMemsetAsync(d_counter, 0, 16, stream);
+        cudaFuncSetAttribute(align_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(ALN_WARPS * sizeof(WarpSmem)));
         cudaEventRecord(e0, stream);
-        align_kernel<<<grid, ALN_WARPS * 32, 0, stream>>>(d_aa, d_off, d_pq, d_pt, d_order, (long long)n_pairs, (long long)n_long, gapo, gape, d_out,
+        align_kernel<<<grid, ALN_WARPS * 32, ALN_WARPS * sizeof(WarpSmem), stream>>>(d_aa, d_off, d_pq, d_pt, d_order, (long long)n_pairs, (long long)n_long, gapo, gape, d_out,
                                                         d_out + n_pairs, d_out + 2 * n_pairs, d_out + 3 * n_pairs, d_scratch, (long long)stride, d_cta,
                                                         (long long)cta_stride, d_counter);
         cudaEventRecord(e1, stream);

@@ -510,11 +510,11 @@ int orfx_align_batch(orfx_ctx* c, const uint8_t* aa, const int64_t* off, int64_t
     return ORFX_OK;
 }
 
-int orfx_int_alu_peak(orfx_ctx* c, double* ops3) {
-    if (!c || !ops3) return fail(ORFX_E_INVALID, "null argument");
+int orfx_int_alu_peak(orfx_ctx* c, double* ops4) {
+    if (!c || !ops4) return fail(ORFX_E_INVALID, "null argument");
     CU(cudaSetDevice(c->device));
     std::string err;
-    int rc = int_alu_peak_device(c->stream, ops3, err);
+    int rc = int_alu_peak_device(c->stream, ops4, err);
     if (rc) return fail(rc, err);
     return ORFX_OK;
 }

@@ -1,0 +1,12 @@
+"""Development probe: one orfx_align_batch call on a C5-law sample (for ncu captures)."""
+import sys, os
+sys.path.insert(0, os.path.join(os.path.dirname(os.path.abspath(__file__)), ".."))
+import bench
+import orfanage_b200 as ob
+
+n = int(sys.argv[1]) if len(sys.argv) > 1 else 20000
+aa, off, pq, pt = bench.c5_pairs(n, 20261104)
+with ob.Context(ob.Params.make(), device=0) as cx:
+    cx.align(aa, off, pq[:64], pt[:64])
+    out, cells, ms = cx.align(aa, off, pq, pt)
+    print("pairs %d cells %.4g ms %.3f GCUPS %.1f" % (n, cells, ms, cells / ms / 1e6))
