@@ -18,6 +18,7 @@
 #include <algorithm>
 #include <numeric>
 #include <string>
+#include <type_traits>
 #include <vector>
 
 namespace orfx {
@@ -70,25 +71,27 @@ struct StripeIO {
 // Per-warp shared memory of the DP (dynamic shared memory, one WarpSmem per warp).
 struct WarpSmem {
     uint2 prof[24][32];     // query profile: prof[r][lane] = the lane's CPL scores against target residue r, one int8 each
-    int   t_ring[64];       // target residues of the current and the previous 32-row chunk
+    int   t_ring[128];      // target residues: previous, current and next 32-row chunk
     int2  in_ring[32];      // left edge {H(i, c_base-1), F(i, c_base)} of the current chunk (borders for the first stripe)
-    int2  out_ring[32];     // right edge of the rows lane 31 finished, until the chunk is stored
+    int2  out_ring[64];     // right edge of the rows lane 31 finished, until their chunk is stored
 };
 constexpr int PAD_SCORE8 = -128;    // score of the virtual columns right of the query's end: padded cells stay below
                                     // H(i, qlen-1) - (gapo+gape) per column as long as gapo+gape <= 64
 
 // One stripe of 32*CPL query columns over all target rows.  Lanes own CPL consecutive columns; lane l works on
 // target row (step - l), so only the lane's right edge (H, F) moves to the next lane (two shuffles per step).
-// The substitution scores of a step come as ONE shared-memory load of the lane's profile entry and are added to
-// the diagonal with dp4a (one-hot selector) on the FMA pipe, which leaves the ALU pipe to the max/add-max chain:
+// The substitution scores of a step come as ONE shared-memory load of the lane's profile entry (fetched one step
+// ahead) and are added to the diagonal with dp4a (one-hot selector) on the FMA pipe, which leaves the ALU pipe
+// to the max / add-max chain:
 //   x = d + s; h = max3(x, E, F); E' = max(E - e, h - (q+e)); F' = max(F - e, h - (q+e))      (4 ALU + 1 FMA per cell)
-template <int CPL, bool PIPE>
+// Steps go in blocks of 32; blocks in which every lane has a row run without per-step range checks.
+// LAST: the stripe holding column qlen-1 (tracks mqe / score, writes no right edge).
+template <int CPL, bool PIPE, bool LAST>
 __device__ __forceinline__ void dp_stripe(const int* __restrict__ s_mat, WarpSmem& ws, const uint8_t* __restrict__ q, const uint8_t* __restrict__ t,
-                                          int qlen, int tlen, int c_base, bool last_stripe, int gapoe, int gape, const StripeIO& io, AlnAcc& acc,
-                                          int lane) {
+                                          int qlen, int tlen, int c_base, int gapoe, int gape, const StripeIO& io, AlnAcc& acc, int lane) {
     static_assert(CPL <= 8, "a profile entry holds 8 scores");
     const int c0 = c_base + lane * CPL;
-    const bool first_stripe = io.h_in == nullptr, have_next = io.h_out != nullptr;
+    const bool first_stripe = io.h_in == nullptr;
     int hp[CPL], ee[CPL];
     {
         int qcode[CPL];
@@ -99,7 +102,7 @@ __device__ __forceinline__ void dp_stripe(const int* __restrict__ s_mat, WarpSme
             hp[k] = -(gapoe + gape * c);                 // H(-1, c)
             ee[k] = -(gapoe + gapoe + gape * c);         // E(0, c)
         }
-        __syncwarp();   // the previous stripe's profile is no longer read
+        __syncwarp();   // the previous stripe's profile and rings are no longer read
         for (int r = 0; r < 24; r++) {
             uint32_t lo = 0, hi = 0;
 #pragma unroll
@@ -109,43 +112,32 @@ __device__ __forceinline__ void dp_stripe(const int* __restrict__ s_mat, WarpSme
             }
             ws.prof[r][lane] = make_uint2(lo, hi);
         }
+        ws.t_ring[lane] = lane < tlen ? min((int)t[lane], 23) : 0;   // rows 0..31; every block loads the chunk after its own
     }
     // lane-local column of qlen-1 (last stripe only)
     const int jq_lane = (qlen - 1 - c_base) / CPL, jq = (qlen - 1 - c_base) % CPL;
     int diag = c0 == 0 ? 0 : -(gapoe + gape * (c0 - 1));   // H(i-1, c0-1), starts at row -1
     int h_out = 0, f_out = 0;                              // what this lane hands to lane+1
     int gmax = acc.gmax, mqe = acc.mqe, mte = acc.mte, score = acc.score;
+    uint2 sc = make_uint2(0, 0);                           // profile entry of this lane's next row
     const int n_steps = tlen + 31;
-    for (int s = 0; s < n_steps; s++) {
-        if ((s & 31) == 0) {   // next 32 target rows: residues and left edge into the rings
-            const int r = s + lane;
-            int2 e = make_int2(-(gapoe + gape * r), -(gapoe + gapoe + gape * r));   // first stripe: H(r, -1), F(r, 0)
-            if (!first_stripe) {
-                if (PIPE && s < tlen) {
-                    const unsigned long long need = io.wait_base + (unsigned long long)min(s + 32, tlen);
-                    if (lane == 0) while (*io.wait_flag < need) __nanosleep(20);
-                    __syncwarp();
-                }
-                e.x = r < tlen ? __ldcg(io.h_in + r) : 0;
-                e.y = r < tlen ? __ldcg(io.f_in + r) : 0;
-            }
-            __syncwarp();   // every lane is done with the rings' previous contents
-            ws.t_ring[r & 63] = r < tlen ? min((int)t[r], 23) : 0;
-            ws.in_ring[lane] = e;
-            __syncwarp();
-        }
+    int stored = 0;                                        // rows of the right edge already in global memory
+
+    auto step = [&](int s, auto full_tag) {
+        constexpr bool FULL = decltype(full_tag)::value;
         // values arriving from the left neighbour (computed in the previous step); lane 0 reads the edge ring
         int h_left = __shfl_up_sync(0xffffffffu, h_out, 1);
         int f_in = __shfl_up_sync(0xffffffffu, f_out, 1);
         const int2 edge = ws.in_ring[s & 31];
         if (lane == 0) { h_left = edge.x; f_in = edge.y; }
         const int i = s - lane;
-        if (i >= 0 && i < tlen) {
-            const uint2 sc = ws.prof[ws.t_ring[i & 63]][lane];
+        if (FULL || (i >= 0 && i < tlen)) {
+            const uint2 cur = sc;
+            sc = ws.prof[ws.t_ring[(i + 1) & 127]][lane];   // next step's scores: off the critical path
             int f = f_in, d = diag, h = 0, m0 = NEG_INF, m1 = NEG_INF;
 #pragma unroll
             for (int k = 0; k < CPL; k++) {
-                const int x = __dp4a((int)(k < 4 ? sc.x : sc.y), 1 << (8 * (k & 3)), d);
+                const int x = __dp4a((int)(k < 4 ? cur.x : cur.y), 1 << (8 * (k & 3)), d);
                 h = __vimax3_s32(x, ee[k], f);
                 d = hp[k];
                 hp[k] = h;
@@ -158,31 +150,58 @@ __device__ __forceinline__ void dp_stripe(const int* __restrict__ s_mat, WarpSme
             gmax = max(gmax, rowmax);
             diag = h_left;
             h_out = h; f_out = f;
-            if (i == tlen - 1) mte = max(mte, rowmax);
-            if (last_stripe && lane == jq_lane) {
+            if (!FULL && i == tlen - 1) mte = max(mte, rowmax);
+            if (LAST && lane == jq_lane) {
                 int hq = hp[0];
 #pragma unroll
                 for (int k = 1; k < CPL; k++) hq = jq == k ? hp[k] : hq;
                 mqe = max(mqe, hq);
                 if (i == tlen - 1) score = hq;
             }
+        } else if (i == -1) {
+            sc = ws.prof[ws.t_ring[0]][lane];   // the step before the lane's first row
         }
-        if (have_next) {
-            // lane 31 finished row s-31: park its edge, store 32 rows at a time, coalesced
-            const int row = s - 31;
-            if (row >= 0) {
-                if (lane == 31) ws.out_ring[row & 31] = make_int2(h_out, f_out);
-                if ((row & 31) == 31 || row == tlen - 1) {
+        if (!LAST && lane == 31 && (FULL || s >= 31)) ws.out_ring[(s - 31) & 63] = make_int2(h_out, f_out);
+    };
+
+    for (int s0 = 0; s0 < n_steps; s0 += 32) {
+        {   // next 32 target rows' left edge into the ring, the residues of the chunk after it
+            const int r = s0 + lane;
+            int2 e = make_int2(-(gapoe + gape * r), -(gapoe + gapoe + gape * r));   // first stripe: H(r, -1), F(r, 0)
+            if (!first_stripe) {
+                if (PIPE && s0 < tlen) {
+                    const unsigned long long need = io.wait_base + (unsigned long long)min(s0 + 32, tlen);
+                    if (lane == 0) while (*io.wait_flag < need) __nanosleep(20);
                     __syncwarp();
-                    const int r = (row & ~31) + lane;
-                    if (r <= row) { const int2 o = ws.out_ring[lane]; __stcg(io.h_out + r, o.x); __stcg(io.f_out + r, o.y); }
-                    if (PIPE) {
-                        __threadfence();
-                        __syncwarp();
-                        if (lane == 0) *io.post_flag = io.post_base + (unsigned long long)(row + 1);
-                    } else {
-                        __syncwarp();
-                    }
+                }
+                e.x = r < tlen ? __ldcg(io.h_in + r) : 0;
+                e.y = r < tlen ? __ldcg(io.f_in + r) : 0;
+            }
+            __syncwarp();   // every lane is done with the rings' previous contents
+            ws.t_ring[(r + 32) & 127] = r + 32 < tlen ? min((int)t[r + 32], 23) : 0;
+            ws.in_ring[lane] = e;
+            __syncwarp();
+            if (s0 == 0 && lane == 0) sc = ws.prof[ws.t_ring[0]][0];
+        }
+        if (s0 >= 32 && s0 + 33 <= tlen) {   // rows s - lane of the whole block lie in [1, tlen - 2]
+#pragma unroll 4
+            for (int u = 0; u < 32; u++) step(s0 + u, std::true_type{});
+        } else {
+            const int ue = min(32, n_steps - s0);
+            for (int u = 0; u < ue; u++) step(s0 + u, std::false_type{});
+        }
+        if (!LAST) {
+            // rows finished by lane 31 so far; store them 32 at a time, coalesced
+            const int done = min(tlen, s0 + 32 - 31);
+            while (stored + 32 <= done || (done == tlen && stored < tlen)) {
+                __syncwarp();
+                const int r = stored + lane;
+                if (r < min(stored + 32, tlen)) { const int2 o = ws.out_ring[r & 63]; __stcg(io.h_out + r, o.x); __stcg(io.f_out + r, o.y); }
+                stored += 32;
+                if (PIPE) {
+                    __threadfence();
+                    __syncwarp();
+                    if (lane == 0) *io.post_flag = io.post_base + (unsigned long long)min(stored, tlen);
                 }
             }
         }
@@ -210,7 +229,8 @@ __device__ __forceinline__ void pair_on_warp(const int* s_mat, WarpSmem& ws, con
         io.h_in = st > 0 ? hb : nullptr; io.f_in = st > 0 ? fb : nullptr;
         io.h_out = st < n_stripes - 1 ? hb : nullptr; io.f_out = st < n_stripes - 1 ? fb : nullptr;
         io.wait_flag = io.post_flag = nullptr; io.wait_base = io.post_base = 0;
-        dp_stripe<CPL, false>(s_mat, ws, q, t, qlen, tlen, st * 32 * CPL, st == n_stripes - 1, gapoe, gape, io, acc, lane);
+        if (st == n_stripes - 1) dp_stripe<CPL, false, true>(s_mat, ws, q, t, qlen, tlen, st * 32 * CPL, gapoe, gape, io, acc, lane);
+        else dp_stripe<CPL, false, false>(s_mat, ws, q, t, qlen, tlen, st * 32 * CPL, gapoe, gape, io, acc, lane);
         __syncwarp();
     }
 }
@@ -266,7 +286,8 @@ align_kernel(const uint8_t* __restrict__ aa, const int64_t* __restrict__ off, co
             io.h_out = st < n_stripes - 1 ? outb : nullptr; io.f_out = st < n_stripes - 1 ? outb + cta_stride : nullptr;
             io.wait_flag = &s_progress[(wib + ALN_WARPS - 1) % ALN_WARPS]; io.wait_base = (unsigned long long)(st - 1 + 1) * per;
             io.post_flag = &s_progress[wib]; io.post_base = (unsigned long long)(st + 1) * per;
-            dp_stripe<LONG_CPL, true>(s_mat, ws, q, t, qlen, tlen, st * 32 * LONG_CPL, st == n_stripes - 1, gapoe, gape, io, acc, lane);
+            if (st == n_stripes - 1) dp_stripe<LONG_CPL, true, true>(s_mat, ws, q, t, qlen, tlen, st * 32 * LONG_CPL, gapoe, gape, io, acc, lane);
+            else dp_stripe<LONG_CPL, true, false>(s_mat, ws, q, t, qlen, tlen, st * 32 * LONG_CPL, gapoe, gape, io, acc, lane);
             __syncwarp();
         }
         acc_reduce_warp(acc);

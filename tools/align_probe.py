@@ -6,6 +6,11 @@ import orfanage_b200 as ob
 
 n = int(sys.argv[1]) if len(sys.argv) > 1 else 20000
 aa, off, pq, pt = bench.c5_pairs(n, 20261104)
+if len(sys.argv) > 2:   # keep pairs shorter than this (steady-state captures without the titin tail)
+    import numpy as np
+    keep = np.nonzero((off[pq + 1] - off[pq]) < int(sys.argv[2]))[0]
+    pq, pt = pq[keep], pt[keep]
+    n = len(pq)
 with ob.Context(ob.Params.make(), device=0) as cx:
     cx.align(aa, off, pq[:64], pt[:64])
     out, cells, ms = cx.align(aa, off, pq, pt)
