@@ -398,6 +398,15 @@ def measured_peak():
     return 6650.0, "fallback (B200_PROFILING.md)"
 
 
+def profiled_traffic(kernel):
+    """DRAM bytes per launch of `kernel` from the committed ncu --set full capture of this workload (profiles/)."""
+    try:
+        t = json.load(open(os.path.join(ROOT, "profiles", "r01_traffic.json")))[kernel]
+        return t["dram_bytes_per_launch"], t["source"]
+    except Exception:
+        return None, None
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -423,6 +432,7 @@ def main():
     scan_ms = m["stage_ms"].get("codon_scan", 0.0) / K
     alg_bytes = ALG_BYTES_PER_NT * m["nt_sum"]
     achieved = alg_bytes / (scan_ms / 1e3) / 1e9 if scan_ms > 0 else 0.0
+    traffic, traffic_src = profiled_traffic("codon_scan_kernel")
     dominant = max(m["stage_ms"], key=lambda k: m["stage_ms"][k]) if m["stage_ms"] else None
     line = {
         "metric": "query transcripts/sec", "value": value, "unit": "transcripts/s", "n_gpus": m["world"], "steps": K,
@@ -443,7 +453,7 @@ def main():
         "gpu_launches": m["launches"],
         "clocks": m["clocks"],
         "roofline": {"bound": "hbm", "kernel": "codon_scan_kernel", "achieved": achieved, "peak": peak, "unit": "GB/s",
-                     "frac": achieved / peak if peak else None, "traffic": None, "peak_source": peak_src,
+                     "frac": achieved / peak if peak else None, "traffic": traffic, "traffic_source": traffic_src, "peak_source": peak_src,
                      "algorithmic_bytes_per_launch": alg_bytes, "kernel_ms": scan_ms,
                      "share_of_step": scan_ms / ms_per_step if ms_per_step else None, "dominant_stage": dominant},
         "stages_ms": {k: v / K for k, v in m["stage_ms"].items()},
