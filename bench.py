@@ -166,7 +166,7 @@ def reference_arm(args):
             "cpu_baseline": {"value": value, "unit": "transcripts/s", "cores": threads, "kind": "reference", "sample": sample},
             "e2e": {"value": value, "unit": "transcripts/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
-    print(json.dumps(line), flush=True)
+    emit(line)
 
 
 # ---- our arm -------------------------------------------------------------------------------------------
@@ -407,6 +407,24 @@ def profiled_traffic(kernel):
         return None, None
 
 
+def emit(line):
+    """The one JSON line goes to the real stdout; everything else that libraries print to fd 1 (NCCL's
+    version banner under torchrun, for one) was sent to stderr by quiet_stdout()."""
+    data = (json.dumps(line) + "\n").encode()
+    os.write(_REAL_STDOUT if _REAL_STDOUT is not None else 1, data)
+
+
+_REAL_STDOUT = None
+
+
+def quiet_stdout():
+    global _REAL_STDOUT
+    if _REAL_STDOUT is None:
+        sys.stdout.flush()
+        _REAL_STDOUT = os.dup(1)
+        os.dup2(2, 1)
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -417,6 +435,7 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--align-pairs", type=int, default=50000, help="protein pairs of the alignment leg (0 = skip; configs[4] = 1000000)")
     args = ap.parse_args()
+    quiet_stdout()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
     if args.impl == "reference":
         reference_arm(args)
@@ -466,7 +485,7 @@ def main():
         except Exception as e:   # the checker being absent must not hide the GPU number
             line["cpu_baseline"] = {"value": None, "unit": "transcripts/s", "cores": os.cpu_count(), "kind": "reference",
                                     "sample": "unavailable: %s" % e}
-    print(json.dumps(line), flush=True)
+    emit(line)
 
 
 if __name__ == "__main__":
