@@ -22,7 +22,7 @@
 extern "C" {
 #endif
 
-#define ORFX_ABI_VERSION 2
+#define ORFX_ABI_VERSION 3
 
 /* error codes */
 #define ORFX_OK            0
@@ -204,6 +204,21 @@ int64_t orfx_resident_query_nt(orfx_ctx* ctx);
  * stop/start says whether the codon starting at spliced position p (5'->3') is a stop / ATG.
  * Buffers must hold ceil(L/32) words, L = spliced length.  Returns L or a negative error. */
 int64_t orfx_get_masks(orfx_ctx* ctx, int32_t tx, uint32_t* stop_bits, uint32_t* start_bits, int64_t max_words);
+
+/* ---- template cleaning: --cleant [--rescue] -------------------------- */
+/* Replaces the per-transcript body of Transcriptome::clean_cds (Transcriptome.cpp:1063-1100): load_seq,
+ * optionally TX::rescue_cds(non_aug, 0, false, nullptr) (cpp:641-677), then "first codon is M (unless
+ * --non_aug), last codon is a stop, CDS length % 3 == 0".  The batch is a *cleaning batch*: every coding
+ * template of the bundles made by the first bundleup (cpp:1066) is packed as ORFX_TX_QUERY with segs = its
+ * exon chain and tx_cds_start / tx_cds_end = its CDS bounds after build_cds + correct_chain_len; anything
+ * else is ORFX_TX_SKIP.  Outputs are caller-owned arrays with one entry per ORFX_TX_QUERY transcript, in
+ * batch order.  Uses params.non_aug of the context; --overhang must be 0. */
+typedef struct orfx_clean_out {
+    uint8_t* keep;        /* 1: the CDS survives cleaning; 0: TX::remove_cds()                       */
+    int32_t* cds_start;   /* genomic CDS bounds after the (optional) rescue; 0 when keep == 0          */
+    int32_t* cds_end;
+} orfx_clean_out;
+int  orfx_clean_templates(orfx_ctx* ctx, const orfx_batch* batch, int rescue, orfx_clean_out* out, int64_t* n_out);
 
 /* ---- protein alignment (src/aln.hpp:27-41 with the build definition) ---- */
 typedef struct orfx_aln_out {

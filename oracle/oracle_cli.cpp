@@ -13,6 +13,7 @@ int orfx_oracle_submit(orfx_ctx*, const orfx_batch*);
 int orfx_oracle_wait(orfx_ctx*, orfx_results*);
 int orfx_oracle_release(orfx_ctx*);
 void orfx_oracle_destroy(orfx_ctx*);
+int orfx_oracle_clean_templates(orfx_ctx*, const orfx_batch*, int, orfx_clean_out*, int64_t*);
 }
 
 int main(int argc, char** argv) {
@@ -20,7 +21,7 @@ int main(int argc, char** argv) {
         orfx::Options opt;
         if (!orfx::parse_cli(argc, argv, opt)) return 0;
         opt.devices.assign(1, 0);
-        orfx::Backend be{orfx_oracle_create, orfx_oracle_submit, orfx_oracle_wait, orfx_oracle_release, orfx_oracle_destroy, orfx_oracle_last_error, nullptr, nullptr};
+        orfx::Backend be{orfx_oracle_create, orfx_oracle_submit, orfx_oracle_wait, orfx_oracle_release, orfx_oracle_destroy, orfx_oracle_last_error, nullptr, nullptr, orfx_oracle_clean_templates};
         return orfx::run_orfanage(opt, be);
     } catch (const std::exception& e) {
         fprintf(stderr, "Error: %s\n", e.what());

@@ -434,6 +434,17 @@ struct T {
         }
         return 0;
     }
+    int rescue_unguided(bool non_aug) {   // cpp:641-677 with t == nullptr (Transcriptome::clean_cds, cpp:1075)
+        if (seq.cds_nt_len() < 3) { remove_cds(); return 0; }
+        adjust_stop();
+        if (cds_len() == 0) { remove_cds(); return 0; }
+        extend_to_stop();
+        if (!non_aug) extend_to_start_search();
+        adjust_start();
+        cds_phase = 0;
+        assign_phase(cds, strand, 0);
+        return 1;
+    }
     int rescue(bool non_aug, const T& t) {   // cpp:641-677
         if (seq.cds_nt_len() < 3) { remove_cds(); return 0; }
         adjust_stop();
@@ -721,6 +732,44 @@ int orfx_oracle_wait(orfx_ctx* ctx, orfx_results* r) {
 
 int orfx_oracle_release(orfx_ctx* ctx) { (void)ctx; return ORFX_OK; }
 void orfx_oracle_destroy(orfx_ctx* ctx) { delete reinterpret_cast<Ctx*>(ctx); }
+
+// Template cleaning oracle: the per-transcript body of Transcriptome::clean_cds (Transcriptome.cpp:1063-1100)
+// on a cleaning batch (see orfx_clean_templates in include/orfx.h).
+int orfx_oracle_clean_templates(orfx_ctx* ctx, const orfx_batch* b, int rescue, orfx_clean_out* out, int64_t* n_out) {
+    Ctx* c = reinterpret_cast<Ctx*>(ctx);
+    if (!c || !b || !out) { g_err = "null argument"; return ORFX_E_INVALID; }
+    if (!b->seq && b->seq_bytes) { g_err = "cleaning needs the sequence"; return ORFX_E_INVALID; }
+    const bool non_aug = c->p.non_aug != 0;
+    int64_t k = 0;
+    for (int bi = 0; bi < b->n_bundles; bi++) {
+        BundleSeq bs(b, bi);
+        for (int x = b->bundle_tx_off[bi]; x < b->bundle_tx_off[bi + 1]; x++) {
+            if (b->tx_kind[x] != ORFX_TX_QUERY) continue;
+            T t = load_tx(b, x);
+            t.bn = &bs.bn;
+            t.cds_start = b->tx_cds_start[x]; t.cds_end = b->tx_cds_end[x]; t.cds_phase = 0;
+            t.build_cds();   // the chain the template carries at this point: exons clipped to the CDS bounds
+            bool keep = !t.cds.empty();
+            if (keep) {
+                t.load_seq();
+                bool alive = true;
+                if (rescue) alive = t.rescue_unguided(non_aug) != 0;
+                if (!alive || t.seq.aa.empty()) keep = false;   // rescue removed the CDS (the reference then drops it, cpp:1083-1089)
+                else {
+                    char start_codon = t.seq.aa[0], stop_codon = t.seq.aa[t.seq.aa.size() - 1];
+                    if ((start_codon != 'M' && !non_aug) || stop_codon != '.') keep = false;
+                    else if (t.cds_len() % 3 != 0) keep = false;
+                }
+            }
+            out->keep[k] = keep ? 1 : 0;
+            out->cds_start[k] = keep ? t.cds_start : 0;
+            out->cds_end[k] = keep ? t.cds_end : 0;
+            k++;
+        }
+    }
+    if (n_out) *n_out = k;
+    return ORFX_OK;
+}
 
 // Codon-scan oracle: stop / ATG masks of one spliced transcript, bit p = codon starting at spliced
 // position p (5'->3').  Follows SEQ::translate / find_inframe_codon (common.hpp:420-450, 477-495):

@@ -121,6 +121,10 @@ def _view(ptr, n, dtype):
     return np.frombuffer(buf, dtype=dtype, count=int(n))
 
 
+class _CleanOut(C.Structure):
+    _fields_ = [("keep", C.c_void_p), ("cds_start", C.c_void_p), ("cds_end", C.c_void_p)]
+
+
 class Batch:
     """A packed set of locus bundles (orfx_batch).  Holds numpy arrays (or views of library-owned
     memory) and the ctypes struct that points at them."""
@@ -418,6 +422,23 @@ class Context:
         self._check(self.lib.orfx_align_batch(self.handle, aa.ctypes.data, off.ctypes.data, len(off) - 1, pq.ctypes.data,
                                               pt.ctypes.data, n, gapo, gape, C.byref(o), C.byref(cells), C.byref(ms)))
         return {k: v[:n] for k, v in out.items()}, cells.value, ms.value
+
+    def clean(self, batch, rescue=False):
+        """orfx_clean_templates on a cleaning batch: returns (keep u8, cds_start i32, cds_end i32), one entry per
+        ORFX_TX_QUERY transcript in batch order."""
+        n = batch.n_queries
+        keep = np.zeros(max(n, 1), dtype=np.uint8)
+        cs = np.zeros(max(n, 1), dtype=np.int32)
+        ce = np.zeros(max(n, 1), dtype=np.int32)
+        out = _CleanOut(keep.ctypes.data, cs.ctypes.data, ce.ctypes.data)
+        n_out = C.c_int64(0)
+        f = self._f("clean_templates")
+        f.restype = C.c_int
+        f.argtypes = [C.c_void_p, C.POINTER(_Batch), C.c_int, C.POINTER(_CleanOut), C.POINTER(C.c_int64)]
+        self._keep = batch
+        self._check(f(self.handle, C.byref(batch.struct), 1 if rescue else 0, C.byref(out), C.byref(n_out)))
+        assert n_out.value == n
+        return keep[:n], cs[:n], ce[:n]
 
     def int_alu_peak(self):
         """orfx_int_alu_peak: measured integer issue rates of this GPU, operations/s."""

@@ -102,6 +102,7 @@ public:
     void remove_non_coding();         // cpp:1146-1150
     size_t deduplicate(bool use_id);  // cpp:1124-1140
     size_t bundleup(bool use_id, uint32_t overhang);   // cpp:920-1032
+    size_t clean_short_orfs(int minlen);   // cpp:1052-1061
 private:
     std::map<std::string, int> seqids_;
 };
@@ -150,10 +151,12 @@ struct PackedBatch {
     void reset();
     orfx_batch view() const;
 };
-// Packs the listed bundles (each must hold a template and a query).
+// Packs the listed bundles (each must hold a template and a query).  clean_mode = true builds a
+// *cleaning batch* instead (orfx_clean_templates in include/orfx.h): every coding transcript with a CDS
+// chain is packed as ORFX_TX_QUERY with its exon chain and CDS bounds, everything else as ORFX_TX_SKIP.
 void pack_bundles(const Transcriptome& tr, const std::vector<int>& bundle_ids, bool keep_all_cds,
                   const std::map<std::string, int>& tid_classes, PackedBatch& out,
-                  void* (*alloc)(size_t) = nullptr, void (*dealloc)(void*) = nullptr, bool islands = true);
+                  void* (*alloc)(size_t) = nullptr, void (*dealloc)(void*) = nullptr, bool islands = true, bool clean_mode = false);
 void build_tid_classes(const Transcriptome& tr, std::map<std::string, int>& out);
 // greedy longest-processing-time split of active bundles over n shards
 void shard_bundles(const Transcriptome& tr, const std::vector<int>& active, int n, std::vector<std::vector<int>>& shards);
@@ -168,10 +171,13 @@ struct Backend {
     const char* (*last_error)();
     void* (*host_alloc)(size_t);      // optional (may be NULL): pinned host memory for the packed arrays
     void (*host_free)(void*);
+    // optional (may be NULL): template cleaning, --cleant / --rescue (orfx_clean_templates)
+    int (*clean)(orfx_ctx*, const orfx_batch*, int, orfx_clean_out*, int64_t*);
 };
 
 // load + template preparation + bundling (orfanage.cpp:313-367)
-void prepare_transcriptome(const Options& opt, Fasta& fasta, Transcriptome& tr, bool verbose);
+// `be` is needed only for --cleant (Transcriptome::clean_cds runs behind Backend::clean)
+void prepare_transcriptome(const Options& opt, Fasta& fasta, Transcriptome& tr, bool verbose, const Backend* be = nullptr);
 // replaces run() (orfanage.cpp:307-822): prepares, bundles, evaluates through `be`, writes outputs
 int run_orfanage(const Options& opt, const Backend& be);
 

@@ -49,11 +49,15 @@ void build_tid_classes(const Transcriptome& tr, std::map<std::string, int>& out)
 namespace {
 // Islands of one bundle: the union of its query exons (what the path reads from the genome when
 // --overhang is 0).  Returns the merged intervals, ascending.
-void bundle_islands(const Transcriptome& tr, const Bundle& b, bool keep_all_cds, std::vector<std::pair<int, int>>& isl) {
+inline uint8_t tx_kind_of(const Tx& t, bool keep_all_cds, bool clean_mode) {
+    if (clean_mode) return (t.is_coding && !t.cds.empty()) ? ORFX_TX_QUERY : ORFX_TX_SKIP;
+    return t.is_templ ? ORFX_TX_TEMPLATE : ((keep_all_cds && t.is_coding) ? ORFX_TX_SKIP : ORFX_TX_QUERY);
+}
+void bundle_islands(const Transcriptome& tr, const Bundle& b, bool keep_all_cds, bool clean_mode, std::vector<std::pair<int, int>>& isl) {
     isl.clear();
     for (int i = 0; i < b.count; i++) {
         const Tx& t = tr.txs[b.first + i];
-        if (t.is_templ || (keep_all_cds && t.is_coding)) continue;
+        if (tx_kind_of(t, keep_all_cds, clean_mode) != ORFX_TX_QUERY) continue;
         for (const Seg& s : t.exons) isl.emplace_back(s.s, s.e);
     }
     std::sort(isl.begin(), isl.end());
@@ -70,7 +74,7 @@ void bundle_islands(const Transcriptome& tr, const Bundle& b, bool keep_all_cds,
 // copied by several threads.  islands = true uploads only the bases under query exons.
 void pack_bundles(const Transcriptome& tr, const std::vector<int>& bundle_ids, bool keep_all_cds,
                   const std::map<std::string, int>& tid_classes, PackedBatch& out,
-                  void* (*alloc)(size_t), void (*dealloc)(void*), bool islands) {
+                  void* (*alloc)(size_t), void (*dealloc)(void*), bool islands, bool clean_mode) {
     out.reset();
     out.bundle_ids = bundle_ids;
     const size_t nb = bundle_ids.size();
@@ -83,13 +87,13 @@ void pack_bundles(const Transcriptome& tr, const std::vector<int>& bundle_ids, b
         const Bundle& b = tr.bundles[bundle_ids[j]];
         if (has_seq) {
             if (islands) {
-                bundle_islands(tr, b, keep_all_cds, isl);
+                bundle_islands(tr, b, keep_all_cds, clean_mode, isl);
                 for (auto& iv : isl) bundle_bytes[j] += iv.second - iv.first + 1;
             } else bundle_bytes[j] = b.bend - b.bstart + 1;
             total_seq += (size_t)bundle_bytes[j];
         }
         total_tx += (size_t)b.count;
-        for (int i = 0; i < b.count; i++) { const Tx& t = tr.txs[b.first + i]; total_segs += t.is_templ ? t.cds.size() : t.exons.size(); }
+        for (int i = 0; i < b.count; i++) { const Tx& t = tr.txs[b.first + i]; total_segs += (t.is_templ && !clean_mode) ? t.cds.size() : t.exons.size(); }
     }
     if (total_tx > (size_t)INT32_MAX || total_segs > (size_t)INT32_MAX) throw std::runtime_error("batch too large for 32-bit transcript / segment indices: shard it");
     auto up = [](size_t x) { return (x + 255) & ~(size_t)255; };
@@ -124,15 +128,16 @@ void pack_bundles(const Transcriptome& tr, const std::vector<int>& bundle_ids, b
         for (int i = 0; i < b.count; i++, x++) {
             const Tx& t = tr.txs[b.first + i];
             out.tx_global[(size_t)x] = b.first + i;
-            const uint8_t kind = t.is_templ ? ORFX_TX_TEMPLATE : ((keep_all_cds && t.is_coding) ? ORFX_TX_SKIP : ORFX_TX_QUERY);
+            const uint8_t kind = tx_kind_of(t, keep_all_cds, clean_mode);
+            const bool as_templ = t.is_templ && !clean_mode;
             if (kind == ORFX_TX_QUERY) out.n_queries++;
             out.tx_kind[x] = kind;
             out.tx_strand[x] = (uint8_t)t.strand;
-            const Chain& c = t.is_templ ? t.cds : t.exons;
-            for (const Seg& s : c) { out.segs[sg] = orfx_seg{s.s, s.e}; out.seg_phase[sg] = t.is_templ ? s.phase : 0; sg++; }
+            const Chain& c = as_templ ? t.cds : t.exons;
+            for (const Seg& s : c) { out.segs[sg] = orfx_seg{s.s, s.e}; out.seg_phase[sg] = as_templ ? s.phase : 0; sg++; }
             out.tx_seg_off[x + 1] = sg;
-            out.tx_cds_start[x] = t.is_templ ? t.cds_start : 0;
-            out.tx_cds_end[x] = t.is_templ ? t.cds_end : 0;
+            out.tx_cds_start[x] = (as_templ || (clean_mode && kind == ORFX_TX_QUERY)) ? t.cds_start : 0;
+            out.tx_cds_end[x] = (as_templ || (clean_mode && kind == ORFX_TX_QUERY)) ? t.cds_end : 0;
             out.tx_tid_class[x] = tid_classes.at(t.tid);
         }
         out.bundle_tx_off[j + 1] = x;
@@ -149,7 +154,7 @@ void pack_bundles(const Transcriptome& tr, const std::vector<int>& bundle_ids, b
                 const char* src = chrom[(size_t)b.seqid]->data();
                 uint8_t* dst = out.seq + out.seq_off[j];
                 if (!islands) { memcpy(dst, src + (b.bstart - 1), (size_t)(b.bend - b.bstart + 1)); continue; }
-                bundle_islands(tr, b, keep_all_cds, il);
+                bundle_islands(tr, b, keep_all_cds, clean_mode, il);
                 il_off.resize(il.size());
                 int32_t o = 0;
                 for (size_t k = 0; k < il.size(); k++) {
@@ -257,9 +262,46 @@ struct Shard {
 }  // namespace
 
 // Everything upstream of the bundle loop (orfanage.cpp:313-367): load, prepare templates, bundle.
-void prepare_transcriptome(const Options& opt, Fasta& fasta, Transcriptome& tr, bool verbose) {
+// Transcriptome::clean_cds (Transcriptome.cpp:1063-1100): bundle the templates, then per coding template
+// load_seq (+ rescue_cds) and the start / stop / length checks — that per-transcript body runs behind
+// Backend::clean on the device; the host applies the verdicts (TX::remove_cds or the rescued CDS bounds).
+static size_t clean_cds(const Options& opt, Transcriptome& tr, const Backend& be) {
+    if (!be.clean) throw std::runtime_error("--cleant needs a backend with template cleaning (orfx_clean_templates)");
+    tr.bundleup(opt.use_id, (uint32_t)opt.overhang);
+    std::vector<int> ids;
+    for (int bi = 0; bi < (int)tr.bundles.size(); bi++) ids.push_back(bi);
+    std::map<std::string, int> tid_classes;
+    build_tid_classes(tr, tid_classes);
+    PackedBatch pb;
+    pack_bundles(tr, ids, false, tid_classes, pb, be.host_alloc, be.host_free, true, true);
+    orfx_params params;
+    fill_params(opt, false, params);
+    orfx_ctx* ctx = nullptr;
+    if (be.create(&ctx, opt.devices.empty() ? 0 : opt.devices[0], &params)) throw std::runtime_error(std::string("template cleaning: ") + be.last_error());
+    std::vector<uint8_t> keep((size_t)pb.n_queries + 1);
+    std::vector<int32_t> cs((size_t)pb.n_queries + 1), ce((size_t)pb.n_queries + 1);
+    orfx_clean_out out{keep.data(), cs.data(), ce.data()};
+    int64_t n = 0;
+    const orfx_batch view = pb.view();
+    const int rc = be.clean(ctx, &view, opt.rescue ? 1 : 0, &out, &n);
+    const std::string err = rc ? be.last_error() : "";
+    be.destroy(ctx);
+    if (rc) throw std::runtime_error("template cleaning: " + err);
+    if (n != pb.n_queries) throw std::runtime_error("template cleaning: result count mismatch");
+    size_t dirty = 0, k = 0;
+    for (int32_t x = 0; x < pb.n_tx; x++) {
+        if (pb.tx_kind[x] != ORFX_TX_QUERY) continue;
+        Tx& t = tr.txs[(size_t)pb.tx_global[(size_t)x]];
+        if (!keep[k]) { t.remove_cds(); dirty++; }
+        else if (cs[k] != t.cds_start || ce[k] != t.cds_end) { t.cds_start = cs[k]; t.cds_end = ce[k]; t.cds_phase = 0; t.build_cds(); }
+        k++;
+    }
+    return dirty;
+}
+
+void prepare_transcriptome(const Options& opt, Fasta& fasta, Transcriptome& tr, bool verbose, const Backend* be) {
     if (opt.overhang != 0) throw std::runtime_error("--overhang is not supported by this build (SURVEY.md §8f row 2)");
-    if (opt.clean_templ || opt.rescue) throw std::runtime_error("--cleant / --rescue are not supported by this build (SURVEY.md §8f row 1)");
+    if (opt.clean_templ && !be) throw std::runtime_error("--cleant needs a compute backend");
     auto say = [&](const char* m) { if (verbose) fprintf(stderr, "%s\n", m); };
     say("loading reference genome");
     if (!opt.reference.empty()) {
@@ -271,8 +313,10 @@ void prepare_transcriptome(const Options& opt, Fasta& fasta, Transcriptome& tr, 
     for (const std::string& k : opt.templates) tr.add(k, true, true);
     tr.build_cds_chains();
     if (opt.clean_templ || !opt.reference.empty()) tr.correct_chain_len();
+    if (opt.clean_templ) tr.clean_short_orfs(opt.minlen);
     say("sorting reference transcriptome");
     tr.sort(false);
+    if (opt.clean_templ) clean_cds(opt, tr, *be);
     tr.set_cds_as_exons();
     tr.remove_non_coding();
     tr.sort(false);
@@ -289,7 +333,7 @@ int run_orfanage(const Options& opt, const Backend& be) {
     auto t0 = clk::now();
     Fasta fasta;
     Transcriptome tr;
-    prepare_transcriptome(opt, fasta, tr, true);
+    prepare_transcriptome(opt, fasta, tr, true, &be);
     auto t1 = clk::now();
 
     FILE* gtf = fopen(opt.output.c_str(), "w");

@@ -380,6 +380,12 @@ size_t Transcriptome::deduplicate(bool use_id) {
     return before - txs.size();
 }
 
+size_t Transcriptome::clean_short_orfs(int minlen) {
+    size_t n = 0;
+    for (Tx& t : txs) if (chain_len(t.cds) <= minlen) { t.remove_cds(); n++; }
+    return n;
+}
+
 size_t Transcriptome::bundleup(bool use_id, uint32_t overhang) {
     sort(use_id);
     if (fasta) {

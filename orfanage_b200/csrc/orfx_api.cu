@@ -23,6 +23,7 @@ int launch_heavy_fill_rescue(const DevBatch& B, const DevRows& R, const orfx_par
 int launch_select(const DevBatch& B, const DevRows& R, const orfx_params& P, int n_queries, orfx_best* best_out, int32_t* ord_scratch, cudaStream_t s);
 void launch_codon_scan(const DevBatch& B, int64_t n_tiles, int n_sm, cudaStream_t stream);
 int launch_base_planes(const DevBatch& B, cudaStream_t stream);
+int launch_clean_templates(const DevBatch& B, int n_queries, int rescue, int non_aug, uint8_t* keep, int32_t* out_start, int32_t* out_end, cudaStream_t s);
 int align_batch_device(int device, cudaStream_t stream, const uint8_t* aa, const int64_t* off, int64_t n_seq, const int32_t* pair_q,
                        const int32_t* pair_t, int64_t n_pairs, int gapo, int gape, orfx_aln_out* out, double* cells, float* ms, std::string& err);
 int int_alu_peak_device(cudaStream_t stream, double* ops, std::string& err);
@@ -91,6 +92,7 @@ struct orfx_ctx {
     DBuf d_seg_cum, d_tx_len, d_tx_bundle, d_mask_off, d_tile_off, d_q_off, d_q_list, d_row_off, d_tile_tx, d_stop, d_start;
     DBuf d_need, d_planes, d_heavy, d_heavy_count;
     DBuf d_cnt_q, d_cnt_words, d_cnt_tiles, d_cnt_rows, d_scan_tmp, d_ord;
+    DBuf d_clean_keep, d_clean_s, d_clean_e;
     // rows
     DBuf r_i32[16], r_f32[3], r_u8[3], r_order, d_best;
     HBuf h_totals, h_best, h_i32[16], h_f32[3], h_u8[3], h_order;
@@ -406,7 +408,7 @@ void orfx_destroy(orfx_ctx* c) {
     DBuf* d[] = {&c->d_sso, &c->d_seq, &c->d_seq_off, &c->d_bstart, &c->d_btx_off, &c->d_kind, &c->d_strand, &c->d_seg_off, &c->d_cds_s, &c->d_cds_e, &c->d_tid,
                  &c->d_segs, &c->d_phase, &c->d_seg_cum, &c->d_tx_len, &c->d_tx_bundle, &c->d_mask_off, &c->d_tile_off, &c->d_q_off, &c->d_q_list,
                  &c->d_row_off, &c->d_tile_tx, &c->d_stop, &c->d_start, &c->d_need, &c->d_planes, &c->d_heavy, &c->d_heavy_count, &c->d_cnt_q, &c->d_cnt_words, &c->d_cnt_tiles, &c->d_cnt_rows, &c->d_scan_tmp,
-                 &c->d_ord, &c->r_order, &c->d_best};
+                 &c->d_ord, &c->r_order, &c->d_best, &c->d_clean_keep, &c->d_clean_s, &c->d_clean_e};
     for (DBuf* b : d) b->free_();
     for (auto& b : c->r_i32) b.free_();
     for (auto& b : c->r_f32) b.free_();
@@ -497,6 +499,50 @@ int64_t orfx_get_masks(orfx_ctx* c, int32_t tx, uint32_t* stop_bits, uint32_t* s
     if (cudaMemcpy(stop_bits, c->B.stop_mask + off[0], (size_t)words * 4, cudaMemcpyDeviceToHost) != cudaSuccess) return fail(ORFX_E_CUDA, "copy stop mask");
     if (cudaMemcpy(start_bits, c->B.start_mask + off[0], (size_t)words * 4, cudaMemcpyDeviceToHost) != cudaSuccess) return fail(ORFX_E_CUDA, "copy start mask");
     return L;
+}
+
+int orfx_clean_templates(orfx_ctx* c, const orfx_batch* batch, int rescue, orfx_clean_out* out, int64_t* n_out) {
+    if (!c || !out || !out->keep || !out->cds_start || !out->cds_end) return fail(ORFX_E_INVALID, "null argument");
+    if (!c->P.has_reference) return fail(ORFX_E_INVALID, "template cleaning needs a reference genome (params.has_reference)");
+    CU(cudaSetDevice(c->device));
+    int rc = upload_batch(c, batch);
+    if (rc) return rc;
+    cudaStream_t s = c->stream;
+    DevBatch& B = c->B;
+    c->n_launches = 0;
+    if (n_out) *n_out = 0;
+    if (B.n_tx == 0) return ORFX_OK;
+    c->n_launches += launch_prep(B, c->d_cnt_q.as<int64_t>(), c->d_cnt_words.as<int64_t>(), c->d_cnt_tiles.as<int64_t>(), c->d_scan_tmp.as<int64_t>(),
+                                 c->d_heavy.as<int32_t>(), c->d_heavy_count.as<unsigned>(), s);
+    int64_t* tot = c->h_totals.as<int64_t>();
+    CU(cudaMemcpyAsync(tot + 0, B.tx_q_off + B.n_tx, 8, cudaMemcpyDeviceToHost, s));
+    CU(cudaMemcpyAsync(tot + 1, B.tx_mask_off + B.n_tx, 8, cudaMemcpyDeviceToHost, s));
+    CU(cudaMemcpyAsync(tot + 2, B.tx_tile_off + B.n_tx, 8, cudaMemcpyDeviceToHost, s));
+    CU(cudaStreamSynchronize(s));
+    const int64_t nq = tot[0], words = tot[1], tiles = tot[2];
+    CU(c->d_tile_tx.ensure((size_t)tiles * 4 + 4));
+    CU(c->d_stop.ensure((size_t)words * 4 + 16));
+    CU(c->d_start.ensure((size_t)words * 4 + 16));
+    B.tile_tx = c->d_tile_tx.as<int32_t>(); B.stop_mask = c->d_stop.as<uint32_t>(); B.start_mask = c->d_start.as<uint32_t>();
+    CU(c->d_clean_keep.ensure((size_t)nq + 4)); CU(c->d_clean_s.ensure((size_t)nq * 4 + 4)); CU(c->d_clean_e.ensure((size_t)nq * 4 + 4));
+    c->n_launches += launch_fill_tiles(B, s);
+    c->n_launches += launch_base_planes(B, s);
+    launch_codon_scan(B, tiles, c->n_sm, s);
+    if (tiles > 0) c->n_launches++;
+    c->n_launches += launch_clean_templates(B, (int)nq, rescue, c->P.non_aug, c->d_clean_keep.as<uint8_t>(), c->d_clean_s.as<int32_t>(),
+                                            c->d_clean_e.as<int32_t>(), s);
+    CU(cudaGetLastError());
+    if (nq) {
+        CU(cudaMemcpyAsync(out->keep, c->d_clean_keep.p, (size_t)nq, cudaMemcpyDeviceToHost, s));
+        CU(cudaMemcpyAsync(out->cds_start, c->d_clean_s.p, (size_t)nq * 4, cudaMemcpyDeviceToHost, s));
+        CU(cudaMemcpyAsync(out->cds_end, c->d_clean_e.p, (size_t)nq * 4, cudaMemcpyDeviceToHost, s));
+    }
+    CU(cudaStreamSynchronize(s));
+    CU(cudaGetLastError());
+    c->n_queries = nq; c->n_words = words; c->n_tiles = tiles; c->n_rows = 0;
+    c->have_results = false;
+    if (n_out) *n_out = nq;
+    return ORFX_OK;
 }
 
 int orfx_align_batch(orfx_ctx* c, const uint8_t* aa, const int64_t* off, int64_t n_seq, const int32_t* pair_q, const int32_t* pair_t,

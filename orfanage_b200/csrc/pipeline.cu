@@ -675,6 +675,61 @@ int launch_heavy_fill_rescue(const DevBatch& B, const DevRows& R, const orfx_par
     return 1;
 }
 
+// ------------------------------------------------------------------------------------------------
+// template cleaning (--cleant [--rescue]): Transcriptome::clean_cds, Transcriptome.cpp:1063-1100
+// ------------------------------------------------------------------------------------------------
+// One thread per transcript of a cleaning batch (every transcript there is a coding template packed as
+// ORFX_TX_QUERY: segs = its exon chain, tx_cds_start / tx_cds_end = its CDS bounds after build_cds +
+// correct_chain_len).  The checks of clean_cds and, with `rescue`, TX::rescue_cds(non_aug, 0, false,
+// nullptr) (cpp:641-677: adjust_stop, extend_to_stop, unguided extend_to_start, adjust_start) are bit
+// scans over the transcript's codon-scan masks, as in process_row.
+__global__ void __launch_bounds__(128) clean_templates_kernel(DevBatch B, int n_queries, int rescue, int non_aug, uint8_t* keep, int32_t* out_start,
+                                                              int32_t* out_end) {
+    const int qi = blockIdx.x * blockDim.x + threadIdx.x;
+    if (qi >= n_queries) return;
+    const int qx = B.q_list[qi];
+    const TxView q = tx_view(B, qx);
+    const int gs = B.tx_cds_start[qx], ge = B.tx_cds_end[qx];
+    int ok = 0, cs = 0, ce = 0;
+    do {
+        if (q.n == 0 || (gs == 0 && ge == 0)) break;
+        const int a = g2t(q, q.plus ? gs : ge), b = g2t(q, q.plus ? ge : gs);
+        if (a < 0 || b < 0 || b < a) break;                    // CDS bounds outside the exon chain: not a usable template
+        const uint32_t* stopm = B.stop_mask + B.tx_mask_off[qx];
+        const uint32_t* startm = B.start_mask + B.tx_mask_off[qx];
+        int start = a, e = b;
+        if (b - a + 1 < 3) break;                              // rescue_cds: cds_nt_len < 3; no rescue: no codon to test
+        if (rescue) {
+            const int p0 = next_inframe(stopm, a, q.L);        // adjust_stop + extend_to_stop
+            if (p0 == a) break;                                // nothing left before the first stop: CDS removed
+            if (p0 >= 0) e = p0 + 2;
+            if (!non_aug && !mask_bit(startm, a) && a >= 3) {  // extend_to_start(-1, ...): nearest upstream ATG before a stop
+                const int prev_stop = prev_inframe(stopm, a - 3);
+                const int m = prev_inframe(startm, a - 3);
+                if (m >= 0 && m > prev_stop) start = m;
+            }
+            if (!mask_bit(startm, start)) {                    // adjust_start: first ATG inside the CDS
+                const int m = next_inframe(startm, start, q.L);
+                if (m >= 0 && m + 2 <= e) start = m;
+            }
+        }
+        const int naa = (e - start + 1) / 3;
+        const int last = start + 3 * (naa - 1);
+        if (!non_aug && !mask_bit(startm, start)) break;       // start codon must be M unless --non_aug
+        if (!mask_bit(stopm, last)) break;                     // last codon must be a stop
+        if ((e - start + 1) % 3 != 0) break;
+        const int g0 = t2g(q, start), g1 = t2g(q, e);
+        cs = min(g0, g1); ce = max(g0, g1);
+        ok = 1;
+    } while (false);
+    keep[qi] = (uint8_t)ok; out_start[qi] = cs; out_end[qi] = ce;
+}
+int launch_clean_templates(const DevBatch& B, int n_queries, int rescue, int non_aug, uint8_t* keep, int32_t* out_start, int32_t* out_end, cudaStream_t s) {
+    if (n_queries == 0) return 0;
+    clean_templates_kernel<<<(n_queries + 127) / 128, 128, 0, s>>>(B, n_queries, rescue, non_aug, keep, out_start, out_end);
+    return 1;
+}
+
 int launch_rescue_score(const DevBatch& B, const DevRows& R, const orfx_params& P, cudaStream_t s) {
     if (R.n_rows == 0) return 0;
     rescue_score_kernel<<<(unsigned)((R.n_rows + 127) / 128), 128, 0, s>>>(B, R, P);

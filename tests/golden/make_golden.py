@@ -47,6 +47,8 @@ SYNTH_RUNS = [
                      "--ilpi", "60", "--mlpi", "70", "--minlen", "300"]),
     ("nonaug_longest", ["--reference", "genome.fa", "--query", "query.gtf", "--mode", "LONGEST", "--non_aug"]),
     ("noref", ["--query", "query.gtf", "--mode", "LONGEST_MATCH,BEST"]),
+    ("cleant", ["--reference", "genome.fa", "--query", "query.gtf", "--cleant", "--mode", "LONGEST_MATCH,BEST"]),
+    ("cleant_rescue", ["--reference", "genome.fa", "--query", "query.gtf", "--cleant", "--rescue"]),
 ]
 C1_SEED = 20261104
 

@@ -33,6 +33,10 @@ for seed in $SEEDS; do
   run $d --query query.gtf --mode LONGEST_MATCH,BEST
   run $d --query query.gtf --mode ALL --lpi 80
   run $d --reference genome.fa --query query.gtf --use_id
+  run $d --reference genome.fa --query query.gtf --cleant
+  run $d --reference genome.fa --query query.gtf --cleant --rescue --mode LONGEST_MATCH,BEST
+  run $d --reference genome.fa --query query.gtf --cleant --rescue --non_aug --mode BEST
+  run $d --reference genome.fa --query query.gtf --cleant --minlen 450 --use_id
   TPL="template1.gtf"
   run $d --reference genome.fa --query template2.gtf --keep_all_cds
   run $d --reference genome.fa --query template3.gtf --keep_cds_if_not_found --mode FIRST

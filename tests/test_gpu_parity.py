@@ -155,3 +155,80 @@ def test_empty_and_degenerate_batches(gpu, oracle_lib):
         want = ox.run(b)
     assert_same_results(got, want, "degenerate")
     assert got.n_queries == 2
+
+
+def cleaning_batch(batch, best, rng):
+    """A cleaning batch (orfx_clean_templates) made from the queries of a packed batch: every query keeps its exon
+    chain and islands and gets CDS bounds derived from the ORF the path chose for it, perturbed so that all the
+    branches of Transcriptome::clean_cds / TX::rescue_cds(t = nullptr) are taken: intact ORFs, 5' ends moved
+    downstream / upstream in and out of frame, 3' ends cut short or pushed past the stop.  Templates become SKIP."""
+    a = {k: v.copy() for k, v in batch.arrays.items()}
+    kind = a["tx_kind"]
+    a["tx_kind"] = np.where(kind == 0, 0, 2).astype(np.uint8)
+    segs, so = a["segs"], a["tx_seg_off"]
+    cs = np.zeros(len(kind), dtype=np.int32)
+    ce = np.zeros(len(kind), dtype=np.int32)
+
+    def spliced(tx):
+        return np.concatenate([np.arange(s, e + 1) for s, e in segs[so[tx]:so[tx + 1]]])
+
+    for b in best:
+        tx = int(b["q_tx"])
+        g = spliced(tx)
+        plus = a["tx_strand"][tx] == ord("+")
+        if b["t_tx"] < 0:
+            lo, hi = 0, min(len(g) - 1, 3 * int(rng.integers(1, 40)) - 1)
+        else:
+            lo, hi = int(np.searchsorted(g, b["cds_start"])), int(np.searchsorted(g, b["cds_end"]))
+        t5, t3 = (lo, hi) if plus else (len(g) - 1 - hi, len(g) - 1 - lo)   # transcript coordinates
+        v = int(rng.integers(0, 8))
+        if v == 1:
+            t5 += 3 * int(rng.integers(1, 30))
+        elif v == 2:
+            t5 -= 3 * int(rng.integers(1, 30))
+        elif v == 3:
+            t5 += int(rng.integers(1, 3))
+        elif v == 4:
+            t3 -= 3 * int(rng.integers(1, 30))
+        elif v == 5:
+            t3 += 3 * int(rng.integers(1, 30))
+        elif v == 6:
+            t5 += 3 * int(rng.integers(1, 10)); t3 -= 3 * int(rng.integers(1, 10))
+        t5 = max(0, min(t5, len(g) - 3))
+        t3 = max(t5 + 2, min(t3, len(g) - 1))
+        t3 = t5 + ((t3 - t5 + 1) // 3) * 3 - 1    # correct_chain_len: the CDS the templates carry is a multiple of 3
+        u5, u3 = (t5, t3) if plus else (len(g) - 1 - t5, len(g) - 1 - t3)
+        cs[tx], ce[tx] = min(g[u5], g[u3]), max(g[u5], g[u3])
+    a["tx_cds_start"], a["tx_cds_end"] = cs, ce
+    return ob.Batch(**a)
+
+
+@pytest.mark.parametrize("seed,kw", [(31, dict(loci=80)), (32, dict(loci=60, titin=0.15, iupac=0.003, lower=0.5))])
+def test_template_cleaning_matches_oracle(synth, oracle_lib, gpu, seed, kw):
+    """--cleant / --rescue kernel (orfx_clean_templates) against the restated Transcriptome::clean_cds body."""
+    d = synth(seed, **kw)
+    w = ob.Workload(os.path.join(d, "query.gtf"), template_files(d), os.path.join(d, "genome.fa"))
+    batch = w.pack()
+    params = ob.Params.make(mode="LONGEST_MATCH,BEST", want_rows=False)
+    gpu.set_params(params)
+    best = gpu.run(batch).best
+    cb = cleaning_batch(batch, best, np.random.default_rng(seed))
+    kept = {}
+    for non_aug in (False, True):
+        for rescue in (False, True):
+            p = ob.Params.make(mode="BEST", non_aug=non_aug)
+            gpu.set_params(p)
+            got = gpu.clean(cb, rescue)
+            with ob.Context(p, lib=oracle_lib, prefix="orfx_oracle_") as ox:
+                want = ox.clean(cb, rescue)
+            for g, x, name in zip(got, want, ("keep", "cds_start", "cds_end")):
+                assert (g == x).all(), (seed, non_aug, rescue, name, int((g != x).sum()))
+            kept[(non_aug, rescue)] = int(got[0].sum())
+    n = cb.n_queries
+    assert n > 200
+    assert 0 < kept[(False, False)] < kept[(False, True)] < n     # rescue repairs some, not all
+    assert kept[(False, False)] <= kept[(True, False)]
+    # the path still answers a regular batch afterwards
+    gpu.set_params(params)
+    assert (gpu.run(batch).best.tobytes() == best.tobytes())
+    w.close()

@@ -31,6 +31,11 @@ OPTION_GRID = [
     ["--query", "query.gtf", "--mode", "LONGEST_MATCH,BEST"],
     ["--query", "query.gtf", "--mode", "ALL", "--lpi", "80"],
     ["--reference", "genome.fa", "--query", "query.gtf", "--use_id"],
+    # template cleaning (Transcriptome::clean_cds / clean_short_orfs)
+    ["--reference", "genome.fa", "--query", "query.gtf", "--cleant"],
+    ["--reference", "genome.fa", "--query", "query.gtf", "--cleant", "--rescue", "--mode", "LONGEST_MATCH,BEST"],
+    ["--reference", "genome.fa", "--query", "query.gtf", "--cleant", "--rescue", "--non_aug", "--mode", "BEST"],
+    ["--reference", "genome.fa", "--query", "query.gtf", "--cleant", "--minlen", "450", "--use_id"],
 ]
 SELF_GRID = [   # query file = a template file (queries that carry a CDS)
     (["--reference", "genome.fa", "--query", "template2.gtf", "--keep_all_cds"], ["template1.gtf"]),
