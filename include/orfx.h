@@ -157,7 +157,9 @@ typedef struct orfx_results {
     const int64_t* print_order;    /* [n_rows] absolute row indices in the stats print order:
                                       per query, keys ascending, inside a key the std::sort by
                                       score_gt (orfanage.cpp:250-283)                            */
-    /* device-side timing of the last batch, milliseconds (CUDA events on the launch stream) */
+    /* device-side timing of the last batch, milliseconds (CUDA events).  orfx_submit uploads the sequence bytes
+     * on a copy stream while the chain kernels already run: ms_h2d (submit -> last byte on the device) and
+     * ms_kernels (chains on the device -> last kernel) overlap, their sum exceeds the batch time. */
     float ms_h2d, ms_kernels, ms_d2h;
 } orfx_results;
 
@@ -219,6 +221,15 @@ typedef struct orfx_clean_out {
     int32_t* cds_end;
 } orfx_clean_out;
 int  orfx_clean_templates(orfx_ctx* ctx, const orfx_batch* batch, int rescue, orfx_clean_out* out, int64_t* n_out);
+
+/* ---- orfcompare: pair scoring only ----------------------------------- */
+/* Replaces the `q->score(*t)` loop of orfcompare.cpp:76-160: TX::score (Transcriptome.cpp:699-762) for every
+ * (query, template) pair of every bundle, no bounding-box test.  The batch is a *compare batch*: queries
+ * (ORFX_TX_QUERY) and templates (ORFX_TX_TEMPLATE) both carry their CDS chain as `segs`; no sequence is read.
+ * Synchronous.  On return out->n_rows pairs are described by row_q_tx, row_t_tx, row_qlen, row_tlen, row_ulen,
+ * row_match, row_inframe, row_outframe, row_extra, row_missing, row_lpi, row_ilpi, row_mlpi (query-major, templates
+ * in bundle order); every other member of *out is NULL / 0.  Buffers are library-owned, valid until the next call. */
+int  orfx_score_pairs(orfx_ctx* ctx, const orfx_batch* batch, orfx_results* out);
 
 /* ---- protein alignment (src/aln.hpp:27-41 with the build definition) ---- */
 typedef struct orfx_aln_out {

@@ -24,6 +24,8 @@ int launch_select(const DevBatch& B, const DevRows& R, const orfx_params& P, int
 void launch_codon_scan(const DevBatch& B, int64_t n_tiles, int n_sm, cudaStream_t stream);
 int launch_base_planes(const DevBatch& B, cudaStream_t stream);
 int launch_clean_templates(const DevBatch& B, int n_queries, int rescue, int non_aug, uint8_t* keep, int32_t* out_start, int32_t* out_end, cudaStream_t s);
+int launch_count_pairs(const DevBatch& B, int64_t* cnt, int64_t* scan_tmp, cudaStream_t s);
+int launch_score_pairs(const DevBatch& B, const DevRows& R, int n_queries, cudaStream_t s);
 int align_batch_device(int device, cudaStream_t stream, const uint8_t* aa, const int64_t* off, int64_t n_seq, const int32_t* pair_q,
                        const int32_t* pair_t, int64_t n_pairs, int gapo, int gape, orfx_aln_out* out, double* cells, float* ms, std::string& err);
 int int_alu_peak_device(cudaStream_t stream, double* ops, std::string& err);
@@ -84,6 +86,9 @@ struct orfx_ctx {
     int device = 0;
     int n_sm = 148;
     cudaStream_t stream = nullptr;
+    cudaStream_t copy_stream = nullptr;   // sequence bytes go up here while the chain kernels already run on `stream`
+    cudaEvent_t ev_chains = nullptr, ev_seq = nullptr;
+    bool seq_in_flight = false;
     orfx_params P;
     // inputs
     DBuf d_sso;
@@ -110,7 +115,10 @@ struct orfx_ctx {
 
 namespace {
 
-int upload_batch(orfx_ctx* c, const orfx_batch* b) {
+// overlap = true (orfx_submit): the chain arrays go first on the launch stream, the sequence bytes (two thirds
+// of the upload) follow on the copy stream; prep / candidate-row kernels only need the chains and start while
+// the sequence is still on the bus.  run_path waits for ev_seq before the first kernel that reads `seq`.
+int upload_batch(orfx_ctx* c, const orfx_batch* b, bool overlap = false) {
     if (!b) return fail(ORFX_E_INVALID, "null batch");
     if (b->n_bundles < 0 || b->n_tx < 0 || b->n_segs < 0) return fail(ORFX_E_INVALID, "negative batch size");
     if (c->P.has_reference && b->seq_bytes > 0 && !b->seq) return fail(ORFX_E_INVALID, "params.has_reference set but batch.seq is NULL");
@@ -133,7 +141,7 @@ int upload_batch(orfx_ctx* c, const orfx_batch* b) {
         if (bytes == 0) return cudaSuccess;
         return cudaMemcpyAsync(d.p, src, bytes, cudaMemcpyHostToDevice, s);
     };
-    if (seqb) {
+    if (seqb && !overlap) {
         CU(cp(c->d_seq, b->seq, seqb));
         CU(cudaMemsetAsync((char*)c->d_seq.p + seqb, 0, 64, s));   // the last aligned 16-byte chunk may read past the end
     }
@@ -150,6 +158,15 @@ int upload_batch(orfx_ctx* c, const orfx_batch* b) {
     CU(cp(c->d_phase, b->seg_phase, ns));
     const bool islands = seqb && b->seg_seq_off;
     if (islands) { CU(c->d_sso.ensure(ns * 4 + 4)); CU(cp(c->d_sso, b->seg_seq_off, ns * 4)); }
+    c->seq_in_flight = false;
+    if (seqb && overlap) {
+        CU(cudaEventRecord(c->ev_chains, s));
+        CU(cudaStreamWaitEvent(c->copy_stream, c->ev_chains, 0));   // after the chains, and after whatever still reads d_seq
+        CU(cudaMemcpyAsync(c->d_seq.p, b->seq, seqb, cudaMemcpyHostToDevice, c->copy_stream));
+        CU(cudaMemsetAsync((char*)c->d_seq.p + seqb, 0, 64, c->copy_stream));
+        CU(cudaEventRecord(c->ev_seq, c->copy_stream));
+        c->seq_in_flight = true;
+    }
     // derived buffers whose size is known now
     CU(c->d_seg_cum.ensure(ns * 4 + 4));
     CU(c->d_tx_len.ensure(nt * 4 + 4));
@@ -197,7 +214,11 @@ int run_path(orfx_ctx* c) {
     c->n_launches = 0;
     c->n_queries = c->n_rows = c->n_tiles = c->n_words = 0;
     cudaEventRecord(c->run_ev[0], s);
-    if (B.n_tx == 0) { cudaEventRecord(c->run_ev[1], s); return ORFX_OK; }
+    if (B.n_tx == 0) {
+        if (c->seq_in_flight) { CU(cudaStreamWaitEvent(s, c->ev_seq, 0)); c->seq_in_flight = false; }
+        cudaEventRecord(c->run_ev[1], s);
+        return ORFX_OK;
+    }
     stage_begin(c, ST_PREP);
     c->n_launches += launch_prep(B, c->d_cnt_q.as<int64_t>(), c->d_cnt_words.as<int64_t>(), c->d_cnt_tiles.as<int64_t>(), c->d_scan_tmp.as<int64_t>(),
                                  c->d_heavy.as<int32_t>(), c->d_heavy_count.as<unsigned>(), s);
@@ -237,6 +258,10 @@ int run_path(orfx_ctx* c) {
     R.status = c->r_u8[0].as<uint8_t>(); R.pass = c->r_u8[1].as<uint8_t>(); R.start_match = c->r_u8[2].as<uint8_t>();
     R.print_order = c->r_order.as<int64_t>();
 
+    stage_begin(c, ST_FILL);
+    c->n_launches += launch_fill_rows(B, R, (int)nq, s);
+    stage_end(c, ST_FILL);
+    if (c->seq_in_flight) { CU(cudaStreamWaitEvent(s, c->ev_seq, 0)); c->seq_in_flight = false; }
     stage_begin(c, ST_PLANES);
     if (c->P.has_reference) {
         c->n_launches += launch_fill_tiles(B, s);
@@ -249,9 +274,6 @@ int run_path(orfx_ctx* c) {
         if (tiles > 0) c->n_launches++;
     }
     stage_end(c, ST_SCAN);
-    stage_begin(c, ST_FILL);
-    c->n_launches += launch_fill_rows(B, R, (int)nq, s);
-    stage_end(c, ST_FILL);
     stage_begin(c, ST_HEAVY);
     c->n_launches += launch_heavy_fill_rescue(B, R, c->P, c->d_heavy.as<int32_t>(), c->d_heavy_count.as<unsigned>(), c->n_sm, s);
     stage_end(c, ST_HEAVY);
@@ -346,7 +368,10 @@ int orfx_create(orfx_ctx** out, int device, const orfx_params* params) {
     c->device = device;
     c->n_sm = prop.multiProcessorCount;
     c->P = *params;
-    if (cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking) != cudaSuccess) { delete c; return fail(ORFX_E_CUDA, "cudaStreamCreate failed"); }
+    if (cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking) != cudaSuccess ||
+        cudaStreamCreateWithFlags(&c->copy_stream, cudaStreamNonBlocking) != cudaSuccess) { delete c; return fail(ORFX_E_CUDA, "cudaStreamCreate failed"); }
+    cudaEventCreateWithFlags(&c->ev_chains, cudaEventDisableTiming);
+    cudaEventCreate(&c->ev_seq);
     for (auto& ev : c->ev) cudaEventCreate(&ev);
     for (int i = 0; i < ST_N; i++) { cudaEventCreate(&c->st_ev[i][0]); cudaEventCreate(&c->st_ev[i][1]); c->st_ms[i] = 0; }
     cudaEventCreate(&c->run_ev[0]); cudaEventCreate(&c->run_ev[1]);
@@ -366,7 +391,7 @@ int orfx_submit(orfx_ctx* c, const orfx_batch* batch) {
     if (!c) return fail(ORFX_E_INVALID, "null ctx");
     CU(cudaSetDevice(c->device));
     CU(cudaEventRecord(c->ev[0], c->stream));
-    int rc = upload_batch(c, batch);
+    int rc = upload_batch(c, batch, true);
     if (rc) return rc;
     CU(cudaEventRecord(c->ev[1], c->stream));
     rc = run_path(c);
@@ -389,7 +414,8 @@ int orfx_wait(orfx_ctx* c, orfx_results* out) {
     c->have_results = true;
     collect_times(c);
     fill_results(c, out);
-    cudaEventElapsedTime(&out->ms_h2d, c->ev[0], c->ev[1]);
+    cudaEventElapsedTime(&out->ms_h2d, c->ev[0], c->ev[1]);   // chain arrays; the sequence upload overlaps the first kernels
+    if (c->B.seq_bytes > 0) { float t = 0; if (cudaEventElapsedTime(&t, c->ev[0], c->ev_seq) == cudaSuccess && t > out->ms_h2d) out->ms_h2d = t; }
     cudaEventElapsedTime(&out->ms_kernels, c->ev[1], c->ev[2]);
     cudaEventElapsedTime(&out->ms_d2h, c->ev[2], c->ev[3]);
     return ORFX_OK;
@@ -420,6 +446,9 @@ void orfx_destroy(orfx_ctx* c) {
     for (auto& ev : c->ev) if (ev) cudaEventDestroy(ev);
     for (int i = 0; i < ST_N; i++) { cudaEventDestroy(c->st_ev[i][0]); cudaEventDestroy(c->st_ev[i][1]); }
     cudaEventDestroy(c->run_ev[0]); cudaEventDestroy(c->run_ev[1]);
+    cudaStreamSynchronize(c->copy_stream);
+    cudaEventDestroy(c->ev_chains); cudaEventDestroy(c->ev_seq);
+    cudaStreamDestroy(c->copy_stream);
     cudaStreamDestroy(c->stream);
     delete c;
 }
@@ -542,6 +571,59 @@ int orfx_clean_templates(orfx_ctx* c, const orfx_batch* batch, int rescue, orfx_
     c->n_queries = nq; c->n_words = words; c->n_tiles = tiles; c->n_rows = 0;
     c->have_results = false;
     if (n_out) *n_out = nq;
+    return ORFX_OK;
+}
+
+int orfx_score_pairs(orfx_ctx* c, const orfx_batch* batch, orfx_results* out) {
+    if (!c || !out) return fail(ORFX_E_INVALID, "null argument");
+    CU(cudaSetDevice(c->device));
+    orfx_batch nb;
+    if (!batch) return fail(ORFX_E_INVALID, "null batch");
+    nb = *batch; nb.seq = nullptr; nb.seq_bytes = 0; nb.seg_seq_off = nullptr;   // a compare batch reads no sequence
+    const int32_t has_ref = c->P.has_reference;
+    c->P.has_reference = 0;
+    int rc = upload_batch(c, &nb);
+    c->P.has_reference = has_ref;
+    if (rc) return rc;
+    cudaStream_t s = c->stream;
+    DevBatch& B = c->B;
+    memset(out, 0, sizeof *out);
+    c->n_launches = 0; c->n_queries = c->n_rows = 0; c->have_results = false;
+    if (B.n_tx == 0) return ORFX_OK;
+    c->n_launches += launch_prep(B, c->d_cnt_q.as<int64_t>(), c->d_cnt_words.as<int64_t>(), c->d_cnt_tiles.as<int64_t>(), c->d_scan_tmp.as<int64_t>(),
+                                 c->d_heavy.as<int32_t>(), c->d_heavy_count.as<unsigned>(), s);
+    c->n_launches += launch_count_pairs(B, c->d_cnt_rows.as<int64_t>(), c->d_scan_tmp.as<int64_t>(), s);
+    int64_t* tot = c->h_totals.as<int64_t>();
+    CU(cudaMemcpyAsync(tot + 0, B.tx_q_off + B.n_tx, 8, cudaMemcpyDeviceToHost, s));
+    CU(cudaMemcpyAsync(tot + 3, B.q_row_off + B.n_tx, 8, cudaMemcpyDeviceToHost, s));
+    CU(cudaStreamSynchronize(s));
+    const int64_t nq = tot[0], nrows = tot[3];
+    if (nrows > (int64_t)INT32_MAX) return fail(ORFX_E_INVALID, "more than 2^31 pairs in one batch: shard it");
+    static const int USED_I32[] = {0, 1, 7, 8, 9, 11, 12, 13, 14, 15};   // q_tx t_tx qlen tlen ulen extra missing match outframe inframe
+    for (int i : USED_I32) CU(c->r_i32[i].ensure((size_t)nrows * 4 + 4));
+    for (int i = 0; i < 3; i++) CU(c->r_f32[i].ensure((size_t)nrows * 4 + 4));
+    DevRows& R = c->R;
+    memset(&R, 0, sizeof R);
+    R.n_rows = nrows;
+    R.q_tx = c->r_i32[0].as<int32_t>(); R.t_tx = c->r_i32[1].as<int32_t>(); R.qlen = c->r_i32[7].as<int32_t>(); R.tlen = c->r_i32[8].as<int32_t>();
+    R.ulen = c->r_i32[9].as<int32_t>(); R.extra = c->r_i32[11].as<int32_t>(); R.missing = c->r_i32[12].as<int32_t>(); R.match = c->r_i32[13].as<int32_t>();
+    R.outframe = c->r_i32[14].as<int32_t>(); R.inframe = c->r_i32[15].as<int32_t>();
+    R.lpi = c->r_f32[0].as<float>(); R.ilpi = c->r_f32[1].as<float>(); R.mlpi = c->r_f32[2].as<float>();
+    c->n_launches += launch_score_pairs(B, R, (int)nq, s);
+    CU(cudaGetLastError());
+    if (nrows) {
+        for (int i : USED_I32) { CU(c->h_i32[i].ensure((size_t)nrows * 4)); CU(cudaMemcpyAsync(c->h_i32[i].p, c->r_i32[i].p, (size_t)nrows * 4, cudaMemcpyDeviceToHost, s)); }
+        for (int i = 0; i < 3; i++) { CU(c->h_f32[i].ensure((size_t)nrows * 4)); CU(cudaMemcpyAsync(c->h_f32[i].p, c->r_f32[i].p, (size_t)nrows * 4, cudaMemcpyDeviceToHost, s)); }
+    }
+    CU(cudaStreamSynchronize(s));
+    CU(cudaGetLastError());
+    c->n_queries = nq; c->n_rows = nrows;
+    out->n_queries = (int32_t)nq; out->n_rows = nrows;
+    out->row_q_tx = c->h_i32[0].as<int32_t>(); out->row_t_tx = c->h_i32[1].as<int32_t>(); out->row_qlen = c->h_i32[7].as<int32_t>();
+    out->row_tlen = c->h_i32[8].as<int32_t>(); out->row_ulen = c->h_i32[9].as<int32_t>(); out->row_extra = c->h_i32[11].as<int32_t>();
+    out->row_missing = c->h_i32[12].as<int32_t>(); out->row_match = c->h_i32[13].as<int32_t>(); out->row_outframe = c->h_i32[14].as<int32_t>();
+    out->row_inframe = c->h_i32[15].as<int32_t>();
+    out->row_lpi = c->h_f32[0].as<float>(); out->row_ilpi = c->h_f32[1].as<float>(); out->row_mlpi = c->h_f32[2].as<float>();
     return ORFX_OK;
 }
 

@@ -10,6 +10,8 @@
 //               in-frame bit scans over the codon-scan masks
 //   score       TX::score (Transcriptome.cpp:699-762): lossy union, sweep classification, lpi/ilpi/mlpi
 #include "chain_ops.cuh"
+#include <climits>
+#include <algorithm>
 
 namespace orfx {
 
@@ -361,6 +363,168 @@ __device__ int guided_start(const TxView& q, const TxView& t, const uint32_t* st
     return m >= lb ? m : far;
 }
 
+// ---- warp-cooperative chain walks (heavy bundles: chains of hundreds of segments) ------------------
+// The per-thread walks above are dependent-load chains of O(exons + segments) steps; on titin-class
+// transcripts a warp does them 32 exons at a time instead.  Every lane of the warp calls these with the
+// same arguments; results are warp-uniform.
+
+// first k in [lo, hi) with segs[k].end >= g, else hi
+__device__ __forceinline__ int first_end_ge(const orfx_seg* segs, int lo, int hi, int g) {
+    while (lo < hi) { const int mid = (lo + hi) >> 1; if (segs[mid].end < g) lo = mid + 1; else hi = mid; }
+    return lo;
+}
+__device__ __forceinline__ int warp_sum(int v) {
+#pragma unroll
+    for (int d = 16; d > 0; d >>= 1) v += __shfl_xor_sync(0xffffffffu, v, d);
+    return v;
+}
+__device__ __forceinline__ int warp_excl_scan(int v, int lane) {
+    int incl = v;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) { const int o = __shfl_up_sync(0xffffffffu, incl, d); if (lane >= d) incl += o; }
+    return incl - v;
+}
+
+// pair_rows for a whole warp.  The reference's merge rule (CHAIN::intersection with segments = true,
+// Transcriptome.h:321-361) joins piece (exon i, segment j) to the piece before it exactly when that piece
+// is (i-1, j-1) with equal ends and this one has equal starts (a shared intron); any other predecessor
+// resets `continue_prev`.  So every piece knows locally whether it opens a row (head) and whether it closes
+// one (tail); row r runs from the r-th head's start to the r-th tail's end.
+template <bool FILL>
+__device__ int pair_rows_warp(const DevBatch& B, const orfx_seg* segs, const DevRows& R, int qx, int t, int64_t out, int lane) {
+    const int q0 = B.tx_seg_off[qx], q1 = B.tx_seg_off[qx + 1];
+    const int t0 = B.tx_seg_off[t], t1 = B.tx_seg_off[t + 1];
+    int heads = 0, tails = 0;
+    if (t0 < t1) {
+        for (int base = q0; base < q1; base += 32) {
+            const int i = base + lane;
+            int nh = 0, nt = 0, j0 = t1;
+            orfx_seg s1 = {0, -1};
+            int prev_end = INT_MIN, next_start = INT_MIN;
+            if (i < q1) {
+                s1 = segs[i];
+                if (i > q0) prev_end = segs[i - 1].end;
+                if (i + 1 < q1) next_start = segs[i + 1].start;
+                j0 = first_end_ge(segs, t0, t1, s1.start);
+                for (int j = j0; j < t1; j++) {
+                    const orfx_seg c2 = segs[j];
+                    if (c2.start > s1.end) break;
+                    const bool lp = j > t0 && prev_end != INT_MIN && s1.start == c2.start && prev_end == segs[j - 1].end;
+                    const bool ln = j + 1 < t1 && next_start != INT_MIN && s1.end == c2.end && next_start == segs[j + 1].start;
+                    nh += !lp; nt += !ln;
+                }
+            }
+            if (FILL) {
+                int64_t hp = out + heads + warp_excl_scan(nh, lane), tp = out + tails + warp_excl_scan(nt, lane);
+                if (i < q1) {
+                    for (int j = j0; j < t1; j++) {
+                        const orfx_seg c2 = segs[j];
+                        if (c2.start > s1.end) break;
+                        const bool lp = j > t0 && prev_end != INT_MIN && s1.start == c2.start && prev_end == segs[j - 1].end;
+                        const bool ln = j + 1 < t1 && next_start != INT_MIN && s1.end == c2.end && next_start == segs[j + 1].start;
+                        if (!lp) { R.q_tx[hp] = qx; R.t_tx[hp] = t; R.seg_start[hp] = max(s1.start, c2.start); R.status[hp] = ORFX_ST_OK; hp++; }
+                        if (!ln) { R.seg_end[tp] = min(s1.end, c2.end); tp++; }
+                    }
+                }
+            }
+            heads += warp_sum(nh); tails += warp_sum(nt);
+        }
+    }
+    if (heads == 0) {
+        if (FILL && lane == 0) put_row(R, out, qx, t, -1, -1, ORFX_ST_NO_OVERLAP);
+        return 1;
+    }
+    return heads;
+}
+
+// CHAIN::compare + the frame walk of TX::score (Transcriptome.h:514-558, cpp:719-745) for a whole warp.
+// The walk bins every match piece by (extra - missing) mod 3 seen so far on the genomic-left side; that
+// difference is (query CDS bases left of the piece) - (template bases left of it), which the prefix arrays
+// give directly, so the pieces are independent.  q segments are clipped to [cs, ce] (indices qk0..qk1).
+struct SweepSums { int match, bin0, bin1, bin2; };
+// CHAIN::get_union (Transcriptome.h:291-319; lossy: both chains advance on an overlap, the tail of the
+// longer chain is dropped) for a whole warp.  When the walk reaches query segment i its template index is
+// F(i) or F(i) + 1, F(i) = first template segment ending at or after the segment's start (skipped segments
+// are added on the way), so a query segment is a map {0, 1} -> (next state, length added); state 2 = template
+// exhausted.  The maps compose associatively: one ordered warp scan per 32 query segments.
+struct UMap { int n0, c0, n1, c1; };
+__device__ __forceinline__ UMap umap_then(const UMap& a, const UMap& b) {
+    UMap r;
+    r.n0 = a.n0 == 2 ? 2 : (a.n0 == 0 ? b.n0 : b.n1);
+    r.c0 = a.c0 + (a.n0 == 2 ? 0 : (a.n0 == 0 ? b.c0 : b.c1));
+    r.n1 = a.n1 == 2 ? 2 : (a.n1 == 0 ? b.n0 : b.n1);
+    r.c1 = a.c1 + (a.n1 == 2 ? 0 : (a.n1 == 0 ? b.c0 : b.c1));
+    return r;
+}
+// Union and sweep in one pass: both need F(i), found once per query segment (the next segment's F comes from
+// the neighbouring lane).
+__device__ int union_sweep_warp(const TxView& q, const TxView& t, int qk0, int qk1, int cs, int ce, int lane, SweepSums& S) {
+    auto tcum = [&](int k) { return k < t.n ? t.cum[k] : t.L; };
+    S.match = S.bin0 = S.bin1 = S.bin2 = 0;
+    const int qbase = q.cum[qk0] + (cs - q.segs[qk0].start);
+    int state = 0;
+    int total = tcum(first_end_ge(t.segs, 0, t.n, max(q.segs[qk0].start, cs)));
+    for (int base = qk0; base <= qk1; base += 32) {
+        const int i = base + lane;
+        const bool valid = i <= qk1;
+        orfx_seg e = {0, -1};
+        int c1s = 0, c1e = -1, F = t.n;
+        if (valid) {
+            e = q.segs[i];
+            c1s = max(e.start, cs); c1e = min(e.end, ce);
+            F = first_end_ge(t.segs, 0, t.n, c1s);
+        }
+        int Fn = __shfl_down_sync(0xffffffffu, F, 1);
+        if (lane == 31 && i < qk1) Fn = first_end_ge(t.segs, F, t.n, q.segs[i + 1].start);
+        UMap m = {0, 0, 1, 0};   // identity
+        if (valid) {
+            // sweep: the match pieces under this query segment
+            for (int j = F; j < t.n; j++) {
+                const orfx_seg c = t.segs[j];
+                if (c.start > c1e) break;
+                const int lo = max(c1s, c.start), hi = min(c1e, c.end);
+                const int qb = q.cum[i] + (lo - e.start) - qbase, tb = t.cum[j] + (lo - c.start);
+                int d = (qb - tb) % 3; if (d < 0) d += 3;
+                const int len = hi - lo + 1;
+                S.match += len;
+                if (d == 0) S.bin0 += len; else if (d == 1) S.bin1 += len; else S.bin2 += len;
+            }
+            // union: this segment's map
+#pragma unroll
+            for (int st = 0; st < 2; st++) {
+                const int jp = F + st;
+                int ns, cost;
+                if (jp >= t.n) { ns = 2; cost = 0; }
+                else {
+                    const orfx_seg c2 = t.segs[jp];
+                    int jo;
+                    if (c2.start > c1e) { cost = c1e - c1s + 1; jo = jp; }
+                    else { cost = max(c1e, c2.end) - min(c1s, c2.start) + 1; jo = jp + 1; }
+                    if (i == qk1) ns = 0;
+                    else if (jo < Fn) { cost += tcum(Fn) - tcum(jo); ns = 0; }
+                    else ns = jo - Fn;
+                }
+                if (st == 0) { m.n0 = ns; m.c0 = cost; } else { m.n1 = ns; m.c1 = cost; }
+            }
+        }
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) {
+            UMap o;
+            o.n0 = __shfl_up_sync(0xffffffffu, m.n0, d); o.c0 = __shfl_up_sync(0xffffffffu, m.c0, d);
+            o.n1 = __shfl_up_sync(0xffffffffu, m.n1, d); o.c1 = __shfl_up_sync(0xffffffffu, m.c1, d);
+            if (lane >= d) m = umap_then(o, m);
+        }
+        const int n0 = __shfl_sync(0xffffffffu, m.n0, 31), c0 = __shfl_sync(0xffffffffu, m.c0, 31);
+        const int n1 = __shfl_sync(0xffffffffu, m.n1, 31), c1 = __shfl_sync(0xffffffffu, m.c1, 31);
+        if (state != 2) {
+            total += state == 0 ? c0 : c1;
+            state = state == 0 ? n0 : n1;
+        }
+    }
+    S.match = warp_sum(S.match); S.bin0 = warp_sum(S.bin0); S.bin1 = warp_sum(S.bin1); S.bin2 = warp_sum(S.bin2);
+    return total;
+}
+
 __device__ __forceinline__ float pct(int num, int den) {
     // 100.0 * ((float)num / (float)den) narrowed to float (Transcriptome.cpp:748-750)
     return __double2float_rn(__dmul_rn(100.0, (double)__fdiv_rn((float)num, (float)den)));
@@ -370,7 +534,81 @@ __device__ __forceinline__ float pct(int num, int den) {
 
 // One candidate row: rescue (when a genome is loaded) + TX::score.  q / t may view the chains in
 // global or in shared memory.
+// TX::score's chain arithmetic (Transcriptome.cpp:699-750) for a query CDS = q's segments clipped to the
+// genomic span [cs, ce] (qlen bases) against the template chain t: lossy union, sweep classification, frame walk.
+struct ChainScore { int ulen, extra, missing, match, inframe, outframe; };
+template <bool WARP>
+__device__ __forceinline__ ChainScore score_chains(const TxView& q, const TxView& t, int cs, int ce, int qlen, bool plus, int lane) {
+    int ulen = 0, extra = 0, missing = 0, match = 0, inframe = 0, outframe = 0;
+    const int tlen = t.L;
+    // query CDS segments = exons clipped to [cs,ce]
+    const int qk0 = seg_of_genomic(q, cs), qk1 = seg_of_genomic(q, ce);
+    if (WARP) {
+        SweepSums S;
+        ulen = union_sweep_warp(q, t, qk0, qk1, cs, ce, lane, S);
+        match = S.match; extra = qlen - match; missing = tlen - match;
+        int want = 0;
+        if (!plus) { want = (extra - missing) % 3; if (want < 0) want += 3; }
+        inframe = want == 0 ? S.bin0 : (want == 1 ? S.bin1 : S.bin2);
+        outframe = match - inframe;
+    }
+    // lossy union (CHAIN::get_union, Transcriptome.h:291-319)
+    if (!WARP) {
+        int i = qk0, j = 0;
+        while (i <= qk1 && j < t.n) {
+            const int c1s = max(q.segs[i].start, cs), c1e = min(q.segs[i].end, ce);
+            const int c2s = t.segs[j].start, c2e = t.segs[j].end;
+            if (c1e < c2s) { ulen += c1e - c1s + 1; i++; }
+            else if (c2e < c1s) { ulen += c2e - c2s + 1; j++; }
+            else { ulen += max(c1e, c2e) - min(c1s, c2s) + 1; i++; j++; }
+        }
+    }
+    // sweep classification (CHAIN::compare + the frame walk, Transcriptome.h:514-558, cpp:719-745):
+    // match pieces are binned by (extra - missing) mod 3 seen so far on the genomic-left side
+    if (!WARP) {
+        int bin[3] = {0, 0, 0};
+        int i = qk0, j = 0;
+        int qs = max(q.segs[i].start, cs), qe = min(q.segs[i].end, ce);
+        int ts = 0, te = -1;
+        if (t.n > 0) { ts = t.segs[0].start; te = t.segs[0].end; }
+        bool hq = true, ht = t.n > 0;
+        while (hq || ht) {
+            if (hq && (!ht || qe < ts)) {          // query-only remainder
+                extra += qe - qs + 1;
+                i++; hq = i <= qk1;
+                if (hq) { qs = max(q.segs[i].start, cs); qe = min(q.segs[i].end, ce); }
+            } else if (ht && (!hq || te < qs)) {   // template-only remainder
+                missing += te - ts + 1;
+                j++; ht = j < t.n;
+                if (ht) { ts = t.segs[j].start; te = t.segs[j].end; }
+            } else {
+                const int lo = max(qs, ts), hi = min(qe, te);
+                if (qs < lo) extra += lo - qs;
+                if (ts < lo) missing += lo - ts;
+                int d = (extra - missing) % 3; if (d < 0) d += 3;
+                bin[d] += hi - lo + 1;
+                match += hi - lo + 1;
+                qs = hi + 1; ts = hi + 1;
+                if (qs > qe) { i++; hq = i <= qk1; if (hq) { qs = max(q.segs[i].start, cs); qe = min(q.segs[i].end, ce); } }
+                if (ts > te) { j++; ht = j < t.n; if (ht) { ts = t.segs[j].start; te = t.segs[j].end; } }
+            }
+        }
+        // 5'->3' on '+' is genomic-left to right: in frame when (extra-missing) so far == 0 (mod 3);
+        // on the reverse strand the 5' side is the genomic-right side: totals minus the left part
+        int want = 0;
+        if (!plus) { want = (extra - missing) % 3; if (want < 0) want += 3; }
+        inframe = bin[want];
+        outframe = match - inframe;
+    }
+    ChainScore r = {ulen, extra, missing, match, inframe, outframe};
+    return r;
+}
+
+// WARP = true: all 32 lanes of a warp work on the same row (heavy bundles); the two O(chain) walks of
+// TX::score are done cooperatively, everything else redundantly, lane 0 stores.
+template <bool WARP>
 __device__ void process_row(const DevBatch& B, const DevRows& R, const orfx_params& P, const int64_t row, const TxView& q, const TxView& t) {
+    const int lane = WARP ? (int)(threadIdx.x & 31) : 0;
     // defaults: an all-zero Score that does not pass
     int status = R.status[row];
     int key_s = 0, key_e = 0;
@@ -473,55 +711,9 @@ __device__ void process_row(const DevBatch& B, const DevRows& R, const orfx_para
 
         // ---- TX::score (Transcriptome.cpp:699-762) ----
         tlen = t.L;
-        // query CDS segments = exons clipped to [cs,ce]
-        const int qk0 = seg_of_genomic(q, cs), qk1 = seg_of_genomic(q, ce);
-        // lossy union (CHAIN::get_union, Transcriptome.h:291-319)
         {
-            int i = qk0, j = 0;
-            while (i <= qk1 && j < t.n) {
-                const int c1s = max(q.segs[i].start, cs), c1e = min(q.segs[i].end, ce);
-                const int c2s = t.segs[j].start, c2e = t.segs[j].end;
-                if (c1e < c2s) { ulen += c1e - c1s + 1; i++; }
-                else if (c2e < c1s) { ulen += c2e - c2s + 1; j++; }
-                else { ulen += max(c1e, c2e) - min(c1s, c2s) + 1; i++; j++; }
-            }
-        }
-        // sweep classification (CHAIN::compare + the frame walk, Transcriptome.h:514-558, cpp:719-745):
-        // match pieces are binned by (extra - missing) mod 3 seen so far on the genomic-left side
-        {
-            int bin[3] = {0, 0, 0};
-            int i = qk0, j = 0;
-            int qs = max(q.segs[i].start, cs), qe = min(q.segs[i].end, ce);
-            int ts = 0, te = -1;
-            if (t.n > 0) { ts = t.segs[0].start; te = t.segs[0].end; }
-            bool hq = true, ht = t.n > 0;
-            while (hq || ht) {
-                if (hq && (!ht || qe < ts)) {          // query-only remainder
-                    extra += qe - qs + 1;
-                    i++; hq = i <= qk1;
-                    if (hq) { qs = max(q.segs[i].start, cs); qe = min(q.segs[i].end, ce); }
-                } else if (ht && (!hq || te < qs)) {   // template-only remainder
-                    missing += te - ts + 1;
-                    j++; ht = j < t.n;
-                    if (ht) { ts = t.segs[j].start; te = t.segs[j].end; }
-                } else {
-                    const int lo = max(qs, ts), hi = min(qe, te);
-                    if (qs < lo) extra += lo - qs;
-                    if (ts < lo) missing += lo - ts;
-                    int d = (extra - missing) % 3; if (d < 0) d += 3;
-                    bin[d] += hi - lo + 1;
-                    match += hi - lo + 1;
-                    qs = hi + 1; ts = hi + 1;
-                    if (qs > qe) { i++; hq = i <= qk1; if (hq) { qs = max(q.segs[i].start, cs); qe = min(q.segs[i].end, ce); } }
-                    if (ts > te) { j++; ht = j < t.n; if (ht) { ts = t.segs[j].start; te = t.segs[j].end; } }
-                }
-            }
-            // 5'->3' on '+' is genomic-left to right: in frame when (extra-missing) so far == 0 (mod 3);
-            // on the reverse strand the 5' side is the genomic-right side: totals minus the left part
-            int want = 0;
-            if (!plus) { want = (extra - missing) % 3; if (want < 0) want += 3; }
-            inframe = bin[want];
-            outframe = match - inframe;
+            const ChainScore cs_ = score_chains<WARP>(q, t, cs, ce, qlen, plus, lane);
+            ulen = cs_.ulen; extra = cs_.extra; missing = cs_.missing; match = cs_.match; inframe = cs_.inframe; outframe = cs_.outframe;
         }
         lpi = pct(qlen, ulen); ilpi = pct(inframe, ulen); mlpi = pct(match, ulen);
         query_start = plus ? cs - q.segs[0].start : q.segs[q.n - 1].end - ce;
@@ -533,6 +725,7 @@ __device__ void process_row(const DevBatch& B, const DevRows& R, const orfx_para
         key_s = cs; key_e = ce;
     } while (false);
 
+    if (WARP && lane != 0) return;
     R.status[row] = (uint8_t)status;
     R.cds_start[row] = key_s; R.cds_end[row] = key_e;
     R.qlen[row] = qlen; R.tlen[row] = tlen; R.ulen[row] = ulen; R.query_start[row] = query_start;
@@ -548,16 +741,15 @@ __global__ void __launch_bounds__(128) rescue_score_kernel(DevBatch B, DevRows R
     const int qx = R.q_tx[row];
     if (B.bundle_need[B.tx_bundle[qx]] & BUNDLE_HEAVY) return;   // done by heavy_fill_rescue_kernel
     const TxView q = tx_view(B, qx), t = tx_view(B, R.t_tx[row]);
-    process_row(B, R, P, row, q, t);
+    process_row<false>(B, R, P, row, q, t);
 }
 
 // ------------------------------------------------------------------------------------------------
 // heavy bundles: one CTA per bundle, the bundle's chains staged in shared memory
 // ------------------------------------------------------------------------------------------------
-constexpr int HB_THREADS = 256;
+constexpr int HB_THREADS = 512;   // x 2 CTAs per SM
 constexpr int HB_MAX_SEGS = 8192;     // segments of one bundle that fit the stage (8 B + 4 B each); two CTAs per SM
 constexpr int HB_MAX_PAIRS = 8192;    // (query, transcript slot) pairs whose row counts fit the stage
-constexpr size_t HB_SMEM = (size_t)HB_MAX_SEGS * (sizeof(orfx_seg) + sizeof(int32_t)) + (size_t)HB_MAX_PAIRS * sizeof(uint16_t);
 
 namespace {
 struct HeavyBundle {
@@ -595,84 +787,115 @@ __device__ __forceinline__ TxView hb_view(const DevBatch& B, const HeavyBundle& 
 }
 }  // namespace
 
-// rows of every query of the heavy bundles, one thread per (query, transcript slot) pair
-__global__ void __launch_bounds__(HB_THREADS) heavy_count_kernel(DevBatch B, int64_t* cnt, const int32_t* heavy_list, const unsigned* heavy_count) {
+// Work item w of a heavy kernel = (heavy bundle w / HB_SLICES, slice w % HB_SLICES): a slice takes every
+// HB_SLICES-th query of the bundle (pair kernels) or every HB_SLICES-th group of rows (row kernel), so that a
+// titin-class bundle is spread over several SMs.  Every CTA stages the whole bundle's chains.
+constexpr int HB_SLICES = 4;
+
+// rows of every query of the heavy bundles, one warp per (query, transcript slot) pair
+__global__ void __launch_bounds__(HB_THREADS, 2) heavy_count_kernel(DevBatch B, int64_t* cnt, const int32_t* heavy_list, const unsigned* heavy_count) {
     extern __shared__ __align__(16) unsigned char hb_smem[];
     orfx_seg* s_seg = reinterpret_cast<orfx_seg*>(hb_smem);
-    const unsigned n = *heavy_count;
+    const unsigned n = *heavy_count * HB_SLICES;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = blockDim.x >> 5;
     DevRows dummy{};
-    for (unsigned h = blockIdx.x; h < n; h += gridDim.x) {
-        const HeavyBundle H = hb_load(B, heavy_list[h], s_seg, nullptr, false);
-        const int64_t npairs = (int64_t)H.nq * H.ntx;
-        for (int64_t p = threadIdx.x; p < npairs; p += blockDim.x) {
-            const int ql = (int)(p / H.ntx), t = H.x0 + (int)(p % H.ntx);
+    for (unsigned w = blockIdx.x; w < n; w += gridDim.x) {
+        const int k = (int)(w % HB_SLICES);
+        const HeavyBundle H = hb_load(B, heavy_list[w / HB_SLICES], s_seg, nullptr, false);
+        const int nq_slice = (H.nq - k + HB_SLICES - 1) / HB_SLICES;
+        const int npairs = nq_slice * H.ntx;
+        for (int p = warp; p < npairs; p += nwarps) {
+            const int ql = k + HB_SLICES * (p / H.ntx), t = H.x0 + p % H.ntx;
             const int qx = B.q_list[H.qbase + ql];
             const int qstart = H.segs[B.tx_seg_off[qx]].start, qend = H.segs[B.tx_seg_off[qx + 1] - 1].end;
             if (!pair_live(B, t, H.x1, qstart, qend)) continue;
-            const int r = pair_rows<false>(B, H.segs, dummy, qx, t, 0);
-            atomicAdd(reinterpret_cast<unsigned long long*>(cnt + H.qbase + ql), (unsigned long long)r);   // zeroed by count_rows_kernel
+            const int r = pair_rows_warp<false>(B, H.segs, dummy, qx, t, 0, lane);
+            if (lane == 0) atomicAdd(reinterpret_cast<unsigned long long*>(cnt + H.qbase + ql), (unsigned long long)r);   // zeroed by count_rows_kernel
         }
         __syncthreads();
     }
 }
 
-// candidate rows of the heavy bundles (in the reference's order), then rescue + score of those rows,
-// all against the staged chains
-__global__ void __launch_bounds__(HB_THREADS) heavy_fill_rescue_kernel(DevBatch B, DevRows R, orfx_params P, const int32_t* heavy_list,
-                                                                      const unsigned* heavy_count) {
+// candidate rows of the heavy bundles, in the reference's order; one warp per pair
+__global__ void __launch_bounds__(HB_THREADS, 2) heavy_fill_kernel(DevBatch B, DevRows R, const int32_t* heavy_list, const unsigned* heavy_count) {
     extern __shared__ __align__(16) unsigned char hb_smem[];
     orfx_seg* s_seg = reinterpret_cast<orfx_seg*>(hb_smem);
-    int32_t* s_cum = reinterpret_cast<int32_t*>(hb_smem + (size_t)HB_MAX_SEGS * sizeof(orfx_seg));
-    uint16_t* s_n = reinterpret_cast<uint16_t*>(hb_smem + (size_t)HB_MAX_SEGS * (sizeof(orfx_seg) + sizeof(int32_t)));
-    const unsigned n = *heavy_count;
-    for (unsigned h = blockIdx.x; h < n; h += gridDim.x) {
-        const HeavyBundle H = hb_load(B, heavy_list[h], s_seg, s_cum, true);
-        const int64_t npairs = (int64_t)H.nq * H.ntx;
-        if (H.staged && npairs <= HB_MAX_PAIRS) {
+    uint16_t* s_n = reinterpret_cast<uint16_t*>(hb_smem + (size_t)HB_MAX_SEGS * sizeof(orfx_seg));
+    const unsigned n = *heavy_count * HB_SLICES;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = blockDim.x >> 5;
+    for (unsigned w = blockIdx.x; w < n; w += gridDim.x) {
+        const int k = (int)(w % HB_SLICES);
+        const HeavyBundle H = hb_load(B, heavy_list[w / HB_SLICES], s_seg, nullptr, false);
+        const int nq_slice = (H.nq - k + HB_SLICES - 1) / HB_SLICES;
+        const int64_t npairs = (int64_t)nq_slice * H.ntx;
+        if (npairs <= HB_MAX_PAIRS) {
             // rows of every pair, then each pair fills at (rows of the query's earlier pairs)
-            for (int p = threadIdx.x; p < (int)npairs; p += blockDim.x) {
-                const int ql = p / H.ntx, t = H.x0 + p % H.ntx;
+            for (int p = warp; p < (int)npairs; p += nwarps) {
+                const int ql = k + HB_SLICES * (p / H.ntx), t = H.x0 + p % H.ntx;
                 const int qx = B.q_list[H.qbase + ql];
                 const int qstart = H.segs[B.tx_seg_off[qx]].start, qend = H.segs[B.tx_seg_off[qx + 1] - 1].end;
-                s_n[p] = pair_live(B, t, H.x1, qstart, qend) ? (uint16_t)pair_rows<false>(B, H.segs, R, qx, t, 0) : (uint16_t)0;
+                const int r = pair_live(B, t, H.x1, qstart, qend) ? pair_rows_warp<false>(B, H.segs, R, qx, t, 0, lane) : 0;
+                if (lane == 0) s_n[p] = (uint16_t)r;
             }
             __syncthreads();
-            for (int p = threadIdx.x; p < (int)npairs; p += blockDim.x) {
+            for (int p = warp; p < (int)npairs; p += nwarps) {
                 if (s_n[p] == 0) continue;   // a live pair has at least its "no-overlap" row
-                const int ql = p / H.ntx, tl = p % H.ntx;
-                int64_t out = B.q_row_off[H.qbase + ql];
-                for (int k = p - tl; k < p; k++) out += s_n[k];
-                pair_rows<true>(B, H.segs, R, B.q_list[H.qbase + ql], H.x0 + tl, out);
+                const int ql = k + HB_SLICES * (p / H.ntx), tl = p % H.ntx;
+                int before = 0;
+                for (int j = p - tl + lane; j < p; j += 32) before += s_n[j];
+                const int64_t out = B.q_row_off[H.qbase + ql] + warp_sum(before);
+                pair_rows_warp<true>(B, H.segs, R, B.q_list[H.qbase + ql], H.x0 + tl, out, lane);
             }
         } else {
-            for (int ql = threadIdx.x; ql < H.nq; ql += blockDim.x) {
+            for (int qs = warp; qs < nq_slice; qs += nwarps) {
+                const int ql = k + HB_SLICES * qs;
                 const int qx = B.q_list[H.qbase + ql];
                 const int qstart = H.segs[B.tx_seg_off[qx]].start, qend = H.segs[B.tx_seg_off[qx + 1] - 1].end;
                 int64_t out = B.q_row_off[H.qbase + ql];
                 for (int t = H.x0; t < H.x1; t++)
-                    if (pair_live(B, t, H.x1, qstart, qend)) out += pair_rows<true>(B, H.segs, R, qx, t, out);
+                    if (pair_live(B, t, H.x1, qstart, qend)) out += pair_rows_warp<true>(B, H.segs, R, qx, t, out, lane);
             }
         }
-        __syncthreads();   // the rows written above are read below by other threads of this CTA
-        const int64_t r0 = B.q_row_off[H.qbase], r1 = B.q_row_off[H.qbase + H.nq];
-        for (int64_t row = r0 + threadIdx.x; row < r1; row += blockDim.x)
-            process_row(B, R, P, row, hb_view(B, H, R.q_tx[row]), hb_view(B, H, R.t_tx[row]));
         __syncthreads();
     }
 }
 
+// rescue + score of the heavy bundles' rows against the staged chains; one warp per row
+__global__ void __launch_bounds__(HB_THREADS, 2) heavy_rescue_kernel(DevBatch B, DevRows R, orfx_params P, const int32_t* heavy_list,
+                                                                    const unsigned* heavy_count) {
+    extern __shared__ __align__(16) unsigned char hb_smem[];
+    orfx_seg* s_seg = reinterpret_cast<orfx_seg*>(hb_smem);
+    int32_t* s_cum = reinterpret_cast<int32_t*>(hb_smem + (size_t)HB_MAX_SEGS * sizeof(orfx_seg));
+    const unsigned n = *heavy_count * HB_SLICES;
+    const int warp = threadIdx.x >> 5, nwarps = blockDim.x >> 5;
+    for (unsigned w = blockIdx.x; w < n; w += gridDim.x) {
+        const int k = (int)(w % HB_SLICES);
+        const HeavyBundle H = hb_load(B, heavy_list[w / HB_SLICES], s_seg, s_cum, true);
+        const int64_t r0 = B.q_row_off[H.qbase], r1 = B.q_row_off[H.qbase + H.nq];
+        for (int64_t row = r0 + (int64_t)k * nwarps + warp; row < r1; row += (int64_t)HB_SLICES * nwarps)
+            process_row<true>(B, R, P, row, hb_view(B, H, R.q_tx[row]), hb_view(B, H, R.t_tx[row]));
+        __syncthreads();
+    }
+}
+
+constexpr size_t HB_SMEM_PAIRS = (size_t)HB_MAX_SEGS * sizeof(orfx_seg) + (size_t)HB_MAX_PAIRS * sizeof(uint16_t);   // segments + row counts
+constexpr size_t HB_SMEM_ROWS = (size_t)HB_MAX_SEGS * (sizeof(orfx_seg) + sizeof(int32_t));                          // segments + prefixes
+
 int launch_heavy_count(const DevBatch& B, int64_t* cnt, const int32_t* heavy_list, const unsigned* heavy_count, int n_sm, cudaStream_t s) {
     if (B.n_bundles == 0) return 0;
-    cudaFuncSetAttribute(heavy_count_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)HB_SMEM);   // per device
-    heavy_count_kernel<<<min(2 * n_sm, B.n_bundles), HB_THREADS, HB_SMEM, s>>>(B, cnt, heavy_list, heavy_count);
+    cudaFuncSetAttribute(heavy_count_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)HB_SMEM_PAIRS);   // per device
+    heavy_count_kernel<<<(unsigned)std::min<int64_t>(4 * n_sm, (int64_t)B.n_bundles * HB_SLICES), HB_THREADS, HB_SMEM_PAIRS, s>>>(B, cnt, heavy_list, heavy_count);
     return 1;
 }
 int launch_heavy_fill_rescue(const DevBatch& B, const DevRows& R, const orfx_params& P, const int32_t* heavy_list, const unsigned* heavy_count, int n_sm,
                              cudaStream_t s) {
     if (B.n_bundles == 0 || R.n_rows == 0) return 0;
-    cudaFuncSetAttribute(heavy_fill_rescue_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)HB_SMEM);
-    heavy_fill_rescue_kernel<<<min(2 * n_sm, B.n_bundles), HB_THREADS, HB_SMEM, s>>>(B, R, P, heavy_list, heavy_count);
-    return 1;
+    const unsigned grid = (unsigned)std::min<int64_t>(4 * n_sm, (int64_t)B.n_bundles * HB_SLICES);
+    cudaFuncSetAttribute(heavy_fill_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)HB_SMEM_PAIRS);
+    cudaFuncSetAttribute(heavy_rescue_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)HB_SMEM_ROWS);
+    heavy_fill_kernel<<<grid, HB_THREADS, HB_SMEM_PAIRS, s>>>(B, R, heavy_list, heavy_count);
+    heavy_rescue_kernel<<<grid, HB_THREADS, HB_SMEM_ROWS, s>>>(B, R, P, heavy_list, heavy_count);
+    return 2;
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -727,6 +950,54 @@ __global__ void __launch_bounds__(128) clean_templates_kernel(DevBatch B, int n_
 int launch_clean_templates(const DevBatch& B, int n_queries, int rescue, int non_aug, uint8_t* keep, int32_t* out_start, int32_t* out_end, cudaStream_t s) {
     if (n_queries == 0) return 0;
     clean_templates_kernel<<<(n_queries + 127) / 128, 128, 0, s>>>(B, n_queries, rescue, non_aug, keep, out_start, out_end);
+    return 1;
+}
+
+// ------------------------------------------------------------------------------------------------
+// orfcompare: TX::score of every (query CDS, template CDS) pair of a bundle (orfcompare.cpp:76-160)
+// ------------------------------------------------------------------------------------------------
+// compare batch: queries and templates both carry their CDS chain as `segs`.  Pairs are laid out per query
+// (q_row_off, filled by count_pairs_kernel + scan), templates in bundle order; no bounding-box test.
+__global__ void __launch_bounds__(256) count_pairs_kernel(DevBatch B, int64_t* cnt) {
+    const int qi = blockIdx.x * blockDim.x + threadIdx.x;
+    if (qi >= B.n_tx) return;
+    const int64_t nq = B.tx_q_off[B.n_tx];
+    int n = 0;
+    if (qi < nq) {
+        const int b = B.tx_bundle[B.q_list[qi]];
+        for (int x = B.bundle_tx_off[b]; x < B.bundle_tx_off[b + 1]; x++) n += B.tx_kind[x] == ORFX_TX_TEMPLATE;
+    }
+    cnt[qi] = n;
+}
+__global__ void __launch_bounds__(128) score_pairs_kernel(DevBatch B, DevRows R, int n_queries) {
+    const int qi = blockIdx.x * blockDim.x + threadIdx.x;
+    if (qi >= n_queries) return;
+    const int qx = B.q_list[qi];
+    const TxView q = tx_view(B, qx);
+    const int b = B.tx_bundle[qx];
+    int64_t row = B.q_row_off[qi];
+    const int qlen = q.L;
+    const int cs = q.n ? q.segs[0].start : 0, ce = q.n ? q.segs[q.n - 1].end : 0;
+    for (int x = B.bundle_tx_off[b]; x < B.bundle_tx_off[b + 1]; x++) {
+        if (B.tx_kind[x] != ORFX_TX_TEMPLATE) continue;
+        const TxView t = tx_view(B, x);
+        ChainScore c = {0, 0, t.L, 0, 0, 0};
+        if (q.n > 0) c = score_chains<false>(q, t, cs, ce, qlen, q.plus, 0);
+        R.q_tx[row] = qx; R.t_tx[row] = x;
+        R.qlen[row] = qlen; R.tlen[row] = t.L; R.ulen[row] = c.ulen;
+        R.extra[row] = c.extra; R.missing[row] = c.missing; R.match[row] = c.match; R.inframe[row] = c.inframe; R.outframe[row] = c.outframe;
+        R.lpi[row] = pct(qlen, c.ulen); R.ilpi[row] = pct(c.inframe, c.ulen); R.mlpi[row] = pct(c.match, c.ulen);
+        row++;
+    }
+}
+int launch_count_pairs(const DevBatch& B, int64_t* cnt, int64_t* scan_tmp, cudaStream_t s) {
+    if (B.n_tx == 0) { cudaMemsetAsync(B.q_row_off, 0, sizeof(int64_t), s); return 0; }
+    count_pairs_kernel<<<(B.n_tx + 255) / 256, 256, 0, s>>>(B, cnt);
+    return 1 + launch_exclusive_scan(cnt, B.q_row_off, scan_tmp, B.n_tx, s);
+}
+int launch_score_pairs(const DevBatch& B, const DevRows& R, int n_queries, cudaStream_t s) {
+    if (n_queries == 0) return 0;
+    score_pairs_kernel<<<(n_queries + 127) / 128, 128, 0, s>>>(B, R, n_queries);
     return 1;
 }
 
