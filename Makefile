@@ -9,7 +9,7 @@ CXXFLAGS := -O2 -g -std=c++17 -fPIC -Wall -Wextra -Wno-unused-parameter -Iinclud
 NVFLAGS := -O3 -std=c++17 -gencode arch=compute_100a,code=sm_100a -lineinfo -Xcompiler -fPIC -Iinclude \
            -Xptxas -v --expt-relaxed-constexpr
 HOST_SRC := $(wildcard orfanage_b200/csrc/host/*.cpp)
-HOST_OBJ := $(patsubst orfanage_b200/csrc/host/%.cpp,build/host/%.o,$(filter-out %/main.cpp,$(HOST_SRC)))
+HOST_OBJ := $(patsubst orfanage_b200/csrc/host/%.cpp,build/host/%.o,$(filter-out %/main.cpp %/orfcompare_main.cpp,$(HOST_SRC)))
 CU_SRC := $(wildcard orfanage_b200/csrc/*.cu)
 CU_HDR := $(wildcard orfanage_b200/csrc/*.cuh) include/orfx.h include/orfx_codon_table.h
 
@@ -20,7 +20,7 @@ build/host/%.o: orfanage_b200/csrc/host/%.cpp orfanage_b200/csrc/host/orfx_host.
 	@mkdir -p build/host
 	$(CXX) $(CXXFLAGS) -c $< -o $@
 
-cuda: orfanage_b200/liborfx.so orfanage_b200/bin/orfanage
+cuda: orfanage_b200/liborfx.so orfanage_b200/bin/orfanage orfanage_b200/bin/orfcompare
 host: orfanage_b200/liborfx_host.so
 orfanage_b200/liborfx_host.so: $(HOST_OBJ)
 	$(CXX) -shared -o $@ $(HOST_OBJ) -lpthread
@@ -30,6 +30,9 @@ orfanage_b200/liborfx.so: $(CU_SRC) $(CU_HDR)
 orfanage_b200/bin/orfanage: $(HOST_OBJ) build/host/main.o orfanage_b200/liborfx.so
 	@mkdir -p orfanage_b200/bin
 	$(CXX) -o $@ $(HOST_OBJ) build/host/main.o -Lorfanage_b200 -lorfx -Wl,-rpath,'$$ORIGIN/..' -lpthread
+orfanage_b200/bin/orfcompare: $(HOST_OBJ) build/host/orfcompare_main.o orfanage_b200/liborfx.so
+	@mkdir -p orfanage_b200/bin
+	$(CXX) -o $@ $(HOST_OBJ) build/host/orfcompare_main.o -Lorfanage_b200 -lorfx -Wl,-rpath,'$$ORIGIN/..' -lpthread
 build/host/main.o: orfanage_b200/csrc/host/main.cpp orfanage_b200/csrc/host/orfx_host.h include/orfx.h
 	@mkdir -p build/host
 	$(CXX) $(CXXFLAGS) -c $< -o $@

@@ -771,6 +771,48 @@ int orfx_oracle_clean_templates(orfx_ctx* ctx, const orfx_batch* b, int rescue, 
     return ORFX_OK;
 }
 
+// orfcompare oracle: TX::score (Transcriptome.cpp:699-762) of every (query, template) pair of every bundle of a
+// compare batch (see orfx_score_pairs in include/orfx.h); results live in the context until the next call.
+int orfx_oracle_score_pairs(orfx_ctx* ctx, const orfx_batch* b, orfx_results* r) {
+    Ctx* c = reinterpret_cast<Ctx*>(ctx);
+    if (!c || !b || !r) { g_err = "null argument"; return ORFX_E_INVALID; }
+    c->q_tx.clear(); c->t_tx.clear(); c->qlen.clear(); c->tlen.clear(); c->ulen.clear(); c->extra.clear(); c->missing.clear();
+    c->match.clear(); c->outframe.clear(); c->inframe.clear(); c->lpi.clear(); c->ilpi.clear(); c->mlpi.clear();
+    int nq = 0;
+    auto load = [&](int x) {
+        T t;
+        t.strand = (char)b->tx_strand[x];
+        for (int k = b->tx_seg_off[x]; k < b->tx_seg_off[x + 1]; k++) t.cds.push_back(mk((uint32_t)b->segs[k].start, (uint32_t)b->segs[k].end, 0));
+        t.exons = t.cds;
+        t.cds_start = b->tx_cds_start[x]; t.cds_end = b->tx_cds_end[x];
+        return t;
+    };
+    for (int bi = 0; bi < b->n_bundles; bi++) {
+        for (int x = b->bundle_tx_off[bi]; x < b->bundle_tx_off[bi + 1]; x++) {
+            if (b->tx_kind[x] != ORFX_TX_QUERY) continue;
+            nq++;
+            T q = load(x);
+            for (int y = b->bundle_tx_off[bi]; y < b->bundle_tx_off[bi + 1]; y++) {
+                if (b->tx_kind[y] != ORFX_TX_TEMPLATE) continue;
+                T t = load(y);
+                Sc sc;
+                if (!q.cds.empty()) sc = score(q, t);
+                else { sc.tlen = clen(t.cds); sc.missing = sc.tlen; sc.lpi = sc.ilpi = sc.mlpi = 100.0 * (0.0f / 0.0f); }
+                c->q_tx.push_back(x); c->t_tx.push_back(y); c->qlen.push_back(sc.qlen); c->tlen.push_back(sc.tlen); c->ulen.push_back(sc.ulen);
+                c->extra.push_back(sc.extra); c->missing.push_back(sc.missing); c->match.push_back(sc.match); c->outframe.push_back(sc.outframe);
+                c->inframe.push_back(sc.inframe); c->lpi.push_back(sc.lpi); c->ilpi.push_back(sc.ilpi); c->mlpi.push_back(sc.mlpi);
+            }
+        }
+    }
+    memset(r, 0, sizeof *r);
+    r->n_queries = nq;
+    r->n_rows = (int64_t)c->q_tx.size();
+    r->row_q_tx = c->q_tx.data(); r->row_t_tx = c->t_tx.data(); r->row_qlen = c->qlen.data(); r->row_tlen = c->tlen.data(); r->row_ulen = c->ulen.data();
+    r->row_extra = c->extra.data(); r->row_missing = c->missing.data(); r->row_match = c->match.data(); r->row_outframe = c->outframe.data();
+    r->row_inframe = c->inframe.data(); r->row_lpi = c->lpi.data(); r->row_ilpi = c->ilpi.data(); r->row_mlpi = c->mlpi.data();
+    return ORFX_OK;
+}
+
 // Codon-scan oracle: stop / ATG masks of one spliced transcript, bit p = codon starting at spliced
 // position p (5'->3').  Follows SEQ::translate / find_inframe_codon (common.hpp:420-450, 477-495):
 // upper-cased bases, reverse-complemented for non-'+' strands (Transcriptome.cpp:155-171).

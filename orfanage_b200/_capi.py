@@ -440,6 +440,23 @@ class Context:
         assert n_out.value == n
         return keep[:n], cs[:n], ce[:n]
 
+    def score_pairs(self, batch):
+        """orfx_score_pairs on a compare batch: dict of per-pair arrays (q_tx, t_tx, qlen, tlen, ulen, match, inframe,
+        outframe, extra, missing as int32; lpi, ilpi, mlpi as float32), query-major."""
+        r = _Results()
+        f = self._f("score_pairs")
+        f.restype = C.c_int
+        f.argtypes = [C.c_void_p, C.POINTER(_Batch), C.POINTER(_Results)]
+        self._keep = batch
+        self._check(f(self.handle, C.byref(batch.struct), C.byref(r)))
+        n = int(r.n_rows)
+        out = {}
+        for name in ("q_tx", "t_tx", "qlen", "tlen", "ulen", "match", "inframe", "outframe", "extra", "missing"):
+            out[name] = _view(getattr(r, "row_" + name), n, np.int32).copy()
+        for name in ("lpi", "ilpi", "mlpi"):
+            out[name] = _view(getattr(r, "row_" + name), n, np.float32).copy()
+        return out
+
     def int_alu_peak(self):
         """orfx_int_alu_peak: measured integer issue rates of this GPU, operations/s."""
         ops = (C.c_double * 4)()

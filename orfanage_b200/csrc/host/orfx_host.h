@@ -151,12 +151,15 @@ struct PackedBatch {
     void reset();
     orfx_batch view() const;
 };
-// Packs the listed bundles (each must hold a template and a query).  clean_mode = true builds a
+// Packs the listed bundles (each must hold a template and a query).  mode = PACK_CLEAN builds a
 // *cleaning batch* instead (orfx_clean_templates in include/orfx.h): every coding transcript with a CDS
 // chain is packed as ORFX_TX_QUERY with its exon chain and CDS bounds, everything else as ORFX_TX_SKIP.
+// mode = PACK_COMPARE builds a *compare batch* (orfx_score_pairs): queries and templates both carry their
+// CDS chain, no sequence.
+enum { PACK_EVAL = 0, PACK_CLEAN = 1, PACK_COMPARE = 2 };
 void pack_bundles(const Transcriptome& tr, const std::vector<int>& bundle_ids, bool keep_all_cds,
                   const std::map<std::string, int>& tid_classes, PackedBatch& out,
-                  void* (*alloc)(size_t) = nullptr, void (*dealloc)(void*) = nullptr, bool islands = true, bool clean_mode = false);
+                  void* (*alloc)(size_t) = nullptr, void (*dealloc)(void*) = nullptr, bool islands = true, int mode = PACK_EVAL);
 void build_tid_classes(const Transcriptome& tr, std::map<std::string, int>& out);
 // greedy longest-processing-time split of active bundles over n shards
 void shard_bundles(const Transcriptome& tr, const std::vector<int>& active, int n, std::vector<std::vector<int>>& shards);
@@ -173,6 +176,8 @@ struct Backend {
     void (*host_free)(void*);
     // optional (may be NULL): template cleaning, --cleant / --rescue (orfx_clean_templates)
     int (*clean)(orfx_ctx*, const orfx_batch*, int, orfx_clean_out*, int64_t*);
+    // optional (may be NULL): pair scoring for the orfcompare front-end (orfx_score_pairs)
+    int (*score_pairs)(orfx_ctx*, const orfx_batch*, orfx_results*);
 };
 
 // load + template preparation + bundling (orfanage.cpp:313-367)
@@ -180,6 +185,9 @@ struct Backend {
 void prepare_transcriptome(const Options& opt, Fasta& fasta, Transcriptome& tr, bool verbose, const Backend* be = nullptr);
 // replaces run() (orfanage.cpp:307-822): prepares, bundles, evaluates through `be`, writes outputs
 int run_orfanage(const Options& opt, const Backend& be);
+// the companion tool (orfcompare.cpp): argument parsing and run()
+bool parse_compare_cli(int argc, char** argv, Options& opt);
+int run_orfcompare(const Options& opt, const Backend& be);
 
 // emission helpers (orfanage.cpp:662-815)
 struct Emitter {

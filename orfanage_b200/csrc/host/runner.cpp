@@ -74,11 +74,12 @@ void bundle_islands(const Transcriptome& tr, const Bundle& b, bool keep_all_cds,
 // copied by several threads.  islands = true uploads only the bases under query exons.
 void pack_bundles(const Transcriptome& tr, const std::vector<int>& bundle_ids, bool keep_all_cds,
                   const std::map<std::string, int>& tid_classes, PackedBatch& out,
-                  void* (*alloc)(size_t), void (*dealloc)(void*), bool islands, bool clean_mode) {
+                  void* (*alloc)(size_t), void (*dealloc)(void*), bool islands, int mode) {
+    const bool clean_mode = mode == PACK_CLEAN, compare_mode = mode == PACK_COMPARE;
     out.reset();
     out.bundle_ids = bundle_ids;
     const size_t nb = bundle_ids.size();
-    const bool has_seq = tr.fasta != nullptr;
+    const bool has_seq = tr.fasta != nullptr && !compare_mode;
     islands = islands && has_seq;
     size_t total_seq = 0, total_tx = 0, total_segs = 0;
     std::vector<int64_t> bundle_bytes(nb, 0);
@@ -93,7 +94,7 @@ void pack_bundles(const Transcriptome& tr, const std::vector<int>& bundle_ids, b
             total_seq += (size_t)bundle_bytes[j];
         }
         total_tx += (size_t)b.count;
-        for (int i = 0; i < b.count; i++) { const Tx& t = tr.txs[b.first + i]; total_segs += (t.is_templ && !clean_mode) ? t.cds.size() : t.exons.size(); }
+        for (int i = 0; i < b.count; i++) { const Tx& t = tr.txs[b.first + i]; total_segs += ((t.is_templ && !clean_mode) || compare_mode) ? t.cds.size() : t.exons.size(); }
     }
     if (total_tx > (size_t)INT32_MAX || total_segs > (size_t)INT32_MAX) throw std::runtime_error("batch too large for 32-bit transcript / segment indices: shard it");
     auto up = [](size_t x) { return (x + 255) & ~(size_t)255; };
@@ -129,7 +130,7 @@ void pack_bundles(const Transcriptome& tr, const std::vector<int>& bundle_ids, b
             const Tx& t = tr.txs[b.first + i];
             out.tx_global[(size_t)x] = b.first + i;
             const uint8_t kind = tx_kind_of(t, keep_all_cds, clean_mode);
-            const bool as_templ = t.is_templ && !clean_mode;
+            const bool as_templ = (t.is_templ && !clean_mode) || compare_mode;   // carries its CDS chain and bounds
             if (kind == ORFX_TX_QUERY) out.n_queries++;
             out.tx_kind[x] = kind;
             out.tx_strand[x] = (uint8_t)t.strand;
@@ -273,7 +274,7 @@ static size_t clean_cds(const Options& opt, Transcriptome& tr, const Backend& be
     std::map<std::string, int> tid_classes;
     build_tid_classes(tr, tid_classes);
     PackedBatch pb;
-    pack_bundles(tr, ids, false, tid_classes, pb, be.host_alloc, be.host_free, true, true);
+    pack_bundles(tr, ids, false, tid_classes, pb, be.host_alloc, be.host_free, true, PACK_CLEAN);
     orfx_params params;
     fill_params(opt, false, params);
     orfx_ctx* ctx = nullptr;

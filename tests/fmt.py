@@ -53,3 +53,12 @@ def stats_lines(res, tx_id, mode_all=False):
                 out.append("\t".join(f))
             o = oe
     return out
+
+
+def compare_lines(r, names):
+    """orfcompare's first 12 TSV columns for the pairs returned by orfx_score_pairs (floats as operator<< prints them)."""
+    out = []
+    for i in range(len(r["q_tx"])):
+        out.append([names[r["q_tx"][i]], names[r["t_tx"][i]]] + [str(int(r[k][i])) for k in ("qlen", "tlen", "match", "inframe", "outframe",
+                   "extra", "missing")] + ["%g" % r[k][i] for k in ("lpi", "mlpi", "ilpi")])
+    return out

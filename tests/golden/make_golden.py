@@ -50,6 +50,11 @@ SYNTH_RUNS = [
     ("cleant", ["--reference", "genome.fa", "--query", "query.gtf", "--cleant", "--mode", "LONGEST_MATCH,BEST"]),
     ("cleant_rescue", ["--reference", "genome.fa", "--query", "query.gtf", "--cleant", "--rescue"]),
 ]
+CMP_RUNS = [   # orfcompare (reference: oracle/_ref/orfcompare_ref) on the same synthetic inputs
+    ("t2_vs_t1_ref", ["--query", "template2.gtf", "--template", "template1.gtf", "--reference", "genome.fa"]),
+    ("t1_vs_t2", ["--query", "template1.gtf", "--template", "template2.gtf"]),
+    ("t1_vs_t1_id", ["--query", "template1.gtf", "--template", "template1.gtf", "--use_id"]),
+]
 C1_SEED = 20261104
 
 
@@ -85,6 +90,39 @@ def orfcompare_kat():
                             "99.8703", "99.8703"], rows[2]
 
 
+def kat_compare_batch():
+    """The docs' orfcompare example as a packed compare batch (orfx_score_pairs): CDS chains of example/patl.chess3.gtf
+    (queries) and example/patl.gencode.gtf (template), one bundle, so that the known-answer rows can be checked on the
+    GPU box, where /root/reference does not exist."""
+    import re
+    import numpy as np
+
+    def cds_chains(path):
+        tx = {}
+        for l in open(path):
+            f = l.rstrip("\n").split("\t")
+            if len(f) < 9 or f[2] != "CDS":
+                continue
+            tid = re.search(r'transcript_id "([^"]+)"', f[8]).group(1)
+            tx.setdefault(tid, dict(strand=f[6], segs=[]))["segs"].append((int(f[3]), int(f[4])))
+        return tx
+    q = cds_chains(os.path.join(REF, "example", "patl.chess3.gtf"))
+    t = cds_chains(os.path.join(REF, "example", "patl.gencode.gtf"))
+    rows = [l.rstrip("\n").split("\t") for l in open(os.path.join(HERE, "orfcompare_kat.tsv"))][1:]
+    names, kind, strand, seg_off, segs, cs, ce = [], [], [], [0], [], [], []
+    for tid, rec, k in [(r[1], t[r[1]], 1) for r in rows[:1]] + [(r[0], q[r[0]], 0) for r in rows]:
+        names.append(tid); kind.append(k); strand.append(ord(rec["strand"]))
+        ch = sorted(rec["segs"])
+        segs += ch; seg_off.append(len(segs)); cs.append(ch[0][0]); ce.append(ch[-1][1])
+    n = len(names)
+    np.savez_compressed(os.path.join(HERE, "kat_compare_batch.npz"), seq=np.zeros(0, np.uint8), seq_off=np.zeros(2, np.int64),
+                        bundle_start=np.array([min(cs)], np.int32), bundle_tx_off=np.array([0, n], np.int32),
+                        tx_kind=np.array(kind, np.uint8), tx_strand=np.array(strand, np.uint8), tx_seg_off=np.array(seg_off, np.int32),
+                        tx_cds_start=np.array(cs, np.int32), tx_cds_end=np.array(ce, np.int32), tx_tid_class=np.arange(n, dtype=np.int32),
+                        segs=np.array(segs, np.int32), seg_phase=np.zeros(len(segs), np.int8), seg_seq_off=np.zeros(0, np.int32))
+    json.dump({"tx_id": names}, open(os.path.join(HERE, "kat_compare_names.json"), "w"))
+
+
 def config1():
     import orfanage_b200 as ob
     d = "/tmp/orfx_c1"
@@ -115,11 +153,15 @@ def synth_goldens():
             base = os.path.join(HERE, "synth_s%d_%s" % (seed, tag))
             subprocess.run([REF_BIN] + args + ["--threads", "1", "--output", base + ".gtf", "--stats", base + ".tsv"] + tpl,
                            cwd=d, check=True, capture_output=True)
+        for tag, args in CMP_RUNS:
+            subprocess.run([os.path.join(os.path.dirname(REF_BIN), "orfcompare_ref")] + args + ["--threads", "1", "--output",
+                           os.path.join(HERE, "cmp_s%d_%s.tsv" % (seed, tag))], cwd=d, check=True, capture_output=True)
 
 
 if __name__ == "__main__":
     parse_constants()
     orfcompare_kat()
+    kat_compare_batch()
     config1()
     synth_goldens()
     print("goldens written to", HERE)

@@ -232,3 +232,60 @@ def test_template_cleaning_matches_oracle(synth, oracle_lib, gpu, seed, kw):
     gpu.set_params(params)
     assert (gpu.run(batch).best.tobytes() == best.tobytes())
     w.close()
+
+
+@pytest.mark.parametrize("seed,kw", [(41, dict(loci=80, template_files=2)), (42, dict(loci=50, titin=0.2))])
+def test_pair_scoring_matches_oracle(synth, oracle_lib, gpu, seed, kw):
+    """orfcompare's kernel (orfx_score_pairs) against the restated TX::score: every (query, template) pair of every
+    bundle, no bounding-box test; the query exon chains stand in for query CDS chains (titin-class chains included)."""
+    d = synth(seed, **kw)
+    w = ob.Workload(os.path.join(d, "query.gtf"), template_files(d), os.path.join(d, "genome.fa"))
+    batch = w.pack()
+    gpu.set_params(ob.Params.make(mode="BEST"))
+    got = gpu.score_pairs(batch)
+    with ob.Context(ob.Params.make(mode="BEST"), lib=oracle_lib, prefix="orfx_oracle_") as ox:
+        want = ox.score_pairs(batch)
+    assert len(want["q_tx"]) > 500
+    for k in want:
+        assert got[k].tobytes() == want[k].tobytes(), (seed, k)
+    assert (want["match"] == 0).any() and (want["inframe"] < want["match"]).any()
+    w.close()
+
+
+CMP_BIN = os.path.join(ROOT, "oracle", "_ref", "orfcompare_ref")
+
+
+@pytest.mark.parametrize("seed", SYNTH_SEEDS)
+def test_orfcompare_cli_matches_goldens(tmp_path, seed):
+    from golden.make_golden import CMP_RUNS
+    d = str(tmp_path)
+    subprocess.run([os.path.join(ROOT, "tools", "orfx_synth"), "--out", d, "--seed", str(seed)] + SYNTH_ARGS, check=True,
+                   capture_output=True)
+    for tag, args in CMP_RUNS:
+        p = subprocess.run([os.path.join(os.path.dirname(ob.cli_path()), "orfcompare")] + args + ["--output", "g_" + tag + ".tsv"], cwd=d,
+                           capture_output=True)
+        assert p.returncode == 0, p.stderr.decode()[-400:]
+        assert open(os.path.join(d, "g_" + tag + ".tsv"), "rb").read() == open(os.path.join(GOLDEN, "cmp_s%d_%s.tsv" % (seed, tag)), "rb").read(), tag
+
+
+def test_orfcompare_docs_rows_on_the_gpu(gpu):
+    """docs/content/csvs/orfcompare_stats.csv Examples 1-2 (and the two other PATL1 rows): committed compare batch ->
+    orfx_score_pairs -> the reference's own orfcompare rows."""
+    from fmt import compare_lines
+    batch = ob.Batch.load(os.path.join(GOLDEN, "kat_compare_batch.npz"))
+    names = json.load(open(os.path.join(GOLDEN, "kat_compare_names.json")))["tx_id"]
+    want = [l.rstrip("\n").split("\t")[:12] for l in open(os.path.join(GOLDEN, "orfcompare_kat.tsv"))][1:]
+    assert compare_lines(gpu.score_pairs(batch), names) == want
+
+
+@pytest.mark.skipif(not os.path.exists(CMP_BIN), reason="oracle/_ref/orfcompare_ref not shipped")
+def test_orfcompare_cli_byte_identical_to_reference_binary(synth):
+    d = synth(3, loci=150, template_files=3, queries=8)
+    exe = os.path.join(os.path.dirname(ob.cli_path()), "orfcompare")
+    for args in (["--query", "template2.gtf", "--template", "template1.gtf", "--reference", "genome.fa"],
+                 ["--query", "template3.gtf", "--template", "template2.gtf"],
+                 ["--query", "template1.gtf", "--template", "template3.gtf", "--use_id", "--reference", "genome.fa"]):
+        subprocess.run([CMP_BIN] + args + ["--threads", "1", "--output", "cmp_ref.tsv"], cwd=d, check=True, capture_output=True)
+        p = subprocess.run([exe] + args + ["--output", "cmp_gpu.tsv"], cwd=d, capture_output=True)
+        assert p.returncode == 0, p.stderr.decode()[-400:]
+        assert open(os.path.join(d, "cmp_ref.tsv"), "rb").read() == open(os.path.join(d, "cmp_gpu.tsv"), "rb").read(), args

@@ -137,3 +137,46 @@ def test_orfcompare_known_answers():
                         "/root/reference/example/patl.gencode.gtf", "--output", out, "--threads", "1"], check=True,
                        capture_output=True)
         assert open(out).read() == open(os.path.join(GOLDEN, "orfcompare_kat.tsv")).read()
+
+
+# ---- orfcompare -------------------------------------------------------------------
+CMP_REF = os.path.join(ROOT, "oracle", "_ref", "orfcompare_ref")
+
+
+def kat_rows():
+    return [l.rstrip("\n").split("\t")[:12] for l in open(os.path.join(GOLDEN, "orfcompare_kat.tsv"))][1:]
+
+
+def test_orfcompare_oracle_library_reproduces_the_docs_rows(oracle_lib):
+    from fmt import compare_lines
+    batch = ob.Batch.load(os.path.join(GOLDEN, "kat_compare_batch.npz"))
+    names = json.load(open(os.path.join(GOLDEN, "kat_compare_names.json")))["tx_id"]
+    with ob.Context(ob.Params.make(mode="BEST"), lib=oracle_lib, prefix="orfx_oracle_") as ox:
+        assert compare_lines(ox.score_pairs(batch), names) == kat_rows()
+
+
+@pytest.mark.parametrize("seed", SYNTH_SEEDS)
+def test_orfcompare_oracle_cli_matches_goldens(tmp_path, seed):
+    from golden.make_golden import CMP_RUNS
+    d = str(tmp_path)
+    subprocess.run([os.path.join(ROOT, "tools", "orfx_synth"), "--out", d, "--seed", str(seed)] + SYNTH_ARGS, check=True,
+                   capture_output=True)
+    for tag, args in CMP_RUNS:
+        p = subprocess.run([ORACLE_CLI, "orfcompare"] + args + ["--output", "o_" + tag + ".tsv"], cwd=d, capture_output=True)
+        assert p.returncode == 0, p.stderr.decode()[-400:]
+        assert open(os.path.join(d, "o_" + tag + ".tsv"), "rb").read() == open(os.path.join(GOLDEN, "cmp_s%d_%s.tsv" % (seed, tag)), "rb").read(), tag
+
+
+@pytest.mark.skipif(not os.path.exists(CMP_REF), reason="oracle/_ref/orfcompare_ref not built")
+def test_orfcompare_oracle_cli_matches_reference_binary(synth):
+    d = synth(3, loci=150, template_files=3, queries=8)
+    total = 0
+    for args in (["--query", "template2.gtf", "--template", "template1.gtf", "--reference", "genome.fa"],
+                 ["--query", "template3.gtf", "--template", "template2.gtf"],
+                 ["--query", "template1.gtf", "--template", "template3.gtf", "--use_id", "--reference", "genome.fa"]):
+        subprocess.run([CMP_REF] + args + ["--threads", "1", "--output", "cmp_ref.tsv"], cwd=d, check=True, capture_output=True)
+        subprocess.run([ORACLE_CLI, "orfcompare"] + args + ["--output", "cmp_or.tsv"], cwd=d, check=True, capture_output=True)
+        a, b = open(os.path.join(d, "cmp_ref.tsv"), "rb").read(), open(os.path.join(d, "cmp_or.tsv"), "rb").read()
+        assert a == b, args
+        total += a.count(b"\n")
+    assert total > 500
