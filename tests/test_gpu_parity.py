@@ -248,7 +248,7 @@ def test_pair_scoring_matches_oracle(synth, oracle_lib, gpu, seed, kw):
     assert len(want["q_tx"]) > 500
     for k in want:
         assert got[k].tobytes() == want[k].tobytes(), (seed, k)
-    assert (want["match"] == 0).any() and (want["inframe"] < want["match"]).any()
+    assert (want["inframe"] < want["match"]).any() and (want["extra"] > 0).any() and (want["missing"] > 0).any()
     w.close()
 
 
