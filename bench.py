@@ -222,7 +222,7 @@ def ours(args):
     d = generate(cfg, "c2")
     t = time.time()
     w = ob.Workload(os.path.join(d, "query.gtf"), [os.path.join(d, "template.gtf")], os.path.join(d, "genome.fa"))
-    batch = w.pack(0, 1, pinned=True)
+    batch = w.pack(0, 1, pinned=True, layout="islands4")
     nq, nt_sum = batch.n_queries, w.count("query_nt")
     log("rank %d: loaded + packed in %.1f s: %d queries, %d templates, %d bundles, %.1f MB windows, %.1f M spliced nt"
         % (rank, time.time() - t, nq, w.count("templates"), w.count("active_bundles"), batch.arrays["seq"].nbytes / 1e6, nt_sum / 1e6))
@@ -460,7 +460,7 @@ def main():
         "config": {"workload": "GENCODE-scale synthetic (BASELINE.json configs[1])", "mode": MODE,
                    "query_transcripts_per_gpu": m["nq"], "templates_after_dedup": m["n_templates"], "bundles": m["n_bundles"],
                    "genome": "%d x %d bp random, planted ORFs, seed %d+rank" % (m["cfg"]["chroms"], m["cfg"]["chrom_len"], C2["seed"]),
-                   "spliced_query_nt_per_gpu": m["nt_sum"], "bundle_window_bytes_per_gpu": m["windows"],
+                   "spliced_query_nt_per_gpu": m["nt_sum"], "sequence_upload_bytes_per_gpu": m["windows"], "sequence_format": "islands, 4-bit base codes (ORFX_SEQ_NT4)",
                    "parallelism": "locus shards, one per GPU, no collective", "orfs_found": m["found"],
                    "l2": "inputs larger than L2 (windows + chains + masks > 126 MB); no explicit flush",
                    "timing": "CUDA events on the library stream around the whole path, summed over steps, max over ranks",

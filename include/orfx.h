@@ -22,7 +22,7 @@
 extern "C" {
 #endif
 
-#define ORFX_ABI_VERSION 3
+#define ORFX_ABI_VERSION 4
 
 /* error codes */
 #define ORFX_OK            0
@@ -109,7 +109,29 @@ typedef struct orfx_batch {
     const int32_t*  seg_seq_off;   /* [n_segs] or NULL.  Islands layout: for every segment of a QUERY
                                       transcript, the offset of its first base relative to
                                       seq_off[bundle]; ignored for other transcripts               */
+    int32_t seq_format;            /* ORFX_SEQ_RAW: `seq` holds one FASTA byte per base.
+                                      ORFX_SEQ_NT4: two bases per byte (base 2k in the low nibble of byte k),
+                                      ORFX_NT4_* codes; seq_bytes / seq_off / seg_seq_off still count BASES and
+                                      the buffer holds (seq_bytes + 1) / 2 bytes.  Halves the largest upload.
+                                      The codes keep exactly what the path can see of a base: the reference
+                                      upper-cases it and only the codons of codon_map (common.hpp:279) that
+                                      translate to '.' or 'M' steer the path -- TAA TAG TGA TAR TRA and ATG -- so
+                                      A C G T U R Y are told apart and every other byte is "other"            */
+    int32_t reserved0;
 } orfx_batch;
+
+#define ORFX_SEQ_RAW 0
+#define ORFX_SEQ_NT4 1
+/* 4-bit base codes of ORFX_SEQ_NT4 (case-insensitive); U is kept apart from T because the reference only
+ * equates them through ntComplement on the reverse strand */
+#define ORFX_NT4_OTHER 0
+#define ORFX_NT4_A 1
+#define ORFX_NT4_C 2
+#define ORFX_NT4_U 3
+#define ORFX_NT4_G 4
+#define ORFX_NT4_R 5
+#define ORFX_NT4_T 8
+#define ORFX_NT4_Y 10
 
 /* One chosen ORF per query transcript; what orfanage.cpp:753-791 needs to write the GTF. */
 typedef struct orfx_best {

@@ -23,6 +23,7 @@
 #include <cstring>
 #include <map>
 #include <set>
+#include <stdexcept>
 #include <string>
 #include <tuple>
 #include <unordered_set>
@@ -551,6 +552,7 @@ struct BundleSeq {
     BundleSeq(const orfx_batch* b, int bi) {
         bn.bstart = b->bundle_start[bi];
         if (!b->seq) { bn.seq = nullptr; return; }
+        if (b->seq_format == ORFX_SEQ_NT4 && !b->seg_seq_off) throw std::runtime_error("ORFX_SEQ_NT4 is defined for the islands layout only");
         if (!b->seg_seq_off) { bn.seq = b->seq + b->seq_off[bi]; return; }
         int hi = bn.bstart;
         for (int x = b->bundle_tx_off[bi]; x < b->bundle_tx_off[bi + 1]; x++)
@@ -560,6 +562,15 @@ struct BundleSeq {
             if (b->tx_kind[x] != ORFX_TX_QUERY) continue;
             for (int k = b->tx_seg_off[x]; k < b->tx_seg_off[x + 1]; k++) {
                 const orfx_seg& sg = b->segs[k];
+                if (b->seq_format == ORFX_SEQ_NT4) {   // decode the 4-bit codes back to letters ("other" -> N)
+                    static const char LET[16] = {'N', 'A', 'C', 'U', 'G', 'R', 'N', 'N', 'T', 'N', 'Y', 'N', 'N', 'N', 'N', 'N'};
+                    const int64_t base0 = b->seq_off[bi] + b->seg_seq_off[k];
+                    for (int i = 0; i <= sg.end - sg.start; i++) {
+                        const int64_t p = base0 + i;
+                        rebuilt[(size_t)(sg.start - bn.bstart + i)] = LET[(b->seq[p >> 1] >> ((p & 1) * 4)) & 15];
+                    }
+                    continue;
+                }
                 memcpy(&rebuilt[(size_t)(sg.start - bn.bstart)], b->seq + b->seq_off[bi] + b->seg_seq_off[k], (size_t)(sg.end - sg.start + 1));
             }
         }

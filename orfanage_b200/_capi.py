@@ -74,7 +74,7 @@ class _Batch(C.Structure):
                 ("seq", C.c_void_p), ("seq_off", C.c_void_p), ("bundle_start", C.c_void_p), ("bundle_tx_off", C.c_void_p),
                 ("tx_kind", C.c_void_p), ("tx_strand", C.c_void_p), ("tx_seg_off", C.c_void_p), ("tx_cds_start", C.c_void_p),
                 ("tx_cds_end", C.c_void_p), ("tx_tid_class", C.c_void_p), ("segs", C.c_void_p), ("seg_phase", C.c_void_p),
-                ("seg_seq_off", C.c_void_p)]
+                ("seg_seq_off", C.c_void_p), ("seq_format", C.c_int32), ("reserved0", C.c_int32)]
 
 
 class _Best(C.Structure):
@@ -138,6 +138,8 @@ class Batch:
             a = np.ascontiguousarray(a, dtype=dt)
             self.arrays[name] = a
         self.owner = arrays.get("owner")
+        # ORFX_SEQ_NT4 batches: `seq` holds two bases per byte and `seq_bases` counts the bases
+        self.seq_format = int(np.asarray(arrays.get("seq_format", 0)).reshape(-1)[0]) if arrays.get("seq_format") is not None else 0
         a = self.arrays
         if a["segs"].ndim == 1:
             a["segs"] = a["segs"].reshape(-1, 2)
@@ -145,7 +147,8 @@ class Batch:
         s.n_bundles = max(len(a["bundle_tx_off"]) - 1, 0)
         s.n_tx = len(a["tx_kind"])
         s.n_segs = a["segs"].shape[0]
-        s.seq_bytes = a["seq"].size
+        s.seq_bytes = int(np.asarray(arrays["seq_bases"]).reshape(-1)[0]) if self.seq_format == 1 else a["seq"].size
+        s.seq_format = self.seq_format
         for name, _ in _BATCH_ARRAYS:
             arr = a[name]
             setattr(s, name, arr.ctypes.data if arr.size else None)
@@ -165,7 +168,7 @@ class Batch:
     def from_struct(cls, s, owner=None):
         nb, nt, ns = s.n_bundles, s.n_tx, s.n_segs
         arrays = dict(
-            seq=_view(s.seq, s.seq_bytes, np.uint8), seq_off=_view(s.seq_off, nb + 1, np.int64),
+            seq=_view(s.seq, (s.seq_bytes + 1) // 2 if s.seq_format == 1 else s.seq_bytes, np.uint8), seq_off=_view(s.seq_off, nb + 1, np.int64),
             bundle_start=_view(s.bundle_start, nb, np.int32), bundle_tx_off=_view(s.bundle_tx_off, nb + 1, np.int32),
             tx_kind=_view(s.tx_kind, nt, np.uint8), tx_strand=_view(s.tx_strand, nt, np.uint8),
             tx_seg_off=_view(s.tx_seg_off, nt + 1, np.int32), tx_cds_start=_view(s.tx_cds_start, nt, np.int32),
@@ -176,6 +179,7 @@ class Batch:
         b.arrays = arrays
         b.arrays["segs"] = b.arrays["segs"].reshape(-1, 2)
         b.owner = owner
+        b.seq_format = int(s.seq_format)
         cp = _Batch()
         C.memmove(C.byref(cp), C.byref(s), C.sizeof(_Batch))
         b.struct = cp
@@ -197,7 +201,8 @@ class Batch:
         return int(tx_len[a["tx_kind"] == 0].sum())
 
     def save(self, path):
-        np.savez_compressed(path, **self.arrays)
+        extra = dict(seq_format=np.array([1], np.int32), seq_bases=np.array([self.struct.seq_bytes], np.int64)) if self.seq_format == 1 else {}
+        np.savez_compressed(path, **self.arrays, **extra)
 
     @classmethod
     def load(cls, path):
@@ -510,7 +515,7 @@ class Workload:
             dev = load_device_library()
             alloc = C.cast(dev.orfx_host_alloc, C.c_void_p)
             dealloc = C.cast(dev.orfx_host_free, C.c_void_p)
-        rc = self.lib.orfxh_pack(self.handle, shard, n_shards, 1 if layout == "islands" else 0, alloc, dealloc, C.byref(s))
+        rc = self.lib.orfxh_pack(self.handle, shard, n_shards, {"windows": 0, "islands": 1, "islands4": 2}[layout], alloc, dealloc, C.byref(s))
         if rc != 0:
             raise OrfxError(rc, self.lib.orfxh_last_error().decode())
         return Batch.from_struct(s, owner=self)

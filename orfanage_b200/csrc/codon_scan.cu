@@ -87,6 +87,43 @@ __global__ void __launch_bounds__(256) base_planes_kernel(DevBatch B, int64_t n_
         out[B.plane_words] = make_uint4(a, plane_word<FOLD_TU, 0x54545454u>(w), plane_word<FOLD, 0x43434343u>(w), plane_word<FOLD, 0x59595959u>(w));
 }
 
+// Same planes from 4-bit base codes (ORFX_SEQ_NT4: two bases per byte): one 128-bit load per 32 bases.
+namespace {
+template <uint32_t CODE>
+__device__ __forceinline__ uint32_t nibble_eq8(uint32_t w) {   // bit k = (nibble k of w == CODE), k = 0..7
+    const uint32_t y = w ^ (CODE * 0x11111111u);
+    const uint32_t t = ((y & 0x77777777u) + 0x77777777u) | y;
+    uint32_t f = (~t & 0x88888888u) >> 3;           // bit 4k
+    f = (f | (f >> 3)) & 0x03030303u;                // two bits per byte
+    f = (f | (f >> 6)) & 0x000F000Fu;                // four bits per half
+    return (f | (f >> 12)) & 0xFFu;
+}
+template <uint32_t CODE>
+__device__ __forceinline__ uint32_t plane_word4(const uint4& v) {
+    return nibble_eq8<CODE>(v.x) | (nibble_eq8<CODE>(v.y) << 8) | (nibble_eq8<CODE>(v.z) << 16) | (nibble_eq8<CODE>(v.w) << 24);
+}
+}  // namespace
+__global__ void __launch_bounds__(256) base_planes_nt4_kernel(DevBatch B, int64_t n_chunks) {
+    const int64_t chunk = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;   // 32 bases = 16 bytes each
+    const int64_t warp_lo = (chunk & ~(int64_t)31) * 32;
+    if (warp_lo >= B.seq_bytes) return;
+    const int64_t warp_hi = min(warp_lo + 1024, B.seq_bytes);
+    int lo = 0, hi = B.n_bundles - 1;
+    while (lo < hi) {   // last bundle with seq_off <= warp_lo
+        const int mid = (lo + hi + 1) >> 1;
+        if (B.seq_off[mid] <= warp_lo) lo = mid; else hi = mid - 1;
+    }
+    uint32_t need = 0;
+    for (int b = lo; b < B.n_bundles && B.seq_off[b] < warp_hi; b++) need |= B.bundle_need[b];
+    if (chunk >= n_chunks || need == 0) return;
+    const uint4 v = __ldg(reinterpret_cast<const uint4*>(B.seq) + chunk);
+    uint4* out = reinterpret_cast<uint4*>(B.planes) + chunk;
+    const uint32_t a = plane_word4<ORFX_NT4_A>(v);
+    if (need & 1u) out[0] = make_uint4(plane_word4<ORFX_NT4_T>(v), a, plane_word4<ORFX_NT4_G>(v), plane_word4<ORFX_NT4_R>(v));
+    if (need & 2u)
+        out[B.plane_words] = make_uint4(a, plane_word4<ORFX_NT4_T>(v) | plane_word4<ORFX_NT4_U>(v), plane_word4<ORFX_NT4_C>(v), plane_word4<ORFX_NT4_Y>(v));
+}
+
 // ---- 2. planes -> per-transcript stop / start masks ---------------------------------------------------
 // One THREAD per run of SCAN_TILE_WORDS consecutive mask words (256 spliced positions) of one transcript.
 // The thread locates the exon under the run's first position once, then streams: every round appends up
@@ -208,7 +245,8 @@ int launch_base_planes(const DevBatch& B, cudaStream_t stream) {
     if (B.seq_bytes <= 0 || B.n_bundles <= 0) return 0;
     const int64_t n_chunks = (B.seq_bytes + 31) / 32;
     const int64_t threads = (n_chunks + 31) / 32 * 32;
-    base_planes_kernel<<<(unsigned)((threads + 255) / 256), 256, 0, stream>>>(B, n_chunks);
+    if (B.seq_format == ORFX_SEQ_NT4) base_planes_nt4_kernel<<<(unsigned)((threads + 255) / 256), 256, 0, stream>>>(B, n_chunks);
+    else base_planes_kernel<<<(unsigned)((threads + 255) / 256), 256, 0, stream>>>(B, n_chunks);
     return 1;
 }
 

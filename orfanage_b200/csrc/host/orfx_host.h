@@ -143,7 +143,8 @@ struct PackedBatch {
     int8_t* seg_phase = nullptr;
     int32_t* seg_seq_off = nullptr;         // islands layout only
     int32_t n_tx = 0;
-    int64_t n_segs = 0, seq_bytes = 0, n_queries = 0;
+    int64_t n_segs = 0, seq_bytes = 0, n_queries = 0;   // seq_bytes counts bases
+    int32_t seq_format = ORFX_SEQ_RAW;
     PackedBatch() {}
     PackedBatch(const PackedBatch&) = delete;
     PackedBatch& operator=(const PackedBatch&) = delete;
@@ -159,7 +160,8 @@ struct PackedBatch {
 enum { PACK_EVAL = 0, PACK_CLEAN = 1, PACK_COMPARE = 2 };
 void pack_bundles(const Transcriptome& tr, const std::vector<int>& bundle_ids, bool keep_all_cds,
                   const std::map<std::string, int>& tid_classes, PackedBatch& out,
-                  void* (*alloc)(size_t) = nullptr, void (*dealloc)(void*) = nullptr, bool islands = true, int mode = PACK_EVAL);
+                  void* (*alloc)(size_t) = nullptr, void (*dealloc)(void*) = nullptr, bool islands = true, int mode = PACK_EVAL,
+                  bool nt4 = false);   // nt4: islands as 4-bit base codes (ORFX_SEQ_NT4), half the upload
 void build_tid_classes(const Transcriptome& tr, std::map<std::string, int>& out);
 // greedy longest-processing-time split of active bundles over n shards
 void shard_bundles(const Transcriptome& tr, const std::vector<int>& active, int n, std::vector<std::vector<int>>& shards);

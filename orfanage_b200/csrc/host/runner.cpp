@@ -16,7 +16,7 @@ void PackedBatch::reset() {
     if (arena) { if (dealloc) dealloc(arena); else free(arena); }
     arena = nullptr; arena_bytes = 0; dealloc = nullptr;
     bundle_ids.clear(); tx_global.clear();
-    n_tx = 0; n_segs = 0; seq_bytes = 0; n_queries = 0;
+    n_tx = 0; n_segs = 0; seq_bytes = 0; n_queries = 0; seq_format = ORFX_SEQ_RAW;
 }
 
 orfx_batch PackedBatch::view() const {
@@ -39,6 +39,7 @@ orfx_batch PackedBatch::view() const {
     b.segs = segs;
     b.seg_phase = seg_phase;
     b.seg_seq_off = seq_bytes ? seg_seq_off : nullptr;
+    b.seq_format = seq_format;
     return b;
 }
 
@@ -47,6 +48,17 @@ void build_tid_classes(const Transcriptome& tr, std::map<std::string, int>& out)
 }
 
 namespace {
+// ORFX_SEQ_NT4 codes of the 256 byte values (include/orfx.h)
+struct Nt4Table {
+    uint8_t code[256];
+    Nt4Table() {
+        memset(code, ORFX_NT4_OTHER, sizeof code);
+        const char* letters = "ACGTURY";
+        const uint8_t codes[] = {ORFX_NT4_A, ORFX_NT4_C, ORFX_NT4_G, ORFX_NT4_T, ORFX_NT4_U, ORFX_NT4_R, ORFX_NT4_Y};
+        for (int i = 0; letters[i]; i++) { code[(unsigned char)letters[i]] = codes[i]; code[(unsigned char)(letters[i] | 0x20)] = codes[i]; }
+    }
+};
+const Nt4Table NT4;
 // Islands of one bundle: the union of its query exons (what the path reads from the genome when
 // --overhang is 0).  Returns the merged intervals, ascending.
 inline uint8_t tx_kind_of(const Tx& t, bool keep_all_cds, bool clean_mode) {
@@ -74,13 +86,14 @@ void bundle_islands(const Transcriptome& tr, const Bundle& b, bool keep_all_cds,
 // copied by several threads.  islands = true uploads only the bases under query exons.
 void pack_bundles(const Transcriptome& tr, const std::vector<int>& bundle_ids, bool keep_all_cds,
                   const std::map<std::string, int>& tid_classes, PackedBatch& out,
-                  void* (*alloc)(size_t), void (*dealloc)(void*), bool islands, int mode) {
+                  void* (*alloc)(size_t), void (*dealloc)(void*), bool islands, int mode, bool nt4) {
     const bool clean_mode = mode == PACK_CLEAN, compare_mode = mode == PACK_COMPARE;
     out.reset();
     out.bundle_ids = bundle_ids;
     const size_t nb = bundle_ids.size();
     const bool has_seq = tr.fasta != nullptr && !compare_mode;
     islands = islands && has_seq;
+    nt4 = nt4 && islands;
     size_t total_seq = 0, total_tx = 0, total_segs = 0;
     std::vector<int64_t> bundle_bytes(nb, 0);
     std::vector<std::pair<int, int>> isl;
@@ -90,6 +103,7 @@ void pack_bundles(const Transcriptome& tr, const std::vector<int>& bundle_ids, b
             if (islands) {
                 bundle_islands(tr, b, keep_all_cds, clean_mode, isl);
                 for (auto& iv : isl) bundle_bytes[j] += iv.second - iv.first + 1;
+                if (nt4) bundle_bytes[j] += bundle_bytes[j] & 1;   // bundles start on a byte boundary
             } else bundle_bytes[j] = b.bend - b.bstart + 1;
             total_seq += (size_t)bundle_bytes[j];
         }
@@ -98,7 +112,7 @@ void pack_bundles(const Transcriptome& tr, const std::vector<int>& bundle_ids, b
     }
     if (total_tx > (size_t)INT32_MAX || total_segs > (size_t)INT32_MAX) throw std::runtime_error("batch too large for 32-bit transcript / segment indices: shard it");
     auto up = [](size_t x) { return (x + 255) & ~(size_t)255; };
-    size_t o_seq = 0, o_seq_off = o_seq + up(total_seq + 64), o_bstart = o_seq_off + up((nb + 1) * 8), o_btx = o_bstart + up(nb * 4 + 4),
+    size_t o_seq = 0, o_seq_off = o_seq + up((nt4 ? (total_seq + 1) / 2 : total_seq) + 64), o_bstart = o_seq_off + up((nb + 1) * 8), o_btx = o_bstart + up(nb * 4 + 4),
            o_kind = o_btx + up((nb + 1) * 4), o_strand = o_kind + up(total_tx + 4), o_segoff = o_strand + up(total_tx + 4),
            o_cs = o_segoff + up((total_tx + 1) * 4), o_ce = o_cs + up(total_tx * 4 + 4), o_tid = o_ce + up(total_tx * 4 + 4),
            o_segs = o_tid + up(total_tx * 4 + 4), o_phase = o_segs + up(total_segs * 8 + 8), o_sso = o_phase + up(total_segs + 4),
@@ -114,6 +128,7 @@ void pack_bundles(const Transcriptome& tr, const std::vector<int>& bundle_ids, b
     out.tx_tid_class = (int32_t*)(base + o_tid); out.segs = (orfx_seg*)(base + o_segs); out.seg_phase = (int8_t*)(base + o_phase);
     out.seg_seq_off = islands ? (int32_t*)(base + o_sso) : nullptr;
     out.n_tx = (int32_t)total_tx; out.n_segs = (int64_t)total_segs; out.seq_bytes = (int64_t)total_seq;
+    out.seq_format = nt4 ? ORFX_SEQ_NT4 : ORFX_SEQ_RAW;
     out.tx_global.resize(total_tx);
 
     int64_t so = 0;
@@ -153,15 +168,23 @@ void pack_bundles(const Transcriptome& tr, const std::vector<int>& bundle_ids, b
             for (size_t j = j0; j < j1; j++) {
                 const Bundle& b = tr.bundles[bundle_ids[j]];
                 const char* src = chrom[(size_t)b.seqid]->data();
-                uint8_t* dst = out.seq + out.seq_off[j];
+                uint8_t* dst = nt4 ? out.seq + out.seq_off[j] / 2 : out.seq + out.seq_off[j];
                 if (!islands) { memcpy(dst, src + (b.bstart - 1), (size_t)(b.bend - b.bstart + 1)); continue; }
                 bundle_islands(tr, b, keep_all_cds, clean_mode, il);
                 il_off.resize(il.size());
                 int32_t o = 0;
                 for (size_t k = 0; k < il.size(); k++) {
                     il_off[k] = o;
-                    memcpy(dst + o, src + (il[k].first - 1), (size_t)(il[k].second - il[k].first + 1));
-                    o += il[k].second - il[k].first + 1;
+                    const int len = il[k].second - il[k].first + 1;
+                    if (!nt4) memcpy(dst + o, src + (il[k].first - 1), (size_t)len);
+                    else {
+                        const uint8_t* sp = (const uint8_t*)src + (il[k].first - 1);
+                        int i = 0, p = o;
+                        if (p & 1) { dst[p >> 1] = (uint8_t)(dst[p >> 1] | (NT4.code[sp[0]] << 4)); i = 1; p++; }
+                        for (; i + 1 < len; i += 2, p += 2) dst[p >> 1] = (uint8_t)(NT4.code[sp[i]] | (NT4.code[sp[i + 1]] << 4));
+                        if (i < len) dst[p >> 1] = NT4.code[sp[i]];   // low nibble; the high one is OR-ed in by the next island
+                    }
+                    o += len;
                 }
                 // offset of every query segment: the island holding its start
                 for (int xx = out.bundle_tx_off[j]; xx < out.bundle_tx_off[j + 1]; xx++) {
@@ -191,7 +214,7 @@ void pack_bundles(const Transcriptome& tr, const std::vector<int>& bundle_ids, b
             }
             for (auto& t : th) t.join();
         }
-        memset(out.seq + total_seq, 0, 64);
+        memset(out.seq + (nt4 ? (total_seq + 1) / 2 : total_seq), 0, 64);
     }
 }
 
@@ -274,7 +297,7 @@ static size_t clean_cds(const Options& opt, Transcriptome& tr, const Backend& be
     std::map<std::string, int> tid_classes;
     build_tid_classes(tr, tid_classes);
     PackedBatch pb;
-    pack_bundles(tr, ids, false, tid_classes, pb, be.host_alloc, be.host_free, true, PACK_CLEAN);
+    pack_bundles(tr, ids, false, tid_classes, pb, be.host_alloc, be.host_free, true, PACK_CLEAN, true);
     orfx_params params;
     fill_params(opt, false, params);
     orfx_ctx* ctx = nullptr;
@@ -375,7 +398,7 @@ int run_orfanage(const Options& opt, const Backend& be) {
             if (s.rc) { s.err = be.last_error(); return; }
             auto a = clk::now();
             s.ms_create = std::chrono::duration<double, std::milli>(a - c0).count();
-            pack_bundles(tr, shard_ids[k], opt.keep_all_cds, tid_classes, s.batch, be.host_alloc, be.host_free);
+            pack_bundles(tr, shard_ids[k], opt.keep_all_cds, tid_classes, s.batch, be.host_alloc, be.host_free, true, PACK_EVAL, true);
             auto b = clk::now();
             s.ms_pack = std::chrono::duration<double, std::milli>(b - a).count();
             orfx_batch v = s.batch.view();

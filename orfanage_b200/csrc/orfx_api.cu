@@ -124,8 +124,10 @@ int upload_batch(orfx_ctx* c, const orfx_batch* b, bool overlap = false) {
     if (c->P.has_reference && b->seq_bytes > 0 && !b->seq) return fail(ORFX_E_INVALID, "params.has_reference set but batch.seq is NULL");
     cudaStream_t s = c->stream;
     const size_t nb = (size_t)b->n_bundles, nt = (size_t)b->n_tx, ns = (size_t)b->n_segs;
-    const size_t seqb = c->P.has_reference ? (size_t)b->seq_bytes : 0;
-    CU(c->d_seq.ensure(seqb + 64));
+    const size_t seqb = c->P.has_reference ? (size_t)b->seq_bytes : 0;                    // bases
+    if (b->seq_format != ORFX_SEQ_RAW && b->seq_format != ORFX_SEQ_NT4) return fail(ORFX_E_INVALID, "unknown batch.seq_format");
+    const size_t seq_store = b->seq_format == ORFX_SEQ_NT4 ? (seqb + 1) / 2 : seqb;        // bytes behind batch.seq
+    CU(c->d_seq.ensure(seq_store + 64));
     CU(c->d_seq_off.ensure((nb + 1) * 8));
     CU(c->d_bstart.ensure(nb * 4 + 4));
     CU(c->d_btx_off.ensure((nb + 1) * 4));
@@ -142,8 +144,8 @@ int upload_batch(orfx_ctx* c, const orfx_batch* b, bool overlap = false) {
         return cudaMemcpyAsync(d.p, src, bytes, cudaMemcpyHostToDevice, s);
     };
     if (seqb && !overlap) {
-        CU(cp(c->d_seq, b->seq, seqb));
-        CU(cudaMemsetAsync((char*)c->d_seq.p + seqb, 0, 64, s));   // the last aligned 16-byte chunk may read past the end
+        CU(cp(c->d_seq, b->seq, seq_store));
+        CU(cudaMemsetAsync((char*)c->d_seq.p + seq_store, 0, 64, s));   // the last aligned 16-byte chunk may read past the end
     }
     CU(cp(c->d_seq_off, b->seq_off, (nb + 1) * 8));
     CU(cp(c->d_bstart, b->bundle_start, nb * 4));
@@ -162,8 +164,8 @@ int upload_batch(orfx_ctx* c, const orfx_batch* b, bool overlap = false) {
     if (seqb && overlap) {
         CU(cudaEventRecord(c->ev_chains, s));
         CU(cudaStreamWaitEvent(c->copy_stream, c->ev_chains, 0));   // after the chains, and after whatever still reads d_seq
-        CU(cudaMemcpyAsync(c->d_seq.p, b->seq, seqb, cudaMemcpyHostToDevice, c->copy_stream));
-        CU(cudaMemsetAsync((char*)c->d_seq.p + seqb, 0, 64, c->copy_stream));
+        CU(cudaMemcpyAsync(c->d_seq.p, b->seq, seq_store, cudaMemcpyHostToDevice, c->copy_stream));
+        CU(cudaMemsetAsync((char*)c->d_seq.p + seq_store, 0, 64, c->copy_stream));
         CU(cudaEventRecord(c->ev_seq, c->copy_stream));
         c->seq_in_flight = true;
     }
@@ -189,7 +191,7 @@ int upload_batch(orfx_ctx* c, const orfx_batch* b, bool overlap = false) {
     CU(c->h_totals.ensure(64));
     DevBatch& B = c->B;
     memset(&B, 0, sizeof B);
-    B.n_bundles = b->n_bundles; B.n_tx = b->n_tx; B.n_segs = b->n_segs; B.seq_bytes = (int64_t)seqb;
+    B.n_bundles = b->n_bundles; B.n_tx = b->n_tx; B.n_segs = b->n_segs; B.seq_bytes = (int64_t)seqb; B.seq_format = b->seq_format;
     B.seq = c->d_seq.as<uint8_t>(); B.seq_off = c->d_seq_off.as<int64_t>(); B.bundle_start = c->d_bstart.as<int32_t>();
     B.bundle_tx_off = c->d_btx_off.as<int32_t>(); B.tx_kind = c->d_kind.as<uint8_t>(); B.tx_strand = c->d_strand.as<uint8_t>();
     B.tx_seg_off = c->d_seg_off.as<int32_t>(); B.tx_cds_start = c->d_cds_s.as<int32_t>(); B.tx_cds_end = c->d_cds_e.as<int32_t>();

@@ -10,7 +10,8 @@ namespace orfx {
 // (orfx_batch); the others are derived on the device by prep kernels.
 struct DevBatch {
     int32_t n_bundles, n_tx;
-    int64_t n_segs, seq_bytes;
+    int64_t n_segs, seq_bytes;   // seq_bytes counts bases (== bytes unless seq_format == ORFX_SEQ_NT4)
+    int32_t seq_format;
     // [in]
     const uint8_t* seq;
     const int64_t* seq_off;

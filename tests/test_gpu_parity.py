@@ -61,6 +61,10 @@ def test_results_match_oracle_bit_for_bit(synth, oracle_lib, gpu, seed, kw):
         with ob.Context(params, lib=oracle_lib, prefix="orfx_oracle_") as ox:
             assert_same_results(got, ox.run(windows), "windows layout")
             assert_same_results(got, ox.run(w.pack(1, 2, layout="islands")), "windows vs islands")
+            nt4 = w.pack(1, 2, layout="islands4")     # 4-bit base codes: same answers from the kernel and from the oracle
+            assert nt4.seq_format == 1 and nt4.arrays["seq"].size * 2 >= nt4.struct.seq_bytes > nt4.arrays["seq"].size
+            assert_same_results(got, ox.run(nt4), "windows vs islands4 (oracle)")
+            assert_same_results(got, gpu.run(nt4), "windows vs islands4 (kernel)")
     for pk in PARAM_GRID:
         params = ob.Params.make(**pk)
         gpu.set_params(params)
@@ -75,13 +79,14 @@ def test_results_match_oracle_bit_for_bit(synth, oracle_lib, gpu, seed, kw):
     w.close()
 
 
-def test_codon_scan_masks_match_oracle(synth, oracle_lib, gpu):
+@pytest.mark.parametrize("layout", ["islands", "islands4"])
+def test_codon_scan_masks_match_oracle(synth, oracle_lib, gpu, layout):
     """Per-stage check (SURVEY.md §4 iii): stop / ATG masks of every query transcript, soft-masked and
     IUPAC bases included, both strands, against SEQ::translate semantics restated in the oracle."""
     import ctypes as C
     d = synth(24, loci=60, lower=0.5, iupac=0.01, titin=0.1)
     w = ob.Workload(os.path.join(d, "query.gtf"), template_files(d), os.path.join(d, "genome.fa"))
-    batch = w.pack()
+    batch = w.pack(layout=layout)
     gpu.set_params(ob.Params.make(mode="BEST"))
     gpu.upload(batch)
     gpu.run_resident()
