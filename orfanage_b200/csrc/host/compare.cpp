@@ -38,27 +38,27 @@ char complement(char c) {   // ntComplement (gclib), IUPAC, case preserving
 }
 // amino acid of the codon that starts at transcript offset `off` of `chain` (SEQ::translate on the spliced,
 // upper-cased, strand-corrected sequence, common.hpp:477-495)
-char aa_at(const std::string& chrom, const Chain& chain, char strand, int off) {
+char aa_at(const Fasta& fa, const Fasta::Seq& chrom, const Chain& chain, char strand, int off) {
     char c3[3];
     const int L = chain_len(chain);
     size_t n = 0;
     for (int k = 0; k < 3 && off + k < L; k++) {
         const int g = nt2genome(chain, off + k, strand);
-        char b = chrom[(size_t)(g - 1)];
+        char b = fa.at(chrom, g - 1);
         if (strand != '+') b = complement(b);
         c3[n++] = (char)toupper((unsigned char)b);
     }
     return codon_aa(c3, n);
 }
 // first and last amino acid of TX::load_seq()'s translation (Transcriptome.cpp:683-697)
-void end_codons(const std::string& chrom, const Tx& t, char& first, char& last) {
+void end_codons(const Fasta& fa, const Fasta::Seq& chrom, const Tx& t, char& first, char& last) {
     const int s5 = t.strand == '+' ? t.cds_start : t.cds_end, s3 = t.strand == '+' ? t.cds_end : t.cds_start;
     const int a = genome2nt(t.exons, s5, t.strand), b = genome2nt(t.exons, s3, t.strand);
     first = last = '\0';
     if (a < 0 || b < a + 2) return;
     const int naa = (b - a + 1) / 3;
-    first = aa_at(chrom, t.exons, t.strand, a);
-    last = aa_at(chrom, t.exons, t.strand, a + 3 * (naa - 1));
+    first = aa_at(fa, chrom, t.exons, t.strand, a);
+    last = aa_at(fa, chrom, t.exons, t.strand, a + 3 * (naa - 1));
 }
 
 }  // namespace
@@ -151,8 +151,8 @@ int run_orfcompare(const Options& opt, const Backend& be) {
     std::vector<char> c_first(tr.txs.size(), '-'), c_last(tr.txs.size(), '-');
     if (ref) {
         for (const Bundle& b : tr.bundles) {
-            const std::string* chrom = fasta.get(tr.seqnames[(size_t)b.seqid]);
-            for (int i = 0; i < b.count; i++) end_codons(*chrom, tr.txs[(size_t)(b.first + i)], c_first[(size_t)(b.first + i)], c_last[(size_t)(b.first + i)]);
+            const Fasta::Seq* chrom = fasta.find(tr.seqnames[(size_t)b.seqid]);
+            for (int i = 0; i < b.count; i++) end_codons(fasta, *chrom, tr.txs[(size_t)(b.first + i)], c_first[(size_t)(b.first + i)], c_last[(size_t)(b.first + i)]);
         }
     }
     int64_t row = 0;

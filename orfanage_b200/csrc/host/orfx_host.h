@@ -67,15 +67,36 @@ struct GtfRecord {   // one transcript as read from a GTF (what the reference ge
 void read_gtf(const std::string& path, std::vector<GtfRecord>& out);
 
 // --- FASTA ------------------------------------------------------------------------------------
+// The FASTA is memory-mapped and read through its samtools-style index (the .fai next to it when present, else
+// one scan that also writes it, as orfanage.cpp:989-1011 does): only the bases under the bundles are ever touched,
+// a 3 Gb genome is not copied into memory.
 class Fasta {
 public:
+    struct Seq {
+        std::string name;
+        int64_t length = 0, file_off = 0;
+        int line_bases = 0, line_bytes = 0;
+        std::string mem;          // records with ragged lines are held in memory instead
+        bool in_mem = false;
+    };
+    Fasta() {}
+    Fasta(const Fasta&) = delete;
+    Fasta& operator=(const Fasta&) = delete;
+    ~Fasta();
     void load(const std::string& path);
-    const std::string* get(const std::string& name) const;
+    const Seq* find(const std::string& name) const;
+    // copies bases [pos0, pos0 + len) (0-based) of a record into dst
+    void fetch(const Seq& s, int64_t pos0, int64_t len, char* dst) const;
+    char at(const Seq& s, int64_t pos0) const { char c; fetch(s, pos0, 1, &c); return c; }
     bool write_fai_if_missing(const std::string& path) const;
 private:
-    struct Rec { std::string name; std::string seq; int64_t file_off = 0; int line_bases = 0, line_bytes = 0; };
-    std::vector<Rec> recs_;
+    bool read_fai(const std::string& fai);
+    void scan();
+    std::vector<Seq> recs_;
     std::map<std::string, size_t> idx_;
+    const char* data_ = nullptr;
+    size_t size_ = 0;
+    bool fai_was_read_ = false;
 };
 
 struct Bundle {

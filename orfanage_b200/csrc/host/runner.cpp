@@ -160,25 +160,28 @@ void pack_bundles(const Transcriptome& tr, const std::vector<int>& bundle_ids, b
     }
     first_seg[nb] = sg;
     if (has_seq && total_seq) {   // Bundle::load_seq, cpp:821-830
-        std::vector<const std::string*> chrom(tr.seqnames.size(), nullptr);
-        for (size_t k = 0; k < chrom.size(); k++) chrom[k] = tr.fasta->get(tr.seqnames[k]);
+        std::vector<const Fasta::Seq*> chrom(tr.seqnames.size(), nullptr);
+        for (size_t k = 0; k < chrom.size(); k++) chrom[k] = tr.fasta->find(tr.seqnames[k]);
         auto copy_range = [&](size_t j0, size_t j1) {
             std::vector<std::pair<int, int>> il;
             std::vector<int32_t> il_off;
+            std::vector<char> raw;
             for (size_t j = j0; j < j1; j++) {
                 const Bundle& b = tr.bundles[bundle_ids[j]];
-                const char* src = chrom[(size_t)b.seqid]->data();
+                const Fasta::Seq& src = *chrom[(size_t)b.seqid];
                 uint8_t* dst = nt4 ? out.seq + out.seq_off[j] / 2 : out.seq + out.seq_off[j];
-                if (!islands) { memcpy(dst, src + (b.bstart - 1), (size_t)(b.bend - b.bstart + 1)); continue; }
+                if (!islands) { tr.fasta->fetch(src, b.bstart - 1, b.bend - b.bstart + 1, (char*)dst); continue; }
                 bundle_islands(tr, b, keep_all_cds, clean_mode, il);
                 il_off.resize(il.size());
                 int32_t o = 0;
                 for (size_t k = 0; k < il.size(); k++) {
                     il_off[k] = o;
                     const int len = il[k].second - il[k].first + 1;
-                    if (!nt4) memcpy(dst + o, src + (il[k].first - 1), (size_t)len);
+                    if (!nt4) tr.fasta->fetch(src, il[k].first - 1, len, (char*)dst + o);
                     else {
-                        const uint8_t* sp = (const uint8_t*)src + (il[k].first - 1);
+                        raw.resize((size_t)len);
+                        tr.fasta->fetch(src, il[k].first - 1, len, raw.data());
+                        const uint8_t* sp = (const uint8_t*)raw.data();
                         int i = 0, p = o;
                         if (p & 1) { dst[p >> 1] = (uint8_t)(dst[p >> 1] | (NT4.code[sp[0]] << 4)); i = 1; p++; }
                         for (; i + 1 < len; i += 2, p += 2) dst[p >> 1] = (uint8_t)(NT4.code[sp[i]] | (NT4.code[sp[i + 1]] << 4));

@@ -394,7 +394,7 @@ size_t Transcriptome::bundleup(bool use_id, uint32_t overhang) {
         int cur = -1;
         bool ok = false;
         for (Tx& t : txs) {
-            if (t.seqid != cur) { cur = t.seqid; ok = fasta->get(seqnames[cur]) != nullptr; }
+            if (t.seqid != cur) { cur = t.seqid; ok = fasta->find(seqnames[cur]) != nullptr; }
             if (!ok) {
                 if (!t.is_templ) throw std::runtime_error("Reference FASTA is missing sequence for query: " + seqnames[cur]);
             } else valid.push_back(std::move(t));
@@ -405,8 +405,8 @@ size_t Transcriptome::bundleup(bool use_id, uint32_t overhang) {
     if (txs.empty()) return 0;
     auto close_bundle = [&](Bundle& b) {
         if (!fasta) return;
-        const std::string* seq = fasta->get(seqnames[b.seqid]);
-        int seqlen = seq ? (int)seq->size() : 0;
+        const Fasta::Seq* seq = fasta->find(seqnames[b.seqid]);
+        int seqlen = seq ? (int)seq->length : 0;
         int ns = std::max(b.bstart - (int)overhang, 1);
         uint32_t ne = std::min((uint32_t)b.bend + overhang, (uint32_t)seqlen);
         b.bstart = std::min(b.bstart, ns); b.bend = std::max(b.bend, ns);
