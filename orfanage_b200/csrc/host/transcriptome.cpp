@@ -1,6 +1,9 @@
 // Interval chains, transcripts, GTF loading, template preparation and locus bundling.
 // Host mirror of the reference's Transcriptome layer; each function cites what it replaces.
 #include "orfx_host.h"
+#include <thread>
+#include <functional>
+#include <unordered_map>
 #include <algorithm>
 #include <cstring>
 #include <fcntl.h>
@@ -183,22 +186,19 @@ void parse_attr_column(const char* p, const char* end, std::vector<std::pair<Spa
 }
 }  // namespace
 
-void read_gtf(const std::string& path, std::vector<GtfRecord>& out) {
-    int fd = open(path.c_str(), O_RDONLY);
-    if (fd < 0) throw std::runtime_error("Couldn't open the GTF file: " + path);
-    struct stat st;
-    fstat(fd, &st);
-    size_t size = (size_t)st.st_size;
-    const char* data = size ? (const char*)mmap(nullptr, size, PROT_READ, MAP_PRIVATE, fd, 0) : nullptr;
-    if (size && data == MAP_FAILED) { close(fd); throw std::runtime_error("Couldn't map the GTF file: " + path); }
+namespace {
+struct GtfWork { std::vector<std::pair<uint32_t, uint32_t>> cds; std::vector<char> frames; };
+// what one parser thread makes of its slice of the file: records in order of first appearance in the slice
+struct GtfSlice {
+    std::vector<GtfRecord> out;
+    std::vector<GtfWork> work;
+    std::vector<uint8_t> has_tx_row;     // the record's `source` and attrs come from a transcript row of this slice
+    std::unordered_map<std::string, size_t> by_id;
+};
 
-    struct Work { std::vector<std::pair<uint32_t, uint32_t>> cds; std::vector<char> frames; };
-    std::vector<Work> work;
-    std::map<std::string, size_t> by_id;
+void parse_gtf_slice(const char* p, const char* fend, GtfSlice& S) {
+    std::vector<GtfRecord>& out = S.out;
     std::vector<std::pair<Span, Span>> av;
-    size_t base = out.size();
-    const char* p = data;
-    const char* fend = data + size;
     std::string tid;
     size_t last = (size_t)-1;   // rows of one transcript are usually consecutive
     while (p < fend) {
@@ -233,12 +233,13 @@ void read_gtf(const std::string& path, std::vector<GtfRecord>& out) {
                         if (last != (size_t)-1 && out[last].tid.size() == tspan->n && memcmp(out[last].tid.data(), tspan->p, tspan->n) == 0) ri = last;
                         else {
                             tid.assign(tspan->p, tspan->n);
-                            auto it = by_id.find(tid);
-                            if (it == by_id.end()) {
+                            auto it = S.by_id.find(tid);
+                            if (it == S.by_id.end()) {
                                 ri = out.size();
-                                by_id[tid] = ri;
+                                S.by_id[tid] = ri;
                                 out.emplace_back();
-                                work.emplace_back();
+                                S.work.emplace_back();
+                                S.has_tx_row.push_back(0);
                                 GtfRecord& r = out.back();
                                 r.tid = tid;
                                 r.seqname.assign(col[0].p, col[0].n);
@@ -248,12 +249,13 @@ void read_gtf(const std::string& path, std::vector<GtfRecord>& out) {
                             last = ri;
                         }
                         GtfRecord& r = out[ri];
-                        Work& w = work[ri - base];
+                        GtfWork& w = S.work[ri];
                         if (gspan && !r.has_gid) { r.has_gid = true; r.gid.assign(gspan->p, gspan->n); }
                         uint32_t s = (uint32_t)strtoul(col[3].p, nullptr, 10);
                         uint32_t e = (uint32_t)strtoul(col[4].p, nullptr, 10);
                         if (s > e) std::swap(s, e);
                         if (is_tx) {
+                            S.has_tx_row[ri] = 1;
                             r.source.assign(col[1].p, col[1].n);
                             for (auto& kv : av) {
                                 if (eq(kv.first, "transcript_id")) continue;
@@ -272,11 +274,74 @@ void read_gtf(const std::string& path, std::vector<GtfRecord>& out) {
         }
         p = eol + 1;
     }
+}
+}  // namespace
+
+// The file is cut at line starts into one slice per hardware thread; the slices are parsed concurrently and
+// stitched in file order, so that "first appearance" (record order, seqname / strand / gene_id of a record)
+// and the order of a record's rows are what a single pass over the file gives.
+void read_gtf(const std::string& path, std::vector<GtfRecord>& out) {
+    int fd = open(path.c_str(), O_RDONLY);
+    if (fd < 0) throw std::runtime_error("Couldn't open the GTF file: " + path);
+    struct stat st;
+    fstat(fd, &st);
+    size_t size = (size_t)st.st_size;
+    const char* data = size ? (const char*)mmap(nullptr, size, PROT_READ, MAP_PRIVATE, fd, 0) : nullptr;
+    if (size && data == MAP_FAILED) { close(fd); throw std::runtime_error("Couldn't map the GTF file: " + path); }
+
+    unsigned nthr = size > (8u << 20) ? std::min(16u, std::max(1u, std::thread::hardware_concurrency())) : 1u;
+    if (const char* e = getenv("ORFX_GTF_SLICES")) nthr = (unsigned)std::max(1, std::min(64, atoi(e)));   // tests: force slicing of small files
+    std::vector<const char*> cut(nthr + 1, data + size);
+    cut[0] = data;
+    for (unsigned k = 1; k < nthr; k++) {
+        const char* p = data + size / nthr * k;
+        const char* nl = (const char*)memchr(p, '\n', (size_t)(data + size - p));
+        cut[k] = nl ? nl + 1 : data + size;
+    }
+    std::vector<GtfSlice> slices(nthr);
+    if (nthr == 1) parse_gtf_slice(data, data + size, slices[0]);
+    else {
+        std::vector<std::thread> th;
+        for (unsigned k = 0; k < nthr; k++) th.emplace_back(parse_gtf_slice, cut[k], cut[k + 1], std::ref(slices[k]));
+        for (auto& t : th) t.join();
+    }
     if (data) munmap((void*)data, size);
     close(fd);
+
+    const size_t base = out.size();
+    std::vector<GtfWork> work;
+    if (nthr == 1) {
+        for (auto& r : slices[0].out) out.push_back(std::move(r));
+        work = std::move(slices[0].work);
+    } else {
+        std::unordered_map<std::string, size_t> by_id;
+        size_t total = 0;
+        for (auto& S : slices) total += S.out.size();
+        out.reserve(base + total); work.reserve(total); by_id.reserve(total * 2);
+        for (auto& S : slices) {
+            for (size_t i = 0; i < S.out.size(); i++) {
+                GtfRecord& r = S.out[i];
+                auto it = by_id.find(r.tid);
+                if (it == by_id.end()) {
+                    by_id.emplace(r.tid, out.size());
+                    out.push_back(std::move(r));
+                    work.push_back(std::move(S.work[i]));
+                    continue;
+                }
+                GtfRecord& g = out[it->second];   // a transcript whose rows straddle a cut (or are scattered)
+                GtfWork& gw = work[it->second - base];
+                if (!g.has_gid && r.has_gid) { g.has_gid = true; g.gid = r.gid; }
+                if (S.has_tx_row[i]) { g.source = r.source; for (auto& a : r.attrs) g.attrs.push_back(std::move(a)); }
+                g.exons.insert(g.exons.end(), r.exons.begin(), r.exons.end());
+                if (r.has_cds) g.has_cds = true;
+                gw.cds.insert(gw.cds.end(), S.work[i].cds.begin(), S.work[i].cds.end());
+                gw.frames.insert(gw.frames.end(), S.work[i].frames.begin(), S.work[i].frames.end());
+            }
+        }
+    }
     for (size_t i = base; i < out.size(); i++) {
         GtfRecord& r = out[i];
-        Work& w = work[i - base];
+        GtfWork& w = work[i - base];
         if (r.exons.empty()) r.exons = w.cds;
         std::sort(r.exons.begin(), r.exons.end());
         if (r.has_cds) {

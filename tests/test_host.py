@@ -195,3 +195,26 @@ def test_two_rank_sharding_over_gloo(synth, tmp_path, oracle_lib):
         r = cx.run(w.pack())
     assert (found, nq, cs) == (int((r.best["t_tx"] >= 0).sum()), r.n_queries, int(r.best["cds_start"].astype(np.int64).sum()))
     w.close()
+
+
+def test_sliced_gtf_reader_gives_the_single_pass_result(tmp_path):
+    """The GTF reader parses big files in concurrent slices; forced on a small file (cuts fall inside transcripts)
+    it must reproduce the goldens written by the reference."""
+    from conftest import GOLDEN, ORACLE_CLI, run_cli
+    from golden.make_golden import SYNTH_ARGS, SYNTH_RUNS
+    d = str(tmp_path)
+    subprocess.run([os.path.join(ROOT, "tools", "orfx_synth"), "--out", d, "--seed", "101"] + SYNTH_ARGS, check=True, capture_output=True)
+    old = os.environ.get("ORFX_GTF_SLICES")
+    try:
+        for n in ("3", "13"):
+            os.environ["ORFX_GTF_SLICES"] = n
+            for tag, args in SYNTH_RUNS[:2]:
+                rc, gtf, tsv, err = run_cli(ORACLE_CLI, d, args, "s_" + tag, ["template1.gtf", "template2.gtf"])
+                assert rc == 0, err
+                assert gtf == open(os.path.join(GOLDEN, "synth_s101_%s.gtf" % tag), "rb").read(), (n, tag)
+                assert tsv == open(os.path.join(GOLDEN, "synth_s101_%s.tsv" % tag), "rb").read(), (n, tag)
+    finally:
+        if old is None:
+            os.environ.pop("ORFX_GTF_SLICES", None)
+        else:
+            os.environ["ORFX_GTF_SLICES"] = old
