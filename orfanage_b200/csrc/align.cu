@@ -199,7 +199,7 @@ __device__ __forceinline__ void dp_stripe(const int* __restrict__ s_mat, WarpSme
                 if (r < min(stored + 32, tlen)) { const int2 o = ws.out_ring[r & 63]; __stcg(io.h_out + r, o.x); __stcg(io.f_out + r, o.y); }
                 stored += 32;
                 if (PIPE) {
-                    __threadfence();
+                    __threadfence_block();   // reader and writer are warps of one CTA; the edges go through L2 (.cg) on both sides
                     __syncwarp();
                     if (lane == 0) *io.post_flag = io.post_base + (unsigned long long)min(stored, tlen);
                 }
@@ -249,9 +249,12 @@ align_kernel(const uint8_t* __restrict__ aa, const int64_t* __restrict__ off, co
              int32_t* __restrict__ scratch, long long scratch_stride, int32_t* __restrict__ cta_scratch, long long cta_stride,
              unsigned long long* counters) {
     __shared__ int s_mat[25 * MAT_STRIDE];
-    __shared__ unsigned long long s_progress[ALN_WARPS];
-    __shared__ unsigned long long s_slot;
-    __shared__ int s_acc[4];
+    __shared__ unsigned long long s_progress[ALN_WARPS];      // per warp: rows posted, monotone over (pair, stripe, row)
+    __shared__ unsigned long long s_slot_ring[8];             // long pairs taken by this CTA, published by warp 0
+    __shared__ unsigned s_fetched;                            // how many of them are published
+    __shared__ unsigned s_pair_done[4];                       // slot k & 3: k + 1 once pair k's results are written
+    __shared__ int s_acc[4][4];
+    __shared__ unsigned s_cnt[4];
     for (int i = threadIdx.x; i < 25 * MAT_STRIDE; i += blockDim.x) {
         int r = i / MAT_STRIDE, c = i % MAT_STRIDE;
         s_mat[i] = (r < 24 && c < 24) ? (int)c_mat50[r * 24 + c] : PAD_SCORE8;
@@ -260,15 +263,28 @@ align_kernel(const uint8_t* __restrict__ aa, const int64_t* __restrict__ off, co
     const int gapoe = gapo + gape;
     extern __shared__ __align__(16) unsigned char aln_smem[];
     WarpSmem& ws = reinterpret_cast<WarpSmem*>(aln_smem)[wib];
+    if (threadIdx.x < ALN_WARPS) s_progress[threadIdx.x] = 0;
+    if (threadIdx.x < 4) { s_pair_done[threadIdx.x] = 0; s_cnt[threadIdx.x] = 0; s_acc[threadIdx.x][0] = 0; s_acc[threadIdx.x][1] = s_acc[threadIdx.x][2] = s_acc[threadIdx.x][3] = NEG_INF; }
+    if (threadIdx.x == 0) s_fetched = 0;
     __syncthreads();
 
-    // ---- phase A: long pairs, one per CTA at a time ----
-    int32_t* edge = cta_scratch + (long long)blockIdx.x * 4 * cta_stride;   // [parity][h|f][row]
-    while (n_long > 0) {
-        if (threadIdx.x == 0) { s_slot = atomicAdd(counters, 1ULL); s_acc[0] = 0; s_acc[1] = s_acc[2] = s_acc[3] = NEG_INF; }
-        if (lane == 0) s_progress[wib] = 0;
-        __syncthreads();
-        const unsigned long long slot = s_slot;
+    // ---- phase A: long pairs, taken by the CTA one after the other, no CTA-wide barrier ----
+    // Warp w runs stripes w, w + 16, ... of every long pair of the CTA as a software pipeline (stripe k starts as soon
+    // as stripe k-1 has posted its first 32 rows), and goes on to the next pair when its own stripes are done: the fill
+    // of one pair overlaps the drain of the one before.  Edges live in global buffers indexed by (pair parity, stripe
+    // parity); a warp enters pair k only after pair k-2 is complete, which frees those buffers and the result slot.
+    int32_t* edge = cta_scratch + (long long)blockIdx.x * 8 * cta_stride;   // [pair parity][stripe parity][h|f][row]
+    unsigned long long base = 0;
+    for (unsigned k = 0; n_long > 0; k++) {
+        if (k >= 2) { if (lane == 0) while (*(volatile unsigned*)&s_pair_done[(k - 2) & 3] < k - 1) __nanosleep(40); __syncwarp(); }
+        if (wib == 0 && lane == 0) {
+            s_slot_ring[k & 7] = atomicAdd(counters, 1ULL);
+            __threadfence_block();
+            *(volatile unsigned*)&s_fetched = k + 1;
+        }
+        if (lane == 0) while (*(volatile unsigned*)&s_fetched < k + 1) __nanosleep(40);
+        __syncwarp();
+        const unsigned long long slot = *(volatile unsigned long long*)&s_slot_ring[k & 7];
         if (slot >= (unsigned long long)n_long) break;
         const int pair = order[slot];
         const int qi = pair_q[pair], ti = pair_t[pair];
@@ -278,23 +294,38 @@ align_kernel(const uint8_t* __restrict__ aa, const int64_t* __restrict__ off, co
         const int n_stripes = (qlen + 32 * LONG_CPL - 1) / (32 * LONG_CPL);
         AlnAcc acc{0, NEG_INF, NEG_INF, NEG_INF};
         const unsigned long long per = (unsigned long long)tlen + 1ULL;
+        int32_t* edge_k = edge + (long long)(k & 1) * 4 * cta_stride;
         for (int st = wib; st < n_stripes; st += ALN_WARPS) {
             StripeIO io;
-            int32_t* in = edge + (long long)((st + 1) & 1) * 2 * cta_stride;    // written by stripe st-1
-            int32_t* outb = edge + (long long)(st & 1) * 2 * cta_stride;
+            int32_t* in = edge_k + (long long)((st + 1) & 1) * 2 * cta_stride;    // written by stripe st-1
+            int32_t* outb = edge_k + (long long)(st & 1) * 2 * cta_stride;
             io.h_in = st > 0 ? in : nullptr; io.f_in = st > 0 ? in + cta_stride : nullptr;
             io.h_out = st < n_stripes - 1 ? outb : nullptr; io.f_out = st < n_stripes - 1 ? outb + cta_stride : nullptr;
-            io.wait_flag = &s_progress[(wib + ALN_WARPS - 1) % ALN_WARPS]; io.wait_base = (unsigned long long)(st - 1 + 1) * per;
-            io.post_flag = &s_progress[wib]; io.post_base = (unsigned long long)(st + 1) * per;
+            io.wait_flag = &s_progress[(wib + ALN_WARPS - 1) % ALN_WARPS]; io.wait_base = base + (unsigned long long)st * per;
+            io.post_flag = &s_progress[wib]; io.post_base = base + (unsigned long long)(st + 1) * per;
             if (st == n_stripes - 1) dp_stripe<LONG_CPL, true, true>(s_mat, ws, q, t, qlen, tlen, st * 32 * LONG_CPL, gapoe, gape, io, acc, lane);
             else dp_stripe<LONG_CPL, true, false>(s_mat, ws, q, t, qlen, tlen, st * 32 * LONG_CPL, gapoe, gape, io, acc, lane);
             __syncwarp();
         }
-        acc_reduce_warp(acc);
-        if (lane == 0) { atomicMax(&s_acc[0], acc.gmax); atomicMax(&s_acc[1], acc.score); atomicMax(&s_acc[2], acc.mqe); atomicMax(&s_acc[3], acc.mte); }
-        __syncthreads();
-        if (threadIdx.x == 0) { out_max[pair] = s_acc[0]; out_score[pair] = s_acc[1]; out_mqe[pair] = s_acc[2]; out_mte[pair] = s_acc[3]; }
-        __syncthreads();
+        if (wib < n_stripes) {   // this warp had stripes of the pair
+            acc_reduce_warp(acc);
+            if (lane == 0) {
+                int* a = s_acc[k & 3];
+                atomicMax(&a[0], acc.gmax); atomicMax(&a[1], acc.score); atomicMax(&a[2], acc.mqe); atomicMax(&a[3], acc.mte);
+                __threadfence_block();
+                const unsigned old = atomicAdd(&s_cnt[k & 3], 1u);
+                if (old + 1 == (unsigned)min(n_stripes, ALN_WARPS)) {   // last warp of the pair: publish and free the slot
+                    __threadfence_block();
+                    out_max[pair] = atomicExch(&a[0], 0); out_score[pair] = atomicExch(&a[1], NEG_INF);
+                    out_mqe[pair] = atomicExch(&a[2], NEG_INF); out_mte[pair] = atomicExch(&a[3], NEG_INF);
+                    s_cnt[k & 3] = 0;
+                    __threadfence_block();
+                    *(volatile unsigned*)&s_pair_done[k & 3] = k + 1;
+                }
+            }
+        }
+        base += (unsigned long long)(n_stripes + 1) * per;
+        __syncwarp();
     }
 
     // ---- phase B: one warp per pair ----
@@ -438,7 +469,7 @@ int align_batch_device(int device, cudaStream_t stream, const uint8_t* aa, const
         if (!ck(cudaMalloc(&d_order, (size_t)n_pairs * 4), "cudaMalloc order")) { rc = ORFX_E_CUDA; break; }
         if (!ck(cudaMalloc(&d_out, (size_t)n_pairs * 16), "cudaMalloc out")) { rc = ORFX_E_CUDA; break; }
         if (!ck(cudaMalloc(&d_scratch, (size_t)(n_warps * 2 * stride) * 4 + 16), "cudaMalloc scratch")) { rc = ORFX_E_CUDA; break; }
-        if (!ck(cudaMalloc(&d_cta, (size_t)((int64_t)grid * 4 * cta_stride) * 4 + 16), "cudaMalloc cta scratch")) { rc = ORFX_E_CUDA; break; }
+        if (!ck(cudaMalloc(&d_cta, (size_t)((int64_t)grid * 8 * cta_stride) * 4 + 16), "cudaMalloc cta scratch")) { rc = ORFX_E_CUDA; break; }
         if (!ck(cudaMalloc(&d_counter, 16), "cudaMalloc counter")) { rc = ORFX_E_CUDA; break; }
         cudaEventCreate(&e0); cudaEventCreate(&e1);
         if (!ck(cudaMemcpyAsync(d_aa, aa, (size_t)total, cudaMemcpyHostToDevice, stream), "H2D aa")) { rc = ORFX_E_CUDA; break; }

@@ -117,3 +117,40 @@ def test_alignment_empty_inputs(gpu):
     aa = np.array([3, 4, 5], dtype=np.uint8)
     out, _, _ = gpu.align(aa, np.array([0, 3, 3], dtype=np.int64), [0], [1])   # empty target
     assert out["max"][0] == 0
+
+
+def test_alignment_many_long_pairs_share_a_cta(gpu, oracle_lib):
+    """More long pairs than CTAs, of very different shapes (1 to 40 stripes, some finishing before their predecessor),
+    plus short ones: the long pairs of a CTA are pipelined into each other without a CTA barrier, so result slots,
+    progress counters and edge buffers are reused while neighbouring pairs are still in flight."""
+    rng = np.random.default_rng(4242)
+    ql = np.concatenate([rng.integers(1024, 2600, size=380), rng.integers(2600, 10000, size=90), [1024, 1025, 4096, 4097, 256 * 16, 256 * 16 + 1]])
+    rng.shuffle(ql)
+    seqs, pq, pt = [], [], []
+    for L in ql:
+        a = rng.choice(20, size=int(L), p=FREQ).astype(np.uint8)
+        tl = int(max(4194304 // int(L) + 1, rng.integers(300, 5000)))       # >= 4 Mi cells: taken by the block-cooperative phase
+        b = mutate(rng, np.resize(a, tl), rng.uniform(0.05, 0.4), int(rng.integers(0, 4))).astype(np.uint8)
+        pq.append(len(seqs)); seqs.append(a)
+        pt.append(len(seqs)); seqs.append(b)
+    for L in rng.integers(20, 900, size=300):                                # phase B work for the same launch
+        a = rng.choice(20, size=int(L), p=FREQ).astype(np.uint8)
+        pq.append(len(seqs)); seqs.append(a)
+        pt.append(len(seqs)); seqs.append(mutate(rng, a, 0.2, 2).astype(np.uint8))
+    aa = np.concatenate(seqs)
+    off = np.concatenate([[0], np.cumsum([len(s) for s in seqs])]).astype(np.int64)
+    pq, pt = np.array(pq, dtype=np.int32), np.array(pt, dtype=np.int32)
+    out, cells, ms = gpu.align(aa, off, pq, pt)
+    n = len(pq)
+    res = [np.zeros(n, dtype=np.int32) for _ in range(4)]
+    mat = np.ascontiguousarray(MAT, dtype=np.int8)
+    oracle_lib.orfx_oracle_align_batch.restype = C.c_int
+    oracle_lib.orfx_oracle_align_batch(C.c_void_p(aa.ctypes.data), C.c_void_p(off.ctypes.data), C.c_void_p(pq.ctypes.data),
+                                       C.c_void_p(pt.ctypes.data), C.c_int64(n), C.c_void_p(mat.ctypes.data), 24, 12, 2, 0,
+                                       *[C.c_void_p(r.ctypes.data) for r in res])
+    for i, name in enumerate(("max", "score", "mqe", "mte")):
+        bad = np.nonzero(out[name] != res[i])[0]
+        assert len(bad) == 0, "%s differs for %d pairs, first: pair %d (qlen %d, tlen %d)" % (
+            name, len(bad), bad[0], len(seqs[pq[bad[0]]]), len(seqs[pt[bad[0]]]))
+    out2, _, _ = gpu.align(aa, off, pq, pt)                                  # and again: no state left behind
+    assert all((out[k] == out2[k]).all() for k in out)
