@@ -54,7 +54,10 @@ __constant__ int8_t c_mat50[24 * 24] = {
 
 constexpr int NEG_INF = -0x40000000;
 constexpr int MAT_STRIDE = 32;
-constexpr int ALN_WARPS = 16;       // one CTA per SM; its warps work alone on short pairs and as a pipeline on long ones
+#ifndef ORFX_ALN_WARPS
+#define ORFX_ALN_WARPS 16
+#endif
+constexpr int ALN_WARPS = ORFX_ALN_WARPS;       // one CTA per SM; its warps work alone on short pairs and as a pipeline on long ones
 
 struct AlnAcc { int gmax, mqe, mte, score; };
 
@@ -219,18 +222,21 @@ __device__ __forceinline__ void acc_reduce_warp(AlnAcc& a) {
     }
 }
 
-// a whole pair on one warp, stripe after stripe (edges through the warp's global scratch)
-template <int CPL>
+// a whole pair on one warp, stripe after stripe (edges through the warp's global scratch): full stripes of 256
+// columns, then the remainder with the narrowest lane width that covers it (64 / 128 / 256 columns), so that a
+// 300-residue query costs 320 columns of work, not 512
 __device__ __forceinline__ void pair_on_warp(const int* s_mat, WarpSmem& ws, const uint8_t* q, const uint8_t* t, int qlen, int tlen, int gapoe, int gape,
                                              int32_t* hb, int32_t* fb, AlnAcc& acc, int lane) {
-    const int n_stripes = (qlen + 32 * CPL - 1) / (32 * CPL);
-    for (int st = 0; st < n_stripes; st++) {
+    for (int c_base = 0; c_base < qlen; c_base += 256) {
+        const int rem = qlen - c_base;
         StripeIO io;
-        io.h_in = st > 0 ? hb : nullptr; io.f_in = st > 0 ? fb : nullptr;
-        io.h_out = st < n_stripes - 1 ? hb : nullptr; io.f_out = st < n_stripes - 1 ? fb : nullptr;
+        io.h_in = c_base > 0 ? hb : nullptr; io.f_in = c_base > 0 ? fb : nullptr;
+        io.h_out = rem > 256 ? hb : nullptr; io.f_out = rem > 256 ? fb : nullptr;
         io.wait_flag = io.post_flag = nullptr; io.wait_base = io.post_base = 0;
-        if (st == n_stripes - 1) dp_stripe<CPL, false, true>(s_mat, ws, q, t, qlen, tlen, st * 32 * CPL, gapoe, gape, io, acc, lane);
-        else dp_stripe<CPL, false, false>(s_mat, ws, q, t, qlen, tlen, st * 32 * CPL, gapoe, gape, io, acc, lane);
+        if (rem > 256) dp_stripe<8, false, false>(s_mat, ws, q, t, qlen, tlen, c_base, gapoe, gape, io, acc, lane);
+        else if (rem <= 64) dp_stripe<2, false, true>(s_mat, ws, q, t, qlen, tlen, c_base, gapoe, gape, io, acc, lane);
+        else if (rem <= 128) dp_stripe<4, false, true>(s_mat, ws, q, t, qlen, tlen, c_base, gapoe, gape, io, acc, lane);
+        else dp_stripe<8, false, true>(s_mat, ws, q, t, qlen, tlen, c_base, gapoe, gape, io, acc, lane);
         __syncwarp();
     }
 }
@@ -347,9 +353,7 @@ align_kernel(const uint8_t* __restrict__ aa, const int64_t* __restrict__ off, co
             continue;
         }
         AlnAcc acc{0, NEG_INF, NEG_INF, NEG_INF};
-        if (qlen <= 64) pair_on_warp<2>(s_mat, ws, q, t, qlen, tlen, gapoe, gape, hb, fb, acc, lane);
-        else if (qlen <= 128) pair_on_warp<4>(s_mat, ws, q, t, qlen, tlen, gapoe, gape, hb, fb, acc, lane);
-        else pair_on_warp<8>(s_mat, ws, q, t, qlen, tlen, gapoe, gape, hb, fb, acc, lane);
+        pair_on_warp(s_mat, ws, q, t, qlen, tlen, gapoe, gape, hb, fb, acc, lane);
         acc_reduce_warp(acc);
         if (lane == 0) { out_max[pair] = acc.gmax; out_score[pair] = acc.score; out_mqe[pair] = acc.mqe; out_mte[pair] = acc.mte; }
     }

@@ -11,7 +11,13 @@ if len(sys.argv) > 2:   # keep pairs shorter than this (steady-state captures wi
     keep = np.nonzero((off[pq + 1] - off[pq]) < int(sys.argv[2]))[0]
     pq, pt = pq[keep], pt[keep]
     n = len(pq)
-with ob.Context(ob.Params.make(), device=0) as cx:
+lib = ob.load_device_library(os.environ["ORFX_LIB"]) if os.environ.get("ORFX_LIB") else None   # a variant build of liborfx.so
+with ob.Context(ob.Params.make(), device=0, lib=lib) as cx:
     cx.align(aa, off, pq[:64], pt[:64])
-    out, cells, ms = cx.align(aa, off, pq, pt)
+    best = None
+    for _ in range(3):
+        out, cells, ms = cx.align(aa, off, pq, pt)
+        best = ms if best is None else min(best, ms)
+    ms = best
+    print(os.environ.get("ORFX_LIB", "liborfx.so"), end=" ")
     print("pairs %d cells %.4g ms %.3f GCUPS %.1f" % (n, cells, ms, cells / ms / 1e6))
