@@ -18,9 +18,11 @@ int launch_fill_tiles(const DevBatch& B, cudaStream_t s);
 int launch_count_rows(const DevBatch& B, int64_t* cnt, int64_t* scan_tmp, const int32_t* heavy_list, const unsigned* heavy_count, int n_sm, cudaStream_t s);
 int launch_fill_rows(const DevBatch& B, const DevRows& R, int n_queries, cudaStream_t s);
 int launch_rescue_score(const DevBatch& B, const DevRows& R, const orfx_params& P, cudaStream_t s);
-int launch_heavy_fill_rescue(const DevBatch& B, const DevRows& R, const orfx_params& P, const int32_t* heavy_list, const unsigned* heavy_count, int n_sm,
-                             cudaStream_t s);
-int launch_select(const DevBatch& B, const DevRows& R, const orfx_params& P, int n_queries, orfx_best* best_out, int32_t* ord_scratch, cudaStream_t s);
+int launch_heavy_fill(const DevBatch& B, const DevRows& R, const int32_t* heavy_list, const unsigned* heavy_count, int n_sm, cudaStream_t s);
+int launch_heavy_rescue(const DevBatch& B, const DevRows& R, const orfx_params& P, const int32_t* heavy_list, const unsigned* heavy_count, int n_sm,
+                        cudaStream_t s);
+int launch_select(const DevBatch& B, const DevRows& R, const orfx_params& P, int n_queries, orfx_best* best_out, int32_t* ord_scratch, int4* key_scratch,
+                  cudaStream_t s);
 void launch_codon_scan(const DevBatch& B, int64_t n_tiles, int n_sm, cudaStream_t stream);
 int launch_base_planes(const DevBatch& B, cudaStream_t stream);
 int launch_clean_templates(const DevBatch& B, int n_queries, int rescue, int non_aug, uint8_t* keep, int32_t* out_start, int32_t* out_end, cudaStream_t s);
@@ -97,7 +99,7 @@ struct orfx_ctx {
     DBuf d_seg_cum, d_tx_len, d_tx_bundle, d_mask_off, d_tile_off, d_q_off, d_q_list, d_row_off, d_tile_tx, d_stop, d_start;
     DBuf d_need, d_planes, d_heavy, d_heavy_count;
     DBuf d_cnt_q, d_cnt_words, d_cnt_tiles, d_cnt_rows, d_scan_tmp, d_ord;
-    DBuf d_clean_keep, d_clean_s, d_clean_e;
+    DBuf d_clean_keep, d_clean_s, d_clean_e, d_keys;
     // rows
     DBuf r_i32[16], r_f32[3], r_u8[3], r_order, d_best;
     HBuf h_totals, h_best, h_i32[16], h_f32[3], h_u8[3], h_order;
@@ -250,6 +252,7 @@ int run_path(orfx_ctx* c) {
     CU(c->r_order.ensure((size_t)nrows * 8 + 8));
     if (nrows > (int64_t)INT32_MAX) return fail(ORFX_E_INVALID, "more than 2^31 candidate rows in one batch: shard it");
     CU(c->d_ord.ensure((size_t)nrows * 4 + 4));
+    CU(c->d_keys.ensure((size_t)nrows * 64 + 16));
     CU(c->d_best.ensure((size_t)nq * sizeof(orfx_best) + 8));
     DevRows& R = c->R;
     R.n_rows = nrows;
@@ -262,6 +265,7 @@ int run_path(orfx_ctx* c) {
 
     stage_begin(c, ST_FILL);
     c->n_launches += launch_fill_rows(B, R, (int)nq, s);
+    c->n_launches += launch_heavy_fill(B, R, c->d_heavy.as<int32_t>(), c->d_heavy_count.as<unsigned>(), c->n_sm, s);
     stage_end(c, ST_FILL);
     if (c->seq_in_flight) { CU(cudaStreamWaitEvent(s, c->ev_seq, 0)); c->seq_in_flight = false; }
     stage_begin(c, ST_PLANES);
@@ -277,13 +281,13 @@ int run_path(orfx_ctx* c) {
     }
     stage_end(c, ST_SCAN);
     stage_begin(c, ST_HEAVY);
-    c->n_launches += launch_heavy_fill_rescue(B, R, c->P, c->d_heavy.as<int32_t>(), c->d_heavy_count.as<unsigned>(), c->n_sm, s);
+    c->n_launches += launch_heavy_rescue(B, R, c->P, c->d_heavy.as<int32_t>(), c->d_heavy_count.as<unsigned>(), c->n_sm, s);
     stage_end(c, ST_HEAVY);
     stage_begin(c, ST_RESCUE);
     c->n_launches += launch_rescue_score(B, R, c->P, s);
     stage_end(c, ST_RESCUE);
     stage_begin(c, ST_SELECT);
-    c->n_launches += launch_select(B, R, c->P, (int)nq, c->d_best.as<orfx_best>(), c->d_ord.as<int32_t>(), s);
+    c->n_launches += launch_select(B, R, c->P, (int)nq, c->d_best.as<orfx_best>(), c->d_ord.as<int32_t>(), c->d_keys.as<int4>(), s);
     stage_end(c, ST_SELECT);
     cudaEventRecord(c->run_ev[1], s);
     CU(cudaGetLastError());
@@ -436,7 +440,7 @@ void orfx_destroy(orfx_ctx* c) {
     DBuf* d[] = {&c->d_sso, &c->d_seq, &c->d_seq_off, &c->d_bstart, &c->d_btx_off, &c->d_kind, &c->d_strand, &c->d_seg_off, &c->d_cds_s, &c->d_cds_e, &c->d_tid,
                  &c->d_segs, &c->d_phase, &c->d_seg_cum, &c->d_tx_len, &c->d_tx_bundle, &c->d_mask_off, &c->d_tile_off, &c->d_q_off, &c->d_q_list,
                  &c->d_row_off, &c->d_tile_tx, &c->d_stop, &c->d_start, &c->d_need, &c->d_planes, &c->d_heavy, &c->d_heavy_count, &c->d_cnt_q, &c->d_cnt_words, &c->d_cnt_tiles, &c->d_cnt_rows, &c->d_scan_tmp,
-                 &c->d_ord, &c->r_order, &c->d_best, &c->d_clean_keep, &c->d_clean_s, &c->d_clean_e};
+                 &c->d_ord, &c->r_order, &c->d_best, &c->d_clean_keep, &c->d_clean_s, &c->d_clean_e, &c->d_keys};
     for (DBuf* b : d) b->free_();
     for (auto& b : c->r_i32) b.free_();
     for (auto& b : c->r_f32) b.free_();

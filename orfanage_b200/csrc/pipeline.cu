@@ -88,23 +88,26 @@ int64_t scan_tmp_elems(int64_t n) { return (n + SCAN_BLOCK - 1) / SCAN_BLOCK + 1
 // ------------------------------------------------------------------------------------------------
 // prep
 // ------------------------------------------------------------------------------------------------
-// one warp per transcript: coalesced segment loads, warp scan of the segment lengths
+// eight lanes per transcript (a chain has ~10 segments): coalesced segment loads, group scan of the segment lengths
+constexpr int PREP_LANES = 8;
 __global__ void __launch_bounds__(256) tx_prep_kernel(DevBatch B, int64_t* cnt_q, int64_t* cnt_words, int64_t* cnt_tiles) {
-    const int tx = (int)(((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5), lane = threadIdx.x & 31;
-    if (tx >= B.n_tx) return;
+    const int64_t gt = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int tx = (int)(gt / PREP_LANES), sub = (int)(gt % PREP_LANES);
+    if (tx >= B.n_tx) return;   // whole groups leave together
+    const unsigned gmask = ((1u << PREP_LANES) - 1u) << ((threadIdx.x & 31) & ~(PREP_LANES - 1));
     const int s0 = B.tx_seg_off[tx], s1 = B.tx_seg_off[tx + 1];
     int acc = 0;
-    for (int base = s0; base < s1; base += 32) {
-        const int k = base + lane;
+    for (int base = s0; base < s1; base += PREP_LANES) {
+        const int k = base + sub;
         int len = 0;
         if (k < s1) { const orfx_seg sg = B.segs[k]; len = sg.end - sg.start + 1; }
         int incl = len;
 #pragma unroll
-        for (int d = 1; d < 32; d <<= 1) { const int v = __shfl_up_sync(0xffffffffu, incl, d); if (lane >= d) incl += v; }
+        for (int d = 1; d < PREP_LANES; d <<= 1) { const int v = __shfl_up_sync(gmask, incl, d, PREP_LANES); if (sub >= d) incl += v; }
         if (k < s1) B.seg_cum[k] = acc + incl - len;
-        acc += __shfl_sync(0xffffffffu, incl, 31);
+        acc += __shfl_sync(gmask, incl, PREP_LANES - 1, PREP_LANES);
     }
-    if (lane != 0) return;
+    if (sub != 0) return;
     B.tx_len[tx] = acc;
     bool isq = B.tx_kind[tx] == ORFX_TX_QUERY;
     const int64_t words = acc > 0 ? (acc + 31) / 32 : 1;
@@ -157,7 +160,7 @@ int launch_prep(const DevBatch& B, int64_t* cnt_q, int64_t* cnt_words, int64_t* 
                 cudaStream_t s) {
     int n = 0;
     if (B.n_tx == 0) return 0;
-    tx_prep_kernel<<<(unsigned)(((int64_t)B.n_tx * 32 + 255) / 256), 256, 0, s>>>(B, cnt_q, cnt_words, cnt_tiles); n++;
+    tx_prep_kernel<<<(unsigned)(((int64_t)B.n_tx * PREP_LANES + 255) / 256), 256, 0, s>>>(B, cnt_q, cnt_words, cnt_tiles); n++;
     cudaMemsetAsync(heavy_count, 0, sizeof(unsigned), s);
     bundle_prep_kernel<<<(B.n_bundles + 127) / 128, 128, 0, s>>>(B, heavy_list, heavy_count); n++;
     n += launch_exclusive_scan(cnt_q, B.tx_q_off, scan_tmp, B.n_tx, s);
@@ -185,8 +188,8 @@ __device__ __forceinline__ void put_row(const DevRows& R, int64_t at, int qx, in
 // share intron boundaries; one row per span, or one "no-overlap" row.  FILL = false only counts.
 // `segs` is B.segs or a shared-memory copy of the bundle's segments biased to accept the same absolute
 // indices.  Same visiting order and state as the reference's double loop at O(exons + segments) per pair.
-template <bool FILL>
-__device__ int pair_rows(const DevBatch& B, const orfx_seg* segs, const DevRows& R, int qx, int t, int64_t out) {
+template <class Emit>
+__device__ __forceinline__ int pair_rows_core(const DevBatch& B, const orfx_seg* segs, int qx, int t, Emit&& emit) {
     const int q0 = B.tx_seg_off[qx], q1 = B.tx_seg_off[qx + 1];
     const int t0 = B.tx_seg_off[t], t1 = B.tx_seg_off[t + 1];
     int nseg = 0, cur_s = 0, cur_e = 0, n = 0;
@@ -211,7 +214,7 @@ __device__ int pair_rows(const DevBatch& B, const orfx_seg* segs, const DevRows&
                 const bool ends_match = ie == s1.end && s1.end == c2.end;
                 const bool starts_match = is == s1.start && s1.start == c2.start;
                 if (!continue_prev || !starts_match) {
-                    if (nseg > 0) { if (FILL) put_row(R, out + n, qx, t, cur_s, cur_e, ORFX_ST_OK); n++; }
+                    if (nseg > 0) { emit(n, cur_s, cur_e, ORFX_ST_OK); n++; }
                     nseg++;
                     cur_s = is; cur_e = ie;
                 } else {
@@ -230,9 +233,24 @@ __device__ int pair_rows(const DevBatch& B, const orfx_seg* segs, const DevRows&
             }
         }
     }
-    if (nseg > 0) { if (FILL) put_row(R, out + n, qx, t, cur_s, cur_e, ORFX_ST_OK); n++; }
-    else { if (FILL) put_row(R, out + n, qx, t, -1, -1, ORFX_ST_NO_OVERLAP); n++; }
+    if (nseg > 0) { emit(n, cur_s, cur_e, ORFX_ST_OK); n++; }
+    else { emit(n, -1, -1, ORFX_ST_NO_OVERLAP); n++; }
     return n;
+}
+template <bool FILL>
+__device__ int pair_rows(const DevBatch& B, const orfx_seg* segs, const DevRows& R, int qx, int t, int64_t out) {
+    if (FILL) return pair_rows_core(B, segs, qx, t, [&](int i, int s, int e, int st) { put_row(R, out + i, qx, t, s, e, st); });
+    return pair_rows_core(B, segs, qx, t, [](int, int, int, int) {});
+}
+// one walk: the first ROWS_BUF rows of the pair are kept in registers (nearly every pair has one or two)
+constexpr int ROWS_BUF = 3;
+struct RowBuf { int s[ROWS_BUF], e[ROWS_BUF]; int st0; };
+__device__ __forceinline__ int pair_rows_buffered(const DevBatch& B, const orfx_seg* segs, int qx, int t, RowBuf& rb) {
+    return pair_rows_core(B, segs, qx, t, [&](int i, int s, int e, int st) {
+#pragma unroll
+        for (int k = 0; k < ROWS_BUF; k++) if (i == k) { rb.s[k] = s; rb.e[k] = e; }
+        if (i == 0) rb.st0 = st;
+    });
 }
 
 // does template slot t of the query's bundle take part?  (bounding box, orfanage.cpp:500-503)
@@ -286,11 +304,17 @@ __global__ void __launch_bounds__(256) fill_rows_kernel(DevBatch B, DevRows R, i
     for (int it = 0; it < rounds; it++) {
         const int t = x0 + it * ROWS_GROUP + sub;
         const bool live = valid && pair_live(B, t, x1, qstart, qend);
-        const int n = live ? pair_rows<false>(B, B.segs, R, qx, t, 0) : 0;
+        RowBuf rb;
+        const int n = live ? pair_rows_buffered(B, B.segs, qx, t, rb) : 0;
         int incl = n;
 #pragma unroll
         for (int d = 1; d < ROWS_GROUP; d <<= 1) { const int v = __shfl_up_sync(0xffffffffu, incl, d, ROWS_GROUP); if (sub >= d) incl += v; }
-        if (live) pair_rows<true>(B, B.segs, R, qx, t, out + incl - n);
+        if (live) {
+            if (n <= ROWS_BUF) {   // a "no-overlap" pair has exactly one row; every other row is ORFX_ST_OK
+#pragma unroll
+                for (int k = 0; k < ROWS_BUF; k++) if (k < n) put_row(R, out + incl - n + k, qx, t, rb.s[k], rb.e[k], k == 0 ? rb.st0 : ORFX_ST_OK);
+            } else pair_rows<true>(B, B.segs, R, qx, t, out + incl - n);
+        }
         out += __shfl_sync(0xffffffffu, incl, ROWS_GROUP - 1, ROWS_GROUP);
     }
 }
@@ -887,15 +911,22 @@ int launch_heavy_count(const DevBatch& B, int64_t* cnt, const int32_t* heavy_lis
     heavy_count_kernel<<<(unsigned)std::min<int64_t>(4 * n_sm, (int64_t)B.n_bundles * HB_SLICES), HB_THREADS, HB_SMEM_PAIRS, s>>>(B, cnt, heavy_list, heavy_count);
     return 1;
 }
-int launch_heavy_fill_rescue(const DevBatch& B, const DevRows& R, const orfx_params& P, const int32_t* heavy_list, const unsigned* heavy_count, int n_sm,
-                             cudaStream_t s) {
+// candidate rows of the heavy bundles: needs the chains only (runs while the sequence is still being uploaded)
+int launch_heavy_fill(const DevBatch& B, const DevRows& R, const int32_t* heavy_list, const unsigned* heavy_count, int n_sm, cudaStream_t s) {
     if (B.n_bundles == 0 || R.n_rows == 0) return 0;
     const unsigned grid = (unsigned)std::min<int64_t>(4 * n_sm, (int64_t)B.n_bundles * HB_SLICES);
     cudaFuncSetAttribute(heavy_fill_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)HB_SMEM_PAIRS);
-    cudaFuncSetAttribute(heavy_rescue_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)HB_SMEM_ROWS);
     heavy_fill_kernel<<<grid, HB_THREADS, HB_SMEM_PAIRS, s>>>(B, R, heavy_list, heavy_count);
+    return 1;
+}
+// rescue + score of those rows: needs the codon-scan masks
+int launch_heavy_rescue(const DevBatch& B, const DevRows& R, const orfx_params& P, const int32_t* heavy_list, const unsigned* heavy_count, int n_sm,
+                        cudaStream_t s) {
+    if (B.n_bundles == 0 || R.n_rows == 0) return 0;
+    const unsigned grid = (unsigned)std::min<int64_t>(4 * n_sm, (int64_t)B.n_bundles * HB_SLICES);
+    cudaFuncSetAttribute(heavy_rescue_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)HB_SMEM_ROWS);
     heavy_rescue_kernel<<<grid, HB_THREADS, HB_SMEM_ROWS, s>>>(B, R, P, heavy_list, heavy_count);
-    return 2;
+    return 1;
 }
 
 // ------------------------------------------------------------------------------------------------

@@ -8,44 +8,67 @@ namespace orfx {
 
 namespace {
 
-struct ScoreGt {   // score_gt, orfanage.cpp:204-245, on row indices relative to `base`
-    const DevRows* R;
-    const orfx_params* P;
-    int64_t base;
-    __device__ bool operator()(int a, int b) const {
-        const int64_t l = base + a, r = base + b;
-        if (R->pass[l] != R->pass[r]) return R->pass[l] > R->pass[r];
-        for (int i = 0; i < P->n_modes; i++) {
-            switch (P->mode_array[i]) {
-                case ORFX_MODE_START_MATCH: if (R->start_match[l] != R->start_match[r]) return R->start_match[l] > R->start_match[r]; break;
-                case ORFX_MODE_LONGEST: if (R->qlen[l] != R->qlen[r]) return R->qlen[l] > R->qlen[r]; break;
-                case ORFX_MODE_LONGEST_MATCH: if (R->inframe[l] != R->inframe[r]) return R->inframe[l] > R->inframe[r]; break;
-                case ORFX_MODE_BEST: if (R->ilpi[l] != R->ilpi[r]) return R->ilpi[l] > R->ilpi[r]; break;
-                case ORFX_MODE_FIRST: if (R->query_start[l] != R->query_start[r]) return R->query_start[l] < R->query_start[r]; break;
-                default: break;   // ALL: only relevant at emission
-            }
+// Sort key of one candidate row, written once per row and read by the comparators as three 128-bit loads (the
+// fields live in ~10 separate SoA arrays; a comparison on those is a dozen dependent scattered loads, and the rows of
+// a titin-class query are compared hundreds of times).
+//   k[0] pass; k[1 .. n_modes] one value per --mode entry, larger = better; k[9] tlen; k[10], k[11] the ORF key;
+//   k[12] transcript_id class of the row's template
+struct __align__(16) RowKey { int k[16]; };
+
+__device__ __forceinline__ RowKey make_key(const DevBatch& B, const DevRows& R, const orfx_params& P, int64_t row) {
+    RowKey K;
+#pragma unroll
+    for (int i = 0; i < 16; i++) K.k[i] = 0;
+    K.k[12] = B.tx_tid_class[R.t_tx[row]];
+    K.k[0] = R.pass[row];
+    for (int i = 0; i < P.n_modes && i < 8; i++) {
+        int v = 0;
+        switch (P.mode_array[i]) {
+            case ORFX_MODE_START_MATCH: v = R.start_match[row]; break;
+            case ORFX_MODE_LONGEST: v = R.qlen[row]; break;
+            case ORFX_MODE_LONGEST_MATCH: v = R.inframe[row]; break;
+            case ORFX_MODE_BEST: v = __float_as_int(R.ilpi[row]); break;   // ilpi >= +0: the bit pattern orders like the float
+            case ORFX_MODE_FIRST: v = -R.query_start[row]; break;          // smaller query_start is better
+            default: break;                                                 // ALL: only relevant at emission
         }
-        return R->tlen[l] > R->tlen[r];
+        K.k[1 + i] = v;
+    }
+    K.k[9] = R.tlen[row]; K.k[10] = R.cds_start[row]; K.k[11] = R.cds_end[row];
+    return K;
+}
+
+struct ScoreGt {   // score_gt, orfanage.cpp:204-245, on row indices relative to the query's first row
+    const RowKey* keys;
+    int n_modes;
+    __device__ bool operator()(int a, int b) const {
+        const int4* pa = reinterpret_cast<const int4*>(keys + a);
+        const int4* pb = reinterpret_cast<const int4*>(keys + b);
+        const int4 a0 = pa[0], b0 = pb[0], a1 = pa[1], b1 = pb[1], a2 = pa[2], b2 = pb[2];
+        const int l[10] = {a0.x, a0.y, a0.z, a0.w, a1.x, a1.y, a1.z, a1.w, a2.x, a2.y};
+        const int r[10] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w, b2.x, b2.y};
+        if (l[0] != r[0]) return l[0] > r[0];
+#pragma unroll
+        for (int i = 1; i <= 8; i++) if (i <= n_modes && l[i] != r[i]) return l[i] > r[i];
+        return l[9] > r[9];
     }
 };
 struct KeyLess {   // std::map<std::pair<int,int>,...> order, rows of one key kept in candidate order
-    const DevRows* R;
-    int64_t base;
+    const RowKey* keys;
     __device__ bool operator()(int a, int b) const {
-        const int64_t l = base + a, r = base + b;
-        if (R->cds_start[l] != R->cds_start[r]) return R->cds_start[l] < R->cds_start[r];
-        if (R->cds_end[l] != R->cds_end[r]) return R->cds_end[l] < R->cds_end[r];
+        const int2 l = *reinterpret_cast<const int2*>(&keys[a].k[10]), r = *reinterpret_cast<const int2*>(&keys[b].k[10]);
+        if (l.x != r.x) return l.x < r.x;
+        if (l.y != r.y) return l.y < r.y;
         return a < b;
     }
 };
 
 // distinct template transcript_id strings among rows ord[g0..g1)
-__device__ int count_distinct_tids(const DevBatch& B, const DevRows& R, int64_t base, const int32_t* ord, int g0, int g1) {
+__device__ int count_distinct_tids(const RowKey* keys, const int32_t* ord, int g0, int g1) {
     int n = 0;
     for (int i = g0; i < g1; i++) {
-        const int c = B.tx_tid_class[R.t_tx[base + ord[i]]];
+        const int c = keys[ord[i]].k[12];
         bool seen = false;
-        for (int j = g0; j < i && !seen; j++) seen = B.tx_tid_class[R.t_tx[base + ord[j]]] == c;
+        for (int j = g0; j < i && !seen; j++) seen = keys[ord[j]].k[12] == c;
         if (!seen) n++;
     }
     return n;
@@ -53,7 +76,8 @@ __device__ int count_distinct_tids(const DevBatch& B, const DevRows& R, int64_t 
 
 }  // namespace
 
-__global__ void __launch_bounds__(128) select_kernel(DevBatch B, DevRows R, orfx_params P, int n_queries, orfx_best* best_out, int32_t* ord_scratch) {
+__global__ void __launch_bounds__(128) select_kernel(DevBatch B, DevRows R, orfx_params P, int n_queries, orfx_best* best_out, int32_t* ord_scratch,
+                                                      int4* key_scratch) {
     const int qi = blockIdx.x * blockDim.x + threadIdx.x;
     if (qi >= n_queries) return;
     const int64_t r0 = B.q_row_off[qi], r1 = B.q_row_off[qi + 1];
@@ -79,20 +103,21 @@ __global__ void __launch_bounds__(128) select_kernel(DevBatch B, DevRows R, orfx
             if (!R.pass[r0 + i] && (st == ORFX_ST_OK || st == ORFX_ST_DUP)) { R.cds_start[r0 + i] = 0; R.cds_end[r0 + i] = 0; }
         }
     }
-    for (int i = 0; i < n; i++) ord[i] = i;
-    stdsort::sort(ord, ord + n, KeyLess{&R, r0});
+    RowKey* keys = reinterpret_cast<RowKey*>(key_scratch) + r0;
+    for (int i = 0; i < n; i++) { ord[i] = i; keys[i] = make_key(B, R, P, r0 + i); }
+    stdsort::sort(ord, ord + n, KeyLess{keys});
 
-    const ScoreGt gt{&R, &P, r0};
+    const ScoreGt gt{keys, min(P.n_modes, 8)};
     const bool mode_all = P.n_modes > 0 && P.mode_array[0] == ORFX_MODE_ALL;
     int best_front = -1, best_g0 = 0, best_g1 = 0;
     for (int g0 = 0; g0 < n;) {
         int g1 = g0 + 1;
-        const int ks = R.cds_start[r0 + ord[g0]], ke = R.cds_end[r0 + ord[g0]];
-        while (g1 < n && R.cds_start[r0 + ord[g1]] == ks && R.cds_end[r0 + ord[g1]] == ke) g1++;
+        const int ks = keys[ord[g0]].k[10], ke = keys[ord[g0]].k[11];
+        while (g1 < n && keys[ord[g1]].k[10] == ks && keys[ord[g1]].k[11] == ke) g1++;
         stdsort::sort(ord + g0, ord + g1, gt);
         const int front = ord[g0];
         if (best_front < 0 || gt(front, best_front)) { best_front = front; best_g0 = g0; best_g1 = g1; }   // find_best_stat
-        if (mode_all && R.pass[r0 + front] && g1 - g0 > 1) R.n_dup[r0 + front] = count_distinct_tids(B, R, r0, ord, g0, g1);
+        if (mode_all && R.pass[r0 + front] && g1 - g0 > 1) R.n_dup[r0 + front] = count_distinct_tids(keys, ord, g0, g1);
         g0 = g1;
     }
     orfx_best b;
@@ -101,7 +126,7 @@ __global__ void __launch_bounds__(128) select_kernel(DevBatch B, DevRows R, orfx
     b.lpi = b.ilpi = b.mlpi = 0.f; b.start_match = 0;
     if (best_front >= 0 && R.pass[r0 + best_front]) {
         const int64_t rb = r0 + best_front;
-        if (!mode_all) R.n_dup[rb] = count_distinct_tids(B, R, r0, ord, best_g0 + 1, best_g1);
+        if (!mode_all) R.n_dup[rb] = count_distinct_tids(keys, ord, best_g0 + 1, best_g1);
         b.t_tx = R.t_tx[rb]; b.cds_start = R.cds_start[rb]; b.cds_end = R.cds_end[rb];
         b.duplicity = R.n_dup[rb]; b.best_row = rb;
         b.lpi = R.lpi[rb]; b.ilpi = R.ilpi[rb]; b.mlpi = R.mlpi[rb]; b.start_match = R.start_match[rb];
@@ -110,9 +135,10 @@ __global__ void __launch_bounds__(128) select_kernel(DevBatch B, DevRows R, orfx
     for (int i = 0; i < n; i++) R.print_order[r0 + i] = r0 + ord[i];
 }
 
-int launch_select(const DevBatch& B, const DevRows& R, const orfx_params& P, int n_queries, orfx_best* best_out, int32_t* ord_scratch, cudaStream_t s) {
+int launch_select(const DevBatch& B, const DevRows& R, const orfx_params& P, int n_queries, orfx_best* best_out, int32_t* ord_scratch, int4* key_scratch,
+                  cudaStream_t s) {
     if (n_queries == 0) return 0;
-    select_kernel<<<(n_queries + 127) / 128, 128, 0, s>>>(B, R, P, n_queries, best_out, ord_scratch);
+    select_kernel<<<(n_queries + 127) / 128, 128, 0, s>>>(B, R, P, n_queries, best_out, ord_scratch, key_scratch);
     return 1;
 }
 
