@@ -252,7 +252,7 @@ int run_path(orfx_ctx* c) {
     CU(c->r_order.ensure((size_t)nrows * 8 + 8));
     if (nrows > (int64_t)INT32_MAX) return fail(ORFX_E_INVALID, "more than 2^31 candidate rows in one batch: shard it");
     CU(c->d_ord.ensure((size_t)nrows * 4 + 4));
-    CU(c->d_keys.ensure((size_t)nrows * 64 + 16));
+    CU(c->d_keys.ensure((size_t)nrows * 48 + 16));
     CU(c->d_best.ensure((size_t)nq * sizeof(orfx_best) + 8));
     DevRows& R = c->R;
     R.n_rows = nrows;
@@ -333,6 +333,20 @@ void fill_results(orfx_ctx* c, orfx_results* r) {
     }
 }
 
+// A repeated --mode entry never decides a comparison (the first occurrence already did): drop the repeats, so that
+// the device sees at most the six distinct modes.
+orfx_params canonical_params(const orfx_params& in) {
+    orfx_params p = in;
+    int n = 0;
+    for (int i = 0; i < in.n_modes; i++) {
+        bool seen = false;
+        for (int j = 0; j < n; j++) seen = seen || p.mode_array[j] == in.mode_array[i];
+        if (!seen) p.mode_array[n++] = in.mode_array[i];
+    }
+    p.n_modes = n;
+    return p;
+}
+
 int check_params(const orfx_params* p) {
     if (!p) return fail(ORFX_E_INVALID, "null params");
     if (p->n_modes < 0 || p->n_modes > 8) return fail(ORFX_E_INVALID, "n_modes out of range");
@@ -373,7 +387,7 @@ int orfx_create(orfx_ctx** out, int device, const orfx_params* params) {
     orfx_ctx* c = new orfx_ctx();
     c->device = device;
     c->n_sm = prop.multiProcessorCount;
-    c->P = *params;
+    c->P = canonical_params(*params);
     if (cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking) != cudaSuccess ||
         cudaStreamCreateWithFlags(&c->copy_stream, cudaStreamNonBlocking) != cudaSuccess) { delete c; return fail(ORFX_E_CUDA, "cudaStreamCreate failed"); }
     cudaEventCreateWithFlags(&c->ev_chains, cudaEventDisableTiming);
@@ -389,7 +403,7 @@ int orfx_set_params(orfx_ctx* c, const orfx_params* params) {
     if (!c) return fail(ORFX_E_INVALID, "null ctx");
     int rc = check_params(params);
     if (rc) return rc;
-    c->P = *params;
+    c->P = canonical_params(*params);
     return ORFX_OK;
 }
 

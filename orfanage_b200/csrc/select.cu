@@ -11,17 +11,21 @@ namespace {
 // Sort key of one candidate row, written once per row and read by the comparators as three 128-bit loads (the
 // fields live in ~10 separate SoA arrays; a comparison on those is a dozen dependent scattered loads, and the rows of
 // a titin-class query are compared hundreds of times).
-//   k[0] pass; k[1 .. n_modes] one value per --mode entry, larger = better; k[9] tlen; k[10], k[11] the ORF key;
-//   k[12] transcript_id class of the row's template
-struct __align__(16) RowKey { int k[16]; };
+//   k[0] pass; k[1 .. n_modes] one value per --mode entry (at most 7), larger = better; k[8] transcript_id class of the
+//   row's template; k[9] tlen; k[10], k[11] the ORF key
+// The records of a block's queries are contiguous (rows are laid out query by query): they are kept in shared memory
+// while they fit, so that the comparisons of the std::sort replay cost a shared-memory load, not an L2 round trip.
+struct __align__(16) RowKey { int k[12]; };
+constexpr int SEL_THREADS = 128;
+constexpr int SEL_SMEM_ROWS = 768;     // 36 KB of keys + 3 KB of order per block
 
 __device__ __forceinline__ RowKey make_key(const DevBatch& B, const DevRows& R, const orfx_params& P, int64_t row) {
     RowKey K;
 #pragma unroll
-    for (int i = 0; i < 16; i++) K.k[i] = 0;
-    K.k[12] = B.tx_tid_class[R.t_tx[row]];
+    for (int i = 0; i < 12; i++) K.k[i] = 0;
+    K.k[8] = B.tx_tid_class[R.t_tx[row]];
     K.k[0] = R.pass[row];
-    for (int i = 0; i < P.n_modes && i < 8; i++) {
+    for (int i = 0; i < P.n_modes && i < 7; i++) {
         int v = 0;
         switch (P.mode_array[i]) {
             case ORFX_MODE_START_MATCH: v = R.start_match[row]; break;
@@ -48,7 +52,7 @@ struct ScoreGt {   // score_gt, orfanage.cpp:204-245, on row indices relative to
         const int r[10] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w, b2.x, b2.y};
         if (l[0] != r[0]) return l[0] > r[0];
 #pragma unroll
-        for (int i = 1; i <= 8; i++) if (i <= n_modes && l[i] != r[i]) return l[i] > r[i];
+        for (int i = 1; i <= 7; i++) if (i <= n_modes && l[i] != r[i]) return l[i] > r[i];
         return l[9] > r[9];
     }
 };
@@ -66,9 +70,9 @@ struct KeyLess {   // std::map<std::pair<int,int>,...> order, rows of one key ke
 __device__ int count_distinct_tids(const RowKey* keys, const int32_t* ord, int g0, int g1) {
     int n = 0;
     for (int i = g0; i < g1; i++) {
-        const int c = keys[ord[i]].k[12];
+        const int c = keys[ord[i]].k[8];
         bool seen = false;
-        for (int j = g0; j < i && !seen; j++) seen = keys[ord[j]].k[12] == c;
+        for (int j = g0; j < i && !seen; j++) seen = keys[ord[j]].k[8] == c;
         if (!seen) n++;
     }
     return n;
@@ -76,13 +80,17 @@ __device__ int count_distinct_tids(const RowKey* keys, const int32_t* ord, int g
 
 }  // namespace
 
-__global__ void __launch_bounds__(128) select_kernel(DevBatch B, DevRows R, orfx_params P, int n_queries, orfx_best* best_out, int32_t* ord_scratch,
+__global__ void __launch_bounds__(SEL_THREADS) select_kernel(DevBatch B, DevRows R, orfx_params P, int n_queries, orfx_best* best_out, int32_t* ord_scratch,
                                                       int4* key_scratch) {
+    __shared__ RowKey s_keys[SEL_SMEM_ROWS];
+    __shared__ int32_t s_ord[SEL_SMEM_ROWS];
     const int qi = blockIdx.x * blockDim.x + threadIdx.x;
     if (qi >= n_queries) return;
     const int64_t r0 = B.q_row_off[qi], r1 = B.q_row_off[qi + 1];
     const int n = (int)(r1 - r0);
-    int32_t* ord = ord_scratch + r0;
+    const int64_t block_r0 = B.q_row_off[blockIdx.x * blockDim.x];
+    const bool in_smem = r1 - block_r0 <= SEL_SMEM_ROWS;      // this query's rows fit the block's stage
+    int32_t* ord = in_smem ? s_ord + (r0 - block_r0) : ord_scratch + r0;
 
     // duplicate ORFs inside one (query, template) pair: std::unordered_set<int> orf_starts keyed on the
     // genomic cds_start of every row that reaches the check (orfanage.cpp:516, 622-627)
@@ -103,11 +111,11 @@ __global__ void __launch_bounds__(128) select_kernel(DevBatch B, DevRows R, orfx
             if (!R.pass[r0 + i] && (st == ORFX_ST_OK || st == ORFX_ST_DUP)) { R.cds_start[r0 + i] = 0; R.cds_end[r0 + i] = 0; }
         }
     }
-    RowKey* keys = reinterpret_cast<RowKey*>(key_scratch) + r0;
+    RowKey* keys = in_smem ? s_keys + (r0 - block_r0) : reinterpret_cast<RowKey*>(key_scratch) + r0;
     for (int i = 0; i < n; i++) { ord[i] = i; keys[i] = make_key(B, R, P, r0 + i); }
     stdsort::sort(ord, ord + n, KeyLess{keys});
 
-    const ScoreGt gt{keys, min(P.n_modes, 8)};
+    const ScoreGt gt{keys, min(P.n_modes, 7)};
     const bool mode_all = P.n_modes > 0 && P.mode_array[0] == ORFX_MODE_ALL;
     int best_front = -1, best_g0 = 0, best_g1 = 0;
     for (int g0 = 0; g0 < n;) {
@@ -138,7 +146,7 @@ __global__ void __launch_bounds__(128) select_kernel(DevBatch B, DevRows R, orfx
 int launch_select(const DevBatch& B, const DevRows& R, const orfx_params& P, int n_queries, orfx_best* best_out, int32_t* ord_scratch, int4* key_scratch,
                   cudaStream_t s) {
     if (n_queries == 0) return 0;
-    select_kernel<<<(n_queries + 127) / 128, 128, 0, s>>>(B, R, P, n_queries, best_out, ord_scratch, key_scratch);
+    select_kernel<<<(n_queries + SEL_THREADS - 1) / SEL_THREADS, SEL_THREADS, 0, s>>>(B, R, P, n_queries, best_out, ord_scratch, key_scratch);
     return 1;
 }
 

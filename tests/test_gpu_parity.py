@@ -294,3 +294,43 @@ def test_orfcompare_cli_byte_identical_to_reference_binary(synth):
         p = subprocess.run([exe] + args + ["--output", "cmp_gpu.tsv"], cwd=d, capture_output=True)
         assert p.returncode == 0, p.stderr.decode()[-400:]
         assert open(os.path.join(d, "cmp_ref.tsv"), "rb").read() == open(os.path.join(d, "cmp_gpu.tsv"), "rb").read(), args
+
+
+def test_full_size_properties(oracle_lib, gpu):
+    """BASELINE.json configs[1] at full size (20 000 loci, ~236 k query transcripts; the bench's workload, generated on the
+    box), checked through size-independent properties: the run is idempotent, the answer does not depend on how the loci
+    are sharded (loci are independent: 1 shard == 3 shards stitched back by transcript id), the chosen ORFs are whole
+    codons, and the first 300 bundles are bit-identical to the oracle."""
+    import bench
+    d = bench.generate(dict(bench.C2), "c2")
+    w = ob.Workload(os.path.join(d, "query.gtf"), [os.path.join(d, "template.gtf")], os.path.join(d, "genome.fa"))
+    params = ob.Params.make(mode=bench.MODE, want_rows=False)
+    gpu.set_params(params)
+    full = w.pack(0, 1, layout="islands4")
+    assert full.n_queries > 200000
+    r1 = gpu.run(full).best
+    r2 = gpu.run(full).best
+    assert r1.tobytes() == r2.tobytes(), "not idempotent"
+    found = r1["t_tx"] >= 0
+    assert found.mean() > 0.9
+    assert ((r1["cds_end"][found] >= r1["cds_start"][found]) & (r1["cds_start"][found] > 0)).all()
+    # sharding invariance: per transcript id, the same ORF and scores from 3 locus shards as from one batch
+    def by_id(best, shard):
+        ids = [w.tx_id(int(t), shard) for t in best["q_tx"]]
+        return dict(zip(ids, zip(best["cds_start"].tolist(), best["cds_end"].tolist(), best["n_rows"].tolist(), best["duplicity"].tolist(),
+                                 best["ilpi"].view(np.uint32).tolist(), (best["t_tx"] >= 0).tolist())))
+    whole = by_id(r1, 0)
+    assert len(whole) == len(r1)
+    stitched = {}
+    for k in range(3):
+        part = w.pack(k, 3, layout="islands4")
+        stitched.update(by_id(gpu.run(part).best, k))
+    assert stitched == whole
+    # the first 300 bundles against the oracle
+    w.truncate(300)
+    head = w.pack(0, 1, layout="islands4")
+    got = gpu.run(head).best
+    with ob.Context(params, lib=oracle_lib, prefix="orfx_oracle_") as ox:
+        want = ox.run(head).best
+    assert got.tobytes() == want.tobytes() and len(got) > 3000
+    w.close()
