@@ -16,8 +16,8 @@ namespace {
 // The records of a block's queries are contiguous (rows are laid out query by query): they are kept in shared memory
 // while they fit, so that the comparisons of the std::sort replay cost a shared-memory load, not an L2 round trip.
 struct __align__(16) RowKey { int k[12]; };
-constexpr int SEL_THREADS = 128;
-constexpr int SEL_SMEM_ROWS = 768;     // 36 KB of keys + 3 KB of order per block
+constexpr int SEL_THREADS = 64;
+constexpr int SEL_SMEM_ROWS = 640;     // 30 KB of keys + 2.5 KB of order per block (a block's queries hold ~270 rows on average)
 
 __device__ __forceinline__ RowKey make_key(const DevBatch& B, const DevRows& R, const orfx_params& P, int64_t row) {
     RowKey K;

@@ -103,6 +103,7 @@ template <class T, class Cmp>
 ORFX_HD inline void sort(T* first, T* last, Cmp comp, int depth_override = -1) {
     const long n = last - first;
     if (n <= 0) return;
+    if (n <= 16) { insertion_sort(first, last, comp); return; }   // the introsort loop does nothing below the threshold
     int lg = 0;
     for (long m = n; m > 1; m >>= 1) lg++;
     int depth0 = depth_override >= 0 ? depth_override : 2 * lg;
