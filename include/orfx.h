@@ -22,7 +22,7 @@
 extern "C" {
 #endif
 
-#define ORFX_ABI_VERSION 4
+#define ORFX_ABI_VERSION 5
 
 /* error codes */
 #define ORFX_OK            0
@@ -64,8 +64,11 @@ typedef struct orfx_params {
     int32_t lpi, ilpi, mlpi;    /* int thresholds, -1 = off (orfanage.cpp:615-617)             */
     int32_t cds_minlen;         /* -1 = off (orfanage.cpp:607)                                 */
     int32_t non_aug;            /* --non_aug                                                   */
-    int32_t overhang;           /* --overhang (must be 0 in this build)                        */
-    int32_t spliced_overhang;
+    int32_t overhang;           /* --overhang N: the stop search may run up to N bases past the 3' end of the
+                                   transcript, the unguided start search up to N bases before its 5' end
+                                   (TX::extend_seq, Transcriptome.cpp:342-399); needs orfx_batch::tx_ext_lo/hi */
+    int32_t spliced_overhang;   /* informational here: the cut at the first GT / last AG is applied by whoever
+                                   fills tx_ext_lo / tx_ext_hi                                               */
     int32_t has_reference;      /* 0: no FASTA, candidates are scored as seeded (orfanage.cpp:564) */
     int32_t want_rows;          /* 1: return every candidate row (needed by --stats and mode ALL) */
     int32_t reserved[4];
@@ -118,6 +121,13 @@ typedef struct orfx_batch {
                                       translate to '.' or 'M' steer the path -- TAA TAG TGA TAR TRA and ATG -- so
                                       A C G T U R Y are told apart and every other byte is "other"            */
     int32_t reserved0;
+    /* --overhang (params.overhang > 0; NULL otherwise): for every QUERY transcript the number of genomic bases
+     * that TX::extend_seq (Transcriptome.cpp:342-399) would add below the first exon / above the last exon: at most
+     * params.overhang, clamped to the bundle window, and with --spliced_overhang cut at the last AG (5' side) /
+     * first GT (3' side) of the strand-corrected flank.  `seq` must hold these bases: in the islands layout they
+     * sit right before the first / right after the last exon's bases (the island is widened). */
+    const int32_t* tx_ext_lo;      /* [n_tx] */
+    const int32_t* tx_ext_hi;      /* [n_tx] */
 } orfx_batch;
 
 #define ORFX_SEQ_RAW 0
@@ -145,6 +155,8 @@ typedef struct orfx_best {
     int64_t best_row;      /* absolute row index of the winner, -1 = none                     */
     float   lpi, ilpi, mlpi;
     int32_t start_match;
+    int32_t ext_lo, ext_hi; /* --overhang: bases by which the emitted transcript's first exon starts earlier /
+                               its last exon ends later than the query's (Transcriptome.cpp:418-429, 461-474) */
 } orfx_best;
 
 /* Results of one batch.  Library-owned pinned host buffers, valid until orfx_release / the next
@@ -176,6 +188,8 @@ typedef struct orfx_results {
     const float*   row_lpi;
     const float*   row_ilpi;
     const float*   row_mlpi;
+    const int32_t* row_ext_lo;     /* --overhang only (else NULL): exon-chain growth of the row's query copy, */
+    const int32_t* row_ext_hi;     /* genomic low / high side, as orfx_best::ext_lo / ext_hi                  */
     const int64_t* print_order;    /* [n_rows] absolute row indices in the stats print order:
                                       per query, keys ascending, inside a key the std::sort by
                                       score_gt (orfanage.cpp:250-283)                            */

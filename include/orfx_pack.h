@@ -30,6 +30,11 @@ const char* orfxh_last_error(void);
 int orfxh_load(orfxh_workload** out, const char* query_gtf, const char* const* template_gtfs, int n_templates,
                const char* reference_fasta, int use_id, int keep_all_cds);
 
+/* The same with --overhang N [--spliced_overhang]: bundle windows are padded by N (Transcriptome.cpp:978-991) and
+ * the batches of orfxh_pack carry tx_ext_lo / tx_ext_hi (orfx.h) and the flank bases. */
+int orfxh_load_overhang(orfxh_workload** out, const char* query_gtf, const char* const* template_gtfs, int n_templates,
+                        const char* reference_fasta, int use_id, int keep_all_cds, int overhang, int spliced_overhang);
+
 /* Counts over the whole workload.  what: 0 = bundles, 1 = bundles holding a template and a query
  * ("active"), 2 = query transcripts in active bundles, 3 = template transcripts, 4 = all query
  * transcripts, 5 = spliced query nucleotides in active bundles. */

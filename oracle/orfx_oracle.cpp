@@ -305,8 +305,25 @@ struct T {
     C exons, cds;
     Seq seq;
     const Bn* bn = nullptr;
+    // --overhang: genomic bases usable beyond the low / high end of the exon chain (orfx_batch::tx_ext_lo / tx_ext_hi:
+    // the flank of TX::extend_seq after its clamp to the bundle window and its --spliced_overhang cut, cpp:342-399)
+    int ext_lo = 0, ext_hi = 0;
 
     int cds_len() const { return clen(cds); }
+    // the string TX::extend_seq adds (cpp:342-399), 5'->3' on the transcript's strand
+    std::string extension(bool towards_stop) const {
+        const bool high = (strand == '+') == towards_stop;
+        const int n = high ? ext_hi : ext_lo;
+        if (n <= 0) return "";
+        std::string g = high ? bn->nts((int)exons.back().e + 1, (int)exons.back().e + n) : bn->nts((int)exons.front().s - n, (int)exons.front().s - 1);
+        if (strand != '+') {
+            std::string r;
+            for (int i = (int)g.size() - 1; i >= 0; i--) r += nt_complement(g[(size_t)i]);
+            g = r;
+        }
+        for (char& ch : g) ch = (char)toupper((unsigned char)ch);
+        return g;
+    }
     void build_cds() {   // cpp:92-122
         cds.clear();
         if (cds_start == 0 && cds_end == 0) return;
@@ -355,11 +372,17 @@ struct T {
         }
         return 0;
     }
-    void extend_to_stop() {   // cpp:400-442 with extend_len == 0
+    void extend_to_stop(int extend_len) {   // cpp:400-442
         if (seq.aa[seq.aa.size() - 1] == '.') return;
+        if (extend_len > 0) seq.nt += extension(true);   // SEQ::append_seq, common.hpp:311-314
         std::vector<uint32_t> stops;
         uint32_t res = seq.find_inframe_codon('.', ';', stops, seq.cds_end + 1, (uint32_t)seq.nt.size(), true, true);
         if (res != 0) {
+            if (extend_len > 0) {   // stop inside the extension: the terminal exon grows up to it (cpp:418-429)
+                int extension_len = std::max(((int)(stops[0] + 2) - clen(exons)) + 1, 0);
+                if (strand == '+') exons.back().e += (uint32_t)extension_len;
+                else exons.front().s -= (uint32_t)extension_len;
+            }
             int ext = (int)(stops[0] + 2) - (int)seq.cds_end;
             seq.extend_to_pos(stops[0] + 2);
             extend(cds, exons, ext, strand == '+');
@@ -374,11 +397,21 @@ struct T {
         cds_start = (int)cds.front().s; cds_end = (int)cds.back().e;
         load_seq();
     }
-    void extend_to_start_search() {   // cpp:446-492, new_start == -1, extend_len == 0
+    void extend_to_start_search(int extend_len) {   // cpp:446-492, new_start == -1
         if (seq.aa[0] == 'M') return;
+        if (extend_len > 0) {   // SEQ::push_front, common.hpp:317-322
+            const std::string e5 = extension(false);
+            seq.cds_start += (uint32_t)e5.size(); seq.cds_end += (uint32_t)e5.size();
+            seq.nt = e5 + seq.nt;
+        }
         std::vector<uint32_t> starts;
         uint32_t res = seq.find_inframe_codon('M', '.', starts, seq.cds_start, 0, false, true);
         if (res == 0) { load_seq(); return; }
+        if (extend_len > 0) {   // as written: measured against --overhang, not against the bases actually added (cpp:461-474)
+            int extension_len = std::max(extend_len - (int)starts[0], 0);
+            if (strand == '+') exons.front().s -= (uint32_t)extension_len;
+            else exons.back().e += (uint32_t)extension_len;
+        }
         extend_to_start_at((int)starts[0]);
     }
     bool extend_to_start_guided(const T& ref, bool non_aug) {   // cpp:496-620
@@ -435,24 +468,24 @@ struct T {
         }
         return 0;
     }
-    int rescue_unguided(bool non_aug) {   // cpp:641-677 with t == nullptr (Transcriptome::clean_cds, cpp:1075)
+    int rescue_unguided(bool non_aug, int extend_len = 0) {   // cpp:641-677 with t == nullptr (Transcriptome::clean_cds, cpp:1075)
         if (seq.cds_nt_len() < 3) { remove_cds(); return 0; }
         adjust_stop();
         if (cds_len() == 0) { remove_cds(); return 0; }
-        extend_to_stop();
-        if (!non_aug) extend_to_start_search();
+        extend_to_stop(extend_len);
+        if (!non_aug) extend_to_start_search(extend_len);
         adjust_start();
         cds_phase = 0;
         assign_phase(cds, strand, 0);
         return 1;
     }
-    int rescue(bool non_aug, const T& t) {   // cpp:641-677
+    int rescue(bool non_aug, const T& t, int extend_len = 0) {   // cpp:641-677
         if (seq.cds_nt_len() < 3) { remove_cds(); return 0; }
         adjust_stop();
         if (cds_len() == 0) { remove_cds(); return 0; }
-        extend_to_stop();
+        extend_to_stop(extend_len);
         bool found = extend_to_start_guided(t, non_aug);
-        if (!found) extend_to_start_search();
+        if (!found) extend_to_start_search(extend_len);
         bool run_adjust = true;
         if (non_aug) run_adjust = !(strand == '+' ? cds_start == t.cds_start : cds_end == t.cds_end);
         if (run_adjust) adjust_start();
@@ -499,12 +532,14 @@ struct Row {
     Sc sc;
     int status;
     int n_dup = 0;
+    int ext_lo = 0, ext_hi = 0;   // growth of the row's query copy (--overhang)
     int64_t idx;
 };
 
 struct Ctx {
     orfx_params p;
     std::vector<orfx_best> best;
+    std::vector<int32_t> ext_lo, ext_hi;
     std::vector<int32_t> q_tx, t_tx, seg_s, seg_e, cds_s, cds_e, n_dup, qlen, tlen, ulen, qstart, extra, missing, match, outframe, inframe;
     std::vector<uint8_t> status, pass, start_match;
     std::vector<float> lpi, ilpi, mlpi;
@@ -538,6 +573,9 @@ T load_tx(const orfx_batch* b, int tx) {
         for (size_t i = 0; i < t.cds.size(); i++) t.cds[i].ph = b->seg_phase[k0 + (int)i];
         t.cds_start = b->tx_cds_start[tx];
         t.cds_end = b->tx_cds_end[tx];
+    } else if (b->tx_kind[tx] == ORFX_TX_QUERY && b->tx_ext_lo && b->tx_ext_hi) {
+        t.ext_lo = b->tx_ext_lo[tx];
+        t.ext_hi = b->tx_ext_hi[tx];
     }
     return t;
 }
@@ -556,22 +594,25 @@ struct BundleSeq {
         if (!b->seg_seq_off) { bn.seq = b->seq + b->seq_off[bi]; return; }
         int hi = bn.bstart;
         for (int x = b->bundle_tx_off[bi]; x < b->bundle_tx_off[bi + 1]; x++)
-            if (b->tx_seg_off[x + 1] > b->tx_seg_off[x]) hi = std::max(hi, (int)b->segs[b->tx_seg_off[x + 1] - 1].end);
+            if (b->tx_seg_off[x + 1] > b->tx_seg_off[x]) hi = std::max(hi, (int)b->segs[b->tx_seg_off[x + 1] - 1].end + (b->tx_ext_hi ? b->tx_ext_hi[x] : 0));
         rebuilt.assign((size_t)(hi - bn.bstart + 1), 'N');
         for (int x = b->bundle_tx_off[bi]; x < b->bundle_tx_off[bi + 1]; x++) {
             if (b->tx_kind[x] != ORFX_TX_QUERY) continue;
             for (int k = b->tx_seg_off[x]; k < b->tx_seg_off[x + 1]; k++) {
-                const orfx_seg& sg = b->segs[k];
+                orfx_seg sg = b->segs[k];
+                int64_t at = b->seg_seq_off[k];
+                if (b->tx_ext_lo && k == b->tx_seg_off[x]) { sg.start -= b->tx_ext_lo[x]; at -= b->tx_ext_lo[x]; }   // the --overhang flanks
+                if (b->tx_ext_hi && k == b->tx_seg_off[x + 1] - 1) sg.end += b->tx_ext_hi[x];
                 if (b->seq_format == ORFX_SEQ_NT4) {   // decode the 4-bit codes back to letters ("other" -> N)
                     static const char LET[16] = {'N', 'A', 'C', 'U', 'G', 'R', 'N', 'N', 'T', 'N', 'Y', 'N', 'N', 'N', 'N', 'N'};
-                    const int64_t base0 = b->seq_off[bi] + b->seg_seq_off[k];
+                    const int64_t base0 = b->seq_off[bi] + at;
                     for (int i = 0; i <= sg.end - sg.start; i++) {
                         const int64_t p = base0 + i;
                         rebuilt[(size_t)(sg.start - bn.bstart + i)] = LET[(b->seq[p >> 1] >> ((p & 1) * 4)) & 15];
                     }
                     continue;
                 }
-                memcpy(&rebuilt[(size_t)(sg.start - bn.bstart)], b->seq + b->seq_off[bi] + b->seg_seq_off[k], (size_t)(sg.end - sg.start + 1));
+                memcpy(&rebuilt[(size_t)(sg.start - bn.bstart)], b->seq + b->seq_off[bi] + at, (size_t)(sg.end - sg.start + 1));
             }
         }
         bn.seq = (const uint8_t*)rebuilt.data();
@@ -623,8 +664,9 @@ void evaluate(Ctx& cx, const orfx_batch* b) {
                     if (qseg.cds_len() < 3) { cur.key_s = qseg.cds_start; cur.key_e = qseg.cds_end; cur.status = ORFX_ST_CDS_LT3; cur.sc.pass = false; continue; }
                     if (p.has_reference) {
                         qseg.load_seq();
-                        int ret = qseg.rescue(p.non_aug != 0, t);
+                        int ret = qseg.rescue(p.non_aug != 0, t, p.overhang);
                         cur.key_s = qseg.cds_start; cur.key_e = qseg.cds_end;
+                        if (!qseg.exons.empty()) { cur.ext_lo = (int)q.exons.front().s - (int)qseg.exons.front().s; cur.ext_hi = (int)qseg.exons.back().e - (int)q.exons.back().e; }
                         if (!ret) { cur.status = ORFX_ST_NOT_RESCUED; cur.sc.pass = false; continue; }
                         const std::string& aa = qseg.seq.aa;
                         bool at_t5 = qseg.strand == '+' ? qseg.cds_start == t.cds_start : qseg.cds_end == t.cds_end;
@@ -676,6 +718,7 @@ void evaluate(Ctx& cx, const orfx_batch* b) {
                 const Row& w = flat[best_se].front();
                 be.t_tx = w.t_tx; be.cds_start = w.key_s; be.cds_end = w.key_e; be.duplicity = w.n_dup; be.best_row = w.idx;
                 be.lpi = w.sc.lpi; be.ilpi = w.sc.ilpi; be.mlpi = w.sc.mlpi; be.start_match = w.sc.start_match;
+                be.ext_lo = w.ext_lo; be.ext_hi = w.ext_hi;
             }
             cx.best.push_back(be);
             // rows in candidate order, with n_dup copied back from the flattened copies
@@ -688,6 +731,7 @@ void evaluate(Ctx& cx, const orfx_batch* b) {
     size_t n = rows_all.size();
     auto rs = [&](std::vector<int32_t>& v) { v.resize(n); };
     rs(cx.q_tx); rs(cx.t_tx); rs(cx.seg_s); rs(cx.seg_e); rs(cx.cds_s); rs(cx.cds_e); rs(cx.n_dup); rs(cx.qlen); rs(cx.tlen); rs(cx.ulen);
+    rs(cx.ext_lo); rs(cx.ext_hi);
     rs(cx.qstart); rs(cx.extra); rs(cx.missing); rs(cx.match); rs(cx.outframe); rs(cx.inframe);
     cx.status.resize(n); cx.pass.resize(n); cx.start_match.resize(n); cx.lpi.resize(n); cx.ilpi.resize(n); cx.mlpi.resize(n);
     for (size_t i = 0; i < n; i++) {
@@ -697,6 +741,7 @@ void evaluate(Ctx& cx, const orfx_batch* b) {
         cx.start_match[i] = r.sc.start_match; cx.qlen[i] = r.sc.qlen; cx.tlen[i] = r.sc.tlen; cx.ulen[i] = r.sc.ulen; cx.qstart[i] = r.sc.query_start;
         cx.extra[i] = r.sc.extra; cx.missing[i] = r.sc.missing; cx.match[i] = r.sc.match; cx.outframe[i] = r.sc.outframe; cx.inframe[i] = r.sc.inframe;
         cx.lpi[i] = r.sc.lpi; cx.ilpi[i] = r.sc.ilpi; cx.mlpi[i] = r.sc.mlpi;
+        cx.ext_lo[i] = r.ext_lo; cx.ext_hi[i] = r.ext_hi;
     }
 }
 
@@ -709,7 +754,7 @@ const char* orfx_oracle_last_error(void) { return g_err.c_str(); }
 int orfx_oracle_create(orfx_ctx** out, int device, const orfx_params* params) {
     (void)device;
     if (!out || !params) { g_err = "null argument"; return ORFX_E_INVALID; }
-    if (params->overhang != 0) { g_err = "overhang > 0 is outside the restated path"; return ORFX_E_UNSUPPORTED; }
+    if (params->overhang < 0) { g_err = "negative overhang"; return ORFX_E_INVALID; }
     Ctx* c = new Ctx();
     c->p = *params;
     *out = reinterpret_cast<orfx_ctx*>(c);
@@ -719,6 +764,7 @@ int orfx_oracle_create(orfx_ctx** out, int device, const orfx_params* params) {
 int orfx_oracle_submit(orfx_ctx* ctx, const orfx_batch* batch) {
     Ctx* c = reinterpret_cast<Ctx*>(ctx);
     if (!c || !batch) { g_err = "null argument"; return ORFX_E_INVALID; }
+    if (c->p.overhang > 0 && c->p.has_reference && batch->n_tx > 0 && (!batch->tx_ext_lo || !batch->tx_ext_hi)) { g_err = "--overhang needs tx_ext_lo / tx_ext_hi"; return ORFX_E_INVALID; }
     try { evaluate(*c, batch); } catch (const std::exception& e) { g_err = e.what(); return ORFX_E_INVALID; }
     c->submitted = true;
     return ORFX_OK;
@@ -738,6 +784,7 @@ int orfx_oracle_wait(orfx_ctx* ctx, orfx_results* r) {
     r->row_ulen = c->ulen.data(); r->row_query_start = c->qstart.data(); r->row_extra = c->extra.data(); r->row_missing = c->missing.data();
     r->row_match = c->match.data(); r->row_outframe = c->outframe.data(); r->row_inframe = c->inframe.data();
     r->row_lpi = c->lpi.data(); r->row_ilpi = c->ilpi.data(); r->row_mlpi = c->mlpi.data(); r->print_order = c->order.data();
+    if (c->p.overhang > 0) { r->row_ext_lo = c->ext_lo.data(); r->row_ext_hi = c->ext_hi.data(); }
     return ORFX_OK;
 }
 
@@ -764,7 +811,7 @@ int orfx_oracle_clean_templates(orfx_ctx* ctx, const orfx_batch* b, int rescue, 
             if (keep) {
                 t.load_seq();
                 bool alive = true;
-                if (rescue) alive = t.rescue_unguided(non_aug) != 0;
+                if (rescue) alive = t.rescue_unguided(non_aug, c->p.overhang) != 0;
                 if (!alive || t.seq.aa.empty()) keep = false;   // rescue removed the CDS (the reference then drops it, cpp:1083-1089)
                 else {
                     char start_codon = t.seq.aa[0], stop_codon = t.seq.aa[t.seq.aa.size() - 1];
@@ -835,6 +882,7 @@ int64_t orfx_oracle_masks(const orfx_batch* b, int32_t tx, uint32_t* stop_bits, 
     const Bn& bn = bseq.bn;
     T t = load_tx(b, tx);
     t.bn = &bn;
+    if (!t.exons.empty()) { t.exons.front().s -= (uint32_t)t.ext_lo; t.exons.back().e += (uint32_t)t.ext_hi; }   // the scanned chain covers the --overhang flanks
     std::string nt;
     if (t.strand == '+') for (const S& c : t.exons) nt += bn.nts((int)c.s, (int)c.e);
     else for (int ci = (int)t.exons.size() - 1; ci >= 0; ci--) { std::string tmp = bn.nts((int)t.exons[ci].s, (int)t.exons[ci].e); for (int i = (int)tmp.size() - 1; i >= 0; i--) nt += nt_complement(tmp[i]); }

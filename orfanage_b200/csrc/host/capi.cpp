@@ -30,6 +30,11 @@ const char* orfxh_last_error(void) { return g_err.c_str(); }
 
 int orfxh_load(orfxh_workload** out, const char* query_gtf, const char* const* template_gtfs, int n_templates,
                const char* reference_fasta, int use_id, int keep_all_cds) {
+    return orfxh_load_overhang(out, query_gtf, template_gtfs, n_templates, reference_fasta, use_id, keep_all_cds, 0, 0);
+}
+
+int orfxh_load_overhang(orfxh_workload** out, const char* query_gtf, const char* const* template_gtfs, int n_templates,
+                        const char* reference_fasta, int use_id, int keep_all_cds, int overhang, int spliced_overhang) {
     if (!out || !query_gtf || !template_gtfs || n_templates <= 0) { g_err = "null or empty argument"; return ORFX_E_INVALID; }
     try {
         std::unique_ptr<orfxh_workload> w(new orfxh_workload());
@@ -38,6 +43,8 @@ int orfxh_load(orfxh_workload** out, const char* query_gtf, const char* const* t
         if (reference_fasta) w->opt.reference = reference_fasta;
         w->opt.use_id = use_id != 0;
         w->opt.keep_all_cds = keep_all_cds != 0;
+        w->opt.overhang = overhang;
+        w->opt.spliced_overhang = spliced_overhang != 0;
         prepare_transcriptome(w->opt, w->fasta, w->tr, false);
         find_active(w.get());
         build_tid_classes(w->tr, w->tid_classes);
@@ -79,7 +86,8 @@ int orfxh_pack(orfxh_workload* w, int shard, int n_shards, int layout, void* (*a
         shard_bundles(w->tr, w->active, n_shards, shards);
         if (w->packed.size() <= (size_t)shard) w->packed.resize((size_t)shard + 1);
         w->packed[(size_t)shard].reset(new PackedBatch());
-        pack_bundles(w->tr, shards[(size_t)shard], w->opt.keep_all_cds, w->tid_classes, *w->packed[(size_t)shard], alloc, dealloc, layout != 0, PACK_EVAL, layout == 2);
+        pack_bundles(w->tr, shards[(size_t)shard], w->opt.keep_all_cds, w->tid_classes, *w->packed[(size_t)shard], alloc, dealloc, layout != 0, PACK_EVAL, layout == 2,
+                     w->opt.overhang, w->opt.spliced_overhang);
         *out = w->packed[(size_t)shard]->view();
         return ORFX_OK;
     } catch (const std::exception& e) { g_err = e.what(); return ORFX_E_INVALID; }

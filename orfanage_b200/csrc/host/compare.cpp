@@ -25,17 +25,7 @@ char codon_aa(const char* c3, size_t n) {
     auto it = m.find(std::string(c3, n));
     return it == m.end() ? '\0' : it->second;
 }
-char complement(char c) {   // ntComplement (gclib), IUPAC, case preserving
-    static char table[256]; static bool init = false;
-    if (!init) {
-        const char* defs = "AaCcTtGgUuMmRrWwSsYyKkVvHhDdBbNnXx-*";
-        const char* comp = "TtGgAaCcAaKkYyWwSsRrMmBbDdHhVvNnXx-*";
-        for (int i = 0; i < 256; i++) table[i] = (char)i;
-        for (int i = 0; defs[i]; i++) table[(unsigned char)defs[i]] = comp[i];
-        init = true;
-    }
-    return table[(unsigned char)c];
-}
+char complement(char c) { return nt_complement(c); }
 // amino acid of the codon that starts at transcript offset `off` of `chain` (SEQ::translate on the spliced,
 // upper-cased, strand-corrected sequence, common.hpp:477-495)
 char aa_at(const Fasta& fa, const Fasta::Seq& chrom, const Chain& chain, char strand, int off) {

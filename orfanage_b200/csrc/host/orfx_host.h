@@ -163,6 +163,8 @@ struct PackedBatch {
     orfx_seg* segs = nullptr;
     int8_t* seg_phase = nullptr;
     int32_t* seg_seq_off = nullptr;         // islands layout only
+    int32_t* tx_ext_lo = nullptr;           // --overhang only: usable flank below / above each query's exon chain
+    int32_t* tx_ext_hi = nullptr;
     int32_t n_tx = 0;
     int64_t n_segs = 0, seq_bytes = 0, n_queries = 0;   // seq_bytes counts bases
     int32_t seq_format = ORFX_SEQ_RAW;
@@ -179,10 +181,12 @@ struct PackedBatch {
 // mode = PACK_COMPARE builds a *compare batch* (orfx_score_pairs): queries and templates both carry their
 // CDS chain, no sequence.
 enum { PACK_EVAL = 0, PACK_CLEAN = 1, PACK_COMPARE = 2 };
+char nt_complement(char c);   // ntComplement (gclib), IUPAC, case preserving
 void pack_bundles(const Transcriptome& tr, const std::vector<int>& bundle_ids, bool keep_all_cds,
                   const std::map<std::string, int>& tid_classes, PackedBatch& out,
                   void* (*alloc)(size_t) = nullptr, void (*dealloc)(void*) = nullptr, bool islands = true, int mode = PACK_EVAL,
-                  bool nt4 = false);   // nt4: islands as 4-bit base codes (ORFX_SEQ_NT4), half the upload
+                  bool nt4 = false,    // nt4: islands as 4-bit base codes (ORFX_SEQ_NT4), half the upload
+                  int overhang = 0, bool spliced_overhang = false);   // --overhang flanks (TX::extend_seq, Transcriptome.cpp:342-399)
 void build_tid_classes(const Transcriptome& tr, std::map<std::string, int>& out);
 // greedy longest-processing-time split of active bundles over n shards
 void shard_bundles(const Transcriptome& tr, const std::vector<int>& active, int n, std::vector<std::vector<int>>& shards);

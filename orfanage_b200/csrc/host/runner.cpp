@@ -12,11 +12,24 @@ namespace orfx {
 std::string float_to_string(float v) { char b[64]; snprintf(b, sizeof b, "%f", (double)v); return b; }
 std::string float_ostream(float v) { char b[64]; snprintf(b, sizeof b, "%g", (double)v); return b; }
 
+char nt_complement(char c) {   // ntComplement (gclib), IUPAC, case preserving
+    static char table[256]; static bool init = false;
+    if (!init) {
+        const char* defs = "AaCcTtGgUuMmRrWwSsYyKkVvHhDdBbNnXx-*";
+        const char* comp = "TtGgAaCcAaKkYyWwSsRrMmBbDdHhVvNnXx-*";
+        for (int i = 0; i < 256; i++) table[i] = (char)i;
+        for (int i = 0; defs[i]; i++) table[(unsigned char)defs[i]] = comp[i];
+        init = true;
+    }
+    return table[(unsigned char)c];
+}
+
 void PackedBatch::reset() {
     if (arena) { if (dealloc) dealloc(arena); else free(arena); }
     arena = nullptr; arena_bytes = 0; dealloc = nullptr;
     bundle_ids.clear(); tx_global.clear();
     n_tx = 0; n_segs = 0; seq_bytes = 0; n_queries = 0; seq_format = ORFX_SEQ_RAW;
+    tx_ext_lo = tx_ext_hi = nullptr;
 }
 
 orfx_batch PackedBatch::view() const {
@@ -40,6 +53,8 @@ orfx_batch PackedBatch::view() const {
     b.seg_phase = seg_phase;
     b.seg_seq_off = seq_bytes ? seg_seq_off : nullptr;
     b.seq_format = seq_format;
+    b.tx_ext_lo = tx_ext_lo;
+    b.tx_ext_hi = tx_ext_hi;
     return b;
 }
 
@@ -65,12 +80,16 @@ inline uint8_t tx_kind_of(const Tx& t, bool keep_all_cds, bool clean_mode) {
     if (clean_mode) return (t.is_coding && !t.cds.empty()) ? ORFX_TX_QUERY : ORFX_TX_SKIP;
     return t.is_templ ? ORFX_TX_TEMPLATE : ((keep_all_cds && t.is_coding) ? ORFX_TX_SKIP : ORFX_TX_QUERY);
 }
-void bundle_islands(const Transcriptome& tr, const Bundle& b, bool keep_all_cds, bool clean_mode, std::vector<std::pair<int, int>>& isl) {
+// ext_lo / ext_hi (per transcript of the bundle, may be null): the --overhang flanks widen the terminal exons.
+void bundle_islands(const Transcriptome& tr, const Bundle& b, bool keep_all_cds, bool clean_mode, std::vector<std::pair<int, int>>& isl,
+                    const int32_t* ext_lo = nullptr, const int32_t* ext_hi = nullptr) {
     isl.clear();
     for (int i = 0; i < b.count; i++) {
         const Tx& t = tr.txs[b.first + i];
         if (tx_kind_of(t, keep_all_cds, clean_mode) != ORFX_TX_QUERY) continue;
+        const size_t first = isl.size();
         for (const Seg& s : t.exons) isl.emplace_back(s.s, s.e);
+        if (ext_lo && isl.size() > first) { isl[first].first -= ext_lo[i]; isl.back().second += ext_hi[i]; }
     }
     std::sort(isl.begin(), isl.end());
     size_t k = 0;
@@ -80,13 +99,35 @@ void bundle_islands(const Transcriptome& tr, const Bundle& b, bool keep_all_cds,
     }
     isl.resize(k);
 }
+// Bases TX::extend_seq (Transcriptome.cpp:342-399) would add on one genomic side of `t`: at most `overhang`, clamped
+// to the (already padded) bundle window, and with --spliced_overhang cut at the first GT (3' side) / after the last AG
+// (5' side) of the strand-corrected, upper-cased flank.  A transcript that touches the window edge (only possible at a
+// chromosome end) gets no flank; the reference re-reads the edge base there.
+int usable_flank(const Fasta& fa, const Fasta::Seq& chrom, const Bundle& b, const Tx& t, bool high, int overhang, bool spliced) {
+    if (overhang <= 0 || t.exons.empty()) return 0;
+    int es, ee;
+    if (high) { es = t.exons.back().e + 1; ee = std::min(t.exons.back().e + overhang, b.bend); }
+    else { es = std::max(t.exons.front().s - overhang, b.bstart); ee = t.exons.front().s - 1; }
+    if (ee < es) return 0;
+    const int len = ee - es + 1;
+    if (!spliced) return len;
+    std::string g((size_t)len, 'N');
+    fa.fetch(chrom, es - 1, len, &g[0]);
+    std::string f;   // 5'->3' on the transcript's strand
+    if (t.strand == '+') f = g; else for (int i = len - 1; i >= 0; i--) f += nt_complement(g[(size_t)i]);
+    for (char& c : f) c = (char)toupper((unsigned char)c);
+    const bool towards_stop = (t.strand == '+') == high;
+    if (towards_stop) { const size_t at = f.find("GT"); return at == std::string::npos ? len : (int)at; }
+    const size_t at = f.rfind("AG");
+    return at == std::string::npos ? len : len - (int)(at + 2);
+}
 }  // namespace
 
 // Two passes: size everything, take one arena from the allocator, fill.  Sequence bytes (the bulk) are
 // copied by several threads.  islands = true uploads only the bases under query exons.
 void pack_bundles(const Transcriptome& tr, const std::vector<int>& bundle_ids, bool keep_all_cds,
                   const std::map<std::string, int>& tid_classes, PackedBatch& out,
-                  void* (*alloc)(size_t), void (*dealloc)(void*), bool islands, int mode, bool nt4) {
+                  void* (*alloc)(size_t), void (*dealloc)(void*), bool islands, int mode, bool nt4, int overhang, bool spliced_overhang) {
     const bool clean_mode = mode == PACK_CLEAN, compare_mode = mode == PACK_COMPARE;
     out.reset();
     out.bundle_ids = bundle_ids;
@@ -94,14 +135,32 @@ void pack_bundles(const Transcriptome& tr, const std::vector<int>& bundle_ids, b
     const bool has_seq = tr.fasta != nullptr && !compare_mode;
     islands = islands && has_seq;
     nt4 = nt4 && islands;
+    if (!has_seq) overhang = 0;
     size_t total_seq = 0, total_tx = 0, total_segs = 0;
     std::vector<int64_t> bundle_bytes(nb, 0);
     std::vector<std::pair<int, int>> isl;
+    // --overhang: usable flanks of every query, per bundle in transcript order
+    std::vector<std::vector<int32_t>> fl_lo(overhang > 0 ? nb : 0), fl_hi(overhang > 0 ? nb : 0);
+    if (overhang > 0) {
+        for (size_t j = 0; j < nb; j++) {
+            const Bundle& b = tr.bundles[bundle_ids[j]];
+            const Fasta::Seq* chrom = tr.fasta->find(tr.seqnames[(size_t)b.seqid]);
+            fl_lo[j].assign((size_t)b.count, 0); fl_hi[j].assign((size_t)b.count, 0);
+            for (int i = 0; i < b.count; i++) {
+                const Tx& t = tr.txs[b.first + i];
+                if (tx_kind_of(t, keep_all_cds, clean_mode) != ORFX_TX_QUERY) continue;
+                fl_lo[j][(size_t)i] = usable_flank(*tr.fasta, *chrom, b, t, false, overhang, spliced_overhang);
+                fl_hi[j][(size_t)i] = usable_flank(*tr.fasta, *chrom, b, t, true, overhang, spliced_overhang);
+            }
+        }
+    }
+    auto flo = [&](size_t j) { return overhang > 0 ? fl_lo[j].data() : nullptr; };
+    auto fhi = [&](size_t j) { return overhang > 0 ? fl_hi[j].data() : nullptr; };
     for (size_t j = 0; j < nb; j++) {
         const Bundle& b = tr.bundles[bundle_ids[j]];
         if (has_seq) {
             if (islands) {
-                bundle_islands(tr, b, keep_all_cds, clean_mode, isl);
+                bundle_islands(tr, b, keep_all_cds, clean_mode, isl, flo(j), fhi(j));
                 for (auto& iv : isl) bundle_bytes[j] += iv.second - iv.first + 1;
                 if (nt4) bundle_bytes[j] += bundle_bytes[j] & 1;   // bundles start on a byte boundary
             } else bundle_bytes[j] = b.bend - b.bstart + 1;
@@ -116,7 +175,8 @@ void pack_bundles(const Transcriptome& tr, const std::vector<int>& bundle_ids, b
            o_kind = o_btx + up((nb + 1) * 4), o_strand = o_kind + up(total_tx + 4), o_segoff = o_strand + up(total_tx + 4),
            o_cs = o_segoff + up((total_tx + 1) * 4), o_ce = o_cs + up(total_tx * 4 + 4), o_tid = o_ce + up(total_tx * 4 + 4),
            o_segs = o_tid + up(total_tx * 4 + 4), o_phase = o_segs + up(total_segs * 8 + 8), o_sso = o_phase + up(total_segs + 4),
-           o_end = o_sso + up(islands ? total_segs * 4 + 4 : 4);
+           o_xlo = o_sso + up(islands ? total_segs * 4 + 4 : 4), o_xhi = o_xlo + up(overhang > 0 ? total_tx * 4 + 4 : 4),
+           o_end = o_xhi + up(overhang > 0 ? total_tx * 4 + 4 : 4);
     out.arena = alloc ? alloc(o_end) : malloc(o_end);
     if (!out.arena) throw std::runtime_error("cannot allocate " + std::to_string(o_end) + " bytes for the packed batch");
     out.arena_bytes = o_end;
@@ -127,6 +187,8 @@ void pack_bundles(const Transcriptome& tr, const std::vector<int>& bundle_ids, b
     out.tx_seg_off = (int32_t*)(base + o_segoff); out.tx_cds_start = (int32_t*)(base + o_cs); out.tx_cds_end = (int32_t*)(base + o_ce);
     out.tx_tid_class = (int32_t*)(base + o_tid); out.segs = (orfx_seg*)(base + o_segs); out.seg_phase = (int8_t*)(base + o_phase);
     out.seg_seq_off = islands ? (int32_t*)(base + o_sso) : nullptr;
+    out.tx_ext_lo = overhang > 0 ? (int32_t*)(base + o_xlo) : nullptr;
+    out.tx_ext_hi = overhang > 0 ? (int32_t*)(base + o_xhi) : nullptr;
     out.n_tx = (int32_t)total_tx; out.n_segs = (int64_t)total_segs; out.seq_bytes = (int64_t)total_seq;
     out.seq_format = nt4 ? ORFX_SEQ_NT4 : ORFX_SEQ_RAW;
     out.tx_global.resize(total_tx);
@@ -155,6 +217,7 @@ void pack_bundles(const Transcriptome& tr, const std::vector<int>& bundle_ids, b
             out.tx_cds_start[x] = (as_templ || (clean_mode && kind == ORFX_TX_QUERY)) ? t.cds_start : 0;
             out.tx_cds_end[x] = (as_templ || (clean_mode && kind == ORFX_TX_QUERY)) ? t.cds_end : 0;
             out.tx_tid_class[x] = tid_classes.at(t.tid);
+            if (overhang > 0) { out.tx_ext_lo[x] = fl_lo[j][(size_t)i]; out.tx_ext_hi[x] = fl_hi[j][(size_t)i]; }
         }
         out.bundle_tx_off[j + 1] = x;
     }
@@ -171,7 +234,7 @@ void pack_bundles(const Transcriptome& tr, const std::vector<int>& bundle_ids, b
                 const Fasta::Seq& src = *chrom[(size_t)b.seqid];
                 uint8_t* dst = nt4 ? out.seq + out.seq_off[j] / 2 : out.seq + out.seq_off[j];
                 if (!islands) { tr.fasta->fetch(src, b.bstart - 1, b.bend - b.bstart + 1, (char*)dst); continue; }
-                bundle_islands(tr, b, keep_all_cds, clean_mode, il);
+                bundle_islands(tr, b, keep_all_cds, clean_mode, il, flo(j), fhi(j));
                 il_off.resize(il.size());
                 int32_t o = 0;
                 for (size_t k = 0; k < il.size(); k++) {
@@ -300,7 +363,7 @@ static size_t clean_cds(const Options& opt, Transcriptome& tr, const Backend& be
     std::map<std::string, int> tid_classes;
     build_tid_classes(tr, tid_classes);
     PackedBatch pb;
-    pack_bundles(tr, ids, false, tid_classes, pb, be.host_alloc, be.host_free, true, PACK_CLEAN, true);
+    pack_bundles(tr, ids, false, tid_classes, pb, be.host_alloc, be.host_free, true, PACK_CLEAN, true, opt.overhang, opt.spliced_overhang);
     orfx_params params;
     fill_params(opt, false, params);
     orfx_ctx* ctx = nullptr;
@@ -327,7 +390,7 @@ static size_t clean_cds(const Options& opt, Transcriptome& tr, const Backend& be
 }
 
 void prepare_transcriptome(const Options& opt, Fasta& fasta, Transcriptome& tr, bool verbose, const Backend* be) {
-    if (opt.overhang != 0) throw std::runtime_error("--overhang is not supported by this build (SURVEY.md §8f row 2)");
+    if (opt.overhang < 0) throw std::runtime_error("--overhang must not be negative");
     if (opt.clean_templ && !be) throw std::runtime_error("--cleant needs a compute backend");
     auto say = [&](const char* m) { if (verbose) fprintf(stderr, "%s\n", m); };
     say("loading reference genome");
@@ -401,7 +464,7 @@ int run_orfanage(const Options& opt, const Backend& be) {
             if (s.rc) { s.err = be.last_error(); return; }
             auto a = clk::now();
             s.ms_create = std::chrono::duration<double, std::milli>(a - c0).count();
-            pack_bundles(tr, shard_ids[k], opt.keep_all_cds, tid_classes, s.batch, be.host_alloc, be.host_free, true, PACK_EVAL, true);
+            pack_bundles(tr, shard_ids[k], opt.keep_all_cds, tid_classes, s.batch, be.host_alloc, be.host_free, true, PACK_EVAL, true, opt.overhang, opt.spliced_overhang);
             auto b = clk::now();
             s.ms_pack = std::chrono::duration<double, std::milli>(b - a).count();
             orfx_batch v = s.batch.view();
@@ -502,6 +565,7 @@ int run_orfanage(const Options& opt, const Backend& be) {
             }
             if (!mode_all) {   // orfanage.cpp:753-791
                 Tx fq = q;
+                if (opt.overhang > 0 && !fq.exons.empty()) { fq.exons.front().s -= best.ext_lo; fq.exons.back().e += best.ext_hi; }   // cpp:418-429, 461-474
                 set_orf(fq, best.cds_start, best.cds_end);
                 const Tx& t = tr.txs[txg[best.t_tx]];
                 add_found_attrs(fq, t, best.duplicity, best.ilpi, best.lpi, best.mlpi, best.start_match);
@@ -522,6 +586,7 @@ int run_orfanage(const Options& opt, const Backend& be) {
                 if (mode_all) {
                     if (r.row_pass[front]) {
                         Tx fq = q;
+                        if (r.row_ext_lo && !fq.exons.empty()) { fq.exons.front().s -= r.row_ext_lo[front]; fq.exons.back().e += r.row_ext_hi[front]; }
                         set_orf(fq, ks, ke);
                         fq.tid = tid;
                         const Tx& t = tr.txs[txg[r.row_t_tx[front]]];

@@ -160,6 +160,25 @@ def test_empty_and_degenerate_batches(gpu, oracle_lib):
         want = ox.run(b)
     assert_same_results(got, want, "degenerate")
     assert got.n_queries == 2
+    # the other entry points on empty and degenerate input
+    keep, cs, ce = gpu.clean(ob.Batch(), rescue=True)
+    assert len(keep) == 0
+    assert len(gpu.score_pairs(ob.Batch())["q_tx"]) == 0
+    pairs = gpu.score_pairs(b)          # 2 queries x 1 template, one of them disjoint from it
+    with ob.Context(ob.Params.make(mode="BEST"), lib=oracle_lib, prefix="orfx_oracle_") as ox:
+        want_pairs = ox.score_pairs(b)
+    assert len(pairs["q_tx"]) == 2
+    for k in ("q_tx", "t_tx", "qlen", "tlen", "ulen", "match", "inframe", "outframe", "extra", "missing"):
+        assert (pairs[k] == want_pairs[k]).all(), k
+    cb = ob.Batch(seq=seq, seq_off=[0, len(seq)], bundle_start=[100], bundle_tx_off=[0, 2], tx_kind=[0, 0], tx_strand=[ord("+"), ord("-")],
+                  tx_seg_off=[0, 1, 2], tx_cds_start=[108, 101], tx_cds_end=[116, 103], tx_tid_class=[0, 1], segs=[[100, 204], [100, 204]],
+                  seg_phase=[0, 0], seg_seq_off=[0, 0])
+    for rescue in (False, True):       # ATGAAATAG at 108..116 on '+'; a 3-base CDS on '-'
+        got_c = gpu.clean(cb, rescue)
+        with ob.Context(ob.Params.make(mode="BEST"), lib=oracle_lib, prefix="orfx_oracle_") as ox:
+            want_c = ox.clean(cb, rescue)
+        assert all((g == x).all() for g, x in zip(got_c, want_c)), rescue
+        assert got_c[0][0] == 1 and (got_c[1][0], got_c[2][0]) == (108, 116)
 
 
 def cleaning_batch(batch, best, rng):
