@@ -74,18 +74,20 @@ class _Batch(C.Structure):
                 ("seq", C.c_void_p), ("seq_off", C.c_void_p), ("bundle_start", C.c_void_p), ("bundle_tx_off", C.c_void_p),
                 ("tx_kind", C.c_void_p), ("tx_strand", C.c_void_p), ("tx_seg_off", C.c_void_p), ("tx_cds_start", C.c_void_p),
                 ("tx_cds_end", C.c_void_p), ("tx_tid_class", C.c_void_p), ("segs", C.c_void_p), ("seg_phase", C.c_void_p),
-                ("seg_seq_off", C.c_void_p), ("seq_format", C.c_int32), ("reserved0", C.c_int32)]
+                ("seg_seq_off", C.c_void_p), ("seq_format", C.c_int32), ("reserved0", C.c_int32),
+                ("tx_ext_lo", C.c_void_p), ("tx_ext_hi", C.c_void_p)]
 
 
 class _Best(C.Structure):
     _fields_ = [("q_tx", C.c_int32), ("t_tx", C.c_int32), ("cds_start", C.c_int32), ("cds_end", C.c_int32),
                 ("duplicity", C.c_int32), ("n_rows", C.c_int32), ("row_off", C.c_int64), ("best_row", C.c_int64),
-                ("lpi", C.c_float), ("ilpi", C.c_float), ("mlpi", C.c_float), ("start_match", C.c_int32)]
+                ("lpi", C.c_float), ("ilpi", C.c_float), ("mlpi", C.c_float), ("start_match", C.c_int32),
+                ("ext_lo", C.c_int32), ("ext_hi", C.c_int32)]
 
 
 BEST_DTYPE = np.dtype([("q_tx", "<i4"), ("t_tx", "<i4"), ("cds_start", "<i4"), ("cds_end", "<i4"), ("duplicity", "<i4"),
                        ("n_rows", "<i4"), ("row_off", "<i8"), ("best_row", "<i8"), ("lpi", "<f4"), ("ilpi", "<f4"),
-                       ("mlpi", "<f4"), ("start_match", "<i4")])
+                       ("mlpi", "<f4"), ("start_match", "<i4"), ("ext_lo", "<i4"), ("ext_hi", "<i4")])
 assert BEST_DTYPE.itemsize == C.sizeof(_Best)
 
 _ROW_I32 = ["row_q_tx", "row_t_tx", "row_seg_start", "row_seg_end", "row_cds_start", "row_cds_end"]
@@ -99,6 +101,7 @@ class _Results(C.Structure):
     _fields_ = ([("n_queries", C.c_int32), ("n_rows", C.c_int64), ("best", C.c_void_p)]
                 + [(n, C.c_void_p) for n in _ROW_I32] + [(n, C.c_void_p) for n in _ROW_U8]
                 + [(n, C.c_void_p) for n in _ROW_I32B] + [(n, C.c_void_p) for n in _ROW_F32]
+                + [("row_ext_lo", C.c_void_p), ("row_ext_hi", C.c_void_p)]
                 + [("print_order", C.c_void_p), ("ms_h2d", C.c_float), ("ms_kernels", C.c_float), ("ms_d2h", C.c_float)])
 
 
@@ -109,7 +112,7 @@ class _AlnOut(C.Structure):
 _BATCH_ARRAYS = [("seq", np.uint8), ("seq_off", np.int64), ("bundle_start", np.int32), ("bundle_tx_off", np.int32),
                  ("tx_kind", np.uint8), ("tx_strand", np.uint8), ("tx_seg_off", np.int32), ("tx_cds_start", np.int32),
                  ("tx_cds_end", np.int32), ("tx_tid_class", np.int32), ("segs", np.int32), ("seg_phase", np.int8),
-                 ("seg_seq_off", np.int32)]
+                 ("seg_seq_off", np.int32), ("tx_ext_lo", np.int32), ("tx_ext_hi", np.int32)]
 
 
 def _view(ptr, n, dtype):
@@ -174,7 +177,8 @@ class Batch:
             tx_seg_off=_view(s.tx_seg_off, nt + 1, np.int32), tx_cds_start=_view(s.tx_cds_start, nt, np.int32),
             tx_cds_end=_view(s.tx_cds_end, nt, np.int32), tx_tid_class=_view(s.tx_tid_class, nt, np.int32),
             segs=_view(s.segs, ns * 2, np.int32), seg_phase=_view(s.seg_phase, ns, np.int8),
-            seg_seq_off=_view(s.seg_seq_off, ns if s.seg_seq_off else 0, np.int32))
+            seg_seq_off=_view(s.seg_seq_off, ns if s.seg_seq_off else 0, np.int32),
+            tx_ext_lo=_view(s.tx_ext_lo, nt if s.tx_ext_lo else 0, np.int32), tx_ext_hi=_view(s.tx_ext_hi, nt if s.tx_ext_hi else 0, np.int32))
         b = cls.__new__(cls)
         b.arrays = arrays
         b.arrays["segs"] = b.arrays["segs"].reshape(-1, 2)
@@ -227,6 +231,9 @@ class Results:
             for name in _ROW_F32:
                 self.rows[name[4:]] = _view(getattr(r, name), n, np.float32).copy()
             self.rows["print_order"] = _view(r.print_order, n, np.int64).copy()
+            if r.row_ext_lo:   # --overhang only
+                self.rows["ext_lo"] = _view(r.row_ext_lo, n, np.int32).copy()
+                self.rows["ext_hi"] = _view(r.row_ext_hi, n, np.int32).copy()
         self.ms_h2d, self.ms_kernels, self.ms_d2h = float(r.ms_h2d), float(r.ms_kernels), float(r.ms_d2h)
 
     def d2h_bytes(self):
@@ -313,6 +320,8 @@ def load_host_library(path=None):
     lib.orfxh_last_error.restype = C.c_char_p
     lib.orfxh_load.restype = C.c_int
     lib.orfxh_load.argtypes = [C.POINTER(C.c_void_p), C.c_char_p, C.POINTER(C.c_char_p), C.c_int, C.c_char_p, C.c_int, C.c_int]
+    lib.orfxh_load_overhang.restype = C.c_int
+    lib.orfxh_load_overhang.argtypes = lib.orfxh_load.argtypes + [C.c_int, C.c_int]
     lib.orfxh_count.restype = C.c_int64
     lib.orfxh_count.argtypes = [C.c_void_p, C.c_int]
     lib.orfxh_pack.restype = C.c_int
@@ -490,12 +499,13 @@ class Context:
 class Workload:
     """Loaded + prepared + bundled transcriptome (orfxh_workload): orfanage.cpp:313-367."""
 
-    def __init__(self, query, templates, reference=None, use_id=False, keep_all_cds=False):
+    def __init__(self, query, templates, reference=None, use_id=False, keep_all_cds=False, overhang=0, spliced_overhang=False):
         self.lib = load_host_library()
         self.handle = C.c_void_p()
         arr = (C.c_char_p * len(templates))(*[t.encode() for t in templates])
-        rc = self.lib.orfxh_load(C.byref(self.handle), query.encode(), arr, len(templates),
-                                 reference.encode() if reference else None, int(use_id), int(keep_all_cds))
+        rc = self.lib.orfxh_load_overhang(C.byref(self.handle), query.encode(), arr, len(templates),
+                                          reference.encode() if reference else None, int(use_id), int(keep_all_cds),
+                                          int(overhang), int(spliced_overhang))
         if rc != 0:
             raise OrfxError(rc, self.lib.orfxh_last_error().decode())
 

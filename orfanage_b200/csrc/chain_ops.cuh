@@ -12,7 +12,18 @@ struct TxView {
     int L;        // spliced length
     bool plus;    // strand == '+'; every other strand byte is handled as the reverse strand, as the
                   // reference does (`strand == '+' ? ... : ...` throughout Transcriptome.cpp)
+    // --overhang: the row's query copy may have grown (Transcriptome.cpp:418-429, 461-474): its first segment
+    // starts xlo bases earlier, its last one ends xhi bases later; L includes both.  0 everywhere else.
+    int xlo, xhi;
 };
+__device__ __forceinline__ orfx_seg vseg(const TxView& v, int k) {
+    orfx_seg s = v.segs[k];
+    if (k == 0) s.start -= v.xlo;
+    if (k == v.n - 1) s.end += v.xhi;
+    return s;
+}
+__device__ __forceinline__ int vcum(const TxView& v, int k) { return v.cum[k] + (k > 0 ? v.xlo : 0); }
+__device__ __forceinline__ void tx_grow(TxView& v, int dlo, int dhi) { v.xlo += dlo; v.xhi += dhi; v.L += dlo + dhi; }
 
 __device__ __forceinline__ TxView tx_view(const DevBatch& B, int tx) {
     TxView v;
@@ -22,24 +33,25 @@ __device__ __forceinline__ TxView tx_view(const DevBatch& B, int tx) {
     v.n = B.tx_seg_off[tx + 1] - s0;
     v.L = B.tx_len[tx];
     v.plus = B.tx_strand[tx] == '+';
+    v.xlo = v.xhi = 0;
     return v;
 }
 
 // index of the segment containing genomic position g, or -1
 __device__ __forceinline__ int seg_of_genomic(const TxView& v, int g) {
     int lo = 0, hi = v.n - 1;
-    if (hi < 0 || g < v.segs[0].start) return -1;
+    if (hi < 0 || g < v.segs[0].start - v.xlo) return -1;
     while (lo < hi) {
         int mid = (lo + hi + 1) >> 1;
-        if (v.segs[mid].start <= g) lo = mid; else hi = mid - 1;
+        if (v.segs[mid].start <= g) lo = mid; else hi = mid - 1;   // mid >= 1: never the grown start
     }
-    return g <= v.segs[lo].end ? lo : -1;
+    return g <= vseg(v, lo).end ? lo : -1;
 }
 // genomic -> transcript-order offset (CHAIN::genome2nt, Transcriptome.h:447-462); -1 when not exonic
 __device__ __forceinline__ int g2t(const TxView& v, int g) {
     int k = seg_of_genomic(v, g);
     if (k < 0) return -1;
-    int u = v.cum[k] + (g - v.segs[k].start);
+    int u = vcum(v, k) + (g - vseg(v, k).start);
     return v.plus ? u : v.L - 1 - u;
 }
 // index of the segment holding genomic-order spliced offset u (0 <= u < L)
@@ -47,7 +59,7 @@ __device__ __forceinline__ int seg_of_offset(const TxView& v, int u) {
     int lo = 0, hi = v.n - 1;
     while (lo < hi) {
         int mid = (lo + hi + 1) >> 1;
-        if (v.cum[mid] <= u) lo = mid; else hi = mid - 1;
+        if (vcum(v, mid) <= u) lo = mid; else hi = mid - 1;
     }
     return lo;
 }
@@ -55,7 +67,7 @@ __device__ __forceinline__ int seg_of_offset(const TxView& v, int u) {
 __device__ __forceinline__ int t2g(const TxView& v, int p) {
     int u = v.plus ? p : v.L - 1 - p;
     int k = seg_of_offset(v, u);
-    return v.segs[k].start + (u - v.cum[k]);
+    return vseg(v, k).start + (u - vcum(v, k));
 }
 
 // ---- in-frame scans over a transcript's bit mask (bit p = codon starting at spliced position p) ----

@@ -154,7 +154,10 @@ __global__ void __launch_bounds__(CSCAN_THREADS) codon_scan_kernel(DevBatch B, i
     const int64_t tile = (int64_t)blockIdx.x * CSCAN_THREADS + tid;
     if (tile >= n_tiles) return;
     const int tx = B.tile_tx[tile];
-    const int L = B.tx_len[tx];
+    // --overhang: the scanned chain is the exon chain with its first segment started xlo bases earlier and its last
+    // one ended xhi bases later (the usable flanks, orfx_batch::tx_ext_lo / tx_ext_hi)
+    const int xlo = B.tx_ext_lo ? B.tx_ext_lo[tx] : 0, xhi = B.tx_ext_hi ? B.tx_ext_hi[tx] : 0;
+    const int L = B.tx_len[tx] + xlo + xhi;
     const int nwords = (L + 31) >> 5;
     const int w0 = (int)(tile - B.tx_tile_off[tx]) * SCAN_TILE_WORDS;
     const int nw = min(SCAN_TILE_WORDS, nwords - w0);
@@ -167,11 +170,12 @@ __global__ void __launch_bounds__(CSCAN_THREADS) codon_scan_kernel(DevBatch B, i
     const int base_sh = (int)(base & 31);
     const int bstart = isl ? 0 : B.bundle_start[bundle];
     const uint4* __restrict__ pl = reinterpret_cast<const uint4*>(B.planes) + (plus ? 0 : B.plane_words) + (base >> 5);
-    const int32_t* __restrict__ cum = B.seg_cum + s0;
+    const int32_t* __restrict__ cum0 = B.seg_cum + s0;
     const orfx_seg* __restrict__ segs = B.segs + s0;
     const int32_t* __restrict__ sso = isl ? B.seg_seq_off + s0 : nullptr;
-    auto cum_at = [&](int k) { return k < nseg ? cum[k] : L; };
-    auto pos_at = [&](int k) { return (isl ? sso[k] : segs[k].start - bstart) + base_sh; };
+    auto cum = [&](int k) { return cum0[k] + (k > 0 ? xlo : 0); };
+    auto cum_at = [&](int k) { return k < nseg ? cum(k) : L; };
+    auto pos_at = [&](int k) { return (isl ? sso[k] : segs[k].start - bstart) + base_sh - (k == 0 ? xlo : 0); };
 
     const int p_lo = w0 << 5;
     const int nbits = min(L, ((w0 + nw) << 5) + 2) - p_lo;   // spliced positions this run reads, look-ahead included
@@ -180,10 +184,10 @@ __global__ void __launch_bounds__(CSCAN_THREADS) codon_scan_kernel(DevBatch B, i
     int k;
     {
         int lo = 0, hi = nseg - 1;
-        while (lo < hi) { const int mid = (lo + hi + 1) >> 1; if (cum[mid] <= u) lo = mid; else hi = mid - 1; }
+        while (lo < hi) { const int mid = (lo + hi + 1) >> 1; if (cum(mid) <= u) lo = mid; else hi = mid - 1; }
         k = lo;
     }
-    int c0 = cum[k], c1 = cum_at(k + 1);
+    int c0 = cum(k), c1 = cum_at(k + 1);
     int rem = plus ? c1 - u : u - c0 + 1;     // positions left in the current exon, in reading direction
     int bit = pos_at(k) + (u - c0);           // plane bit of the next position to read
     Win w{0, 0, 0, 0};
@@ -207,7 +211,7 @@ __global__ void __launch_bounds__(CSCAN_THREADS) codon_scan_kernel(DevBatch B, i
             bit += plus ? take : -take;
             if (rem == 0 && produced < nbits) {   // next exon in reading direction
                 k += plus ? 1 : -1;
-                c0 = cum[k]; c1 = cum_at(k + 1);
+                c0 = cum(k); c1 = cum_at(k + 1);
                 rem = c1 - c0;
                 bit = pos_at(k) + (plus ? 0 : rem - 1);
             }

@@ -383,7 +383,12 @@ static size_t clean_cds(const Options& opt, Transcriptome& tr, const Backend& be
         if (pb.tx_kind[x] != ORFX_TX_QUERY) continue;
         Tx& t = tr.txs[(size_t)pb.tx_global[(size_t)x]];
         if (!keep[k]) { t.remove_cds(); dirty++; }
-        else if (cs[k] != t.cds_start || ce[k] != t.cds_end) { t.cds_start = cs[k]; t.cds_end = ce[k]; t.cds_phase = 0; t.build_cds(); }
+        else if (cs[k] != t.cds_start || ce[k] != t.cds_end) {
+            // --overhang: a rescued CDS may reach into the flank; the terminal exons grow with it (cpp:418-429, 461-474;
+            // the template's exon chain is replaced by its CDS chain right after, orfanage.cpp:351)
+            if (!t.exons.empty()) { t.exons.front().s = std::min(t.exons.front().s, cs[k]); t.exons.back().e = std::max(t.exons.back().e, ce[k]); }
+            t.cds_start = cs[k]; t.cds_end = ce[k]; t.cds_phase = 0; t.build_cds();
+        }
         k++;
     }
     return dirty;

@@ -100,9 +100,10 @@ struct orfx_ctx {
     DBuf d_need, d_planes, d_heavy, d_heavy_count;
     DBuf d_cnt_q, d_cnt_words, d_cnt_tiles, d_cnt_rows, d_scan_tmp, d_ord;
     DBuf d_clean_keep, d_clean_s, d_clean_e, d_keys;
+    DBuf d_xlo, d_xhi;   // --overhang flanks
     // rows
-    DBuf r_i32[16], r_f32[3], r_u8[3], r_order, d_best;
-    HBuf h_totals, h_best, h_i32[16], h_f32[3], h_u8[3], h_order;
+    DBuf r_i32[16], r_f32[3], r_u8[3], r_order, d_best, r_ext[2];
+    HBuf h_totals, h_best, h_i32[16], h_f32[3], h_u8[3], h_order, h_ext[2];
     DevBatch B;
     DevRows R;
     bool resident = false, pending = false, have_results = false;
@@ -162,6 +163,12 @@ int upload_batch(orfx_ctx* c, const orfx_batch* b, bool overlap = false) {
     CU(cp(c->d_phase, b->seg_phase, ns));
     const bool islands = seqb && b->seg_seq_off;
     if (islands) { CU(c->d_sso.ensure(ns * 4 + 4)); CU(cp(c->d_sso, b->seg_seq_off, ns * 4)); }
+    const bool flanks = seqb && c->P.overhang > 0;
+    if (flanks) {
+        if (nt && (!b->tx_ext_lo || !b->tx_ext_hi)) return fail(ORFX_E_INVALID, "params.overhang > 0 needs batch.tx_ext_lo / tx_ext_hi");
+        CU(c->d_xlo.ensure(nt * 4 + 4)); CU(c->d_xhi.ensure(nt * 4 + 4));
+        CU(cp(c->d_xlo, b->tx_ext_lo, nt * 4)); CU(cp(c->d_xhi, b->tx_ext_hi, nt * 4));
+    }
     c->seq_in_flight = false;
     if (seqb && overlap) {
         CU(cudaEventRecord(c->ev_chains, s));
@@ -202,6 +209,8 @@ int upload_batch(orfx_ctx* c, const orfx_batch* b, bool overlap = false) {
     B.tx_mask_off = c->d_mask_off.as<int64_t>(); B.tx_tile_off = c->d_tile_off.as<int64_t>(); B.tx_q_off = c->d_q_off.as<int64_t>();
     B.q_list = c->d_q_list.as<int32_t>(); B.q_row_off = c->d_row_off.as<int64_t>();
     B.seg_seq_off = islands ? c->d_sso.as<int32_t>() : nullptr;
+    B.tx_ext_lo = flanks ? c->d_xlo.as<int32_t>() : nullptr;
+    B.tx_ext_hi = flanks ? c->d_xhi.as<int32_t>() : nullptr;
     B.bundle_need = c->d_need.as<uint8_t>(); B.planes = c->d_planes.as<uint32_t>(); B.plane_words = (int64_t)plane_words;
     c->resident = true;
     c->have_results = false;
@@ -262,6 +271,11 @@ int run_path(orfx_ctx* c) {
     R.lpi = c->r_f32[0].as<float>(); R.ilpi = c->r_f32[1].as<float>(); R.mlpi = c->r_f32[2].as<float>();
     R.status = c->r_u8[0].as<uint8_t>(); R.pass = c->r_u8[1].as<uint8_t>(); R.start_match = c->r_u8[2].as<uint8_t>();
     R.print_order = c->r_order.as<int64_t>();
+    R.ext_lo = R.ext_hi = nullptr;
+    if (B.tx_ext_lo) {
+        for (int i = 0; i < 2; i++) CU(c->r_ext[i].ensure((size_t)nrows * 4 + 4));
+        R.ext_lo = c->r_ext[0].as<int32_t>(); R.ext_hi = c->r_ext[1].as<int32_t>();
+    }
 
     stage_begin(c, ST_FILL);
     c->n_launches += launch_fill_rows(B, R, (int)nq, s);
@@ -313,6 +327,7 @@ int download_results(orfx_ctx* c) {
         for (int i = 0; i < 3; i++) { CU(c->h_u8[i].ensure(nr)); CU(cudaMemcpyAsync(c->h_u8[i].p, c->r_u8[i].p, nr, cudaMemcpyDeviceToHost, s)); }
         CU(c->h_order.ensure(nr * 8));
         CU(cudaMemcpyAsync(c->h_order.p, c->r_order.p, nr * 8, cudaMemcpyDeviceToHost, s));
+        if (c->R.ext_lo) for (int i = 0; i < 2; i++) { CU(c->h_ext[i].ensure(nr * 4)); CU(cudaMemcpyAsync(c->h_ext[i].p, c->r_ext[i].p, nr * 4, cudaMemcpyDeviceToHost, s)); }
     }
     return ORFX_OK;
 }
@@ -330,6 +345,7 @@ void fill_results(orfx_ctx* c, orfx_results* r) {
         r->row_lpi = c->h_f32[0].as<float>(); r->row_ilpi = c->h_f32[1].as<float>(); r->row_mlpi = c->h_f32[2].as<float>();
         r->row_status = c->h_u8[0].as<uint8_t>(); r->row_pass = c->h_u8[1].as<uint8_t>(); r->row_start_match = c->h_u8[2].as<uint8_t>();
         r->print_order = c->h_order.as<int64_t>();
+        if (c->R.ext_lo && c->n_rows) { r->row_ext_lo = c->h_ext[0].as<int32_t>(); r->row_ext_hi = c->h_ext[1].as<int32_t>(); }
     }
 }
 
@@ -351,7 +367,7 @@ int check_params(const orfx_params* p) {
     if (!p) return fail(ORFX_E_INVALID, "null params");
     if (p->n_modes < 0 || p->n_modes > 8) return fail(ORFX_E_INVALID, "n_modes out of range");
     for (int i = 0; i < p->n_modes; i++) if (p->mode_array[i] < 0 || p->mode_array[i] > ORFX_MODE_FIRST) return fail(ORFX_E_INVALID, "invalid mode");
-    if (p->overhang != 0) return fail(ORFX_E_UNSUPPORTED, "--overhang > 0 is not implemented in this build");
+    if (p->overhang < 0) return fail(ORFX_E_INVALID, "negative overhang");
     return ORFX_OK;
 }
 
@@ -454,7 +470,8 @@ void orfx_destroy(orfx_ctx* c) {
     DBuf* d[] = {&c->d_sso, &c->d_seq, &c->d_seq_off, &c->d_bstart, &c->d_btx_off, &c->d_kind, &c->d_strand, &c->d_seg_off, &c->d_cds_s, &c->d_cds_e, &c->d_tid,
                  &c->d_segs, &c->d_phase, &c->d_seg_cum, &c->d_tx_len, &c->d_tx_bundle, &c->d_mask_off, &c->d_tile_off, &c->d_q_off, &c->d_q_list,
                  &c->d_row_off, &c->d_tile_tx, &c->d_stop, &c->d_start, &c->d_need, &c->d_planes, &c->d_heavy, &c->d_heavy_count, &c->d_cnt_q, &c->d_cnt_words, &c->d_cnt_tiles, &c->d_cnt_rows, &c->d_scan_tmp,
-                 &c->d_ord, &c->r_order, &c->d_best, &c->d_clean_keep, &c->d_clean_s, &c->d_clean_e, &c->d_keys};
+                 &c->d_ord, &c->r_order, &c->d_best, &c->d_clean_keep, &c->d_clean_s, &c->d_clean_e, &c->d_keys,
+                 &c->d_xlo, &c->d_xhi, &c->r_ext[0], &c->r_ext[1]};
     for (DBuf* b : d) b->free_();
     for (auto& b : c->r_i32) b.free_();
     for (auto& b : c->r_f32) b.free_();
@@ -463,6 +480,7 @@ void orfx_destroy(orfx_ctx* c) {
     for (auto& b : c->h_i32) b.free_();
     for (auto& b : c->h_f32) b.free_();
     for (auto& b : c->h_u8) b.free_();
+    for (auto& b : c->h_ext) b.free_();
     for (auto& ev : c->ev) if (ev) cudaEventDestroy(ev);
     for (int i = 0; i < ST_N; i++) { cudaEventDestroy(c->st_ev[i][0]); cudaEventDestroy(c->st_ev[i][1]); }
     cudaEventDestroy(c->run_ev[0]); cudaEventDestroy(c->run_ev[1]);
@@ -543,6 +561,12 @@ int64_t orfx_get_masks(orfx_ctx* c, int32_t tx, uint32_t* stop_bits, uint32_t* s
     if (cudaMemcpy(&L, c->B.tx_len + tx, 4, cudaMemcpyDeviceToHost) != cudaSuccess) return fail(ORFX_E_CUDA, "copy len");
     if (cudaMemcpy(&kind, c->B.tx_kind + tx, 1, cudaMemcpyDeviceToHost) != cudaSuccess) return fail(ORFX_E_CUDA, "copy kind");
     if (kind != ORFX_TX_QUERY) return fail(ORFX_E_INVALID, "not a query transcript");
+    if (c->B.tx_ext_lo) {   // --overhang: the scanned chain covers the flanks
+        int32_t x[2];
+        if (cudaMemcpy(&x[0], c->B.tx_ext_lo + tx, 4, cudaMemcpyDeviceToHost) != cudaSuccess || cudaMemcpy(&x[1], c->B.tx_ext_hi + tx, 4, cudaMemcpyDeviceToHost) != cudaSuccess)
+            return fail(ORFX_E_CUDA, "copy flanks");
+        L += x[0] + x[1];
+    }
     int64_t words = ((int64_t)L + 31) / 32;
     if (words > max_words || words > off[1] - off[0]) return fail(ORFX_E_INVALID, "mask buffer too small");
     if (cudaMemcpy(stop_bits, c->B.stop_mask + off[0], (size_t)words * 4, cudaMemcpyDeviceToHost) != cudaSuccess) return fail(ORFX_E_CUDA, "copy stop mask");

@@ -26,6 +26,8 @@ struct DevBatch {
     const orfx_seg* segs;
     const int8_t* seg_phase;
     const int32_t* seg_seq_off;   // islands layout (else nullptr)
+    const int32_t* tx_ext_lo;     // --overhang: usable flank below the first / above the last exon of each query (else nullptr)
+    const int32_t* tx_ext_hi;
     // derived
     int32_t* seg_cum;        // [n_segs] bases of the transcript before this segment (genomic order)
     int32_t* tx_len;         // [n_tx] spliced length
@@ -53,6 +55,7 @@ struct DevRows {
     float *lpi, *ilpi, *mlpi;
     uint8_t *status, *pass, *start_match;
     int64_t* print_order;
+    int32_t *ext_lo, *ext_hi;   // --overhang: exon-chain growth of the row's query copy (else nullptr)
 };
 
 static constexpr int SCAN_TILE_WORDS = 16;     // mask words (32 spliced positions each) per codon-scan run (one thread)

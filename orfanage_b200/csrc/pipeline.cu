@@ -110,6 +110,7 @@ __global__ void __launch_bounds__(256) tx_prep_kernel(DevBatch B, int64_t* cnt_q
     if (sub != 0) return;
     B.tx_len[tx] = acc;
     bool isq = B.tx_kind[tx] == ORFX_TX_QUERY;
+    if (isq && B.tx_ext_lo) acc += B.tx_ext_lo[tx] + B.tx_ext_hi[tx];   // the scanned chain covers the --overhang flanks
     const int64_t words = acc > 0 ? (acc + 31) / 32 : 1;
     cnt_q[tx] = isq ? 1 : 0;
     cnt_tiles[tx] = isq ? (words + SCAN_TILE_WORDS - 1) / SCAN_TILE_WORDS : 0;
@@ -341,7 +342,7 @@ namespace {
 // are walked 5'->3' until the first piece where both CDSs are in the same frame; the start is the
 // nearest ATG whose transcript position does not exceed that piece's CDS-relative position (mixed
 // coordinate systems exactly as written, cpp:581-590), else the farthest ATG.
-__device__ int guided_start(const TxView& q, const TxView& t, const uint32_t* start_mask, int far, int a, int e, int lb) {
+__device__ int guided_start(const TxView& q, const TxView& t, const uint32_t* start_mask, int far, int a, int e, int lb, int o) {
     const int g_far = t2g(q, far), g_e = t2g(q, e);
     const int glo = min(g_far, g_e), ghi = max(g_far, g_e);
     const bool plus = q.plus;
@@ -349,7 +350,7 @@ __device__ int guided_start(const TxView& q, const TxView& t, const uint32_t* st
     uint32_t Q = 0;
     int qi = seg_of_genomic(q, plus ? glo : ghi);
     for (; qi >= 0 && qi < q.n && !done; qi += plus ? 1 : -1) {
-        const orfx_seg qs = q.segs[qi];
+        const orfx_seg qs = vseg(q, qi);
         if (qs.end < glo || qs.start > ghi) break;
         const int s = max(qs.start, glo), en = min(qs.end, ghi);
         if (plus) {
@@ -359,7 +360,7 @@ __device__ int guided_start(const TxView& q, const TxView& t, const uint32_t* st
                 const orfx_seg ts = t.segs[tj];
                 if (ts.start > en) break;
                 const int pos5 = max(s, ts.start);
-                const uint32_t q_tpos = (uint32_t)(q.cum[qi] + (pos5 - qs.start) - far);
+                const uint32_t q_tpos = (uint32_t)(vcum(q, qi) + (pos5 - qs.start) - far);
                 const uint32_t t_tpos = (uint32_t)(t.cum[tj] + (pos5 - ts.start));
                 seen = true; Q = q_tpos;
                 if (t_tpos % 3 == q_tpos % 3) { done = true; break; }
@@ -371,7 +372,7 @@ __device__ int guided_start(const TxView& q, const TxView& t, const uint32_t* st
                 const orfx_seg ts = t.segs[tj];
                 if (ts.end < s) break;
                 const int pos5 = min(en, ts.end);
-                const uint32_t q_tpos = (uint32_t)(q.L - 1 - (q.cum[qi] + (pos5 - qs.start)) - far);
+                const uint32_t q_tpos = (uint32_t)(q.L - 1 - (vcum(q, qi) + (pos5 - qs.start)) - far);
                 const uint32_t t_tpos = (uint32_t)(t.L - 1 - (t.cum[tj] + (pos5 - ts.start)));
                 seen = true; Q = q_tpos;
                 if (t_tpos % 3 == q_tpos % 3) { done = true; break; }
@@ -383,7 +384,7 @@ __device__ int guided_start(const TxView& q, const TxView& t, const uint32_t* st
     const uint32_t r = (uint32_t)(a % 3);
     if (lim < r) return far;
     const int p = (int)(lim - ((lim - r) % 3));
-    const int m = prev_inframe(start_mask, p);
+    const int m = prev_inframe(start_mask, p + o) - o;   // o: mask index of transcript position 0 (--overhang flank)
     return m >= lb ? m : far;
 }
 
@@ -485,21 +486,21 @@ __device__ __forceinline__ UMap umap_then(const UMap& a, const UMap& b) {
 __device__ int union_sweep_warp(const TxView& q, const TxView& t, int qk0, int qk1, int cs, int ce, int lane, SweepSums& S) {
     auto tcum = [&](int k) { return k < t.n ? t.cum[k] : t.L; };
     S.match = S.bin0 = S.bin1 = S.bin2 = 0;
-    const int qbase = q.cum[qk0] + (cs - q.segs[qk0].start);
+    const int qbase = vcum(q, qk0) + (cs - vseg(q, qk0).start);
     int state = 0;
-    int total = tcum(first_end_ge(t.segs, 0, t.n, max(q.segs[qk0].start, cs)));
+    int total = tcum(first_end_ge(t.segs, 0, t.n, max(vseg(q, qk0).start, cs)));
     for (int base = qk0; base <= qk1; base += 32) {
         const int i = base + lane;
         const bool valid = i <= qk1;
         orfx_seg e = {0, -1};
         int c1s = 0, c1e = -1, F = t.n;
         if (valid) {
-            e = q.segs[i];
+            e = vseg(q, i);
             c1s = max(e.start, cs); c1e = min(e.end, ce);
             F = first_end_ge(t.segs, 0, t.n, c1s);
         }
         int Fn = __shfl_down_sync(0xffffffffu, F, 1);
-        if (lane == 31 && i < qk1) Fn = first_end_ge(t.segs, F, t.n, q.segs[i + 1].start);
+        if (lane == 31 && i < qk1) Fn = first_end_ge(t.segs, F, t.n, vseg(q, i + 1).start);
         UMap m = {0, 0, 1, 0};   // identity
         if (valid) {
             // sweep: the match pieces under this query segment
@@ -507,7 +508,7 @@ __device__ int union_sweep_warp(const TxView& q, const TxView& t, int qk0, int q
                 const orfx_seg c = t.segs[j];
                 if (c.start > c1e) break;
                 const int lo = max(c1s, c.start), hi = min(c1e, c.end);
-                const int qb = q.cum[i] + (lo - e.start) - qbase, tb = t.cum[j] + (lo - c.start);
+                const int qb = vcum(q, i) + (lo - e.start) - qbase, tb = t.cum[j] + (lo - c.start);
                 int d = (qb - tb) % 3; if (d < 0) d += 3;
                 const int len = hi - lo + 1;
                 S.match += len;
@@ -580,7 +581,7 @@ __device__ __forceinline__ ChainScore score_chains(const TxView& q, const TxView
     if (!WARP) {
         int i = qk0, j = 0;
         while (i <= qk1 && j < t.n) {
-            const int c1s = max(q.segs[i].start, cs), c1e = min(q.segs[i].end, ce);
+            const int c1s = max(vseg(q, i).start, cs), c1e = min(vseg(q, i).end, ce);
             const int c2s = t.segs[j].start, c2e = t.segs[j].end;
             if (c1e < c2s) { ulen += c1e - c1s + 1; i++; }
             else if (c2e < c1s) { ulen += c2e - c2s + 1; j++; }
@@ -592,7 +593,7 @@ __device__ __forceinline__ ChainScore score_chains(const TxView& q, const TxView
     if (!WARP) {
         int bin[3] = {0, 0, 0};
         int i = qk0, j = 0;
-        int qs = max(q.segs[i].start, cs), qe = min(q.segs[i].end, ce);
+        int qs = max(vseg(q, i).start, cs), qe = min(vseg(q, i).end, ce);
         int ts = 0, te = -1;
         if (t.n > 0) { ts = t.segs[0].start; te = t.segs[0].end; }
         bool hq = true, ht = t.n > 0;
@@ -600,7 +601,7 @@ __device__ __forceinline__ ChainScore score_chains(const TxView& q, const TxView
             if (hq && (!ht || qe < ts)) {          // query-only remainder
                 extra += qe - qs + 1;
                 i++; hq = i <= qk1;
-                if (hq) { qs = max(q.segs[i].start, cs); qe = min(q.segs[i].end, ce); }
+                if (hq) { qs = max(vseg(q, i).start, cs); qe = min(vseg(q, i).end, ce); }
             } else if (ht && (!hq || te < qs)) {   // template-only remainder
                 missing += te - ts + 1;
                 j++; ht = j < t.n;
@@ -613,7 +614,7 @@ __device__ __forceinline__ ChainScore score_chains(const TxView& q, const TxView
                 bin[d] += hi - lo + 1;
                 match += hi - lo + 1;
                 qs = hi + 1; ts = hi + 1;
-                if (qs > qe) { i++; hq = i <= qk1; if (hq) { qs = max(q.segs[i].start, cs); qe = min(q.segs[i].end, ce); } }
+                if (qs > qe) { i++; hq = i <= qk1; if (hq) { qs = max(vseg(q, i).start, cs); qe = min(vseg(q, i).end, ce); } }
                 if (ts > te) { j++; ht = j < t.n; if (ht) { ts = t.segs[j].start; te = t.segs[j].end; } }
             }
         }
@@ -631,8 +632,9 @@ __device__ __forceinline__ ChainScore score_chains(const TxView& q, const TxView
 // WARP = true: all 32 lanes of a warp work on the same row (heavy bundles); the two O(chain) walks of
 // TX::score are done cooperatively, everything else redundantly, lane 0 stores.
 template <bool WARP>
-__device__ void process_row(const DevBatch& B, const DevRows& R, const orfx_params& P, const int64_t row, const TxView& q, const TxView& t) {
+__device__ void process_row(const DevBatch& B, const DevRows& R, const orfx_params& P, const int64_t row, const TxView& q_in, const TxView& t) {
     const int lane = WARP ? (int)(threadIdx.x & 31) : 0;
+    TxView q = q_in;   // the row's query copy: --overhang may grow its terminal exons
     // defaults: an all-zero Score that does not pass
     int status = R.status[row];
     int key_s = 0, key_e = 0;
@@ -646,6 +648,15 @@ __device__ void process_row(const DevBatch& B, const DevRows& R, const orfx_para
     const int t_cds_start = B.tx_cds_start[tx], t_cds_end = B.tx_cds_end[tx];
     const int t5 = plus ? t_cds_start : t_cds_end;
     int start = 0, e = 0;   // final ORF, transcript coordinates
+    // --overhang: the masks cover [5' flank][transcript][3' flank]; transcript position p is mask bit p + o
+    int E5 = 0, E3 = 0;
+    if (B.tx_ext_lo) { const int lo = B.tx_ext_lo[qx], hi = B.tx_ext_hi[qx]; E5 = plus ? lo : hi; E3 = plus ? hi : lo; }
+    int o = E5;
+    const uint32_t* stopm = nullptr;
+    const uint32_t* startm = nullptr;
+    auto mbit = [&](const uint32_t* m, int p) { return mask_bit(m, p + o); };
+    auto nxt = [&](const uint32_t* m, int p, int lim) { const int r = next_inframe(m, p + o, lim + o); return r < 0 ? -1 : r - o; };   // first hit in [p, lim)
+    auto prv = [&](const uint32_t* m, int p) { const int r = p < 0 ? -1 : prev_inframe(m, p + o); return r < o ? -1 : r - o; };       // last hit in [0, p]
 
     do {
         if (status != ORFX_ST_OK) break;   // no-overlap
@@ -675,23 +686,30 @@ __device__ void process_row(const DevBatch& B, const DevRows& R, const orfx_para
         const int b = a + ((b0 - a + 1) / 3) * 3 - 1;
         start = a; e = b;
         if (P.has_reference) {
-            const uint32_t* stopm = B.stop_mask + B.tx_mask_off[qx];
-            const uint32_t* startm = B.start_mask + B.tx_mask_off[qx];
-            // adjust_stop + extend_to_stop (Transcriptome.cpp:182-201, 400-442): first in-frame stop at or after a
-            const int p0 = next_inframe(stopm, a, q.L);
+            stopm = B.stop_mask + B.tx_mask_off[qx];
+            startm = B.start_mask + B.tx_mask_off[qx];
+            // adjust_stop + extend_to_stop (Transcriptome.cpp:182-201, 400-442): first in-frame stop at or after a,
+            // searched through the 3' flank too (TX::extend_seq, cpp:342-399)
+            const int p0 = nxt(stopm, a, q.L + E3);
             if (p0 == a) { status = ORFX_ST_NOT_RESCUED; break; }
             const bool has_stop = p0 >= 0;
             e = has_stop ? p0 + 2 : b;
+            if (has_stop && P.overhang > 0) {   // stop inside the flank: the terminal exon grows up to it (cpp:418-429)
+                const int g3 = max(p0 + 2 - q.L + 1, 0);
+                if (g3 > 0) tx_grow(q, plus ? 0 : g3, plus ? g3 : 0);
+            }
             // extend_to_start(TX*, non_aug) (Transcriptome.cpp:496-620)
-            const bool m_at_a = mask_bit(startm, a);
+            const bool m_at_a = mbit(startm, a);
             bool found_start = false;
+            bool searched = false;   // the walk over the upstream in-frame ATGs ran and found none
+            int prev_stop = -1, lb = 0;
             if ((m_at_a || P.non_aug) && g_a == t5) found_start = true;
             if (!found_start && P.non_aug) {
                 const int ref = g2t(q, t5);
                 if (ref >= 0 && ref % 3 == a % 3) {
                     bool stop_between = false;
                     for (int i = a;; i -= 3) {   // SEQ::find_inframe_codon('.',';',...,backward,first), common.hpp:420-450
-                        if (mask_bit(stopm, i)) { stop_between = true; break; }
+                        if (mbit(stopm, i)) { stop_between = true; break; }
                         if (i < ref) break;
                         if (i < 3) break;
                     }
@@ -700,21 +718,32 @@ __device__ void process_row(const DevBatch& B, const DevRows& R, const orfx_para
             }
             if (!found_start) {
                 // all in-frame ATG walking back from a until a stop codon or the transcript start
-                const int prev_stop = a >= 3 ? prev_inframe(stopm, a - 3) : -1;
-                const int lb = prev_stop >= 0 ? prev_stop + 3 : a % 3;
-                int far = next_inframe(startm, lb, q.L);
-                if (far > a) far = -1;
+                prev_stop = a >= 3 ? prv(stopm, a - 3) : -1;
+                lb = prev_stop >= 0 ? prev_stop + 3 : a % 3;
+                int far = nxt(startm, lb, a + 1);
                 if (far >= 0) {
                     const int ref = g2t(q, t5);
-                    if (ref >= lb && ref <= a && ref % 3 == a % 3 && mask_bit(startm, ref)) start = ref;
-                    else start = guided_start(q, t, startm, far, a, e, lb);
+                    if (ref >= lb && ref <= a && ref % 3 == a % 3 && mbit(startm, ref)) start = ref;
+                    else start = guided_start(q, t, startm, far, a, e, lb, o);
+                } else searched = true;
+            }
+            // no upstream ATG: extend_to_start(-1, overhang, spliced) (cpp:446-492) walks on into the 5' flank — nearest
+            // in-frame ATG before a stop.  Without a flank it finds nothing either.
+            if (searched && P.overhang > 0 && prev_stop < 0 && lb - 3 + o >= 0) {
+                const int top = lb - 3 + o;   // mask coordinates from here
+                const int m5 = prev_inframe(startm, top), s5 = prev_inframe(stopm, top);
+                if (m5 >= 0 && m5 > s5) {
+                    // as written: the exon grows by overhang - position in the flanked sequence, not by the distance
+                    // to the old 5' end (cpp:461-474); the flank may be shorter than --overhang
+                    const int g5 = max(P.overhang - m5, 0);
+                    tx_grow(q, plus ? g5 : 0, plus ? 0 : g5);
+                    start = m5 - o + g5; e += g5; o -= g5;
                 }
-                // no upstream ATG: extend_to_start(-1,...) finds nothing either (cpp:446-492)
             }
             // adjust_start (Transcriptome.cpp:202-227) unless --non_aug kept the template's start
             const bool at_t5 = t2g(q, start) == t5;
-            if (!(P.non_aug && at_t5) && !mask_bit(startm, start)) {
-                const int m = next_inframe(startm, start, q.L);
+            if (!(P.non_aug && at_t5) && !mbit(startm, start)) {
+                const int m = nxt(startm, start, e - 1);
                 if (m >= 0 && m + 2 <= e) start = m;
             }
         }
@@ -722,10 +751,8 @@ __device__ void process_row(const DevBatch& B, const DevRows& R, const orfx_para
         const int cs = min(gs, ge), ce = max(gs, ge);
         if (P.has_reference) {
             key_s = cs; key_e = ce;
-            const uint32_t* stopm = B.stop_mask + B.tx_mask_off[qx];
-            const uint32_t* startm = B.start_mask + B.tx_mask_off[qx];
-            const bool ends_in_stop = e >= 2 && mask_bit(stopm, e - 2) && ((e - 2 - start) % 3 == 0);
-            const bool front_m = mask_bit(startm, start);
+            const bool ends_in_stop = e >= 2 && mbit(stopm, e - 2) && ((e - 2 - start) % 3 == 0);
+            const bool front_m = mbit(startm, start);
             const bool at_t5 = (plus ? cs : ce) == t5;
             if (!ends_in_stop) { status = ORFX_ST_MISSING_STOP; break; }
             if ((!P.non_aug && !front_m) || (P.non_aug && !front_m && !at_t5)) { status = ORFX_ST_MISSING_START; break; }
@@ -740,7 +767,7 @@ __device__ void process_row(const DevBatch& B, const DevRows& R, const orfx_para
             ulen = cs_.ulen; extra = cs_.extra; missing = cs_.missing; match = cs_.match; inframe = cs_.inframe; outframe = cs_.outframe;
         }
         lpi = pct(qlen, ulen); ilpi = pct(inframe, ulen); mlpi = pct(match, ulen);
-        query_start = plus ? cs - q.segs[0].start : q.segs[q.n - 1].end - ce;
+        query_start = plus ? cs - vseg(q, 0).start : vseg(q, q.n - 1).end - ce;
         start_match = (B.tx_strand[qx] == B.tx_strand[tx]) && ((plus ? cs : ce) == t5);
         pass = 1;
         if (lpi < (float)P.lpi || ilpi < (float)P.ilpi || mlpi < (float)P.mlpi) pass = 0;
@@ -757,6 +784,7 @@ __device__ void process_row(const DevBatch& B, const DevRows& R, const orfx_para
     R.lpi[row] = lpi; R.ilpi[row] = ilpi; R.mlpi[row] = mlpi;
     R.pass[row] = (uint8_t)pass; R.start_match[row] = (uint8_t)start_match;
     R.n_dup[row] = 0;
+    if (R.ext_lo) { R.ext_lo[row] = q.xlo; R.ext_hi[row] = q.xhi; }
 }
 
 __global__ void __launch_bounds__(128) rescue_score_kernel(DevBatch B, DevRows R, orfx_params P) {
@@ -806,7 +834,7 @@ __device__ __forceinline__ TxView hb_view(const DevBatch& B, const HeavyBundle& 
     TxView v;
     const int s0 = B.tx_seg_off[tx];
     v.segs = H.segs + s0; v.cum = H.cum + s0;
-    v.n = B.tx_seg_off[tx + 1] - s0; v.L = B.tx_len[tx]; v.plus = B.tx_strand[tx] == '+';
+    v.n = B.tx_seg_off[tx + 1] - s0; v.L = B.tx_len[tx]; v.plus = B.tx_strand[tx] == '+'; v.xlo = v.xhi = 0;
     return v;
 }
 }  // namespace
@@ -951,26 +979,31 @@ __global__ void __launch_bounds__(128) clean_templates_kernel(DevBatch B, int n_
         if (a < 0 || b < 0 || b < a) break;                    // CDS bounds outside the exon chain: not a usable template
         const uint32_t* stopm = B.stop_mask + B.tx_mask_off[qx];
         const uint32_t* startm = B.start_mask + B.tx_mask_off[qx];
+        // --overhang: the masks cover [5' flank][transcript][3' flank]; transcript position p is mask bit p + o.  Only the
+        // CDS bounds leave this kernel, and t2g extrapolates past the terminal exons, so the chain itself is not grown.
+        int o = 0, E3 = 0;
+        if (B.tx_ext_lo) { const int lo = B.tx_ext_lo[qx], hi = B.tx_ext_hi[qx]; o = q.plus ? lo : hi; E3 = q.plus ? hi : lo; }
         int start = a, e = b;
         if (b - a + 1 < 3) break;                              // rescue_cds: cds_nt_len < 3; no rescue: no codon to test
         if (rescue) {
-            const int p0 = next_inframe(stopm, a, q.L);        // adjust_stop + extend_to_stop
+            int p0 = next_inframe(stopm, a + o, q.L + E3 + o);  // adjust_stop + extend_to_stop (3' flank included)
+            if (p0 >= 0) p0 -= o;
             if (p0 == a) break;                                // nothing left before the first stop: CDS removed
             if (p0 >= 0) e = p0 + 2;
-            if (!non_aug && !mask_bit(startm, a) && a >= 3) {  // extend_to_start(-1, ...): nearest upstream ATG before a stop
-                const int prev_stop = prev_inframe(stopm, a - 3);
-                const int m = prev_inframe(startm, a - 3);
-                if (m >= 0 && m > prev_stop) start = m;
+            if (!non_aug && !mask_bit(startm, a + o) && a - 3 + o >= 0) {  // extend_to_start(-1, ...): nearest upstream ATG before a stop, 5' flank included
+                const int prev_stop = prev_inframe(stopm, a - 3 + o);
+                const int m = prev_inframe(startm, a - 3 + o);
+                if (m >= 0 && m > prev_stop) start = m - o;
             }
-            if (!mask_bit(startm, start)) {                    // adjust_start: first ATG inside the CDS
-                const int m = next_inframe(startm, start, q.L);
-                if (m >= 0 && m + 2 <= e) start = m;
+            if (!mask_bit(startm, start + o)) {                // adjust_start: first ATG inside the CDS
+                int m = next_inframe(startm, start + o, e - 1 + o);
+                if (m >= 0 && m - o + 2 <= e) start = m - o;
             }
         }
         const int naa = (e - start + 1) / 3;
         const int last = start + 3 * (naa - 1);
-        if (!non_aug && !mask_bit(startm, start)) break;       // start codon must be M unless --non_aug
-        if (!mask_bit(stopm, last)) break;                     // last codon must be a stop
+        if (!non_aug && !mask_bit(startm, start + o)) break;   // start codon must be M unless --non_aug
+        if (!mask_bit(stopm, last + o)) break;                 // last codon must be a stop
         if ((e - start + 1) % 3 != 0) break;
         const int g0 = t2g(q, start), g1 = t2g(q, e);
         cs = min(g0, g1); ce = max(g0, g1);
@@ -1008,7 +1041,7 @@ __global__ void __launch_bounds__(128) score_pairs_kernel(DevBatch B, DevRows R,
     const int b = B.tx_bundle[qx];
     int64_t row = B.q_row_off[qi];
     const int qlen = q.L;
-    const int cs = q.n ? q.segs[0].start : 0, ce = q.n ? q.segs[q.n - 1].end : 0;
+    const int cs = q.n ? vseg(q, 0).start : 0, ce = q.n ? vseg(q, q.n - 1).end : 0;
     for (int x = B.bundle_tx_off[b]; x < B.bundle_tx_off[b + 1]; x++) {
         if (B.tx_kind[x] != ORFX_TX_TEMPLATE) continue;
         const TxView t = tx_view(B, x);

@@ -16,8 +16,8 @@ namespace {
 // The records of a block's queries are contiguous (rows are laid out query by query): they are kept in shared memory
 // while they fit, so that the comparisons of the std::sort replay cost a shared-memory load, not an L2 round trip.
 struct __align__(16) RowKey { int k[12]; };
-constexpr int SEL_THREADS = 64;
-constexpr int SEL_SMEM_ROWS = 640;     // 30 KB of keys + 2.5 KB of order per block (a block's queries hold ~270 rows on average)
+constexpr int SEL_THREADS = 128;
+constexpr int SEL_SMEM_ROWS = 768;     // 30 KB of keys + 2.5 KB of order per block (a block's queries hold ~270 rows on average)
 
 __device__ __forceinline__ RowKey make_key(const DevBatch& B, const DevRows& R, const orfx_params& P, int64_t row) {
     RowKey K;
@@ -131,13 +131,14 @@ __global__ void __launch_bounds__(SEL_THREADS) select_kernel(DevBatch B, DevRows
     orfx_best b;
     b.q_tx = B.q_list[qi];
     b.t_tx = -1; b.cds_start = 0; b.cds_end = 0; b.duplicity = 0; b.n_rows = n; b.row_off = r0; b.best_row = -1;
-    b.lpi = b.ilpi = b.mlpi = 0.f; b.start_match = 0;
+    b.lpi = b.ilpi = b.mlpi = 0.f; b.start_match = 0; b.ext_lo = b.ext_hi = 0;
     if (best_front >= 0 && R.pass[r0 + best_front]) {
         const int64_t rb = r0 + best_front;
         if (!mode_all) R.n_dup[rb] = count_distinct_tids(keys, ord, best_g0 + 1, best_g1);
         b.t_tx = R.t_tx[rb]; b.cds_start = R.cds_start[rb]; b.cds_end = R.cds_end[rb];
         b.duplicity = R.n_dup[rb]; b.best_row = rb;
         b.lpi = R.lpi[rb]; b.ilpi = R.ilpi[rb]; b.mlpi = R.mlpi[rb]; b.start_match = R.start_match[rb];
+        if (R.ext_lo) { b.ext_lo = R.ext_lo[rb]; b.ext_hi = R.ext_hi[rb]; }
     }
     best_out[qi] = b;
     for (int i = 0; i < n; i++) R.print_order[r0 + i] = r0 + ord[i];

@@ -49,6 +49,9 @@ SYNTH_RUNS = [
     ("noref", ["--query", "query.gtf", "--mode", "LONGEST_MATCH,BEST"]),
     ("cleant", ["--reference", "genome.fa", "--query", "query.gtf", "--cleant", "--mode", "LONGEST_MATCH,BEST"]),
     ("cleant_rescue", ["--reference", "genome.fa", "--query", "query.gtf", "--cleant", "--rescue"]),
+    # --overhang / --spliced_overhang (TX::extend_seq, Transcriptome.cpp:342-399)
+    ("overhang300", ["--reference", "genome.fa", "--query", "query.gtf", "--overhang", "300"]),
+    ("overhang60_spliced_all", ["--reference", "genome.fa", "--query", "query.gtf", "--overhang", "60", "--spliced_overhang", "--mode", "ALL"]),
 ]
 CMP_RUNS = [   # orfcompare (reference: oracle/_ref/orfcompare_ref) on the same synthetic inputs
     ("t2_vs_t1_ref", ["--query", "template2.gtf", "--template", "template1.gtf", "--reference", "genome.fa"]),

@@ -37,6 +37,11 @@ for seed in $SEEDS; do
   run $d --reference genome.fa --query query.gtf --cleant --rescue --mode LONGEST_MATCH,BEST
   run $d --reference genome.fa --query query.gtf --cleant --rescue --non_aug --mode BEST
   run $d --reference genome.fa --query query.gtf --cleant --minlen 450 --use_id
+  run $d --reference genome.fa --query query.gtf --overhang 30
+  run $d --reference genome.fa --query query.gtf --overhang 300 --mode ALL
+  run $d --reference genome.fa --query query.gtf --overhang 90 --spliced_overhang --mode BEST
+  run $d --reference genome.fa --query query.gtf --overhang 2000 --spliced_overhang --non_aug --mode LONGEST
+  run $d --reference genome.fa --query query.gtf --overhang 150 --cleant --rescue
   TPL="template1.gtf"
   run $d --reference genome.fa --query template2.gtf --keep_all_cds
   run $d --reference genome.fa --query template3.gtf --keep_cds_if_not_found --mode FIRST

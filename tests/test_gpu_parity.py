@@ -112,6 +112,49 @@ def test_codon_scan_masks_match_oracle(synth, oracle_lib, gpu, layout):
     w.close()
 
 
+@pytest.mark.parametrize("seed,overhang,spliced,kw", [(51, 30, False, dict(loci=150)), (52, 300, False, dict(loci=150, titin=0.1, iupac=0.002)),
+                                                      (53, 90, True, dict(loci=100, lower=0.4)), (54, 2000, True, dict(loci=60, queries=12))])
+def test_overhang_matches_oracle(synth, oracle_lib, gpu, seed, overhang, spliced, kw):
+    """--overhang / --spliced_overhang (TX::extend_seq and the exon growth of extend_to_stop / extend_to_start,
+    Transcriptome.cpp:342-492): rows, winners and the growth of every row's query copy, plus
+    the masks over the flanked chains."""
+    import ctypes as C
+    d = synth(seed, **kw)
+    w = ob.Workload(os.path.join(d, "query.gtf"), template_files(d), os.path.join(d, "genome.fa"), overhang=overhang, spliced_overhang=spliced)
+    grown = 0
+    for layout in ("islands4", "windows"):
+        batch = w.pack(layout=layout)
+        a = batch.arrays
+        assert a["tx_ext_lo"].size == a["tx_kind"].size and a["tx_ext_lo"].max() <= overhang and a["tx_ext_hi"].max() > 0
+        for pk in (dict(mode="LONGEST_MATCH,BEST"), dict(mode="ALL", non_aug=True), dict(mode="BEST", lpi=50, ilpi=60, mlpi=70, minlen=300)):
+            params = ob.Params.make(overhang=overhang, spliced_overhang=spliced, **pk)
+            gpu.set_params(params)
+            got = gpu.run(batch)
+            with ob.Context(params, lib=oracle_lib, prefix="orfx_oracle_") as ox:
+                want = ox.run(batch)
+            assert "ext_lo" in want.rows
+            assert_same_results(got, want, "overhang %d seed %d %s %s" % (overhang, seed, layout, pk))
+            grown += int((want.best["ext_lo"] > 0).sum() + (want.best["ext_hi"] > 0).sum())
+    assert grown > 0   # some winners end in the flank
+    # masks over [5' flank][transcript][3' flank]
+    gpu.upload(batch)
+    gpu.run_resident()
+    oracle_lib.orfx_oracle_masks.restype = C.c_int64
+    oracle_lib.orfx_oracle_masks.argtypes = [C.c_void_p, C.c_int32, C.c_void_p, C.c_void_p, C.c_int64]
+    seg_len = a["segs"][:, 1] - a["segs"][:, 0] + 1
+    for tx in np.nonzero(a["tx_kind"] == 0)[0][:150]:
+        L = int(seg_len[a["tx_seg_off"][tx]:a["tx_seg_off"][tx + 1]].sum()) + int(a["tx_ext_lo"][tx]) + int(a["tx_ext_hi"][tx])
+        gl, gstop, gstart = gpu.masks(int(tx), L)
+        words = (L + 31) // 32
+        ostop = np.zeros(words, dtype=np.uint32)
+        ostart = np.zeros(words, dtype=np.uint32)
+        ol = oracle_lib.orfx_oracle_masks(C.byref(batch.struct), int(tx), ostop.ctypes.data, ostart.ctypes.data, words)
+        assert gl == ol == L
+        assert (gstop == ostop).all() and (gstart == ostart).all(), "masks differ for transcript %d" % tx
+    gpu.set_params(ob.Params.make())
+    w.close()
+
+
 def test_config1_golden_batch(gpu):
     """Config 1 (example/query.gtf x example/template.gtf, random chr19, --mode BEST): committed packed
     batch -> CUDA path -> the reference's own stats rows."""

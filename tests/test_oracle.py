@@ -36,6 +36,12 @@ OPTION_GRID = [
     ["--reference", "genome.fa", "--query", "query.gtf", "--cleant", "--rescue", "--mode", "LONGEST_MATCH,BEST"],
     ["--reference", "genome.fa", "--query", "query.gtf", "--cleant", "--rescue", "--non_aug", "--mode", "BEST"],
     ["--reference", "genome.fa", "--query", "query.gtf", "--cleant", "--minlen", "450", "--use_id"],
+    # --overhang (TX::extend_seq and the exon growth of extend_to_stop / extend_to_start)
+    ["--reference", "genome.fa", "--query", "query.gtf", "--overhang", "30"],
+    ["--reference", "genome.fa", "--query", "query.gtf", "--overhang", "300", "--mode", "ALL"],
+    ["--reference", "genome.fa", "--query", "query.gtf", "--overhang", "90", "--spliced_overhang", "--mode", "BEST"],
+    ["--reference", "genome.fa", "--query", "query.gtf", "--overhang", "2000", "--spliced_overhang", "--non_aug", "--mode", "LONGEST"],
+    ["--reference", "genome.fa", "--query", "query.gtf", "--overhang", "150", "--cleant", "--rescue"],
 ]
 SELF_GRID = [   # query file = a template file (queries that carry a CDS)
     (["--reference", "genome.fa", "--query", "template2.gtf", "--keep_all_cds"], ["template1.gtf"]),
