@@ -266,20 +266,51 @@ def ours(args):
     e2e_ms = (time.perf_counter() - t0) * 1e3
     d2h_bytes = int(nq * ob._capi.BEST_DTYPE.itemsize + 32)
 
+    # ---- leg 3: the same call sequence on two contexts, each with half of the loci: the upload of one half overlaps the
+    # kernels of the other (orfx_submit returns once everything is enqueued).  Same work, same bytes, same API.
+    e2e2_ms = None
+    if not args.no_pipelined:
+        halves = [w.pack(k, 2, pinned=True, layout="islands4") for k in range(2)]
+        assert sum(h.n_queries for h in halves) == nq
+        cx2 = ob.Context(params, device=local)
+        pair = [(cx, halves[0]), (cx2, halves[1])]
+        for _ in range(max(1, args.warmup // 2)):
+            for c_, b_ in pair:
+                c_.submit(b_)
+            found2 = sum(int((c_.wait().best["t_tx"] >= 0).sum()) for c_, _ in pair)
+        assert found2 == found, "two half batches find the same ORFs as the whole one"
+        barrier()
+        t0 = time.perf_counter()
+        for _ in range(args.steps):
+            for c_, b_ in pair:
+                c_.submit(b_)
+            for c_, _ in pair:
+                c_.wait(copy=False)
+        barrier()
+        e2e2_ms = (time.perf_counter() - t0) * 1e3
+        cx2.close()
+
     # max over ranks of the timed regions, sum of the units
-    tt = torch.tensor([dev_ms, wall_ms, e2e_ms], dtype=torch.float64, device="cuda")
+    tt = torch.tensor([dev_ms, wall_ms, e2e_ms, e2e2_ms if e2e2_ms is not None else 0.0], dtype=torch.float64, device="cuda")
     cnt = torch.tensor([nq, launches, found, nt_sum], dtype=torch.int64, device="cuda")
+    per_rank = None
     if world > 1:
+        mine = tt.clone()
+        gathered = [torch.zeros_like(tt) for _ in range(world)]
+        dist.all_gather(gathered, mine)   # per-rank device / e2e times beside the max: shards differ (distinct loci per rank)
+        per_rank = {"device_ms_per_step": [round(float(g[0]) / args.steps, 4) for g in gathered],
+                    "e2e_ms_per_step": [round(float(g[2]) / args.steps, 4) for g in gathered],
+                    "e2e_two_contexts_ms_per_step": [round(float(g[3]) / args.steps, 4) for g in gathered]}
         dist.all_reduce(tt, op=dist.ReduceOp.MAX)
         dist.all_reduce(cnt)
-    dev_ms, wall_ms, e2e_ms = [float(x) for x in tt.tolist()]
+    dev_ms, wall_ms, e2e_ms, e2e2_ms = [float(x) for x in tt.tolist()]
     nq_all, launches_all, found_all, nt_all = [int(x) for x in cnt.tolist()]
     align = None
     if rank == 0 and args.align_pairs > 0:
         t = time.time()
         align = alignment_leg(cx, args.align_pairs)
         log("alignment leg: %.1f s, %.1f GCUPS" % (time.time() - t, align["gcups"]))
-    return dict(align=align, rank=rank, world=world, cfg=cfg, nq=nq, nq_all=nq_all, nt_sum=nt_sum, dev_ms=dev_ms, wall_ms=wall_ms, e2e_ms=e2e_ms,
+    return dict(e2e2_ms=e2e2_ms, per_rank=per_rank, align=align, rank=rank, world=world, cfg=cfg, nq=nq, nq_all=nq_all, nt_sum=nt_sum, dev_ms=dev_ms, wall_ms=wall_ms, e2e_ms=e2e_ms,
                 e2e_dev=e2e_dev, stage_ms=stage_ms, launches=launches_all, found=found_all, clocks=clocks, h2d=batch.h2d_bytes,
                 d2h=d2h_bytes, windows=int(batch.arrays["seq"].nbytes), n_templates=w.count("templates"),
                 n_bundles=w.count("active_bundles"))
@@ -440,6 +471,7 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--loci", type=int, default=0, help="override the number of loci (development only; 0 = configs[1])")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-pipelined", action="store_true", help="skip the two-context end-to-end leg")
     ap.add_argument("--align-pairs", type=int, default=50000, help="protein pairs of the alignment leg (0 = skip; configs[4] = 1000000)")
     args = ap.parse_args()
     quiet_stdout()
@@ -454,6 +486,16 @@ def main():
     ms_per_step = m["dev_ms"] / K
     value = m["nq_all"] / (ms_per_step / 1e3)
     e2e_value = m["nq_all"] / (m["e2e_ms"] / K / 1e3)
+    e2e_api = "orfx_submit + orfx_wait on a pinned host batch (include/orfx.h)"
+    e2e_single = {"value": e2e_value, "ms_per_step": m["e2e_ms"] / K}
+    e2e_step_ms = m["e2e_ms"] / K
+    if m.get("e2e2_ms"):   # two contexts, half of the loci each: same calls, same bytes; uploads overlap kernels
+        v2 = m["nq_all"] / (m["e2e2_ms"] / K / 1e3)
+        if v2 > e2e_value:
+            e2e_value, e2e_step_ms = v2, m["e2e2_ms"] / K
+            e2e_api = ("orfx_submit + orfx_wait on pinned host batches (include/orfx.h), two contexts per GPU with half of the loci each, "
+                       "submitted back to back: the upload of one half overlaps the kernels of the other")
+        e2e_single["two_contexts"] = {"value": v2, "ms_per_step": m["e2e2_ms"] / K}
     peak, peak_src = measured_peak()
     scan_ms = m["stage_ms"].get("codon_scan", 0.0) / K
     alg_bytes = ALG_BYTES_PER_NT * m["nt_sum"]
@@ -473,9 +515,9 @@ def main():
                    "timing": "CUDA events on the library stream around the whole path, summed over steps, max over ranks",
                    "wall_ms_per_step": m["wall_ms"] / K},
         "e2e": {"value": e2e_value, "unit": "transcripts/s", "h2d_bytes_per_step": m["h2d"], "d2h_bytes_per_step": m["d2h"],
-                "ms_per_step": m["e2e_ms"] / K, "device_ms_per_step": {"h2d": m["e2e_dev"][0] / K, "kernels": m["e2e_dev"][1] / K,
-                                                                      "d2h": m["e2e_dev"][2] / K},
-                "api": "orfx_submit + orfx_wait on a pinned host batch (include/orfx.h)"},
+                "ms_per_step": e2e_step_ms, "device_ms_per_step": {"h2d": m["e2e_dev"][0] / K, "kernels": m["e2e_dev"][1] / K,
+                                                                   "d2h": m["e2e_dev"][2] / K},
+                "single_context": e2e_single, "api": e2e_api},
         "gpu_launches": m["launches"],
         "clocks": m["clocks"],
         "roofline": {"bound": "hbm", "kernel": "codon_scan_kernel", "achieved": achieved, "peak": peak, "unit": "GB/s",
@@ -486,6 +528,8 @@ def main():
     }
     if m["align"] is not None:
         line["alignment"] = m["align"]
+    if m.get("per_rank"):
+        line["per_rank"] = m["per_rank"]
     if m["world"] == 1 and not args.no_cpu_baseline:
         try:
             line["cpu_baseline"] = cpu_baseline_leg()

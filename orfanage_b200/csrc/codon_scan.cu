@@ -194,6 +194,11 @@ __global__ void __launch_bounds__(CSCAN_THREADS) codon_scan_kernel(DevBatch B, i
     uint4 lo = make_uint4(0, 0, 0, 0), hi = lo;
     int ci = INT_MIN;                         // plane chunk held in lo (hi = chunk ci + 1)
     int fill = 0, produced = 0, emitted = 0;
+    // Tried and measured slower on configs[1] (0.176 ms for this loop): requesting the next chunk a round ahead and the
+    // next exon's table entries an exon ahead (+27 % instructions on a kernel whose ALU pipe is 70 % busy: 0.204 ms); a
+    // per-word formulation with a 3-funnel-shift fast path for words inside one exon and piecewise assembly for the rest,
+    // in one loop (0.330 ms: lanes work on different transcripts, so the warp pays both paths at every word) or with the
+    // junction words deferred to a second pass (0.289 ms).
     while (emitted < nw) {
         if (fill < 34 && produced < nbits) {
             const int take = min(min(32, rem), min(nbits - produced, 64 - fill));
