@@ -525,6 +525,7 @@ def main():
                      "algorithmic_bytes_per_launch": alg_bytes, "kernel_ms": scan_ms,
                      "share_of_step": scan_ms / ms_per_step if ms_per_step else None, "dominant_stage": dominant},
         "stages_ms": {k: v / K for k, v in m["stage_ms"].items()},
+        "stages_note": "heavy_bundles (CTA-per-bundle kernels of the titin-class loci) runs on a side stream beside fill_rows / rescue_score: the stages overlap and do not add up to the step",
     }
     if m["align"] is not None:
         line["alignment"] = m["align"]

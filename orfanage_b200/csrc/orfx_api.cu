@@ -15,7 +15,8 @@ int64_t scan_tmp_elems(int64_t n);
 int launch_prep(const DevBatch& B, int64_t* cnt_q, int64_t* cnt_words, int64_t* cnt_tiles, int64_t* scan_tmp, int32_t* heavy_list, unsigned* heavy_count,
                 cudaStream_t s);
 int launch_fill_tiles(const DevBatch& B, cudaStream_t s);
-int launch_count_rows(const DevBatch& B, int64_t* cnt, int64_t* scan_tmp, const int32_t* heavy_list, const unsigned* heavy_count, int n_sm, cudaStream_t s);
+int launch_count_rows(const DevBatch& B, int64_t* cnt, int64_t* scan_tmp, const int32_t* heavy_list, const unsigned* heavy_count, int n_sm, cudaStream_t s,
+                      cudaStream_t side, cudaEvent_t ev_fork, cudaEvent_t ev_join);
 int launch_fill_rows(const DevBatch& B, const DevRows& R, int n_queries, cudaStream_t s);
 int launch_rescue_score(const DevBatch& B, const DevRows& R, const orfx_params& P, cudaStream_t s);
 int launch_heavy_fill(const DevBatch& B, const DevRows& R, const int32_t* heavy_list, const unsigned* heavy_count, int n_sm, cudaStream_t s);
@@ -89,6 +90,8 @@ struct orfx_ctx {
     int n_sm = 148;
     cudaStream_t stream = nullptr;
     cudaStream_t copy_stream = nullptr;   // sequence bytes go up here while the chain kernels already run on `stream`
+    cudaStream_t side_stream = nullptr;   // the heavy bundles' kernels run here, beside the per-query / per-row kernels on `stream`
+    cudaEvent_t ev_fork[3] = {nullptr, nullptr, nullptr}, ev_join[3] = {nullptr, nullptr, nullptr};
     cudaEvent_t ev_chains = nullptr, ev_seq = nullptr;
     bool seq_in_flight = false;
     orfx_params P;
@@ -217,8 +220,8 @@ int upload_batch(orfx_ctx* c, const orfx_batch* b, bool overlap = false) {
     return ORFX_OK;
 }
 
-void stage_begin(orfx_ctx* c, int st) { cudaEventRecord(c->st_ev[st][0], c->stream); }
-void stage_end(orfx_ctx* c, int st) { cudaEventRecord(c->st_ev[st][1], c->stream); }
+void stage_begin(orfx_ctx* c, int st, cudaStream_t s = nullptr) { cudaEventRecord(c->st_ev[st][0], s ? s : c->stream); }
+void stage_end(orfx_ctx* c, int st, cudaStream_t s = nullptr) { cudaEventRecord(c->st_ev[st][1], s ? s : c->stream); }
 
 // the whole path on the resident batch; leaves results in device memory
 int run_path(orfx_ctx* c) {
@@ -238,7 +241,7 @@ int run_path(orfx_ctx* c) {
     stage_end(c, ST_PREP);
     stage_begin(c, ST_COUNT);
     c->n_launches += launch_count_rows(B, c->d_cnt_rows.as<int64_t>(), c->d_scan_tmp.as<int64_t>(), c->d_heavy.as<int32_t>(), c->d_heavy_count.as<unsigned>(),
-                                       c->n_sm, s);
+                                       c->n_sm, s, c->side_stream, c->ev_fork[0], c->ev_join[0]);
     stage_end(c, ST_COUNT);
     // the only host round trip of the path: four totals that size the remaining buffers
     int64_t* tot = c->h_totals.as<int64_t>();
@@ -277,9 +280,15 @@ int run_path(orfx_ctx* c) {
         R.ext_lo = c->r_ext[0].as<int32_t>(); R.ext_hi = c->r_ext[1].as<int32_t>();
     }
 
+    // The heavy bundles (titin-class loci, ~1 % of the bundles, a fifth of the chain work) have their own CTA-per-bundle
+    // kernels over disjoint queries / rows; they run on the side stream next to the thread-per-query / thread-per-row
+    // kernels, which leave most of the GPU's latency-hiding capacity unused.
+    cudaStream_t side = c->side_stream;
     stage_begin(c, ST_FILL);
+    CU(cudaEventRecord(c->ev_fork[1], s));
+    CU(cudaStreamWaitEvent(side, c->ev_fork[1], 0));
     c->n_launches += launch_fill_rows(B, R, (int)nq, s);
-    c->n_launches += launch_heavy_fill(B, R, c->d_heavy.as<int32_t>(), c->d_heavy_count.as<unsigned>(), c->n_sm, s);
+    c->n_launches += launch_heavy_fill(B, R, c->d_heavy.as<int32_t>(), c->d_heavy_count.as<unsigned>(), c->n_sm, side);
     stage_end(c, ST_FILL);
     if (c->seq_in_flight) { CU(cudaStreamWaitEvent(s, c->ev_seq, 0)); c->seq_in_flight = false; }
     stage_begin(c, ST_PLANES);
@@ -294,12 +303,16 @@ int run_path(orfx_ctx* c) {
         if (tiles > 0) c->n_launches++;
     }
     stage_end(c, ST_SCAN);
-    stage_begin(c, ST_HEAVY);
-    c->n_launches += launch_heavy_rescue(B, R, c->P, c->d_heavy.as<int32_t>(), c->d_heavy_count.as<unsigned>(), c->n_sm, s);
-    stage_end(c, ST_HEAVY);
+    CU(cudaEventRecord(c->ev_fork[2], s));                 // masks ready
+    CU(cudaStreamWaitEvent(side, c->ev_fork[2], 0));       // (heavy_fill is already ahead of it on the side stream)
+    stage_begin(c, ST_HEAVY, side);
+    c->n_launches += launch_heavy_rescue(B, R, c->P, c->d_heavy.as<int32_t>(), c->d_heavy_count.as<unsigned>(), c->n_sm, side);
+    stage_end(c, ST_HEAVY, side);
+    CU(cudaEventRecord(c->ev_join[2], side));
     stage_begin(c, ST_RESCUE);
     c->n_launches += launch_rescue_score(B, R, c->P, s);
     stage_end(c, ST_RESCUE);
+    CU(cudaStreamWaitEvent(s, c->ev_join[2], 0));
     stage_begin(c, ST_SELECT);
     c->n_launches += launch_select(B, R, c->P, (int)nq, c->d_best.as<orfx_best>(), c->d_ord.as<int32_t>(), c->d_keys.as<int4>(), s);
     stage_end(c, ST_SELECT);
@@ -405,9 +418,11 @@ int orfx_create(orfx_ctx** out, int device, const orfx_params* params) {
     c->n_sm = prop.multiProcessorCount;
     c->P = canonical_params(*params);
     if (cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking) != cudaSuccess ||
-        cudaStreamCreateWithFlags(&c->copy_stream, cudaStreamNonBlocking) != cudaSuccess) { delete c; return fail(ORFX_E_CUDA, "cudaStreamCreate failed"); }
+        cudaStreamCreateWithFlags(&c->copy_stream, cudaStreamNonBlocking) != cudaSuccess ||
+        cudaStreamCreateWithFlags(&c->side_stream, cudaStreamNonBlocking) != cudaSuccess) { delete c; return fail(ORFX_E_CUDA, "cudaStreamCreate failed"); }
     cudaEventCreateWithFlags(&c->ev_chains, cudaEventDisableTiming);
     cudaEventCreate(&c->ev_seq);
+    for (int i = 0; i < 3; i++) { cudaEventCreateWithFlags(&c->ev_fork[i], cudaEventDisableTiming); cudaEventCreateWithFlags(&c->ev_join[i], cudaEventDisableTiming); }
     for (auto& ev : c->ev) cudaEventCreate(&ev);
     for (int i = 0; i < ST_N; i++) { cudaEventCreate(&c->st_ev[i][0]); cudaEventCreate(&c->st_ev[i][1]); c->st_ms[i] = 0; }
     cudaEventCreate(&c->run_ev[0]); cudaEventCreate(&c->run_ev[1]);
@@ -487,6 +502,9 @@ void orfx_destroy(orfx_ctx* c) {
     cudaStreamSynchronize(c->copy_stream);
     cudaEventDestroy(c->ev_chains); cudaEventDestroy(c->ev_seq);
     cudaStreamDestroy(c->copy_stream);
+    cudaStreamSynchronize(c->side_stream);
+    for (int i = 0; i < 3; i++) { cudaEventDestroy(c->ev_fork[i]); cudaEventDestroy(c->ev_join[i]); }
+    cudaStreamDestroy(c->side_stream);
     cudaStreamDestroy(c->stream);
     delete c;
 }

@@ -270,10 +270,12 @@ __global__ void __launch_bounds__(256) count_rows_kernel(DevBatch B, int64_t* cn
     const int qi = (int)(gt / ROWS_GROUP), sub = (int)(gt % ROWS_GROUP);
     const int64_t nq = B.tx_q_off[B.n_tx];
     int total = 0;
+    bool heavy = false;
     if (qi < nq) {
         const int qx = B.q_list[qi];
         const int b = B.tx_bundle[qx];
-        const int x0 = B.bundle_tx_off[b], x1 = (B.bundle_need[b] & BUNDLE_HEAVY) ? x0 : B.bundle_tx_off[b + 1];   // heavy: counted by heavy_count_kernel
+        heavy = (B.bundle_need[b] & BUNDLE_HEAVY) != 0;   // counted by heavy_count_kernel, which may run at the same time
+        const int x0 = B.bundle_tx_off[b], x1 = heavy ? x0 : B.bundle_tx_off[b + 1];
         const int q0 = B.tx_seg_off[qx], q1 = B.tx_seg_off[qx + 1];
         const int qstart = B.segs[q0].start, qend = B.segs[q1 - 1].end;
         DevRows dummy{};
@@ -282,7 +284,7 @@ __global__ void __launch_bounds__(256) count_rows_kernel(DevBatch B, int64_t* cn
     }
 #pragma unroll
     for (int d = ROWS_GROUP / 2; d > 0; d >>= 1) total += __shfl_xor_sync(0xffffffffu, total, d);
-    if (sub == 0 && qi < B.n_tx) cnt[qi] = total;
+    if (sub == 0 && qi < B.n_tx && !heavy) cnt[qi] = total;
 }
 __global__ void __launch_bounds__(256) fill_rows_kernel(DevBatch B, DevRows R, int n_queries) {
     const int64_t gt = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -320,10 +322,18 @@ __global__ void __launch_bounds__(256) fill_rows_kernel(DevBatch B, DevRows R, i
     }
 }
 int launch_heavy_count(const DevBatch& B, int64_t* cnt, const int32_t* heavy_list, const unsigned* heavy_count, int n_sm, cudaStream_t s);
-int launch_count_rows(const DevBatch& B, int64_t* cnt, int64_t* scan_tmp, const int32_t* heavy_list, const unsigned* heavy_count, int n_sm, cudaStream_t s) {
+// The heavy bundles' kernel runs beside the thread-per-query kernel on `side` (disjoint queries; both are latency-bound
+// and neither fills the GPU): fork after the zeroing, join before the scan.
+int launch_count_rows(const DevBatch& B, int64_t* cnt, int64_t* scan_tmp, const int32_t* heavy_list, const unsigned* heavy_count, int n_sm, cudaStream_t s,
+                      cudaStream_t side, cudaEvent_t ev_fork, cudaEvent_t ev_join) {
     if (B.n_tx == 0) { cudaMemsetAsync(B.q_row_off, 0, sizeof(int64_t), s); return 0; }
+    cudaMemsetAsync(cnt, 0, (size_t)B.n_tx * sizeof(int64_t), s);   // heavy_count_kernel adds into its queries' counters
+    cudaEventRecord(ev_fork, s);
+    cudaStreamWaitEvent(side, ev_fork, 0);
     count_rows_kernel<<<(unsigned)(((int64_t)B.n_tx * ROWS_GROUP + 255) / 256), 256, 0, s>>>(B, cnt);
-    int n = 1 + launch_heavy_count(B, cnt, heavy_list, heavy_count, n_sm, s);
+    int n = 1 + launch_heavy_count(B, cnt, heavy_list, heavy_count, n_sm, side);
+    cudaEventRecord(ev_join, side);
+    cudaStreamWaitEvent(s, ev_join, 0);
     return n + launch_exclusive_scan(cnt, B.q_row_off, scan_tmp, B.n_tx, s);
 }
 int launch_fill_rows(const DevBatch& B, const DevRows& R, int n_queries, cudaStream_t s) {
@@ -862,7 +872,7 @@ __global__ void __launch_bounds__(HB_THREADS, 2) heavy_count_kernel(DevBatch B, 
             const int qstart = H.segs[B.tx_seg_off[qx]].start, qend = H.segs[B.tx_seg_off[qx + 1] - 1].end;
             if (!pair_live(B, t, H.x1, qstart, qend)) continue;
             const int r = pair_rows_warp<false>(B, H.segs, dummy, qx, t, 0, lane);
-            if (lane == 0) atomicAdd(reinterpret_cast<unsigned long long*>(cnt + H.qbase + ql), (unsigned long long)r);   // zeroed by count_rows_kernel
+            if (lane == 0) atomicAdd(reinterpret_cast<unsigned long long*>(cnt + H.qbase + ql), (unsigned long long)r);   // zeroed by launch_count_rows
         }
         __syncthreads();
     }

@@ -203,6 +203,15 @@ def test_empty_and_degenerate_batches(gpu, oracle_lib):
         want = ox.run(b)
     assert_same_results(got, want, "degenerate")
     assert got.n_queries == 2
+    # --overhang without the flank arrays is refused, by the kernel library and by the oracle alike
+    ov = ob.Params.make(mode="BEST", overhang=10)
+    gpu.set_params(ov)
+    with pytest.raises(ob.OrfxError):
+        gpu.run(b)
+    with ob.Context(ov, lib=oracle_lib, prefix="orfx_oracle_") as ox:
+        with pytest.raises(ob.OrfxError):
+            ox.run(b)
+    gpu.set_params(ob.Params.make(mode="BEST"))
     # the other entry points on empty and degenerate input
     keep, cs, ce = gpu.clean(ob.Batch(), rescue=True)
     assert len(keep) == 0
