@@ -23,10 +23,11 @@ from ._capi import (  # noqa: F401
     MODES,
     STATUS_NOTES,
     encode_protein,
+    shard_pairs,
 )
 
 __all__ = [
     "OrfxError", "Params", "Batch", "Results", "Context", "Workload", "load_device_library",
     "load_host_library", "device_library_path", "host_library_path", "cli_path", "MODES",
-    "STATUS_NOTES", "encode_protein",
+    "STATUS_NOTES", "encode_protein", "shard_pairs",
 ]

@@ -496,6 +496,21 @@ class Context:
             pass
 
 
+def shard_pairs(off, pair_q, pair_t, n_shards):
+    """Deals protein pairs to n_shards GPUs ("length-bucketed pairs dealt round-robin by cells"): pairs in
+    descending order of DP cells (qlen x tlen), dealt in snake order so that every shard gets the same mix of lengths.
+    Pairs are independent, so there is no exchange step.  Returns one index array (into pair_q / pair_t) per shard."""
+    off = np.asarray(off, dtype=np.int64)
+    pq = np.asarray(pair_q, dtype=np.int64)
+    pt = np.asarray(pair_t, dtype=np.int64)
+    cells = (off[pq + 1] - off[pq]) * (off[pt + 1] - off[pt])
+    order = np.argsort(-cells, kind="stable")
+    pos = np.arange(len(order))
+    rnd, col = pos // n_shards, pos % n_shards
+    owner = np.where(rnd % 2 == 0, col, n_shards - 1 - col)
+    return [order[owner == k] for k in range(n_shards)]
+
+
 class Workload:
     """Loaded + prepared + bundled transcriptome (orfxh_workload): orfanage.cpp:313-367."""
 

@@ -197,6 +197,24 @@ def test_two_rank_sharding_over_gloo(synth, tmp_path, oracle_lib):
     w.close()
 
 
+def test_pair_sharding_partitions_and_balances():
+    """C5 pairs over N GPUs: every pair lands in exactly one shard and the DP cells per shard are balanced."""
+    rng = np.random.default_rng(5)
+    lens = np.clip(np.exp(rng.normal(np.log(400.0), 0.9, 4000)), 50, 35000).astype(np.int64)
+    lens[:6] = 33000                                      # a few titin-class sequences
+    off = np.concatenate([[0], np.cumsum(lens)])
+    pq, pt = rng.integers(0, 4000, 3000), rng.integers(0, 4000, 3000)
+    pq[:3], pt[:3] = [0, 1, 2], [3, 4, 5]                 # ... paired with each other: the heaviest pairs
+    cells = (off[pq + 1] - off[pq]) * (off[pt + 1] - off[pt])
+    for n in (1, 2, 8):
+        shards = ob.shard_pairs(off, pq, pt, n)
+        assert len(shards) == n
+        assert sorted(np.concatenate(shards).tolist()) == list(range(3000))
+        load = np.array([cells[s].sum() for s in shards], dtype=np.float64)
+        assert load.max() <= max(load.mean() * 1.05, load.mean() + cells.max())
+    assert ob.shard_pairs(off, pq[:0], pt[:0], 4)[0].size == 0
+
+
 def test_sliced_gtf_reader_gives_the_single_pass_result(tmp_path):
     """The GTF reader parses big files in concurrent slices; forced on a small file (cuts fall inside transcripts)
     it must reproduce the goldens written by the reference."""
