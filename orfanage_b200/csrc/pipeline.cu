@@ -961,6 +961,9 @@ int launch_heavy_fill(const DevBatch& B, const DevRows& R, const int32_t* heavy_
 int launch_heavy_rescue(const DevBatch& B, const DevRows& R, const orfx_params& P, const int32_t* heavy_list, const unsigned* heavy_count, int n_sm,
                         cudaStream_t s) {
     if (B.n_bundles == 0 || R.n_rows == 0) return 0;
+    // 2 CTAs per SM take every register of the SM: beside rescue_score_kernel the two kernels end up one after the other
+    // (0.51 ms together).  Smaller grids that leave room for the other kernel were measured and are slower (1 / 2 / 3 CTA
+    // waves per SM: 0.81 / 0.60 / 0.54 ms for the pair).
     const unsigned grid = (unsigned)std::min<int64_t>(4 * n_sm, (int64_t)B.n_bundles * HB_SLICES);
     cudaFuncSetAttribute(heavy_rescue_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)HB_SMEM_ROWS);
     heavy_rescue_kernel<<<grid, HB_THREADS, HB_SMEM_ROWS, s>>>(B, R, P, heavy_list, heavy_count);
