@@ -214,7 +214,7 @@ def ours(args):
     os.makedirs(base, exist_ok=True)
     need = world * (cfg["chroms"] * cfg["chrom_len"] * 1.2 + 1e9)
     shared = world > 1 and shutil.disk_usage(base).free < need
-    cfg["seed"] = C2["seed"] + (0 if shared else rank)
+    cfg["seed"] = C2["seed"] + (0 if shared else rank) + args.seed_offset
     if shared:
         if rank == 0:
             generate(cfg, "c2")
@@ -226,6 +226,15 @@ def ours(args):
     nq, nt_sum = batch.n_queries, w.count("query_nt")
     log("rank %d: loaded + packed in %.1f s: %d queries, %d templates, %d bundles, %.1f MB windows, %.1f M spliced nt"
         % (rank, time.time() - t, nq, w.count("templates"), w.count("active_bundles"), batch.arrays["seq"].nbytes / 1e6, nt_sum / 1e6))
+    if args.verbose_shard:   # what makes one rank's shard slower than another's: its largest loci
+        import numpy as np
+        a_ = batch.arrays
+        per_tx = np.diff(a_["tx_seg_off"]).astype(np.int64)
+        per_b = np.add.reduceat(per_tx, a_["bundle_tx_off"][:-1].astype(np.int64))
+        ntx_b = np.diff(a_["bundle_tx_off"])
+        top = np.argsort(-per_b)[:5]
+        log("rank %d: largest bundles by segments: %s (transcripts %s); bundles with > 8192 segments: %d; transcripts with > 32 segments: %d"
+            % (rank, per_b[top].tolist(), ntx_b[top].tolist(), int((per_b > 8192).sum()), int((per_tx > 32).sum())))
     params = ob.Params.make(mode=MODE, want_rows=False)
     cx = ob.Context(params, device=local)
 
@@ -496,6 +505,8 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--loci", type=int, default=0, help="override the number of loci (development only; 0 = configs[1])")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--verbose-shard", action="store_true", help="log the largest loci of this rank's shard")
+    ap.add_argument("--seed-offset", type=int, default=0, help="generate the shard rank k of a multi-GPU run would get (k = offset)")
     ap.add_argument("--no-pipelined", action="store_true", help="skip the two-context end-to-end leg")
     ap.add_argument("--align-pairs", type=int, default=50000, help="protein pairs of the alignment leg (0 = skip; configs[4] = 1000000)")
     args = ap.parse_args()

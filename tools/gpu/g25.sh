@@ -1,0 +1,4 @@
+mkdir -p gpurun_out
+for k in 0 3 7; do
+python bench.py --seed-offset $k --verbose-shard --no-cpu-baseline --align-pairs 0 --no-pipelined > gpurun_out/g25_bench_o$k.json 2> gpurun_out/g25_bench_o$k.err
+done
