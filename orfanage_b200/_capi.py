@@ -30,7 +30,8 @@ class OrfxError(RuntimeError):
 
 
 def device_library_path():
-    return os.path.join(_HERE, "liborfx.so")
+    # ORFX_LIB: a differently-tuned build of the same library (kernel experiments); never a CPU stand-in
+    return os.environ.get("ORFX_LIB") or os.path.join(_HERE, "liborfx.so")
 
 
 def host_library_path():

@@ -331,7 +331,7 @@ int launch_count_rows(const DevBatch& B, int64_t* cnt, int64_t* scan_tmp, const 
     cudaEventRecord(ev_fork, s);
     cudaStreamWaitEvent(side, ev_fork, 0);
     count_rows_kernel<<<(unsigned)(((int64_t)B.n_tx * ROWS_GROUP + 255) / 256), 256, 0, s>>>(B, cnt);
-    int n = 1 + launch_heavy_count(B, cnt, heavy_list, heavy_count, n_sm, side);
+    int n = 1 + launch_heavy_count(B, cnt, heavy_list, heavy_count, n_sm, side);   // (plans the heavy work items first)
     cudaEventRecord(ev_join, side);
     cudaStreamWaitEvent(s, ev_join, 0);
     return n + launch_exclusive_scan(cnt, B.q_row_off, scan_tmp, B.n_tx, s);
@@ -810,7 +810,7 @@ __global__ void __launch_bounds__(128) rescue_score_kernel(DevBatch B, DevRows R
 // heavy bundles: one CTA per bundle, the bundle's chains staged in shared memory
 // ------------------------------------------------------------------------------------------------
 constexpr int HB_THREADS = 512;   // x 2 CTAs per SM
-constexpr int HB_MAX_SEGS = 8192;     // segments of one bundle that fit the stage (8 B + 4 B each); two CTAs per SM
+constexpr int HB_MAX_SEGS = 9216;     // segments of one bundle that fit the stage (8 B + 4 B each): 108 KB, two CTAs per SM
 constexpr int HB_MAX_PAIRS = 8192;    // (query, transcript slot) pairs whose row counts fit the stage
 
 namespace {
@@ -849,21 +849,77 @@ __device__ __forceinline__ TxView hb_view(const DevBatch& B, const HeavyBundle& 
 }
 }  // namespace
 
-// Work item w of a heavy kernel = (heavy bundle w / HB_SLICES, slice w % HB_SLICES): a slice takes every
-// HB_SLICES-th query of the bundle (pair kernels) or every HB_SLICES-th group of rows (row kernel), so that a
+// Work item of a heavy kernel = (heavy bundle, slice k of S): a slice takes every
+// S-th query of the bundle (pair kernels) or every S-th group of rows (row kernel), so that a
 // titin-class bundle is spread over several SMs.  Every CTA stages the whole bundle's chains.
-constexpr int HB_SLICES = 4;
+constexpr int HB_MAX_SLICES = 8;
+
+// Work plan of the heavy kernels.  The buffer behind heavy_list holds [list: n_bundles ints][scratch: n_bundles int4]
+// [work: HB_MAX_SLICES * n_bundles int4]; heavy_count[0] = heavy bundles, heavy_count[1] = work items.
+// A work item is (bundle, slice k, slices S of that bundle): slice k takes every S-th query (pair kernels) or every S-th
+// group of rows (row kernel).  S grows with the bundle's queries (a third of them, 1..8: fewer queries per slice than
+// that leaves warps idle, measured with 16 slices for all), and the items are listed by descending cost (queries x
+// segments) so that the static round-robin over the CTAs starts with the largest loci: without it one 8 500-segment locus
+// made one rank's step 0.24 ms longer than another's.
+__device__ __forceinline__ int4* heavy_scratch(const DevBatch& B, const int32_t* heavy_list) {
+    return reinterpret_cast<int4*>(const_cast<int32_t*>(heavy_list) + ((B.n_bundles + 3) & ~3));
+}
+__device__ __forceinline__ int4* heavy_work(const DevBatch& B, const int32_t* heavy_list) { return heavy_scratch(B, heavy_list) + B.n_bundles; }
+
+__global__ void __launch_bounds__(1024) heavy_plan_kernel(DevBatch B, int32_t* heavy_list, unsigned* heavy_count) {
+    int4* scr = heavy_scratch(B, heavy_list);
+    int4* work = heavy_work(B, heavy_list);
+    const int n = (int)heavy_count[0];
+    for (int i = threadIdx.x; i < n; i += blockDim.x) {
+        const int b = heavy_list[i];
+        const int x0 = B.bundle_tx_off[b], x1 = B.bundle_tx_off[b + 1];
+        const int nq = (int)(B.tx_q_off[x1] - B.tx_q_off[x0]);
+        const int ns = B.tx_seg_off[x1] - B.tx_seg_off[x0];
+        const int64_t cost = (int64_t)nq * ns;
+        scr[i] = make_int4((int)(cost & 0x7FFFFFFF), (int)(cost >> 31), min(max((nq + 2) / 3, 1), HB_MAX_SLICES), b);
+    }
+    __syncthreads();
+    const bool sorted = n <= 4096;   // rank sort, quadratic: beyond this the list keeps its order
+    for (int i = threadIdx.x; i < n; i += blockDim.x) {
+        int rank = i;
+        if (sorted) {
+            const int4 me = scr[i];
+            rank = 0;
+            for (int j = 0; j < n; j++) {
+                const int4 o = scr[j];
+                const bool before = o.y != me.y ? o.y > me.y : (o.x != me.x ? o.x > me.x : o.w < me.w);
+                rank += before ? 1 : 0;
+            }
+        }
+        work[i].x = rank;   // parked in the (still unused) work area: the scratch records are being read by other threads
+    }
+    __syncthreads();
+    for (int i = threadIdx.x; i < n; i += blockDim.x) heavy_list[work[i].x] = i;   // rank -> entry
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        int off = 0;
+        for (int r = 0; r < n; r++) { const int i = heavy_list[r]; scr[i].y = off; off += scr[i].z; }
+        heavy_count[1] = (unsigned)off;
+    }
+    __syncthreads();
+    for (int i = threadIdx.x; i < n; i += blockDim.x) {
+        const int4 me = scr[i];
+        for (int k = 0; k < me.z; k++) work[me.y + k] = make_int4(me.w, k, me.z, 0);
+    }
+}
 
 // rows of every query of the heavy bundles, one warp per (query, transcript slot) pair
 __global__ void __launch_bounds__(HB_THREADS, 2) heavy_count_kernel(DevBatch B, int64_t* cnt, const int32_t* heavy_list, const unsigned* heavy_count) {
     extern __shared__ __align__(16) unsigned char hb_smem[];
     orfx_seg* s_seg = reinterpret_cast<orfx_seg*>(hb_smem);
-    const unsigned n = *heavy_count * HB_SLICES;
+    const unsigned n = heavy_count[1];
+    const int4* work = heavy_work(B, heavy_list);
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = blockDim.x >> 5;
     DevRows dummy{};
     for (unsigned w = blockIdx.x; w < n; w += gridDim.x) {
-        const int k = (int)(w % HB_SLICES);
-        const HeavyBundle H = hb_load(B, heavy_list[w / HB_SLICES], s_seg, nullptr, false);
+        const int4 item = work[w];
+        const int k = item.y, HB_SLICES = item.z;
+        const HeavyBundle H = hb_load(B, item.x, s_seg, nullptr, false);
         const int nq_slice = (H.nq - k + HB_SLICES - 1) / HB_SLICES;
         const int npairs = nq_slice * H.ntx;
         for (int p = warp; p < npairs; p += nwarps) {
@@ -883,11 +939,13 @@ __global__ void __launch_bounds__(HB_THREADS, 2) heavy_fill_kernel(DevBatch B, D
     extern __shared__ __align__(16) unsigned char hb_smem[];
     orfx_seg* s_seg = reinterpret_cast<orfx_seg*>(hb_smem);
     uint16_t* s_n = reinterpret_cast<uint16_t*>(hb_smem + (size_t)HB_MAX_SEGS * sizeof(orfx_seg));
-    const unsigned n = *heavy_count * HB_SLICES;
+    const unsigned n = heavy_count[1];
+    const int4* work = heavy_work(B, heavy_list);
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = blockDim.x >> 5;
     for (unsigned w = blockIdx.x; w < n; w += gridDim.x) {
-        const int k = (int)(w % HB_SLICES);
-        const HeavyBundle H = hb_load(B, heavy_list[w / HB_SLICES], s_seg, nullptr, false);
+        const int4 item = work[w];
+        const int k = item.y, HB_SLICES = item.z;
+        const HeavyBundle H = hb_load(B, item.x, s_seg, nullptr, false);
         const int nq_slice = (H.nq - k + HB_SLICES - 1) / HB_SLICES;
         const int64_t npairs = (int64_t)nq_slice * H.ntx;
         if (npairs <= HB_MAX_PAIRS) {
@@ -928,11 +986,13 @@ __global__ void __launch_bounds__(HB_THREADS, 2) heavy_rescue_kernel(DevBatch B,
     extern __shared__ __align__(16) unsigned char hb_smem[];
     orfx_seg* s_seg = reinterpret_cast<orfx_seg*>(hb_smem);
     int32_t* s_cum = reinterpret_cast<int32_t*>(hb_smem + (size_t)HB_MAX_SEGS * sizeof(orfx_seg));
-    const unsigned n = *heavy_count * HB_SLICES;
+    const unsigned n = heavy_count[1];
+    const int4* work = heavy_work(B, heavy_list);
     const int warp = threadIdx.x >> 5, nwarps = blockDim.x >> 5;
     for (unsigned w = blockIdx.x; w < n; w += gridDim.x) {
-        const int k = (int)(w % HB_SLICES);
-        const HeavyBundle H = hb_load(B, heavy_list[w / HB_SLICES], s_seg, s_cum, true);
+        const int4 item = work[w];
+        const int k = item.y, HB_SLICES = item.z;
+        const HeavyBundle H = hb_load(B, item.x, s_seg, s_cum, true);
         const int64_t r0 = B.q_row_off[H.qbase], r1 = B.q_row_off[H.qbase + H.nq];
         for (int64_t row = r0 + (int64_t)k * nwarps + warp; row < r1; row += (int64_t)HB_SLICES * nwarps)
             process_row<true>(B, R, P, row, hb_view(B, H, R.q_tx[row]), hb_view(B, H, R.t_tx[row]));
@@ -945,14 +1005,15 @@ constexpr size_t HB_SMEM_ROWS = (size_t)HB_MAX_SEGS * (sizeof(orfx_seg) + sizeof
 
 int launch_heavy_count(const DevBatch& B, int64_t* cnt, const int32_t* heavy_list, const unsigned* heavy_count, int n_sm, cudaStream_t s) {
     if (B.n_bundles == 0) return 0;
+    heavy_plan_kernel<<<1, 1024, 0, s>>>(B, const_cast<int32_t*>(heavy_list), const_cast<unsigned*>(heavy_count));
     cudaFuncSetAttribute(heavy_count_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)HB_SMEM_PAIRS);   // per device
-    heavy_count_kernel<<<(unsigned)std::min<int64_t>(4 * n_sm, (int64_t)B.n_bundles * HB_SLICES), HB_THREADS, HB_SMEM_PAIRS, s>>>(B, cnt, heavy_list, heavy_count);
-    return 1;
+    heavy_count_kernel<<<(unsigned)std::min<int64_t>(4 * n_sm, (int64_t)B.n_bundles * HB_MAX_SLICES), HB_THREADS, HB_SMEM_PAIRS, s>>>(B, cnt, heavy_list, heavy_count);
+    return 2;
 }
 // candidate rows of the heavy bundles: needs the chains only (runs while the sequence is still being uploaded)
 int launch_heavy_fill(const DevBatch& B, const DevRows& R, const int32_t* heavy_list, const unsigned* heavy_count, int n_sm, cudaStream_t s) {
     if (B.n_bundles == 0 || R.n_rows == 0) return 0;
-    const unsigned grid = (unsigned)std::min<int64_t>(4 * n_sm, (int64_t)B.n_bundles * HB_SLICES);
+    const unsigned grid = (unsigned)std::min<int64_t>(4 * n_sm, (int64_t)B.n_bundles * HB_MAX_SLICES);
     cudaFuncSetAttribute(heavy_fill_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)HB_SMEM_PAIRS);
     heavy_fill_kernel<<<grid, HB_THREADS, HB_SMEM_PAIRS, s>>>(B, R, heavy_list, heavy_count);
     return 1;
@@ -964,7 +1025,7 @@ int launch_heavy_rescue(const DevBatch& B, const DevRows& R, const orfx_params& 
     // 2 CTAs per SM take every register of the SM: beside rescue_score_kernel the two kernels end up one after the other
     // (0.51 ms together).  Smaller grids that leave room for the other kernel were measured and are slower (1 / 2 / 3 CTA
     // waves per SM: 0.81 / 0.60 / 0.54 ms for the pair).
-    const unsigned grid = (unsigned)std::min<int64_t>(4 * n_sm, (int64_t)B.n_bundles * HB_SLICES);
+    const unsigned grid = (unsigned)std::min<int64_t>(4 * n_sm, (int64_t)B.n_bundles * HB_MAX_SLICES);
     cudaFuncSetAttribute(heavy_rescue_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)HB_SMEM_ROWS);
     heavy_rescue_kernel<<<grid, HB_THREADS, HB_SMEM_ROWS, s>>>(B, R, P, heavy_list, heavy_count);
     return 1;
