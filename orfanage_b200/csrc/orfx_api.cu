@@ -196,7 +196,7 @@ int upload_batch(orfx_ctx* c, const orfx_batch* b, bool overlap = false) {
     CU(c->d_cnt_rows.ensure(nt * 8 + 8));
     CU(c->d_scan_tmp.ensure((size_t)scan_tmp_elems((int64_t)nt) * 8 + 8));
     CU(c->d_need.ensure(nb + 4));
-    CU(c->d_heavy.ensure((nb + 4) * 4 + nb * 16 + nb * 8 * 16 + 64));   // heavy list, plan scratch, work items (pipeline.cu: heavy_plan_kernel)
+    CU(c->d_heavy.ensure((nb + 4) * 4 + nb * 16 + nb * 16 * 16 + 64));   // heavy list, plan scratch, work items (pipeline.cu: heavy_plan_kernel)
     CU(c->d_heavy_count.ensure(16));
     const size_t plane_words = (seqb + 31) / 32 + 4;
     if (seqb) CU(c->d_planes.ensure(2 * plane_words * 16));

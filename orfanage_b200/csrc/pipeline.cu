@@ -852,13 +852,14 @@ __device__ __forceinline__ TxView hb_view(const DevBatch& B, const HeavyBundle& 
 // Work item of a heavy kernel = (heavy bundle, slice k of S): a slice takes every
 // S-th query of the bundle (pair kernels) or every S-th group of rows (row kernel), so that a
 // titin-class bundle is spread over several SMs.  Every CTA stages the whole bundle's chains.
-constexpr int HB_MAX_SLICES = 8;
+constexpr int HB_MAX_SLICES = 16;
 
 // Work plan of the heavy kernels.  The buffer behind heavy_list holds [list: n_bundles ints][scratch: n_bundles int4]
 // [work: HB_MAX_SLICES * n_bundles int4]; heavy_count[0] = heavy bundles, heavy_count[1] = work items.
 // A work item is (bundle, slice k, slices S of that bundle): slice k takes every S-th query (pair kernels) or every S-th
 // group of rows (row kernel).  S grows with the bundle's queries (a third of them, 1..8: fewer queries per slice than
-// that leaves warps idle, measured with 16 slices for all), and the items are listed by descending cost (queries x
+// that leaves warps idle, measured with 16 slices for all; the largest loci get one slice per 16 K of cost, up to 16),
+// and the items are listed by descending cost (queries x
 // segments) so that the static round-robin over the CTAs starts with the largest loci: without it one 8 500-segment locus
 // made one rank's step 0.24 ms longer than another's.
 __device__ __forceinline__ int4* heavy_scratch(const DevBatch& B, const int32_t* heavy_list) {
@@ -876,7 +877,8 @@ __global__ void __launch_bounds__(1024) heavy_plan_kernel(DevBatch B, int32_t* h
         const int nq = (int)(B.tx_q_off[x1] - B.tx_q_off[x0]);
         const int ns = B.tx_seg_off[x1] - B.tx_seg_off[x0];
         const int64_t cost = (int64_t)nq * ns;
-        scr[i] = make_int4((int)(cost & 0x7FFFFFFF), (int)(cost >> 31), min(max((nq + 2) / 3, 1), HB_MAX_SLICES), b);
+        const int by_cost = (int)min(cost >> 14, (int64_t)HB_MAX_SLICES);   // the largest loci: more slices than a third of their queries
+        scr[i] = make_int4((int)(cost & 0x7FFFFFFF), (int)(cost >> 31), max(1, min(max((nq + 2) / 3, by_cost), min(HB_MAX_SLICES, nq))), b);
     }
     __syncthreads();
     const bool sorted = n <= 4096;   // rank sort, quadratic: beyond this the list keeps its order
