@@ -896,12 +896,24 @@ __global__ void __launch_bounds__(1024) heavy_plan_kernel(DevBatch B, int32_t* h
         work[i].x = rank;   // parked in the (still unused) work area: the scratch records are being read by other threads
     }
     __syncthreads();
-    for (int i = threadIdx.x; i < n; i += blockDim.x) heavy_list[work[i].x] = i;   // rank -> entry
-    __syncthreads();
-    if (threadIdx.x == 0) {
-        int off = 0;
-        for (int r = 0; r < n; r++) { const int i = heavy_list[r]; scr[i].y = off; off += scr[i].z; }
-        heavy_count[1] = (unsigned)off;
+    // first work item of every bundle: exclusive prefix of the slice counts in rank order (in shared memory while it fits)
+    __shared__ int s_off[4096];
+    if (sorted) {
+        for (int i = threadIdx.x; i < n; i += blockDim.x) s_off[work[i].x] = scr[i].z;
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            int off = 0;
+            for (int r = 0; r < n; r++) { const int v = s_off[r]; s_off[r] = off; off += v; }
+            heavy_count[1] = (unsigned)off;
+        }
+        __syncthreads();
+        for (int i = threadIdx.x; i < n; i += blockDim.x) scr[i].y = s_off[work[i].x];
+    } else {
+        if (threadIdx.x == 0) {   // list order
+            int off = 0;
+            for (int i = 0; i < n; i++) { scr[i].y = off; off += scr[i].z; }
+            heavy_count[1] = (unsigned)off;
+        }
     }
     __syncthreads();
     for (int i = threadIdx.x; i < n; i += blockDim.x) {
