@@ -279,20 +279,22 @@ def cleaning_batch(batch, best, rng):
     return ob.Batch(**a)
 
 
-@pytest.mark.parametrize("seed,kw", [(31, dict(loci=80)), (32, dict(loci=60, titin=0.15, iupac=0.003, lower=0.5))])
-def test_template_cleaning_matches_oracle(synth, oracle_lib, gpu, seed, kw):
-    """--cleant / --rescue kernel (orfx_clean_templates) against the restated Transcriptome::clean_cds body."""
+@pytest.mark.parametrize("seed,overhang,kw", [(31, 0, dict(loci=80)), (32, 0, dict(loci=60, titin=0.15, iupac=0.003, lower=0.5)),
+                                              (33, 150, dict(loci=80, lower=0.3))])
+def test_template_cleaning_matches_oracle(synth, oracle_lib, gpu, seed, overhang, kw):
+    """--cleant / --rescue kernel (orfx_clean_templates) against the restated Transcriptome::clean_cds body; with
+    --overhang the unguided searches of the rescue run into the flanks (TX::extend_seq, cpp:342-399)."""
     d = synth(seed, **kw)
-    w = ob.Workload(os.path.join(d, "query.gtf"), template_files(d), os.path.join(d, "genome.fa"))
+    w = ob.Workload(os.path.join(d, "query.gtf"), template_files(d), os.path.join(d, "genome.fa"), overhang=overhang)
     batch = w.pack()
-    params = ob.Params.make(mode="LONGEST_MATCH,BEST", want_rows=False)
+    params = ob.Params.make(mode="LONGEST_MATCH,BEST", want_rows=False, overhang=overhang)
     gpu.set_params(params)
     best = gpu.run(batch).best
     cb = cleaning_batch(batch, best, np.random.default_rng(seed))
     kept = {}
     for non_aug in (False, True):
         for rescue in (False, True):
-            p = ob.Params.make(mode="BEST", non_aug=non_aug)
+            p = ob.Params.make(mode="BEST", non_aug=non_aug, overhang=overhang)
             gpu.set_params(p)
             got = gpu.clean(cb, rescue)
             with ob.Context(p, lib=oracle_lib, prefix="orfx_oracle_") as ox:
@@ -302,6 +304,14 @@ def test_template_cleaning_matches_oracle(synth, oracle_lib, gpu, seed, kw):
             kept[(non_aug, rescue)] = int(got[0].sum())
     n = cb.n_queries
     assert n > 200
+    if overhang:   # some rescued CDSs end or start in a flank
+        with ob.Context(ob.Params.make(mode="BEST", overhang=overhang), lib=oracle_lib, prefix="orfx_oracle_") as ox:
+            keep, s_, e_ = ox.clean(cb, True)
+        a = cb.arrays
+        qidx = np.nonzero(a["tx_kind"] == 0)[0]
+        first = a["segs"][a["tx_seg_off"][qidx], 0]
+        last = a["segs"][a["tx_seg_off"][qidx + 1] - 1, 1]
+        assert int(((keep == 1) & ((s_ < first) | (e_ > last))).sum()) > 0
     assert 0 < kept[(False, False)] < kept[(False, True)] < n     # rescue repairs some, not all
     assert kept[(False, False)] <= kept[(True, False)]
     # the path still answers a regular batch afterwards
