@@ -797,7 +797,8 @@ __device__ void process_row(const DevBatch& B, const DevRows& R, const orfx_para
     if (R.ext_lo) { R.ext_lo[row] = q.xlo; R.ext_hi[row] = q.xhi; }
 }
 
-__global__ void __launch_bounds__(128) rescue_score_kernel(DevBatch B, DevRows R, orfx_params P) {
+// 8 CTAs per SM = 64 registers (16 bytes of spill): 0.237 ms against 0.245 ms at the 72 the compiler takes unasked, 0.263 ms at 78
+__global__ void __launch_bounds__(128, 8) rescue_score_kernel(DevBatch B, DevRows R, orfx_params P) {
     const int64_t row = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (row >= R.n_rows) return;
     const int qx = R.q_tx[row];
