@@ -197,6 +197,75 @@ def test_two_rank_sharding_over_gloo(synth, tmp_path, oracle_lib):
     w.close()
 
 
+def _read_fasta(path):
+    seqs, name = {}, None
+    for line in open(path):
+        if line.startswith(">"):
+            name = line[1:].split()[0]
+            seqs[name] = []
+        else:
+            seqs[name].append(line.strip())
+    return {k: "".join(v) for k, v in seqs.items()}
+
+
+@pytest.mark.parametrize("spliced", [False, True])
+def test_overhang_flanks_of_the_packer(synth, spliced):
+    """orfx_batch::tx_ext_lo / tx_ext_hi against a direct restatement of TX::extend_seq (Transcriptome.cpp:342-399): at most
+    --overhang bases per side, clamped to the padded bundle window, cut before the first GT (3' side) / after the last AG (5'
+    side) of the strand-corrected, upper-cased flank with --spliced_overhang; and the islands hold exactly those bases."""
+    N = 75
+    d = synth(61, loci=40, lower=0.4)
+    genome = _read_fasta(os.path.join(d, "genome.fa"))
+    w = ob.Workload(os.path.join(d, "query.gtf"), template_files(d), os.path.join(d, "genome.fa"), overhang=N, spliced_overhang=spliced)
+    b = w.pack(layout="islands")
+    a = b.arrays
+    comp = str.maketrans("ACGTUacgtu", "TGCAAtgcaa")
+    chrom_of = {}
+    for line in open(os.path.join(d, "query.gtf")):
+        f = line.split("\t")
+        if len(f) > 8 and f[2] == "transcript":
+            chrom_of[re.search(r'transcript_id "([^"]+)"', f[8]).group(1)] = f[0]
+    checked = cut = 0
+    for bi in range(len(a["bundle_start"])):
+        x0, x1 = a["bundle_tx_off"][bi], a["bundle_tx_off"][bi + 1]
+        bstart = int(a["bundle_start"][bi])
+        for x in range(x0, x1):
+            if a["tx_kind"][x] != 0:
+                assert a["tx_ext_lo"][x] == 0 and a["tx_ext_hi"][x] == 0
+                continue
+            g = genome[chrom_of[w.tx_id(int(x))]]
+            s0, s1 = a["tx_seg_off"][x], a["tx_seg_off"][x + 1]
+            first, last = int(a["segs"][s0, 0]), int(a["segs"][s1 - 1, 1])
+            plus = a["tx_strand"][x] == ord("+")
+            for high in (False, True):
+                lo, hi = (last + 1, min(last + N, len(g))) if high else (max(first - N, max(bstart, 1)), first - 1)
+                flank = g[lo - 1:hi] if hi >= lo else ""
+                want = len(flank)
+                if spliced and flank:
+                    f5 = (flank if plus else flank.translate(comp)[::-1]).upper()
+                    if plus == high:                      # towards the stop
+                        at = f5.find("GT")
+                        want = len(flank) if at < 0 else at
+                    else:
+                        at = f5.rfind("AG")
+                        want = len(flank) if at < 0 else len(flank) - (at + 2)
+                    cut += want < len(flank)
+                got = int(a["tx_ext_hi"][x] if high else a["tx_ext_lo"][x])
+                assert got == want, (w.tx_id(int(x)), high, got, want)
+                # the island bytes next to the terminal exon are the flank bases
+                if got:
+                    off = int(a["seq_off"][bi])
+                    if high:
+                        p0 = off + int(a["seg_seq_off"][s1 - 1]) + (last - int(a["segs"][s1 - 1, 0]) + 1)
+                        assert bytes(a["seq"][p0:p0 + got]).decode() == g[last:last + got]
+                    else:
+                        p0 = off + int(a["seg_seq_off"][s0]) - got
+                        assert bytes(a["seq"][p0:p0 + got]).decode() == g[first - 1 - got:first - 1]
+                checked += 1
+    assert checked > 400 and (cut > 100 if spliced else cut == 0)
+    w.close()
+
+
 def test_pair_sharding_partitions_and_balances():
     """C5 pairs over N GPUs: every pair lands in exactly one shard and the DP cells per shard are balanced."""
     rng = np.random.default_rng(5)
