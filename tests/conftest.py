@@ -88,3 +88,52 @@ def has_gpu():
         return torch.cuda.is_available()
     except Exception:
         return False
+
+
+def write_overhang_kat(d):
+    """Two hand-derivable --overhang cases on an all-C genome (no codon of interest outside what is planted):
+    Q1, exon 131-160 = CC ATG (GCT)x8 G with CT TAA right behind it: the stop search runs 5 bases into the 3' flank, the
+       exon and the CDS grow to 165 (Transcriptome.cpp:418-429);
+    Q2, exon 231-260 = (GCT)x9 TAA, no ATG, with ATG at 225-227 and AG at 215-216: the unguided start search finds the ATG
+       6 bases into the 5' flank -> exon and CDS start at 225; with --spliced_overhang the flank is cut after the AG (14
+       bases left), the ATG sits at position 8 of the flanked sequence and the exon grows by overhang - 8 = 12 -> exon
+       starts at 219 while the CDS starts at 225 (cpp:461-474, as written).
+    Returns the expected (exon start, exon end, CDS start, CDS end) per transcript for plain and spliced runs."""
+    g = ["C"] * 400
+
+    def put(pos, s):
+        for i, ch in enumerate(s):
+            g[pos - 1 + i] = ch
+    put(131, "CC" + "ATG" + "GCT" * 8 + "G")
+    put(161, "CT" + "TAA")
+    put(231, "GCT" * 9 + "TAA")
+    put(225, "ATG")
+    put(215, "AG")
+    open(os.path.join(d, "genome.fa"), "w").write(">chr1\n" + "".join(g) + "\n")
+
+    def tx(tid, gid, s, e, cds=None):
+        attrs = 'transcript_id "%s"; gene_id "%s";' % (tid, gid)
+        rows = ["chr1\tKAT\ttranscript\t%d\t%d\t.\t+\t.\t%s" % (s, e, attrs), "chr1\tKAT\texon\t%d\t%d\t.\t+\t.\t%s" % (s, e, attrs)]
+        if cds:
+            rows.append("chr1\tKAT\tCDS\t%d\t%d\t.\t+\t0\t%s" % (cds[0], cds[1], attrs))
+        return "\n".join(rows) + "\n"
+    open(os.path.join(d, "query.gtf"), "w").write(tx("Q1", "G1", 131, 160) + tx("Q2", "G2", 231, 260))
+    open(os.path.join(d, "template.gtf"), "w").write(tx("T1", "G1", 133, 160, (133, 159)) + tx("T2", "G2", 231, 260, (231, 260)))
+    return {False: {"Q1": (131, 165, 133, 165), "Q2": (225, 260, 225, 260)},
+            True: {"Q1": (131, 165, 133, 165), "Q2": (219, 260, 225, 260)}}
+
+
+def check_overhang_kat(binary, d, expected):
+    for spliced, want in expected.items():
+        args = ["--reference", "genome.fa", "--query", "query.gtf", "--overhang", "20"] + (["--spliced_overhang"] if spliced else [])
+        rc, gtf, tsv, err = run_cli(binary, d, args, "kat%d" % spliced, ["template.gtf"])
+        assert rc == 0, err
+        got = {}
+        for line in gtf.decode().splitlines():
+            f = line.split("\t")
+            if len(f) < 9 or f[2] not in ("exon", "CDS"):
+                continue
+            tid = f[8].split('"')[1]
+            got.setdefault(tid, {})[f[2]] = (int(f[3]), int(f[4]))
+        for tid, (es, ee, cs, ce) in want.items():
+            assert got[tid]["exon"] == (es, ee) and got[tid]["CDS"] == (cs, ce), (spliced, tid, got[tid])

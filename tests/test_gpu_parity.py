@@ -155,6 +155,13 @@ def test_overhang_matches_oracle(synth, oracle_lib, gpu, seed, overhang, spliced
     w.close()
 
 
+def test_overhang_worked_examples_on_the_gpu(tmp_path):
+    """The hand-derived --overhang cases of tests/conftest.py through the CUDA CLI."""
+    from conftest import check_overhang_kat, write_overhang_kat
+    d = str(tmp_path)
+    check_overhang_kat(ob.cli_path(), d, write_overhang_kat(d))
+
+
 def test_config1_golden_batch(gpu):
     """Config 1 (example/query.gtf x example/template.gtf, random chr19, --mode BEST): committed packed
     batch -> CUDA path -> the reference's own stats rows."""

@@ -86,6 +86,17 @@ def test_oracle_cli_matches_goldens(tmp_path, seed):
         assert tsv == open(base + ".tsv", "rb").read(), tag
 
 
+def test_overhang_worked_examples(tmp_path):
+    """--overhang by hand: stop in the 3' flank, ATG in the 5' flank, and the reference's
+    `extend_len - starts[0]` growth after a splice cut — the oracle-backed CLI and, where built, the reference binary."""
+    from conftest import check_overhang_kat, write_overhang_kat
+    d = str(tmp_path)
+    expected = write_overhang_kat(d)
+    check_overhang_kat(ORACLE_CLI, d, expected)
+    if os.path.exists(REF_BIN):
+        check_overhang_kat(REF_BIN, d, expected)
+
+
 def test_config1_oracle_library_matches_reference_rows(oracle_lib):
     batch = ob.Batch.load(os.path.join(GOLDEN, "c1_batch.npz"))
     names = json.load(open(os.path.join(GOLDEN, "c1_names.json")))["tx_id"]
