@@ -90,7 +90,7 @@ def has_gpu():
         return False
 
 
-def write_overhang_kat(d):
+def write_overhang_kat(d, minus=False):
     """Two hand-derivable --overhang cases on an all-C genome (no codon of interest outside what is planted):
     Q1, exon 131-160 = CC ATG (GCT)x8 G with CT TAA right behind it: the stop search runs 5 bases into the 3' flank, the
        exon and the CDS grow to 165 (Transcriptome.cpp:418-429);
@@ -98,8 +98,10 @@ def write_overhang_kat(d):
        6 bases into the 5' flank -> exon and CDS start at 225; with --spliced_overhang the flank is cut after the AG (14
        bases left), the ATG sits at position 8 of the flanked sequence and the exon grows by overhang - 8 = 12 -> exon
        starts at 219 while the CDS starts at 225 (cpp:461-474, as written).
+    minus=True mirrors everything onto the reverse strand (reverse-complemented genome, coordinates 401 - x).
     Returns the expected (exon start, exon end, CDS start, CDS end) per transcript for plain and spliced runs."""
     g = ["C"] * 400
+    L = 400
 
     def put(pos, s):
         for i, ch in enumerate(s):
@@ -109,18 +111,28 @@ def write_overhang_kat(d):
     put(231, "GCT" * 9 + "TAA")
     put(225, "ATG")
     put(215, "AG")
+    if minus:
+        g = [{"A": "T", "C": "G", "G": "C", "T": "A"}[c] for c in reversed(g)]
     open(os.path.join(d, "genome.fa"), "w").write(">chr1\n" + "".join(g) + "\n")
+    strand = "-" if minus else "+"
+
+    def span(s, e):
+        return (L + 1 - e, L + 1 - s) if minus else (s, e)
 
     def tx(tid, gid, s, e, cds=None):
         attrs = 'transcript_id "%s"; gene_id "%s";' % (tid, gid)
-        rows = ["chr1\tKAT\ttranscript\t%d\t%d\t.\t+\t.\t%s" % (s, e, attrs), "chr1\tKAT\texon\t%d\t%d\t.\t+\t.\t%s" % (s, e, attrs)]
+        s, e = span(s, e)
+        rows = ["chr1\tKAT\ttranscript\t%d\t%d\t.\t%s\t.\t%s" % (s, e, strand, attrs), "chr1\tKAT\texon\t%d\t%d\t.\t%s\t.\t%s" % (s, e, strand, attrs)]
         if cds:
-            rows.append("chr1\tKAT\tCDS\t%d\t%d\t.\t+\t0\t%s" % (cds[0], cds[1], attrs))
+            rows.append("chr1\tKAT\tCDS\t%d\t%d\t.\t%s\t0\t%s" % (span(*cds) + (strand, attrs)))
         return "\n".join(rows) + "\n"
-    open(os.path.join(d, "query.gtf"), "w").write(tx("Q1", "G1", 131, 160) + tx("Q2", "G2", 231, 260))
-    open(os.path.join(d, "template.gtf"), "w").write(tx("T1", "G1", 133, 160, (133, 159)) + tx("T2", "G2", 231, 260, (231, 260)))
-    return {False: {"Q1": (131, 165, 133, 165), "Q2": (225, 260, 225, 260)},
+    q = [tx("Q1", "G1", 131, 160), tx("Q2", "G2", 231, 260)]
+    t = [tx("T1", "G1", 133, 160, (133, 159)), tx("T2", "G2", 231, 260, (231, 260))]
+    open(os.path.join(d, "query.gtf"), "w").write("".join(reversed(q) if minus else q))
+    open(os.path.join(d, "template.gtf"), "w").write("".join(reversed(t) if minus else t))
+    want = {False: {"Q1": (131, 165, 133, 165), "Q2": (225, 260, 225, 260)},
             True: {"Q1": (131, 165, 133, 165), "Q2": (219, 260, 225, 260)}}
+    return {sp: {tid: span(v[0], v[1]) + span(v[2], v[3]) for tid, v in w.items()} for sp, w in want.items()}
 
 
 def check_overhang_kat(binary, d, expected):

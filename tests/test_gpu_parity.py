@@ -158,8 +158,10 @@ def test_overhang_matches_oracle(synth, oracle_lib, gpu, seed, overhang, spliced
 def test_overhang_worked_examples_on_the_gpu(tmp_path):
     """The hand-derived --overhang cases of tests/conftest.py through the CUDA CLI."""
     from conftest import check_overhang_kat, write_overhang_kat
-    d = str(tmp_path)
-    check_overhang_kat(ob.cli_path(), d, write_overhang_kat(d))
+    for minus in (False, True):
+        d = str(tmp_path / ("minus" if minus else "plus"))
+        os.makedirs(d)
+        check_overhang_kat(ob.cli_path(), d, write_overhang_kat(d, minus))
 
 
 def test_config1_golden_batch(gpu):

@@ -90,11 +90,13 @@ def test_overhang_worked_examples(tmp_path):
     """--overhang by hand: stop in the 3' flank, ATG in the 5' flank, and the reference's
     `extend_len - starts[0]` growth after a splice cut — the oracle-backed CLI and, where built, the reference binary."""
     from conftest import check_overhang_kat, write_overhang_kat
-    d = str(tmp_path)
-    expected = write_overhang_kat(d)
-    check_overhang_kat(ORACLE_CLI, d, expected)
-    if os.path.exists(REF_BIN):
-        check_overhang_kat(REF_BIN, d, expected)
+    for minus in (False, True):   # and mirrored onto the reverse strand
+        d = str(tmp_path / ("minus" if minus else "plus"))
+        os.makedirs(d)
+        expected = write_overhang_kat(d, minus)
+        check_overhang_kat(ORACLE_CLI, d, expected)
+        if os.path.exists(REF_BIN):
+            check_overhang_kat(REF_BIN, d, expected)
 
 
 def test_config1_oracle_library_matches_reference_rows(oracle_lib):
