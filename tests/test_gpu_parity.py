@@ -158,10 +158,10 @@ def test_overhang_matches_oracle(synth, oracle_lib, gpu, seed, overhang, spliced
 def test_overhang_worked_examples_on_the_gpu(tmp_path):
     """The hand-derived --overhang cases of tests/conftest.py through the CUDA CLI."""
     from conftest import check_overhang_kat, write_overhang_kat
-    for minus in (False, True):
-        d = str(tmp_path / ("minus" if minus else "plus"))
-        os.makedirs(d)
-        check_overhang_kat(ob.cli_path(), d, write_overhang_kat(d, minus))
+    # (the reverse-strand mirror of these cases runs in the CPU suite against the reference binary and the oracle CLI;
+    # reverse-strand --overhang loci reach the CUDA CLI through tests/sweep_parity.sh)
+    d = str(tmp_path)
+    check_overhang_kat(ob.cli_path(), d, write_overhang_kat(d))
 
 
 def test_config1_golden_batch(gpu):
