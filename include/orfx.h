@@ -22,14 +22,14 @@
 extern "C" {
 #endif
 
-#define ORFX_ABI_VERSION 5
+#define ORFX_ABI_VERSION 6
 
 /* error codes */
 #define ORFX_OK            0
 #define ORFX_E_INVALID    -1   /* bad argument / malformed batch */
 #define ORFX_E_CUDA       -2   /* CUDA runtime or kernel failure */
 #define ORFX_E_NODEVICE   -3   /* no usable GPU: the product path never computes on the CPU */
-#define ORFX_E_UNSUPPORTED -4  /* option outside this build's scope (e.g. --overhang > 0) */
+#define ORFX_E_UNSUPPORTED -4  /* option outside this build's scope (e.g. gap costs with gapo + gape > 64) */
 #define ORFX_E_STATE      -5   /* call sequence error (wait without submit, ...) */
 
 /* --mode selector entries; replaces enum FindMode, orfanage.cpp:29-39 */
@@ -71,7 +71,16 @@ typedef struct orfx_params {
                                    fills tx_ext_lo / tx_ext_hi                                               */
     int32_t has_reference;      /* 0: no FASTA, candidates are scored as seeded (orfanage.cpp:564) */
     int32_t want_rows;          /* 1: return every candidate row (needed by --stats and mode ALL) */
-    int32_t reserved[4];
+    /* Protein alignment of every scored candidate (Finder::align, src/aln.hpp:27-41, with the build definition of
+     * m = 24, mat50, aa_table, unbanded, no z-drop, score only).  Needs has_reference and a batch whose
+     * `seq` also covers the template CDS segments (seg_seq_off set for TEMPLATE segments, raw bytes: ORFX_SEQ_RAW).
+     * Query protein = SEQ::translate (common.hpp:477-495) of the row's rescued CDS on the spliced query, template protein =
+     * the same over the template's spliced CDS chain from its first base; both keep their stop codon; a codon that is
+     * not a codon_map key translates to '\0' there and to residue 23 here, like every byte aa_table does not know. */
+    int32_t align_enabled;
+    int32_t align_gapo;         /* gap open, 0 = the reference's default 12 (aln.hpp:146)                       */
+    int32_t align_gape;         /* gap extend, 0 = the reference's default 2                                    */
+    int32_t reserved[1];
 } orfx_params;
 
 /* 1-based inclusive genomic interval; replaces SEGTP (Transcriptome.h:23-169) */
@@ -128,7 +137,20 @@ typedef struct orfx_batch {
      * sit right before the first / right after the last exon's bases (the island is widened). */
     const int32_t* tx_ext_lo;      /* [n_tx] */
     const int32_t* tx_ext_hi;      /* [n_tx] */
+    /* Which side the bases come from is the packer's business (TX::extend_seq picks it, cpp:348-364): the path reads the
+     * 3' flank next to the 3' terminal exon and the 5' flank next to the 5' one, where "3'" is above the last exon for
+     * strand '+' and below the first exon for every other strand byte.  A strand '.' transcript takes BOTH its flanks from
+     * the low genomic side in the reference; its packer gives it private island bases with the far end of the low-side
+     * flank copied above its last exon (host/runner.cpp: query_flanks) -- islands layout only.
+     * tx_ext_flags ([n_tx] or NULL): ORFX_EXT_LO_VIRTUAL / ORFX_EXT_HI_VIRTUAL mark a one-base flank that is a re-read of the
+     * transcript's own edge base: the transcript touches the end of its chromosome and the clamp arithmetic of
+     * cpp:352-364 yields that base again.  The position does not exist: a stop codon completed by it grows the exon by
+     * one, and the re-loaded sequence then ends one base short, so the row ends as "missing_stop" (cpp:418-442, 155-171). */
+    const uint8_t* tx_ext_flags;
 } orfx_batch;
+
+#define ORFX_EXT_LO_VIRTUAL 1
+#define ORFX_EXT_HI_VIRTUAL 2
 
 #define ORFX_SEQ_RAW 0
 #define ORFX_SEQ_NT4 1
@@ -197,6 +219,15 @@ typedef struct orfx_results {
      * on a copy stream while the chain kernels already run: ms_h2d (submit -> last byte on the device) and
      * ms_kernels (chains on the device -> last kernel) overlap, their sum exceeds the batch time. */
     float ms_h2d, ms_kernels, ms_d2h;
+    /* params.align_enabled && params.want_rows (else NULL): ksw_extz_t fields of the alignment of the row's ORF protein
+     * (query) against its template's protein (target), for every row that reached TX::score (status "-" or "dup");
+     * 0 / INT32_MIN-like sentinels never appear: rows that were not scored hold 0 in all four. */
+    const int32_t* row_aln_max;    /* ez.max   */
+    const int32_t* row_aln_score;  /* ez.score */
+    const int32_t* row_aln_mqe;    /* ez.mqe   */
+    const int32_t* row_aln_mte;    /* ez.mte   */
+    float ms_align;                /* device time of the alignment stage of the last batch (inside ms_kernels) */
+    float reserved1;
 } orfx_results;
 
 typedef struct orfx_ctx orfx_ctx;
@@ -243,6 +274,12 @@ int64_t orfx_resident_query_nt(orfx_ctx* ctx);
  * Buffers must hold ceil(L/32) words, L = spliced length.  Returns L or a negative error. */
 int64_t orfx_get_masks(orfx_ctx* ctx, int32_t tx, uint32_t* stop_bits, uint32_t* start_bits, int64_t max_words);
 
+/* Test hook: lowers an internal capacity so that small inputs reach the code paths of very large ones.
+ * "hb_max_segs" / "hb_max_pairs": segments of a titin-class bundle / (query, transcript) pairs of a bundle slice that
+ * the heavy-bundle kernels keep in shared memory (defaults 9216 / 8192); bundles above take their global-memory branches.
+ * Takes effect at the next orfx_submit / orfx_upload.  Results never depend on these values. */
+int  orfx_debug_set(orfx_ctx* ctx, const char* key, int64_t value);
+
 /* ---- template cleaning: --cleant [--rescue] -------------------------- */
 /* Replaces the per-transcript body of Transcriptome::clean_cds (Transcriptome.cpp:1063-1100): load_seq,
  * optionally TX::rescue_cds(non_aug, 0, false, nullptr) (cpp:641-677), then "first codon is M (unless
@@ -250,7 +287,8 @@ int64_t orfx_get_masks(orfx_ctx* ctx, int32_t tx, uint32_t* stop_bits, uint32_t*
  * template of the bundles made by the first bundleup (cpp:1066) is packed as ORFX_TX_QUERY with segs = its
  * exon chain and tx_cds_start / tx_cds_end = its CDS bounds after build_cds + correct_chain_len; anything
  * else is ORFX_TX_SKIP.  Outputs are caller-owned arrays with one entry per ORFX_TX_QUERY transcript, in
- * batch order.  Uses params.non_aug of the context; --overhang must be 0. */
+ * batch order.  Uses params.non_aug and params.overhang of the context (with --overhang the unguided searches of the
+ * rescue run into the flanks, tx_ext_lo / tx_ext_hi as for orfx_submit). */
 typedef struct orfx_clean_out {
     uint8_t* keep;        /* 1: the CDS survives cleaning; 0: TX::remove_cds()                       */
     int32_t* cds_start;   /* genomic CDS bounds after the (optional) rescue; 0 when keep == 0          */

@@ -22,6 +22,7 @@
 #endif
 #include <cstring>
 #include <map>
+#include <memory>
 #include <set>
 #include <stdexcept>
 #include <string>
@@ -308,6 +309,18 @@ struct T {
     // --overhang: genomic bases usable beyond the low / high end of the exon chain (orfx_batch::tx_ext_lo / tx_ext_hi:
     // the flank of TX::extend_seq after its clamp to the bundle window and its --spliced_overhang cut, cpp:342-399)
     int ext_lo = 0, ext_hi = 0;
+    // ORFX_EXT_*_VIRTUAL: the one-base flank on that side re-reads the transcript's own edge base at the end of the
+    // chromosome (clamp of cpp:352-364).  Positions beyond [real_lo, real_hi] do not exist: Bundle::get_nts (cpp:776-782)
+    // returns a string that ends early for them (std::string::substr clamps the length; below the window start the
+    // reference asserts / throws instead -- mirrored here as the same short read).
+    bool virt_lo = false, virt_hi = false;
+    int real_lo = 0, real_hi = 0;
+    std::string exon_nts(const S& c) const {
+        int s_ = (int)c.s, e_ = (int)c.e;
+        if (virt_lo) s_ = std::max(s_, real_lo);
+        if (virt_hi) e_ = std::min(e_, real_hi);
+        return e_ < s_ ? std::string() : bn->nts(s_, e_);
+    }
 
     int cds_len() const { return clen(cds); }
     // the string TX::extend_seq adds (cpp:342-399), 5'->3' on the transcript's strand
@@ -352,9 +365,9 @@ struct T {
     void load_seq() {   // cpp:683-697, 155-171
         seq = Seq();
         std::string nt;
-        if (strand == '+') for (const S& c : exons) nt += bn->nts((int)c.s, (int)c.e);
+        if (strand == '+') for (const S& c : exons) nt += exon_nts(c);
         else for (int ci = (int)exons.size() - 1; ci >= 0; ci--) {
-            std::string tmp = bn->nts((int)exons[ci].s, (int)exons[ci].e);
+            std::string tmp = exon_nts(exons[ci]);
             for (int i = (int)tmp.size() - 1; i >= 0; i--) nt += nt_complement(tmp[i]);
         }
         for (char& ch : nt) ch = (char)toupper((unsigned char)ch);
@@ -576,6 +589,10 @@ T load_tx(const orfx_batch* b, int tx) {
     } else if (b->tx_kind[tx] == ORFX_TX_QUERY && b->tx_ext_lo && b->tx_ext_hi) {
         t.ext_lo = b->tx_ext_lo[tx];
         t.ext_hi = b->tx_ext_hi[tx];
+        if (b->tx_ext_flags && !t.exons.empty()) {
+            t.virt_lo = (b->tx_ext_flags[tx] & ORFX_EXT_LO_VIRTUAL) != 0; t.virt_hi = (b->tx_ext_flags[tx] & ORFX_EXT_HI_VIRTUAL) != 0;
+            t.real_lo = (int)t.exons.front().s; t.real_hi = (int)t.exons.back().e;
+        }
     }
     return t;
 }
@@ -584,20 +601,37 @@ T load_tx(const orfx_batch* b, int tx) {
 // islands layout of orfx_batch only the bases under query exons were packed: the window is rebuilt
 // here with 'N' everywhere else, so that the rest of this file indexes it exactly as the reference
 // does (an access outside the query exons would then show up as a mismatch in the parity tests).
+// A strand '.' query with a 5' flank carries a private copy of its bases (include/orfx.h, orfx_batch::tx_ext_flags): the
+// bases stored above its last exon are not the genome's.  It is left out of the bundle's window and read through a window
+// of its own.
+bool has_private_copy(const orfx_batch* b, int x) {
+    return b->seg_seq_off && b->tx_ext_hi && b->tx_kind[x] == ORFX_TX_QUERY && b->tx_strand[x] != '+' && b->tx_strand[x] != '-' && b->tx_ext_hi[x] > 0;
+}
 struct BundleSeq {
     std::string rebuilt;
     Bn bn;
-    BundleSeq(const orfx_batch* b, int bi) {
+    // only_tx >= 0: the window of that one (private-copy) transcript, padded so that exon growth beyond the stored flank
+    // (growth is measured against --overhang, cpp:461-474) stays inside it
+    BundleSeq(const orfx_batch* b, int bi, int only_tx = -1, int pad = 0) {
         bn.bstart = b->bundle_start[bi];
         if (!b->seq) { bn.seq = nullptr; return; }
         if (b->seq_format == ORFX_SEQ_NT4 && !b->seg_seq_off) throw std::runtime_error("ORFX_SEQ_NT4 is defined for the islands layout only");
         if (!b->seg_seq_off) { bn.seq = b->seq + b->seq_off[bi]; return; }
         int hi = bn.bstart;
         for (int x = b->bundle_tx_off[bi]; x < b->bundle_tx_off[bi + 1]; x++)
-            if (b->tx_seg_off[x + 1] > b->tx_seg_off[x]) hi = std::max(hi, (int)b->segs[b->tx_seg_off[x + 1] - 1].end + (b->tx_ext_hi ? b->tx_ext_hi[x] : 0));
+            if (b->tx_seg_off[x + 1] > b->tx_seg_off[x]) {
+                hi = std::max(hi, (int)b->segs[b->tx_seg_off[x + 1] - 1].end + (b->tx_ext_hi ? b->tx_ext_hi[x] : 0));
+                if (b->tx_ext_lo && b->tx_kind[x] == ORFX_TX_QUERY)   // a one-base flank below the chromosome's first base (ORFX_EXT_LO_VIRTUAL)
+                    bn.bstart = std::min(bn.bstart, (int)b->segs[b->tx_seg_off[x]].start - b->tx_ext_lo[x]);
+            }
+        if (only_tx >= 0) {
+            bn.bstart = (int)b->segs[b->tx_seg_off[only_tx]].start - (b->tx_ext_lo ? b->tx_ext_lo[only_tx] : 0) - pad - 1;
+            hi = (int)b->segs[b->tx_seg_off[only_tx + 1] - 1].end + b->tx_ext_hi[only_tx] + pad + 1;
+        }
         rebuilt.assign((size_t)(hi - bn.bstart + 1), 'N');
         for (int x = b->bundle_tx_off[bi]; x < b->bundle_tx_off[bi + 1]; x++) {
             if (b->tx_kind[x] != ORFX_TX_QUERY) continue;
+            if (only_tx >= 0 ? x != only_tx : has_private_copy(b, x)) continue;
             for (int k = b->tx_seg_off[x]; k < b->tx_seg_off[x + 1]; k++) {
                 orfx_seg sg = b->segs[k];
                 int64_t at = b->seg_seq_off[k];
@@ -633,7 +667,9 @@ void evaluate(Ctx& cx, const orfx_batch* b) {
         for (int qx = x0; qx < x1; qx++) {
             if (b->tx_kind[qx] != ORFX_TX_QUERY) continue;
             T q = txs[(size_t)(qx - x0)];
-            q.bn = &bn;
+            std::unique_ptr<BundleSeq> own;
+            if (has_private_copy(b, qx)) own.reset(new BundleSeq(b, bi, qx, p.overhang));
+            q.bn = own ? &own->bn : &bn;
             q.remove_cds();
             std::vector<std::vector<Row>> stats;
             for (int tx = x0; tx < x1; tx++) {   // orfanage.cpp:495-637
@@ -804,7 +840,9 @@ int orfx_oracle_clean_templates(orfx_ctx* ctx, const orfx_batch* b, int rescue, 
         for (int x = b->bundle_tx_off[bi]; x < b->bundle_tx_off[bi + 1]; x++) {
             if (b->tx_kind[x] != ORFX_TX_QUERY) continue;
             T t = load_tx(b, x);
-            t.bn = &bs.bn;
+            std::unique_ptr<BundleSeq> own;
+            if (has_private_copy(b, x)) own.reset(new BundleSeq(b, bi, x, c->p.overhang));
+            t.bn = own ? &own->bn : &bs.bn;
             t.cds_start = b->tx_cds_start[x]; t.cds_end = b->tx_cds_end[x]; t.cds_phase = 0;
             t.build_cds();   // the chain the template carries at this point: exons clipped to the CDS bounds
             bool keep = !t.cds.empty();
@@ -878,7 +916,7 @@ int64_t orfx_oracle_masks(const orfx_batch* b, int32_t tx, uint32_t* stop_bits, 
     int bi = 0;
     while (bi < b->n_bundles && !(tx >= b->bundle_tx_off[bi] && tx < b->bundle_tx_off[bi + 1])) bi++;
     if (bi >= b->n_bundles) return ORFX_E_INVALID;
-    BundleSeq bseq(b, bi);
+    BundleSeq bseq(b, bi, has_private_copy(b, tx) ? tx : -1);
     const Bn& bn = bseq.bn;
     T t = load_tx(b, tx);
     t.bn = &bn;

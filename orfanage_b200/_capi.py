@@ -47,11 +47,11 @@ class Params(C.Structure):
     _fields_ = [("n_modes", C.c_int32), ("mode_array", C.c_int32 * 8), ("lpi", C.c_int32), ("ilpi", C.c_int32),
                 ("mlpi", C.c_int32), ("cds_minlen", C.c_int32), ("non_aug", C.c_int32), ("overhang", C.c_int32),
                 ("spliced_overhang", C.c_int32), ("has_reference", C.c_int32), ("want_rows", C.c_int32),
-                ("reserved", C.c_int32 * 4)]
+                ("align_enabled", C.c_int32), ("align_gapo", C.c_int32), ("align_gape", C.c_int32), ("reserved", C.c_int32 * 1)]
 
     @classmethod
     def make(cls, mode="LONGEST_MATCH,BEST,START_MATCH,LONGEST,FIRST,ALL", lpi=-1, ilpi=-1, mlpi=-1, minlen=-1,
-             non_aug=False, has_reference=True, want_rows=True, overhang=0, spliced_overhang=False):
+             non_aug=False, has_reference=True, want_rows=True, overhang=0, spliced_overhang=False, align=False, gapo=0, gape=0):
         p = cls()
         names = [m.strip().upper() for m in mode.split(",")] if isinstance(mode, str) else list(mode)
         p.n_modes = len(names)
@@ -63,6 +63,7 @@ class Params(C.Structure):
         p.spliced_overhang = int(spliced_overhang)
         p.has_reference = int(has_reference)
         p.want_rows = int(want_rows)
+        p.align_enabled, p.align_gapo, p.align_gape = int(align), int(gapo), int(gape)
         return p
 
 
@@ -76,7 +77,7 @@ class _Batch(C.Structure):
                 ("tx_kind", C.c_void_p), ("tx_strand", C.c_void_p), ("tx_seg_off", C.c_void_p), ("tx_cds_start", C.c_void_p),
                 ("tx_cds_end", C.c_void_p), ("tx_tid_class", C.c_void_p), ("segs", C.c_void_p), ("seg_phase", C.c_void_p),
                 ("seg_seq_off", C.c_void_p), ("seq_format", C.c_int32), ("reserved0", C.c_int32),
-                ("tx_ext_lo", C.c_void_p), ("tx_ext_hi", C.c_void_p)]
+                ("tx_ext_lo", C.c_void_p), ("tx_ext_hi", C.c_void_p), ("tx_ext_flags", C.c_void_p)]
 
 
 class _Best(C.Structure):
@@ -96,6 +97,7 @@ _ROW_U8 = ["row_status", "row_pass", "row_start_match"]
 _ROW_I32B = ["row_n_dup", "row_qlen", "row_tlen", "row_ulen", "row_query_start", "row_extra", "row_missing", "row_match",
              "row_outframe", "row_inframe"]
 _ROW_F32 = ["row_lpi", "row_ilpi", "row_mlpi"]
+_ROW_ALN = ["row_aln_max", "row_aln_score", "row_aln_mqe", "row_aln_mte"]
 
 
 class _Results(C.Structure):
@@ -103,7 +105,8 @@ class _Results(C.Structure):
                 + [(n, C.c_void_p) for n in _ROW_I32] + [(n, C.c_void_p) for n in _ROW_U8]
                 + [(n, C.c_void_p) for n in _ROW_I32B] + [(n, C.c_void_p) for n in _ROW_F32]
                 + [("row_ext_lo", C.c_void_p), ("row_ext_hi", C.c_void_p)]
-                + [("print_order", C.c_void_p), ("ms_h2d", C.c_float), ("ms_kernels", C.c_float), ("ms_d2h", C.c_float)])
+                + [("print_order", C.c_void_p), ("ms_h2d", C.c_float), ("ms_kernels", C.c_float), ("ms_d2h", C.c_float)]
+                + [(n, C.c_void_p) for n in _ROW_ALN] + [("ms_align", C.c_float), ("reserved1", C.c_float)])
 
 
 class _AlnOut(C.Structure):
@@ -113,7 +116,7 @@ class _AlnOut(C.Structure):
 _BATCH_ARRAYS = [("seq", np.uint8), ("seq_off", np.int64), ("bundle_start", np.int32), ("bundle_tx_off", np.int32),
                  ("tx_kind", np.uint8), ("tx_strand", np.uint8), ("tx_seg_off", np.int32), ("tx_cds_start", np.int32),
                  ("tx_cds_end", np.int32), ("tx_tid_class", np.int32), ("segs", np.int32), ("seg_phase", np.int8),
-                 ("seg_seq_off", np.int32), ("tx_ext_lo", np.int32), ("tx_ext_hi", np.int32)]
+                 ("seg_seq_off", np.int32), ("tx_ext_lo", np.int32), ("tx_ext_hi", np.int32), ("tx_ext_flags", np.uint8)]
 
 
 def _view(ptr, n, dtype):
@@ -179,7 +182,8 @@ class Batch:
             tx_cds_end=_view(s.tx_cds_end, nt, np.int32), tx_tid_class=_view(s.tx_tid_class, nt, np.int32),
             segs=_view(s.segs, ns * 2, np.int32), seg_phase=_view(s.seg_phase, ns, np.int8),
             seg_seq_off=_view(s.seg_seq_off, ns if s.seg_seq_off else 0, np.int32),
-            tx_ext_lo=_view(s.tx_ext_lo, nt if s.tx_ext_lo else 0, np.int32), tx_ext_hi=_view(s.tx_ext_hi, nt if s.tx_ext_hi else 0, np.int32))
+            tx_ext_lo=_view(s.tx_ext_lo, nt if s.tx_ext_lo else 0, np.int32), tx_ext_hi=_view(s.tx_ext_hi, nt if s.tx_ext_hi else 0, np.int32),
+            tx_ext_flags=_view(s.tx_ext_flags, nt if s.tx_ext_flags else 0, np.uint8))
         b = cls.__new__(cls)
         b.arrays = arrays
         b.arrays["segs"] = b.arrays["segs"].reshape(-1, 2)
@@ -235,7 +239,10 @@ class Results:
             if r.row_ext_lo:   # --overhang only
                 self.rows["ext_lo"] = _view(r.row_ext_lo, n, np.int32).copy()
                 self.rows["ext_hi"] = _view(r.row_ext_hi, n, np.int32).copy()
-        self.ms_h2d, self.ms_kernels, self.ms_d2h = float(r.ms_h2d), float(r.ms_kernels), float(r.ms_d2h)
+            if r.row_aln_max:   # params.align_enabled only
+                for name in _ROW_ALN:
+                    self.rows[name[4:]] = _view(getattr(r, name), n, np.int32).copy()
+        self.ms_h2d, self.ms_kernels, self.ms_d2h, self.ms_align = float(r.ms_h2d), float(r.ms_kernels), float(r.ms_d2h), float(r.ms_align)
 
     def d2h_bytes(self):
         return int(self.best.nbytes + sum(a.nbytes for a in self.rows.values()))
@@ -302,6 +309,8 @@ def load_device_library(path=None):
     lib.orfx_align_batch.restype = C.c_int
     lib.orfx_align_batch.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_int64,
                                      C.c_int, C.c_int, C.POINTER(_AlnOut), C.POINTER(C.c_double), C.POINTER(C.c_float)]
+    lib.orfx_debug_set.restype = C.c_int
+    lib.orfx_debug_set.argtypes = [C.c_void_p, C.c_char_p, C.c_int64]
     if hasattr(lib, "orfx_int_alu_peak"):
         lib.orfx_int_alu_peak.restype = C.c_int
         lib.orfx_int_alu_peak.argtypes = [C.c_void_p, C.POINTER(C.c_double)]
@@ -364,6 +373,10 @@ class Context:
     def set_params(self, params):
         self.params = params
         self._check(self.lib.orfx_set_params(self.handle, C.byref(params)))
+
+    def debug_set(self, key, value):
+        """orfx_debug_set: test hook that lowers an internal capacity (see include/orfx.h)."""
+        self._check(self.lib.orfx_debug_set(self.handle, key.encode(), int(value)))
 
     def submit(self, batch):
         self._keep = batch

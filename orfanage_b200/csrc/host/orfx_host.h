@@ -165,6 +165,7 @@ struct PackedBatch {
     int32_t* seg_seq_off = nullptr;         // islands layout only
     int32_t* tx_ext_lo = nullptr;           // --overhang only: usable flank below / above each query's exon chain
     int32_t* tx_ext_hi = nullptr;
+    uint8_t* tx_ext_flags = nullptr;        // ORFX_EXT_* (a flank that re-reads the chromosome's edge base)
     int32_t n_tx = 0;
     int64_t n_segs = 0, seq_bytes = 0, n_queries = 0;   // seq_bytes counts bases
     int32_t seq_format = ORFX_SEQ_RAW;

@@ -29,7 +29,7 @@ void PackedBatch::reset() {
     arena = nullptr; arena_bytes = 0; dealloc = nullptr;
     bundle_ids.clear(); tx_global.clear();
     n_tx = 0; n_segs = 0; seq_bytes = 0; n_queries = 0; seq_format = ORFX_SEQ_RAW;
-    tx_ext_lo = tx_ext_hi = nullptr;
+    tx_ext_lo = tx_ext_hi = nullptr; tx_ext_flags = nullptr;
 }
 
 orfx_batch PackedBatch::view() const {
@@ -55,6 +55,7 @@ orfx_batch PackedBatch::view() const {
     b.seq_format = seq_format;
     b.tx_ext_lo = tx_ext_lo;
     b.tx_ext_hi = tx_ext_hi;
+    b.tx_ext_flags = tx_ext_flags;
     return b;
 }
 
@@ -80,16 +81,25 @@ inline uint8_t tx_kind_of(const Tx& t, bool keep_all_cds, bool clean_mode) {
     if (clean_mode) return (t.is_coding && !t.cds.empty()) ? ORFX_TX_QUERY : ORFX_TX_SKIP;
     return t.is_templ ? ORFX_TX_TEMPLATE : ((keep_all_cds && t.is_coding) ? ORFX_TX_SKIP : ORFX_TX_QUERY);
 }
-// ext_lo / ext_hi (per transcript of the bundle, may be null): the --overhang flanks widen the terminal exons.
+// --overhang flanks of one query transcript, as the batch carries them (orfx_batch::tx_ext_lo / tx_ext_hi / tx_ext_flags).
+struct QFlank {
+    int32_t lo = 0, hi = 0;      // bases stored right before the first / right after the last exon's bases
+    uint8_t flags = 0;           // ORFX_EXT_*
+    bool private_copy = false;   // strand '.' with a 5' flank: the transcript gets its own copy of its bases (see below)
+    int fake_from = 0;           // ... and the `hi` bases after its last exon are genomic [fake_from, fake_from + hi)
+};
+// ext (per transcript of the bundle, may be null): the flanks widen the terminal exons; transcripts with a private copy
+// are left out of the shared islands.
 void bundle_islands(const Transcriptome& tr, const Bundle& b, bool keep_all_cds, bool clean_mode, std::vector<std::pair<int, int>>& isl,
-                    const int32_t* ext_lo = nullptr, const int32_t* ext_hi = nullptr) {
+                    const QFlank* ext = nullptr) {
     isl.clear();
     for (int i = 0; i < b.count; i++) {
         const Tx& t = tr.txs[b.first + i];
         if (tx_kind_of(t, keep_all_cds, clean_mode) != ORFX_TX_QUERY) continue;
+        if (ext && ext[i].private_copy) continue;
         const size_t first = isl.size();
         for (const Seg& s : t.exons) isl.emplace_back(s.s, s.e);
-        if (ext_lo && isl.size() > first) { isl[first].first -= ext_lo[i]; isl.back().second += ext_hi[i]; }
+        if (ext && isl.size() > first) { isl[first].first -= ext[i].lo; isl.back().second += ext[i].hi; }
     }
     std::sort(isl.begin(), isl.end());
     size_t k = 0;
@@ -99,27 +109,58 @@ void bundle_islands(const Transcriptome& tr, const Bundle& b, bool keep_all_cds,
     }
     isl.resize(k);
 }
-// Bases TX::extend_seq (Transcriptome.cpp:342-399) would add on one genomic side of `t`: at most `overhang`, clamped
-// to the (already padded) bundle window, and with --spliced_overhang cut at the first GT (3' side) / after the last AG
-// (5' side) of the strand-corrected, upper-cased flank.  A transcript that touches the window edge (only possible at a
-// chromosome end) gets no flank; the reference re-reads the edge base there.
-int usable_flank(const Fasta& fa, const Fasta::Seq& chrom, const Bundle& b, const Tx& t, bool high, int overhang, bool spliced) {
-    if (overhang <= 0 || t.exons.empty()) return 0;
-    int es, ee;
-    if (high) { es = t.exons.back().e + 1; ee = std::min(t.exons.back().e + overhang, b.bend); }
-    else { es = std::max(t.exons.front().s - overhang, b.bstart); ee = t.exons.front().s - 1; }
-    if (ee < es) return 0;
-    const int len = ee - es + 1;
-    if (!spliced) return len;
+// Bases [pos0, pos0 + len) (0-based) of a record; positions outside it read the record's first / last base.  The only such
+// reads are the one-base "flank" of a transcript that touches the end of its chromosome (see query_flanks).
+void fetch_clamped(const Fasta& fa, const Fasta::Seq& chrom, int64_t pos0, int64_t len, char* dst) {
+    int64_t a = pos0, n = len;
+    while (n > 0 && a < 0) { *dst++ = fa.at(chrom, 0); a++; n--; }
+    const int64_t inside = std::max<int64_t>(0, std::min<int64_t>(n, chrom.length - a));
+    if (inside > 0) fa.fetch(chrom, a, inside, dst);
+    for (int64_t i = inside; i < n; i++) dst[i] = fa.at(chrom, chrom.length - 1);
+}
+// The string TX::extend_seq (Transcriptome.cpp:342-399) adds on one end of `t`, described by where its bases lie.
+//   side    high when (strand == '+' && towards_stop) || (strand == '-' && !towards_stop), low otherwise -- so a strand '.'
+//           transcript takes BOTH flanks from the low side, exactly as written (neither '+' / '-' test fires for it);
+//   clamp   [min(end + 1, bend), min(end + N, bend)] resp. [max(start - N, bstart), max(start - 1, bstart)]: a transcript that
+//           touches the (padded) bundle window -- only possible at an end of the chromosome -- re-reads its own edge base as a
+//           one-base flank, a position that does not exist (`virt`);
+//   splice  with --spliced_overhang the strand-corrected, upper-cased string is cut before its first GT (towards the stop) or
+//           after its last AG (towards the start).
+// n bases survive; `nearest` says whether they are the n bases next to the exon (every case but the 5' flank of a strand '.'
+// transcript, whose reverse-complemented low-side string is cut from the far end).
+struct RefFlank { int es = 0, ee = -1, n = 0; bool high = false, nearest = true, virt = false; };
+RefFlank reference_flank(const Fasta& fa, const Fasta::Seq& chrom, const Bundle& b, const Tx& t, bool towards_stop, int overhang, bool spliced) {
+    RefFlank f;
+    if (overhang <= 0 || t.exons.empty()) return f;
+    f.high = (t.strand == '+' && towards_stop) || (t.strand == '-' && !towards_stop);
+    if (f.high) { f.es = std::min(t.exons.back().e + 1, b.bend); f.ee = std::min(t.exons.back().e + overhang, b.bend); f.virt = t.exons.back().e >= b.bend; }
+    else { f.es = std::max(t.exons.front().s - overhang, b.bstart); f.ee = std::max(t.exons.front().s - 1, b.bstart); f.virt = t.exons.front().s <= b.bstart; }
+    const int len = f.ee - f.es + 1;
+    f.n = len;
+    f.nearest = towards_stop || t.strand == '+' || t.strand == '-';
+    if (!spliced || len <= 0) return f;
     std::string g((size_t)len, 'N');
-    fa.fetch(chrom, es - 1, len, &g[0]);
-    std::string f;   // 5'->3' on the transcript's strand
-    if (t.strand == '+') f = g; else for (int i = len - 1; i >= 0; i--) f += nt_complement(g[(size_t)i]);
-    for (char& c : f) c = (char)toupper((unsigned char)c);
-    const bool towards_stop = (t.strand == '+') == high;
-    if (towards_stop) { const size_t at = f.find("GT"); return at == std::string::npos ? len : (int)at; }
-    const size_t at = f.rfind("AG");
-    return at == std::string::npos ? len : len - (int)(at + 2);
+    fa.fetch(chrom, f.es - 1, len, &g[0]);
+    std::string s5;   // 5'->3' on the transcript's strand
+    if (t.strand == '+') s5 = g; else for (int i = len - 1; i >= 0; i--) s5 += nt_complement(g[(size_t)i]);
+    for (char& c : s5) c = (char)toupper((unsigned char)c);
+    if (towards_stop) { const size_t at = s5.find("GT"); if (at != std::string::npos) f.n = (int)at; }
+    else { const size_t at = s5.rfind("AG"); if (at != std::string::npos) f.n = len - (int)(at + 2); }
+    return f;
+}
+// What the batch carries for one query (include/orfx.h, orfx_batch::tx_ext_*).  The device reads a flank as the bases stored
+// next to the terminal exon on the side the strand byte implies ('+': 5' below, 3' above; any other strand: 5' above, 3'
+// below).  That is where the reference takes them from for '+' and '-'.  A strand '.' transcript takes its 5' flank from the
+// LOW side: it gets a private copy of its bases in which those low-side bases are stored above its last exon, in ascending
+// order -- read downwards and complemented they are the string the reference prepends.
+QFlank query_flanks(const Fasta& fa, const Fasta::Seq& chrom, const Bundle& b, const Tx& t, int overhang, bool spliced) {
+    QFlank q;
+    const RefFlank f3 = reference_flank(fa, chrom, b, t, true, overhang, spliced), f5 = reference_flank(fa, chrom, b, t, false, overhang, spliced);
+    (f3.high ? q.hi : q.lo) = f3.n;
+    if (f3.virt && f3.n > 0) q.flags |= f3.high ? ORFX_EXT_HI_VIRTUAL : ORFX_EXT_LO_VIRTUAL;
+    if (f5.high != f3.high) (f5.high ? q.hi : q.lo) = f5.n;   // '+' and '-': the other side, bases next to the exon
+    else if (f5.n > 0) { q.hi = f5.n; q.private_copy = true; q.fake_from = f5.es; }   // strand '.': the far end of the low-side string
+    return q;
 }
 }  // namespace
 
@@ -139,31 +180,37 @@ void pack_bundles(const Transcriptome& tr, const std::vector<int>& bundle_ids, b
     size_t total_seq = 0, total_tx = 0, total_segs = 0;
     std::vector<int64_t> bundle_bytes(nb, 0);
     std::vector<std::pair<int, int>> isl;
-    // --overhang: usable flanks of every query, per bundle in transcript order
-    std::vector<std::vector<int32_t>> fl_lo(overhang > 0 ? nb : 0), fl_hi(overhang > 0 ? nb : 0);
+    // --overhang: flanks of every query, per bundle in transcript order
+    std::vector<std::vector<QFlank>> fl(overhang > 0 ? nb : 0);
     if (overhang > 0) {
         for (size_t j = 0; j < nb; j++) {
             const Bundle& b = tr.bundles[bundle_ids[j]];
             const Fasta::Seq* chrom = tr.fasta->find(tr.seqnames[(size_t)b.seqid]);
-            fl_lo[j].assign((size_t)b.count, 0); fl_hi[j].assign((size_t)b.count, 0);
+            fl[j].assign((size_t)b.count, QFlank());
             for (int i = 0; i < b.count; i++) {
                 const Tx& t = tr.txs[b.first + i];
                 if (tx_kind_of(t, keep_all_cds, clean_mode) != ORFX_TX_QUERY) continue;
-                fl_lo[j][(size_t)i] = usable_flank(*tr.fasta, *chrom, b, t, false, overhang, spliced_overhang);
-                fl_hi[j][(size_t)i] = usable_flank(*tr.fasta, *chrom, b, t, true, overhang, spliced_overhang);
+                fl[j][(size_t)i] = query_flanks(*tr.fasta, *chrom, b, t, overhang, spliced_overhang);
+                if (fl[j][(size_t)i].private_copy && !islands)
+                    throw std::runtime_error("--overhang with strand '.' transcripts needs the islands layout (their 5' flank is a private copy of low-side bases)");
             }
         }
     }
-    auto flo = [&](size_t j) { return overhang > 0 ? fl_lo[j].data() : nullptr; };
-    auto fhi = [&](size_t j) { return overhang > 0 ? fl_hi[j].data() : nullptr; };
+    auto flk = [&](size_t j) { return overhang > 0 ? fl[j].data() : nullptr; };
+    // bases of the private copy of transcript i of bundle j: [lo flank][exons][hi "flank"]
+    auto private_len = [&](size_t j, int i, const Tx& t) { return (int64_t)fl[j][(size_t)i].lo + chain_len(t.exons) + fl[j][(size_t)i].hi; };
+    // whole-window layout with --overhang: one more base on either side, so that the one-base flank of a transcript that
+    // touches the end of its chromosome (a re-read of the edge base) has a place
+    const int wpad = (!islands && overhang > 0) ? 1 : 0;
     for (size_t j = 0; j < nb; j++) {
         const Bundle& b = tr.bundles[bundle_ids[j]];
         if (has_seq) {
             if (islands) {
-                bundle_islands(tr, b, keep_all_cds, clean_mode, isl, flo(j), fhi(j));
+                bundle_islands(tr, b, keep_all_cds, clean_mode, isl, flk(j));
                 for (auto& iv : isl) bundle_bytes[j] += iv.second - iv.first + 1;
+                if (overhang > 0) for (int i = 0; i < b.count; i++) if (fl[j][(size_t)i].private_copy) bundle_bytes[j] += private_len(j, i, tr.txs[b.first + i]);
                 if (nt4) bundle_bytes[j] += bundle_bytes[j] & 1;   // bundles start on a byte boundary
-            } else bundle_bytes[j] = b.bend - b.bstart + 1;
+            } else bundle_bytes[j] = b.bend - b.bstart + 1 + 2 * wpad;
             total_seq += (size_t)bundle_bytes[j];
         }
         total_tx += (size_t)b.count;
@@ -176,7 +223,7 @@ void pack_bundles(const Transcriptome& tr, const std::vector<int>& bundle_ids, b
            o_cs = o_segoff + up((total_tx + 1) * 4), o_ce = o_cs + up(total_tx * 4 + 4), o_tid = o_ce + up(total_tx * 4 + 4),
            o_segs = o_tid + up(total_tx * 4 + 4), o_phase = o_segs + up(total_segs * 8 + 8), o_sso = o_phase + up(total_segs + 4),
            o_xlo = o_sso + up(islands ? total_segs * 4 + 4 : 4), o_xhi = o_xlo + up(overhang > 0 ? total_tx * 4 + 4 : 4),
-           o_end = o_xhi + up(overhang > 0 ? total_tx * 4 + 4 : 4);
+           o_xfl = o_xhi + up(overhang > 0 ? total_tx * 4 + 4 : 4), o_end = o_xfl + up(overhang > 0 ? total_tx + 4 : 4);
     out.arena = alloc ? alloc(o_end) : malloc(o_end);
     if (!out.arena) throw std::runtime_error("cannot allocate " + std::to_string(o_end) + " bytes for the packed batch");
     out.arena_bytes = o_end;
@@ -189,20 +236,19 @@ void pack_bundles(const Transcriptome& tr, const std::vector<int>& bundle_ids, b
     out.seg_seq_off = islands ? (int32_t*)(base + o_sso) : nullptr;
     out.tx_ext_lo = overhang > 0 ? (int32_t*)(base + o_xlo) : nullptr;
     out.tx_ext_hi = overhang > 0 ? (int32_t*)(base + o_xhi) : nullptr;
+    out.tx_ext_flags = overhang > 0 ? (uint8_t*)(base + o_xfl) : nullptr;
     out.n_tx = (int32_t)total_tx; out.n_segs = (int64_t)total_segs; out.seq_bytes = (int64_t)total_seq;
     out.seq_format = nt4 ? ORFX_SEQ_NT4 : ORFX_SEQ_RAW;
     out.tx_global.resize(total_tx);
 
     int64_t so = 0;
     int32_t x = 0, sg = 0;
-    std::vector<int32_t> first_seg(nb + 1, 0);
     out.seq_off[0] = 0; out.bundle_tx_off[0] = 0; out.tx_seg_off[0] = 0;
     for (size_t j = 0; j < nb; j++) {
         const Bundle& b = tr.bundles[bundle_ids[j]];
         so += bundle_bytes[j];
         out.seq_off[j + 1] = so;
-        out.bundle_start[j] = b.bstart;
-        first_seg[j] = sg;
+        out.bundle_start[j] = b.bstart - wpad;
         for (int i = 0; i < b.count; i++, x++) {
             const Tx& t = tr.txs[b.first + i];
             out.tx_global[(size_t)x] = b.first + i;
@@ -217,11 +263,10 @@ void pack_bundles(const Transcriptome& tr, const std::vector<int>& bundle_ids, b
             out.tx_cds_start[x] = (as_templ || (clean_mode && kind == ORFX_TX_QUERY)) ? t.cds_start : 0;
             out.tx_cds_end[x] = (as_templ || (clean_mode && kind == ORFX_TX_QUERY)) ? t.cds_end : 0;
             out.tx_tid_class[x] = tid_classes.at(t.tid);
-            if (overhang > 0) { out.tx_ext_lo[x] = fl_lo[j][(size_t)i]; out.tx_ext_hi[x] = fl_hi[j][(size_t)i]; }
+            if (overhang > 0) { const QFlank& f = fl[j][(size_t)i]; out.tx_ext_lo[x] = f.lo; out.tx_ext_hi[x] = f.hi; out.tx_ext_flags[x] = f.flags; }
         }
         out.bundle_tx_off[j + 1] = x;
     }
-    first_seg[nb] = sg;
     if (has_seq && total_seq) {   // Bundle::load_seq, cpp:821-830
         std::vector<const Fasta::Seq*> chrom(tr.seqnames.size(), nullptr);
         for (size_t k = 0; k < chrom.size(); k++) chrom[k] = tr.fasta->find(tr.seqnames[k]);
@@ -233,28 +278,41 @@ void pack_bundles(const Transcriptome& tr, const std::vector<int>& bundle_ids, b
                 const Bundle& b = tr.bundles[bundle_ids[j]];
                 const Fasta::Seq& src = *chrom[(size_t)b.seqid];
                 uint8_t* dst = nt4 ? out.seq + out.seq_off[j] / 2 : out.seq + out.seq_off[j];
-                if (!islands) { tr.fasta->fetch(src, b.bstart - 1, b.bend - b.bstart + 1, (char*)dst); continue; }
-                bundle_islands(tr, b, keep_all_cds, clean_mode, il, flo(j), fhi(j));
-                il_off.resize(il.size());
+                if (!islands) {
+                    if (wpad) fetch_clamped(*tr.fasta, src, (int64_t)b.bstart - 2, (int64_t)b.bend - b.bstart + 3, (char*)dst);
+                    else tr.fasta->fetch(src, b.bstart - 1, b.bend - b.bstart + 1, (char*)dst);
+                    continue;
+                }
                 int32_t o = 0;
-                for (size_t k = 0; k < il.size(); k++) {
-                    il_off[k] = o;
-                    const int len = il[k].second - il[k].first + 1;
-                    if (!nt4) tr.fasta->fetch(src, il[k].first - 1, len, (char*)dst + o);
+                // appends genomic [g0, g0 + len) (1-based; clamped reads past a chromosome end) at base offset o of the bundle
+                auto append = [&](int64_t g0, int len) {
+                    if (len <= 0) return;
+                    raw.resize((size_t)len);
+                    fetch_clamped(*tr.fasta, src, g0 - 1, len, raw.data());
+                    if (!nt4) memcpy((char*)dst + o, raw.data(), (size_t)len);
                     else {
-                        raw.resize((size_t)len);
-                        tr.fasta->fetch(src, il[k].first - 1, len, raw.data());
                         const uint8_t* sp = (const uint8_t*)raw.data();
                         int i = 0, p = o;
                         if (p & 1) { dst[p >> 1] = (uint8_t)(dst[p >> 1] | (NT4.code[sp[0]] << 4)); i = 1; p++; }
                         for (; i + 1 < len; i += 2, p += 2) dst[p >> 1] = (uint8_t)(NT4.code[sp[i]] | (NT4.code[sp[i + 1]] << 4));
-                        if (i < len) dst[p >> 1] = NT4.code[sp[i]];   // low nibble; the high one is OR-ed in by the next island
+                        if (i < len) dst[p >> 1] = NT4.code[sp[i]];   // low nibble; the high one is OR-ed in by whatever follows
                     }
                     o += len;
-                }
-                // offset of every query segment: the island holding its start
+                };
+                bundle_islands(tr, b, keep_all_cds, clean_mode, il, flk(j));
+                il_off.resize(il.size());
+                for (size_t k = 0; k < il.size(); k++) { il_off[k] = o; append(il[k].first, il[k].second - il[k].first + 1); }
+                // offset of every query segment: the island holding its start, or the transcript's private copy
                 for (int xx = out.bundle_tx_off[j]; xx < out.bundle_tx_off[j + 1]; xx++) {
                     const bool isq = out.tx_kind[xx] == ORFX_TX_QUERY;
+                    const QFlank* f = overhang > 0 ? &fl[j][(size_t)(xx - out.bundle_tx_off[j])] : nullptr;
+                    if (isq && f && f->private_copy) {
+                        const int k0 = out.tx_seg_off[xx], k1 = out.tx_seg_off[xx + 1];
+                        append((int64_t)out.segs[k0].start - f->lo, f->lo);
+                        for (int k = k0; k < k1; k++) { out.seg_seq_off[k] = o; append(out.segs[k].start, out.segs[k].end - out.segs[k].start + 1); }
+                        append(f->fake_from, f->hi);
+                        continue;
+                    }
                     for (int k = out.tx_seg_off[xx]; k < out.tx_seg_off[xx + 1]; k++) {
                         if (!isq) { out.seg_seq_off[k] = 0; continue; }
                         const int st = out.segs[k].start;

@@ -15,6 +15,7 @@ int64_t scan_tmp_elems(int64_t n);
 int launch_prep(const DevBatch& B, int64_t* cnt_q, int64_t* cnt_words, int64_t* cnt_tiles, int64_t* scan_tmp, int32_t* heavy_list, unsigned* heavy_count,
                 cudaStream_t s);
 int launch_fill_tiles(const DevBatch& B, cudaStream_t s);
+int launch_validate(const DevBatch& B, int has_seq, int allow_empty, int* flag, cudaStream_t s);
 int launch_count_rows(const DevBatch& B, int64_t* cnt, int64_t* scan_tmp, const int32_t* heavy_list, const unsigned* heavy_count, int n_sm, cudaStream_t s,
                       cudaStream_t side, cudaEvent_t ev_fork, cudaEvent_t ev_join);
 int launch_fill_rows(const DevBatch& B, const DevRows& R, int n_queries, cudaStream_t s);
@@ -103,7 +104,10 @@ struct orfx_ctx {
     DBuf d_need, d_planes, d_heavy, d_heavy_count;
     DBuf d_cnt_q, d_cnt_words, d_cnt_tiles, d_cnt_rows, d_scan_tmp, d_ord;
     DBuf d_clean_keep, d_clean_s, d_clean_e, d_keys;
-    DBuf d_xlo, d_xhi;   // --overhang flanks
+    DBuf d_xlo, d_xhi, d_xfl;   // --overhang flanks
+    DBuf d_flag;
+    int hb_max_segs = HB_MAX_SEGS, hb_max_pairs = HB_MAX_PAIRS;   // orfx_debug_set
+    bool allow_empty_chains = false;   // compare batches (orfx_score_pairs): a query without a CDS is legal there
     // rows
     DBuf r_i32[16], r_f32[3], r_u8[3], r_order, d_best, r_ext[2];
     HBuf h_totals, h_best, h_i32[16], h_f32[3], h_u8[3], h_order, h_ext[2];
@@ -128,6 +132,9 @@ int upload_batch(orfx_ctx* c, const orfx_batch* b, bool overlap = false) {
     if (!b) return fail(ORFX_E_INVALID, "null batch");
     if (b->n_bundles < 0 || b->n_tx < 0 || b->n_segs < 0) return fail(ORFX_E_INVALID, "negative batch size");
     if (c->P.has_reference && b->seq_bytes > 0 && !b->seq) return fail(ORFX_E_INVALID, "params.has_reference set but batch.seq is NULL");
+    if ((b->n_bundles > 0 || b->n_tx > 0) && (!b->bundle_tx_off || !b->tx_seg_off || !b->tx_kind || !b->tx_strand || !b->tx_cds_start || !b->tx_cds_end || !b->tx_tid_class ||
+                                              !b->bundle_start || (b->n_segs > 0 && (!b->segs || !b->seg_phase)) || (c->P.has_reference && b->seq_bytes > 0 && !b->seq_off)))
+        return fail(ORFX_E_INVALID, "null array in a non-empty batch");
     cudaStream_t s = c->stream;
     const size_t nb = (size_t)b->n_bundles, nt = (size_t)b->n_tx, ns = (size_t)b->n_segs;
     const size_t seqb = c->P.has_reference ? (size_t)b->seq_bytes : 0;                    // bases
@@ -171,6 +178,11 @@ int upload_batch(orfx_ctx* c, const orfx_batch* b, bool overlap = false) {
         if (nt && (!b->tx_ext_lo || !b->tx_ext_hi)) return fail(ORFX_E_INVALID, "params.overhang > 0 needs batch.tx_ext_lo / tx_ext_hi");
         CU(c->d_xlo.ensure(nt * 4 + 4)); CU(c->d_xhi.ensure(nt * 4 + 4));
         CU(cp(c->d_xlo, b->tx_ext_lo, nt * 4)); CU(cp(c->d_xhi, b->tx_ext_hi, nt * 4));
+        if (b->tx_ext_flags) { CU(c->d_xfl.ensure(nt + 4)); CU(cp(c->d_xfl, b->tx_ext_flags, nt)); }
+        if (!b->seg_seq_off)   // a strand '.' query takes its 5' flank from the low side: only a private copy of its bases can hold that
+            for (size_t i = 0; i < nt; i++)
+                if (b->tx_kind[i] == ORFX_TX_QUERY && b->tx_strand[i] != '+' && b->tx_strand[i] != '-' && b->tx_ext_hi[i] > 0)
+                    return fail(ORFX_E_UNSUPPORTED, "--overhang with strand '.' query transcripts needs the islands layout (seg_seq_off)");
     }
     c->seq_in_flight = false;
     if (seqb && overlap) {
@@ -200,7 +212,7 @@ int upload_batch(orfx_ctx* c, const orfx_batch* b, bool overlap = false) {
     CU(c->d_heavy_count.ensure(16));
     const size_t plane_words = (seqb + 31) / 32 + 4;
     if (seqb) CU(c->d_planes.ensure(2 * plane_words * 16));
-    CU(c->h_totals.ensure(64));
+    CU(c->h_totals.ensure(128));
     DevBatch& B = c->B;
     memset(&B, 0, sizeof B);
     B.n_bundles = b->n_bundles; B.n_tx = b->n_tx; B.n_segs = b->n_segs; B.seq_bytes = (int64_t)seqb; B.seq_format = b->seq_format;
@@ -214,9 +226,27 @@ int upload_batch(orfx_ctx* c, const orfx_batch* b, bool overlap = false) {
     B.seg_seq_off = islands ? c->d_sso.as<int32_t>() : nullptr;
     B.tx_ext_lo = flanks ? c->d_xlo.as<int32_t>() : nullptr;
     B.tx_ext_hi = flanks ? c->d_xhi.as<int32_t>() : nullptr;
+    B.tx_ext_flags = flanks && b->tx_ext_flags ? c->d_xfl.as<uint8_t>() : nullptr;
     B.bundle_need = c->d_need.as<uint8_t>(); B.planes = c->d_planes.as<uint32_t>(); B.plane_words = (int64_t)plane_words;
-    c->resident = true;
+    B.hb_max_segs = c->hb_max_segs; B.hb_max_pairs = c->hb_max_pairs;
     c->have_results = false;
+    // The batch is caller-supplied: check what every kernel relies on (monotone CSR offsets, ordered chains, bases in
+    // range) before anything walks it.  One small kernel and one flag read-back; the sequence bytes are already on their way.
+    if (nt || nb) {
+        CU(c->d_flag.ensure(16));
+        launch_validate(B, seqb ? 1 : 0, c->allow_empty_chains ? 1 : 0, c->d_flag.as<int>(), s);
+        int* hflag = reinterpret_cast<int*>(c->h_totals.as<int64_t>() + 6);
+        CU(cudaMemcpyAsync(hflag, c->d_flag.p, sizeof(int), cudaMemcpyDeviceToHost, s));
+        CU(cudaStreamSynchronize(s));
+        if (*hflag) {
+            c->resident = false;
+            if (c->seq_in_flight) { cudaStreamSynchronize(c->copy_stream); c->seq_in_flight = false; }
+            char msg[160];
+            snprintf(msg, sizeof msg, "malformed batch (check bits 0x%x: 1 offsets, 2 transcript kind, 4 empty chain, 8 segment order, 16 negative flank, 32 bases out of range)", *hflag);
+            return fail(ORFX_E_INVALID, msg);
+        }
+    }
+    c->resident = true;
     return ORFX_OK;
 }
 
@@ -258,11 +288,11 @@ int run_path(orfx_ctx* c) {
         CU(c->d_start.ensure((size_t)words * 4 + 16));
         B.tile_tx = c->d_tile_tx.as<int32_t>(); B.stop_mask = c->d_stop.as<uint32_t>(); B.start_mask = c->d_start.as<uint32_t>();
     }
+    if (nrows > (int64_t)INT32_MAX) return fail(ORFX_E_INVALID, "more than 2^31 candidate rows in one batch: shard it");
     for (int i = 0; i < 16; i++) CU(c->r_i32[i].ensure((size_t)nrows * 4 + 4));
     for (int i = 0; i < 3; i++) CU(c->r_f32[i].ensure((size_t)nrows * 4 + 4));
     for (int i = 0; i < 3; i++) CU(c->r_u8[i].ensure((size_t)nrows + 4));
     CU(c->r_order.ensure((size_t)nrows * 8 + 8));
-    if (nrows > (int64_t)INT32_MAX) return fail(ORFX_E_INVALID, "more than 2^31 candidate rows in one batch: shard it");
     CU(c->d_ord.ensure((size_t)nrows * 4 + 4));
     CU(c->d_keys.ensure((size_t)nrows * 48 + 16));
     CU(c->d_best.ensure((size_t)nq * sizeof(orfx_best) + 8));
@@ -486,7 +516,7 @@ void orfx_destroy(orfx_ctx* c) {
                  &c->d_segs, &c->d_phase, &c->d_seg_cum, &c->d_tx_len, &c->d_tx_bundle, &c->d_mask_off, &c->d_tile_off, &c->d_q_off, &c->d_q_list,
                  &c->d_row_off, &c->d_tile_tx, &c->d_stop, &c->d_start, &c->d_need, &c->d_planes, &c->d_heavy, &c->d_heavy_count, &c->d_cnt_q, &c->d_cnt_words, &c->d_cnt_tiles, &c->d_cnt_rows, &c->d_scan_tmp,
                  &c->d_ord, &c->r_order, &c->d_best, &c->d_clean_keep, &c->d_clean_s, &c->d_clean_e, &c->d_keys,
-                 &c->d_xlo, &c->d_xhi, &c->r_ext[0], &c->r_ext[1]};
+                 &c->d_xlo, &c->d_xhi, &c->d_xfl, &c->d_flag, &c->r_ext[0], &c->r_ext[1]};
     for (DBuf* b : d) b->free_();
     for (auto& b : c->r_i32) b.free_();
     for (auto& b : c->r_f32) b.free_();
@@ -592,6 +622,15 @@ int64_t orfx_get_masks(orfx_ctx* c, int32_t tx, uint32_t* stop_bits, uint32_t* s
     return L;
 }
 
+int orfx_debug_set(orfx_ctx* c, const char* key, int64_t value) {
+    if (!c || !key) return fail(ORFX_E_INVALID, "null argument");
+    const std::string k(key);
+    if (k == "hb_max_segs") { if (value < 0 || value > HB_MAX_SEGS) return fail(ORFX_E_INVALID, "hb_max_segs out of range"); c->hb_max_segs = (int)value; }
+    else if (k == "hb_max_pairs") { if (value < 0 || value > HB_MAX_PAIRS) return fail(ORFX_E_INVALID, "hb_max_pairs out of range"); c->hb_max_pairs = (int)value; }
+    else return fail(ORFX_E_INVALID, "unknown debug key " + k);
+    return ORFX_OK;
+}
+
 int orfx_clean_templates(orfx_ctx* c, const orfx_batch* batch, int rescue, orfx_clean_out* out, int64_t* n_out) {
     if (!c || !out || !out->keep || !out->cds_start || !out->cds_end) return fail(ORFX_E_INVALID, "null argument");
     if (!c->P.has_reference) return fail(ORFX_E_INVALID, "template cleaning needs a reference genome (params.has_reference)");
@@ -644,7 +683,9 @@ int orfx_score_pairs(orfx_ctx* c, const orfx_batch* batch, orfx_results* out) {
     nb = *batch; nb.seq = nullptr; nb.seq_bytes = 0; nb.seg_seq_off = nullptr;   // a compare batch reads no sequence
     const int32_t has_ref = c->P.has_reference;
     c->P.has_reference = 0;
+    c->allow_empty_chains = true;
     int rc = upload_batch(c, &nb);
+    c->allow_empty_chains = false;
     c->P.has_reference = has_ref;
     if (rc) return rc;
     cudaStream_t s = c->stream;

@@ -12,6 +12,7 @@ struct DevBatch {
     int32_t n_bundles, n_tx;
     int64_t n_segs, seq_bytes;   // seq_bytes counts bases (== bytes unless seq_format == ORFX_SEQ_NT4)
     int32_t seq_format;
+    int32_t hb_max_segs, hb_max_pairs;   // <= HB_MAX_SEGS / HB_MAX_PAIRS: bundles above them take the heavy kernels' global-memory branches
     // [in]
     const uint8_t* seq;
     const int64_t* seq_off;
@@ -28,6 +29,7 @@ struct DevBatch {
     const int32_t* seg_seq_off;   // islands layout (else nullptr)
     const int32_t* tx_ext_lo;     // --overhang: usable flank below the first / above the last exon of each query (else nullptr)
     const int32_t* tx_ext_hi;
+    const uint8_t* tx_ext_flags;  // ORFX_EXT_*_VIRTUAL per query (nullptr when no flank of the batch is a re-read edge base)
     // derived
     int32_t* seg_cum;        // [n_segs] bases of the transcript before this segment (genomic order)
     int32_t* tx_len;         // [n_tx] spliced length
@@ -58,6 +60,8 @@ struct DevRows {
     int32_t *ext_lo, *ext_hi;   // --overhang: exon-chain growth of the row's query copy (else nullptr)
 };
 
+static constexpr int HB_MAX_SEGS = 9216;      // heavy-bundle kernels (pipeline.cu): capacity of the shared-memory stage
+static constexpr int HB_MAX_PAIRS = 8192;
 static constexpr int SCAN_TILE_WORDS = 16;     // mask words (32 spliced positions each) per codon-scan run (one thread)
 static constexpr int CSCAN_THREADS = 256;
 

@@ -86,6 +86,62 @@ int launch_exclusive_scan(const int64_t* in, int64_t* out, int64_t* tmp, int64_t
 int64_t scan_tmp_elems(int64_t n) { return (n + SCAN_BLOCK - 1) / SCAN_BLOCK + 1; }
 
 // ------------------------------------------------------------------------------------------------
+// validation of a caller-supplied batch (include/orfx.h is a public seam: the host packer is not the only caller)
+// ------------------------------------------------------------------------------------------------
+// Bit set in *flag: 1 offsets of the bundle / transcript / sequence CSR not monotone or out of range, 2 unknown
+// transcript kind, 4 QUERY / TEMPLATE transcript without a segment, 8 segment with end < start or start < 0 or a chain
+// that is not ascending and disjoint, 16 negative --overhang flank, 32 a query segment (with its flank) outside its
+// bundle's bases.  Every later kernel trusts these properties.
+__global__ void __launch_bounds__(256) validate_batch_kernel(DevBatch B, int has_seq, int allow_empty, int* flag) {
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    int bad = 0;
+    if (i == 0) {
+        if (B.bundle_tx_off[0] != 0 || B.bundle_tx_off[B.n_bundles] != B.n_tx || B.tx_seg_off[0] != 0 || (int64_t)B.tx_seg_off[B.n_tx] != B.n_segs) bad |= 1;
+        if (has_seq && (B.seq_off[0] != 0 || B.seq_off[B.n_bundles] > B.seq_bytes)) bad |= 1;
+    }
+    if (i < B.n_bundles) {
+        const int x0 = B.bundle_tx_off[i], x1 = B.bundle_tx_off[i + 1];
+        if (x0 < 0 || x1 < x0 || x1 > B.n_tx) bad |= 1;
+        if (has_seq) { const int64_t a = B.seq_off[i], b = B.seq_off[i + 1]; if (a < 0 || b < a || b > B.seq_bytes) bad |= 1; }
+    }
+    if (i < B.n_tx) {
+        const int s0 = B.tx_seg_off[i], s1 = B.tx_seg_off[i + 1];
+        const int kind = B.tx_kind[i];
+        if (kind > ORFX_TX_SKIP) bad |= 2;
+        if (s0 < 0 || s1 < s0 || (int64_t)s1 > B.n_segs) bad |= 1;
+        else {
+            if (kind != ORFX_TX_SKIP && s1 == s0 && !allow_empty) bad |= 4;
+            int xlo = 0, xhi = 0;
+            if (B.tx_ext_lo && kind == ORFX_TX_QUERY) { xlo = B.tx_ext_lo[i]; xhi = B.tx_ext_hi[i]; if (xlo < 0 || xhi < 0) { bad |= 16; xlo = xhi = 0; } }
+            // the transcript's bundle: last b with bundle_tx_off[b] <= i (a broken array is reported by its own threads)
+            int lo = 0, hi = max(B.n_bundles - 1, 0);
+            while (lo < hi) { const int mid = (lo + hi + 1) >> 1; if (B.bundle_tx_off[mid] <= (int)i) lo = mid; else hi = mid - 1; }
+            const bool check_seq = has_seq && kind == ORFX_TX_QUERY && B.n_bundles > 0;
+            const int64_t nbases = check_seq ? B.seq_off[lo + 1] - B.seq_off[lo] : 0;
+            const int bstart = check_seq && !B.seg_seq_off ? B.bundle_start[lo] : 0;
+            int prev_end = INT_MIN;
+            for (int k = s0; k < s1; k++) {
+                const orfx_seg sg = B.segs[k];
+                if (sg.end < sg.start || sg.start < 0 || (prev_end != INT_MIN && sg.start <= prev_end)) bad |= 8;
+                prev_end = sg.end;
+                if (check_seq) {
+                    const int64_t first = (B.seg_seq_off ? (int64_t)B.seg_seq_off[k] : (int64_t)sg.start - bstart) - (k == s0 ? xlo : 0);
+                    const int64_t last = (B.seg_seq_off ? (int64_t)B.seg_seq_off[k] : (int64_t)sg.start - bstart) + (sg.end - sg.start) + (k == s1 - 1 ? xhi : 0);
+                    if (first < 0 || last >= nbases) bad |= 32;
+                }
+            }
+        }
+    }
+    if (bad) atomicOr(flag, bad);
+}
+int launch_validate(const DevBatch& B, int has_seq, int allow_empty, int* flag, cudaStream_t s) {
+    cudaMemsetAsync(flag, 0, sizeof(int), s);
+    const int64_t n = std::max<int64_t>(std::max<int64_t>(B.n_tx, B.n_bundles), 1);
+    validate_batch_kernel<<<(unsigned)((n + 255) / 256), 256, 0, s>>>(B, has_seq, allow_empty, flag);
+    return 1;
+}
+
+// ------------------------------------------------------------------------------------------------
 // prep
 // ------------------------------------------------------------------------------------------------
 // eight lanes per transcript (a chain has ~10 segments): coalesced segment loads, group scan of the segment lengths
@@ -352,8 +408,10 @@ namespace {
 // are walked 5'->3' until the first piece where both CDSs are in the same frame; the start is the
 // nearest ATG whose transcript position does not exceed that piece's CDS-relative position (mixed
 // coordinate systems exactly as written, cpp:581-590), else the farthest ATG.
-__device__ int guided_start(const TxView& q, const TxView& t, const uint32_t* start_mask, int far, int a, int e, int lb, int o) {
-    const int g_far = t2g(q, far), g_e = t2g(q, e);
+// `base`: 5' end of the query CDS that is intersected and the origin of its CDS-relative positions -- the farthest ATG
+// (`far`) everywhere except on strand '.', where the reference extends the chain at the wrong end (see process_row).
+__device__ int guided_start(const TxView& q, const TxView& t, const uint32_t* start_mask, int far, int base, int a, int e, int lb, int o) {
+    const int g_far = t2g(q, base), g_e = t2g(q, e);
     const int glo = min(g_far, g_e), ghi = max(g_far, g_e);
     const bool plus = q.plus;
     bool seen = false, done = false;
@@ -370,7 +428,7 @@ __device__ int guided_start(const TxView& q, const TxView& t, const uint32_t* st
                 const orfx_seg ts = t.segs[tj];
                 if (ts.start > en) break;
                 const int pos5 = max(s, ts.start);
-                const uint32_t q_tpos = (uint32_t)(vcum(q, qi) + (pos5 - qs.start) - far);
+                const uint32_t q_tpos = (uint32_t)(vcum(q, qi) + (pos5 - qs.start) - base);
                 const uint32_t t_tpos = (uint32_t)(t.cum[tj] + (pos5 - ts.start));
                 seen = true; Q = q_tpos;
                 if (t_tpos % 3 == q_tpos % 3) { done = true; break; }
@@ -382,7 +440,7 @@ __device__ int guided_start(const TxView& q, const TxView& t, const uint32_t* st
                 const orfx_seg ts = t.segs[tj];
                 if (ts.end < s) break;
                 const int pos5 = min(en, ts.end);
-                const uint32_t q_tpos = (uint32_t)(q.L - 1 - (vcum(q, qi) + (pos5 - qs.start)) - far);
+                const uint32_t q_tpos = (uint32_t)(q.L - 1 - (vcum(q, qi) + (pos5 - qs.start)) - base);
                 const uint32_t t_tpos = (uint32_t)(t.L - 1 - (t.cum[tj] + (pos5 - ts.start)));
                 seen = true; Q = q_tpos;
                 if (t_tpos % 3 == q_tpos % 3) { done = true; break; }
@@ -658,9 +716,20 @@ __device__ void process_row(const DevBatch& B, const DevRows& R, const orfx_para
     const int t_cds_start = B.tx_cds_start[tx], t_cds_end = B.tx_cds_end[tx];
     const int t5 = plus ? t_cds_start : t_cds_end;
     int start = 0, e = 0;   // final ORF, transcript coordinates
+    // Strand '.': the reference reads such a transcript as reverse-strand sequence, but TX::extend_cds_chain is told
+    // `strand == '-'` (Transcriptome.cpp:487, 566), so every 5' extension of the CDS chain lands on its 3' end instead:
+    // the chain keeps its start and grows downstream by the same number of bases (CHAIN::extend, h:365-397, stops at the
+    // end of the exon chain).  Reproduced as written; `sq_*` is what SEQ (get_aa) holds when that differs from the chain.
+    const bool dot = !plus && B.tx_strand[qx] != '-';
+    int sq_start = -1, sq_e = -1;
     // --overhang: the masks cover [5' flank][transcript][3' flank]; transcript position p is mask bit p + o
     int E5 = 0, E3 = 0;
-    if (B.tx_ext_lo) { const int lo = B.tx_ext_lo[qx], hi = B.tx_ext_hi[qx]; E5 = plus ? lo : hi; E3 = plus ? hi : lo; }
+    bool virt3 = false;   // the one-base 3' flank re-reads the edge base of the chromosome (ORFX_EXT_*_VIRTUAL)
+    if (B.tx_ext_lo) {
+        const int lo = B.tx_ext_lo[qx], hi = B.tx_ext_hi[qx]; E5 = plus ? lo : hi; E3 = plus ? hi : lo;
+        if (B.tx_ext_flags) virt3 = (B.tx_ext_flags[qx] & (plus ? ORFX_EXT_HI_VIRTUAL : ORFX_EXT_LO_VIRTUAL)) != 0;
+    }
+    bool stop_in_virtual = false;
     int o = E5;
     const uint32_t* stopm = nullptr;
     const uint32_t* startm = nullptr;
@@ -707,6 +776,9 @@ __device__ void process_row(const DevBatch& B, const DevRows& R, const orfx_para
             if (has_stop && P.overhang > 0) {   // stop inside the flank: the terminal exon grows up to it (cpp:418-429)
                 const int g3 = max(p0 + 2 - q.L + 1, 0);
                 if (g3 > 0) tx_grow(q, plus ? 0 : g3, plus ? g3 : 0);
+                // ... but a base past the end of the chromosome is not there when the sequence is loaded again (cpp:437,
+                // Bundle::get_nts): the last codon comes back incomplete, '\0', and the row ends as "missing_stop"
+                stop_in_virtual = g3 > 0 && virt3;
             }
             // extend_to_start(TX*, non_aug) (Transcriptome.cpp:496-620)
             const bool m_at_a = mbit(startm, a);
@@ -723,7 +795,10 @@ __device__ void process_row(const DevBatch& B, const DevRows& R, const orfx_para
                         if (i < ref) break;
                         if (i < 3) break;
                     }
-                    if (!stop_between) { if (ref < a) start = ref; found_start = true; }
+                    if (!stop_between) {
+                        if (ref < a) { if (dot) e = min(e + (a - ref), q.L - 1); else start = ref; }
+                        found_start = true;
+                    }
                 }
             }
             if (!found_start) {
@@ -733,8 +808,18 @@ __device__ void process_row(const DevBatch& B, const DevRows& R, const orfx_para
                 int far = nxt(startm, lb, a + 1);
                 if (far >= 0) {
                     const int ref = g2t(q, t5);
-                    if (ref >= lb && ref <= a && ref % 3 == a % 3 && mbit(startm, ref)) start = ref;
-                    else start = guided_start(q, t, startm, far, a, e, lb, o);
+                    if (ref >= lb && ref <= a && ref % 3 == a % 3 && mbit(startm, ref)) {
+                        if (dot) e = min(e + (a - ref), q.L - 1); else start = ref;
+                    } else if (!dot) start = guided_start(q, t, startm, far, far, a, e, lb, o);
+                    else {
+                        // strand '.': the chain [a, e] grows by a - far bases at its 3' end, is intersected with the template
+                        // from `a`, and loses tb - far bases at its 5' end (trim_to_pos, h:483-494: a start past the chain's
+                        // end lands on its last base); SEQ takes the chosen ATG as its start and keeps its end (cpp:611-613)
+                        const int e2 = min(e + (a - far), q.L - 1);
+                        const int tb = guided_start(q, t, startm, far, a, a, e2, lb, o);
+                        sq_start = tb; sq_e = e;
+                        start = min(a + (tb - far), e2); e = e2;
+                    }
                 } else searched = true;
             }
             // no upstream ATG: extend_to_start(-1, overhang, spliced) (cpp:446-492) walks on into the 5' flank — nearest
@@ -747,12 +832,13 @@ __device__ void process_row(const DevBatch& B, const DevRows& R, const orfx_para
                     // to the old 5' end (cpp:461-474); the flank may be shorter than --overhang
                     const int g5 = max(P.overhang - m5, 0);
                     tx_grow(q, plus ? g5 : 0, plus ? 0 : g5);
-                    start = m5 - o + g5; e += g5; o -= g5;
+                    if (dot) { start += g5; e = min(e + g5 + (start - g5 + o - m5), q.L - 1); o -= g5; }   // a + E5 - m5 bases, at the 3' end
+                    else { start = m5 - o + g5; e += g5; o -= g5; }
                 }
             }
             // adjust_start (Transcriptome.cpp:202-227) unless --non_aug kept the template's start
             const bool at_t5 = t2g(q, start) == t5;
-            if (!(P.non_aug && at_t5) && !mbit(startm, start)) {
+            if (sq_start < 0 && !(P.non_aug && at_t5) && !mbit(startm, start)) {   // (sq_start >= 0: SEQ starts with the chosen ATG)
                 const int m = nxt(startm, start, e - 1);
                 if (m >= 0 && m + 2 <= e) start = m;
             }
@@ -761,8 +847,12 @@ __device__ void process_row(const DevBatch& B, const DevRows& R, const orfx_para
         const int cs = min(gs, ge), ce = max(gs, ge);
         if (P.has_reference) {
             key_s = cs; key_e = ce;
-            const bool ends_in_stop = e >= 2 && mbit(stopm, e - 2) && ((e - 2 - start) % 3 == 0);
-            const bool front_m = mbit(startm, start);
+            // get_aa(): SEQ::translate of SEQ's own bounds -- the chain's, except after the strand '.' guided choice; the
+            // last amino acid is the last whole codon (a length that is no multiple of 3 only arises on strand '.')
+            const int s0 = sq_start >= 0 ? sq_start : start, e0 = sq_start >= 0 ? sq_e : e;
+            const int ncod = (e0 - s0 + 1) / 3;
+            const bool ends_in_stop = ncod >= 1 && mbit(stopm, s0 + 3 * (ncod - 1)) && !stop_in_virtual;
+            const bool front_m = mbit(startm, s0);
             const bool at_t5 = (plus ? cs : ce) == t5;
             if (!ends_in_stop) { status = ORFX_ST_MISSING_STOP; break; }
             if ((!P.non_aug && !front_m) || (P.non_aug && !front_m && !at_t5)) { status = ORFX_ST_MISSING_START; break; }
@@ -811,8 +901,8 @@ __global__ void __launch_bounds__(128, 8) rescue_score_kernel(DevBatch B, DevRow
 // heavy bundles: one CTA per bundle, the bundle's chains staged in shared memory
 // ------------------------------------------------------------------------------------------------
 constexpr int HB_THREADS = 512;   // x 2 CTAs per SM
-constexpr int HB_MAX_SEGS = 9216;     // segments of one bundle that fit the stage (8 B + 4 B each): 108 KB, two CTAs per SM
-constexpr int HB_MAX_PAIRS = 8192;    // (query, transcript slot) pairs whose row counts fit the stage
+// HB_MAX_SEGS / HB_MAX_PAIRS (orfx_device.cuh): segments of one bundle that fit the stage (8 B + 4 B each: 108 KB, two CTAs
+// per SM) and (query, transcript slot) pairs whose row counts fit it
 
 namespace {
 struct HeavyBundle {
@@ -828,7 +918,7 @@ __device__ HeavyBundle hb_load(const DevBatch& B, int b, orfx_seg* s_seg, int32_
     H.x0 = B.bundle_tx_off[b]; H.x1 = B.bundle_tx_off[b + 1]; H.ntx = H.x1 - H.x0;
     H.qbase = (int)B.tx_q_off[H.x0]; H.nq = (int)B.tx_q_off[H.x1] - H.qbase;
     H.seg_lo = B.tx_seg_off[H.x0]; H.ns = B.tx_seg_off[H.x1] - H.seg_lo;
-    H.staged = H.ns <= HB_MAX_SEGS;
+    H.staged = H.ns <= B.hb_max_segs;   // HB_MAX_SEGS unless a test lowered it (orfx_debug_set)
     if (H.staged) {
         for (int i = threadIdx.x; i < H.ns; i += blockDim.x) {
             s_seg[i] = B.segs[H.seg_lo + i];
@@ -953,7 +1043,7 @@ __global__ void __launch_bounds__(HB_THREADS, 2) heavy_count_kernel(DevBatch B, 
 __global__ void __launch_bounds__(HB_THREADS, 2) heavy_fill_kernel(DevBatch B, DevRows R, const int32_t* heavy_list, const unsigned* heavy_count) {
     extern __shared__ __align__(16) unsigned char hb_smem[];
     orfx_seg* s_seg = reinterpret_cast<orfx_seg*>(hb_smem);
-    uint16_t* s_n = reinterpret_cast<uint16_t*>(hb_smem + (size_t)HB_MAX_SEGS * sizeof(orfx_seg));
+    int32_t* s_n = reinterpret_cast<int32_t*>(hb_smem + (size_t)HB_MAX_SEGS * sizeof(orfx_seg));   // rows of a pair: not bounded by 65 535 when the chains are walked in global memory
     const unsigned n = heavy_count[1];
     const int4* work = heavy_work(B, heavy_list);
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = blockDim.x >> 5;
@@ -963,14 +1053,14 @@ __global__ void __launch_bounds__(HB_THREADS, 2) heavy_fill_kernel(DevBatch B, D
         const HeavyBundle H = hb_load(B, item.x, s_seg, nullptr, false);
         const int nq_slice = (H.nq - k + HB_SLICES - 1) / HB_SLICES;
         const int64_t npairs = (int64_t)nq_slice * H.ntx;
-        if (npairs <= HB_MAX_PAIRS) {
+        if (npairs <= B.hb_max_pairs) {
             // rows of every pair, then each pair fills at (rows of the query's earlier pairs)
             for (int p = warp; p < (int)npairs; p += nwarps) {
                 const int ql = k + HB_SLICES * (p / H.ntx), t = H.x0 + p % H.ntx;
                 const int qx = B.q_list[H.qbase + ql];
                 const int qstart = H.segs[B.tx_seg_off[qx]].start, qend = H.segs[B.tx_seg_off[qx + 1] - 1].end;
                 const int r = pair_live(B, t, H.x1, qstart, qend) ? pair_rows_warp<false>(B, H.segs, R, qx, t, 0, lane) : 0;
-                if (lane == 0) s_n[p] = (uint16_t)r;
+                if (lane == 0) s_n[p] = r;
             }
             __syncthreads();
             for (int p = warp; p < (int)npairs; p += nwarps) {
@@ -1015,7 +1105,7 @@ __global__ void __launch_bounds__(HB_THREADS, 2) heavy_rescue_kernel(DevBatch B,
     }
 }
 
-constexpr size_t HB_SMEM_PAIRS = (size_t)HB_MAX_SEGS * sizeof(orfx_seg) + (size_t)HB_MAX_PAIRS * sizeof(uint16_t);   // segments + row counts
+constexpr size_t HB_SMEM_PAIRS = (size_t)HB_MAX_SEGS * sizeof(orfx_seg) + (size_t)HB_MAX_PAIRS * sizeof(int32_t);    // segments + row counts
 constexpr size_t HB_SMEM_ROWS = (size_t)HB_MAX_SEGS * (sizeof(orfx_seg) + sizeof(int32_t));                          // segments + prefixes
 
 int launch_heavy_count(const DevBatch& B, int64_t* cnt, const int32_t* heavy_list, const unsigned* heavy_count, int n_sm, cudaStream_t s) {
@@ -1071,7 +1161,12 @@ __global__ void __launch_bounds__(128) clean_templates_kernel(DevBatch B, int n_
         // --overhang: the masks cover [5' flank][transcript][3' flank]; transcript position p is mask bit p + o.  Only the
         // CDS bounds leave this kernel, and t2g extrapolates past the terminal exons, so the chain itself is not grown.
         int o = 0, E3 = 0;
-        if (B.tx_ext_lo) { const int lo = B.tx_ext_lo[qx], hi = B.tx_ext_hi[qx]; o = q.plus ? lo : hi; E3 = q.plus ? hi : lo; }
+        bool virt3 = false;
+        if (B.tx_ext_lo) {
+            const int lo = B.tx_ext_lo[qx], hi = B.tx_ext_hi[qx]; o = q.plus ? lo : hi; E3 = q.plus ? hi : lo;
+            if (B.tx_ext_flags) virt3 = (B.tx_ext_flags[qx] & (q.plus ? ORFX_EXT_HI_VIRTUAL : ORFX_EXT_LO_VIRTUAL)) != 0;
+        }
+        const bool dot = !q.plus && B.tx_strand[qx] != '-';      // see process_row: 5' extensions of the chain land on its 3' end
         int start = a, e = b;
         if (b - a + 1 < 3) break;                              // rescue_cds: cds_nt_len < 3; no rescue: no codon to test
         if (rescue) {
@@ -1079,10 +1174,14 @@ __global__ void __launch_bounds__(128) clean_templates_kernel(DevBatch B, int n_
             if (p0 >= 0) p0 -= o;
             if (p0 == a) break;                                // nothing left before the first stop: CDS removed
             if (p0 >= 0) e = p0 + 2;
+            if (virt3 && e >= q.L) break;                      // the stop needs a base past the chromosome's end: it is gone after the reload
+            int Lg = max(q.L, e + 1);                          // exon chain after the growth towards the stop (cpp:418-429)
             if (!non_aug && !mask_bit(startm, a + o) && a - 3 + o >= 0) {  // extend_to_start(-1, ...): nearest upstream ATG before a stop, 5' flank included
                 const int prev_stop = prev_inframe(stopm, a - 3 + o);
                 const int m = prev_inframe(startm, a - 3 + o);
-                if (m >= 0 && m > prev_stop) start = m - o;
+                if (m >= 0 && m > prev_stop) {
+                    if (dot) e = min(e + (a - (m - o)), Lg - 1); else start = m - o;
+                }
             }
             if (!mask_bit(startm, start + o)) {                // adjust_start: first ATG inside the CDS
                 int m = next_inframe(startm, start + o, e - 1 + o);

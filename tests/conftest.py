@@ -36,15 +36,16 @@ _SYNTH_CACHE = {}
 
 
 def synth_dir(tmp_root, seed, loci=60, chroms=2, chrom_len=3000000, queries=6, templates=3, template_files=1, lower=0.3,
-              iupac=0.0005, titin=0.02):
-    key = (seed, loci, chroms, chrom_len, queries, templates, template_files, lower, iupac, titin)
+              iupac=0.0005, titin=0.02, dot=0.0, edge=False):
+    key = (seed, loci, chroms, chrom_len, queries, templates, template_files, lower, iupac, titin, dot, edge)
     if key in _SYNTH_CACHE:
         return _SYNTH_CACHE[key]
     d = os.path.join(str(tmp_root), "synth_%d_%d_%d_%d" % (seed, loci, template_files, len(_SYNTH_CACHE)))
     os.makedirs(d, exist_ok=True)
     subprocess.run([SYNTH, "--out", d, "--seed", str(seed), "--loci", str(loci), "--chroms", str(chroms), "--chrom-len",
                     str(chrom_len), "--queries", str(queries), "--templates", str(templates), "--template-files",
-                    str(template_files), "--lower-frac", str(lower), "--iupac-rate", str(iupac), "--titin-frac", str(titin)],
+                    str(template_files), "--lower-frac", str(lower), "--iupac-rate", str(iupac), "--titin-frac", str(titin)]
+                   + (["--dot-frac", str(dot)] if dot else []) + (["--edge-loci"] if edge else []),
                    check=True, stderr=subprocess.DEVNULL)
     _SYNTH_CACHE[key] = d
     return d
@@ -149,3 +150,39 @@ def check_overhang_kat(binary, d, expected):
             got.setdefault(tid, {})[f[2]] = (int(f[3]), int(f[4]))
         for tid, (es, ee, cs, ce) in want.items():
             assert got[tid]["exon"] == (es, ee) and got[tid]["CDS"] == (cs, ce), (spliced, tid, got[tid])
+
+
+def write_edge_kat(d):
+    """A transcript that ends on the last base of its chromosome (TX::extend_seq, Transcriptome.cpp:348-364: the clamp
+    re-reads that base as a one-base 3' flank).  Exon 201-300 of a 300-base chromosome; ORF A, ATG at 203, runs to the end
+    and stops short at "TA": the repeated last base completes TAA, the exon and the CDS grow to 301, the re-loaded sequence
+    ends one base early (Bundle::get_nts, cpp:776-782) and the row ends as "missing_stop" keyed 203-301.  ORF B (213-224,
+    another frame) is complete and is what gets reported.  Returns the expected stats keys in print order."""
+    L = 300
+    g = ["C"] * L
+
+    def put(pos, s):
+        for i, ch in enumerate(s):
+            g[pos - 1 + i] = ch
+    put(203, "ATG" + "GCC" * 31 + "TA")
+    put(213, "ATGGCCGCCTAA")
+    open(os.path.join(d, "genome.fa"), "w").write(">chr1\n" + "".join(g) + "\n")
+
+    def tx(tid, s, e, cds=None):
+        attrs = 'transcript_id "%s"; gene_id "G1";' % tid
+        rows = ["chr1\tKAT\ttranscript\t%d\t%d\t.\t+\t.\t%s" % (s, e, attrs), "chr1\tKAT\texon\t%d\t%d\t.\t+\t.\t%s" % (s, e, attrs)]
+        if cds:
+            rows.append("chr1\tKAT\tCDS\t%d\t%d\t.\t+\t0\t%s" % (cds + (attrs,)))
+        return "\n".join(rows) + "\n"
+    open(os.path.join(d, "query.gtf"), "w").write(tx("Q1", 201, 300))
+    open(os.path.join(d, "template.gtf"), "w").write(tx("T1", 201, 300, (203, 298)) + tx("T2", 201, 300, (213, 224)))
+    return [("Q1.203-301", "T1", "missing_stop"), ("Q1.213-224", "T2", "best_gtf")]
+
+
+def check_edge_kat(binary, d, expected):
+    rc, gtf, tsv, err = run_cli(binary, d, ["--reference", "genome.fa", "--query", "query.gtf", "--overhang", "20", "--mode", "ALL"] +
+                                (["--threads", "1"] if binary == REF_BIN else []), "edge", ["template.gtf"])
+    assert rc == 0, err
+    rows = [tuple(l.split("\t")[i] for i in (0, 1, 3)) for l in tsv.decode().splitlines()[1:]]
+    assert rows == expected, rows
+    return gtf, tsv

@@ -164,6 +164,104 @@ def test_overhang_worked_examples_on_the_gpu(tmp_path):
     check_overhang_kat(ob.cli_path(), d, write_overhang_kat(d))
 
 
+@pytest.mark.parametrize("seed,overhang,spliced", [(71, 0, False), (72, 60, False), (73, 200, True)])
+def test_strand_dot_and_chromosome_edges_match_oracle(synth, oracle_lib, gpu, seed, overhang, spliced):
+    """Strand '.' loci (both flanks from the low side, 5' CDS extensions landing on the chain's 3' end -- Transcriptome.cpp:348-364,
+    487, 566 as written) and transcripts that touch an end of their chromosome (ORFX_EXT_*_VIRTUAL): rows, winners, exon growth
+    and template cleaning against the oracle, which test_oracle.py pins to the reference binary on the same loci."""
+    from test_oracle import dot_edge_dir
+    d = dot_edge_dir(synth, seed)
+    w = ob.Workload(os.path.join(d, "query.gtf"), template_files(d), os.path.join(d, "genome.fa"), overhang=overhang, spliced_overhang=spliced)
+    batch = w.pack(layout="islands4")
+    a = batch.arrays
+    dots = (a["tx_kind"] == 0) & (a["tx_strand"] == ord("."))
+    assert dots.sum() > 100
+    if overhang:
+        assert (a["tx_ext_hi"][dots] > 0).any() and a["tx_ext_flags"].any()
+    for pk in (dict(mode="LONGEST_MATCH,BEST"), dict(mode="ALL", non_aug=True), dict(mode="BEST", lpi=50, ilpi=60, mlpi=70, minlen=300)):
+        params = ob.Params.make(overhang=overhang, spliced_overhang=spliced, **pk)
+        gpu.set_params(params)
+        got = gpu.run(batch)
+        with ob.Context(params, lib=oracle_lib, prefix="orfx_oracle_") as ox:
+            want = ox.run(batch)
+        assert_same_results(got, want, "strand '.', seed %d overhang %d %s" % (seed, overhang, pk))
+    dot_rows = np.isin(want.rows["q_tx"], np.nonzero(dots)[0])
+    assert (want.rows["pass"][dot_rows] == 1).any() and (want.rows["status"][dot_rows] == 5).any()   # some pass, some end without their stop
+    cb = cleaning_batch(batch, got.best, np.random.default_rng(seed))
+    for non_aug in (False, True):
+        p = ob.Params.make(mode="BEST", non_aug=non_aug, overhang=overhang, spliced_overhang=spliced)
+        gpu.set_params(p)
+        got_c = gpu.clean(cb, True)
+        with ob.Context(p, lib=oracle_lib, prefix="orfx_oracle_") as ox:
+            want_c = ox.clean(cb, True)
+        for g, x, name in zip(got_c, want_c, ("keep", "cds_start", "cds_end")):
+            assert (g == x).all(), (seed, non_aug, name, int((g != x).sum()))
+    if overhang:   # the whole-window layout cannot hold a strand '.' transcript's 5' flank: refused, not approximated
+        with pytest.raises(ob.OrfxError):
+            w.pack(layout="windows")
+    gpu.set_params(ob.Params.make())
+    w.close()
+
+
+@pytest.mark.skipif(not os.path.exists(REF_BIN), reason="oracle/_ref/orfanage_ref not shipped")
+def test_cli_byte_identical_to_reference_on_strand_dot_and_edges(synth, tmp_path):
+    from conftest import check_edge_kat, write_edge_kat
+    from test_oracle import DOT_EDGE_GRID, dot_edge_dir
+    d = dot_edge_dir(synth, 71)
+    for args in DOT_EDGE_GRID:
+        compare_clis(ob.cli_path(), d, args)
+    k = str(tmp_path)
+    expected = write_edge_kat(k)
+    assert check_edge_kat(ob.cli_path(), k, expected) == check_edge_kat(REF_BIN, k, expected)
+
+
+def test_heavy_bundle_global_memory_branches_match_oracle(synth, oracle_lib):
+    """The heavy-bundle kernels stage a titin-class bundle's chains and per-pair row counts in shared memory while they fit
+    (9 216 segments / 8 192 pairs) and walk global memory above that.  orfx_debug_set lowers the two capacities so that
+    ordinary titin-class test loci take the global-memory branches (pipeline.cu: hb_load, heavy_fill_kernel); results
+    must not change."""
+    d = synth(22, loci=60, titin=0.15, iupac=0.002)
+    w = ob.Workload(os.path.join(d, "query.gtf"), template_files(d), os.path.join(d, "genome.fa"))
+    batch = w.pack(layout="islands4")
+    a = batch.arrays
+    per_tx = np.diff(a["tx_seg_off"])
+    assert (per_tx > 32).sum() > 20     # heavy bundles are present
+    for pk in (dict(mode="LONGEST_MATCH,BEST"), dict(mode="ALL"), dict(mode="BEST", has_reference=False)):
+        params = ob.Params.make(**pk)
+        with ob.Context(params, lib=oracle_lib, prefix="orfx_oracle_") as ox:
+            want = ox.run(batch)
+        for segs, pairs in ((9216, 8192), (64, 8192), (9216, 8), (0, 0)):
+            with ob.Context(params, device=0) as cx:
+                cx.debug_set("hb_max_segs", segs)
+                cx.debug_set("hb_max_pairs", pairs)
+                assert_same_results(cx.run(batch), want, "hb_max_segs %d hb_max_pairs %d %s" % (segs, pairs, pk))
+    w.close()
+
+
+def test_malformed_batches_are_refused(gpu):
+    """include/orfx.h is a public seam: a batch that breaks what the kernels rely on is answered with ORFX_E_INVALID,
+    not walked (validate_batch_kernel)."""
+    seq = np.frombuffer(b"ACGTACGTATGAAATAGACGT" * 5, dtype=np.uint8)
+    good = dict(seq=seq, seq_off=[0, len(seq)], bundle_start=[100], bundle_tx_off=[0, 2], tx_kind=[1, 0], tx_strand=[ord("+")] * 2,
+                tx_seg_off=[0, 1, 3], tx_cds_start=[150, 0], tx_cds_end=[170, 0], tx_tid_class=[0, 1],
+                segs=[[150, 170], [101, 120], [140, 180]], seg_phase=[0, 0, 0])
+    gpu.set_params(ob.Params.make(mode="BEST"))
+    assert gpu.run(ob.Batch(**good)).n_queries == 1
+    bad = [dict(tx_seg_off=[0, 2, 1]),                       # offsets not monotone
+           dict(tx_seg_off=[0, 1, 1]),                       # a query without a segment
+           dict(segs=[[150, 170], [120, 101], [140, 180]]),  # end < start
+           dict(segs=[[150, 170], [140, 180], [101, 120]]),  # chain not ascending
+           dict(tx_kind=[1, 7]),                             # unknown kind
+           dict(bundle_tx_off=[0, 3]),                       # more transcripts than the batch has
+           dict(segs=[[150, 170], [101, 120], [140, 280]]),  # exon outside the window's bases
+           dict(seq_off=[0, len(seq) + 50])]                 # more bases than were given
+    for patch in bad:
+        with pytest.raises(ob.OrfxError) as e:
+            gpu.run(ob.Batch(**dict(good, **patch)))
+        assert e.value.code == -1, patch
+    assert gpu.run(ob.Batch(**good)).n_queries == 1         # the context is still usable
+
+
 def test_config1_golden_batch(gpu):
     """Config 1 (example/query.gtf x example/template.gtf, random chr19, --mode BEST): committed packed
     batch -> CUDA path -> the reference's own stats rows."""

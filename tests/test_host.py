@@ -25,7 +25,7 @@ def test_device_library_exports_every_declared_symbol():
     for n in names:
         assert hasattr(lib, n), "liborfx.so does not export %s" % n
     ob.load_device_library()
-    assert lib.orfx_abi_version() == 5
+    assert lib.orfx_abi_version() == 6
 
 
 def test_host_library_exports_every_declared_symbol():

@@ -99,6 +99,45 @@ def test_overhang_worked_examples(tmp_path):
             check_overhang_kat(REF_BIN, d, expected)
 
 
+DOT_EDGE_GRID = [
+    ["--reference", "genome.fa", "--query", "query.gtf"],
+    ["--reference", "genome.fa", "--query", "query.gtf", "--mode", "ALL", "--non_aug"],
+    ["--reference", "genome.fa", "--query", "query.gtf", "--cleant", "--rescue", "--mode", "LONGEST_MATCH,BEST"],
+    ["--reference", "genome.fa", "--query", "query.gtf", "--overhang", "30"],
+    ["--reference", "genome.fa", "--query", "query.gtf", "--overhang", "300", "--mode", "ALL"],
+    ["--reference", "genome.fa", "--query", "query.gtf", "--overhang", "90", "--spliced_overhang", "--mode", "BEST"],
+    ["--reference", "genome.fa", "--query", "query.gtf", "--overhang", "2000", "--spliced_overhang", "--non_aug", "--mode", "LONGEST"],
+    ["--reference", "genome.fa", "--query", "query.gtf", "--overhang", "40", "--cleant", "--rescue", "--spliced_overhang", "--mode", "ALL"],
+]
+
+
+def dot_edge_dir(synth, seed):
+    """Loci written with strand '.' (read as reverse-strand sequence, with the reference's `strand == '-'` / `strand == '+'`
+    asymmetries: both --overhang flanks from the low side, 5' CDS extensions landing on the 3' end) and loci whose main
+    isoform touches the first / last base of its chromosome (one-base flank that re-reads the edge base)."""
+    return synth(seed, loci=120, chroms=6, chrom_len=800000, queries=8, templates=3, template_files=2, dot=0.3, edge=True)
+
+
+@needs_ref_bin
+@pytest.mark.parametrize("seed", [71, 72])
+def test_oracle_cli_matches_reference_on_strand_dot_and_chromosome_edges(synth, seed):
+    d = dot_edge_dir(synth, seed)
+    strands = {l.split("\t")[6] for l in open(os.path.join(d, "query.gtf")) if "\ttranscript\t" in l}
+    assert strands == {"+", "-", "."}
+    for args in DOT_EDGE_GRID:
+        compare_clis(ORACLE_CLI, d, args)
+
+
+def test_chromosome_edge_worked_example(tmp_path):
+    """The one-base flank of a transcript that ends on its chromosome's last base, by hand (conftest.write_edge_kat)."""
+    from conftest import check_edge_kat, write_edge_kat
+    d = str(tmp_path)
+    expected = write_edge_kat(d)
+    got = check_edge_kat(ORACLE_CLI, d, expected)
+    if os.path.exists(REF_BIN):
+        assert check_edge_kat(REF_BIN, d, expected) == got
+
+
 def test_config1_oracle_library_matches_reference_rows(oracle_lib):
     batch = ob.Batch.load(os.path.join(GOLDEN, "c1_batch.npz"))
     names = json.load(open(os.path.join(GOLDEN, "c1_names.json")))["tx_id"]

@@ -10,7 +10,7 @@
 // usage: orfx_synth --out DIR [--seed S] [--chroms N] [--chrom-len L] [--loci N]
 //                   [--queries Q] [--templates T] [--template-files F] [--titin-frac X]
 //                   [--lower-frac X] [--iupac-rate X] [--no-genome] [--line-width W]
-//                   [--chrom-offset K]
+//                   [--chrom-offset K] [--dot-frac X] [--edge-loci]
 #include <cstdio>
 #include <cstdlib>
 #include <cstdint>
@@ -56,7 +56,7 @@ struct Opts {
     std::string out=".";
     uint64_t seed=1;
     int chroms=1; int64_t chrom_len=2000000; int loci=20; int queries=10; int templates=2; int tfiles=1;
-    double titin=0.01, lower=0.0, iupac=0.0; bool genome=true; int width=80; int chrom_offset=0;
+    double titin=0.01, lower=0.0, iupac=0.0, dot=0.0; bool genome=true, edge=false; int width=80; int chrom_offset=0;
     int64_t spacing=0;
 };
 
@@ -126,6 +126,7 @@ int main(int argc,char** argv){
         else if(a=="--templates") o.templates=atoi(val().c_str()); else if(a=="--template-files") o.tfiles=atoi(val().c_str());
         else if(a=="--titin-frac") o.titin=atof(val().c_str()); else if(a=="--lower-frac") o.lower=atof(val().c_str());
         else if(a=="--iupac-rate") o.iupac=atof(val().c_str()); else if(a=="--no-genome") o.genome=false;
+        else if(a=="--dot-frac") o.dot=atof(val().c_str()); else if(a=="--edge-loci") o.edge=true;
         else if(a=="--line-width") o.width=atoi(val().c_str()); else if(a=="--chrom-offset") o.chrom_offset=atoi(val().c_str());
         else { fprintf(stderr,"unknown option %s\n",a.c_str()); return 2; }
     }
@@ -156,6 +157,10 @@ int main(int argc,char** argv){
         for(int li=0;li<nl;li++,locus_id++){
             bool titin=lr.chance(o.titin);
             char strand=lr.chance(0.5)?'+':'-';
+            // --dot-frac: the locus is written with strand '.' (the reference reads such transcripts as reverse-strand
+            // sequence); drawn only when asked for, so that existing seeds keep their streams
+            const bool dot=o.dot>0 && lr.chance(o.dot);
+            if(dot) strand='-';
             int nex=titin?(int)lr.range(100,360):(int)lr.range(4,14);
             int64_t budget=spacing-2000;      // locus must fit its slot
             // exon/intron lengths
@@ -174,6 +179,9 @@ int main(int argc,char** argv){
                 continue;
             }
             int64_t start=slot_lo+lr.range(0,std::max<int64_t>(0,(slot_hi-slot_lo)-span-10));
+            // --edge-loci: the first locus of a chromosome starts at its first base, the last one ends at its last base
+            if(o.edge && li==0) start=1;
+            else if(o.edge && li==nl-1) start=o.chrom_len-span+1;
             Chain ex(nex); int64_t p=start;
             for(int i=0;i<nex;i++){ ex[i].s=p; ex[i].e=p+el[i]-1; p+=el[i]; if(i<nex-1) p+=il[i]; }
             int64_t L=chain_len(ex);
@@ -233,7 +241,7 @@ int main(int argc,char** argv){
                     std::vector<int> ph=gtf_phases(cds,strand,lead);
                     std::string tid=std::string(SRC[fi%3])+"."+gid+".T"+std::to_string(k+1);
                     std::string extra=" gene_name \"N"+std::to_string(locus_id+1)+"\"; Tag \"v"+std::to_string(variant)+"\";";
-                    emit_tx(ft[fi],chr,SRC[fi%3],tid,gid,strand,tex,&cds,&ph,extra);
+                    emit_tx(ft[fi],chr,SRC[fi%3],tid,gid,dot?'.':strand,tex,&cds,&ph,extra);
                     n_t++;
                 }
             }
@@ -244,7 +252,7 @@ int main(int argc,char** argv){
                     Chain qex= k==0? ex : mutate_isoform(lr,ex,slot_lo,slot_hi);
                     std::string tid=gid+".Q"+std::to_string(k+1);
                     std::string extra=" gene_name \"N"+std::to_string(locus_id+1)+"\"; sample_count \""+std::to_string((int)lr.range(1,900))+"\";";
-                    emit_tx(fq,chr,"StringTie",tid,gid,strand,qex,nullptr,nullptr,extra);
+                    emit_tx(fq,chr,"StringTie",tid,gid,dot?'.':strand,qex,nullptr,nullptr,extra);
                     n_q++;
                 }
             }
