@@ -15,6 +15,7 @@
 // 32*CPL columns are processed in stripes; the right edge of a stripe (2 int32 per target row) goes
 // through a per-warp scratch in global memory, read and written 32 rows at a time, coalesced.
 #include "orfx_device.cuh"
+#include "orfx_buffers.cuh"
 #include <algorithm>
 #include <numeric>
 #include <string>
@@ -89,8 +90,14 @@ constexpr int PAD_SCORE8 = -128;    // score of the virtual columns right of the
 //   x = d + s; h = max3(x, E, F); E' = max(E - e, h - (q+e)); F' = max(F - e, h - (q+e))      (4 ALU + 1 FMA per cell)
 // Steps go in blocks of 32; blocks in which every lane has a row run without per-step range checks.
 // LAST: the stripe holding column qlen-1 (tracks mqe / score, writes no right edge).
+// A protein as the kernels read it: residue i is p[i * stride] (stride 1: caller-supplied proteins; stride 3: the codons of one
+// reading frame in the per-position translation of a transcript, translate.cu).
+struct Res {
+    const uint8_t* p; int stride;
+    __device__ __forceinline__ int operator[](int i) const { return min((int)p[(long long)i * stride], 23); }
+};
 template <int CPL, bool PIPE, bool LAST>
-__device__ __forceinline__ void dp_stripe(const int* __restrict__ s_mat, WarpSmem& ws, const uint8_t* __restrict__ q, const uint8_t* __restrict__ t,
+__device__ __forceinline__ void dp_stripe(const int* __restrict__ s_mat, WarpSmem& ws, const Res q, const Res t,
                                           int qlen, int tlen, int c_base, int gapoe, int gape, const StripeIO& io, AlnAcc& acc, int lane) {
     static_assert(CPL <= 8, "a profile entry holds 8 scores");
     const int c0 = c_base + lane * CPL;
@@ -101,7 +108,7 @@ __device__ __forceinline__ void dp_stripe(const int* __restrict__ s_mat, WarpSme
 #pragma unroll
         for (int k = 0; k < CPL; k++) {
             const int c = c0 + k;
-            qcode[k] = c < qlen ? min((int)q[c], 23) : -1;
+            qcode[k] = c < qlen ? q[c] : -1;
             hp[k] = -(gapoe + gape * c);                 // H(-1, c)
             ee[k] = -(gapoe + gapoe + gape * c);         // E(0, c)
         }
@@ -115,7 +122,7 @@ __device__ __forceinline__ void dp_stripe(const int* __restrict__ s_mat, WarpSme
             }
             ws.prof[r][lane] = make_uint2(lo, hi);
         }
-        ws.t_ring[lane] = lane < tlen ? min((int)t[lane], 23) : 0;   // rows 0..31; every block loads the chunk after its own
+        ws.t_ring[lane] = lane < tlen ? t[lane] : 0;   // rows 0..31; every block loads the chunk after its own
     }
     // lane-local column of qlen-1 (last stripe only)
     const int jq_lane = (qlen - 1 - c_base) / CPL, jq = (qlen - 1 - c_base) % CPL;
@@ -181,7 +188,7 @@ __device__ __forceinline__ void dp_stripe(const int* __restrict__ s_mat, WarpSme
                 e.y = r < tlen ? __ldcg(io.f_in + r) : 0;
             }
             __syncwarp();   // every lane is done with the rings' previous contents
-            ws.t_ring[(r + 32) & 127] = r + 32 < tlen ? min((int)t[r + 32], 23) : 0;
+            ws.t_ring[(r + 32) & 127] = r + 32 < tlen ? t[r + 32] : 0;
             ws.in_ring[lane] = e;
             __syncwarp();
             if (s0 == 0 && lane == 0) sc = ws.prof[ws.t_ring[0]][0];
@@ -225,7 +232,7 @@ __device__ __forceinline__ void acc_reduce_warp(AlnAcc& a) {
 // a whole pair on one warp, stripe after stripe (edges through the warp's global scratch): full stripes of 256
 // columns, then the remainder with the narrowest lane width that covers it (64 / 128 / 256 columns), so that a
 // 300-residue query costs 320 columns of work, not 512
-__device__ __forceinline__ void pair_on_warp(const int* s_mat, WarpSmem& ws, const uint8_t* q, const uint8_t* t, int qlen, int tlen, int gapoe, int gape,
+__device__ __forceinline__ void pair_on_warp(const int* s_mat, WarpSmem& ws, const Res q, const Res t, int qlen, int tlen, int gapoe, int gape,
                                              int32_t* hb, int32_t* fb, AlnAcc& acc, int lane) {
     for (int c_base = 0; c_base < qlen; c_base += 256) {
         const int rem = qlen - c_base;
@@ -249,8 +256,8 @@ constexpr int LONG_CPL = 8;
 // global buffers per CTA (stripe parity), handed over with shared-memory progress counters.  Phase B: every warp
 // takes the remaining pairs on its own from a second counter.
 __global__ void __launch_bounds__(ALN_WARPS * 32, 1)
-align_kernel(const uint8_t* __restrict__ aa, const int64_t* __restrict__ off, const int32_t* __restrict__ pair_q,
-             const int32_t* __restrict__ pair_t, const int32_t* __restrict__ order, long long n_pairs, long long n_long, int gapo, int gape,
+align_kernel(const uint8_t* __restrict__ aa, int q_stride, int t_stride, const AlnPair* __restrict__ pairs,
+             const int32_t* __restrict__ order, long long n_pairs, long long n_long, int gapo, int gape,
              int32_t* __restrict__ out_max, int32_t* __restrict__ out_score, int32_t* __restrict__ out_mqe, int32_t* __restrict__ out_mte,
              int32_t* __restrict__ scratch, long long scratch_stride, int32_t* __restrict__ cta_scratch, long long cta_stride,
              unsigned long long* counters) {
@@ -293,10 +300,9 @@ align_kernel(const uint8_t* __restrict__ aa, const int64_t* __restrict__ off, co
         const unsigned long long slot = *(volatile unsigned long long*)&s_slot_ring[k & 7];
         if (slot >= (unsigned long long)n_long) break;
         const int pair = order[slot];
-        const int qi = pair_q[pair], ti = pair_t[pair];
-        const uint8_t* q = aa + off[qi];
-        const uint8_t* t = aa + off[ti];
-        const int qlen = (int)(off[qi + 1] - off[qi]), tlen = (int)(off[ti + 1] - off[ti]);
+        const AlnPair pr = pairs[pair];
+        const Res q{aa + pr.q_off, q_stride}, t{aa + pr.t_off, t_stride};
+        const int qlen = pr.qlen, tlen = pr.tlen;
         const int n_stripes = (qlen + 32 * LONG_CPL - 1) / (32 * LONG_CPL);
         AlnAcc acc{0, NEG_INF, NEG_INF, NEG_INF};
         const unsigned long long per = (unsigned long long)tlen + 1ULL;
@@ -344,10 +350,9 @@ align_kernel(const uint8_t* __restrict__ aa, const int64_t* __restrict__ off, co
         slot = (unsigned long long)n_long + __shfl_sync(0xffffffffu, slot, 0);
         if (slot >= (unsigned long long)n_pairs) break;
         const int pair = order[slot];
-        const int qi = pair_q[pair], ti = pair_t[pair];
-        const uint8_t* q = aa + off[qi];
-        const uint8_t* t = aa + off[ti];
-        const int qlen = (int)(off[qi + 1] - off[qi]), tlen = (int)(off[ti + 1] - off[ti]);
+        const AlnPair pr = pairs[pair];
+        const Res q{aa + pr.q_off, q_stride}, t{aa + pr.t_off, t_stride};
+        const int qlen = pr.qlen, tlen = pr.tlen;
         if (qlen <= 0 || tlen <= 0) {
             if (lane == 0) { out_max[pair] = 0; out_score[pair] = NEG_INF; out_mqe[pair] = NEG_INF; out_mte[pair] = NEG_INF; }
             continue;
@@ -422,87 +427,159 @@ int int_alu_peak_device(cudaStream_t stream, double* ops, std::string& err) {
     return ORFX_OK;
 }
 
-int align_batch_device(int device, cudaStream_t stream, const uint8_t* aa, const int64_t* off, int64_t n_seq, const int32_t* pair_q,
+// ---- ordering and scheduling of the pairs, on the device ------------------------------------------------
+// Long pairs (>= 1024 x 256, >= 4 M cells: whole CTAs, phase A) first, then the rest; both by descending cost in
+// quarter-octave classes of qlen * tlen (a counting sort: the long tail starts early, no host-side std::sort).
+namespace {
+constexpr int ALN_NCLS = 128;                 // quarter octaves of the cell count, 2^0 .. 2^32
+constexpr int ALN_NBINS = 2 * ALN_NCLS;       // [long, descending cost][short, descending cost]
+struct AlnMeta { unsigned long long n_long, n_active, max_tlen, max_tlen_long; double cells; };
+
+__device__ __forceinline__ int cost_class(long long cells) {
+    if (cells <= 0) return 0;
+    const int lg = 63 - __clzll(cells);
+    const int frac = lg >= 2 ? (int)((cells >> (lg - 2)) & 3) : 0;
+    return min(ALN_NCLS - 1, lg * 4 + frac);
+}
+__global__ void __launch_bounds__(256) aln_pairs_from_index_kernel(const int64_t* __restrict__ off, const int32_t* __restrict__ pq, const int32_t* __restrict__ pt,
+                                                                  long long n, AlnPair* __restrict__ out) {
+    const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const int a = pq[i], b = pt[i];
+    AlnPair p;
+    p.q_off = off[a]; p.t_off = off[b]; p.qlen = (int)(off[a + 1] - off[a]); p.tlen = (int)(off[b + 1] - off[b]);
+    out[i] = p;
+}
+__global__ void __launch_bounds__(256) aln_classify_kernel(const AlnPair* __restrict__ pairs, long long n, uint16_t* __restrict__ cls, unsigned* __restrict__ hist,
+                                                          AlnMeta* meta) {
+    __shared__ unsigned s_hist[ALN_NBINS];
+    __shared__ double s_cells[8];
+    for (int i = threadIdx.x; i < ALN_NBINS; i += blockDim.x) s_hist[i] = 0;
+    __syncthreads();
+    const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    double cells = 0;
+    if (i < n) {
+        const AlnPair p = pairs[i];
+        int bin = 0xFFFF;
+        if (p.qlen >= 0) {
+            const long long c = (long long)p.qlen * (long long)max(p.tlen, 0);
+            cells = (double)c;
+            const bool is_long = p.qlen >= 1024 && p.tlen >= 256 && c >= 4194304LL;
+            bin = (is_long ? 0 : ALN_NCLS) + (ALN_NCLS - 1 - cost_class(c));
+            atomicAdd(&s_hist[bin], 1u);
+            if (is_long) atomicMax(&meta->max_tlen_long, (unsigned long long)p.tlen);
+            else if (p.qlen > 64) atomicMax(&meta->max_tlen, (unsigned long long)max(p.tlen, 0));
+        }
+        cls[i] = (uint16_t)bin;
+    }
+#pragma unroll
+    for (int d = 16; d > 0; d >>= 1) cells += __shfl_xor_sync(0xffffffffu, cells, d);
+    if ((threadIdx.x & 31) == 0) s_cells[threadIdx.x >> 5] = cells;
+    __syncthreads();
+    if (threadIdx.x == 0) { double c = 0; for (int w = 0; w < 8; w++) c += s_cells[w]; if (c != 0) atomicAdd(&meta->cells, c); }
+    for (int b = threadIdx.x; b < ALN_NBINS; b += blockDim.x) if (s_hist[b]) atomicAdd(&hist[b], s_hist[b]);
+}
+// exclusive prefix of the bins (in place: hist becomes the scatter cursors); totals into meta
+__global__ void aln_scan_kernel(unsigned* hist, AlnMeta* meta) {
+    if (threadIdx.x != 0) return;
+    unsigned long long at = 0, n_long = 0;
+    for (int b = 0; b < ALN_NBINS; b++) { const unsigned v = hist[b]; hist[b] = (unsigned)at; at += v; if (b == ALN_NCLS - 1) n_long = at; }
+    meta->n_long = n_long; meta->n_active = at;
+}
+__global__ void __launch_bounds__(256) aln_scatter_kernel(const uint16_t* __restrict__ cls, long long n, unsigned* cursor, int32_t* __restrict__ order) {
+    const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const int bin = cls[i];
+    if (bin == 0xFFFF) return;
+    order[atomicAdd(&cursor[bin], 1u)] = (int32_t)i;
+}
+}  // namespace
+
+// Aligns the pairs described by d_pairs (device memory, n entries) over the residues at d_aa; results into the four device
+// arrays d_out[0..3] (max, score, mqe, mte), indexed like d_pairs.  Buffers come from `w` (grow-only).  One host round trip
+// (five numbers that size the stripe-edge scratch).  Returns the number of kernels launched in *n_launches.
+int align_pairs_device(AlnWork& w, cudaStream_t stream, int n_sm, const uint8_t* d_aa, int q_stride, int t_stride, const AlnPair* d_pairs, long long n,
+                       int gapo, int gape, int32_t* const d_out[4], double* cells, float* ms, int* n_launches, std::string& err) {
+    auto ck = [&](cudaError_t e, const char* what) { if (e != cudaSuccess) { err = std::string(what) + ": " + cudaGetErrorString(e); return false; } return true; };
+    if (n_launches) *n_launches = 0;
+    if (cells) *cells = 0;
+    if (ms) *ms = 0;
+    if (n <= 0) return ORFX_OK;
+    if (gapo < 0 || gape < 0 || gapo + gape > 64) { err = "gap costs outside this build's range (0 <= gapo + gape <= 64)"; return ORFX_E_UNSUPPORTED; }
+    if (n > 0x7FFFFFFFLL) { err = "more than 2^31 pairs in one call"; return ORFX_E_INVALID; }
+    if (!ck(w.cls.ensure((size_t)n * 2 + 16), "cudaMalloc cls") || !ck(w.order.ensure((size_t)n * 4 + 16), "cudaMalloc order") ||
+        !ck(w.hist.ensure(ALN_NBINS * 4), "cudaMalloc hist") || !ck(w.meta.ensure(sizeof(AlnMeta)), "cudaMalloc meta") ||
+        !ck(w.counters.ensure(16), "cudaMalloc counters") || !ck(w.h_meta.ensure(sizeof(AlnMeta)), "cudaMallocHost meta"))
+        return ORFX_E_CUDA;
+    cudaMemsetAsync(w.hist.p, 0, ALN_NBINS * 4, stream);
+    cudaMemsetAsync(w.meta.p, 0, sizeof(AlnMeta), stream);
+    cudaMemsetAsync(w.counters.p, 0, 16, stream);
+    const unsigned nblk = (unsigned)((n + 255) / 256);
+    aln_classify_kernel<<<nblk, 256, 0, stream>>>(d_pairs, n, w.cls.as<uint16_t>(), w.hist.as<unsigned>(), w.meta.as<AlnMeta>());
+    aln_scan_kernel<<<1, 32, 0, stream>>>(w.hist.as<unsigned>(), w.meta.as<AlnMeta>());
+    cudaMemcpyAsync(w.h_meta.p, w.meta.p, sizeof(AlnMeta), cudaMemcpyDeviceToHost, stream);
+    aln_scatter_kernel<<<nblk, 256, 0, stream>>>(w.cls.as<uint16_t>(), n, w.hist.as<unsigned>(), w.order.as<int32_t>());
+    if (!ck(cudaStreamSynchronize(stream), "alignment scheduling")) return ORFX_E_CUDA;
+    const AlnMeta m = *w.h_meta.as<AlnMeta>();
+    if (n_launches) *n_launches = 3;
+    if (cells) *cells = m.cells;
+    if (m.n_active == 0) return ORFX_OK;
+    const long long n_long = (long long)m.n_long, n_active = (long long)m.n_active;
+    int grid = n_sm;
+    const long long max_grid = std::max<long long>(n_long, (n_active - n_long + ALN_WARPS - 1) / ALN_WARPS);
+    if (grid > max_grid) grid = (int)std::max<long long>(1, max_grid);
+    const long long n_warps = (long long)grid * ALN_WARPS;
+    const long long stride = ((long long)std::max<unsigned long long>(m.max_tlen, 1) + 31) / 32 * 32;
+    const long long cta_stride = ((long long)std::max<unsigned long long>(m.max_tlen_long, 1) + 31) / 32 * 32;
+    if (!ck(w.scratch.ensure((size_t)(n_warps * 2 * stride) * 4 + 16), "cudaMalloc stripe scratch") ||
+        !ck(w.cta.ensure((size_t)((long long)grid * 8 * cta_stride) * 4 + 16), "cudaMalloc CTA scratch"))
+        return ORFX_E_CUDA;
+    cudaEvent_t e0 = nullptr, e1 = nullptr;
+    if (ms) { cudaEventCreate(&e0); cudaEventCreate(&e1); cudaEventRecord(e0, stream); }
+    cudaFuncSetAttribute(align_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(ALN_WARPS * sizeof(WarpSmem)));
+    align_kernel<<<grid, ALN_WARPS * 32, ALN_WARPS * sizeof(WarpSmem), stream>>>(d_aa, q_stride, t_stride, d_pairs, w.order.as<int32_t>(), n_active, n_long, gapo, gape,
+                                                                               d_out[0], d_out[1], d_out[2], d_out[3], w.scratch.as<int32_t>(), stride,
+                                                                               w.cta.as<int32_t>(), cta_stride, w.counters.as<unsigned long long>());
+    if (n_launches) *n_launches = 4;
+    if (ms) {
+        cudaEventRecord(e1, stream);
+        const bool ok = ck(cudaStreamSynchronize(stream), "alignment kernel");
+        if (ok) cudaEventElapsedTime(ms, e0, e1);
+        cudaEventDestroy(e0); cudaEventDestroy(e1);
+        if (!ok) return ORFX_E_CUDA;
+    }
+    if (!ck(cudaGetLastError(), "alignment kernel launch")) return ORFX_E_CUDA;
+    return ORFX_OK;
+}
+
+// orfx_align_batch: caller-supplied proteins in host memory (BASELINE.json configs[4])
+int align_batch_device(AlnWork& w, cudaStream_t stream, int n_sm, const uint8_t* aa, const int64_t* off, int64_t n_seq, const int32_t* pair_q,
                        const int32_t* pair_t, int64_t n_pairs, int gapo, int gape, orfx_aln_out* out, double* cells, float* ms, std::string& err) {
-    (void)device;
     auto ck = [&](cudaError_t e, const char* what) { if (e != cudaSuccess) { err = std::string(what) + ": " + cudaGetErrorString(e); return false; } return true; };
     if (n_pairs == 0) { if (cells) *cells = 0; if (ms) *ms = 0; return ORFX_OK; }
-    if (gapo < 0 || gape < 0 || gapo + gape > 64) { err = "gap costs outside this build's range (0 <= gapo + gape <= 64)"; return ORFX_E_UNSUPPORTED; }
-    const int64_t total = off[n_seq];
-    // long pairs first (they take whole CTAs, phase A), then the rest; both longest-first (cells = qlen * tlen),
-    // so the long tail starts early
-    std::vector<int32_t> order((size_t)n_pairs);
-    std::iota(order.begin(), order.end(), 0);
-    std::vector<double> cost((size_t)n_pairs);
-    std::vector<uint8_t> is_long((size_t)n_pairs);
-    double sum_cells = 0;
-    int64_t max_tlen = 1, max_tlen_long = 1, n_long = 0;
-    for (int64_t p = 0; p < n_pairs; p++) {
+    for (int64_t p = 0; p < n_pairs; p++)
         if (pair_q[p] < 0 || pair_q[p] >= n_seq || pair_t[p] < 0 || pair_t[p] >= n_seq) { err = "pair index out of range"; return ORFX_E_INVALID; }
-        const int64_t ql = off[pair_q[p] + 1] - off[pair_q[p]], tl = off[pair_t[p] + 1] - off[pair_t[p]];
-        cost[(size_t)p] = (double)ql * (double)tl;
-        sum_cells += cost[(size_t)p];
-        is_long[(size_t)p] = ql >= 1024 && tl >= 256 && cost[(size_t)p] >= 4194304.0;
-        if (is_long[(size_t)p]) { n_long++; max_tlen_long = std::max(max_tlen_long, tl); }
-        else if (ql > 64) max_tlen = std::max(max_tlen, tl);
-    }
-    std::sort(order.begin(), order.end(), [&](int32_t a, int32_t b) {
-        if (is_long[(size_t)a] != is_long[(size_t)b]) return is_long[(size_t)a] > is_long[(size_t)b];
-        return cost[(size_t)a] != cost[(size_t)b] ? cost[(size_t)a] > cost[(size_t)b] : a < b;
-    });
-    cudaDeviceProp prop;
-    int dev = 0;
-    cudaGetDevice(&dev);
-    if (!ck(cudaGetDeviceProperties(&prop, dev), "cudaGetDeviceProperties")) return ORFX_E_CUDA;
-    int grid = prop.multiProcessorCount;
-    const int64_t max_grid = std::max<int64_t>(n_long, (n_pairs - n_long + ALN_WARPS - 1) / ALN_WARPS);
-    if (grid > max_grid) grid = (int)std::max<int64_t>(1, max_grid);
-    const int64_t n_warps = (int64_t)grid * ALN_WARPS;
-    const int64_t stride = (max_tlen + 31) / 32 * 32;
-    const int64_t cta_stride = (max_tlen_long + 31) / 32 * 32;
-
-    uint8_t* d_aa = nullptr; int64_t* d_off = nullptr; int32_t *d_pq = nullptr, *d_pt = nullptr, *d_order = nullptr, *d_out = nullptr, *d_scratch = nullptr, *d_cta = nullptr;
-    unsigned long long* d_counter = nullptr;
-    cudaEvent_t e0 = nullptr, e1 = nullptr;
-    int rc = ORFX_OK;
-    do {
-        if (!ck(cudaMalloc(&d_aa, (size_t)total + 16), "cudaMalloc aa")) { rc = ORFX_E_CUDA; break; }
-        if (!ck(cudaMalloc(&d_off, (size_t)(n_seq + 1) * 8), "cudaMalloc off")) { rc = ORFX_E_CUDA; break; }
-        if (!ck(cudaMalloc(&d_pq, (size_t)n_pairs * 4), "cudaMalloc pair_q")) { rc = ORFX_E_CUDA; break; }
-        if (!ck(cudaMalloc(&d_pt, (size_t)n_pairs * 4), "cudaMalloc pair_t")) { rc = ORFX_E_CUDA; break; }
-        if (!ck(cudaMalloc(&d_order, (size_t)n_pairs * 4), "cudaMalloc order")) { rc = ORFX_E_CUDA; break; }
-        if (!ck(cudaMalloc(&d_out, (size_t)n_pairs * 16), "cudaMalloc out")) { rc = ORFX_E_CUDA; break; }
-        if (!ck(cudaMalloc(&d_scratch, (size_t)(n_warps * 2 * stride) * 4 + 16), "cudaMalloc scratch")) { rc = ORFX_E_CUDA; break; }
-        if (!ck(cudaMalloc(&d_cta, (size_t)((int64_t)grid * 8 * cta_stride) * 4 + 16), "cudaMalloc cta scratch")) { rc = ORFX_E_CUDA; break; }
-        if (!ck(cudaMalloc(&d_counter, 16), "cudaMalloc counter")) { rc = ORFX_E_CUDA; break; }
-        cudaEventCreate(&e0); cudaEventCreate(&e1);
-        if (!ck(cudaMemcpyAsync(d_aa, aa, (size_t)total, cudaMemcpyHostToDevice, stream), "H2D aa")) { rc = ORFX_E_CUDA; break; }
-        cudaMemcpyAsync(d_off, off, (size_t)(n_seq + 1) * 8, cudaMemcpyHostToDevice, stream);
-        cudaMemcpyAsync(d_pq, pair_q, (size_t)n_pairs * 4, cudaMemcpyHostToDevice, stream);
-        cudaMemcpyAsync(d_pt, pair_t, (size_t)n_pairs * 4, cudaMemcpyHostToDevice, stream);
-        cudaMemcpyAsync(d_order, order.data(), (size_t)n_pairs * 4, cudaMemcpyHostToDevice, stream);
-        cudaMemsetAsync(d_counter, 0, 16, stream);
-        cudaFuncSetAttribute(align_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(ALN_WARPS * sizeof(WarpSmem)));
-        cudaEventRecord(e0, stream);
-        align_kernel<<<grid, ALN_WARPS * 32, ALN_WARPS * sizeof(WarpSmem), stream>>>(d_aa, d_off, d_pq, d_pt, d_order, (long long)n_pairs, (long long)n_long, gapo, gape, d_out,
-                                                        d_out + n_pairs, d_out + 2 * n_pairs, d_out + 3 * n_pairs, d_scratch, (long long)stride, d_cta,
-                                                        (long long)cta_stride, d_counter);
-        cudaEventRecord(e1, stream);
-        cudaMemcpyAsync(out->max, d_out, (size_t)n_pairs * 4, cudaMemcpyDeviceToHost, stream);
-        cudaMemcpyAsync(out->score, d_out + n_pairs, (size_t)n_pairs * 4, cudaMemcpyDeviceToHost, stream);
-        cudaMemcpyAsync(out->mqe, d_out + 2 * n_pairs, (size_t)n_pairs * 4, cudaMemcpyDeviceToHost, stream);
-        cudaMemcpyAsync(out->mte, d_out + 3 * n_pairs, (size_t)n_pairs * 4, cudaMemcpyDeviceToHost, stream);
-        if (!ck(cudaStreamSynchronize(stream), "alignment kernel")) { rc = ORFX_E_CUDA; break; }
-        if (!ck(cudaGetLastError(), "alignment kernel launch")) { rc = ORFX_E_CUDA; break; }
-        float t_ms = 0;
-        cudaEventElapsedTime(&t_ms, e0, e1);
-        if (ms) *ms = t_ms;
-        if (cells) *cells = sum_cells;
-    } while (false);
-    if (e0) cudaEventDestroy(e0);
-    if (e1) cudaEventDestroy(e1);
-    cudaFree(d_aa); cudaFree(d_off); cudaFree(d_pq); cudaFree(d_pt); cudaFree(d_order); cudaFree(d_out); cudaFree(d_scratch); cudaFree(d_cta); cudaFree(d_counter);
-    return rc;
+    const int64_t total = off[n_seq];
+    if (!ck(w.aa.ensure((size_t)total + 16), "cudaMalloc aa") || !ck(w.off.ensure((size_t)(n_seq + 1) * 8), "cudaMalloc off") ||
+        !ck(w.pq.ensure((size_t)n_pairs * 4), "cudaMalloc pair_q") || !ck(w.pt.ensure((size_t)n_pairs * 4), "cudaMalloc pair_t") ||
+        !ck(w.pairs.ensure((size_t)n_pairs * sizeof(AlnPair)), "cudaMalloc pairs") || !ck(w.out.ensure((size_t)n_pairs * 16), "cudaMalloc out"))
+        return ORFX_E_CUDA;
+    if (!ck(cudaMemcpyAsync(w.aa.p, aa, (size_t)total, cudaMemcpyHostToDevice, stream), "H2D aa")) return ORFX_E_CUDA;
+    cudaMemcpyAsync(w.off.p, off, (size_t)(n_seq + 1) * 8, cudaMemcpyHostToDevice, stream);
+    cudaMemcpyAsync(w.pq.p, pair_q, (size_t)n_pairs * 4, cudaMemcpyHostToDevice, stream);
+    cudaMemcpyAsync(w.pt.p, pair_t, (size_t)n_pairs * 4, cudaMemcpyHostToDevice, stream);
+    aln_pairs_from_index_kernel<<<(unsigned)((n_pairs + 255) / 256), 256, 0, stream>>>(w.off.as<int64_t>(), w.pq.as<int32_t>(), w.pt.as<int32_t>(), n_pairs, w.pairs.as<AlnPair>());
+    int32_t* d_out[4] = {w.out.as<int32_t>(), w.out.as<int32_t>() + n_pairs, w.out.as<int32_t>() + 2 * n_pairs, w.out.as<int32_t>() + 3 * n_pairs};
+    float kms = 0;
+    const int rc = align_pairs_device(w, stream, n_sm, w.aa.as<uint8_t>(), 1, 1, w.pairs.as<AlnPair>(), n_pairs, gapo, gape, d_out, cells, &kms, nullptr, err);
+    if (rc) return rc;
+    if (ms) *ms = kms;
+    cudaMemcpyAsync(out->max, d_out[0], (size_t)n_pairs * 4, cudaMemcpyDeviceToHost, stream);
+    cudaMemcpyAsync(out->score, d_out[1], (size_t)n_pairs * 4, cudaMemcpyDeviceToHost, stream);
+    cudaMemcpyAsync(out->mqe, d_out[2], (size_t)n_pairs * 4, cudaMemcpyDeviceToHost, stream);
+    cudaMemcpyAsync(out->mte, d_out[3], (size_t)n_pairs * 4, cudaMemcpyDeviceToHost, stream);
+    if (!ck(cudaStreamSynchronize(stream), "alignment results")) return ORFX_E_CUDA;
+    return ORFX_OK;
 }
 
 }  // namespace orfx

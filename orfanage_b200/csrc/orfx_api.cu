@@ -2,6 +2,7 @@
 // One context = one GPU, one stream.  No CPU fallback: every entry point that computes needs a
 // CUDA device, and orfx_create fails without one.
 #include "orfx_device.cuh"
+#include "orfx_buffers.cuh"
 
 #include <climits>
 #include <cstdio>
@@ -47,39 +48,6 @@ int fail(int code, const std::string& msg) { g_err = msg; return code; }
         cudaError_t e_ = (call);                                                                   \
         if (e_ != cudaSuccess) return fail(ORFX_E_CUDA, std::string(#call) + ": " + cudaGetErrorString(e_)); \
     } while (0)
-
-// grow-only device buffer
-struct DBuf {
-    void* p = nullptr;
-    size_t cap = 0;
-    cudaError_t ensure(size_t bytes) {
-        if (bytes <= cap) return cudaSuccess;
-        if (p) cudaFree(p);
-        p = nullptr; cap = 0;
-        size_t want = bytes + bytes / 8 + 256;
-        cudaError_t e = cudaMalloc(&p, want);
-        if (e == cudaSuccess) cap = want;
-        return e;
-    }
-    void free_() { if (p) cudaFree(p); p = nullptr; cap = 0; }
-    template <class T> T* as() const { return reinterpret_cast<T*>(p); }
-};
-// grow-only pinned host buffer
-struct HBuf {
-    void* p = nullptr;
-    size_t cap = 0;
-    cudaError_t ensure(size_t bytes) {
-        if (bytes <= cap) return cudaSuccess;
-        if (p) cudaFreeHost(p);
-        p = nullptr; cap = 0;
-        size_t want = bytes + bytes / 8 + 256;
-        cudaError_t e = cudaMallocHost(&p, want);
-        if (e == cudaSuccess) cap = want;
-        return e;
-    }
-    void free_() { if (p) cudaFreeHost(p); p = nullptr; cap = 0; }
-    template <class T> T* as() const { return reinterpret_cast<T*>(p); }
-};
 
 enum { ST_PREP = 0, ST_COUNT, ST_PLANES, ST_SCAN, ST_FILL, ST_HEAVY, ST_RESCUE, ST_SELECT, ST_N };
 const char* STAGE_NAME[ST_N] = {"prep", "count_rows", "base_planes", "codon_scan", "fill_rows", "heavy_bundles", "rescue_score", "select"};

@@ -383,6 +383,8 @@ def cleaning_batch(batch, best, rng):
         u5, u3 = (t5, t3) if plus else (len(g) - 1 - t5, len(g) - 1 - t3)
         cs[tx], ce[tx] = min(g[u5], g[u3]), max(g[u5], g[u3])
     a["tx_cds_start"], a["tx_cds_end"] = cs, ce
+    if batch.seq_format == 1:   # 4-bit base codes: `seq` holds two bases per byte
+        a["seq_format"], a["seq_bases"] = np.array([1], np.int32), np.array([batch.struct.seq_bytes], np.int64)
     return ob.Batch(**a)
 
 
