@@ -15,6 +15,7 @@
 // orfx_oracle_align below and DESIGN.md).
 #include "../include/orfx.h"
 #include "../include/orfx_codon_table.h"
+#include "../include/orfx_mat50.h"
 
 #include <algorithm>
 #ifdef _OPENMP
@@ -546,13 +547,14 @@ struct Row {
     int status;
     int n_dup = 0;
     int ext_lo = 0, ext_hi = 0;   // growth of the row's query copy (--overhang)
+    int32_t aln[4] = {0, 0, 0, 0};   // ez.max, ez.score, ez.mqe, ez.mte (params.align_enabled; 0 when the row was not scored)
     int64_t idx;
 };
 
 struct Ctx {
     orfx_params p;
     std::vector<orfx_best> best;
-    std::vector<int32_t> ext_lo, ext_hi;
+    std::vector<int32_t> ext_lo, ext_hi, aln[4];
     std::vector<int32_t> q_tx, t_tx, seg_s, seg_e, cds_s, cds_e, n_dup, qlen, tlen, ulen, qstart, extra, missing, match, outframe, inframe;
     std::vector<uint8_t> status, pass, start_match;
     std::vector<float> lpi, ilpi, mlpi;
@@ -612,7 +614,8 @@ struct BundleSeq {
     Bn bn;
     // only_tx >= 0: the window of that one (private-copy) transcript, padded so that exon growth beyond the stored flank
     // (growth is measured against --overhang, cpp:461-474) stays inside it
-    BundleSeq(const orfx_batch* b, int bi, int only_tx = -1, int pad = 0) {
+    // with_templates: the batch also carries the bases under the template CDS segments (params.align_enabled)
+    BundleSeq(const orfx_batch* b, int bi, int only_tx = -1, int pad = 0, bool with_templates = false) {
         bn.bstart = b->bundle_start[bi];
         if (!b->seq) { bn.seq = nullptr; return; }
         if (b->seq_format == ORFX_SEQ_NT4 && !b->seg_seq_off) throw std::runtime_error("ORFX_SEQ_NT4 is defined for the islands layout only");
@@ -630,13 +633,14 @@ struct BundleSeq {
         }
         rebuilt.assign((size_t)(hi - bn.bstart + 1), 'N');
         for (int x = b->bundle_tx_off[bi]; x < b->bundle_tx_off[bi + 1]; x++) {
-            if (b->tx_kind[x] != ORFX_TX_QUERY) continue;
+            if (b->tx_kind[x] != ORFX_TX_QUERY && !(with_templates && b->tx_kind[x] == ORFX_TX_TEMPLATE)) continue;
             if (only_tx >= 0 ? x != only_tx : has_private_copy(b, x)) continue;
             for (int k = b->tx_seg_off[x]; k < b->tx_seg_off[x + 1]; k++) {
                 orfx_seg sg = b->segs[k];
                 int64_t at = b->seg_seq_off[k];
-                if (b->tx_ext_lo && k == b->tx_seg_off[x]) { sg.start -= b->tx_ext_lo[x]; at -= b->tx_ext_lo[x]; }   // the --overhang flanks
-                if (b->tx_ext_hi && k == b->tx_seg_off[x + 1] - 1) sg.end += b->tx_ext_hi[x];
+                const bool isq = b->tx_kind[x] == ORFX_TX_QUERY;
+                if (isq && b->tx_ext_lo && k == b->tx_seg_off[x]) { sg.start -= b->tx_ext_lo[x]; at -= b->tx_ext_lo[x]; }   // the --overhang flanks
+                if (isq && b->tx_ext_hi && k == b->tx_seg_off[x + 1] - 1) sg.end += b->tx_ext_hi[x];
                 if (b->seq_format == ORFX_SEQ_NT4) {   // decode the 4-bit codes back to letters ("other" -> N)
                     static const char LET[16] = {'N', 'A', 'C', 'U', 'G', 'R', 'N', 'N', 'T', 'N', 'Y', 'N', 'N', 'N', 'N', 'N'};
                     const int64_t base0 = b->seq_off[bi] + at;
@@ -653,17 +657,53 @@ struct BundleSeq {
     }
 };
 
+// ---- alignment stage (params.align_enabled): Finder::align (aln.hpp:27-41) with the build definition ----------------
+const int8_t MAT50[24 * 24] = ORFX_MAT50_LITERAL;   // common.hpp:239-265
+// Finder::align's encoding loop (aln.hpp:35-36) through aa_table (common.hpp:268-277: the 24 letters in both cases, every
+// other byte 23).  The strings come from SEQ::translate: '.' for a stop, '\0' for a triplet codon_map does not know.
+std::vector<uint8_t> encode_protein(const std::string& aa) {
+    static int8_t table[256]; static bool init = false;
+    if (!init) {
+        for (int i = 0; i < 256; i++) table[i] = 23;
+        const char* order = ORFX_AA_ORDER;
+        for (int i = 0; order[i]; i++) { table[(unsigned char)order[i]] = (int8_t)i; table[(unsigned char)tolower(order[i])] = (int8_t)i; }
+        init = true;
+    }
+    std::vector<uint8_t> r(aa.size());
+    for (size_t i = 0; i < aa.size(); i++) r[i] = (uint8_t)table[(unsigned char)aa[i]];
+    return r;
+}
+// protein of a template: SEQ::translate over its spliced CDS chain from the first base (load_seq + set_cds of a transcript
+// whose exon chain is its CDS chain, orfanage.cpp:351)
+std::vector<uint8_t> template_protein(const T& t, const Bn& bn) {
+    T c = t;
+    c.bn = &bn;
+    c.seq = Seq();
+    std::string nt;
+    if (c.strand == '+') for (const S& e : c.exons) nt += c.exon_nts(e);
+    else for (int ci = (int)c.exons.size() - 1; ci >= 0; ci--) { std::string tmp = c.exon_nts(c.exons[(size_t)ci]); for (int i = (int)tmp.size() - 1; i >= 0; i--) nt += nt_complement(tmp[(size_t)i]); }
+    for (char& ch : nt) ch = (char)toupper((unsigned char)ch);
+    return encode_protein(nt.size() >= 3 ? Seq::translate(nt, 0, (int)nt.size() - 1) : std::string());
+}
+}  // namespace
+extern "C" int orfx_oracle_align(const uint8_t* query, int qlen, const uint8_t* target, int tlen, const int8_t* mat, int m, int gapo, int gape,
+                                 int32_t* out_max, int32_t* out_score, int32_t* out_mqe, int32_t* out_mte);
+namespace {
+
 void evaluate(Ctx& cx, const orfx_batch* b) {
     const orfx_params& p = cx.p;
+    const bool align = p.align_enabled && p.has_reference && b->seq;
+    const int gapo = p.align_gapo ? p.align_gapo : 12, gape = p.align_gape ? p.align_gape : 2;   // aln.hpp:146
     std::vector<Row> rows_all;
     cx.best.clear();
     cx.order.clear();
     for (int bi = 0; bi < b->n_bundles; bi++) {
-        BundleSeq bseq(b, bi);
+        BundleSeq bseq(b, bi, -1, 0, align);
         const Bn& bn = bseq.bn;
         int x0 = b->bundle_tx_off[bi], x1 = b->bundle_tx_off[bi + 1];
         std::vector<T> txs;
         for (int x = x0; x < x1; x++) txs.push_back(load_tx(b, x));
+        std::map<int, std::vector<uint8_t>> t_prot;   // proteins of the bundle's templates, on first use
         for (int qx = x0; qx < x1; qx++) {
             if (b->tx_kind[qx] != ORFX_TX_QUERY) continue;
             T q = txs[(size_t)(qx - x0)];
@@ -715,6 +755,12 @@ void evaluate(Ctx& cx, const orfx_batch* b) {
                     if (clen(qseg.cds) < p.cds_minlen) { cur.status = ORFX_ST_MINLEN; cur.sc.pass = false; continue; }
                     Sc sc = score(qseg, t);
                     cur.sc = sc;
+                    if (align) {   // the row's ORF as SEQ holds it, against its template's protein
+                        if (!t_prot.count(tx)) t_prot[tx] = template_protein(t, bn);
+                        const std::vector<uint8_t> qa = encode_protein(qseg.seq.aa);
+                        const std::vector<uint8_t>& ta = t_prot[tx];
+                        orfx_oracle_align(qa.data(), (int)qa.size(), ta.data(), (int)ta.size(), MAT50, 24, gapo, gape, &cur.aln[0], &cur.aln[1], &cur.aln[2], &cur.aln[3]);
+                    }
                     if (sc.lpi < p.lpi || sc.ilpi < p.ilpi || sc.mlpi < p.mlpi) { cur.sc.pass = false; continue; }
                     if (!orf_starts.insert(qseg.cds_start).second) { cur.status = ORFX_ST_DUP; cur.sc.pass = false; continue; }
                     cur.key_s = qseg.cds_start; cur.key_e = qseg.cds_end;
@@ -768,6 +814,7 @@ void evaluate(Ctx& cx, const orfx_batch* b) {
     auto rs = [&](std::vector<int32_t>& v) { v.resize(n); };
     rs(cx.q_tx); rs(cx.t_tx); rs(cx.seg_s); rs(cx.seg_e); rs(cx.cds_s); rs(cx.cds_e); rs(cx.n_dup); rs(cx.qlen); rs(cx.tlen); rs(cx.ulen);
     rs(cx.ext_lo); rs(cx.ext_hi);
+    for (int k = 0; k < 4; k++) rs(cx.aln[k]);
     rs(cx.qstart); rs(cx.extra); rs(cx.missing); rs(cx.match); rs(cx.outframe); rs(cx.inframe);
     cx.status.resize(n); cx.pass.resize(n); cx.start_match.resize(n); cx.lpi.resize(n); cx.ilpi.resize(n); cx.mlpi.resize(n);
     for (size_t i = 0; i < n; i++) {
@@ -778,6 +825,7 @@ void evaluate(Ctx& cx, const orfx_batch* b) {
         cx.extra[i] = r.sc.extra; cx.missing[i] = r.sc.missing; cx.match[i] = r.sc.match; cx.outframe[i] = r.sc.outframe; cx.inframe[i] = r.sc.inframe;
         cx.lpi[i] = r.sc.lpi; cx.ilpi[i] = r.sc.ilpi; cx.mlpi[i] = r.sc.mlpi;
         cx.ext_lo[i] = r.ext_lo; cx.ext_hi[i] = r.ext_hi;
+        for (int k = 0; k < 4; k++) cx.aln[k][i] = r.aln[k];
     }
 }
 
@@ -821,6 +869,9 @@ int orfx_oracle_wait(orfx_ctx* ctx, orfx_results* r) {
     r->row_match = c->match.data(); r->row_outframe = c->outframe.data(); r->row_inframe = c->inframe.data();
     r->row_lpi = c->lpi.data(); r->row_ilpi = c->ilpi.data(); r->row_mlpi = c->mlpi.data(); r->print_order = c->order.data();
     if (c->p.overhang > 0) { r->row_ext_lo = c->ext_lo.data(); r->row_ext_hi = c->ext_hi.data(); }
+    if (c->p.align_enabled && c->p.has_reference && r->n_rows > 0) {
+        r->row_aln_max = c->aln[0].data(); r->row_aln_score = c->aln[1].data(); r->row_aln_mqe = c->aln[2].data(); r->row_aln_mte = c->aln[3].data();
+    }
     return ORFX_OK;
 }
 

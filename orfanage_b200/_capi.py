@@ -554,7 +554,7 @@ class Workload:
             dev = load_device_library()
             alloc = C.cast(dev.orfx_host_alloc, C.c_void_p)
             dealloc = C.cast(dev.orfx_host_free, C.c_void_p)
-        rc = self.lib.orfxh_pack(self.handle, shard, n_shards, {"windows": 0, "islands": 1, "islands4": 2}[layout], alloc, dealloc, C.byref(s))
+        rc = self.lib.orfxh_pack(self.handle, shard, n_shards, {"windows": 0, "islands": 1, "islands4": 2, "islands_t": 3}[layout], alloc, dealloc, C.byref(s))
         if rc != 0:
             raise OrfxError(rc, self.lib.orfxh_last_error().decode())
         return Batch.from_struct(s, owner=self)

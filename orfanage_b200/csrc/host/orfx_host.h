@@ -133,6 +133,7 @@ struct Options {
     bool clean_query = false, clean_templ = false, rescue = false, use_id = false, non_aug = false;
     bool keep_all_cds = false, keep_cds_if_not_found = false, spliced_overhang = false;
     int lpi = -1, ilpi = -1, mlpi = -1, minlen = -1, overhang = 0, threads = 1;
+    int pi = 0;   // --pi: != 0 enables the protein alignment of every scored candidate (orfx_params::align_enabled)
     std::vector<int> modes{ORFX_MODE_LONGEST_MATCH, ORFX_MODE_BEST, ORFX_MODE_START_MATCH,
                            ORFX_MODE_LONGEST, ORFX_MODE_FIRST, ORFX_MODE_ALL};
     std::string reference, query, output, stats;
@@ -187,7 +188,8 @@ void pack_bundles(const Transcriptome& tr, const std::vector<int>& bundle_ids, b
                   const std::map<std::string, int>& tid_classes, PackedBatch& out,
                   void* (*alloc)(size_t) = nullptr, void (*dealloc)(void*) = nullptr, bool islands = true, int mode = PACK_EVAL,
                   bool nt4 = false,    // nt4: islands as 4-bit base codes (ORFX_SEQ_NT4), half the upload
-                  int overhang = 0, bool spliced_overhang = false);   // --overhang flanks (TX::extend_seq, Transcriptome.cpp:342-399)
+                  int overhang = 0, bool spliced_overhang = false,   // --overhang flanks (TX::extend_seq, Transcriptome.cpp:342-399)
+                  bool template_seq = false);   // islands also cover the template CDS segments (orfx_params::align_enabled)
 void build_tid_classes(const Transcriptome& tr, std::map<std::string, int>& out);
 // greedy longest-processing-time split of active bundles over n shards
 void shard_bundles(const Transcriptome& tr, const std::vector<int>& active, int n, std::vector<std::vector<int>>& shards);

@@ -91,11 +91,13 @@ struct QFlank {
 // ext (per transcript of the bundle, may be null): the flanks widen the terminal exons; transcripts with a private copy
 // are left out of the shared islands.
 void bundle_islands(const Transcriptome& tr, const Bundle& b, bool keep_all_cds, bool clean_mode, std::vector<std::pair<int, int>>& isl,
-                    const QFlank* ext = nullptr) {
+                    const QFlank* ext = nullptr, bool template_seq = false) {
     isl.clear();
     for (int i = 0; i < b.count; i++) {
         const Tx& t = tr.txs[b.first + i];
-        if (tx_kind_of(t, keep_all_cds, clean_mode) != ORFX_TX_QUERY) continue;
+        const uint8_t kind = tx_kind_of(t, keep_all_cds, clean_mode);
+        if (template_seq && kind == ORFX_TX_TEMPLATE) { for (const Seg& s : t.cds) isl.emplace_back(s.s, s.e); continue; }   // the alignment stage translates the templates
+        if (kind != ORFX_TX_QUERY) continue;
         if (ext && ext[i].private_copy) continue;
         const size_t first = isl.size();
         for (const Seg& s : t.exons) isl.emplace_back(s.s, s.e);
@@ -168,8 +170,10 @@ QFlank query_flanks(const Fasta& fa, const Fasta::Seq& chrom, const Bundle& b, c
 // copied by several threads.  islands = true uploads only the bases under query exons.
 void pack_bundles(const Transcriptome& tr, const std::vector<int>& bundle_ids, bool keep_all_cds,
                   const std::map<std::string, int>& tid_classes, PackedBatch& out,
-                  void* (*alloc)(size_t), void (*dealloc)(void*), bool islands, int mode, bool nt4, int overhang, bool spliced_overhang) {
+                  void* (*alloc)(size_t), void (*dealloc)(void*), bool islands, int mode, bool nt4, int overhang, bool spliced_overhang, bool template_seq) {
     const bool clean_mode = mode == PACK_CLEAN, compare_mode = mode == PACK_COMPARE;
+    template_seq = template_seq && mode == PACK_EVAL;
+    if (template_seq) nt4 = false;   // the translation needs the letters themselves
     out.reset();
     out.bundle_ids = bundle_ids;
     const size_t nb = bundle_ids.size();
@@ -206,7 +210,7 @@ void pack_bundles(const Transcriptome& tr, const std::vector<int>& bundle_ids, b
         const Bundle& b = tr.bundles[bundle_ids[j]];
         if (has_seq) {
             if (islands) {
-                bundle_islands(tr, b, keep_all_cds, clean_mode, isl, flk(j));
+                bundle_islands(tr, b, keep_all_cds, clean_mode, isl, flk(j), template_seq);
                 for (auto& iv : isl) bundle_bytes[j] += iv.second - iv.first + 1;
                 if (overhang > 0) for (int i = 0; i < b.count; i++) if (fl[j][(size_t)i].private_copy) bundle_bytes[j] += private_len(j, i, tr.txs[b.first + i]);
                 if (nt4) bundle_bytes[j] += bundle_bytes[j] & 1;   // bundles start on a byte boundary
@@ -299,7 +303,7 @@ void pack_bundles(const Transcriptome& tr, const std::vector<int>& bundle_ids, b
                     }
                     o += len;
                 };
-                bundle_islands(tr, b, keep_all_cds, clean_mode, il, flk(j));
+                bundle_islands(tr, b, keep_all_cds, clean_mode, il, flk(j), template_seq);
                 il_off.resize(il.size());
                 for (size_t k = 0; k < il.size(); k++) { il_off[k] = o; append(il[k].first, il[k].second - il[k].first + 1); }
                 // offset of every query segment: the island holding its start, or the transcript's private copy
@@ -313,8 +317,9 @@ void pack_bundles(const Transcriptome& tr, const std::vector<int>& bundle_ids, b
                         append(f->fake_from, f->hi);
                         continue;
                     }
+                    const bool ist = template_seq && out.tx_kind[xx] == ORFX_TX_TEMPLATE;
                     for (int k = out.tx_seg_off[xx]; k < out.tx_seg_off[xx + 1]; k++) {
-                        if (!isq) { out.seg_seq_off[k] = 0; continue; }
+                        if (!isq && !ist) { out.seg_seq_off[k] = 0; continue; }
                         const int st = out.segs[k].start;
                         size_t lo = 0, hi = il.size() - 1;
                         while (lo < hi) { size_t mid = (lo + hi + 1) >> 1; if (il[mid].first <= st) lo = mid; else hi = mid - 1; }
@@ -496,7 +501,9 @@ int run_orfanage(const Options& opt, const Backend& be) {
         stats = fopen(opt.stats.c_str(), "w");
         if (!stats) throw std::runtime_error("Cannot open stats file: " + opt.stats);
         fputs("query_id\ttemplate_id\tsegment\tnotes\tnum_templates\tquery_len\ttemplate_len\tunion_len\tpass\tlen_match\tlen_inframe\t"
-              "len_outframe\tlen_extra\tlen_missing\tlength_pi\tmatch_length_pi\tinframe_length_pi\talignment_match\tstart_match\tstop_match\tpi\n", stats);
+              "len_outframe\tlen_extra\tlen_missing\tlength_pi\tmatch_length_pi\tinframe_length_pi\talignment_match\tstart_match\tstop_match\tpi", stats);
+        // --pi (this build): the four integers of the protein alignment behind every scored row
+        fputs(opt.pi != 0 && !opt.reference.empty() ? "\taln_max\taln_score\taln_mqe\taln_mte\n" : "\n", stats);
     }
     static std::vector<char> gtf_buf(1 << 22), stats_buf(1 << 22);
     setvbuf(gtf, gtf_buf.data(), _IOFBF, gtf_buf.size());
@@ -527,7 +534,8 @@ int run_orfanage(const Options& opt, const Backend& be) {
             if (s.rc) { s.err = be.last_error(); return; }
             auto a = clk::now();
             s.ms_create = std::chrono::duration<double, std::milli>(a - c0).count();
-            pack_bundles(tr, shard_ids[k], opt.keep_all_cds, tid_classes, s.batch, be.host_alloc, be.host_free, true, PACK_EVAL, true, opt.overhang, opt.spliced_overhang);
+            pack_bundles(tr, shard_ids[k], opt.keep_all_cds, tid_classes, s.batch, be.host_alloc, be.host_free, true, PACK_EVAL, true, opt.overhang, opt.spliced_overhang,
+                         params.align_enabled != 0);
             auto b = clk::now();
             s.ms_pack = std::chrono::duration<double, std::milli>(b - a).count();
             orfx_batch v = s.batch.view();
@@ -565,10 +573,12 @@ int run_orfanage(const Options& opt, const Backend& be) {
 
     std::string line;
     auto stats_score = [&](const orfx_results& r, int64_t row) {
-        fprintf(stats, "%d\t%d\t%d\t%d\t%d\t%d\t%d\t%d\t%d\t%s\t%s\t%s\t0\t%d\t0\t0\n", r.row_qlen[row], r.row_tlen[row], r.row_ulen[row],
+        fprintf(stats, "%d\t%d\t%d\t%d\t%d\t%d\t%d\t%d\t%d\t%s\t%s\t%s\t0\t%d\t0\t0", r.row_qlen[row], r.row_tlen[row], r.row_ulen[row],
                 (int)r.row_pass[row], r.row_match[row], r.row_inframe[row], r.row_outframe[row], r.row_extra[row], r.row_missing[row],
                 float_ostream(r.row_lpi[row]).c_str(), float_ostream(r.row_mlpi[row]).c_str(), float_ostream(r.row_ilpi[row]).c_str(),
                 (int)r.row_start_match[row]);
+        if (r.row_aln_max) fprintf(stats, "\t%d\t%d\t%d\t%d", r.row_aln_max[row], r.row_aln_score[row], r.row_aln_mqe[row], r.row_aln_mte[row]);
+        fputc('\n', stats);
     };
     auto add_found_attrs = [&](Tx& fq, const Tx& t, int duplicity, float ilpi, float lpi, float mlpi, int start_match) {
         fq.add_attribute("orfanage_status", "1");

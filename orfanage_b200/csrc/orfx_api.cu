@@ -31,8 +31,14 @@ int launch_base_planes(const DevBatch& B, cudaStream_t stream);
 int launch_clean_templates(const DevBatch& B, int n_queries, int rescue, int non_aug, uint8_t* keep, int32_t* out_start, int32_t* out_end, cudaStream_t s);
 int launch_count_pairs(const DevBatch& B, int64_t* cnt, int64_t* scan_tmp, cudaStream_t s);
 int launch_score_pairs(const DevBatch& B, const DevRows& R, int n_queries, cudaStream_t s);
-int align_batch_device(int device, cudaStream_t stream, const uint8_t* aa, const int64_t* off, int64_t n_seq, const int32_t* pair_q,
+int align_batch_device(AlnWork& w, cudaStream_t stream, int n_sm, const uint8_t* aa, const int64_t* off, int64_t n_seq, const int32_t* pair_q,
                        const int32_t* pair_t, int64_t n_pairs, int gapo, int gape, orfx_aln_out* out, double* cells, float* ms, std::string& err);
+int align_pairs_device(AlnWork& w, cudaStream_t stream, int n_sm, const uint8_t* d_aa, int q_stride, int t_stride, const AlnPair* d_pairs, long long n,
+                       int gapo, int gape, int32_t* const d_out[4], double* cells, float* ms, int* n_launches, std::string& err);
+void build_translate_tables(TranslateTables& T);
+int launch_aa_len(const DevBatch& B, int64_t* cnt, cudaStream_t s);
+int launch_translate(const DevBatch& B, const TranslateTables* d_tables, int64_t total_positions, cudaStream_t s);
+int launch_row_pairs(const DevBatch& B, const DevRows& R, AlnPair* pairs, cudaStream_t s);
 int int_alu_peak_device(cudaStream_t stream, double* ops, std::string& err);
 }  // namespace orfx
 
@@ -49,8 +55,8 @@ int fail(int code, const std::string& msg) { g_err = msg; return code; }
         if (e_ != cudaSuccess) return fail(ORFX_E_CUDA, std::string(#call) + ": " + cudaGetErrorString(e_)); \
     } while (0)
 
-enum { ST_PREP = 0, ST_COUNT, ST_PLANES, ST_SCAN, ST_FILL, ST_HEAVY, ST_RESCUE, ST_SELECT, ST_N };
-const char* STAGE_NAME[ST_N] = {"prep", "count_rows", "base_planes", "codon_scan", "fill_rows", "heavy_bundles", "rescue_score", "select"};
+enum { ST_PREP = 0, ST_COUNT, ST_PLANES, ST_SCAN, ST_FILL, ST_HEAVY, ST_RESCUE, ST_SELECT, ST_TRANSLATE, ST_ALIGN, ST_N };
+const char* STAGE_NAME[ST_N] = {"prep", "count_rows", "base_planes", "codon_scan", "fill_rows", "heavy_bundles", "rescue_score", "select", "translate", "align"};
 
 }  // namespace
 
@@ -74,6 +80,13 @@ struct orfx_ctx {
     DBuf d_clean_keep, d_clean_s, d_clean_e, d_keys;
     DBuf d_xlo, d_xhi, d_xfl;   // --overhang flanks
     DBuf d_flag;
+    // alignment stage (params.align_enabled)
+    AlnWork aln;
+    DBuf d_aa_off, d_aa_pos, d_cnt_aa, d_tables, d_row_pairs, r_aln[6];
+    HBuf h_aln[4];
+    double aln_cells = 0;
+    float ms_align = 0;
+    int64_t n_aa = 0;
     int hb_max_segs = HB_MAX_SEGS, hb_max_pairs = HB_MAX_PAIRS;   // orfx_debug_set
     bool allow_empty_chains = false;   // compare batches (orfx_score_pairs): a query without a CDS is legal there
     // rows
@@ -152,6 +165,10 @@ int upload_batch(orfx_ctx* c, const orfx_batch* b, bool overlap = false) {
                 if (b->tx_kind[i] == ORFX_TX_QUERY && b->tx_strand[i] != '+' && b->tx_strand[i] != '-' && b->tx_ext_hi[i] > 0)
                     return fail(ORFX_E_UNSUPPORTED, "--overhang with strand '.' query transcripts needs the islands layout (seg_seq_off)");
     }
+    const bool align = c->P.align_enabled && seqb;
+    if (align && b->seq_format != ORFX_SEQ_RAW)
+        return fail(ORFX_E_UNSUPPORTED, "params.align_enabled needs raw sequence bytes (ORFX_SEQ_RAW): the 4-bit codes do not tell the IUPAC letters of codon_map apart");
+    if (align) { CU(c->d_aa_off.ensure((nt + 1) * 8)); CU(c->d_cnt_aa.ensure(nt * 8 + 8)); }
     c->seq_in_flight = false;
     if (seqb && overlap) {
         CU(cudaEventRecord(c->ev_chains, s));
@@ -197,6 +214,7 @@ int upload_batch(orfx_ctx* c, const orfx_batch* b, bool overlap = false) {
     B.tx_ext_flags = flanks && b->tx_ext_flags ? c->d_xfl.as<uint8_t>() : nullptr;
     B.bundle_need = c->d_need.as<uint8_t>(); B.planes = c->d_planes.as<uint32_t>(); B.plane_words = (int64_t)plane_words;
     B.hb_max_segs = c->hb_max_segs; B.hb_max_pairs = c->hb_max_pairs;
+    B.tx_aa_off = align ? c->d_aa_off.as<int64_t>() : nullptr;
     c->have_results = false;
     // The batch is caller-supplied: check what every kernel relies on (monotone CSR offsets, ordered chains, bases in
     // range) before anything walks it.  One small kernel and one flag read-back; the sequence bytes are already on their way.
@@ -241,8 +259,17 @@ int run_path(orfx_ctx* c) {
     c->n_launches += launch_count_rows(B, c->d_cnt_rows.as<int64_t>(), c->d_scan_tmp.as<int64_t>(), c->d_heavy.as<int32_t>(), c->d_heavy_count.as<unsigned>(),
                                        c->n_sm, s, c->side_stream, c->ev_fork[0], c->ev_join[0]);
     stage_end(c, ST_COUNT);
+    if (c->P.align_enabled && c->P.has_reference && B.seq_bytes > 0 && !B.tx_aa_off)
+        return fail(ORFX_E_STATE, "params.align_enabled was set after the batch was uploaded: upload it again");
+    const bool align = B.tx_aa_off != nullptr && c->P.align_enabled;
+    if (align) {
+        c->n_launches += launch_aa_len(B, c->d_cnt_aa.as<int64_t>(), s);
+        c->n_launches += launch_exclusive_scan(c->d_cnt_aa.as<int64_t>(), B.tx_aa_off, c->d_scan_tmp.as<int64_t>(), B.n_tx, s);
+    }
     // the only host round trip of the path: four totals that size the remaining buffers
     int64_t* tot = c->h_totals.as<int64_t>();
+    tot[4] = 0;
+    if (align) CU(cudaMemcpyAsync(tot + 4, B.tx_aa_off + B.n_tx, 8, cudaMemcpyDeviceToHost, s));
     CU(cudaMemcpyAsync(tot + 0, B.tx_q_off + B.n_tx, 8, cudaMemcpyDeviceToHost, s));
     CU(cudaMemcpyAsync(tot + 1, B.tx_mask_off + B.n_tx, 8, cudaMemcpyDeviceToHost, s));
     CU(cudaMemcpyAsync(tot + 2, B.tx_tile_off + B.n_tx, 8, cudaMemcpyDeviceToHost, s));
@@ -272,6 +299,17 @@ int run_path(orfx_ctx* c) {
     R.lpi = c->r_f32[0].as<float>(); R.ilpi = c->r_f32[1].as<float>(); R.mlpi = c->r_f32[2].as<float>();
     R.status = c->r_u8[0].as<uint8_t>(); R.pass = c->r_u8[1].as<uint8_t>(); R.start_match = c->r_u8[2].as<uint8_t>();
     R.print_order = c->r_order.as<int64_t>();
+    R.aln_q0 = R.aln_qn = R.aln_max = R.aln_score = R.aln_mqe = R.aln_mte = nullptr;
+    c->n_aa = 0; c->aln_cells = 0; c->ms_align = 0;
+    if (align) {
+        c->n_aa = tot[4];
+        CU(c->d_aa_pos.ensure((size_t)tot[4] + 64));
+        B.aa_pos = c->d_aa_pos.as<uint8_t>();
+        for (int i = 0; i < 6; i++) CU(c->r_aln[i].ensure((size_t)nrows * 4 + 4));
+        CU(c->d_row_pairs.ensure((size_t)nrows * sizeof(AlnPair) + 16));
+        R.aln_q0 = c->r_aln[0].as<int32_t>(); R.aln_qn = c->r_aln[1].as<int32_t>(); R.aln_max = c->r_aln[2].as<int32_t>();
+        R.aln_score = c->r_aln[3].as<int32_t>(); R.aln_mqe = c->r_aln[4].as<int32_t>(); R.aln_mte = c->r_aln[5].as<int32_t>();
+    }
     R.ext_lo = R.ext_hi = nullptr;
     if (B.tx_ext_lo) {
         for (int i = 0; i < 2; i++) CU(c->r_ext[i].ensure((size_t)nrows * 4 + 4));
@@ -301,6 +339,9 @@ int run_path(orfx_ctx* c) {
         if (tiles > 0) c->n_launches++;
     }
     stage_end(c, ST_SCAN);
+    stage_begin(c, ST_TRANSLATE);
+    if (align) c->n_launches += launch_translate(B, c->d_tables.as<TranslateTables>(), c->n_aa, s);
+    stage_end(c, ST_TRANSLATE);
     CU(cudaEventRecord(c->ev_fork[2], s));                 // masks ready
     CU(cudaStreamWaitEvent(side, c->ev_fork[2], 0));       // (heavy_fill is already ahead of it on the side stream)
     stage_begin(c, ST_HEAVY, side);
@@ -314,6 +355,20 @@ int run_path(orfx_ctx* c) {
     stage_begin(c, ST_SELECT);
     c->n_launches += launch_select(B, R, c->P, (int)nq, c->d_best.as<orfx_best>(), c->d_ord.as<int32_t>(), c->d_keys.as<int4>(), s);
     stage_end(c, ST_SELECT);
+    // alignment of every scored row's ORF against its template's protein (Finder::align, aln.hpp:27-41)
+    stage_begin(c, ST_ALIGN);
+    if (align && nrows > 0) {
+        for (int i = 2; i < 6; i++) CU(cudaMemsetAsync(c->r_aln[i].p, 0, (size_t)nrows * 4, s));   // rows that were not scored hold 0
+        c->n_launches += launch_row_pairs(B, R, c->d_row_pairs.as<AlnPair>(), s);
+        int32_t* outp[4] = {R.aln_max, R.aln_score, R.aln_mqe, R.aln_mte};
+        std::string err;
+        int nl = 0;
+        const int rc = align_pairs_device(c->aln, s, c->n_sm, B.aa_pos, 3, 3, c->d_row_pairs.as<AlnPair>(), nrows, c->P.align_gapo ? c->P.align_gapo : 12,
+                                          c->P.align_gape ? c->P.align_gape : 2, outp, &c->aln_cells, nullptr, &nl, err);
+        if (rc) return fail(rc, err);
+        c->n_launches += nl;
+    }
+    stage_end(c, ST_ALIGN);
     cudaEventRecord(c->run_ev[1], s);
     CU(cudaGetLastError());
     return ORFX_OK;
@@ -339,6 +394,7 @@ int download_results(orfx_ctx* c) {
         CU(c->h_order.ensure(nr * 8));
         CU(cudaMemcpyAsync(c->h_order.p, c->r_order.p, nr * 8, cudaMemcpyDeviceToHost, s));
         if (c->R.ext_lo) for (int i = 0; i < 2; i++) { CU(c->h_ext[i].ensure(nr * 4)); CU(cudaMemcpyAsync(c->h_ext[i].p, c->r_ext[i].p, nr * 4, cudaMemcpyDeviceToHost, s)); }
+        if (c->R.aln_max) for (int i = 0; i < 4; i++) { CU(c->h_aln[i].ensure(nr * 4)); CU(cudaMemcpyAsync(c->h_aln[i].p, c->r_aln[2 + i].p, nr * 4, cudaMemcpyDeviceToHost, s)); }
     }
     return ORFX_OK;
 }
@@ -357,6 +413,10 @@ void fill_results(orfx_ctx* c, orfx_results* r) {
         r->row_status = c->h_u8[0].as<uint8_t>(); r->row_pass = c->h_u8[1].as<uint8_t>(); r->row_start_match = c->h_u8[2].as<uint8_t>();
         r->print_order = c->h_order.as<int64_t>();
         if (c->R.ext_lo && c->n_rows) { r->row_ext_lo = c->h_ext[0].as<int32_t>(); r->row_ext_hi = c->h_ext[1].as<int32_t>(); }
+        if (c->R.aln_max && c->n_rows) {
+            r->row_aln_max = c->h_aln[0].as<int32_t>(); r->row_aln_score = c->h_aln[1].as<int32_t>();
+            r->row_aln_mqe = c->h_aln[2].as<int32_t>(); r->row_aln_mte = c->h_aln[3].as<int32_t>();
+        }
     }
 }
 
@@ -379,6 +439,11 @@ int check_params(const orfx_params* p) {
     if (p->n_modes < 0 || p->n_modes > 8) return fail(ORFX_E_INVALID, "n_modes out of range");
     for (int i = 0; i < p->n_modes; i++) if (p->mode_array[i] < 0 || p->mode_array[i] > ORFX_MODE_FIRST) return fail(ORFX_E_INVALID, "invalid mode");
     if (p->overhang < 0) return fail(ORFX_E_INVALID, "negative overhang");
+    if (p->align_enabled) {
+        if (!p->has_reference) return fail(ORFX_E_INVALID, "params.align_enabled needs params.has_reference (proteins are translated from the genome)");
+        const int go = p->align_gapo ? p->align_gapo : 12, ge = p->align_gape ? p->align_gape : 2;
+        if (go < 0 || ge < 0 || go + ge > 64) return fail(ORFX_E_UNSUPPORTED, "gap costs outside this build's range (0 <= gapo + gape <= 64)");
+    }
     return ORFX_OK;
 }
 
@@ -424,6 +489,14 @@ int orfx_create(orfx_ctx** out, int device, const orfx_params* params) {
     for (auto& ev : c->ev) cudaEventCreate(&ev);
     for (int i = 0; i < ST_N; i++) { cudaEventCreate(&c->st_ev[i][0]); cudaEventCreate(&c->st_ev[i][1]); c->st_ms[i] = 0; }
     cudaEventCreate(&c->run_ev[0]); cudaEventCreate(&c->run_ev[1]);
+    {
+        TranslateTables T;
+        build_translate_tables(T);
+        if (c->d_tables.ensure(sizeof T) != cudaSuccess || cudaMemcpy(c->d_tables.p, &T, sizeof T, cudaMemcpyHostToDevice) != cudaSuccess) {
+            orfx_destroy(c);
+            return fail(ORFX_E_CUDA, "cannot upload the translation tables");
+        }
+    }
     *out = c;
     return ORFX_OK;
 }
@@ -467,6 +540,7 @@ int orfx_wait(orfx_ctx* c, orfx_results* out) {
     if (c->B.seq_bytes > 0) { float t = 0; if (cudaEventElapsedTime(&t, c->ev[0], c->ev_seq) == cudaSuccess && t > out->ms_h2d) out->ms_h2d = t; }
     cudaEventElapsedTime(&out->ms_kernels, c->ev[1], c->ev[2]);
     cudaEventElapsedTime(&out->ms_d2h, c->ev[2], c->ev[3]);
+    out->ms_align = c->st_ms[ST_ALIGN];
     return ORFX_OK;
 }
 
@@ -486,6 +560,10 @@ void orfx_destroy(orfx_ctx* c) {
                  &c->d_ord, &c->r_order, &c->d_best, &c->d_clean_keep, &c->d_clean_s, &c->d_clean_e, &c->d_keys,
                  &c->d_xlo, &c->d_xhi, &c->d_xfl, &c->d_flag, &c->r_ext[0], &c->r_ext[1]};
     for (DBuf* b : d) b->free_();
+    c->aln.free_();
+    c->d_aa_off.free_(); c->d_aa_pos.free_(); c->d_cnt_aa.free_(); c->d_tables.free_(); c->d_row_pairs.free_();
+    for (auto& b : c->r_aln) b.free_();
+    for (auto& b : c->h_aln) b.free_();
     for (auto& b : c->r_i32) b.free_();
     for (auto& b : c->r_f32) b.free_();
     for (auto& b : c->r_u8) b.free_();
@@ -704,7 +782,7 @@ int orfx_align_batch(orfx_ctx* c, const uint8_t* aa, const int64_t* off, int64_t
     if (!aa || !off || !pair_q || !pair_t || !out || n_pairs < 0 || n_seq < 0) return fail(ORFX_E_INVALID, "null or negative argument");
     CU(cudaSetDevice(c->device));
     std::string err;
-    int rc = align_batch_device(c->device, c->stream, aa, off, n_seq, pair_q, pair_t, n_pairs, gapo, gape, out, cells, ms, err);
+    int rc = align_batch_device(c->aln, c->stream, c->n_sm, aa, off, n_seq, pair_q, pair_t, n_pairs, gapo, gape, out, cells, ms, err);
     if (rc) return fail(rc, err);
     return ORFX_OK;
 }

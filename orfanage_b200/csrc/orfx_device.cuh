@@ -47,7 +47,15 @@ struct DevBatch {
     // codon-scan output: bit p of a transcript's region = codon starting at spliced position p (5'->3')
     uint32_t* stop_mask;
     uint32_t* start_mask;
+    // alignment stage (params.align_enabled, translate.cu; else nullptr): residue code of the codon starting at every
+    // position of every QUERY (flanked chain, the masks' coordinates) and TEMPLATE (spliced CDS chain) transcript
+    int64_t* tx_aa_off;      // [n_tx+1] first byte of the transcript's region in aa_pos (16-byte aligned)
+    uint8_t* aa_pos;
 };
+
+// Lookup tables of translate.cu: letter class of a sequence byte on the forward / on any other strand (upper-cased, and
+// complemented first on the latter), residue code of a triplet of letter classes.
+struct TranslateTables { uint8_t cls_fwd[256], cls_rev[256], aa3[17 * 17 * 17]; };
 
 // Candidate rows, SoA (orfx_results row_* arrays mirror these)
 struct DevRows {
@@ -58,6 +66,9 @@ struct DevRows {
     uint8_t *status, *pass, *start_match;
     int64_t* print_order;
     int32_t *ext_lo, *ext_hi;   // --overhang: exon-chain growth of the row's query copy (else nullptr)
+    // alignment stage (else nullptr): the row's ORF as SEQ holds it -- first codon (mask coordinate) and codons, 0 when the
+    // row never reached TX::score -- and the four ksw_extz_t fields of its alignment against the template's protein
+    int32_t *aln_q0, *aln_qn, *aln_max, *aln_score, *aln_mqe, *aln_mte;
 };
 
 static constexpr int HB_MAX_SEGS = 9216;      // heavy-bundle kernels (pipeline.cu): capacity of the shared-memory stage

@@ -709,6 +709,7 @@ __device__ void process_row(const DevBatch& B, const DevRows& R, const orfx_para
     int qlen = 0, tlen = 0, ulen = 0, query_start = 0, extra = 0, missing = 0, match = 0, outframe = 0, inframe = 0;
     float lpi = 0.f, ilpi = 0.f, mlpi = 0.f;
     int pass = 0, start_match = 0;
+    int aln_0 = 0, aln_n = 0, seq_0 = 0, seq_n = 0;   // the ORF as SEQ holds it (alignment stage)
 
     const int qx = R.q_tx[row], tx = R.t_tx[row];
     const int seg_s = R.seg_start[row], seg_e = R.seg_end[row];
@@ -853,6 +854,7 @@ __device__ void process_row(const DevBatch& B, const DevRows& R, const orfx_para
             const int ncod = (e0 - s0 + 1) / 3;
             const bool ends_in_stop = ncod >= 1 && mbit(stopm, s0 + 3 * (ncod - 1)) && !stop_in_virtual;
             const bool front_m = mbit(startm, s0);
+            seq_0 = s0 + o; seq_n = ncod;
             const bool at_t5 = (plus ? cs : ce) == t5;
             if (!ends_in_stop) { status = ORFX_ST_MISSING_STOP; break; }
             if ((!P.non_aug && !front_m) || (P.non_aug && !front_m && !at_t5)) { status = ORFX_ST_MISSING_START; break; }
@@ -861,6 +863,7 @@ __device__ void process_row(const DevBatch& B, const DevRows& R, const orfx_para
         if (qlen < P.cds_minlen) { status = ORFX_ST_MINLEN; qlen = 0; break; }
 
         // ---- TX::score (Transcriptome.cpp:699-762) ----
+        aln_0 = seq_0; aln_n = seq_n;
         tlen = t.L;
         {
             const ChainScore cs_ = score_chains<WARP>(q, t, cs, ce, qlen, plus, lane);
@@ -885,6 +888,7 @@ __device__ void process_row(const DevBatch& B, const DevRows& R, const orfx_para
     R.pass[row] = (uint8_t)pass; R.start_match[row] = (uint8_t)start_match;
     R.n_dup[row] = 0;
     if (R.ext_lo) { R.ext_lo[row] = q.xlo; R.ext_hi[row] = q.xhi; }
+    if (R.aln_qn) { R.aln_q0[row] = aln_0; R.aln_qn[row] = aln_n; }
 }
 
 // 8 CTAs per SM = 64 registers (16 bytes of spill): 0.237 ms against 0.245 ms at the 72 the compiler takes unasked, 0.263 ms at 78

@@ -8,7 +8,7 @@ import numpy as np
 import pytest
 
 import orfanage_b200 as ob
-from conftest import GOLDEN
+from conftest import GOLDEN, ORACLE_CLI, run_cli, template_files
 
 pytestmark = pytest.mark.gpu
 
@@ -154,3 +154,97 @@ def test_alignment_many_long_pairs_share_a_cta(gpu, oracle_lib):
             name, len(bad), bad[0], len(seqs[pq[bad[0]]]), len(seqs[pt[bad[0]]]))
     out2, _, _ = gpu.align(aa, off, pq, pt)                                  # and again: no state left behind
     assert all((out[k] == out2[k]).all() for k in out)
+
+
+def test_alignment_padded_columns_never_reach_the_results(gpu, oracle_lib):
+    """Query lengths around every stripe boundary (64 / 128 / 256 columns and their multiples) at the largest gap costs the
+    kernel accepts (gapo + gape = 64): the virtual columns right of the query's end score -128 and must stay below
+    everything that max / mte / mqe / score look at."""
+    rng = np.random.default_rng(64)
+    lengths = [b + d for b in (64, 128, 192, 256, 320, 384, 512, 768, 1024) for d in (-2, -1, 0, 1, 2)] + [1, 2, 3, 31, 32, 33]
+    seqs, pq, pt = [], [], []
+    for L in lengths:
+        a = rng.choice(24, size=int(L)).astype(np.uint8)
+        for tl in (1, 7, 33, 200):
+            pq.append(len(seqs)); seqs.append(a)
+            pt.append(len(seqs)); seqs.append(np.resize(mutate(rng, a, 0.3, 2), tl).astype(np.uint8))
+    aa = np.concatenate(seqs)
+    off = np.concatenate([[0], np.cumsum([len(x) for x in seqs])]).astype(np.int64)
+    for gapo, gape in ((60, 4), (32, 32), (12, 2), (0, 64)):
+        out, _, _ = gpu.align(aa, off, pq, pt, gapo, gape)
+        for i, (q, t) in enumerate(zip(pq, pt)):
+            want = oracle_align(oracle_lib, seqs[q], seqs[t], gapo, gape)
+            assert (int(out["max"][i]), int(out["score"][i]), int(out["mqe"][i]), int(out["mte"][i])) == want, (gapo, gape, len(seqs[q]), len(seqs[t]))
+    with pytest.raises(ob.OrfxError):
+        gpu.align(aa, off, pq[:2], pt[:2], 60, 5)
+
+
+def test_alignment_true_titin_class_pair(gpu, oracle_lib):
+    """BASELINE.json configs[4]'s upper end: one 33 k x 33 k pair (1.1 G cells, ~130 stripes of the block-cooperative path)
+    and one 35 k x 30 k pair against the scalar restatement."""
+    rng = np.random.default_rng(35000)
+    a = rng.choice(20, size=33000, p=FREQ).astype(np.uint8)
+    b = mutate(rng, a, 0.25, 3).astype(np.uint8)
+    c = rng.choice(20, size=35000, p=FREQ).astype(np.uint8)
+    d = mutate(rng, c[:30000], 0.1, 3).astype(np.uint8)
+    seqs = [a, b, c, d]
+    aa = np.concatenate(seqs)
+    off = np.concatenate([[0], np.cumsum([len(x) for x in seqs])]).astype(np.int64)
+    out, cells, ms = gpu.align(aa, off, [0, 2], [1, 3])
+    for i, (q, t) in enumerate(((0, 1), (2, 3))):
+        want = oracle_align(oracle_lib, seqs[q], seqs[t])
+        assert (int(out["max"][i]), int(out["score"][i]), int(out["mqe"][i]), int(out["mte"][i])) == want
+        assert want[0] > 100000
+
+
+@pytest.mark.parametrize("seed,kw,overhang", [(91, dict(loci=60, lower=0.4, iupac=0.002), 0), (92, dict(loci=50, titin=0.1), 0),
+                                              (93, dict(loci=60, queries=8, template_files=2, dot=0.3, edge=True, chroms=6, chrom_len=800000), 90)])
+def test_in_path_alignment_matches_oracle(synth, oracle_lib, seed, kw, overhang):
+    """params.align_enabled: every scored row's ORF protein against its template's protein (Finder::align, src/aln.hpp:27-41,
+    build definition) -- translation on the device (translate.cu), pair list from the rows, the DP kernel on the library's
+    stream -- against the oracle, which tests/test_align_oracle.py pins to an independent restatement.  Both strands, IUPAC
+    and soft-masked bases, titin-class loci, --overhang flanks, strand '.'."""
+    from test_gpu_parity import assert_same_results
+    d = synth(seed, **kw)
+    w = ob.Workload(os.path.join(d, "query.gtf"), template_files(d), os.path.join(d, "genome.fa"), overhang=overhang)
+    layouts = ["islands_t"] + (["windows"] if not kw.get("dot") else [])
+    for layout in layouts:
+        batch = w.pack(layout=layout)
+        for pk in (dict(mode="LONGEST_MATCH,BEST"), dict(mode="ALL", non_aug=True, gapo=10, gape=1), dict(mode="BEST", lpi=50, ilpi=60, mlpi=70, minlen=300)):
+            params = ob.Params.make(align=True, overhang=overhang, **pk)
+            with ob.Context(params, device=0) as cx:
+                got = cx.run(batch)
+                again = cx.run(batch)
+            with ob.Context(params, lib=oracle_lib, prefix="orfx_oracle_") as ox:
+                want = ox.run(batch)
+            assert "aln_max" in want.rows and (want.rows["aln_max"] > 0).sum() > 100
+            assert_same_results(got, want, "in-path alignment, seed %d %s %s" % (seed, layout, pk))
+            assert_same_results(again, want, "second batch on the same context")
+            scored = want.rows["qlen"] > 0
+            assert not want.rows["aln_score"][~scored].any()
+    # the 4-bit base codes cannot feed the translation: refused, not approximated
+    with ob.Context(ob.Params.make(align=True, overhang=overhang), device=0) as cx:
+        with pytest.raises(ob.OrfxError):
+            cx.run(w.pack(layout="islands4"))
+    w.close()
+
+
+def test_cli_pi_flag_adds_alignment_columns_and_leaves_the_gtf_alone(synth):
+    d = synth(94, loci=80, template_files=2)
+    base = ["--reference", "genome.fa", "--query", "query.gtf", "--mode", "LONGEST_MATCH,BEST"]
+    rc0, gtf0, tsv0, err0 = run_cli(ob.cli_path(), d, base, "nopi")
+    rc1, gtf1, tsv1, err1 = run_cli(ob.cli_path(), d, base + ["--pi", "1"], "pi")
+    rc2, gtf2, tsv2, err2 = run_cli(ORACLE_CLI, d, base + ["--pi", "1"], "pi_oracle")
+    assert rc0 == 0 and rc1 == 0 and rc2 == 0, (err0, err1, err2)
+    assert gtf1 == gtf0 and gtf2 == gtf0
+    assert tsv1 == tsv2
+    l0, l1 = tsv0.decode().splitlines(), tsv1.decode().splitlines()
+    assert l1[0] == l0[0] + "\taln_max\taln_score\taln_mqe\taln_mte" and len(l0) == len(l1)
+    n = 0
+    for x, y in zip(l0[1:], l1[1:]):
+        if len(y.split("\t")) == 25:
+            assert y.startswith(x + "\t")
+            n += 1
+        else:
+            assert x == y     # the 20-column "-" rows of queries without a candidate
+    assert n > 300

@@ -170,9 +170,9 @@ def test_codon_table_matches_reference_literal():
 
 def test_mat50_and_aa_table_match_reference_literals():
     mat = np.load(os.path.join(GOLDEN, "mat50.npy"))
-    cu = open(os.path.join(ROOT, "orfanage_b200", "csrc", "align.cu")).read()
-    body = cu[cu.index("c_mat50[24 * 24] = {"):]
-    body = body[body.index("{") + 1:body.index("};")]
+    hdr = open(os.path.join(ROOT, "include", "orfx_mat50.h")).read()   # the literal the device library and the oracle share
+    body = hdr[hdr.index("#define ORFX_MAT50_LITERAL"):]
+    body = body[body.index("{") + 1:body.index("}")]
     got = np.array([int(x) for x in re.findall(r"-?\d+", body)], dtype=np.int8).reshape(24, 24)
     assert (got == mat).all()
     assert (mat == mat.T).all()
