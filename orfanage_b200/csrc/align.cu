@@ -39,7 +39,7 @@ constexpr int ALN_WARPS = ORFX_ALN_WARPS;       // one CTA per SM; its warps wor
 
 struct AlnAcc { int gmax, mqe, mte, score; };
 
-// What a stripe reads on its left and writes on its right: H(i, c_base-1) / F(i, c_base) per target row.
+// What a stripe reads on its left and writes on its right: H(i, c_base-1) / F(i, c_base) + (q+e) per target row.
 // PIPE: the stripes of one pair run concurrently on the warps of a CTA; a stripe may read row chunk
 // [s, s+32) of its left edge once the warp of the previous stripe has posted that many rows.
 struct StripeIO {
@@ -53,7 +53,7 @@ struct StripeIO {
 struct WarpSmem {
     uint2 prof[24][32];     // query profile: prof[r][lane] = the lane's CPL scores against target residue r, one int8 each
     int   t_ring[128];      // target residues: previous, current and next 32-row chunk
-    int2  in_ring[32];      // left edge {H(i, c_base-1), F(i, c_base)} of the current chunk (borders for the first stripe)
+    int2  in_ring[32];      // left edge {H(i, c_base-1), F(i, c_base) + (q+e)} of the current chunk (borders for the first stripe)
     int2  out_ring[64];     // right edge of the rows lane 31 finished, until their chunk is stored
 };
 constexpr int PAD_SCORE8 = -128;    // score of the virtual columns right of the query's end: padded cells stay below
@@ -64,7 +64,11 @@ constexpr int PAD_SCORE8 = -128;    // score of the virtual columns right of the
 // The substitution scores of a step come as ONE shared-memory load of the lane's profile entry (fetched one step
 // ahead) and are added to the diagonal with dp4a (one-hot selector) on the FMA pipe, which leaves the ALU pipe
 // to the max / add-max chain:
-//   x = d + s; h = max3(x, E, F); E' = max(E - e, h - (q+e)); F' = max(F - e, h - (q+e))      (4 ALU + 1 FMA per cell)
+//   x = d + s;  u = max(x, E);  h = max(u, F);  F' = max(F - e, u - (q+e));  E' = max(E - e, h - (q+e))
+// F' may take u instead of h because F - (q+e) <= F - e; with E and F kept shifted up by (q+e) all four are add-max
+// instructions (VIADDMNMX), no plain add is left, and the chain carried from cell to cell is ONE instruction deep (F' needs
+// only F and u, and u does not depend on F):
+//   u = max(Eh - (q+e), x);  h = max(Fh - (q+e), u);  Fh' = max(Fh - e, u);  Eh' = max(Eh - e, h)      (4.5 ALU + 1 FMA per cell)
 // Steps go in blocks of 32; blocks in which every lane has a row run without per-step range checks.
 // LAST: the stripe holding column qlen-1 (tracks mqe / score, writes no right edge).
 // A protein as the kernels read it: residue i is p[i * stride] (stride 1: caller-supplied proteins; stride 3: the codons of one
@@ -87,7 +91,7 @@ __device__ __forceinline__ void dp_stripe(const int* __restrict__ s_mat, WarpSme
             const int c = c0 + k;
             qcode[k] = c < qlen ? q[c] : -1;
             hp[k] = -(gapoe + gape * c);                 // H(-1, c)
-            ee[k] = -(gapoe + gapoe + gape * c);         // E(0, c)
+            ee[k] = -(gapoe + gape * c);                 // E(0, c) + (q+e)
         }
         __syncwarp();   // the previous stripe's profile and rings are no longer read
         for (int r = 0; r < 24; r++) {
@@ -125,13 +129,13 @@ __device__ __forceinline__ void dp_stripe(const int* __restrict__ s_mat, WarpSme
 #pragma unroll
             for (int k = 0; k < CPL; k++) {
                 const int x = __dp4a((int)(k < 4 ? cur.x : cur.y), 1 << (8 * (k & 3)), d);
-                h = __vimax3_s32(x, ee[k], f);
+                const int u = __viaddmax_s32(ee[k], -gapoe, x);
+                h = __viaddmax_s32(f, -gapoe, u);
+                f = __viaddmax_s32(f, -gape, u);
+                ee[k] = __viaddmax_s32(ee[k], -gape, h);
                 d = hp[k];
                 hp[k] = h;
                 if (k & 1) m1 = __vimax3_s32(m1, m0, h); else m0 = h;
-                const int tt = h - gapoe;
-                ee[k] = __viaddmax_s32(ee[k], -gape, tt);
-                f = __viaddmax_s32(f, -gape, tt);
             }
             const int rowmax = (CPL & 1) ? max(m1, m0) : m1;
             gmax = max(gmax, rowmax);
@@ -154,7 +158,7 @@ __device__ __forceinline__ void dp_stripe(const int* __restrict__ s_mat, WarpSme
     for (int s0 = 0; s0 < n_steps; s0 += 32) {
         {   // next 32 target rows' left edge into the ring, the residues of the chunk after it
             const int r = s0 + lane;
-            int2 e = make_int2(-(gapoe + gape * r), -(gapoe + gapoe + gape * r));   // first stripe: H(r, -1), F(r, 0)
+            int2 e = make_int2(-(gapoe + gape * r), -(gapoe + gape * r));   // first stripe: H(r, -1), F(r, 0) + (q+e)
             if (!first_stripe) {
                 if (PIPE && s0 < tlen) {
                     const unsigned long long need = io.wait_base + (unsigned long long)min(s0 + 32, tlen);
