@@ -434,6 +434,8 @@ def alignment_leg(cx, n_pairs, cpu_seconds=12.0):
             "gcups_by_length": buckets,
             "checksum": int(np.bitwise_xor.reduce(out["score"].astype(np.int64) * 31 + out["max"]))}
     # CPU baseline: same recurrence, scalar int32, all cores, bounded subsample
+    if cpu_seconds <= 0:
+        return line
     try:
         lib = C.CDLL(os.path.join(ROOT, "oracle", "liborfx_oracle.so"))
         lib.orfx_oracle_align_batch.restype = C.c_int
@@ -509,11 +511,17 @@ def main():
     ap.add_argument("--seed-offset", type=int, default=0, help="generate the shard rank k of a multi-GPU run would get (k = offset)")
     ap.add_argument("--no-pipelined", action="store_true", help="skip the two-context end-to-end leg")
     ap.add_argument("--align-pairs", type=int, default=50000, help="protein pairs of the alignment leg (0 = skip; configs[4] = 1000000)")
+    ap.add_argument("--only-align", action="store_true", help="development: run the alignment leg alone and print its object")
     args = ap.parse_args()
     quiet_stdout()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
     if args.impl == "reference":
         reference_arm(args)
+        return
+    if args.only_align:
+        import orfanage_b200 as ob
+        cx = ob.Context(ob.Params.make(mode=MODE, want_rows=False), device=int(os.environ.get("LOCAL_RANK", "0")))
+        emit(alignment_leg(cx, args.align_pairs, cpu_seconds=0.0 if args.no_cpu_baseline else 12.0))
         return
     m = ours(args)
     if m["rank"] != 0:

@@ -29,6 +29,9 @@ for step in "$@"; do
     full)
       ncu --set full --clock-control none --import-source on -k "regex:$arg" -c 40 -o gpurun_out/${TAG}_full -f $SHORT > gpurun_out/${TAG}_ncu_full.log 2>&1
       echo "full rc=$?" ;;
+    alignfull)   # ncu --set full of the alignment kernel alone (bench.py --only-align on <arg> pairs)
+      ncu --set full --clock-control none --import-source on -k "regex:align_kernel" -c 2 -o gpurun_out/${TAG}_alignfull -f python bench.py --only-align --no-cpu-baseline --align-pairs ${arg:-20000} > gpurun_out/${TAG}_ncu_alignfull.log 2>&1
+      echo "alignfull rc=$?" ;;
     sanitize)
       tool=${arg%%:*}; sel=${arg#*:}
       compute-sanitizer --tool $tool --error-exitcode 9 python -m pytest tests -m gpu -q -x -k "$sel" > gpurun_out/${TAG}_sanitize_${tool}.log 2>&1
