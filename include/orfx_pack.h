@@ -54,6 +54,11 @@ int orfxh_truncate(orfxh_workload* w, int64_t n_active_bundles);
 /* transcript_id of transcript `tx` of the batch last packed for `shard`; NULL when out of range. */
 const char* orfxh_tx_id(const orfxh_workload* w, int shard, int32_t tx);
 
+/* Workload-wide index (position in the loaded, sorted transcriptome: the same on every rank that loaded the same files)
+ * of every transcript of the batch last packed for `shard`: out[n_tx].  Lets results of different shards be merged or
+ * compared without going through transcript_id strings.  Returns n_tx or a negative error. */
+int64_t orfxh_tx_global(const orfxh_workload* w, int shard, int32_t* out, int64_t capacity);
+
 void orfxh_free(orfxh_workload* w);
 
 #ifdef __cplusplus

@@ -340,6 +340,8 @@ def load_host_library(path=None):
     lib.orfxh_truncate.argtypes = [C.c_void_p, C.c_int64]
     lib.orfxh_tx_id.restype = C.c_char_p
     lib.orfxh_tx_id.argtypes = [C.c_void_p, C.c_int, C.c_int32]
+    lib.orfxh_tx_global.restype = C.c_int64
+    lib.orfxh_tx_global.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_int64]
     lib.orfxh_free.restype = None
     lib.orfxh_free.argtypes = [C.c_void_p]
     if path is None:
@@ -558,6 +560,14 @@ class Workload:
         if rc != 0:
             raise OrfxError(rc, self.lib.orfxh_last_error().decode())
         return Batch.from_struct(s, owner=self)
+
+    def tx_global(self, n_tx, shard=0):
+        """Workload-wide transcript index of every transcript of the batch last packed for `shard`."""
+        out = np.zeros(max(int(n_tx), 1), dtype=np.int32)
+        n = self.lib.orfxh_tx_global(self.handle, shard, out.ctypes.data, len(out))
+        if n < 0:
+            raise OrfxError(int(n), self.lib.orfxh_last_error().decode())
+        return out[:n]
 
     def tx_id(self, tx, shard=0):
         v = self.lib.orfxh_tx_id(self.handle, shard, tx)

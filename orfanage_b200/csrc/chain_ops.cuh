@@ -119,6 +119,36 @@ __device__ __forceinline__ int next_inframe(const uint32_t* m, int p, int L) {
         const uint32_t t = pa; pa = pb; pb = pc; pc = t;  // 16 words on: one step as well
     }
 }
+// The same for a whole warp (heavy bundles: all 32 lanes work on one row and call this with the same arguments).  A
+// titin-class ORF is tens of kilobases long; the scalar scan above walks it 16 words per round, one lane's loads at a
+// time.  Here every lane takes its own 4-word block of the round (128 words = 4 096 positions per round), the lowest
+// lane with a hit wins.
+__device__ __forceinline__ int next_inframe_warp(const uint32_t* m, int p, int L, int lane) {
+    if (p < 0 || p >= L) return -1;
+    const int r = p % 3, nw = (L + 31) >> 5;
+    const int w_first = p >> 5;
+    for (int base = w_first & ~3; base < nw; base += 128) {
+        const int w = base + 4 * lane;                        // this lane's block: words [w, w + 4)
+        int q = -1;
+        if (w < nw) {                                         // regions are padded to 4 words: the load stays inside
+            const uint4 v = *reinterpret_cast<const uint4*>(m + w);
+            uint32_t x[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+            for (int k = 3; k >= 0; k--) {
+                uint32_t bits = x[k] & frame_pattern(w + k, r);
+                if (w + k < w_first) bits = 0;
+                else if (w + k == w_first) bits &= 0xFFFFFFFFu << (p & 31);
+                if (bits) q = ((w + k) << 5) + __ffs(bits) - 1;
+            }
+        }
+        const unsigned hit = __ballot_sync(0xffffffffu, q >= 0);
+        if (hit) {
+            q = __shfl_sync(0xffffffffu, q, __ffs(hit) - 1);
+            return q < L ? q : -1;                            // bits past the last real position are padding
+        }
+    }
+    return -1;
+}
 // largest q <= p with q == p (mod 3), q >= 0 and bit set; -1 when none
 __device__ __forceinline__ int prev_inframe(const uint32_t* m, int p) {
     if (p < 0) return -1;

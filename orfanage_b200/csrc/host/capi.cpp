@@ -106,6 +106,14 @@ const char* orfxh_tx_id(const orfxh_workload* w, int shard, int32_t tx) {
     return w->tr.txs[(size_t)pb.tx_global[(size_t)tx]].tid.c_str();
 }
 
+int64_t orfxh_tx_global(const orfxh_workload* w, int shard, int32_t* out, int64_t capacity) {
+    if (!w || !out || shard < 0 || (size_t)shard >= w->packed.size() || !w->packed[(size_t)shard]) { g_err = "no packed batch for this shard"; return ORFX_E_INVALID; }
+    const PackedBatch& pb = *w->packed[(size_t)shard];
+    if ((int64_t)pb.tx_global.size() > capacity) { g_err = "output too small"; return ORFX_E_INVALID; }
+    for (size_t i = 0; i < pb.tx_global.size(); i++) out[i] = pb.tx_global[i];
+    return (int64_t)pb.tx_global.size();
+}
+
 void orfxh_free(orfxh_workload* w) { delete w; }
 
 }  // extern "C"

@@ -735,7 +735,10 @@ __device__ void process_row(const DevBatch& B, const DevRows& R, const orfx_para
     const uint32_t* stopm = nullptr;
     const uint32_t* startm = nullptr;
     auto mbit = [&](const uint32_t* m, int p) { return mask_bit(m, p + o); };
-    auto nxt = [&](const uint32_t* m, int p, int lim) { const int r = next_inframe(m, p + o, lim + o); return r < 0 ? -1 : r - o; };   // first hit in [p, lim)
+    auto nxt = [&](const uint32_t* m, int p, int lim) {   // first hit in [p, lim)
+        const int r = WARP ? next_inframe_warp(m, p + o, lim + o, lane) : next_inframe(m, p + o, lim + o);
+        return r < 0 ? -1 : r - o;
+    };
     auto prv = [&](const uint32_t* m, int p) { const int r = p < 0 ? -1 : prev_inframe(m, p + o); return r < o ? -1 : r - o; };       // last hit in [0, p]
 
     do {
