@@ -25,7 +25,7 @@ host: orfanage_b200/liborfx_host.so
 orfanage_b200/liborfx_host.so: $(HOST_OBJ)
 	$(CXX) -shared -o $@ $(HOST_OBJ) -lpthread
 orfanage_b200/liborfx.so: $(CU_SRC) $(CU_HDR)
-	$(NVCC) $(NVFLAGS) -shared $(CU_SRC) -o $@ 2> build/ptxas.log || (cat build/ptxas.log; false)
+	$(NVCC) $(NVFLAGS) -shared $(CU_SRC) -o $@ -ldl 2> build/ptxas.log || (cat build/ptxas.log; false)
 	@grep -E "registers|spill|error" build/ptxas.log | sort | uniq -c | sort -rn | head -40 || true
 orfanage_b200/bin/orfanage: $(HOST_OBJ) build/host/main.o orfanage_b200/liborfx.so
 	@mkdir -p orfanage_b200/bin

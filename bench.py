@@ -26,6 +26,9 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
 C2 = dict(seed=20261104, loci=20000, chroms=24, chrom_len=125000000, queries=13, templates=8, template_files=1)
+# BASELINE.json configs[3]: long-read novel isoforms, ~2 M query transcripts (100 per locus), ONE workload sharded by locus
+# over the GPUs of the box (strong scaling; the product's own shard_bundles deals the loci)
+C4 = dict(seed=20261107, loci=20000, chroms=24, chrom_len=125000000, queries=100, templates=8, template_files=1)
 MODE = "LONGEST_MATCH,BEST"
 ALG_BYTES_PER_NT = 1.25      # codon scan: 1 B read per spliced nucleotide + 2 mask bits written
 
@@ -104,14 +107,76 @@ class ClockSampler(threading.Thread):
 SAMPLE = dict(C2, loci=3336, chroms=4)     # same generator law and locus spacing as configs[1], 1/6 of the loci
 
 
-def evaluated_queries(d):
-    """Query transcripts in bundles that hold a template (the ones the hot path evaluates; the rest are
-    copied through unchanged by both implementations, orfanage.cpp:383-432)."""
-    import orfanage_b200 as ob
-    w = ob.Workload(os.path.join(d, "query.gtf"), [os.path.join(d, "template.gtf")], None)
-    n = w.count("queries")
-    w.close()
+def evaluated_queries(gtf_path):
+    """Query transcripts the hot path evaluated, counted from an output GTF without any of this repo's code: the
+    transcript rows that carry an orfanage_status attribute are exactly the queries of bundles that hold a template
+    (orfanage.cpp:383-432 copies the others through without one)."""
+    n = 0
+    with open(gtf_path, "rb") as f:
+        for line in f:
+            if b"\ttranscript\t" in line and b"orfanage_status" in line:
+                n += 1
     return n
+
+
+def source_digest():
+    """SHA-256 over the CUDA sources and the public headers: ties a profile (profiles/r02_traffic.json) to the build."""
+    import hashlib
+    h = hashlib.sha256()
+    files = []
+    for d in ("orfanage_b200/csrc", "include"):
+        for f in sorted(os.listdir(os.path.join(ROOT, d))):
+            if f.endswith((".cu", ".cuh", ".h")):
+                files.append(os.path.join(ROOT, d, f))
+    for f in files:
+        h.update(open(f, "rb").read())
+    return h.hexdigest()[:16]
+
+
+def file_sha256(path):
+    import hashlib
+    h = hashlib.sha256()
+    with open(path, "rb") as f:
+        for chunk in iter(lambda: f.read(1 << 22), b""):
+            h.update(chunk)
+    return h.hexdigest()
+
+
+def cli_leg(d):
+    """The thing a user runs: whole-process wall time of orfanage_b200/bin/orfanage on the configs[1] files (its own stage
+    timers beside it), next to the reference binary's whole-process time on the same files with all host threads; the GTF
+    is checked against the reference's (SHA-256 of the reference's --threads 1 output, tests/golden/fullsize_hashes.json:
+    above one thread the reference's output order is nondeterministic)."""
+    import orfanage_b200 as ob
+    out = {"workload": "GENCODE-scale synthetic (BASELINE.json configs[1]) from the files on disk", "mode": MODE}
+    args = ["--reference", "genome.fa", "--query", "query.gtf", "--mode", MODE]
+    walls, stderr = [], ""
+    for _ in range(2):   # the second run has the page cache the reference run below also gets
+        t0 = time.time()
+        p = subprocess.run([ob.cli_path()] + args + ["--output", "cli.gtf", "--timing", "template.gtf"], cwd=d, capture_output=True, text=True)
+        walls.append(time.time() - t0)
+        if p.returncode != 0:
+            return {"error": p.stderr[-300:]}
+        stderr = p.stderr
+    nq = evaluated_queries(os.path.join(d, "cli.gtf"))
+    out.update({"wall_s": min(walls), "wall_s_runs": walls, "evaluated_query_transcripts": nq, "transcripts_per_s": nq / min(walls),
+                "stage_timers": [l[len("[timing] "):] for l in stderr.splitlines() if l.startswith("[timing]")]})
+    try:
+        want = json.load(open(os.path.join(ROOT, "tests", "golden", "fullsize_hashes.json")))["c2"]
+        same_gen = all(want["generator"].get(k) == C2.get(k) for k in ("seed", "loci", "chroms", "chrom_len", "queries", "templates", "template_files"))
+        out["gtf_identical_to_reference"] = bool(same_gen and file_sha256(os.path.join(d, "cli.gtf")) == want["gtf_sha256"])
+    except Exception as e:
+        out["gtf_identical_to_reference"] = None
+        out["note"] = "no digest to compare with: %s" % e
+    try:
+        threads = os.cpu_count() or 1
+        ev, whole = time_reference_once(d, threads)
+        out["reference"] = {"binary": "oracle/_ref/orfanage_ref (the reference's own sources)", "threads": threads, "wall_s": whole, "main_loop_s": ev,
+                            "evaluated_query_transcripts": evaluated_queries(os.path.join(d, "ref_out.gtf"))}
+        out["speedup_whole_process"] = whole / min(walls)
+    except Exception as e:
+        out["reference"] = {"unavailable": str(e)}
+    return out
 
 
 def time_reference_once(d, threads):
@@ -145,8 +210,10 @@ def reference_arm(args):
     if rank != 0:
         return
     threads = os.cpu_count() or 1
-    d = generate(SAMPLE, "sample")
-    nq = evaluated_queries(d)
+    # A step = one run of the reference binary (it reloads its inputs every time: ~14 s per run at configs[1]).  Runs of a few
+    # steps take configs[1] itself; the driver's 20 + 5 steps take the bounded 1/6 sample so that the arm ends within minutes.
+    full = args.steps + args.warmup <= 6
+    d = generate(C2 if full else SAMPLE, "c2" if full else "sample")
     for _ in range(args.warmup):
         time_reference_once(d, threads)
     evals, wholes = [], []
@@ -154,13 +221,15 @@ def reference_arm(args):
         e, w = time_reference_once(d, threads)
         evals.append(e)
         wholes.append(w)
+    nq = evaluated_queries(os.path.join(d, "ref_out.gtf"))   # counted from the reference's own output
     ms = 1e3 * sum(evals) / len(evals)
     value = nq / (ms / 1e3)
-    sample = "%d loci / %d query transcripts of the configs[1] generator (1/6 of the loci, same locus spacing)" % (SAMPLE["loci"], nq)
+    sample = ("configs[1] itself: %d loci / %d evaluated query transcripts" % (C2["loci"], nq)) if full else \
+        "%d loci / %d query transcripts of the configs[1] generator (1/6 of the loci, same locus spacing)" % (SAMPLE["loci"], nq)
     line = {"impl": "reference", "metric": "query transcripts/sec", "value": value, "unit": "transcripts/s", "n_gpus": args.gpus,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "int32", "data": "synthetic",
-            "config": {"workload": "GENCODE-scale synthetic (configs[1]) — bounded sample", "mode": MODE, "sample": sample,
+            "config": {"workload": "GENCODE-scale synthetic (BASELINE.json configs[1])" + ("" if full else " — bounded sample"), "mode": MODE, "sample": sample,
                        "timed": "reference main evaluation loop (orfanage.cpp:369-819), mean of %d runs" % args.steps,
                        "whole_process_s": sum(wholes) / len(wholes)},
             "cpu_baseline": {"value": value, "unit": "transcripts/s", "cores": threads, "kind": "reference", "sample": sample},
@@ -174,10 +243,10 @@ def cpu_baseline_leg():
     """Reference binary on the bounded sample, all host threads, one warm-up + two timed runs."""
     threads = os.cpu_count() or 1
     d = generate(SAMPLE, "sample")
-    nq = evaluated_queries(d)
     time_reference_once(d, threads)
     ev = [time_reference_once(d, threads)[0] for _ in range(2)]
     e1 = time_reference_once(d, 1)[0]
+    nq = evaluated_queries(os.path.join(d, "ref_out.gtf"))
     sample = "%d loci / %d query transcripts of the configs[1] generator; main evaluation loop only" % (SAMPLE["loci"], nq)
     return {"value": nq / (sum(ev) / len(ev)), "unit": "transcripts/s", "cores": threads, "kind": "reference", "sample": sample,
             "single_thread_value": nq / e1}
@@ -203,7 +272,8 @@ def ours(args):
             dist.barrier()
         torch.cuda.synchronize()
 
-    cfg = dict(C2)
+    c4 = args.config == "c4"
+    cfg = dict(C4 if c4 else C2)
     if args.loci:
         cfg["loci"] = args.loci
         cfg["chroms"] = max(1, min(24, args.loci // 834 + 1))
@@ -213,17 +283,20 @@ def ours(args):
     base = os.environ.get("ORFX_BENCH_DIR", "/tmp/orfx_bench")
     os.makedirs(base, exist_ok=True)
     need = world * (cfg["chroms"] * cfg["chrom_len"] * 1.2 + 1e9)
-    shared = world > 1 and shutil.disk_usage(base).free < need
-    cfg["seed"] = C2["seed"] + (0 if shared else rank) + args.seed_offset
+    shared = world > 1 and (c4 or shutil.disk_usage(base).free < need)
+    cfg["seed"] = cfg["seed"] + (0 if shared or c4 else rank) + args.seed_offset
+    tag = "c4" if c4 else "c2"
     if shared:
         if rank == 0:
-            generate(cfg, "c2")
+            generate(cfg, tag)
         barrier()
-    d = generate(cfg, "c2")
+    d = generate(cfg, tag)
     t = time.time()
     w = ob.Workload(os.path.join(d, "query.gtf"), [os.path.join(d, "template.gtf")], os.path.join(d, "genome.fa"))
-    batch = w.pack(0, 1, pinned=True, layout="islands4")
-    nq, nt_sum = batch.n_queries, w.count("query_nt")
+    # configs[1]: every rank its own workload (weak scaling); configs[3]: every rank loads the one workload and packs the
+    # locus shard shard_bundles deals it (strong scaling)
+    batch = w.pack(rank, world, pinned=True, layout="islands4") if c4 else w.pack(0, 1, pinned=True, layout="islands4")
+    nq, nt_sum = batch.n_queries, (batch.query_nt() if c4 else w.count("query_nt"))
     log("rank %d: loaded + packed in %.1f s: %d queries, %d templates, %d bundles, %.1f MB windows, %.1f M spliced nt"
         % (rank, time.time() - t, nq, w.count("templates"), w.count("active_bundles"), batch.arrays["seq"].nbytes / 1e6, nt_sum / 1e6))
     if args.verbose_shard:   # what makes one rank's shard slower than another's: its largest loci
@@ -259,6 +332,30 @@ def ours(args):
     clocks = sampler.result()
     res = cx.fetch()
     found = int((res.best["t_tx"] >= 0).sum())
+    # ---- leg 1b: the same resident batch with every kernel alone on the one stream (orfx_debug_set "serialize"): per-kernel
+    # launch times without anything running beside them -- the codon-scan roofline's kernel time (in the product path the scan
+    # of the ordinary loci shares the GPU with the heavy bundles' rescue kernel)
+    stage_ms_alone, alone_ms = {}, 0.0
+    cx.debug_set("serialize", 1)
+    for _ in range(2):
+        cx.run_resident()
+    for _ in range(args.steps):
+        cx.run_resident()
+        alone_ms += cx.last_run_ms()
+        for k, v in cx.kernel_times().items():
+            stage_ms_alone[k] = stage_ms_alone.get(k, 0.0) + v
+    cx.debug_set("serialize", 0)
+    assert cx.fetch().best.tobytes() == res.best.tobytes(), "serialized and overlapped runs give the same answers"
+    # order-independent digest of the chosen ORFs over workload-wide transcript indices: the same whatever the sharding
+    gl = w.tx_global(len(batch.arrays["tx_kind"]), rank if c4 else 0).astype(np.uint64)
+    b_ = res.best
+    tq = gl[b_["q_tx"]]
+    tt_ = np.where(b_["t_tx"] >= 0, gl[np.maximum(b_["t_tx"], 0)], np.uint64(0xFFFFFFFF))
+    mix = (tq * np.uint64(0x9E3779B97F4A7C15)) ^ (tt_ * np.uint64(0xC2B2AE3D27D4EB4F)) ^ (b_["cds_start"].astype(np.uint64) * np.uint64(0x165667B19E3779F9)) \
+        ^ (b_["cds_end"].astype(np.uint64) * np.uint64(0x27D4EB2F165667C5)) ^ (b_["ilpi"].view(np.uint32).astype(np.uint64) << np.uint64(17)) \
+        ^ (b_["duplicity"].astype(np.uint64) << np.uint64(49))
+    mix ^= mix >> np.uint64(29)
+    dig_lo, dig_hi = int((mix & np.uint64(0xFFFFFFFF)).sum()), int((mix >> np.uint64(32)).sum())
 
     # ---- leg 2: end to end through orfx_submit / orfx_wait, batch in pinned host memory -----------
     for _ in range(max(1, args.warmup // 2)):
@@ -275,19 +372,20 @@ def ours(args):
     e2e_ms = (time.perf_counter() - t0) * 1e3
     d2h_bytes = int(nq * ob._capi.BEST_DTYPE.itemsize + 32)
 
-    # ---- leg 3: the same call sequence on two contexts, each with half of the loci: the upload of one half overlaps the
-    # kernels of the other (orfx_submit returns once everything is enqueued).  Same work, same bytes, same API.
+    # ---- leg 3: the same call sequence on several contexts, each with its share of the loci (shard_bundles): the upload of one
+    # share overlaps the kernels of another (orfx_submit returns once everything is enqueued).  Same work, same bytes, same API.
     e2e2_ms = None
-    if not args.no_pipelined:
-        halves = [w.pack(k, 2, pinned=True, layout="islands4") for k in range(2)]
-        assert sum(h.n_queries for h in halves) == nq
-        cx2 = ob.Context(params, device=local)
-        pair = [(cx, halves[0]), (cx2, halves[1])]
+    n_ctx = max(2, args.e2e_contexts)
+    if not args.no_pipelined and not c4:
+        parts = [w.pack(k, n_ctx, pinned=True, layout="islands4") for k in range(n_ctx)]
+        assert sum(h.n_queries for h in parts) == nq
+        extra = [ob.Context(params, device=local) for _ in range(n_ctx - 1)]
+        pair = list(zip([cx] + extra, parts))
         for _ in range(max(1, args.warmup // 2)):
             for c_, b_ in pair:
                 c_.submit(b_)
             found2 = sum(int((c_.wait().best["t_tx"] >= 0).sum()) for c_, _ in pair)
-        assert found2 == found, "two half batches find the same ORFs as the whole one"
+        assert found2 == found, "the locus shards find the same ORFs as the whole batch"
         barrier()
         t0 = time.perf_counter()
         for _ in range(args.steps):
@@ -297,11 +395,12 @@ def ours(args):
                 c_.wait(copy=False)
         barrier()
         e2e2_ms = (time.perf_counter() - t0) * 1e3
-        cx2.close()
+        for c_ in extra:
+            c_.close()
 
     # max over ranks of the timed regions, sum of the units
     tt = torch.tensor([dev_ms, wall_ms, e2e_ms, e2e2_ms if e2e2_ms is not None else 0.0], dtype=torch.float64, device="cuda")
-    cnt = torch.tensor([nq, launches, found, nt_sum], dtype=torch.int64, device="cuda")
+    cnt = torch.tensor([nq, launches, found, nt_sum, dig_lo, dig_hi], dtype=torch.int64, device="cuda")
     per_rank = None
     if world > 1:
         mine = tt.clone()
@@ -309,13 +408,16 @@ def ours(args):
         dist.all_gather(gathered, mine)   # per-rank device / e2e times beside the max: shards differ (distinct loci per rank)
         per_rank = {"device_ms_per_step": [round(float(g[0]) / args.steps, 4) for g in gathered],
                     "e2e_ms_per_step": [round(float(g[2]) / args.steps, 4) for g in gathered],
-                    "e2e_two_contexts_ms_per_step": [round(float(g[3]) / args.steps, 4) for g in gathered]}
+                    "e2e_pipelined_ms_per_step": [round(float(g[3]) / args.steps, 4) for g in gathered]}
         dist.all_reduce(tt, op=dist.ReduceOp.MAX)
         dist.all_reduce(cnt)
     dev_ms, wall_ms, e2e_ms, e2e2_ms = [float(x) for x in tt.tolist()]
-    nq_all, launches_all, found_all, nt_all = [int(x) for x in cnt.tolist()]
+    nq_all, launches_all, found_all, nt_all, dig_lo, dig_hi = [int(x) for x in cnt.tolist()]
+    digest = "%08x%08x" % (dig_hi & 0xFFFFFFFF, dig_lo & 0xFFFFFFFF)
     align = None
-    if args.align_pairs > 0 and world > 1:
+    if c4:
+        pass
+    elif args.align_pairs > 0 and world > 1:
         # C5 pairs are independent: dealt to the ranks by DP cells (ob.shard_pairs), no exchange step; device time = max over ranks
         import numpy as np
         t = time.time()
@@ -344,7 +446,7 @@ def ours(args):
         t = time.time()
         align = alignment_leg(cx, args.align_pairs)
         log("alignment leg: %.1f s, %.1f GCUPS" % (time.time() - t, align["gcups"]))
-    return dict(e2e2_ms=e2e2_ms, per_rank=per_rank, align=align, rank=rank, world=world, cfg=cfg, nq=nq, nq_all=nq_all, nt_sum=nt_sum, dev_ms=dev_ms, wall_ms=wall_ms, e2e_ms=e2e_ms,
+    return dict(stage_ms_alone=stage_ms_alone, alone_ms=alone_ms, c4=c4, digest=digest, nt_all=nt_all, e2e2_ms=e2e2_ms, per_rank=per_rank, align=align, rank=rank, world=world, cfg=cfg, nq=nq, nq_all=nq_all, nt_sum=nt_sum, dev_ms=dev_ms, wall_ms=wall_ms, e2e_ms=e2e_ms,
                 e2e_dev=e2e_dev, stage_ms=stage_ms, launches=launches_all, found=found_all, clocks=clocks, h2d=batch.h2d_bytes,
                 d2h=d2h_bytes, windows=int(batch.arrays["seq"].nbytes), n_templates=w.count("templates"),
                 n_bundles=w.count("active_bundles"))
@@ -473,12 +575,17 @@ def measured_peak():
 
 
 def profiled_traffic(kernel):
-    """DRAM bytes per launch of `kernel` from the committed ncu --set full capture of this workload (profiles/)."""
+    """DRAM bytes per launch of `kernel` from the committed ncu --set full capture of this workload (profiles/r02_traffic.json,
+    written by tools/ncu_summary.py from a capture of THIS build: the file records the digest of the CUDA sources it was
+    taken from and is refused when that differs from the sources next to this script)."""
     try:
-        t = json.load(open(os.path.join(ROOT, "profiles", "r01_traffic.json")))[kernel]
-        return t["dram_bytes_per_launch"], t["source"]
-    except Exception:
-        return None, None
+        doc = json.load(open(os.path.join(ROOT, "profiles", "r02_traffic.json")))
+        if doc.get("source_digest") != source_digest():
+            return None, "profiles/r02_traffic.json was captured from other sources (digest %s, these are %s): refused" % (doc.get("source_digest"), source_digest())
+        t = doc["kernels"][kernel]
+        return t["dram_bytes_per_launch"], doc.get("source")
+    except Exception as e:
+        return None, "no usable profiles/r02_traffic.json (%s)" % e
 
 
 def emit(line):
@@ -509,8 +616,12 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--verbose-shard", action="store_true", help="log the largest loci of this rank's shard")
     ap.add_argument("--seed-offset", type=int, default=0, help="generate the shard rank k of a multi-GPU run would get (k = offset)")
-    ap.add_argument("--no-pipelined", action="store_true", help="skip the two-context end-to-end leg")
+    ap.add_argument("--no-pipelined", action="store_true", help="skip the multi-context end-to-end leg")
+    ap.add_argument("--e2e-contexts", type=int, default=4, help="contexts (locus shards) of the pipelined end-to-end leg")
     ap.add_argument("--align-pairs", type=int, default=50000, help="protein pairs of the alignment leg (0 = skip; configs[4] = 1000000)")
+    ap.add_argument("--config", default="c2", choices=["c2", "c4"], help="c2 = BASELINE.json configs[1] (the driver's metric; weak scaling); "
+                    "c4 = configs[3], one 2 M-query workload sharded by locus over the GPUs (strong scaling)")
+    ap.add_argument("--no-cli", action="store_true", help="skip the whole-process CLI leg")
     ap.add_argument("--only-align", action="store_true", help="development: run the alignment leg alone and print its object")
     args = ap.parse_args()
     quiet_stdout()
@@ -533,26 +644,34 @@ def main():
     e2e_api = "orfx_submit + orfx_wait on a pinned host batch (include/orfx.h)"
     e2e_single = {"value": e2e_value, "ms_per_step": m["e2e_ms"] / K}
     e2e_step_ms = m["e2e_ms"] / K
-    if m.get("e2e2_ms"):   # two contexts, half of the loci each: same calls, same bytes; uploads overlap kernels
+    if m.get("e2e2_ms"):   # several contexts, a share of the loci each: same calls, same bytes; uploads overlap kernels
         v2 = m["nq_all"] / (m["e2e2_ms"] / K / 1e3)
+        nc = max(2, args.e2e_contexts)
         if v2 > e2e_value:
             e2e_value, e2e_step_ms = v2, m["e2e2_ms"] / K
-            e2e_api = ("orfx_submit + orfx_wait on pinned host batches (include/orfx.h), two contexts per GPU with half of the loci each, "
-                       "submitted back to back: the upload of one half overlaps the kernels of the other")
-        e2e_single["two_contexts"] = {"value": v2, "ms_per_step": m["e2e2_ms"] / K}
+            e2e_api = ("orfx_submit + orfx_wait on pinned host batches (include/orfx.h), %d contexts per GPU with a locus shard each, "
+                       "submitted back to back: the upload of one shard overlaps the kernels of another" % nc)
+        e2e_single["pipelined_contexts"] = {"contexts": nc, "value": v2, "ms_per_step": m["e2e2_ms"] / K}
     peak, peak_src = measured_peak()
-    scan_ms = m["stage_ms"].get("codon_scan", 0.0) / K
-    alg_bytes = ALG_BYTES_PER_NT * m["nt_sum"]
+    c4 = m["c4"]
+    nt_per_launch = m["nt_sum"]          # spliced query nucleotides one rank's codon_scan launch covers
+    scan_in_step_ms = m["stage_ms"].get("codon_scan", 0.0) / K
+    scan_ms = m["stage_ms_alone"].get("codon_scan", 0.0) / K      # one launch over all transcripts, nothing beside it
+    planes_ms = m["stage_ms_alone"].get("base_planes", 0.0) / K
+    alg_bytes = ALG_BYTES_PER_NT * nt_per_launch
     achieved = alg_bytes / (scan_ms / 1e3) / 1e9 if scan_ms > 0 else 0.0
+    stage_achieved = alg_bytes / ((scan_ms + planes_ms) / 1e3) / 1e9 if scan_ms + planes_ms > 0 else 0.0
     traffic, traffic_src = profiled_traffic("codon_scan_kernel")
     dominant = max(m["stage_ms"], key=lambda k: m["stage_ms"][k]) if m["stage_ms"] else None
     line = {
         "metric": "query transcripts/sec", "value": value, "unit": "transcripts/s", "n_gpus": m["world"], "steps": K,
-        "warmup": args.warmup, "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "warmup": args.warmup, "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "strong" if c4 else "weak", "vs_baseline": None,
         "dtype": "int32", "data": "synthetic",
-        "config": {"workload": "GENCODE-scale synthetic (BASELINE.json configs[1])", "mode": MODE,
-                   "query_transcripts_per_gpu": m["nq"], "templates_after_dedup": m["n_templates"], "bundles": m["n_bundles"],
-                   "genome": "%d x %d bp random, planted ORFs, seed %d+rank" % (m["cfg"]["chroms"], m["cfg"]["chrom_len"], C2["seed"]),
+        "config": {"workload": "long-read novel-isoform scale synthetic (BASELINE.json configs[3]): one workload, loci dealt to the GPUs by shard_bundles" if c4
+                   else "GENCODE-scale synthetic (BASELINE.json configs[1])", "mode": MODE,
+                   "query_transcripts_per_gpu": m["nq"], "query_transcripts_total": m["nq_all"], "templates_after_dedup": m["n_templates"], "bundles": m["n_bundles"],
+                   "best_digest": m["digest"],
+                   "genome": "%d x %d bp random, planted ORFs, seed %d%s" % (m["cfg"]["chroms"], m["cfg"]["chrom_len"], m["cfg"]["seed"], "" if c4 else "+rank"),
                    "spliced_query_nt_per_gpu": m["nt_sum"], "sequence_upload_bytes_per_gpu": m["windows"], "sequence_format": "islands, 4-bit base codes (ORFX_SEQ_NT4)",
                    "parallelism": "locus shards, one per GPU, no collective", "orfs_found": m["found"],
                    "l2": "inputs larger than L2 (windows + chains + masks > 126 MB); no explicit flush",
@@ -564,18 +683,45 @@ def main():
                 "single_context": e2e_single, "api": e2e_api},
         "gpu_launches": m["launches"],
         "clocks": m["clocks"],
+        # `achieved` / `frac` follow the contract: ALGORITHMIC bytes (1.25 B per spliced nucleotide) over the kernel's
+        # launch time against the measured HBM copy bandwidth.  That is a streaming-equivalent rate, not DRAM utilisation: the
+        # kernel reads bit planes, so its real DRAM traffic (`traffic`, ncu) is a fraction of the algorithmic bytes (`dram_frac`)
+        # and what limits it is instruction issue on the ALU pipe (`limiter`).  `stage` is the same figure for the whole
+        # bases -> masks stage (plane build + scan).
         "roofline": {"bound": "hbm", "kernel": "codon_scan_kernel", "achieved": achieved, "peak": peak, "unit": "GB/s",
-                     "frac": achieved / peak if peak else None, "traffic": traffic, "traffic_source": traffic_src, "peak_source": peak_src,
+                     "frac": achieved / peak if peak else None, "algorithmic_frac": achieved / peak if peak else None,
+                     "traffic": traffic, "traffic_source": traffic_src, "peak_source": peak_src,
+                     "dram_frac": (traffic / (scan_ms / 1e3) / 1e9 / peak) if (traffic and scan_ms > 0 and peak) else None,
+                     "limiter": "instruction issue (ALU pipe), not DRAM: see profiles/r02_ncu_full.md",
                      "algorithmic_bytes_per_launch": alg_bytes, "kernel_ms": scan_ms,
-                     "share_of_step": scan_ms / ms_per_step if ms_per_step else None, "dominant_stage": dominant},
+                     "kernel_ms_source": "CUDA events around the codon_scan_kernel launch, mean of %d launches on the resident batch with every kernel alone on "
+                                         "one stream (orfx_debug_set serialize); `in_step` is the same stage inside the timed steps" % K,
+                     "in_step": {"ms": scan_in_step_ms, "achieved": alg_bytes / (scan_in_step_ms / 1e3) / 1e9 if scan_in_step_ms > 0 else None,
+                                 "frac": (alg_bytes / (scan_in_step_ms / 1e3) / 1e9 / peak) if (scan_in_step_ms > 0 and peak) else None,
+                                 "note": "two launches (heavy bundles' transcripts first), the heavy bundles' rescue kernel running beside the second"},
+                     "share_of_step": scan_in_step_ms / ms_per_step if ms_per_step else None,
+                     "stage": {"kernels": "base_planes_nt4_kernel + codon_scan_kernel", "ms": scan_ms + planes_ms, "achieved": stage_achieved,
+                               "frac": stage_achieved / peak if peak else None},
+                     "dominant_stage": dominant,
+                     "dominant": {"stage": dominant, "ms": m["stage_ms"][dominant] / K if dominant else None, "bound": "latency (dependent chain walks and mask scans; "
+                                  "low DRAM and SM throughput, see profiles/r02_ncu_full.md)", "share_of_step": (m["stage_ms"][dominant] / K) / ms_per_step if dominant else None}},
         "stages_ms": {k: v / K for k, v in m["stage_ms"].items()},
+        "stages_ms_alone": {k: v / K for k, v in m["stage_ms_alone"].items()},
+        "ms_per_step_serialized": m["alone_ms"] / K,
         "stages_note": "heavy_bundles (CTA-per-bundle kernels of the titin-class loci) runs on a side stream beside fill_rows / rescue_score: the stages overlap and do not add up to the step",
     }
     if m["align"] is not None:
         line["alignment"] = m["align"]
     if m.get("per_rank"):
         line["per_rank"] = m["per_rank"]
-    if m["world"] == 1 and not args.no_cpu_baseline:
+        dm = m["per_rank"]["device_ms_per_step"]
+        line["per_rank"]["imbalance_max_over_mean"] = max(dm) / (sum(dm) / len(dm)) if dm and sum(dm) > 0 else None
+    if m["world"] == 1 and not c4 and not args.no_cli:
+        try:
+            line["cli"] = cli_leg(generate(dict(C2), "c2"))
+        except Exception as e:
+            line["cli"] = {"error": str(e)}
+    if m["world"] == 1 and not args.no_cpu_baseline and not c4:
         try:
             line["cpu_baseline"] = cpu_baseline_leg()
         except Exception as e:   # the checker being absent must not hide the GPU number

@@ -52,9 +52,11 @@ struct StripeIO {
 // Per-warp shared memory of the DP (dynamic shared memory, one WarpSmem per warp).
 struct WarpSmem {
     uint2 prof[24][32];     // query profile: prof[r][lane] = the lane's CPL scores against target residue r, one int8 each
-    int   t_ring[128];      // target residues: previous, current and next 32-row chunk
+    int   tl[96];           // target residues of rows blk - 32 .. blk + 63 (blk = first step of the current 32-step block), as byte
+                            // offsets into a lane's profile column (residue * 256): a step's lookup is base + immediate, no index math
     int2  in_ring[32];      // left edge {H(i, c_base-1), F(i, c_base) + (q+e)} of the current chunk (borders for the first stripe)
     int2  out_ring[64];     // right edge of the rows lane 31 finished, until their chunk is stored
+    int   q_ring[32][8];    // last stripe: H of the CPL columns of the lane that owns column qlen-1, one row per step of the block
 };
 constexpr int PAD_SCORE8 = -128;    // score of the virtual columns right of the query's end: padded cells stay below
                                     // H(i, qlen-1) - (gapo+gape) per column as long as gapo+gape <= 64
@@ -103,7 +105,8 @@ __device__ __forceinline__ void dp_stripe(const int* __restrict__ s_mat, WarpSme
             }
             ws.prof[r][lane] = make_uint2(lo, hi);
         }
-        ws.t_ring[lane] = lane < tlen ? t[lane] : 0;   // rows 0..31; every block loads the chunk after its own
+        ws.tl[lane] = 0;                                      // rows -32 .. -1
+        ws.tl[32 + lane] = lane < tlen ? t[lane] << 8 : 0;     // rows 0 .. 31; every block loads the chunk after its own
     }
     // lane-local column of qlen-1 (last stripe only)
     const int jq_lane = (qlen - 1 - c_base) / CPL, jq = (qlen - 1 - c_base) % CPL;
@@ -113,6 +116,9 @@ __device__ __forceinline__ void dp_stripe(const int* __restrict__ s_mat, WarpSme
     uint2 sc = make_uint2(0, 0);                           // profile entry of this lane's next row
     const int n_steps = tlen + 31;
     int stored = 0;                                        // rows of the right edge already in global memory
+    int blk = 0;                                           // first step of the current block
+    const char* const prof_lane = reinterpret_cast<const char*>(&ws.prof[0][lane]);
+    const int* const tl_lane = ws.tl + 33 - lane;          // tl_lane[s - blk] = profile offset of the lane's row at step s + 1
 
     auto step = [&](int s, auto full_tag) {
         constexpr bool FULL = decltype(full_tag)::value;
@@ -124,7 +130,7 @@ __device__ __forceinline__ void dp_stripe(const int* __restrict__ s_mat, WarpSme
         const int i = s - lane;
         if (FULL || (i >= 0 && i < tlen)) {
             const uint2 cur = sc;
-            sc = ws.prof[ws.t_ring[(i + 1) & 127]][lane];   // next step's scores: off the critical path
+            sc = *reinterpret_cast<const uint2*>(prof_lane + tl_lane[s - blk]);   // next step's scores: off the critical path
             int f = f_in, d = diag, h = 0, m0 = NEG_INF, m1 = NEG_INF;
 #pragma unroll
             for (int k = 0; k < CPL; k++) {
@@ -142,15 +148,19 @@ __device__ __forceinline__ void dp_stripe(const int* __restrict__ s_mat, WarpSme
             diag = h_left;
             h_out = h; f_out = f;
             if (!FULL && i == tlen - 1) mte = max(mte, rowmax);
+            // mqe / score need H(i, qlen-1): column jq of lane jq_lane, a runtime register index.  That lane parks its CPL values
+            // (vector stores, no select chain on the ALU pipe); the block's 32 rows are picked out of shared memory afterwards.
             if (LAST && lane == jq_lane) {
-                int hq = hp[0];
+                int* qr = ws.q_ring[(s - blk) & 31];
+                if (CPL == 8) { *reinterpret_cast<int4*>(qr) = make_int4(hp[0], hp[1], hp[2], hp[3]); *reinterpret_cast<int4*>(qr + 4) = make_int4(hp[4], hp[5], hp[6], hp[7]); }
+                else if (CPL == 4) *reinterpret_cast<int4*>(qr) = make_int4(hp[0], hp[1], hp[2], hp[3]);
+                else {
 #pragma unroll
-                for (int k = 1; k < CPL; k++) hq = jq == k ? hp[k] : hq;
-                mqe = max(mqe, hq);
-                if (i == tlen - 1) score = hq;
+                    for (int k = 0; k < CPL; k++) qr[k] = hp[k];
+                }
             }
         } else if (i == -1) {
-            sc = ws.prof[ws.t_ring[0]][lane];   // the step before the lane's first row
+            sc = *reinterpret_cast<const uint2*>(prof_lane + ws.tl[32]);   // the step before the lane's first row (first block: row 0 is tl[32])
         }
         if (!LAST && lane == 31 && (FULL || s >= 31)) ws.out_ring[(s - 31) & 63] = make_int2(h_out, f_out);
     };
@@ -169,10 +179,12 @@ __device__ __forceinline__ void dp_stripe(const int* __restrict__ s_mat, WarpSme
                 e.y = r < tlen ? __ldcg(io.f_in + r) : 0;
             }
             __syncwarp();   // every lane is done with the rings' previous contents
-            ws.t_ring[(r + 32) & 127] = r + 32 < tlen ? t[r + 32] : 0;
+            blk = s0;
+            if (s0 > 0) { const int a = ws.tl[32 + lane], b = ws.tl[64 + lane]; ws.tl[lane] = a; ws.tl[32 + lane] = b; }   // the window moves on by 32 rows
+            ws.tl[64 + lane] = r + 32 < tlen ? t[r + 32] << 8 : 0;
             ws.in_ring[lane] = e;
             __syncwarp();
-            if (s0 == 0 && lane == 0) sc = ws.prof[ws.t_ring[0]][0];
+            if (s0 == 0 && lane == 0) sc = *reinterpret_cast<const uint2*>(prof_lane + ws.tl[32]);
         }
         if (s0 >= 32 && s0 + 33 <= tlen) {   // rows s - lane of the whole block lie in [1, tlen - 2]
 #pragma unroll 4
@@ -180,6 +192,15 @@ __device__ __forceinline__ void dp_stripe(const int* __restrict__ s_mat, WarpSme
         } else {
             const int ue = min(32, n_steps - s0);
             for (int u = 0; u < ue; u++) step(s0 + u, std::false_type{});
+        }
+        if (LAST) {   // column qlen-1 of the rows lane jq_lane worked on in this block: lane u looks at step s0 + u
+            __syncwarp();
+            const int i = s0 + lane - jq_lane;
+            if (s0 + lane < n_steps && i >= 0 && i < tlen) {
+                const int hq = ws.q_ring[lane][jq];
+                mqe = max(mqe, hq);
+                if (i == tlen - 1) score = hq;
+            }
         }
         if (!LAST) {
             // rows finished by lane 31 so far; store them 32 at a time, coalesced

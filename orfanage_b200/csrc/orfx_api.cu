@@ -5,6 +5,7 @@
 #include "orfx_buffers.cuh"
 
 #include <climits>
+#include <nvtx3/nvToolsExt.h>   // header-only; ranges show up in Nsight timelines, cost nothing without a tool attached
 #include <cstdio>
 #include <cstring>
 #include <string>
@@ -26,7 +27,7 @@ int launch_heavy_rescue(const DevBatch& B, const DevRows& R, const orfx_params& 
                         cudaStream_t s);
 int launch_select(const DevBatch& B, const DevRows& R, const orfx_params& P, int n_queries, orfx_best* best_out, int32_t* ord_scratch, int4* key_scratch,
                   cudaStream_t s);
-void launch_codon_scan(const DevBatch& B, int64_t n_tiles, int n_sm, cudaStream_t stream);
+void launch_codon_scan(const DevBatch& B, int64_t n_tiles, int which, cudaStream_t stream);
 int launch_base_planes(const DevBatch& B, cudaStream_t stream);
 int launch_clean_templates(const DevBatch& B, int n_queries, int rescue, int non_aug, uint8_t* keep, int32_t* out_start, int32_t* out_end, cudaStream_t s);
 int launch_count_pairs(const DevBatch& B, int64_t* cnt, int64_t* scan_tmp, cudaStream_t s);
@@ -88,6 +89,7 @@ struct orfx_ctx {
     float ms_align = 0;
     int64_t n_aa = 0;
     int hb_max_segs = HB_MAX_SEGS, hb_max_pairs = HB_MAX_PAIRS;   // orfx_debug_set
+    bool serialize = false;            // orfx_debug_set "serialize": one scan launch, heavy rescue after it (per-kernel timings without overlap)
     bool allow_empty_chains = false;   // compare batches (orfx_score_pairs): a query without a CDS is legal there
     // rows
     DBuf r_i32[16], r_f32[3], r_u8[3], r_order, d_best, r_ext[2];
@@ -236,8 +238,9 @@ int upload_batch(orfx_ctx* c, const orfx_batch* b, bool overlap = false) {
     return ORFX_OK;
 }
 
-void stage_begin(orfx_ctx* c, int st, cudaStream_t s = nullptr) { cudaEventRecord(c->st_ev[st][0], s ? s : c->stream); }
-void stage_end(orfx_ctx* c, int st, cudaStream_t s = nullptr) { cudaEventRecord(c->st_ev[st][1], s ? s : c->stream); }
+// a stage = a CUDA event pair on the stream it is launched on (orfx_kernel_times) + an NVTX range around its launches
+void stage_begin(orfx_ctx* c, int st, cudaStream_t s = nullptr) { nvtxRangePushA(STAGE_NAME[st]); cudaEventRecord(c->st_ev[st][0], s ? s : c->stream); }
+void stage_end(orfx_ctx* c, int st, cudaStream_t s = nullptr) { cudaEventRecord(c->st_ev[st][1], s ? s : c->stream); nvtxRangePop(); }
 
 // the whole path on the resident batch; leaves results in device memory
 int run_path(orfx_ctx* c) {
@@ -257,7 +260,7 @@ int run_path(orfx_ctx* c) {
     stage_end(c, ST_PREP);
     stage_begin(c, ST_COUNT);
     c->n_launches += launch_count_rows(B, c->d_cnt_rows.as<int64_t>(), c->d_scan_tmp.as<int64_t>(), c->d_heavy.as<int32_t>(), c->d_heavy_count.as<unsigned>(),
-                                       c->n_sm, s, c->side_stream, c->ev_fork[0], c->ev_join[0]);
+                                       c->n_sm, s, c->serialize ? s : c->side_stream, c->ev_fork[0], c->ev_join[0]);
     stage_end(c, ST_COUNT);
     if (c->P.align_enabled && c->P.has_reference && B.seq_bytes > 0 && !B.tx_aa_off)
         return fail(ORFX_E_STATE, "params.align_enabled was set after the batch was uploaded: upload it again");
@@ -319,7 +322,7 @@ int run_path(orfx_ctx* c) {
     // The heavy bundles (titin-class loci, ~1 % of the bundles, a fifth of the chain work) have their own CTA-per-bundle
     // kernels over disjoint queries / rows; they run on the side stream next to the thread-per-query / thread-per-row
     // kernels, which leave most of the GPU's latency-hiding capacity unused.
-    cudaStream_t side = c->side_stream;
+    cudaStream_t side = c->serialize ? s : c->side_stream;
     stage_begin(c, ST_FILL);
     CU(cudaEventRecord(c->ev_fork[1], s));
     CU(cudaStreamWaitEvent(side, c->ev_fork[1], 0));
@@ -333,20 +336,32 @@ int run_path(orfx_ctx* c) {
         c->n_launches += launch_base_planes(B, s);
     }
     stage_end(c, ST_PLANES);
-    stage_begin(c, ST_SCAN);   // the codon_scan_kernel launch alone: this is the roofline's kernel time
-    if (c->P.has_reference) {
-        launch_codon_scan(B, tiles, c->n_sm, s);
-        if (tiles > 0) c->n_launches++;
+    // The codon scan, in two launches: the transcripts of the heavy (titin-class) bundles first -- a quarter of the
+    // nucleotides -- so that their rescue kernel (latency-bound, on the side stream) runs beside the scan of everything else
+    // (issue-bound) instead of after it.  ST_SCAN covers both launches: the roofline's kernel time.  (orfx_debug_set
+    // "serialize": one launch, and every kernel on the one stream -- per-kernel times without anything beside them.)
+    const bool scan = c->P.has_reference && tiles > 0, split = scan && !c->serialize;
+    stage_begin(c, ST_SCAN);
+    if (scan) { launch_codon_scan(B, tiles, split ? 1 : 0, s); c->n_launches++; }
+    if (split) {
+        CU(cudaEventRecord(c->ev_fork[2], s));             // masks of the heavy bundles ready
+        CU(cudaStreamWaitEvent(side, c->ev_fork[2], 0));   // (heavy_fill is already ahead of it on the side stream)
+        stage_begin(c, ST_HEAVY, side);
+        c->n_launches += launch_heavy_rescue(B, R, c->P, c->d_heavy.as<int32_t>(), c->d_heavy_count.as<unsigned>(), c->n_sm, side);
+        stage_end(c, ST_HEAVY, side);
+        launch_codon_scan(B, tiles, 2, s); c->n_launches++;
     }
     stage_end(c, ST_SCAN);
     stage_begin(c, ST_TRANSLATE);
     if (align) c->n_launches += launch_translate(B, c->d_tables.as<TranslateTables>(), c->n_aa, s);
     stage_end(c, ST_TRANSLATE);
-    CU(cudaEventRecord(c->ev_fork[2], s));                 // masks ready
-    CU(cudaStreamWaitEvent(side, c->ev_fork[2], 0));       // (heavy_fill is already ahead of it on the side stream)
-    stage_begin(c, ST_HEAVY, side);
-    c->n_launches += launch_heavy_rescue(B, R, c->P, c->d_heavy.as<int32_t>(), c->d_heavy_count.as<unsigned>(), c->n_sm, side);
-    stage_end(c, ST_HEAVY, side);
+    if (!split) {
+        CU(cudaEventRecord(c->ev_fork[2], s));
+        CU(cudaStreamWaitEvent(side, c->ev_fork[2], 0));
+        stage_begin(c, ST_HEAVY, side);
+        c->n_launches += launch_heavy_rescue(B, R, c->P, c->d_heavy.as<int32_t>(), c->d_heavy_count.as<unsigned>(), c->n_sm, side);
+        stage_end(c, ST_HEAVY, side);
+    }
     CU(cudaEventRecord(c->ev_join[2], side));
     stage_begin(c, ST_RESCUE);
     c->n_launches += launch_rescue_score(B, R, c->P, s);
@@ -513,13 +528,19 @@ int orfx_submit(orfx_ctx* c, const orfx_batch* batch) {
     if (!c) return fail(ORFX_E_INVALID, "null ctx");
     CU(cudaSetDevice(c->device));
     CU(cudaEventRecord(c->ev[0], c->stream));
+    nvtxRangePushA("orfx_submit: upload");
     int rc = upload_batch(c, batch, true);
+    nvtxRangePop();
     if (rc) return rc;
     CU(cudaEventRecord(c->ev[1], c->stream));
+    nvtxRangePushA("orfx_submit: path");
     rc = run_path(c);
+    nvtxRangePop();
     if (rc) return rc;
     CU(cudaEventRecord(c->ev[2], c->stream));
+    nvtxRangePushA("orfx_submit: download");
     rc = download_results(c);
+    nvtxRangePop();
     if (rc) return rc;
     CU(cudaEventRecord(c->ev[3], c->stream));
     c->pending = true;
@@ -673,6 +694,7 @@ int orfx_debug_set(orfx_ctx* c, const char* key, int64_t value) {
     const std::string k(key);
     if (k == "hb_max_segs") { if (value < 0 || value > HB_MAX_SEGS) return fail(ORFX_E_INVALID, "hb_max_segs out of range"); c->hb_max_segs = (int)value; }
     else if (k == "hb_max_pairs") { if (value < 0 || value > HB_MAX_PAIRS) return fail(ORFX_E_INVALID, "hb_max_pairs out of range"); c->hb_max_pairs = (int)value; }
+    else if (k == "serialize") c->serialize = value != 0;
     else return fail(ORFX_E_INVALID, "unknown debug key " + k);
     return ORFX_OK;
 }
@@ -703,7 +725,7 @@ int orfx_clean_templates(orfx_ctx* c, const orfx_batch* batch, int rescue, orfx_
     CU(c->d_clean_keep.ensure((size_t)nq + 4)); CU(c->d_clean_s.ensure((size_t)nq * 4 + 4)); CU(c->d_clean_e.ensure((size_t)nq * 4 + 4));
     c->n_launches += launch_fill_tiles(B, s);
     c->n_launches += launch_base_planes(B, s);
-    launch_codon_scan(B, tiles, c->n_sm, s);
+    launch_codon_scan(B, tiles, 0, s);
     if (tiles > 0) c->n_launches++;
     c->n_launches += launch_clean_templates(B, (int)nq, rescue, c->P.non_aug, c->d_clean_keep.as<uint8_t>(), c->d_clean_s.as<int32_t>(),
                                             c->d_clean_e.as<int32_t>(), s);

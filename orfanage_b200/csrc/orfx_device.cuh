@@ -71,6 +71,7 @@ struct DevRows {
     int32_t *aln_q0, *aln_qn, *aln_max, *aln_score, *aln_mqe, *aln_mte;
 };
 
+static constexpr uint8_t BUNDLE_HEAVY = 4;     // bundle_need bit: a transcript of the bundle has more than HEAVY_TX_SEGS segments (pipeline.cu)
 static constexpr int HB_MAX_SEGS = 9216;      // heavy-bundle kernels (pipeline.cu): capacity of the shared-memory stage
 static constexpr int HB_MAX_PAIRS = 8192;
 static constexpr int SCAN_TILE_WORDS = 16;     // mask words (32 spliced positions each) per codon-scan run (one thread)

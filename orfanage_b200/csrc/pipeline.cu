@@ -178,7 +178,6 @@ __global__ void __launch_bounds__(256) tx_prep_kernel(DevBatch B, int64_t* cnt_q
 // below, which stage the bundle's chains in shared memory; the thread-per-query / thread-per-row
 // kernels skip them.
 constexpr int HEAVY_TX_SEGS = 32;
-constexpr uint8_t BUNDLE_HEAVY = 4;
 
 __global__ void bundle_prep_kernel(DevBatch B, int32_t* heavy_list, unsigned* heavy_count) {
     int b = blockIdx.x * blockDim.x + threadIdx.x;

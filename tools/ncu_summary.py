@@ -1,9 +1,10 @@
 #!/usr/bin/env python3
 """Markdown summary of an `ncu --set full` report: one row per kernel (first captured launch of each name).
 
-usage: ncu_summary.py report.ncu-rep [title]  > profiles/xyz.md
-Prints the table and a JSON line with DRAM bytes (read + write) per launch, which bench.py reads from
-profiles/r01_traffic.json.
+usage: ncu_summary.py report.ncu-rep [title] [traffic.json]  > profiles/xyz.md
+Prints the table and a JSON line with DRAM bytes (read + write) per launch.  With a third argument the same numbers are
+written as the traffic file bench.py reads (profiles/r02_traffic.json), stamped with the digest of the CUDA sources in
+this tree (bench.source_digest): bench.py refuses the file when the sources have changed since the capture.
 """
 import csv
 import io
@@ -14,7 +15,7 @@ import sys
 METRICS = ["dram__bytes_read.sum", "dram__bytes_write.sum", "gpu__dram_throughput.avg.pct_of_peak_sustained_elapsed", "gpu__time_duration.sum",
            "launch__registers_per_thread", "lts__t_sector_hit_rate.pct", "sm__pipe_alu_cycles_active.avg.pct_of_peak_sustained_active",
            "sm__pipe_fma_cycles_active.avg.pct_of_peak_sustained_active", "sm__throughput.avg.pct_of_peak_sustained_elapsed",
-           "sm__warps_active.avg.pct_of_peak_sustained_active", "smsp__inst_executed.sum"]
+           "sm__warps_active.avg.pct_of_peak_sustained_active", "smsp__issue_active.avg.pct_of_peak_sustained_active", "smsp__inst_executed.sum"]
 SCALE = {"byte": 1, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
 
 
@@ -48,6 +49,13 @@ def main():
         traffic[name] = int(tot)
     print()
     print("DRAM traffic per launch (read + write), bytes: " + json.dumps(traffic))
+    if len(sys.argv) > 3:
+        import os
+        sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+        import bench
+        doc = {"source": "%s (ncu --set full, dram__bytes_read.sum + dram__bytes_write.sum, first captured launch of each kernel)" % title,
+               "source_digest": bench.source_digest(), "kernels": {k: {"dram_bytes_per_launch": v} for k, v in traffic.items()}}
+        json.dump(doc, open(sys.argv[3], "w"), indent=1, sort_keys=True)
 
 
 if __name__ == "__main__":
