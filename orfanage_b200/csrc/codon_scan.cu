@@ -148,15 +148,12 @@ __device__ __forceinline__ void win_append(Win& w, const uint4& lo, const uint4&
 }
 }  // namespace
 
-// which: 0 = every transcript; 1 = only the transcripts of heavy (titin-class) bundles; 2 = only the others.  The path
-// scans the heavy bundles first, so that their rescue kernel can start beside the scan of everything else.
-__global__ void __launch_bounds__(CSCAN_THREADS) codon_scan_kernel(DevBatch B, int64_t n_tiles, int which) {
+__global__ void __launch_bounds__(CSCAN_THREADS) codon_scan_kernel(DevBatch B, int64_t n_tiles) {
     __shared__ uint32_t s_out[2][SCAN_TILE_WORDS][CSCAN_THREADS];
     const int tid = threadIdx.x;
     const int64_t tile = (int64_t)blockIdx.x * CSCAN_THREADS + tid;
     if (tile >= n_tiles) return;
     const int tx = B.tile_tx[tile];
-    if (which != 0 && (((B.bundle_need[B.tx_bundle[tx]] & BUNDLE_HEAVY) != 0) != (which == 1))) return;
     // --overhang: the scanned chain is the exon chain with its first segment started xlo bases earlier and its last
     // one ended xhi bases later (the usable flanks, orfx_batch::tx_ext_lo / tx_ext_hi)
     const int xlo = B.tx_ext_lo ? B.tx_ext_lo[tx] : 0, xhi = B.tx_ext_hi ? B.tx_ext_hi[tx] : 0;
@@ -262,10 +259,10 @@ int launch_base_planes(const DevBatch& B, cudaStream_t stream) {
     return 1;
 }
 
-void launch_codon_scan(const DevBatch& B, int64_t n_items, int which, cudaStream_t stream) {
+void launch_codon_scan(const DevBatch& B, int64_t n_items, int, cudaStream_t stream) {
     if (n_items <= 0) return;
     const int64_t grid = (n_items + CSCAN_THREADS - 1) / CSCAN_THREADS;
-    codon_scan_kernel<<<(unsigned)grid, CSCAN_THREADS, 0, stream>>>(B, n_items, which);
+    codon_scan_kernel<<<(unsigned)grid, CSCAN_THREADS, 0, stream>>>(B, n_items);
 }
 
 }  // namespace orfx

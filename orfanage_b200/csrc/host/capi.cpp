@@ -11,7 +11,7 @@ struct orfxh_workload {
     Fasta fasta;
     Transcriptome tr;
     std::vector<int> active;
-    std::map<std::string, int> tid_classes;
+    TidClasses tid_classes;
     std::vector<std::unique_ptr<PackedBatch>> packed;
 };
 

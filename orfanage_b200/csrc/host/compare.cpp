@@ -122,7 +122,7 @@ int run_orfcompare(const Options& opt, const Backend& be) {
     for (Tx& t : tr.txs) t.build_cds();
     std::vector<int> active;
     for (int bi = 0; bi < (int)tr.bundles.size(); bi++) if (tr.bundles[bi].has_template && tr.bundles[bi].has_query) active.push_back(bi);
-    std::map<std::string, int> tid_classes;
+    TidClasses tid_classes;
     build_tid_classes(tr, tid_classes);
     PackedBatch pb;
     pack_bundles(tr, active, false, tid_classes, pb, be.host_alloc, be.host_free, false, PACK_COMPARE);

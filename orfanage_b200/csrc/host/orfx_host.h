@@ -182,15 +182,17 @@ struct PackedBatch {
 // chain is packed as ORFX_TX_QUERY with its exon chain and CDS bounds, everything else as ORFX_TX_SKIP.
 // mode = PACK_COMPARE builds a *compare batch* (orfx_score_pairs): queries and templates both carry their
 // CDS chain, no sequence.
+// equal transcript_id strings <=> equal value, one entry per transcript of tr.txs (orfx_batch::tx_tid_class)
+typedef std::vector<int> TidClasses;
 enum { PACK_EVAL = 0, PACK_CLEAN = 1, PACK_COMPARE = 2 };
 char nt_complement(char c);   // ntComplement (gclib), IUPAC, case preserving
 void pack_bundles(const Transcriptome& tr, const std::vector<int>& bundle_ids, bool keep_all_cds,
-                  const std::map<std::string, int>& tid_classes, PackedBatch& out,
+                  const TidClasses& tid_classes, PackedBatch& out,
                   void* (*alloc)(size_t) = nullptr, void (*dealloc)(void*) = nullptr, bool islands = true, int mode = PACK_EVAL,
                   bool nt4 = false,    // nt4: islands as 4-bit base codes (ORFX_SEQ_NT4), half the upload
                   int overhang = 0, bool spliced_overhang = false,   // --overhang flanks (TX::extend_seq, Transcriptome.cpp:342-399)
                   bool template_seq = false);   // islands also cover the template CDS segments (orfx_params::align_enabled)
-void build_tid_classes(const Transcriptome& tr, std::map<std::string, int>& out);
+void build_tid_classes(const Transcriptome& tr, TidClasses& out);
 // greedy longest-processing-time split of active bundles over n shards
 void shard_bundles(const Transcriptome& tr, const std::vector<int>& active, int n, std::vector<std::vector<int>>& shards);
 

@@ -7,6 +7,7 @@
 #include <chrono>
 #include <cstring>
 #include <thread>
+#include <unordered_map>
 
 namespace orfx {
 
@@ -60,8 +61,11 @@ orfx_batch PackedBatch::view() const {
     return b;
 }
 
-void build_tid_classes(const Transcriptome& tr, std::map<std::string, int>& out) {
-    for (const Tx& t : tr.txs) out.insert(std::make_pair(t.tid, (int)out.size()));
+void build_tid_classes(const Transcriptome& tr, TidClasses& out) {
+    std::unordered_map<std::string, int> ids;
+    ids.reserve(tr.txs.size() * 2);
+    out.resize(tr.txs.size());
+    for (size_t i = 0; i < tr.txs.size(); i++) out[i] = ids.emplace(tr.txs[i].tid, (int)ids.size()).first->second;
 }
 
 namespace {
@@ -170,7 +174,7 @@ QFlank query_flanks(const Fasta& fa, const Fasta::Seq& chrom, const Bundle& b, c
 // Two passes: size everything, take one arena from the allocator, fill.  Sequence bytes (the bulk) are
 // copied by several threads.  islands = true uploads only the bases under query exons.
 void pack_bundles(const Transcriptome& tr, const std::vector<int>& bundle_ids, bool keep_all_cds,
-                  const std::map<std::string, int>& tid_classes, PackedBatch& out,
+                  const TidClasses& tid_classes, PackedBatch& out,
                   void* (*alloc)(size_t), void (*dealloc)(void*), bool islands, int mode, bool nt4, int overhang, bool spliced_overhang, bool template_seq) {
     const bool clean_mode = mode == PACK_CLEAN, compare_mode = mode == PACK_COMPARE;
     template_seq = template_seq && mode == PACK_EVAL;
@@ -267,7 +271,7 @@ void pack_bundles(const Transcriptome& tr, const std::vector<int>& bundle_ids, b
             out.tx_seg_off[x + 1] = sg;
             out.tx_cds_start[x] = (as_templ || (clean_mode && kind == ORFX_TX_QUERY)) ? t.cds_start : 0;
             out.tx_cds_end[x] = (as_templ || (clean_mode && kind == ORFX_TX_QUERY)) ? t.cds_end : 0;
-            out.tx_tid_class[x] = tid_classes.at(t.tid);
+            out.tx_tid_class[x] = tid_classes[(size_t)(b.first + i)];
             if (overhang > 0) { const QFlank& f = fl[j][(size_t)i]; out.tx_ext_lo[x] = f.lo; out.tx_ext_hi[x] = f.hi; out.tx_ext_flags[x] = f.flags; }
         }
         out.bundle_tx_off[j + 1] = x;
@@ -424,7 +428,7 @@ static size_t clean_cds(const Options& opt, Transcriptome& tr, const Backend& be
     tr.bundleup(opt.use_id, (uint32_t)opt.overhang);
     std::vector<int> ids;
     for (int bi = 0; bi < (int)tr.bundles.size(); bi++) ids.push_back(bi);
-    std::map<std::string, int> tid_classes;
+    TidClasses tid_classes;
     build_tid_classes(tr, tid_classes);
     PackedBatch pb;
     pack_bundles(tr, ids, false, tid_classes, pb, be.host_alloc, be.host_free, true, PACK_CLEAN, true, opt.overhang, opt.spliced_overhang);
@@ -549,7 +553,7 @@ int run_orfanage(const Options& opt, const Backend& be) {
     fprintf(stderr, "starting main evaluation\n");
     std::vector<int> active;
     for (int bi = 0; bi < (int)tr.bundles.size(); bi++) if (tr.bundles[bi].has_template && tr.bundles[bi].has_query) active.push_back(bi);
-    std::map<std::string, int> tid_classes;
+    TidClasses tid_classes;
     build_tid_classes(tr, tid_classes);
 
     std::vector<std::vector<int>> shard_ids;

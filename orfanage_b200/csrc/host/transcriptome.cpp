@@ -310,26 +310,58 @@ void read_gtf(const std::string& path, std::vector<GtfRecord>& out) {
 
     const size_t base = out.size();
     std::vector<GtfWork> work;
+    auto in_parallel = [&](unsigned n, const std::function<void(unsigned)>& f) {
+        if (n <= 1) { for (unsigned k = 0; k < n; k++) f(k); return; }
+        std::vector<std::thread> th;
+        for (unsigned k = 0; k < n; k++) th.emplace_back(f, k);
+        for (auto& t : th) t.join();
+    };
     if (nthr == 1) {
         for (auto& r : slices[0].out) out.push_back(std::move(r));
         work = std::move(slices[0].work);
     } else {
-        std::unordered_map<std::string, size_t> by_id;
-        size_t total = 0;
-        for (auto& S : slices) total += S.out.size();
-        out.reserve(base + total); work.reserve(total); by_id.reserve(total * 2);
-        for (auto& S : slices) {
+        // A transcript whose rows straddle a cut (or are scattered over the file) appears in several slices: its first
+        // appearance keeps the record, later ones are folded into it in file order.  Every slice looks its ids up in the
+        // slices before it (concurrently); the records are then moved to their final places concurrently as well.
+        struct Dup { int slice; size_t idx; };
+        std::vector<std::vector<Dup>> first(nthr);        // per record: where it appeared first, slice -1 = here
+        std::vector<std::vector<size_t>> place(nthr);     // per record: its index among the kept records of the slice
+        std::vector<size_t> kept(nthr, 0);
+        in_parallel(nthr, [&](unsigned k) {
+            GtfSlice& S = slices[k];
+            first[k].assign(S.out.size(), Dup{-1, 0});
+            place[k].assign(S.out.size(), 0);
+            size_t n = 0;
             for (size_t i = 0; i < S.out.size(); i++) {
-                GtfRecord& r = S.out[i];
-                auto it = by_id.find(r.tid);
-                if (it == by_id.end()) {
-                    by_id.emplace(r.tid, out.size());
-                    out.push_back(std::move(r));
-                    work.push_back(std::move(S.work[i]));
-                    continue;
+                for (unsigned j = 0; j < k; j++) {
+                    auto it = slices[j].by_id.find(S.out[i].tid);
+                    if (it != slices[j].by_id.end()) { first[k][i] = Dup{(int)j, it->second}; break; }
                 }
-                GtfRecord& g = out[it->second];   // a transcript whose rows straddle a cut (or are scattered)
-                GtfWork& gw = work[it->second - base];
+                if (first[k][i].slice < 0) place[k][i] = n++;
+            }
+            kept[k] = n;
+        });
+        std::vector<size_t> at(nthr + 1, 0);
+        for (unsigned k = 0; k < nthr; k++) at[k + 1] = at[k] + kept[k];
+        out.resize(base + at[nthr]);
+        work.resize(at[nthr]);
+        in_parallel(nthr, [&](unsigned k) {
+            GtfSlice& S = slices[k];
+            for (size_t i = 0; i < S.out.size(); i++) {
+                if (first[k][i].slice >= 0) continue;
+                out[base + at[k] + place[k][i]] = std::move(S.out[i]);
+                work[at[k] + place[k][i]] = std::move(S.work[i]);
+            }
+        });
+        for (unsigned k = 1; k < nthr; k++) {   // the (rare) later appearances, in file order
+            GtfSlice& S = slices[k];
+            for (size_t i = 0; i < S.out.size(); i++) {
+                const Dup d = first[k][i];
+                if (d.slice < 0) continue;
+                const size_t gi = at[(size_t)d.slice] + place[(size_t)d.slice][d.idx];
+                GtfRecord& g = out[base + gi];
+                GtfWork& gw = work[gi];
+                GtfRecord& r = S.out[i];
                 if (!g.has_gid && r.has_gid) { g.has_gid = true; g.gid = r.gid; }
                 if (S.has_tx_row[i]) { g.source = r.source; for (auto& a : r.attrs) g.attrs.push_back(std::move(a)); }
                 g.exons.insert(g.exons.end(), r.exons.begin(), r.exons.end());
@@ -338,24 +370,29 @@ void read_gtf(const std::string& path, std::vector<GtfRecord>& out) {
                 gw.frames.insert(gw.frames.end(), S.work[i].frames.begin(), S.work[i].frames.end());
             }
         }
+        in_parallel(nthr, [&](unsigned k) { GtfSlice().by_id.swap(slices[k].by_id); std::vector<GtfRecord>().swap(slices[k].out); std::vector<GtfWork>().swap(slices[k].work); });
     }
-    for (size_t i = base; i < out.size(); i++) {
-        GtfRecord& r = out[i];
-        GtfWork& w = work[i - base];
-        if (r.exons.empty()) r.exons = w.cds;
-        std::sort(r.exons.begin(), r.exons.end());
-        if (r.has_cds) {
-            uint32_t mn = UINT32_MAX, mx = 0;
-            size_t imn = 0, imx = 0;
-            for (size_t k = 0; k < w.cds.size(); k++) {
-                if (w.cds[k].first < mn) { mn = w.cds[k].first; imn = k; }
-                if (w.cds[k].second > mx) { mx = w.cds[k].second; imx = k; }
+    const size_t n_new = out.size() - base;
+    in_parallel(n_new > 20000 ? nthr : 1u, [&](unsigned k) {
+        const unsigned parts = n_new > 20000 ? nthr : 1u;
+        for (size_t i = base + n_new * k / parts; i < base + n_new * (k + 1) / parts; i++) {
+            GtfRecord& r = out[i];
+            GtfWork& w = work[i - base];
+            if (r.exons.empty()) r.exons = w.cds;
+            std::sort(r.exons.begin(), r.exons.end());
+            if (r.has_cds) {
+                uint32_t mn = UINT32_MAX, mx = 0;
+                size_t imn = 0, imx = 0;
+                for (size_t c = 0; c < w.cds.size(); c++) {
+                    if (w.cds[c].first < mn) { mn = w.cds[c].first; imn = c; }
+                    if (w.cds[c].second > mx) { mx = w.cds[c].second; imx = c; }
+                }
+                r.cd_start = mn;
+                r.cd_end = mx;
+                r.cd_phase = r.strand == '-' ? w.frames[imx] : w.frames[imn];
             }
-            r.cd_start = mn;
-            r.cd_end = mx;
-            r.cd_phase = r.strand == '-' ? w.frames[imx] : w.frames[imn];
         }
-    }
+    });
 }
 
 // ---- Transcriptome -----------------------------------------------------------------------------
@@ -367,44 +404,64 @@ void Transcriptome::add(const std::string& gtf_path, bool is_templ, bool coding_
         auto ins = seqids_.insert(std::make_pair(r.seqname, (int)seqnames.size()));
         if (ins.second) seqnames.push_back(r.seqname);
     }
-    for (const GtfRecord& r : recs) {
-        if (coding_only && !r.has_cds) continue;
-        if (r.exons.empty()) continue;
-        Tx t;   // TX::TX(GffObj*), cpp:11-82
-        if (r.has_cds) {
-            t.is_coding = true;
-            t.cds_start = (int)r.cd_start;
-            t.cds_end = (int)r.cd_end;
-            switch (r.cd_phase) {
-                case '0': t.cds_phase = 0; break;
-                case '1': t.cds_phase = 1; break;
-                case '2': t.cds_phase = 2; break;
-                case '3': t.cds_phase = 3; break;
-                case '.': t.cds_phase = 0; break;
-                default: throw std::runtime_error("Unknown CDS phase for the initial segment");
+    // TX::TX(GffObj*), cpp:11-82, for every record that is kept; the conversions are independent of each other
+    std::vector<size_t> keep;
+    keep.reserve(recs.size());
+    for (size_t i = 0; i < recs.size(); i++) if (!(coding_only && !recs[i].has_cds) && !recs[i].exons.empty()) keep.push_back(i);
+    const size_t base = txs.size();
+    txs.resize(base + keep.size());
+    std::vector<int> seqid_of(recs.size());
+    for (size_t i : keep) seqid_of[i] = seqids_[recs[i].seqname];
+    auto convert = [&](size_t k0, size_t k1, std::string* err) {
+        try {
+            for (size_t k = k0; k < k1; k++) {
+                const GtfRecord& r = recs[keep[k]];
+                Tx& t = txs[base + k];
+                if (r.has_cds) {
+                    t.is_coding = true;
+                    t.cds_start = (int)r.cd_start;
+                    t.cds_end = (int)r.cd_end;
+                    switch (r.cd_phase) {
+                        case '0': t.cds_phase = 0; break;
+                        case '1': t.cds_phase = 1; break;
+                        case '2': t.cds_phase = 2; break;
+                        case '3': t.cds_phase = 3; break;
+                        case '.': t.cds_phase = 0; break;
+                        default: throw std::runtime_error("Unknown CDS phase for the initial segment");
+                    }
+                }
+                t.is_templ = is_templ;
+                t.id = (int)(base + k);
+                t.tid = r.tid;
+                t.gid = r.has_gid ? r.gid : r.tid;
+                t.seqid = seqid_of[keep[k]];
+                t.strand = r.strand;
+                t.source = r.source;
+                t.cds_source = r.source;
+                t.exons.reserve(r.exons.size());
+                for (auto& e : r.exons) { Seg s; s.s = (int)e.first; s.e = (int)e.second; s.phase = 0; t.exons.push_back(s); }
+                bool tr_id = false;
+                for (const auto& kv : r.attrs) {
+                    if (kv.second.empty()) continue;
+                    std::string name = kv.first;
+                    if (name == "transcriptID") { if (tr_id) continue; tr_id = true; }
+                    if (name == "transcript_id" && !tr_id) { name = "transcriptID"; tr_id = true; }
+                    if (name == "geneID" || name == "gene_id") continue;
+                    if (!t.attrs.insert(std::make_pair(name, kv.second)).second)
+                        throw std::runtime_error("Attribute: " + name + " already exists");
+                }
             }
-        }
-        t.is_templ = is_templ;
-        t.id = (int)txs.size();
-        t.tid = r.tid;
-        t.gid = r.has_gid ? r.gid : r.tid;
-        t.seqid = seqids_[r.seqname];
-        t.strand = r.strand;
-        t.source = r.source;
-        t.cds_source = r.source;
-        for (auto& e : r.exons) { Seg s; s.s = (int)e.first; s.e = (int)e.second; s.phase = 0; t.exons.push_back(s); }
-        bool tr_id = false;
-        for (const auto& kv : r.attrs) {
-            if (kv.second.empty()) continue;
-            std::string name = kv.first;
-            if (name == "transcriptID") { if (tr_id) continue; tr_id = true; }
-            if (name == "transcript_id" && !tr_id) { name = "transcriptID"; tr_id = true; }
-            if (name == "geneID" || name == "gene_id") continue;
-            if (!t.attrs.insert(std::make_pair(name, kv.second)).second)
-                throw std::runtime_error("Attribute: " + name + " already exists");
-        }
-        txs.push_back(std::move(t));
+        } catch (const std::exception& e) { *err = e.what(); }
+    };
+    const unsigned nthr = keep.size() > 20000 ? std::min(16u, std::max(1u, std::thread::hardware_concurrency())) : 1u;
+    std::vector<std::string> errs(nthr);
+    if (nthr == 1) convert(0, keep.size(), &errs[0]);
+    else {
+        std::vector<std::thread> th;
+        for (unsigned k = 0; k < nthr; k++) th.emplace_back(convert, keep.size() * k / nthr, keep.size() * (k + 1) / nthr, &errs[k]);
+        for (auto& t : th) t.join();
     }
+    for (const std::string& e : errs) if (!e.empty()) throw std::runtime_error(e);   // the first failing slice in file order
 }
 
 void Transcriptome::build_cds_chains() {
@@ -414,18 +471,34 @@ void Transcriptome::correct_chain_len() {
     for (Tx& t : txs) if (t.is_coding && t.is_templ) t.correct_chain_len();
 }
 void Transcriptome::sort(bool use_id) {
-    // std::sort on purpose: the reference sorts with libstdc++'s introsort, whose order among
-    // equal keys decides the bundle-internal transcript order (SURVEY.md §7 hard parts).
+    // std::sort on purpose: the reference sorts with libstdc++'s introsort, whose order among equal keys decides the
+    // bundle-internal transcript order (SURVEY.md §7 hard parts).  The permutation introsort produces depends only on the
+    // initial order and the comparison outcomes, so it is computed on small key records (the fields TX::operator< reads,
+    // Transcriptome.h:668-684) and the transcripts -- strings, maps, chains -- are moved once, into place.
+    struct Key { int seqid, start, end; char strand; uint32_t idx; const std::string* gid; };
+    std::vector<Key> keys(txs.size());
+    for (size_t i = 0; i < txs.size(); i++) keys[i] = Key{txs[i].seqid, txs[i].start(), txs[i].end(), txs[i].strand, (uint32_t)i, &txs[i].gid};
+    auto less = [](const Key& a, const Key& b) {
+        if (a.seqid != b.seqid) return a.seqid < b.seqid;
+        if (a.strand != b.strand) return a.strand < b.strand;
+        if (a.start != b.start) return a.start < b.start;
+        if (a.end != b.end) return a.end < b.end;
+        return false;
+    };
     if (use_id) {
-        std::sort(txs.begin(), txs.end(), [](const Tx& a, const Tx& b) {
+        std::sort(keys.begin(), keys.end(), [&](const Key& a, const Key& b) {
             if (a.seqid != b.seqid) return a.seqid < b.seqid;
             if (a.strand != b.strand) return a.strand < b.strand;
-            if (a.gid != b.gid) return a.gid < b.gid;
-            return tx_less(a, b);
+            if (*a.gid != *b.gid) return *a.gid < *b.gid;
+            return less(a, b);
         });
     } else {
-        std::sort(txs.begin(), txs.end(), tx_less);
+        std::sort(keys.begin(), keys.end(), less);
     }
+    std::vector<Tx> sorted;
+    sorted.reserve(txs.size());
+    for (size_t i = 0; i < keys.size(); i++) sorted.emplace_back(std::move(txs[keys[i].idx]));
+    txs.swap(sorted);
 }
 void Transcriptome::set_cds_as_exons() {
     for (Tx& t : txs) {

@@ -89,7 +89,7 @@ struct orfx_ctx {
     float ms_align = 0;
     int64_t n_aa = 0;
     int hb_max_segs = HB_MAX_SEGS, hb_max_pairs = HB_MAX_PAIRS;   // orfx_debug_set
-    bool serialize = false;            // orfx_debug_set "serialize": one scan launch, heavy rescue after it (per-kernel timings without overlap)
+    bool serialize = false;            // orfx_debug_set "serialize": every kernel on the one stream (per-kernel times with nothing beside them)
     bool allow_empty_chains = false;   // compare batches (orfx_score_pairs): a query without a CDS is legal there
     // rows
     DBuf r_i32[16], r_f32[3], r_u8[3], r_order, d_best, r_ext[2];
@@ -336,32 +336,19 @@ int run_path(orfx_ctx* c) {
         c->n_launches += launch_base_planes(B, s);
     }
     stage_end(c, ST_PLANES);
-    // The codon scan, in two launches: the transcripts of the heavy (titin-class) bundles first -- a quarter of the
-    // nucleotides -- so that their rescue kernel (latency-bound, on the side stream) runs beside the scan of everything else
-    // (issue-bound) instead of after it.  ST_SCAN covers both launches: the roofline's kernel time.  (orfx_debug_set
-    // "serialize": one launch, and every kernel on the one stream -- per-kernel times without anything beside them.)
-    const bool scan = c->P.has_reference && tiles > 0, split = scan && !c->serialize;
-    stage_begin(c, ST_SCAN);
-    if (scan) { launch_codon_scan(B, tiles, split ? 1 : 0, s); c->n_launches++; }
-    if (split) {
-        CU(cudaEventRecord(c->ev_fork[2], s));             // masks of the heavy bundles ready
-        CU(cudaStreamWaitEvent(side, c->ev_fork[2], 0));   // (heavy_fill is already ahead of it on the side stream)
-        stage_begin(c, ST_HEAVY, side);
-        c->n_launches += launch_heavy_rescue(B, R, c->P, c->d_heavy.as<int32_t>(), c->d_heavy_count.as<unsigned>(), c->n_sm, side);
-        stage_end(c, ST_HEAVY, side);
-        launch_codon_scan(B, tiles, 2, s); c->n_launches++;
-    }
+    stage_begin(c, ST_SCAN);   // the codon_scan_kernel launch alone: this is the roofline's kernel time
+    if (c->P.has_reference && tiles > 0) { launch_codon_scan(B, tiles, 0, s); c->n_launches++; }
     stage_end(c, ST_SCAN);
     stage_begin(c, ST_TRANSLATE);
     if (align) c->n_launches += launch_translate(B, c->d_tables.as<TranslateTables>(), c->n_aa, s);
     stage_end(c, ST_TRANSLATE);
-    if (!split) {
-        CU(cudaEventRecord(c->ev_fork[2], s));
-        CU(cudaStreamWaitEvent(side, c->ev_fork[2], 0));
-        stage_begin(c, ST_HEAVY, side);
-        c->n_launches += launch_heavy_rescue(B, R, c->P, c->d_heavy.as<int32_t>(), c->d_heavy_count.as<unsigned>(), c->n_sm, side);
-        stage_end(c, ST_HEAVY, side);
-    }
+    // (Measured and dropped: scanning the heavy bundles' transcripts in a first launch so that heavy_rescue_kernel could start
+    // beside the scan of the rest.  The kernels only trade SM time with each other: the step went from 1.34 to 1.37 ms.)
+    CU(cudaEventRecord(c->ev_fork[2], s));                 // masks ready
+    CU(cudaStreamWaitEvent(side, c->ev_fork[2], 0));       // (heavy_fill is already ahead of it on the side stream)
+    stage_begin(c, ST_HEAVY, side);
+    c->n_launches += launch_heavy_rescue(B, R, c->P, c->d_heavy.as<int32_t>(), c->d_heavy_count.as<unsigned>(), c->n_sm, side);
+    stage_end(c, ST_HEAVY, side);
     CU(cudaEventRecord(c->ev_join[2], side));
     stage_begin(c, ST_RESCUE);
     c->n_launches += launch_rescue_score(B, R, c->P, s);

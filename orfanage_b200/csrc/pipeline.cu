@@ -83,7 +83,58 @@ int launch_exclusive_scan(const int64_t* in, int64_t* out, int64_t* tmp, int64_t
     scan_add_kernel<<<(unsigned)nb, SCAN_THREADS, 0, s>>>(out, tmp, n);
     return 3;
 }
-int64_t scan_tmp_elems(int64_t n) { return (n + SCAN_BLOCK - 1) / SCAN_BLOCK + 1; }
+int64_t scan_tmp_elems(int64_t n) { return 3 * ((n + SCAN_BLOCK - 1) / SCAN_BLOCK + 1); }   // room for scan3
+
+// Three independent exclusive scans of the same length in three launches instead of nine (the prep stage is a chain of
+// small kernels: launch latency is what it costs).  blockIdx.y picks the array.
+namespace {
+struct Scan3 { const int64_t* in[3]; int64_t* out[3]; };
+__global__ void __launch_bounds__(SCAN_THREADS) scan3_local_kernel(Scan3 a, int64_t* block_sums, int64_t nb, int64_t n) {
+    const int w = blockIdx.y;
+    const int64_t base = (int64_t)blockIdx.x * SCAN_BLOCK + (int64_t)threadIdx.x * SCAN_ITEMS;
+    const int64_t* in = a.in[w];
+    int64_t* out = a.out[w];
+    int64_t v[SCAN_ITEMS], sum = 0;
+#pragma unroll
+    for (int i = 0; i < SCAN_ITEMS; i++) { v[i] = base + i < n ? in[base + i] : 0; sum += v[i]; }
+    int64_t total;
+    int64_t ex = block_exclusive_scan(sum, &total);
+#pragma unroll
+    for (int i = 0; i < SCAN_ITEMS; i++) { if (base + i < n) out[base + i] = ex; ex += v[i]; }
+    if (threadIdx.x == 0) block_sums[(int64_t)w * (nb + 1) + blockIdx.x] = total;
+}
+__global__ void __launch_bounds__(SCAN_THREADS) scan3_tops_kernel(Scan3 a, int64_t* block_sums, int64_t nb, int64_t n) {
+    const int w = blockIdx.x;
+    int64_t* bs = block_sums + (int64_t)w * (nb + 1);
+    int64_t carry = 0;
+    for (int64_t c = 0; c < nb; c += SCAN_THREADS) {
+        int64_t i = c + threadIdx.x;
+        int64_t v = i < nb ? bs[i] : 0, total;
+        int64_t ex = block_exclusive_scan(v, &total);
+        if (i < nb) bs[i] = carry + ex;
+        carry += total;
+    }
+    if (threadIdx.x == 0) a.out[w][n] = carry;
+}
+__global__ void __launch_bounds__(SCAN_THREADS) scan3_add_kernel(Scan3 a, const int64_t* block_sums, int64_t nb, int64_t n) {
+    const int w = blockIdx.y;
+    const int64_t base = (int64_t)blockIdx.x * SCAN_BLOCK + (int64_t)threadIdx.x * SCAN_ITEMS;
+    const int64_t add = block_sums[(int64_t)w * (nb + 1) + blockIdx.x];
+    int64_t* out = a.out[w];
+#pragma unroll
+    for (int i = 0; i < SCAN_ITEMS; i++) if (base + i < n) out[base + i] += add;
+}
+}  // namespace
+int launch_exclusive_scan3(const int64_t* in0, int64_t* out0, const int64_t* in1, int64_t* out1, const int64_t* in2, int64_t* out2, int64_t* tmp, int64_t n,
+                           cudaStream_t s) {
+    if (n <= 0) { cudaMemsetAsync(out0, 0, 8, s); cudaMemsetAsync(out1, 0, 8, s); cudaMemsetAsync(out2, 0, 8, s); return 0; }
+    const int64_t nb = (n + SCAN_BLOCK - 1) / SCAN_BLOCK;
+    Scan3 a{{in0, in1, in2}, {out0, out1, out2}};
+    scan3_local_kernel<<<dim3((unsigned)nb, 3), SCAN_THREADS, 0, s>>>(a, tmp, nb, n);
+    scan3_tops_kernel<<<3, SCAN_THREADS, 0, s>>>(a, tmp, nb, n);
+    scan3_add_kernel<<<dim3((unsigned)nb, 3), SCAN_THREADS, 0, s>>>(a, tmp, nb, n);
+    return 3;
+}
 
 // ------------------------------------------------------------------------------------------------
 // validation of a caller-supplied batch (include/orfx.h is a public seam: the host packer is not the only caller)
@@ -219,9 +270,7 @@ int launch_prep(const DevBatch& B, int64_t* cnt_q, int64_t* cnt_words, int64_t* 
     tx_prep_kernel<<<(unsigned)(((int64_t)B.n_tx * PREP_LANES + 255) / 256), 256, 0, s>>>(B, cnt_q, cnt_words, cnt_tiles); n++;
     cudaMemsetAsync(heavy_count, 0, sizeof(unsigned), s);
     bundle_prep_kernel<<<(B.n_bundles + 127) / 128, 128, 0, s>>>(B, heavy_list, heavy_count); n++;
-    n += launch_exclusive_scan(cnt_q, B.tx_q_off, scan_tmp, B.n_tx, s);
-    n += launch_exclusive_scan(cnt_words, B.tx_mask_off, scan_tmp, B.n_tx, s);
-    n += launch_exclusive_scan(cnt_tiles, B.tx_tile_off, scan_tmp, B.n_tx, s);
+    n += launch_exclusive_scan3(cnt_q, B.tx_q_off, cnt_words, B.tx_mask_off, cnt_tiles, B.tx_tile_off, scan_tmp, B.n_tx, s);
     fill_q_list_kernel<<<(B.n_tx + 255) / 256, 256, 0, s>>>(B); n++;
     return n;
 }
