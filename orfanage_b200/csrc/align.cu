@@ -45,8 +45,8 @@ struct AlnAcc { int gmax, mqe, mte, score; };
 struct StripeIO {
     const int32_t* h_in; const int32_t* f_in;      // nullptr for the first stripe
     int32_t* h_out; int32_t* f_out;                // nullptr for the last stripe
-    volatile unsigned long long* wait_flag; unsigned long long wait_base;
-    volatile unsigned long long* post_flag; unsigned long long post_base;
+    unsigned long long* wait_flag; unsigned long long wait_base;   // shared-memory progress counters, read and written with atomics
+    unsigned long long* post_flag; unsigned long long post_base;
 };
 
 // Per-warp shared memory of the DP (dynamic shared memory, one WarpSmem per warp).
@@ -172,7 +172,7 @@ __device__ __forceinline__ void dp_stripe(const int* __restrict__ s_mat, WarpSme
             if (!first_stripe) {
                 if (PIPE && s0 < tlen) {
                     const unsigned long long need = io.wait_base + (unsigned long long)min(s0 + 32, tlen);
-                    if (lane == 0) while (*io.wait_flag < need) __nanosleep(20);
+                    if (lane == 0) while (atomicAdd(io.wait_flag, 0ULL) < need) __nanosleep(20);
                     __syncwarp();
                 }
                 e.x = r < tlen ? __ldcg(io.h_in + r) : 0;
@@ -213,7 +213,7 @@ __device__ __forceinline__ void dp_stripe(const int* __restrict__ s_mat, WarpSme
                 if (PIPE) {
                     __threadfence_block();   // reader and writer are warps of one CTA; the edges go through L2 (.cg) on both sides
                     __syncwarp();
-                    if (lane == 0) *io.post_flag = io.post_base + (unsigned long long)min(stored, tlen);
+                    if (lane == 0) atomicExch(io.post_flag, io.post_base + (unsigned long long)min(stored, tlen));
                 }
             }
         }
@@ -291,15 +291,17 @@ align_kernel(const uint8_t* __restrict__ aa, int q_stride, int t_stride, const A
     int32_t* edge = cta_scratch + (long long)blockIdx.x * 8 * cta_stride;   // [pair parity][stripe parity][h|f][row]
     unsigned long long base = 0;
     for (unsigned k = 0; n_long > 0; k++) {
-        if (k >= 2) { if (lane == 0) while (*(volatile unsigned*)&s_pair_done[(k - 2) & 3] < k - 1) __nanosleep(40); __syncwarp(); }
+        if (k >= 2) { if (lane == 0) while (atomicAdd(&s_pair_done[(k - 2) & 3], 0u) < k - 1) __nanosleep(40); __syncwarp(); }
         if (wib == 0 && lane == 0) {
-            s_slot_ring[k & 7] = atomicAdd(counters, 1ULL);
+            atomicExch(&s_slot_ring[k & 7], atomicAdd(counters, 1ULL));
             __threadfence_block();
-            *(volatile unsigned*)&s_fetched = k + 1;
+            atomicExch(&s_fetched, k + 1);
         }
-        if (lane == 0) while (*(volatile unsigned*)&s_fetched < k + 1) __nanosleep(40);
+        if (lane == 0) while (atomicAdd(&s_fetched, 0u) < k + 1) __nanosleep(40);
         __syncwarp();
-        const unsigned long long slot = *(volatile unsigned long long*)&s_slot_ring[k & 7];
+        unsigned long long slot = 0;
+        if (lane == 0) slot = atomicAdd(&s_slot_ring[k & 7], 0ULL);
+        slot = __shfl_sync(0xffffffffu, slot, 0);
         if (slot >= (unsigned long long)n_long) break;
         const int pair = order[slot];
         const AlnPair pr = pairs[pair];
@@ -332,9 +334,9 @@ align_kernel(const uint8_t* __restrict__ aa, int q_stride, int t_stride, const A
                     __threadfence_block();
                     out_max[pair] = atomicExch(&a[0], 0); out_score[pair] = atomicExch(&a[1], NEG_INF);
                     out_mqe[pair] = atomicExch(&a[2], NEG_INF); out_mte[pair] = atomicExch(&a[3], NEG_INF);
-                    s_cnt[k & 3] = 0;
+                    atomicExch(&s_cnt[k & 3], 0u);
                     __threadfence_block();
-                    *(volatile unsigned*)&s_pair_done[k & 3] = k + 1;
+                    atomicExch(&s_pair_done[k & 3], k + 1);
                 }
             }
         }
