@@ -61,3 +61,32 @@ def test_full_size_output_is_byte_identical_to_the_reference(case):
         json.dump(record, open(os.path.join(out, "fullsize_parity_%s.json" % case), "w"), indent=1)
     assert record["gtf_identical"] and record["tsv_identical"], record
     assert record.get("cmp_gtf", True) and record.get("cmp_tsv", True), record
+
+
+def _n_gpus():
+    try:
+        import torch
+        return torch.cuda.device_count()
+    except Exception:
+        return 0
+
+
+@pytest.mark.skipif(_n_gpus() < 2, reason="needs more than one GPU on the box")
+@pytest.mark.parametrize("case", ["c4", "c2"])
+def test_multi_gpu_cli_is_byte_identical_to_the_reference(case):
+    """The product's own multi-GPU path -- shard_bundles (LPT) over --gpus 0,1,...,N-1, one host thread and one context per
+    device, results merged back into bundle order (host/runner.cpp) -- writes the same bytes as the reference."""
+    n = _n_gpus()
+    want = HASHES[case]
+    d = fs.generate(case, os.environ.get("ORFX_BENCH_DIR", "/tmp/orfx_bench"))
+    gpus = ",".join(str(k) for k in range(n))
+    t = time.time()
+    p = subprocess.run([ob.cli_path()] + fs.cli_args(case, "mgpu", ["--timing", "--gpus", gpus]), cwd=d, capture_output=True, text=True)
+    wall = time.time() - t
+    assert p.returncode == 0, p.stderr[-800:]
+    record = {"case": case, "gpus": gpus, "cli_wall_s": round(wall, 2), "gtf_identical": sha(os.path.join(d, "mgpu.gtf")) == want["gtf_sha256"],
+              "tsv_identical": sha(os.path.join(d, "mgpu.tsv")) == want["tsv_sha256"], "timing": [l for l in p.stderr.splitlines() if l.startswith("[timing]")]}
+    out = os.path.join(ROOT, "gpurun_out")
+    if os.path.isdir(out):
+        json.dump(record, open(os.path.join(out, "fullsize_parity_%s_%dgpu.json" % (case, n)), "w"), indent=1)
+    assert record["gtf_identical"] and record["tsv_identical"], record

@@ -4,6 +4,7 @@
 #   steps: tests[:<pytest -k expr>]   pytest -m gpu (whole suite, or a -k selection)
 #          smoke                      __graft_entry__.smoke()
 #          bench[:<extra args>]       python bench.py <extra args>  -> <tag>_bench.json
+#          mbench:<N>[:<extra args>]  the same under torchrun on N GPUs
 #          launches[:<extra args>]    ncu launch list (gpu__time_duration) of a short bench command
 #          full:<kernel regex>        ncu --set full of the matching kernels of a short bench command -> .ncu-rep
 #          sanitize:<tool>:<k expr>   compute-sanitizer --tool <memcheck|racecheck|synccheck|initcheck> over a pytest selection
@@ -21,8 +22,15 @@ for step in "$@"; do
     smoke)
       python -c "import __graft_entry__ as g; g.smoke()" > gpurun_out/${TAG}_smoke.log 2>&1; echo "smoke rc=$?" >> gpurun_out/${TAG}_smoke.log; tail -3 gpurun_out/${TAG}_smoke.log ;;
     bench)
-      python bench.py $arg > gpurun_out/${TAG}_bench.json 2> gpurun_out/${TAG}_bench.err; echo "rc=$?" >> gpurun_out/${TAG}_bench.err
-      tail -5 gpurun_out/${TAG}_bench.err; head -c 1500 gpurun_out/${TAG}_bench.json; echo ;;
+      label=$(echo "$arg" | grep -o "c4\|reference" | head -1); [ -n "$label" ] && label="_$label"
+      python bench.py $arg > gpurun_out/${TAG}_bench${label}.json 2> gpurun_out/${TAG}_bench${label}.err; echo "rc=$?" >> gpurun_out/${TAG}_bench${label}.err
+      tail -5 gpurun_out/${TAG}_bench${label}.err; head -c 1500 gpurun_out/${TAG}_bench${label}.json; echo ;;
+    mbench)     # mbench:<N>[:<extra args>]  bench.py under torchrun on N GPUs -> <tag>_bench_<N>gpu[_<label>].json
+      n=${arg%%:*}; rest=""; [ "$arg" != "$n" ] && rest=${arg#*:}
+      label=$(echo "$rest" | grep -o "c4" | head -1); [ -n "$label" ] && label="_$label"
+      python -m torch.distributed.run --nnodes=1 --nproc-per-node $n --master-addr 127.0.0.1 --master-port 29517 bench.py --gpus $n $rest \
+        > gpurun_out/${TAG}_bench_${n}gpu${label}.json 2> gpurun_out/${TAG}_bench_${n}gpu${label}.err; echo "rc=$?" >> gpurun_out/${TAG}_bench_${n}gpu${label}.err
+      tail -4 gpurun_out/${TAG}_bench_${n}gpu${label}.err; head -c 600 gpurun_out/${TAG}_bench_${n}gpu${label}.json; echo ;;
     launches)
       ncu --metrics gpu__time_duration.sum --clock-control none -c 1500 --csv --log-file gpurun_out/${TAG}_launches.csv $SHORT $arg > gpurun_out/${TAG}_ncu_launches.log 2>&1
       echo "launches rc=$?" ;;
