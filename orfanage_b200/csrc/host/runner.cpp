@@ -533,8 +533,11 @@ int run_orfanage(const Options& opt, const Backend& be) {
             s.ms_create = ms(c0, clk::now());
         });
     struct JoinAll { std::vector<std::thread>& t; ~JoinAll() { for (auto& x : t) if (x.joinable()) x.join(); } } join_ctx{ctx_threads};
-    Fasta fasta;
-    Transcriptome tr;
+    // The loaded annotation (several hundred thousand transcripts with their strings, maps and chains) and the mapped genome
+    // are left to the operating system when the process ends: tearing them down one object at a time costs a few hundred
+    // milliseconds that a command-line run has no use for.
+    Fasta& fasta = *new Fasta();
+    Transcriptome& tr = *new Transcriptome();
     prepare_transcriptome(opt, fasta, tr, true, &be);
     auto t1 = clk::now();
 

@@ -8,6 +8,7 @@
 #          launches[:<extra args>]    ncu launch list (gpu__time_duration) of a short bench command
 #          full:<kernel regex>        ncu --set full of the matching kernels of a short bench command -> .ncu-rep
 #          sanitize:<tool>:<k expr>   compute-sanitizer --tool <memcheck|racecheck|synccheck|initcheck> over a pytest selection
+#          sancase:<tool>             compute-sanitizer over tools/gpu/sanitize_case.py
 #          sh:<command>               anything else
 TAG=$1; shift
 mkdir -p gpurun_out
@@ -44,6 +45,9 @@ for step in "$@"; do
       tool=${arg%%:*}; sel=${arg#*:}
       compute-sanitizer --tool $tool --error-exitcode 9 python -m pytest tests -m gpu -q -x -k "$sel" > gpurun_out/${TAG}_sanitize_${tool}.log 2>&1
       echo "sanitize $tool rc=$?" >> gpurun_out/${TAG}_sanitize_${tool}.log; tail -6 gpurun_out/${TAG}_sanitize_${tool}.log ;;
+    sancase)    # sancase:<tool>  compute-sanitizer over tools/gpu/sanitize_case.py (every kernel once or twice, results checked)
+      compute-sanitizer --tool $arg --error-exitcode 9 python tools/gpu/sanitize_case.py > gpurun_out/${TAG}_sanitize_${arg}.log 2>&1
+      echo "sanitize $arg rc=$?" >> gpurun_out/${TAG}_sanitize_${arg}.log; tail -8 gpurun_out/${TAG}_sanitize_${arg}.log ;;
     sh)
       bash -c "$arg" ;;
     *) echo "unknown step $step" ;;
