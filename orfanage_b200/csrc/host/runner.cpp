@@ -6,6 +6,7 @@
 #include <atomic>
 #include <chrono>
 #include <cstring>
+#include <functional>
 #include <thread>
 #include <unordered_map>
 
@@ -211,20 +212,34 @@ void pack_bundles(const Transcriptome& tr, const std::vector<int>& bundle_ids, b
     // whole-window layout with --overhang: one more base on either side, so that the one-base flank of a transcript that
     // touches the end of its chromosome (a re-read of the edge base) has a place
     const int wpad = (!islands && overhang > 0) ? 1 : 0;
-    for (size_t j = 0; j < nb; j++) {
-        const Bundle& b = tr.bundles[bundle_ids[j]];
-        if (has_seq) {
-            if (islands) {
-                bundle_islands(tr, b, keep_all_cds, clean_mode, isl, flk(j), template_seq);
-                for (auto& iv : isl) bundle_bytes[j] += iv.second - iv.first + 1;
-                if (overhang > 0) for (int i = 0; i < b.count; i++) if (fl[j][(size_t)i].private_copy) bundle_bytes[j] += private_len(j, i, tr.txs[b.first + i]);
-                if (nt4) bundle_bytes[j] += bundle_bytes[j] & 1;   // bundles start on a byte boundary
-            } else bundle_bytes[j] = b.bend - b.bstart + 1 + 2 * wpad;
-            total_seq += (size_t)bundle_bytes[j];
+    // sizes per bundle (bases, transcripts, segments), by several threads: the island merge is a sort per bundle
+    std::vector<int32_t> bundle_ntx(nb, 0), bundle_nseg(nb, 0);
+    auto over_bundles = [&](const std::function<void(size_t, size_t)>& f) {
+        const unsigned nthr = nb > 2000 ? std::min(8u, std::max(1u, std::thread::hardware_concurrency())) : 1u;
+        if (nthr <= 1) { f(0, nb); return; }
+        std::vector<std::thread> th;
+        for (unsigned k = 0; k < nthr; k++) th.emplace_back(f, nb * k / nthr, nb * (k + 1) / nthr);
+        for (auto& t : th) t.join();
+    };
+    over_bundles([&](size_t j0, size_t j1) {
+        std::vector<std::pair<int, int>> il;
+        for (size_t j = j0; j < j1; j++) {
+            const Bundle& b = tr.bundles[bundle_ids[j]];
+            if (has_seq) {
+                if (islands) {
+                    bundle_islands(tr, b, keep_all_cds, clean_mode, il, flk(j), template_seq);
+                    for (auto& iv : il) bundle_bytes[j] += iv.second - iv.first + 1;
+                    if (overhang > 0) for (int i = 0; i < b.count; i++) if (fl[j][(size_t)i].private_copy) bundle_bytes[j] += private_len(j, i, tr.txs[b.first + i]);
+                    if (nt4) bundle_bytes[j] += bundle_bytes[j] & 1;   // bundles start on a byte boundary
+                } else bundle_bytes[j] = b.bend - b.bstart + 1 + 2 * wpad;
+            }
+            bundle_ntx[j] = b.count;
+            int64_t ns = 0;
+            for (int i = 0; i < b.count; i++) { const Tx& t = tr.txs[b.first + i]; ns += (int64_t)(((t.is_templ && !clean_mode) || compare_mode) ? t.cds.size() : t.exons.size()); }
+            bundle_nseg[j] = (int32_t)std::min<int64_t>(ns, INT32_MAX);
         }
-        total_tx += (size_t)b.count;
-        for (int i = 0; i < b.count; i++) { const Tx& t = tr.txs[b.first + i]; total_segs += ((t.is_templ && !clean_mode) || compare_mode) ? t.cds.size() : t.exons.size(); }
-    }
+    });
+    for (size_t j = 0; j < nb; j++) { total_seq += (size_t)bundle_bytes[j]; total_tx += (size_t)bundle_ntx[j]; total_segs += (size_t)bundle_nseg[j]; }
     if (total_tx > (size_t)INT32_MAX || total_segs > (size_t)INT32_MAX) throw std::runtime_error("batch too large for 32-bit transcript / segment indices: shard it");
     auto up = [](size_t x) { return (x + 255) & ~(size_t)255; };
     size_t o_seq = 0, o_seq_off = o_seq + up((nt4 ? (total_seq + 1) / 2 : total_seq) + 64), o_bstart = o_seq_off + up((nb + 1) * 8), o_btx = o_bstart + up(nb * 4 + 4),
@@ -250,32 +265,40 @@ void pack_bundles(const Transcriptome& tr, const std::vector<int>& bundle_ids, b
     out.seq_format = nt4 ? ORFX_SEQ_NT4 : ORFX_SEQ_RAW;
     out.tx_global.resize(total_tx);
 
-    int64_t so = 0;
-    int32_t x = 0, sg = 0;
+    // offsets per bundle, then the per-transcript / per-segment arrays by several threads
+    std::vector<int32_t> x_at(nb + 1, 0), sg_at(nb + 1, 0);
     out.seq_off[0] = 0; out.bundle_tx_off[0] = 0; out.tx_seg_off[0] = 0;
     for (size_t j = 0; j < nb; j++) {
-        const Bundle& b = tr.bundles[bundle_ids[j]];
-        so += bundle_bytes[j];
-        out.seq_off[j + 1] = so;
-        out.bundle_start[j] = b.bstart - wpad;
-        for (int i = 0; i < b.count; i++, x++) {
-            const Tx& t = tr.txs[b.first + i];
-            out.tx_global[(size_t)x] = b.first + i;
-            const uint8_t kind = tx_kind_of(t, keep_all_cds, clean_mode);
-            const bool as_templ = (t.is_templ && !clean_mode) || compare_mode;   // carries its CDS chain and bounds
-            if (kind == ORFX_TX_QUERY) out.n_queries++;
-            out.tx_kind[x] = kind;
-            out.tx_strand[x] = (uint8_t)t.strand;
-            const Chain& c = as_templ ? t.cds : t.exons;
-            for (const Seg& s : c) { out.segs[sg] = orfx_seg{s.s, s.e}; out.seg_phase[sg] = as_templ ? s.phase : 0; sg++; }
-            out.tx_seg_off[x + 1] = sg;
-            out.tx_cds_start[x] = (as_templ || (clean_mode && kind == ORFX_TX_QUERY)) ? t.cds_start : 0;
-            out.tx_cds_end[x] = (as_templ || (clean_mode && kind == ORFX_TX_QUERY)) ? t.cds_end : 0;
-            out.tx_tid_class[x] = tid_classes[(size_t)(b.first + i)];
-            if (overhang > 0) { const QFlank& f = fl[j][(size_t)i]; out.tx_ext_lo[x] = f.lo; out.tx_ext_hi[x] = f.hi; out.tx_ext_flags[x] = f.flags; }
-        }
-        out.bundle_tx_off[j + 1] = x;
+        out.seq_off[j + 1] = out.seq_off[j] + bundle_bytes[j];
+        x_at[j + 1] = x_at[j] + bundle_ntx[j];
+        sg_at[j + 1] = sg_at[j] + bundle_nseg[j];
+        out.bundle_tx_off[j + 1] = x_at[j + 1];
     }
+    std::vector<int64_t> nq_part(nb, 0);
+    over_bundles([&](size_t j0, size_t j1) {
+        for (size_t j = j0; j < j1; j++) {
+            const Bundle& b = tr.bundles[bundle_ids[j]];
+            out.bundle_start[j] = b.bstart - wpad;
+            int32_t x = x_at[j], sg = sg_at[j];
+            for (int i = 0; i < b.count; i++, x++) {
+                const Tx& t = tr.txs[b.first + i];
+                out.tx_global[(size_t)x] = b.first + i;
+                const uint8_t kind = tx_kind_of(t, keep_all_cds, clean_mode);
+                const bool as_templ = (t.is_templ && !clean_mode) || compare_mode;   // carries its CDS chain and bounds
+                if (kind == ORFX_TX_QUERY) nq_part[j]++;
+                out.tx_kind[x] = kind;
+                out.tx_strand[x] = (uint8_t)t.strand;
+                const Chain& c = as_templ ? t.cds : t.exons;
+                for (const Seg& sgm : c) { out.segs[sg] = orfx_seg{sgm.s, sgm.e}; out.seg_phase[sg] = as_templ ? sgm.phase : 0; sg++; }
+                out.tx_seg_off[x + 1] = sg;
+                out.tx_cds_start[x] = (as_templ || (clean_mode && kind == ORFX_TX_QUERY)) ? t.cds_start : 0;
+                out.tx_cds_end[x] = (as_templ || (clean_mode && kind == ORFX_TX_QUERY)) ? t.cds_end : 0;
+                out.tx_tid_class[x] = tid_classes[(size_t)(b.first + i)];
+                if (overhang > 0) { const QFlank& f = fl[j][(size_t)i]; out.tx_ext_lo[x] = f.lo; out.tx_ext_hi[x] = f.hi; out.tx_ext_flags[x] = f.flags; }
+            }
+        }
+    });
+    for (size_t j = 0; j < nb; j++) out.n_queries += nq_part[j];
     if (has_seq && total_seq) {   // Bundle::load_seq, cpp:821-830
         std::vector<const Fasta::Seq*> chrom(tr.seqnames.size(), nullptr);
         for (size_t k = 0; k < chrom.size(); k++) chrom[k] = tr.fasta->find(tr.seqnames[k]);

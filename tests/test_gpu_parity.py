@@ -524,3 +524,14 @@ def test_full_size_properties(oracle_lib, gpu):
         want = ox.run(head).best
     assert got.tobytes() == want.tobytes() and len(got) > 3000
     w.close()
+
+
+def test_every_kernel_once_on_a_compact_case():
+    """tools/gpu/sanitize_case.py without a sanitizer around it (compute-sanitizer is closed on this GPU pool,
+    profiles/r02_sanitizer_closed_on_pool.log): every kernel of the library on one small input with heavy bundles, flanks,
+    strand '.', the alignment stage and block-cooperative alignment pairs, each result compared with the oracle."""
+    import importlib.util
+    spec = importlib.util.spec_from_file_location("sanitize_case", os.path.join(ROOT, "tools", "gpu", "sanitize_case.py"))
+    mod = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(mod)
+    mod.main()
