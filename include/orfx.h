@@ -80,7 +80,9 @@ typedef struct orfx_params {
     int32_t align_enabled;
     int32_t align_gapo;         /* gap open, 0 = the reference's default 12 (aln.hpp:146)                       */
     int32_t align_gape;         /* gap extend, 0 = the reference's default 2                                    */
-    int32_t reserved[1];
+    int32_t host_results_pageable;   /* 1: the library's result buffers are ordinary memory instead of page-locked memory.  For a
+                                        caller that evaluates one batch per process (the command-line tool) page-locking tens of
+                                        megabytes costs more than the one download gains                                        */
 } orfx_params;
 
 /* 1-based inclusive genomic interval; replaces SEGTP (Transcriptome.h:23-169) */

@@ -47,7 +47,7 @@ class Params(C.Structure):
     _fields_ = [("n_modes", C.c_int32), ("mode_array", C.c_int32 * 8), ("lpi", C.c_int32), ("ilpi", C.c_int32),
                 ("mlpi", C.c_int32), ("cds_minlen", C.c_int32), ("non_aug", C.c_int32), ("overhang", C.c_int32),
                 ("spliced_overhang", C.c_int32), ("has_reference", C.c_int32), ("want_rows", C.c_int32),
-                ("align_enabled", C.c_int32), ("align_gapo", C.c_int32), ("align_gape", C.c_int32), ("reserved", C.c_int32 * 1)]
+                ("align_enabled", C.c_int32), ("align_gapo", C.c_int32), ("align_gape", C.c_int32), ("host_results_pageable", C.c_int32)]
 
     @classmethod
     def make(cls, mode="LONGEST_MATCH,BEST,START_MATCH,LONGEST,FIRST,ALL", lpi=-1, ilpi=-1, mlpi=-1, minlen=-1,

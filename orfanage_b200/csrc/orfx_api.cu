@@ -387,16 +387,17 @@ void collect_times(orfx_ctx* c) {
 int download_results(orfx_ctx* c) {
     cudaStream_t s = c->stream;
     const size_t nq = (size_t)c->n_queries, nr = (size_t)c->n_rows;
-    CU(c->h_best.ensure(nq * sizeof(orfx_best) + 8));
+    const bool pg = c->P.host_results_pageable != 0;
+    CU(c->h_best.ensure(nq * sizeof(orfx_best) + 8, pg));
     if (nq) CU(cudaMemcpyAsync(c->h_best.p, c->d_best.p, nq * sizeof(orfx_best), cudaMemcpyDeviceToHost, s));
     if (c->P.want_rows && nr) {
-        for (int i = 0; i < 16; i++) { CU(c->h_i32[i].ensure(nr * 4)); CU(cudaMemcpyAsync(c->h_i32[i].p, c->r_i32[i].p, nr * 4, cudaMemcpyDeviceToHost, s)); }
-        for (int i = 0; i < 3; i++) { CU(c->h_f32[i].ensure(nr * 4)); CU(cudaMemcpyAsync(c->h_f32[i].p, c->r_f32[i].p, nr * 4, cudaMemcpyDeviceToHost, s)); }
-        for (int i = 0; i < 3; i++) { CU(c->h_u8[i].ensure(nr)); CU(cudaMemcpyAsync(c->h_u8[i].p, c->r_u8[i].p, nr, cudaMemcpyDeviceToHost, s)); }
-        CU(c->h_order.ensure(nr * 8));
+        for (int i = 0; i < 16; i++) { CU(c->h_i32[i].ensure(nr * 4, pg)); CU(cudaMemcpyAsync(c->h_i32[i].p, c->r_i32[i].p, nr * 4, cudaMemcpyDeviceToHost, s)); }
+        for (int i = 0; i < 3; i++) { CU(c->h_f32[i].ensure(nr * 4, pg)); CU(cudaMemcpyAsync(c->h_f32[i].p, c->r_f32[i].p, nr * 4, cudaMemcpyDeviceToHost, s)); }
+        for (int i = 0; i < 3; i++) { CU(c->h_u8[i].ensure(nr, pg)); CU(cudaMemcpyAsync(c->h_u8[i].p, c->r_u8[i].p, nr, cudaMemcpyDeviceToHost, s)); }
+        CU(c->h_order.ensure(nr * 8, pg));
         CU(cudaMemcpyAsync(c->h_order.p, c->r_order.p, nr * 8, cudaMemcpyDeviceToHost, s));
-        if (c->R.ext_lo) for (int i = 0; i < 2; i++) { CU(c->h_ext[i].ensure(nr * 4)); CU(cudaMemcpyAsync(c->h_ext[i].p, c->r_ext[i].p, nr * 4, cudaMemcpyDeviceToHost, s)); }
-        if (c->R.aln_max) for (int i = 0; i < 4; i++) { CU(c->h_aln[i].ensure(nr * 4)); CU(cudaMemcpyAsync(c->h_aln[i].p, c->r_aln[2 + i].p, nr * 4, cudaMemcpyDeviceToHost, s)); }
+        if (c->R.ext_lo) for (int i = 0; i < 2; i++) { CU(c->h_ext[i].ensure(nr * 4, pg)); CU(cudaMemcpyAsync(c->h_ext[i].p, c->r_ext[i].p, nr * 4, cudaMemcpyDeviceToHost, s)); }
+        if (c->R.aln_max) for (int i = 0; i < 4; i++) { CU(c->h_aln[i].ensure(nr * 4, pg)); CU(cudaMemcpyAsync(c->h_aln[i].p, c->r_aln[2 + i].p, nr * 4, cudaMemcpyDeviceToHost, s)); }
     }
     return ORFX_OK;
 }

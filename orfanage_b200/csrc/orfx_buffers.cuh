@@ -2,6 +2,7 @@
 #pragma once
 #include <cuda_runtime.h>
 #include <stddef.h>
+#include <stdlib.h>
 
 namespace orfx {
 
@@ -23,16 +24,19 @@ struct DBuf {
 struct HBuf {
     void* p = nullptr;
     size_t cap = 0;
-    cudaError_t ensure(size_t bytes) {
-        if (bytes <= cap) return cudaSuccess;
-        if (p) cudaFreeHost(p);
-        p = nullptr; cap = 0;
+    bool pinned = true;
+    // pageable = true: ordinary memory (a caller that evaluates one batch per process: page-locking a result buffer
+    // costs more than the one download gains)
+    cudaError_t ensure(size_t bytes, bool pageable = false) {
+        if (bytes <= cap && pinned == !pageable) return cudaSuccess;
+        free_();
         size_t want = bytes + bytes / 8 + 256;
+        if (pageable) { p = malloc(want); if (!p) return cudaErrorMemoryAllocation; pinned = false; cap = want; return cudaSuccess; }
         cudaError_t e = cudaMallocHost(&p, want);
-        if (e == cudaSuccess) cap = want;
+        if (e == cudaSuccess) { cap = want; pinned = true; }
         return e;
     }
-    void free_() { if (p) cudaFreeHost(p); p = nullptr; cap = 0; }
+    void free_() { if (p) { if (pinned) cudaFreeHost(p); else free(p); } p = nullptr; cap = 0; pinned = true; }
     template <class T> T* as() const { return reinterpret_cast<T*>(p); }
 };
 
