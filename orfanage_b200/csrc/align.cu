@@ -122,11 +122,17 @@ __device__ __forceinline__ void dp_stripe(const int* __restrict__ s_mat, WarpSme
 
     auto step = [&](int s, auto full_tag) {
         constexpr bool FULL = decltype(full_tag)::value;
-        // values arriving from the left neighbour (computed in the previous step); lane 0 reads the edge ring
-        int h_left = __shfl_up_sync(0xffffffffu, h_out, 1);
-        int f_in = __shfl_up_sync(0xffffffffu, f_out, 1);
-        const int2 edge = ws.in_ring[s & 31];
-        if (lane == 0) { h_left = edge.x; f_in = edge.y; }
+        // Values arriving from the left neighbour (computed in the previous step).  Lane 0's left neighbour is the previous
+        // stripe: lane 31 -- whose own right edge leaves the warp anyway -- first parks the edge of the row it finished in the
+        // previous step, then loads the left edge of the row lane 0 starts now into the same registers, and the shuffle is a
+        // rotation.  (Selecting the ring value into lane 0 after a shuffle-up costs two ALU-pipe selects per step in all lanes.)
+        if (lane == 31) {
+            if (!LAST && (FULL || s >= 32)) ws.out_ring[(s - 32) & 63] = make_int2(h_out, f_out);
+            const int2 edge = ws.in_ring[s & 31];
+            h_out = edge.x; f_out = edge.y;
+        }
+        const int h_left = __shfl_sync(0xffffffffu, h_out, (lane + 31) & 31);
+        const int f_in = __shfl_sync(0xffffffffu, f_out, (lane + 31) & 31);
         const int i = s - lane;
         if (FULL || (i >= 0 && i < tlen)) {
             const uint2 cur = sc;
@@ -162,7 +168,6 @@ __device__ __forceinline__ void dp_stripe(const int* __restrict__ s_mat, WarpSme
         } else if (i == -1) {
             sc = *reinterpret_cast<const uint2*>(prof_lane + ws.tl[32]);   // the step before the lane's first row (first block: row 0 is tl[32])
         }
-        if (!LAST && lane == 31 && (FULL || s >= 31)) ws.out_ring[(s - 31) & 63] = make_int2(h_out, f_out);
     };
 
     for (int s0 = 0; s0 < n_steps; s0 += 32) {
@@ -203,9 +208,10 @@ __device__ __forceinline__ void dp_stripe(const int* __restrict__ s_mat, WarpSme
             }
         }
         if (!LAST) {
-            // rows finished by lane 31 so far; store them 32 at a time, coalesced
-            const int done = min(tlen, s0 + 32 - 31);
-            while (stored + 32 <= done || (done == tlen && stored < tlen)) {
+            // rows lane 31 has parked so far (a row is parked at the start of the step after it was finished: all but the
+            // last one by the end of the loop); store them 32 at a time, coalesced
+            const int done = min(tlen - 1, s0);
+            while (stored + 32 <= done) {
                 __syncwarp();
                 const int r = stored + lane;
                 if (r < min(stored + 32, tlen)) { const int2 o = ws.out_ring[r & 63]; __stcg(io.h_out + r, o.x); __stcg(io.f_out + r, o.y); }
@@ -215,6 +221,20 @@ __device__ __forceinline__ void dp_stripe(const int* __restrict__ s_mat, WarpSme
                     __syncwarp();
                     if (lane == 0) atomicExch(io.post_flag, io.post_base + (unsigned long long)min(stored, tlen));
                 }
+            }
+        }
+    }
+    if (!LAST) {   // the last row is still in lane 31's registers; then whatever has not been stored yet
+        if (lane == 31) ws.out_ring[(tlen - 1) & 63] = make_int2(h_out, f_out);
+        while (stored < tlen) {
+            __syncwarp();
+            const int r = stored + lane;
+            if (r < min(stored + 32, tlen)) { const int2 o = ws.out_ring[r & 63]; __stcg(io.h_out + r, o.x); __stcg(io.f_out + r, o.y); }
+            stored += 32;
+            if (PIPE) {
+                __threadfence_block();
+                __syncwarp();
+                if (lane == 0) atomicExch(io.post_flag, io.post_base + (unsigned long long)min(stored, tlen));
             }
         }
     }
@@ -468,11 +488,13 @@ __global__ void __launch_bounds__(256) aln_classify_kernel(const AlnPair* __rest
         if (p.qlen >= 0) {
             const long long c = (long long)p.qlen * (long long)max(p.tlen, 0);
             cells = (double)c;
-            const bool is_long = p.qlen >= 1024 && p.tlen >= 256 && c >= 4194304LL;
+            // a whole CTA (16 warps, one stripe of 256 columns each at a time) pays off from ~12 stripes on, or when the pair is
+            // so large that a single warp would be the tail of the launch
+            const bool is_long = p.qlen >= 1024 && p.tlen >= 256 && (p.qlen >= 3072 ? c >= 4194304LL : c >= 33554432LL);
             bin = (is_long ? 0 : ALN_NCLS) + (ALN_NCLS - 1 - cost_class(c));
             atomicAdd(&s_hist[bin], 1u);
             if (is_long) atomicMax(&meta->max_tlen_long, (unsigned long long)p.tlen);
-            else if (p.qlen > 64) atomicMax(&meta->max_tlen, (unsigned long long)max(p.tlen, 0));
+            else if (p.qlen > 256) atomicMax(&meta->max_tlen, (unsigned long long)max(p.tlen, 0));   // only a multi-stripe pair parks edges in the warp's scratch
         }
         cls[i] = (uint16_t)bin;
     }
