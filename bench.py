@@ -238,6 +238,33 @@ def reference_arm(args):
     emit(line)
 
 
+def bind_to_gpu_numa_node(index):
+    """Pins this process (and the pages it first touches: the pinned batch arena, the result buffers) to the NUMA node the
+    GPU hangs off, so that eight ranks pushing their batches at once do not cross the socket interconnect.  Returns what was
+    done for the JSON line; silently does nothing where the topology cannot be read."""
+    try:
+        import pynvml
+        pynvml.nvmlInit()
+        bus = pynvml.nvmlDeviceGetPciInfo(pynvml.nvmlDeviceGetHandleByIndex(index)).busId
+        bus = bus.decode() if isinstance(bus, bytes) else bus
+        bus = bus.lower()
+        if len(bus.split(":")[0]) == 8:      # NVML prints an 8-digit PCI domain, sysfs a 4-digit one
+            bus = bus[4:]
+        node = int(open("/sys/bus/pci/devices/%s/numa_node" % bus).read().strip())
+        if node < 0:
+            return {"gpu": index, "node": None}
+        cpus = set()
+        for part in open("/sys/devices/system/node/node%d/cpulist" % node).read().strip().split(","):
+            a, _, b = part.partition("-")
+            cpus.update(range(int(a), int(b or a) + 1))
+        cpus &= os.sched_getaffinity(0)
+        if cpus:
+            os.sched_setaffinity(0, cpus)
+        return {"gpu": index, "pci": bus, "node": node, "cpus": len(cpus)}
+    except Exception as e:
+        return {"gpu": index, "node": None, "note": str(e)[:80]}
+
+
 # ---- our arm -------------------------------------------------------------------------------------------
 def cpu_baseline_leg():
     """Reference binary on the bounded sample, all host threads, one warm-up + two timed runs."""
@@ -264,6 +291,7 @@ def ours(args):
     if not torch.cuda.is_available():
         raise SystemExit("bench.py: no CUDA device; the product has no CPU path (use --impl reference for the CPU arm)")
     torch.cuda.set_device(local)
+    numa = bind_to_gpu_numa_node(local) if world > 1 and not args.no_numa else None
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
 
@@ -503,7 +531,7 @@ def ours(args):
         t = time.time()
         align = alignment_leg(cx, args.align_pairs)
         log("alignment leg: %.1f s, %.1f GCUPS" % (time.time() - t, align["gcups"]))
-    return dict(align_path=align_path, e2e3_ms=e2e3_ms, stage_ms_alone=stage_ms_alone, alone_ms=alone_ms, c4=c4, digest=digest, nt_all=nt_all, e2e2_ms=e2e2_ms, per_rank=per_rank, align=align, rank=rank, world=world, cfg=cfg, nq=nq, nq_all=nq_all, nt_sum=nt_sum, dev_ms=dev_ms, wall_ms=wall_ms, e2e_ms=e2e_ms,
+    return dict(numa=numa, align_path=align_path, e2e3_ms=e2e3_ms, stage_ms_alone=stage_ms_alone, alone_ms=alone_ms, c4=c4, digest=digest, nt_all=nt_all, e2e2_ms=e2e2_ms, per_rank=per_rank, align=align, rank=rank, world=world, cfg=cfg, nq=nq, nq_all=nq_all, nt_sum=nt_sum, dev_ms=dev_ms, wall_ms=wall_ms, e2e_ms=e2e_ms,
                 e2e_dev=e2e_dev, stage_ms=stage_ms, launches=launches_all, found=found_all, clocks=clocks, h2d=h2d_bytes,
                 d2h=d2h_bytes, windows=seq_bytes, n_templates=w.count("templates"),
                 n_bundles=w.count("active_bundles"))
@@ -680,6 +708,7 @@ def main():
     ap.add_argument("--config", default="c2", choices=["c2", "c4"], help="c2 = BASELINE.json configs[1] (the driver's metric; weak scaling); "
                     "c4 = configs[3], one 2 M-query workload sharded by locus over the GPUs (strong scaling)")
     ap.add_argument("--no-align-path", action="store_true", help="skip the leg that runs the path with the alignment stage enabled")
+    ap.add_argument("--no-numa", action="store_true", help="multi-GPU runs: do not bind the rank to its GPU's NUMA node")
     ap.add_argument("--no-cli", action="store_true", help="skip the whole-process CLI leg")
     ap.add_argument("--only-align", action="store_true", help="development: run the alignment leg alone and print its object")
     args = ap.parse_args()
@@ -782,6 +811,8 @@ def main():
         line["alignment"] = m["align"]
     if m.get("align_path"):
         line["alignment_in_path"] = m["align_path"]
+    if m.get("numa"):
+        line["config"]["numa_binding_rank0"] = m["numa"]
     if m.get("per_rank"):
         line["per_rank"] = m["per_rank"]
         dm = m["per_rank"]["device_ms_per_step"]

@@ -383,9 +383,20 @@ void shard_bundles(const Transcriptome& tr, const std::vector<int>& active, int 
     cost.reserve(active.size());
     for (int bi : active) {
         const Bundle& b = tr.bundles[bi];
-        double nq = 0, nt = 0, nts = 0;
-        for (int i = 0; i < b.count; i++) { const Tx& t = tr.txs[b.first + i]; if (t.is_templ) nt++; else { nq++; nts += chain_len(t.exons); } }
-        cost.emplace_back(nq * nt * 64.0 + nts + (double)(b.bend - b.bstart + 1) * 0.05, bi);
+        // Calibrated against the measured stage times of configs[1] and configs[3] on one B200 (profiles/r02_bench_1gpu.json,
+        // r02_bench_c4_1gpu.json): the sequence stages cost ~1 unit per spliced query base; the row stages (candidate rows,
+        // rescue + score, select) ~150 units per (query, template) pair and exon of the query; rows of heavy (titin-class)
+        // bundles, which take a warp each, 2.5 times that.  (Round 1's model, pairs x 64 + bases, put a third of the time of
+        // a configs[3] shard -- its titin-class loci -- at a sixth of the cost: LPT imbalance 1.11 on 8 GPUs.)
+        double nq = 0, nt = 0, nts = 0, nex = 0;
+        bool heavy = false;
+        for (int i = 0; i < b.count; i++) {
+            const Tx& t = tr.txs[b.first + i];
+            const size_t segs = t.is_templ ? t.cds.size() : t.exons.size();
+            heavy = heavy || segs > 32;
+            if (t.is_templ) nt++; else { nq++; nts += chain_len(t.exons); nex += (double)t.exons.size(); }
+        }
+        cost.emplace_back(nts + 150.0 * nt * nex * (heavy ? 2.5 : 1.0), bi);
     }
     std::sort(cost.begin(), cost.end(), [](const std::pair<double, int>& a, const std::pair<double, int>& b) { return a.first != b.first ? a.first > b.first : a.second < b.second; });
     std::vector<double> load((size_t)n, 0.0);
