@@ -595,18 +595,20 @@ int run_orfanage(const Options& opt, const Backend& be) {
 
     std::vector<std::vector<int>> shard_ids;
     shard_bundles(tr, active, n_shards, shard_ids);
-    for (auto& t : ctx_threads) t.join();
     auto work = [&](int k) {
         Shard& s = shards[(size_t)k];
         try {
             memset(&s.res, 0, sizeof s.res);
-            if (s.rc || shard_ids[(size_t)k].empty()) return;
             auto a = clk::now();
             // one batch per process: page-locking the arena would cost more than the one upload saves
-            pack_bundles(tr, shard_ids[(size_t)k], opt.keep_all_cds, tid_classes, s.batch, nullptr, nullptr, true, PACK_EVAL, true, opt.overhang, opt.spliced_overhang,
-                         params.align_enabled != 0);
+            if (!shard_ids[(size_t)k].empty())
+                pack_bundles(tr, shard_ids[(size_t)k], opt.keep_all_cds, tid_classes, s.batch, nullptr, nullptr, true, PACK_EVAL, true, opt.overhang, opt.spliced_overhang,
+                             params.align_enabled != 0);
             auto b = clk::now();
             s.ms_pack = ms(a, b);
+            ctx_threads[(size_t)k].join();   // this shard's context (the contexts of one process come up one after the other)
+            if (s.rc || shard_ids[(size_t)k].empty()) return;
+            b = clk::now();
             orfx_batch v = s.batch.view();
             s.rc = be.submit(s.ctx, &v);
             if (s.rc) { s.err = be.last_error(); return; }
