@@ -30,6 +30,7 @@ C2 = dict(seed=20261104, loci=20000, chroms=24, chrom_len=125000000, queries=13,
 # over the GPUs of the box (strong scaling; the product's own shard_bundles deals the loci)
 C4 = dict(seed=20261107, loci=20000, chroms=24, chrom_len=125000000, queries=100, templates=8, template_files=1)
 MODE = "LONGEST_MATCH,BEST"
+LAYOUT = "islands2"          # islands of query-exon bases as 2-bit codes + exception list (ORFX_SEQ_NT2): the smallest upload
 ALG_BYTES_PER_NT = 1.25      # codon scan: 1 B read per spliced nucleotide + 2 mask bits written
 
 
@@ -323,7 +324,7 @@ def ours(args):
     w = ob.Workload(os.path.join(d, "query.gtf"), [os.path.join(d, "template.gtf")], os.path.join(d, "genome.fa"))
     # configs[1]: every rank its own workload (weak scaling); configs[3]: every rank loads the one workload and packs the
     # locus shard shard_bundles deals it (strong scaling)
-    batch = w.pack(rank, world, pinned=True, layout="islands4") if c4 else w.pack(0, 1, pinned=True, layout="islands4")
+    batch = w.pack(rank, world, pinned=True, layout=LAYOUT) if c4 else w.pack(0, 1, pinned=True, layout=LAYOUT)
     nq, nt_sum = batch.n_queries, (batch.query_nt() if c4 else w.count("query_nt"))
     h2d_bytes, seq_bytes = batch.h2d_bytes, int(batch.arrays["seq"].nbytes)
     log("rank %d: loaded + packed in %.1f s: %d queries, %d templates, %d bundles, %.1f MB windows, %.1f M spliced nt"
@@ -426,7 +427,7 @@ def ours(args):
                       "cells_per_step": cells_a, "gcups_in_path": cells_a / (st_a.get("align", 1e-9) / n_a * 1e-3) / 1e9,
                       "sequence_upload_bytes": int(tb.arrays["seq"].nbytes), "checksum": int(np.bitwise_xor.reduce(ra.rows["aln_score"].astype(np.int64) * 31 + ra.rows["aln_max"]))}
         cxa.close()
-        batch = w.pack(0, 1, pinned=True, layout="islands4")   # packing shard 0 again released the arrays `batch` viewed
+        batch = w.pack(0, 1, pinned=True, layout=LAYOUT)   # packing shard 0 again released the arrays `batch` viewed
 
     # ---- leg 3: the same calls as a stream of batches: two contexts, the next batch is submitted while the previous one is
     # still being evaluated (orfx_submit returns once everything is enqueued; a context is waited for before it is reused).
@@ -461,7 +462,7 @@ def ours(args):
     e2e2_ms = None
     n_ctx = max(2, args.e2e_contexts)
     if not args.no_pipelined and not c4:
-        parts = [w.pack(k, n_ctx, pinned=True, layout="islands4") for k in range(n_ctx)]
+        parts = [w.pack(k, n_ctx, pinned=True, layout=LAYOUT) for k in range(n_ctx)]
         assert sum(h.n_queries for h in parts) == nq
         extra = [ob.Context(params, device=local) for _ in range(n_ctx - 1)]
         pair = list(zip([cx] + extra, parts))
@@ -769,7 +770,7 @@ def main():
                    "query_transcripts_per_gpu": m["nq"], "query_transcripts_total": m["nq_all"], "templates_after_dedup": m["n_templates"], "bundles": m["n_bundles"],
                    "best_digest": m["digest"],
                    "genome": "%d x %d bp random, planted ORFs, seed %d%s" % (m["cfg"]["chroms"], m["cfg"]["chrom_len"], m["cfg"]["seed"], "" if c4 else "+rank"),
-                   "spliced_query_nt_per_gpu": m["nt_sum"], "sequence_upload_bytes_per_gpu": m["windows"], "sequence_format": "islands, 4-bit base codes (ORFX_SEQ_NT4)",
+                   "spliced_query_nt_per_gpu": m["nt_sum"], "sequence_upload_bytes_per_gpu": m["windows"], "sequence_format": "islands, 2-bit base codes + exception list (ORFX_SEQ_NT2)",
                    "parallelism": "locus shards, one per GPU, no collective", "orfs_found": m["found"],
                    "l2": "inputs larger than L2 (windows + chains + masks > 126 MB); no explicit flush",
                    "timing": "CUDA events on the library stream around the whole path, summed over steps, max over ranks",
@@ -797,7 +798,7 @@ def main():
                                  "frac": (alg_bytes / (scan_in_step_ms / 1e3) / 1e9 / peak) if (scan_in_step_ms > 0 and peak) else None,
                                  "note": "two launches (heavy bundles' transcripts first), the heavy bundles' rescue kernel running beside the second"},
                      "share_of_step": scan_in_step_ms / ms_per_step if ms_per_step else None,
-                     "stage": {"kernels": "base_planes_nt4_kernel + codon_scan_kernel", "ms": scan_ms + planes_ms, "achieved": stage_achieved,
+                     "stage": {"kernels": "base_planes_nt2_kernel + plane_exceptions_kernel + codon_scan_kernel", "ms": scan_ms + planes_ms, "achieved": stage_achieved,
                                "frac": stage_achieved / peak if peak else None},
                      "dominant_stage": dominant,
                      "dominant": {"stage": dominant, "ms": m["stage_ms"][dominant] / K if dominant else None, "bound": "latency (dependent chain walks and mask scans; "

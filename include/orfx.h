@@ -149,6 +149,11 @@ typedef struct orfx_batch {
      * cpp:352-364 yields that base again.  The position does not exist: a stop codon completed by it grows the exon by
      * one, and the re-loaded sequence then ends one base short, so the row ends as "missing_stop" (cpp:418-442, 155-171). */
     const uint8_t* tx_ext_flags;
+    /* ORFX_SEQ_NT2 only: the bases that are none of A C G T (case-insensitive) -- their position (offset in bases into `seq`,
+     * ascending) and their ORFX_NT4_* code; `seq` holds 0 in their place.  Genomes have few of them under exons. */
+    const int64_t* seq_exc_pos;    /* [n_seq_exc] */
+    const uint8_t* seq_exc_code;   /* [n_seq_exc] */
+    int64_t n_seq_exc;
 } orfx_batch;
 
 #define ORFX_EXT_LO_VIRTUAL 1
@@ -156,6 +161,9 @@ typedef struct orfx_batch {
 
 #define ORFX_SEQ_RAW 0
 #define ORFX_SEQ_NT4 1
+#define ORFX_SEQ_NT2 2   /* islands layout only: four bases per byte (base 4k in bits 0-1 of byte k), A = 0, C = 1, G = 2, T = 3; every
+                            other base is listed in seq_exc_pos / seq_exc_code.  seq_bytes / seq_off / seg_seq_off count BASES, seq_off
+                            entries are multiples of 4 and the buffer holds (seq_bytes + 3) / 4 bytes.  A quarter of the raw upload. */
 /* 4-bit base codes of ORFX_SEQ_NT4 (case-insensitive); U is kept apart from T because the reference only
  * equates them through ntComplement on the reverse strand */
 #define ORFX_NT4_OTHER 0

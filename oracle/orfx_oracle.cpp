@@ -618,7 +618,7 @@ struct BundleSeq {
     BundleSeq(const orfx_batch* b, int bi, int only_tx = -1, int pad = 0, bool with_templates = false) {
         bn.bstart = b->bundle_start[bi];
         if (!b->seq) { bn.seq = nullptr; return; }
-        if (b->seq_format == ORFX_SEQ_NT4 && !b->seg_seq_off) throw std::runtime_error("ORFX_SEQ_NT4 is defined for the islands layout only");
+        if (b->seq_format != ORFX_SEQ_RAW && !b->seg_seq_off) throw std::runtime_error("ORFX_SEQ_NT4 / ORFX_SEQ_NT2 are defined for the islands layout only");
         if (!b->seg_seq_off) { bn.seq = b->seq + b->seq_off[bi]; return; }
         int hi = bn.bstart;
         for (int x = b->bundle_tx_off[bi]; x < b->bundle_tx_off[bi + 1]; x++)
@@ -648,6 +648,19 @@ struct BundleSeq {
                         const int64_t p = base0 + i;
                         rebuilt[(size_t)(sg.start - bn.bstart + i)] = LET[(b->seq[p >> 1] >> ((p & 1) * 4)) & 15];
                     }
+                    continue;
+                }
+                if (b->seq_format == ORFX_SEQ_NT2) {   // 2-bit codes, then the listed exceptions of this segment on top
+                    static const char LET[16] = {'N', 'A', 'C', 'U', 'G', 'R', 'N', 'N', 'T', 'N', 'Y', 'N', 'N', 'N', 'N', 'N'};
+                    const int64_t base0 = b->seq_off[bi] + at, n = sg.end - sg.start + 1;
+                    char* out = &rebuilt[(size_t)(sg.start - bn.bstart)];
+                    for (int64_t i = 0; i < n; i++) {
+                        const int64_t p = base0 + i;
+                        out[i] = "ACGT"[(b->seq[p >> 2] >> ((p & 3) * 2)) & 3];
+                    }
+                    const int64_t* e0 = b->seq_exc_pos, * e1 = b->seq_exc_pos + b->n_seq_exc;
+                    for (const int64_t* e = std::lower_bound(e0, e1, base0); e != e1 && *e < base0 + n; ++e)
+                        out[*e - base0] = LET[b->seq_exc_code[e - e0] & 15];
                     continue;
                 }
                 memcpy(&rebuilt[(size_t)(sg.start - bn.bstart)], b->seq + b->seq_off[bi] + at, (size_t)(sg.end - sg.start + 1));

@@ -77,7 +77,8 @@ class _Batch(C.Structure):
                 ("tx_kind", C.c_void_p), ("tx_strand", C.c_void_p), ("tx_seg_off", C.c_void_p), ("tx_cds_start", C.c_void_p),
                 ("tx_cds_end", C.c_void_p), ("tx_tid_class", C.c_void_p), ("segs", C.c_void_p), ("seg_phase", C.c_void_p),
                 ("seg_seq_off", C.c_void_p), ("seq_format", C.c_int32), ("reserved0", C.c_int32),
-                ("tx_ext_lo", C.c_void_p), ("tx_ext_hi", C.c_void_p), ("tx_ext_flags", C.c_void_p)]
+                ("tx_ext_lo", C.c_void_p), ("tx_ext_hi", C.c_void_p), ("tx_ext_flags", C.c_void_p),
+                ("seq_exc_pos", C.c_void_p), ("seq_exc_code", C.c_void_p), ("n_seq_exc", C.c_int64)]
 
 
 class _Best(C.Structure):
@@ -116,7 +117,8 @@ class _AlnOut(C.Structure):
 _BATCH_ARRAYS = [("seq", np.uint8), ("seq_off", np.int64), ("bundle_start", np.int32), ("bundle_tx_off", np.int32),
                  ("tx_kind", np.uint8), ("tx_strand", np.uint8), ("tx_seg_off", np.int32), ("tx_cds_start", np.int32),
                  ("tx_cds_end", np.int32), ("tx_tid_class", np.int32), ("segs", np.int32), ("seg_phase", np.int8),
-                 ("seg_seq_off", np.int32), ("tx_ext_lo", np.int32), ("tx_ext_hi", np.int32), ("tx_ext_flags", np.uint8)]
+                 ("seg_seq_off", np.int32), ("tx_ext_lo", np.int32), ("tx_ext_hi", np.int32), ("tx_ext_flags", np.uint8),
+                 ("seq_exc_pos", np.int64), ("seq_exc_code", np.uint8)]
 
 
 def _view(ptr, n, dtype):
@@ -145,7 +147,7 @@ class Batch:
             a = np.ascontiguousarray(a, dtype=dt)
             self.arrays[name] = a
         self.owner = arrays.get("owner")
-        # ORFX_SEQ_NT4 batches: `seq` holds two bases per byte and `seq_bases` counts the bases
+        # ORFX_SEQ_NT4 / ORFX_SEQ_NT2 batches: `seq` holds two / four bases per byte and `seq_bases` counts the bases
         self.seq_format = int(np.asarray(arrays.get("seq_format", 0)).reshape(-1)[0]) if arrays.get("seq_format") is not None else 0
         a = self.arrays
         if a["segs"].ndim == 1:
@@ -154,8 +156,9 @@ class Batch:
         s.n_bundles = max(len(a["bundle_tx_off"]) - 1, 0)
         s.n_tx = len(a["tx_kind"])
         s.n_segs = a["segs"].shape[0]
-        s.seq_bytes = int(np.asarray(arrays["seq_bases"]).reshape(-1)[0]) if self.seq_format == 1 else a["seq"].size
+        s.seq_bytes = int(np.asarray(arrays["seq_bases"]).reshape(-1)[0]) if self.seq_format in (1, 2) else a["seq"].size
         s.seq_format = self.seq_format
+        s.n_seq_exc = a["seq_exc_pos"].size
         for name, _ in _BATCH_ARRAYS:
             arr = a[name]
             setattr(s, name, arr.ctypes.data if arr.size else None)
@@ -175,7 +178,7 @@ class Batch:
     def from_struct(cls, s, owner=None):
         nb, nt, ns = s.n_bundles, s.n_tx, s.n_segs
         arrays = dict(
-            seq=_view(s.seq, (s.seq_bytes + 1) // 2 if s.seq_format == 1 else s.seq_bytes, np.uint8), seq_off=_view(s.seq_off, nb + 1, np.int64),
+            seq=_view(s.seq, {1: (s.seq_bytes + 1) // 2, 2: (s.seq_bytes + 3) // 4}.get(s.seq_format, s.seq_bytes), np.uint8), seq_off=_view(s.seq_off, nb + 1, np.int64),
             bundle_start=_view(s.bundle_start, nb, np.int32), bundle_tx_off=_view(s.bundle_tx_off, nb + 1, np.int32),
             tx_kind=_view(s.tx_kind, nt, np.uint8), tx_strand=_view(s.tx_strand, nt, np.uint8),
             tx_seg_off=_view(s.tx_seg_off, nt + 1, np.int32), tx_cds_start=_view(s.tx_cds_start, nt, np.int32),
@@ -183,7 +186,9 @@ class Batch:
             segs=_view(s.segs, ns * 2, np.int32), seg_phase=_view(s.seg_phase, ns, np.int8),
             seg_seq_off=_view(s.seg_seq_off, ns if s.seg_seq_off else 0, np.int32),
             tx_ext_lo=_view(s.tx_ext_lo, nt if s.tx_ext_lo else 0, np.int32), tx_ext_hi=_view(s.tx_ext_hi, nt if s.tx_ext_hi else 0, np.int32),
-            tx_ext_flags=_view(s.tx_ext_flags, nt if s.tx_ext_flags else 0, np.uint8))
+            tx_ext_flags=_view(s.tx_ext_flags, nt if s.tx_ext_flags else 0, np.uint8),
+            seq_exc_pos=_view(s.seq_exc_pos, s.n_seq_exc if s.seq_exc_pos else 0, np.int64),
+            seq_exc_code=_view(s.seq_exc_code, s.n_seq_exc if s.seq_exc_code else 0, np.uint8))
         b = cls.__new__(cls)
         b.arrays = arrays
         b.arrays["segs"] = b.arrays["segs"].reshape(-1, 2)
@@ -210,7 +215,7 @@ class Batch:
         return int(tx_len[a["tx_kind"] == 0].sum())
 
     def save(self, path):
-        extra = dict(seq_format=np.array([1], np.int32), seq_bases=np.array([self.struct.seq_bytes], np.int64)) if self.seq_format == 1 else {}
+        extra = dict(seq_format=np.array([self.seq_format], np.int32), seq_bases=np.array([self.struct.seq_bytes], np.int64)) if self.seq_format else {}
         np.savez_compressed(path, **self.arrays, **extra)
 
     @classmethod
@@ -556,7 +561,7 @@ class Workload:
             dev = load_device_library()
             alloc = C.cast(dev.orfx_host_alloc, C.c_void_p)
             dealloc = C.cast(dev.orfx_host_free, C.c_void_p)
-        rc = self.lib.orfxh_pack(self.handle, shard, n_shards, {"windows": 0, "islands": 1, "islands4": 2, "islands_t": 3}[layout], alloc, dealloc, C.byref(s))
+        rc = self.lib.orfxh_pack(self.handle, shard, n_shards, {"windows": 0, "islands": 1, "islands4": 2, "islands_t": 3, "islands2": 4}[layout], alloc, dealloc, C.byref(s))
         if rc != 0:
             raise OrfxError(rc, self.lib.orfxh_last_error().decode())
         return Batch.from_struct(s, owner=self)

@@ -124,6 +124,58 @@ __global__ void __launch_bounds__(256) base_planes_nt4_kernel(DevBatch B, int64_
         out[B.plane_words] = make_uint4(a, plane_word4<ORFX_NT4_T>(v) | plane_word4<ORFX_NT4_U>(v), plane_word4<ORFX_NT4_C>(v), plane_word4<ORFX_NT4_Y>(v));
 }
 
+// Same planes from 2-bit base codes (ORFX_SEQ_NT2: four bases per byte, A C G T only): one 64-bit load per 32 bases.  The few
+// bases that are none of the four are listed apart (seq_exc_*) and patched into the planes by plane_exceptions_kernel.
+namespace {
+__device__ __forceinline__ uint32_t compact_even16(uint32_t x) {   // bits 0, 2, 4, ... 30 -> bits 0 .. 15
+    x = (x | (x >> 1)) & 0x33333333u;
+    x = (x | (x >> 2)) & 0x0F0F0F0Fu;
+    x = (x | (x >> 4)) & 0x00FF00FFu;
+    return (x | (x >> 8)) & 0x0000FFFFu;
+}
+}  // namespace
+__global__ void __launch_bounds__(256) base_planes_nt2_kernel(DevBatch B, int64_t n_chunks) {
+    const int64_t chunk = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;   // 32 bases = 8 bytes each
+    const int64_t warp_lo = (chunk & ~(int64_t)31) * 32;
+    if (warp_lo >= B.seq_bytes) return;
+    const int64_t warp_hi = min(warp_lo + 1024, B.seq_bytes);
+    int lo = 0, hi = B.n_bundles - 1;
+    while (lo < hi) {   // last bundle with seq_off <= warp_lo
+        const int mid = (lo + hi + 1) >> 1;
+        if (B.seq_off[mid] <= warp_lo) lo = mid; else hi = mid - 1;
+    }
+    uint32_t need = 0;
+    for (int b = lo; b < B.n_bundles && B.seq_off[b] < warp_hi; b++) need |= B.bundle_need[b];
+    if (chunk >= n_chunks || need == 0) return;
+    const uint2 v = __ldg(reinterpret_cast<const uint2*>(B.seq) + chunk);
+    const uint32_t M = 0x55555555u;
+    const uint32_t l0 = v.x & M, h0 = (v.x >> 1) & M, l1 = v.y & M, h1 = (v.y >> 1) & M;
+    const uint32_t a = compact_even16(~h0 & ~l0 & M) | (compact_even16(~h1 & ~l1 & M) << 16);
+    const uint32_t c = compact_even16(~h0 & l0) | (compact_even16(~h1 & l1) << 16);
+    const uint32_t g = compact_even16(h0 & ~l0) | (compact_even16(h1 & ~l1) << 16);
+    const uint32_t t = compact_even16(h0 & l0) | (compact_even16(h1 & l1) << 16);
+    uint4* out = reinterpret_cast<uint4*>(B.planes) + chunk;
+    if (need & 1u) out[0] = make_uint4(t, a, g, 0u);
+    if (need & 2u) out[B.plane_words] = make_uint4(a, t, c, 0u);
+}
+// one thread per listed base: its bit in the eight plane words of its chunk is rewritten from its ORFX_NT4_* code
+__global__ void __launch_bounds__(256) plane_exceptions_kernel(DevBatch B) {
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= B.n_seq_exc) return;
+    const int64_t pos = B.seq_exc_pos[i];
+    if (pos < 0 || pos >= B.seq_bytes) return;
+    const uint32_t code = B.seq_exc_code[i], bit = 1u << (pos & 31);
+    uint32_t* fwd = B.planes + (pos >> 5) * 4;                     // {T, A, G, R}
+    uint32_t* rev = B.planes + (B.plane_words + (pos >> 5)) * 4;   // {A, T|U, C, Y}
+    const bool f[4] = {code == ORFX_NT4_T, code == ORFX_NT4_A, code == ORFX_NT4_G, code == ORFX_NT4_R};
+    const bool r[4] = {code == ORFX_NT4_A, code == ORFX_NT4_T || code == ORFX_NT4_U, code == ORFX_NT4_C, code == ORFX_NT4_Y};
+#pragma unroll
+    for (int k = 0; k < 4; k++) {
+        if (f[k]) atomicOr(fwd + k, bit); else atomicAnd(fwd + k, ~bit);
+        if (r[k]) atomicOr(rev + k, bit); else atomicAnd(rev + k, ~bit);
+    }
+}
+
 // ---- 2. planes -> per-transcript stop / start masks ---------------------------------------------------
 // One THREAD per run of SCAN_TILE_WORDS consecutive mask words (256 spliced positions) of one transcript.
 // The thread locates the exon under the run's first position once, then streams: every round appends up
@@ -254,6 +306,12 @@ int launch_base_planes(const DevBatch& B, cudaStream_t stream) {
     if (B.seq_bytes <= 0 || B.n_bundles <= 0) return 0;
     const int64_t n_chunks = (B.seq_bytes + 31) / 32;
     const int64_t threads = (n_chunks + 31) / 32 * 32;
+    if (B.seq_format == ORFX_SEQ_NT2) {
+        base_planes_nt2_kernel<<<(unsigned)((threads + 255) / 256), 256, 0, stream>>>(B, n_chunks);
+        if (B.n_seq_exc <= 0) return 1;
+        plane_exceptions_kernel<<<(unsigned)((B.n_seq_exc + 255) / 256), 256, 0, stream>>>(B);
+        return 2;
+    }
     if (B.seq_format == ORFX_SEQ_NT4) base_planes_nt4_kernel<<<(unsigned)((threads + 255) / 256), 256, 0, stream>>>(B, n_chunks);
     else base_planes_kernel<<<(unsigned)((threads + 255) / 256), 256, 0, stream>>>(B, n_chunks);
     return 1;

@@ -167,6 +167,8 @@ struct PackedBatch {
     int32_t* tx_ext_lo = nullptr;           // --overhang only: usable flank below / above each query's exon chain
     int32_t* tx_ext_hi = nullptr;
     uint8_t* tx_ext_flags = nullptr;        // ORFX_EXT_* (a flank that re-reads the chromosome's edge base)
+    std::vector<int64_t> seq_exc_pos;       // ORFX_SEQ_NT2: the bases that are none of A C G T
+    std::vector<uint8_t> seq_exc_code;
     int32_t n_tx = 0;
     int64_t n_segs = 0, seq_bytes = 0, n_queries = 0;   // seq_bytes counts bases
     int32_t seq_format = ORFX_SEQ_RAW;
@@ -191,7 +193,8 @@ void pack_bundles(const Transcriptome& tr, const std::vector<int>& bundle_ids, b
                   void* (*alloc)(size_t) = nullptr, void (*dealloc)(void*) = nullptr, bool islands = true, int mode = PACK_EVAL,
                   bool nt4 = false,    // nt4: islands as 4-bit base codes (ORFX_SEQ_NT4), half the upload
                   int overhang = 0, bool spliced_overhang = false,   // --overhang flanks (TX::extend_seq, Transcriptome.cpp:342-399)
-                  bool template_seq = false);   // islands also cover the template CDS segments (orfx_params::align_enabled)
+                  bool template_seq = false,    // islands also cover the template CDS segments (orfx_params::align_enabled)
+                  bool nt2 = false);            // islands as 2-bit base codes + exception list (ORFX_SEQ_NT2), a quarter of the raw upload
 void build_tid_classes(const Transcriptome& tr, TidClasses& out);
 // greedy longest-processing-time split of active bundles over n shards
 void shard_bundles(const Transcriptome& tr, const std::vector<int>& active, int n, std::vector<std::vector<int>>& shards);

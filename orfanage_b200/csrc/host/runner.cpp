@@ -33,6 +33,7 @@ void PackedBatch::reset() {
     bundle_ids.clear(); tx_global.clear();
     n_tx = 0; n_segs = 0; seq_bytes = 0; n_queries = 0; seq_format = ORFX_SEQ_RAW;
     tx_ext_lo = tx_ext_hi = nullptr; tx_ext_flags = nullptr;
+    seq_exc_pos.clear(); seq_exc_code.clear();
 }
 
 orfx_batch PackedBatch::view() const {
@@ -59,6 +60,9 @@ orfx_batch PackedBatch::view() const {
     b.tx_ext_lo = tx_ext_lo;
     b.tx_ext_hi = tx_ext_hi;
     b.tx_ext_flags = tx_ext_flags;
+    b.seq_exc_pos = seq_exc_pos.empty() ? nullptr : seq_exc_pos.data();
+    b.seq_exc_code = seq_exc_code.empty() ? nullptr : seq_exc_code.data();
+    b.n_seq_exc = (int64_t)seq_exc_pos.size();
     return b;
 }
 
@@ -81,6 +85,16 @@ struct Nt4Table {
     }
 };
 const Nt4Table NT4;
+// ORFX_SEQ_NT2 codes: A C G T (either case) -> 0..3, every other byte 0xFF (listed as an exception with its NT4 code)
+struct Nt2Table {
+    uint8_t code[256];
+    Nt2Table() {
+        memset(code, 0xFF, sizeof code);
+        const char* letters = "ACGT";
+        for (int i = 0; letters[i]; i++) { code[(unsigned char)letters[i]] = (uint8_t)i; code[(unsigned char)(letters[i] | 0x20)] = (uint8_t)i; }
+    }
+};
+const Nt2Table NT2;
 // Islands of one bundle: the union of its query exons (what the path reads from the genome when
 // --overhang is 0).  Returns the merged intervals, ascending.
 inline uint8_t tx_kind_of(const Tx& t, bool keep_all_cds, bool clean_mode) {
@@ -176,16 +190,18 @@ QFlank query_flanks(const Fasta& fa, const Fasta::Seq& chrom, const Bundle& b, c
 // copied by several threads.  islands = true uploads only the bases under query exons.
 void pack_bundles(const Transcriptome& tr, const std::vector<int>& bundle_ids, bool keep_all_cds,
                   const TidClasses& tid_classes, PackedBatch& out,
-                  void* (*alloc)(size_t), void (*dealloc)(void*), bool islands, int mode, bool nt4, int overhang, bool spliced_overhang, bool template_seq) {
+                  void* (*alloc)(size_t), void (*dealloc)(void*), bool islands, int mode, bool nt4, int overhang, bool spliced_overhang, bool template_seq,
+                  bool nt2) {
     const bool clean_mode = mode == PACK_CLEAN, compare_mode = mode == PACK_COMPARE;
     template_seq = template_seq && mode == PACK_EVAL;
-    if (template_seq) nt4 = false;   // the translation needs the letters themselves
+    if (template_seq) nt4 = nt2 = false;   // the translation needs the letters themselves
     out.reset();
     out.bundle_ids = bundle_ids;
     const size_t nb = bundle_ids.size();
     const bool has_seq = tr.fasta != nullptr && !compare_mode;
     islands = islands && has_seq;
-    nt4 = nt4 && islands;
+    nt2 = nt2 && islands;
+    nt4 = nt4 && islands && !nt2;
     if (!has_seq) overhang = 0;
     size_t total_seq = 0, total_tx = 0, total_segs = 0;
     std::vector<int64_t> bundle_bytes(nb, 0);
@@ -231,6 +247,7 @@ void pack_bundles(const Transcriptome& tr, const std::vector<int>& bundle_ids, b
                     for (auto& iv : il) bundle_bytes[j] += iv.second - iv.first + 1;
                     if (overhang > 0) for (int i = 0; i < b.count; i++) if (fl[j][(size_t)i].private_copy) bundle_bytes[j] += private_len(j, i, tr.txs[b.first + i]);
                     if (nt4) bundle_bytes[j] += bundle_bytes[j] & 1;   // bundles start on a byte boundary
+                    if (nt2) bundle_bytes[j] = (bundle_bytes[j] + 3) & ~(int64_t)3;
                 } else bundle_bytes[j] = b.bend - b.bstart + 1 + 2 * wpad;
             }
             bundle_ntx[j] = b.count;
@@ -242,7 +259,7 @@ void pack_bundles(const Transcriptome& tr, const std::vector<int>& bundle_ids, b
     for (size_t j = 0; j < nb; j++) { total_seq += (size_t)bundle_bytes[j]; total_tx += (size_t)bundle_ntx[j]; total_segs += (size_t)bundle_nseg[j]; }
     if (total_tx > (size_t)INT32_MAX || total_segs > (size_t)INT32_MAX) throw std::runtime_error("batch too large for 32-bit transcript / segment indices: shard it");
     auto up = [](size_t x) { return (x + 255) & ~(size_t)255; };
-    size_t o_seq = 0, o_seq_off = o_seq + up((nt4 ? (total_seq + 1) / 2 : total_seq) + 64), o_bstart = o_seq_off + up((nb + 1) * 8), o_btx = o_bstart + up(nb * 4 + 4),
+    size_t o_seq = 0, o_seq_off = o_seq + up((nt2 ? (total_seq + 3) / 4 : nt4 ? (total_seq + 1) / 2 : total_seq) + 64), o_bstart = o_seq_off + up((nb + 1) * 8), o_btx = o_bstart + up(nb * 4 + 4),
            o_kind = o_btx + up((nb + 1) * 4), o_strand = o_kind + up(total_tx + 4), o_segoff = o_strand + up(total_tx + 4),
            o_cs = o_segoff + up((total_tx + 1) * 4), o_ce = o_cs + up(total_tx * 4 + 4), o_tid = o_ce + up(total_tx * 4 + 4),
            o_segs = o_tid + up(total_tx * 4 + 4), o_phase = o_segs + up(total_segs * 8 + 8), o_sso = o_phase + up(total_segs + 4),
@@ -262,7 +279,7 @@ void pack_bundles(const Transcriptome& tr, const std::vector<int>& bundle_ids, b
     out.tx_ext_hi = overhang > 0 ? (int32_t*)(base + o_xhi) : nullptr;
     out.tx_ext_flags = overhang > 0 ? (uint8_t*)(base + o_xfl) : nullptr;
     out.n_tx = (int32_t)total_tx; out.n_segs = (int64_t)total_segs; out.seq_bytes = (int64_t)total_seq;
-    out.seq_format = nt4 ? ORFX_SEQ_NT4 : ORFX_SEQ_RAW;
+    out.seq_format = nt2 ? ORFX_SEQ_NT2 : nt4 ? ORFX_SEQ_NT4 : ORFX_SEQ_RAW;
     out.tx_global.resize(total_tx);
 
     // offsets per bundle, then the per-transcript / per-segment arrays by several threads
@@ -302,14 +319,17 @@ void pack_bundles(const Transcriptome& tr, const std::vector<int>& bundle_ids, b
     if (has_seq && total_seq) {   // Bundle::load_seq, cpp:821-830
         std::vector<const Fasta::Seq*> chrom(tr.seqnames.size(), nullptr);
         for (size_t k = 0; k < chrom.size(); k++) chrom[k] = tr.fasta->find(tr.seqnames[k]);
-        auto copy_range = [&](size_t j0, size_t j1) {
+        std::vector<std::vector<int64_t>> exc_pos_part(16);
+        std::vector<std::vector<uint8_t>> exc_code_part(16);
+        auto copy_range = [&](size_t j0, size_t j1, unsigned part) {
             std::vector<std::pair<int, int>> il;
             std::vector<int32_t> il_off;
             std::vector<char> raw;
             for (size_t j = j0; j < j1; j++) {
                 const Bundle& b = tr.bundles[bundle_ids[j]];
                 const Fasta::Seq& src = *chrom[(size_t)b.seqid];
-                uint8_t* dst = nt4 ? out.seq + out.seq_off[j] / 2 : out.seq + out.seq_off[j];
+                uint8_t* dst = nt2 ? out.seq + out.seq_off[j] / 4 : nt4 ? out.seq + out.seq_off[j] / 2 : out.seq + out.seq_off[j];
+                if (nt2) memset(dst, 0, (size_t)(bundle_bytes[j] / 4));
                 if (!islands) {
                     if (wpad) fetch_clamped(*tr.fasta, src, (int64_t)b.bstart - 2, (int64_t)b.bend - b.bstart + 3, (char*)dst);
                     else tr.fasta->fetch(src, b.bstart - 1, b.bend - b.bstart + 1, (char*)dst);
@@ -321,7 +341,22 @@ void pack_bundles(const Transcriptome& tr, const std::vector<int>& bundle_ids, b
                     if (len <= 0) return;
                     raw.resize((size_t)len);
                     fetch_clamped(*tr.fasta, src, g0 - 1, len, raw.data());
-                    if (!nt4) memcpy((char*)dst + o, raw.data(), (size_t)len);
+                    if (nt2) {
+                        const uint8_t* sp = (const uint8_t*)raw.data();
+                        auto one = [&](int i, int p) {
+                            const uint8_t c2 = NT2.code[sp[i]];
+                            if (c2 < 4) dst[p >> 2] = (uint8_t)(dst[p >> 2] | (c2 << ((p & 3) * 2)));
+                            else { exc_pos_part[part].push_back(out.seq_off[j] + p); exc_code_part[part].push_back(NT4.code[sp[i]]); }
+                        };
+                        int i = 0, p = o;
+                        for (; i < len && (p & 3); i++, p++) one(i, p);
+                        for (; i + 4 <= len; i += 4, p += 4) {   // whole bytes
+                            const uint8_t c0 = NT2.code[sp[i]], c1 = NT2.code[sp[i + 1]], c2 = NT2.code[sp[i + 2]], c3 = NT2.code[sp[i + 3]];
+                            if (!((c0 | c1 | c2 | c3) & 0x80)) dst[p >> 2] = (uint8_t)(c0 | (c1 << 2) | (c2 << 4) | (c3 << 6));
+                            else for (int k = 0; k < 4; k++) one(i + k, p + k);
+                        }
+                        for (; i < len; i++, p++) one(i, p);
+                    } else if (!nt4) memcpy((char*)dst + o, raw.data(), (size_t)len);
                     else {
                         const uint8_t* sp = (const uint8_t*)raw.data();
                         int i = 0, p = o;
@@ -357,7 +392,8 @@ void pack_bundles(const Transcriptome& tr, const std::vector<int>& bundle_ids, b
             }
         };
         unsigned nthr = (total_seq > (32u << 20) || (islands && nb > 2000)) ? std::min(8u, std::max(1u, std::thread::hardware_concurrency())) : 1u;
-        if (nthr <= 1) copy_range(0, nb);
+        nthr = std::min(nthr, 16u);
+        if (nthr <= 1) copy_range(0, nb, 0);
         else {
             std::vector<std::thread> th;
             size_t j0 = 0;
@@ -366,12 +402,16 @@ void pack_bundles(const Transcriptome& tr, const std::vector<int>& bundle_ids, b
                 size_t j1 = j0;
                 while (j1 < nb && out.seq_off[j1 + 1] <= want) j1++;
                 if (k == nthr - 1) j1 = nb;
-                th.emplace_back(copy_range, j0, j1);
+                th.emplace_back(copy_range, j0, j1, k);
                 j0 = j1;
             }
             for (auto& t : th) t.join();
         }
-        memset(out.seq + (nt4 ? (total_seq + 1) / 2 : total_seq), 0, 64);
+        memset(out.seq + (nt2 ? (total_seq + 3) / 4 : nt4 ? (total_seq + 1) / 2 : total_seq), 0, 64);
+        for (size_t k = 0; k < exc_pos_part.size(); k++) {   // parts hold consecutive bundle ranges: positions stay ascending
+            out.seq_exc_pos.insert(out.seq_exc_pos.end(), exc_pos_part[k].begin(), exc_pos_part[k].end());
+            out.seq_exc_code.insert(out.seq_exc_code.end(), exc_code_part[k].begin(), exc_code_part[k].end());
+        }
     }
 }
 
@@ -602,8 +642,8 @@ int run_orfanage(const Options& opt, const Backend& be) {
             auto a = clk::now();
             // one batch per process: page-locking the arena would cost more than the one upload saves
             if (!shard_ids[(size_t)k].empty())
-                pack_bundles(tr, shard_ids[(size_t)k], opt.keep_all_cds, tid_classes, s.batch, nullptr, nullptr, true, PACK_EVAL, true, opt.overhang, opt.spliced_overhang,
-                             params.align_enabled != 0);
+                pack_bundles(tr, shard_ids[(size_t)k], opt.keep_all_cds, tid_classes, s.batch, nullptr, nullptr, true, PACK_EVAL, false, opt.overhang, opt.spliced_overhang,
+                             params.align_enabled != 0, true);
             auto b = clk::now();
             s.ms_pack = ms(a, b);
             ctx_threads[(size_t)k].join();   // this shard's context (the contexts of one process come up one after the other)

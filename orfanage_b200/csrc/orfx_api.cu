@@ -80,7 +80,7 @@ struct orfx_ctx {
     DBuf d_cnt_q, d_cnt_words, d_cnt_tiles, d_cnt_rows, d_scan_tmp, d_ord;
     DBuf d_clean_keep, d_clean_s, d_clean_e, d_keys;
     DBuf d_xlo, d_xhi, d_xfl;   // --overhang flanks
-    DBuf d_flag;
+    DBuf d_flag, d_exc_pos, d_exc_code;
     // alignment stage (params.align_enabled)
     AlnWork aln;
     DBuf d_aa_off, d_aa_pos, d_cnt_aa, d_tables, d_row_pairs, r_aln[6];
@@ -121,8 +121,12 @@ int upload_batch(orfx_ctx* c, const orfx_batch* b, bool overlap = false) {
     cudaStream_t s = c->stream;
     const size_t nb = (size_t)b->n_bundles, nt = (size_t)b->n_tx, ns = (size_t)b->n_segs;
     const size_t seqb = c->P.has_reference ? (size_t)b->seq_bytes : 0;                    // bases
-    if (b->seq_format != ORFX_SEQ_RAW && b->seq_format != ORFX_SEQ_NT4) return fail(ORFX_E_INVALID, "unknown batch.seq_format");
-    const size_t seq_store = b->seq_format == ORFX_SEQ_NT4 ? (seqb + 1) / 2 : seqb;        // bytes behind batch.seq
+    if (b->seq_format != ORFX_SEQ_RAW && b->seq_format != ORFX_SEQ_NT4 && b->seq_format != ORFX_SEQ_NT2) return fail(ORFX_E_INVALID, "unknown batch.seq_format");
+    if (b->seq_format == ORFX_SEQ_NT2 && seqb) {
+        if (!b->seg_seq_off) return fail(ORFX_E_INVALID, "ORFX_SEQ_NT2 is defined for the islands layout (seg_seq_off)");
+        if (b->n_seq_exc < 0 || (b->n_seq_exc > 0 && (!b->seq_exc_pos || !b->seq_exc_code))) return fail(ORFX_E_INVALID, "ORFX_SEQ_NT2: bad exception list");
+    }
+    const size_t seq_store = b->seq_format == ORFX_SEQ_NT4 ? (seqb + 1) / 2 : (b->seq_format == ORFX_SEQ_NT2 ? (seqb + 3) / 4 : seqb);   // bytes behind batch.seq
     CU(c->d_seq.ensure(seq_store + 64));
     CU(c->d_seq_off.ensure((nb + 1) * 8));
     CU(c->d_bstart.ensure(nb * 4 + 4));
@@ -154,6 +158,11 @@ int upload_batch(orfx_ctx* c, const orfx_batch* b, bool overlap = false) {
     CU(cp(c->d_tid, b->tx_tid_class, nt * 4));
     CU(cp(c->d_segs, b->segs, ns * 8));
     CU(cp(c->d_phase, b->seg_phase, ns));
+    const size_t nexc = (seqb && b->seq_format == ORFX_SEQ_NT2) ? (size_t)b->n_seq_exc : 0;
+    if (nexc) {
+        CU(c->d_exc_pos.ensure(nexc * 8)); CU(c->d_exc_code.ensure(nexc + 4));
+        CU(cp(c->d_exc_pos, b->seq_exc_pos, nexc * 8)); CU(cp(c->d_exc_code, b->seq_exc_code, nexc));
+    }
     const bool islands = seqb && b->seg_seq_off;
     if (islands) { CU(c->d_sso.ensure(ns * 4 + 4)); CU(cp(c->d_sso, b->seg_seq_off, ns * 4)); }
     const bool flanks = seqb && c->P.overhang > 0;
@@ -216,6 +225,7 @@ int upload_batch(orfx_ctx* c, const orfx_batch* b, bool overlap = false) {
     B.tx_ext_flags = flanks && b->tx_ext_flags ? c->d_xfl.as<uint8_t>() : nullptr;
     B.bundle_need = c->d_need.as<uint8_t>(); B.planes = c->d_planes.as<uint32_t>(); B.plane_words = (int64_t)plane_words;
     B.hb_max_segs = c->hb_max_segs; B.hb_max_pairs = c->hb_max_pairs;
+    B.seq_exc_pos = nexc ? c->d_exc_pos.as<int64_t>() : nullptr; B.seq_exc_code = nexc ? c->d_exc_code.as<uint8_t>() : nullptr; B.n_seq_exc = (int64_t)nexc;
     B.tx_aa_off = align ? c->d_aa_off.as<int64_t>() : nullptr;
     c->have_results = false;
     // The batch is caller-supplied: check what every kernel relies on (monotone CSR offsets, ordered chains, bases in
@@ -567,7 +577,7 @@ void orfx_destroy(orfx_ctx* c) {
                  &c->d_segs, &c->d_phase, &c->d_seg_cum, &c->d_tx_len, &c->d_tx_bundle, &c->d_mask_off, &c->d_tile_off, &c->d_q_off, &c->d_q_list,
                  &c->d_row_off, &c->d_tile_tx, &c->d_stop, &c->d_start, &c->d_need, &c->d_planes, &c->d_heavy, &c->d_heavy_count, &c->d_cnt_q, &c->d_cnt_words, &c->d_cnt_tiles, &c->d_cnt_rows, &c->d_scan_tmp,
                  &c->d_ord, &c->r_order, &c->d_best, &c->d_clean_keep, &c->d_clean_s, &c->d_clean_e, &c->d_keys,
-                 &c->d_xlo, &c->d_xhi, &c->d_xfl, &c->d_flag, &c->r_ext[0], &c->r_ext[1]};
+                 &c->d_xlo, &c->d_xhi, &c->d_xfl, &c->d_flag, &c->d_exc_pos, &c->d_exc_code, &c->r_ext[0], &c->r_ext[1]};
     for (DBuf* b : d) b->free_();
     c->aln.free_();
     c->d_aa_off.free_(); c->d_aa_pos.free_(); c->d_cnt_aa.free_(); c->d_tables.free_(); c->d_row_pairs.free_();

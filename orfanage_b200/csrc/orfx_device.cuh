@@ -29,6 +29,9 @@ struct DevBatch {
     const int32_t* seg_seq_off;   // islands layout (else nullptr)
     const int32_t* tx_ext_lo;     // --overhang: usable flank below the first / above the last exon of each query (else nullptr)
     const int32_t* tx_ext_hi;
+    const int64_t* seq_exc_pos;   // ORFX_SEQ_NT2: bases that are none of A C G T (position, ORFX_NT4_* code)
+    const uint8_t* seq_exc_code;
+    int64_t n_seq_exc;
     const uint8_t* tx_ext_flags;  // ORFX_EXT_*_VIRTUAL per query (nullptr when no flank of the batch is a re-read edge base)
     // derived
     int32_t* seg_cum;        // [n_segs] bases of the transcript before this segment (genomic order)

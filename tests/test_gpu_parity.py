@@ -65,6 +65,10 @@ def test_results_match_oracle_bit_for_bit(synth, oracle_lib, gpu, seed, kw):
             assert nt4.seq_format == 1 and nt4.arrays["seq"].size * 2 >= nt4.struct.seq_bytes > nt4.arrays["seq"].size
             assert_same_results(got, ox.run(nt4), "windows vs islands4 (oracle)")
             assert_same_results(got, gpu.run(nt4), "windows vs islands4 (kernel)")
+            nt2 = w.pack(1, 2, layout="islands2")     # 2-bit base codes + exception list
+            assert nt2.seq_format == 2 and nt2.arrays["seq"].size == (nt2.struct.seq_bytes + 3) // 4
+            assert_same_results(got, ox.run(nt2), "windows vs islands2 (oracle)")
+            assert_same_results(got, gpu.run(nt2), "windows vs islands2 (kernel)")
     for pk in PARAM_GRID:
         params = ob.Params.make(**pk)
         gpu.set_params(params)
@@ -79,7 +83,7 @@ def test_results_match_oracle_bit_for_bit(synth, oracle_lib, gpu, seed, kw):
     w.close()
 
 
-@pytest.mark.parametrize("layout", ["islands", "islands4"])
+@pytest.mark.parametrize("layout", ["islands", "islands4", "islands2"])
 def test_codon_scan_masks_match_oracle(synth, oracle_lib, gpu, layout):
     """Per-stage check (SURVEY.md §4 iii): stop / ATG masks of every query transcript, soft-masked and
     IUPAC bases included, both strands, against SEQ::translate semantics restated in the oracle."""
@@ -122,7 +126,7 @@ def test_overhang_matches_oracle(synth, oracle_lib, gpu, seed, overhang, spliced
     d = synth(seed, **kw)
     w = ob.Workload(os.path.join(d, "query.gtf"), template_files(d), os.path.join(d, "genome.fa"), overhang=overhang, spliced_overhang=spliced)
     grown = 0
-    for layout in ("islands4", "windows"):
+    for layout in ("islands4", "islands2", "windows"):
         batch = w.pack(layout=layout)
         a = batch.arrays
         assert a["tx_ext_lo"].size == a["tx_kind"].size and a["tx_ext_lo"].max() <= overhang and a["tx_ext_hi"].max() > 0

@@ -129,6 +129,54 @@ def test_workload_counts_and_batch_layout(synth):
     w.close()
 
 
+def test_nt2_islands_decode_to_the_raw_islands(synth, oracle_lib):
+    """ORFX_SEQ_NT2 (include/orfx.h): four bases per byte plus an exception list.  Decoded with numpy, the batch gives back the
+    raw islands (case folded, non-IUPAC-pair letters as the 4-bit codes name them), bundles start on whole bytes, exception
+    positions ascend, and the oracle answers the same on both batches."""
+    d = synth(7, loci=50, lower=0.4, iupac=0.004, titin=0.1)
+    w = ob.Workload(os.path.join(d, "query.gtf"), template_files(d), os.path.join(d, "genome.fa"), overhang=45)
+    raw = w.pack(1, 2, layout="islands")
+    ar = {k: v.copy() for k, v in raw.arrays.items()}
+    want_raw = None
+    params = ob.Params.make(mode="ALL", overhang=45)
+    with ob.Context(params, lib=oracle_lib, prefix="orfx_oracle_") as ox:
+        want_raw = ox.run(raw)
+    b2 = w.pack(1, 2, layout="islands2")
+    a2 = b2.arrays
+    assert b2.seq_format == 2 and a2["seq"].size == (b2.struct.seq_bytes + 3) // 4
+    assert (a2["seq_off"] % 4 == 0).all() and a2["seq_exc_pos"].size == a2["seq_exc_code"].size > 0
+    assert (np.diff(a2["seq_exc_pos"]) > 0).all()
+    for k in ("segs", "tx_kind", "tx_seg_off", "bundle_tx_off", "seg_seq_off", "tx_ext_lo", "tx_ext_hi"):
+        assert (a2[k] == ar[k]).all(), k
+    codes = (a2["seq"][:, None] >> (np.arange(4, dtype=np.uint8) * 2)[None, :]) & 3
+    letters = np.frombuffer(b"ACGT", dtype=np.uint8)[codes.reshape(-1)].copy()
+    nt4_letter = np.frombuffer(b"NACUGRNNTNYNNNNN", dtype=np.uint8)
+    letters[a2["seq_exc_pos"]] = nt4_letter[a2["seq_exc_code"]]
+    known = set(b"ACGTURYN")
+    n_checked = n_exc = 0
+    for j in range(len(ar["bundle_start"])):
+        n = int(ar["seq_off"][j + 1] - ar["seq_off"][j])
+        r = bytes(ar["seq"][ar["seq_off"][j]:ar["seq_off"][j + 1]]).upper()
+        got = bytes(letters[a2["seq_off"][j]:a2["seq_off"][j] + n])
+        assert a2["seq_off"][j + 1] - a2["seq_off"][j] == (n + 3) // 4 * 4
+        r = bytes(c if c in known else ord("N") for c in r)
+        assert got == r, j
+        n_checked += n
+        n_exc += sum(c not in b"ACGT" for c in r)
+    assert n_checked > 50000 and n_exc == a2["seq_exc_pos"].size
+    with ob.Context(params, lib=oracle_lib, prefix="orfx_oracle_") as ox:
+        got = ox.run(b2)
+    assert got.best.tobytes() == want_raw.best.tobytes()
+    for k in want_raw.rows:
+        assert got.rows[k].tobytes() == want_raw.rows[k].tobytes(), k
+    # save / load keeps the format
+    path = os.path.join(d, "b2.npz")
+    b2.save(path)
+    again = ob.Batch.load(path)
+    assert again.seq_format == 2 and again.struct.seq_bytes == b2.struct.seq_bytes and again.struct.n_seq_exc == b2.struct.n_seq_exc
+    w.close()
+
+
 def test_sharding_is_a_partition(synth, oracle_lib):
     """Shards are disjoint, cover every active bundle, and evaluating them separately gives the same
     per-query answers as one batch (loci are independent: SURVEY.md §8e)."""
