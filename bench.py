@@ -441,20 +441,29 @@ def ours(args):
             c_.submit(batch)
         for c_ in ring:
             c_.wait(copy=False)
+        # one host thread per context (as the CLI drives its shards): orfx_submit blocks on the batch's validation flag and on
+        # the four totals that size the row buffers, and a second caller thread keeps the copy engine fed meanwhile
+        import threading
+        share = [(args.steps + 1) // 2, args.steps // 2]
+        errs = []
+
+        def drive(c_, n):
+            try:
+                for _ in range(n):
+                    c_.submit(batch)
+                    c_.wait(copy=False)
+            except Exception as e:   # noqa: BLE001
+                errs.append(e)
         barrier()
         t0 = time.perf_counter()
-        busy = [False, False]
-        for i in range(args.steps):
-            k = i & 1
-            if busy[k]:
-                ring[k].wait(copy=False)
-            ring[k].submit(batch)
-            busy[k] = True
-        for k in (args.steps & 1, (args.steps + 1) & 1):   # oldest first
-            if busy[k]:
-                ring[k].wait(copy=False)
+        th = [threading.Thread(target=drive, args=(ring[k], share[k])) for k in range(2)]
+        for t_ in th:
+            t_.start()
+        for t_ in th:
+            t_.join()
         barrier()
         e2e3_ms = (time.perf_counter() - t0) * 1e3
+        assert not errs, errs
         cxb.close()
 
     # ---- leg 4 (last: packing the shards releases the whole-batch arrays `batch` views): the same call sequence on several contexts, each with its share of the loci (shard_bundles): the upload of one
@@ -747,8 +756,8 @@ def main():
         v3 = m["nq_all"] / (m["e2e3_ms"] / K / 1e3)
         if v3 > e2e_value:
             e2e_value, e2e_step_ms = v3, m["e2e3_ms"] / K
-            e2e_api = ("orfx_submit + orfx_wait on pinned host batches (include/orfx.h) as a stream of batches over two contexts: batch k + 1 is "
-                       "submitted while batch k is evaluated; every batch is uploaded and its results read back inside the timed region")
+            e2e_api = ("orfx_submit + orfx_wait on pinned host batches (include/orfx.h) as a stream of batches over two contexts, one caller thread each: batch k + 1 is "
+                       "uploaded while batch k is evaluated; every batch is uploaded and its results read back inside the timed region")
         e2e_single["streamed"] = {"contexts": 2, "value": v3, "ms_per_step": m["e2e3_ms"] / K}
     peak, peak_src = measured_peak()
     c4 = m["c4"]
