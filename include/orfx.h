@@ -331,6 +331,27 @@ int  orfx_align_batch(orfx_ctx* ctx, const uint8_t* aa, const int64_t* off, int6
                       const int32_t* pair_q, const int32_t* pair_t, int64_t n_pairs,
                       int gapo, int gape, orfx_aln_out* out, double* cells, float* ms);
 
+/* orfx_align_batch with NO allocation inside the call.  No counterpart in the reference: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid
+ * it).  The call makes no cudaMalloc / cudaFree / cudaMallocHost and creates no events; its scratch (pair descriptors, the
+ * longest-first schedule, the per-warp stripe edges) is one file-scope `static __device__` array of ORFX_STATIC_SCRATCH_MIB
+ * MiB that every GPU which loads the library holds until the process exits.
+ *   - aa, off[n_seq+1], pair_q, pair_t and the four arrays of *out are DEVICE memory of the context's device (the caller's
+ *     own allocations); meaning and results are those of orfx_align_batch, bit for bit.
+ *   - limits: n_pairs <= ORFX_STATIC_MAX_PAIRS per call, every protein <= ORFX_STATIC_MAX_LEN residues; beyond either the call
+ *     answers ORFX_E_UNSUPPORTED and names the limit in orfx_last_error() (use orfx_align_batch, or split the call).  A pair
+ *     index outside [0, n_seq) or descending offsets: ORFX_E_INVALID.  After an error the output arrays are unspecified.
+ *   - the call returns after the context's stream has drained (it synchronises it twice).
+ *   - all calls share the one array, which keeps the previous call's contents (what has to start at zero is cleared by every
+ *     call): calls that overlap on the GPU -- two contexts of one device driven from two threads -- race.  One at a time per
+ *     device. */
+#define ORFX_STATIC_MAX_PAIRS 65536
+#define ORFX_STATIC_MAX_LEN 1024
+#define ORFX_STATIC_SCRATCH_MIB 21
+int  orfx_align_pairs_static(orfx_ctx* ctx, const uint8_t* aa, const int64_t* off, int64_t n_seq,
+                             const int32_t* pair_q, const int32_t* pair_t, int64_t n_pairs,
+                             int gapo, int gape, const orfx_aln_out* out);
+
 /* Integer-ALU issue-rate microbenchmark on the context's device: the denominator of the alignment roofline
  * (SURVEY.md §8d).  ops4[0] = IADD3 instructions/s; ops4[1] = IADD + VIMNMX3 pairs (2 operations each)/s;
  * ops4[2] = VIADDMNMX (add + max, 2 operations each)/s; ops4[3] = IDP.4A instructions/s; all SMs, 8

@@ -314,6 +314,10 @@ def load_device_library(path=None):
     lib.orfx_align_batch.restype = C.c_int
     lib.orfx_align_batch.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_int64,
                                      C.c_int, C.c_int, C.POINTER(_AlnOut), C.POINTER(C.c_double), C.POINTER(C.c_float)]
+    if hasattr(lib, "orfx_align_pairs_static"):   # the CUDA library only
+        lib.orfx_align_pairs_static.restype = C.c_int
+        lib.orfx_align_pairs_static.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_int64,
+                                                C.c_int, C.c_int, C.POINTER(_AlnOut)]
     lib.orfx_debug_set.restype = C.c_int
     lib.orfx_debug_set.argtypes = [C.c_void_p, C.c_char_p, C.c_int64]
     if hasattr(lib, "orfx_int_alu_peak"):
@@ -457,6 +461,14 @@ class Context:
         self._check(self.lib.orfx_align_batch(self.handle, aa.ctypes.data, off.ctypes.data, len(off) - 1, pq.ctypes.data,
                                               pt.ctypes.data, n, gapo, gape, C.byref(o), C.byref(cells), C.byref(ms)))
         return {k: v[:n] for k, v in out.items()}, cells.value, ms.value
+
+    def align_static(self, d_aa, d_off, n_seq, d_pair_q, d_pair_t, n_pairs, d_out, gapo=12, gape=2):
+        """orfx_align_pairs_static: every pointer is a DEVICE address (int) of the context's device; d_out = four addresses
+        (max, score, mqe, mte).  Nothing is allocated inside the call (scratch = a static __device__ array of the library);
+        limits ORFX_STATIC_MAX_PAIRS / ORFX_STATIC_MAX_LEN of include/orfx.h."""
+        o = _AlnOut(*[int(x) for x in d_out])
+        self._check(self.lib.orfx_align_pairs_static(self.handle, int(d_aa), int(d_off), int(n_seq), int(d_pair_q), int(d_pair_t), int(n_pairs),
+                                                     gapo, gape, C.byref(o)))
 
     def clean(self, batch, rescue=False):
         """orfx_clean_templates on a cleaning batch: returns (keep u8, cds_start i32, cds_end i32), one entry per

@@ -18,6 +18,7 @@
 #include "orfx_buffers.cuh"
 #include "orfx_mat50.h"
 #include <algorithm>
+#include <mutex>
 #include <numeric>
 #include <string>
 #include <type_traits>
@@ -587,6 +588,125 @@ int align_batch_device(AlnWork& w, cudaStream_t stream, int n_sm, const uint8_t*
     cudaMemcpyAsync(out->mqe, d_out[2], (size_t)n_pairs * 4, cudaMemcpyDeviceToHost, stream);
     cudaMemcpyAsync(out->mte, d_out[3], (size_t)n_pairs * 4, cudaMemcpyDeviceToHost, stream);
     if (!ck(cudaStreamSynchronize(stream), "alignment results")) return ORFX_E_CUDA;
+    return ORFX_OK;
+}
+
+}  // namespace orfx
+
+// ---- orfx_align_pairs_static: the alignment with no allocation inside the call --------------------------------------
+// No counterpart in the reference; added for callers that cannot call cudaMalloc
+// (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  Everything orfx_align_batch keeps in
+// context-owned, grow-on-demand buffers (pair descriptors, cost classes, the longest-first order, the histogram, the
+// scheduling counters, the per-warp stripe edges) lives in ONE file-scope device array of a fixed size: every GPU that
+// loads the library holds these bytes until the process exits.  All calls share the array and it keeps the last call's
+// contents: the histogram, totals, counters and the error flag are cleared at the start of every call, everything else is
+// written before it is read.  Two calls that overlap on the GPU (different contexts / streams of one device) race.
+namespace {
+constexpr size_t st_up(size_t x) { return (x + 255) & ~(size_t)255; }
+constexpr long long ST_MAX_PAIRS = ORFX_STATIC_MAX_PAIRS;   // pairs per call
+constexpr long long ST_MAX_LEN = ORFX_STATIC_MAX_LEN;       // residues per protein: no pair reaches the block-cooperative class
+constexpr int ST_MAX_CTAS = 148;                            // one CTA per SM of a B200
+constexpr size_t ST_PAIRS = 0;
+constexpr size_t ST_CLS = ST_PAIRS + st_up((size_t)ST_MAX_PAIRS * 24);
+constexpr size_t ST_ORDER = ST_CLS + st_up((size_t)ST_MAX_PAIRS * 2 + 16);
+constexpr size_t ST_HIST = ST_ORDER + st_up((size_t)ST_MAX_PAIRS * 4 + 16);
+constexpr size_t ST_META = ST_HIST + st_up(2 * 128 * 4);    // AlnMeta (40 bytes), the error flag at +64
+constexpr size_t ST_COUNTERS = ST_META + 256;
+constexpr size_t ST_STRIPES = ST_COUNTERS + 256;            // [CTA][warp][H | F][ST_MAX_LEN] int32
+constexpr size_t ST_BYTES = ST_STRIPES + (size_t)ST_MAX_CTAS * ORFX_ALN_WARPS * 2 * (size_t)ST_MAX_LEN * 4;
+static_assert(ST_BYTES <= ((size_t)ORFX_STATIC_SCRATCH_MIB << 20), "the static scratch outgrew the size include/orfx.h states");
+}  // namespace
+static __device__ __align__(256) unsigned char g_static_scratch[ST_BYTES];
+
+namespace orfx {
+namespace {
+static_assert(sizeof(AlnPair) == 24 && ALN_NBINS == 2 * 128, "static scratch layout");
+// In host code `g_static_scratch` is a host-side stand-in, not a device address: ask the runtime once per device (with that
+// device current) and hand the answer to the kernels.
+std::mutex g_static_mu;
+unsigned char* g_static_ptr[64] = {};
+int static_scratch(int device, unsigned char** out, std::string& err) {
+    if (device < 0 || device >= 64) { err = "device ordinal outside the static scratch table"; return ORFX_E_UNSUPPORTED; }
+    std::lock_guard<std::mutex> lk(g_static_mu);
+    if (!g_static_ptr[device]) {
+        void* p = nullptr;
+        const cudaError_t e = cudaGetSymbolAddress(&p, g_static_scratch);
+        if (e != cudaSuccess || !p) { err = std::string("cudaGetSymbolAddress(static scratch): ") + cudaGetErrorString(e); return ORFX_E_CUDA; }
+        g_static_ptr[device] = (unsigned char*)p;
+    }
+    *out = g_static_ptr[device];
+    return ORFX_OK;
+}
+// pair descriptors from the caller's index arrays (all in device memory), with the checks orfx_align_batch makes on the
+// host: flag bit 0 = index out of range, bit 1 = a protein longer than the static limit, bit 2 = offsets not ascending
+__global__ void __launch_bounds__(256) aln_pairs_static_kernel(const int64_t* __restrict__ off, long long n_seq, const int32_t* __restrict__ pq,
+                                                              const int32_t* __restrict__ pt, long long n, int max_len, AlnPair* __restrict__ out, unsigned* flag) {
+    const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const int a = pq[i], b = pt[i];
+    AlnPair p{0, 0, -1, 0};
+    unsigned bad = 0;
+    if (a < 0 || a >= n_seq || b < 0 || b >= n_seq) bad = 1;
+    else {
+        const long long qa = off[a], qb = off[a + 1], ta = off[b], tb = off[b + 1];
+        if (qa < 0 || ta < 0 || qb < qa || tb < ta) bad = 4;
+        else if (qb - qa > max_len || tb - ta > max_len) bad = 2;
+        else { p.q_off = qa; p.t_off = ta; p.qlen = (int)(qb - qa); p.tlen = (int)(tb - ta); }
+    }
+    if (bad) atomicOr(flag, bad);
+    out[i] = p;
+}
+}  // namespace
+
+// d_aa / d_off / d_pair_q / d_pair_t and the four output arrays are DEVICE memory of the context's device.  Synchronises the
+// stream twice (after the scheduling kernels: the totals come back through a plain cudaMemcpy into a stack variable; and at
+// the end).  No cudaMalloc / cudaFree / cudaMallocHost / event creation in here.
+int align_pairs_static_device(int device, cudaStream_t stream, int n_sm, const uint8_t* d_aa, const int64_t* d_off, int64_t n_seq, const int32_t* d_pq,
+                              const int32_t* d_pt, int64_t n_pairs, int gapo, int gape, const orfx_aln_out* d_out, std::string& err) {
+    auto ck = [&](cudaError_t e, const char* what) { if (e != cudaSuccess) { err = std::string(what) + ": " + cudaGetErrorString(e); return false; } return true; };
+    if (n_pairs > ST_MAX_PAIRS) {
+        err = "orfx_align_pairs_static: " + std::to_string((long long)n_pairs) + " pairs in one call, the static scratch holds " + std::to_string(ST_MAX_PAIRS) +
+              " (ORFX_STATIC_MAX_PAIRS); split the call or use orfx_align_batch";
+        return ORFX_E_UNSUPPORTED;
+    }
+    if (gapo < 0 || gape < 0 || gapo + gape > 64) { err = "gap costs outside this build's range (0 <= gapo + gape <= 64)"; return ORFX_E_UNSUPPORTED; }
+    if (n_pairs == 0) return ORFX_OK;
+    unsigned char* base = nullptr;
+    const int rc = static_scratch(device, &base, err);
+    if (rc) return rc;
+    AlnPair* pairs = reinterpret_cast<AlnPair*>(base + ST_PAIRS);
+    uint16_t* cls = reinterpret_cast<uint16_t*>(base + ST_CLS);
+    int32_t* order = reinterpret_cast<int32_t*>(base + ST_ORDER);
+    unsigned* hist = reinterpret_cast<unsigned*>(base + ST_HIST);
+    AlnMeta* meta = reinterpret_cast<AlnMeta*>(base + ST_META);
+    unsigned* flag = reinterpret_cast<unsigned*>(base + ST_META + 64);
+    unsigned long long* counters = reinterpret_cast<unsigned long long*>(base + ST_COUNTERS);
+    int32_t* stripes = reinterpret_cast<int32_t*>(base + ST_STRIPES);
+    // what must start at zero: histogram, totals + error flag, scheduling counters (one contiguous range)
+    if (!ck(cudaMemsetAsync(base + ST_HIST, 0, ST_STRIPES - ST_HIST, stream), "clearing the static scratch")) return ORFX_E_CUDA;
+    const unsigned nblk = (unsigned)((n_pairs + 255) / 256);
+    aln_pairs_static_kernel<<<nblk, 256, 0, stream>>>(d_off, n_seq, d_pq, d_pt, n_pairs, (int)ST_MAX_LEN, pairs, flag);
+    aln_classify_kernel<<<nblk, 256, 0, stream>>>(pairs, n_pairs, cls, hist, meta);
+    aln_scan_kernel<<<1, 32, 0, stream>>>(hist, meta);
+    aln_scatter_kernel<<<nblk, 256, 0, stream>>>(cls, n_pairs, hist, order);
+    if (!ck(cudaStreamSynchronize(stream), "alignment scheduling")) return ORFX_E_CUDA;
+    struct { AlnMeta m; unsigned char pad[64 - sizeof(AlnMeta)]; unsigned flag; } h;
+    static_assert(sizeof(AlnMeta) <= 64, "flag offset");
+    if (!ck(cudaMemcpy(&h, meta, 68, cudaMemcpyDeviceToHost), "reading the alignment totals")) return ORFX_E_CUDA;
+    if (h.flag) {
+        err = std::string("orfx_align_pairs_static: ") + ((h.flag & 1) ? "pair index out of range" : (h.flag & 4) ? "sequence offsets are not ascending"
+              : "a protein is longer than " + std::to_string(ST_MAX_LEN) + " residues (ORFX_STATIC_MAX_LEN); use orfx_align_batch");
+        return (h.flag & 5) ? ORFX_E_INVALID : ORFX_E_UNSUPPORTED;
+    }
+    if (h.m.n_active == 0) return ORFX_OK;
+    if (h.m.n_long != 0 || h.m.max_tlen > (unsigned long long)ST_MAX_LEN) { err = "orfx_align_pairs_static: internal: a pair outside the static limits was scheduled"; return ORFX_E_INVALID; }
+    const long long n_active = (long long)h.m.n_active;
+    const int grid = (int)std::max<long long>(1, std::min<long long>(std::min(n_sm, ST_MAX_CTAS), (n_active + ALN_WARPS - 1) / ALN_WARPS));
+    cudaFuncSetAttribute(align_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(ALN_WARPS * sizeof(WarpSmem)));
+    align_kernel<<<grid, ALN_WARPS * 32, ALN_WARPS * sizeof(WarpSmem), stream>>>(d_aa, 1, 1, pairs, order, n_active, 0, gapo, gape, d_out->max, d_out->score, d_out->mqe,
+                                                                               d_out->mte, stripes, ST_MAX_LEN, stripes, 32, counters);
+    if (!ck(cudaGetLastError(), "alignment kernel launch")) return ORFX_E_CUDA;
+    if (!ck(cudaStreamSynchronize(stream), "alignment kernel")) return ORFX_E_CUDA;
     return ORFX_OK;
 }
 

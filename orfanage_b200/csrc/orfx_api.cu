@@ -34,6 +34,8 @@ int launch_count_pairs(const DevBatch& B, int64_t* cnt, int64_t* scan_tmp, cudaS
 int launch_score_pairs(const DevBatch& B, const DevRows& R, int n_queries, cudaStream_t s);
 int align_batch_device(AlnWork& w, cudaStream_t stream, int n_sm, const uint8_t* aa, const int64_t* off, int64_t n_seq, const int32_t* pair_q,
                        const int32_t* pair_t, int64_t n_pairs, int gapo, int gape, orfx_aln_out* out, double* cells, float* ms, std::string& err);
+int align_pairs_static_device(int device, cudaStream_t stream, int n_sm, const uint8_t* d_aa, const int64_t* d_off, int64_t n_seq, const int32_t* d_pq,
+                              const int32_t* d_pt, int64_t n_pairs, int gapo, int gape, const orfx_aln_out* d_out, std::string& err);
 int align_pairs_device(AlnWork& w, cudaStream_t stream, int n_sm, const uint8_t* d_aa, int q_stride, int t_stride, const AlnPair* d_pairs, long long n,
                        int gapo, int gape, int32_t* const d_out[4], double* cells, float* ms, int* n_launches, std::string& err);
 void build_translate_tables(TranslateTables& T);
@@ -803,6 +805,21 @@ int orfx_align_batch(orfx_ctx* c, const uint8_t* aa, const int64_t* off, int64_t
     CU(cudaSetDevice(c->device));
     std::string err;
     int rc = align_batch_device(c->aln, c->stream, c->n_sm, aa, off, n_seq, pair_q, pair_t, n_pairs, gapo, gape, out, cells, ms, err);
+    if (rc) return fail(rc, err);
+    return ORFX_OK;
+}
+
+// no counterpart in the reference (see include/orfx.h): the alignment over caller-owned device arrays, scratch in a static
+// __device__ array (align.cu), nothing allocated in the call
+int orfx_align_pairs_static(orfx_ctx* c, const uint8_t* aa, const int64_t* off, int64_t n_seq, const int32_t* pair_q, const int32_t* pair_t,
+                            int64_t n_pairs, int gapo, int gape, const orfx_aln_out* out) {
+    if (!c) return fail(ORFX_E_INVALID, "null ctx");
+    if (n_pairs < 0 || n_seq < 0) return fail(ORFX_E_INVALID, "negative argument");
+    if (n_pairs > 0 && (!aa || !off || !pair_q || !pair_t || !out || !out->max || !out->score || !out->mqe || !out->mte)) return fail(ORFX_E_INVALID, "null argument");
+    if (c->pending) return fail(ORFX_E_STATE, "orfx_align_pairs_static: a submitted batch is still pending on this context (orfx_wait first)");
+    CU(cudaSetDevice(c->device));
+    std::string err;
+    const int rc = align_pairs_static_device(c->device, c->stream, c->n_sm, aa, off, n_seq, pair_q, pair_t, n_pairs, gapo, gape, out, err);
     if (rc) return fail(rc, err);
     return ORFX_OK;
 }
