@@ -143,17 +143,20 @@ int launch_exclusive_scan3(const int64_t* in0, int64_t* out0, const int64_t* in1
 // transcript kind, 4 QUERY / TEMPLATE transcript without a segment, 8 segment with end < start or start < 0 or a chain
 // that is not ascending and disjoint, 16 negative --overhang flank, 32 a query segment (with its flank) outside its
 // bundle's bases.  Every later kernel trusts these properties.
+// eight lanes per transcript (as tx_prep_kernel): the segment loads of a chain are coalesced
 __global__ void __launch_bounds__(256) validate_batch_kernel(DevBatch B, int has_seq, int allow_empty, int* flag) {
-    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int64_t gt = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int64_t i = gt >> 3;
+    const int sub = (int)(gt & 7);
     int bad = 0;
-    if (i == 0) {
+    if (gt == 0) {
         if (B.bundle_tx_off[0] != 0 || B.bundle_tx_off[B.n_bundles] != B.n_tx || B.tx_seg_off[0] != 0 || (int64_t)B.tx_seg_off[B.n_tx] != B.n_segs) bad |= 1;
         if (has_seq && (B.seq_off[0] != 0 || B.seq_off[B.n_bundles] > B.seq_bytes)) bad |= 1;
     }
-    if (i < B.n_bundles) {
-        const int x0 = B.bundle_tx_off[i], x1 = B.bundle_tx_off[i + 1];
+    if (gt < B.n_bundles) {
+        const int x0 = B.bundle_tx_off[gt], x1 = B.bundle_tx_off[gt + 1];
         if (x0 < 0 || x1 < x0 || x1 > B.n_tx) bad |= 1;
-        if (has_seq) { const int64_t a = B.seq_off[i], b = B.seq_off[i + 1]; if (a < 0 || b < a || b > B.seq_bytes) bad |= 1; }
+        if (has_seq) { const int64_t a = B.seq_off[gt], b = B.seq_off[gt + 1]; if (a < 0 || b < a || b > B.seq_bytes) bad |= 1; }
     }
     if (i < B.n_tx) {
         const int s0 = B.tx_seg_off[i], s1 = B.tx_seg_off[i + 1];
@@ -170,14 +173,13 @@ __global__ void __launch_bounds__(256) validate_batch_kernel(DevBatch B, int has
             const bool check_seq = has_seq && kind == ORFX_TX_QUERY && B.n_bundles > 0;
             const int64_t nbases = check_seq ? B.seq_off[lo + 1] - B.seq_off[lo] : 0;
             const int bstart = check_seq && !B.seg_seq_off ? B.bundle_start[lo] : 0;
-            int prev_end = INT_MIN;
-            for (int k = s0; k < s1; k++) {
+            for (int k = s0 + sub; k < s1; k += 8) {
                 const orfx_seg sg = B.segs[k];
-                if (sg.end < sg.start || sg.start < 0 || (prev_end != INT_MIN && sg.start <= prev_end)) bad |= 8;
-                prev_end = sg.end;
+                if (sg.end < sg.start || sg.start < 0 || (k > s0 && sg.start <= B.segs[k - 1].end)) bad |= 8;
                 if (check_seq) {
-                    const int64_t first = (B.seg_seq_off ? (int64_t)B.seg_seq_off[k] : (int64_t)sg.start - bstart) - (k == s0 ? xlo : 0);
-                    const int64_t last = (B.seg_seq_off ? (int64_t)B.seg_seq_off[k] : (int64_t)sg.start - bstart) + (sg.end - sg.start) + (k == s1 - 1 ? xhi : 0);
+                    const int64_t at = B.seg_seq_off ? (int64_t)B.seg_seq_off[k] : (int64_t)sg.start - bstart;
+                    const int64_t first = at - (k == s0 ? xlo : 0);
+                    const int64_t last = at + (sg.end - sg.start) + (k == s1 - 1 ? xhi : 0);
                     if (first < 0 || last >= nbases) bad |= 32;
                 }
             }
@@ -187,7 +189,7 @@ __global__ void __launch_bounds__(256) validate_batch_kernel(DevBatch B, int has
 }
 int launch_validate(const DevBatch& B, int has_seq, int allow_empty, int* flag, cudaStream_t s) {
     cudaMemsetAsync(flag, 0, sizeof(int), s);
-    const int64_t n = std::max<int64_t>(std::max<int64_t>(B.n_tx, B.n_bundles), 1);
+    const int64_t n = std::max<int64_t>(std::max<int64_t>((int64_t)B.n_tx * 8, B.n_bundles), 1);
     validate_batch_kernel<<<(unsigned)((n + 255) / 256), 256, 0, s>>>(B, has_seq, allow_empty, flag);
     return 1;
 }
