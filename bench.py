@@ -30,7 +30,8 @@ C2 = dict(seed=20261104, loci=20000, chroms=24, chrom_len=125000000, queries=13,
 # over the GPUs of the box (strong scaling; the product's own shard_bundles deals the loci)
 C4 = dict(seed=20261107, loci=20000, chroms=24, chrom_len=125000000, queries=100, templates=8, template_files=1)
 MODE = "LONGEST_MATCH,BEST"
-LAYOUT = "islands2"          # islands of query-exon bases as 2-bit codes + exception list (ORFX_SEQ_NT2): the smallest upload
+LAYOUT = "islands2d"         # islands of query-exon bases as 2-bit codes + exception list (ORFX_SEQ_NT2), chains through the
+                             # segment dictionary (orfx_batch::seg_ref): the smallest upload
 ALG_BYTES_PER_NT = 1.25      # codon scan: 1 B read per spliced nucleotide + 2 mask bits written
 
 
@@ -400,6 +401,7 @@ def ours(args):
         e2e_dev = [e2e_dev[0] + r.ms_h2d, e2e_dev[1] + r.ms_kernels, e2e_dev[2] + r.ms_d2h]
     barrier()
     e2e_ms = (time.perf_counter() - t0) * 1e3
+    assert cx.last_upload_bytes() == h2d_bytes, "the library copied %d bytes per step, the batch arrays say %d" % (cx.last_upload_bytes(), h2d_bytes)
     d2h_bytes = int(nq * ob._capi.BEST_DTYPE.itemsize + 32)
 
     # ---- leg 2b: the path with the alignment stage enabled (params.align_enabled, --pi): every scored row's ORF protein against
@@ -781,7 +783,7 @@ def main():
                    "query_transcripts_per_gpu": m["nq"], "query_transcripts_total": m["nq_all"], "templates_after_dedup": m["n_templates"], "bundles": m["n_bundles"],
                    "best_digest": m["digest"],
                    "genome": "%d x %d bp random, planted ORFs, seed %d%s" % (m["cfg"]["chroms"], m["cfg"]["chrom_len"], m["cfg"]["seed"], "" if c4 else "+rank"),
-                   "spliced_query_nt_per_gpu": m["nt_sum"], "sequence_upload_bytes_per_gpu": m["windows"], "sequence_format": "islands, 2-bit base codes + exception list (ORFX_SEQ_NT2)",
+                   "spliced_query_nt_per_gpu": m["nt_sum"], "sequence_upload_bytes_per_gpu": m["windows"], "sequence_format": "islands, 2-bit base codes + exception list (ORFX_SEQ_NT2)", "chain_format": "segment dictionary (orfx_batch::seg_ref): 16-bit reference per segment + the distinct records of each locus",
                    "parallelism": "locus shards, one per GPU, no collective", "orfs_found": m["found"],
                    "l2": "inputs larger than L2 (windows + chains + masks > 126 MB); no explicit flush",
                    "timing": "CUDA events on the library stream around the whole path, summed over steps, max over ranks",

@@ -43,7 +43,8 @@ int64_t orfxh_count(const orfxh_workload* w, int what);
 /* Splits the active bundles over n_shards (longest-processing-time greedy) and packs
  * shard `shard`.  layout: 0 = whole locus windows, 1 = islands (only the bases under query exons; see
  * orfx_batch.seq in orfx.h), 2 = islands as 4-bit base codes (ORFX_SEQ_NT4), 3 = islands as raw bytes that also cover the template
- * CDS segments (what orfx_params::align_enabled needs), 4 = islands as 2-bit base codes plus an exception list (ORFX_SEQ_NT2).  The arrays behind *out are owned by the workload and stay valid until the next
+ * CDS segments (what orfx_params::align_enabled needs), 4 = islands as 2-bit base codes plus an exception list (ORFX_SEQ_NT2), 5 = layout 4 with the segment dictionary (orfx_batch::seg_ref;
+ * the per-segment arrays are still there for host readers, the device library takes the chains from the dictionary).  The arrays behind *out are owned by the workload and stay valid until the next
  * orfxh_pack with the same shard index or orfxh_free.  alloc/dealloc (both NULL = malloc/free) let
  * the caller place the arrays in pinned memory (orfx_host_alloc / orfx_host_free of orfx.h). */
 int orfxh_pack(orfxh_workload* w, int shard, int n_shards, int layout, void* (*alloc)(size_t), void (*dealloc)(void*), orfx_batch* out);

@@ -578,6 +578,33 @@ bool score_gt(const orfx_params& p, const Sc& l, const Sc& r) {   // orfanage.cp
     return l.tlen > r.tlen;
 }
 
+// Segment dictionary (orfx_batch::seg_ref, include/orfx.h): when present it is the only source of the chains.  A copy of the
+// batch header whose segs / seg_phase / seg_seq_off point at the expanded records.
+struct Expanded {
+    orfx_batch b;
+    std::vector<orfx_seg> segs;
+    std::vector<int8_t> phase;
+    std::vector<int32_t> sso;
+    explicit Expanded(const orfx_batch* in) : b(*in) {
+        if (!in->seg_ref || in->n_segs <= 0) return;
+        if (!in->bundle_dict_off || !in->dict_segs || !in->dict_phase || in->n_dict <= 0) throw std::runtime_error("seg_ref without a dictionary");
+        segs.resize((size_t)in->n_segs); phase.resize((size_t)in->n_segs);
+        if (in->dict_seq_off) sso.resize((size_t)in->n_segs);
+        for (int bi = 0; bi < in->n_bundles; bi++) {
+            const int64_t d0 = in->bundle_dict_off[bi], d1 = in->bundle_dict_off[bi + 1];
+            if (d0 < 0 || d1 < d0 || d1 > in->n_dict) throw std::runtime_error("bundle_dict_off not monotone / beyond n_dict");
+            for (int x = in->bundle_tx_off[bi]; x < in->bundle_tx_off[bi + 1]; x++)
+                for (int k = in->tx_seg_off[x]; k < in->tx_seg_off[x + 1]; k++) {
+                    const int64_t d = d0 + in->seg_ref[k];
+                    if (d >= d1) throw std::runtime_error("seg_ref outside its bundle's dictionary records");
+                    segs[(size_t)k] = in->dict_segs[d]; phase[(size_t)k] = in->dict_phase[d];
+                    if (in->dict_seq_off) sso[(size_t)k] = in->dict_seq_off[d];
+                }
+        }
+        b.segs = segs.data(); b.seg_phase = phase.data(); b.seg_seq_off = in->dict_seq_off ? sso.data() : nullptr;
+    }
+};
+
 T load_tx(const orfx_batch* b, int tx) {
     T t;
     t.strand = (char)b->tx_strand[tx];
@@ -862,7 +889,7 @@ int orfx_oracle_submit(orfx_ctx* ctx, const orfx_batch* batch) {
     Ctx* c = reinterpret_cast<Ctx*>(ctx);
     if (!c || !batch) { g_err = "null argument"; return ORFX_E_INVALID; }
     if (c->p.overhang > 0 && c->p.has_reference && batch->n_tx > 0 && (!batch->tx_ext_lo || !batch->tx_ext_hi)) { g_err = "--overhang needs tx_ext_lo / tx_ext_hi"; return ORFX_E_INVALID; }
-    try { evaluate(*c, batch); } catch (const std::exception& e) { g_err = e.what(); return ORFX_E_INVALID; }
+    try { const Expanded ex(batch); evaluate(*c, &ex.b); } catch (const std::exception& e) { g_err = e.what(); return ORFX_E_INVALID; }
     c->submitted = true;
     return ORFX_OK;
 }
@@ -893,9 +920,12 @@ void orfx_oracle_destroy(orfx_ctx* ctx) { delete reinterpret_cast<Ctx*>(ctx); }
 
 // Template cleaning oracle: the per-transcript body of Transcriptome::clean_cds (Transcriptome.cpp:1063-1100)
 // on a cleaning batch (see orfx_clean_templates in include/orfx.h).
-int orfx_oracle_clean_templates(orfx_ctx* ctx, const orfx_batch* b, int rescue, orfx_clean_out* out, int64_t* n_out) {
+int orfx_oracle_clean_templates(orfx_ctx* ctx, const orfx_batch* b_in, int rescue, orfx_clean_out* out, int64_t* n_out) {
     Ctx* c = reinterpret_cast<Ctx*>(ctx);
-    if (!c || !b || !out) { g_err = "null argument"; return ORFX_E_INVALID; }
+    if (!c || !b_in || !out) { g_err = "null argument"; return ORFX_E_INVALID; }
+    std::unique_ptr<Expanded> ex;
+    try { ex.reset(new Expanded(b_in)); } catch (const std::exception& e) { g_err = e.what(); return ORFX_E_INVALID; }
+    const orfx_batch* b = &ex->b;
     if (!b->seq && b->seq_bytes) { g_err = "cleaning needs the sequence"; return ORFX_E_INVALID; }
     const bool non_aug = c->p.non_aug != 0;
     int64_t k = 0;
@@ -933,9 +963,12 @@ int orfx_oracle_clean_templates(orfx_ctx* ctx, const orfx_batch* b, int rescue, 
 
 // orfcompare oracle: TX::score (Transcriptome.cpp:699-762) of every (query, template) pair of every bundle of a
 // compare batch (see orfx_score_pairs in include/orfx.h); results live in the context until the next call.
-int orfx_oracle_score_pairs(orfx_ctx* ctx, const orfx_batch* b, orfx_results* r) {
+int orfx_oracle_score_pairs(orfx_ctx* ctx, const orfx_batch* b_in, orfx_results* r) {
     Ctx* c = reinterpret_cast<Ctx*>(ctx);
-    if (!c || !b || !r) { g_err = "null argument"; return ORFX_E_INVALID; }
+    if (!c || !b_in || !r) { g_err = "null argument"; return ORFX_E_INVALID; }
+    std::unique_ptr<Expanded> ex;
+    try { ex.reset(new Expanded(b_in)); } catch (const std::exception& e) { g_err = e.what(); return ORFX_E_INVALID; }
+    const orfx_batch* b = &ex->b;
     c->q_tx.clear(); c->t_tx.clear(); c->qlen.clear(); c->tlen.clear(); c->ulen.clear(); c->extra.clear(); c->missing.clear();
     c->match.clear(); c->outframe.clear(); c->inframe.clear(); c->lpi.clear(); c->ilpi.clear(); c->mlpi.clear();
     int nq = 0;
@@ -976,7 +1009,10 @@ int orfx_oracle_score_pairs(orfx_ctx* ctx, const orfx_batch* b, orfx_results* r)
 // Codon-scan oracle: stop / ATG masks of one spliced transcript, bit p = codon starting at spliced
 // position p (5'->3').  Follows SEQ::translate / find_inframe_codon (common.hpp:420-450, 477-495):
 // upper-cased bases, reverse-complemented for non-'+' strands (Transcriptome.cpp:155-171).
-int64_t orfx_oracle_masks(const orfx_batch* b, int32_t tx, uint32_t* stop_bits, uint32_t* start_bits, int64_t max_words) {
+int64_t orfx_oracle_masks(const orfx_batch* b_in, int32_t tx, uint32_t* stop_bits, uint32_t* start_bits, int64_t max_words) {
+    std::unique_ptr<Expanded> ex;
+    try { ex.reset(new Expanded(b_in)); } catch (const std::exception&) { return ORFX_E_INVALID; }
+    const orfx_batch* b = &ex->b;
     int bi = 0;
     while (bi < b->n_bundles && !(tx >= b->bundle_tx_off[bi] && tx < b->bundle_tx_off[bi + 1])) bi++;
     if (bi >= b->n_bundles) return ORFX_E_INVALID;

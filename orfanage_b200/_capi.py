@@ -78,7 +78,9 @@ class _Batch(C.Structure):
                 ("tx_cds_end", C.c_void_p), ("tx_tid_class", C.c_void_p), ("segs", C.c_void_p), ("seg_phase", C.c_void_p),
                 ("seg_seq_off", C.c_void_p), ("seq_format", C.c_int32), ("reserved0", C.c_int32),
                 ("tx_ext_lo", C.c_void_p), ("tx_ext_hi", C.c_void_p), ("tx_ext_flags", C.c_void_p),
-                ("seq_exc_pos", C.c_void_p), ("seq_exc_code", C.c_void_p), ("n_seq_exc", C.c_int64)]
+                ("seq_exc_pos", C.c_void_p), ("seq_exc_code", C.c_void_p), ("n_seq_exc", C.c_int64),
+                ("seg_ref", C.c_void_p), ("bundle_dict_off", C.c_void_p), ("dict_segs", C.c_void_p), ("dict_phase", C.c_void_p),
+                ("dict_seq_off", C.c_void_p), ("n_dict", C.c_int64)]
 
 
 class _Best(C.Structure):
@@ -118,7 +120,11 @@ _BATCH_ARRAYS = [("seq", np.uint8), ("seq_off", np.int64), ("bundle_start", np.i
                  ("tx_kind", np.uint8), ("tx_strand", np.uint8), ("tx_seg_off", np.int32), ("tx_cds_start", np.int32),
                  ("tx_cds_end", np.int32), ("tx_tid_class", np.int32), ("segs", np.int32), ("seg_phase", np.int8),
                  ("seg_seq_off", np.int32), ("tx_ext_lo", np.int32), ("tx_ext_hi", np.int32), ("tx_ext_flags", np.uint8),
-                 ("seq_exc_pos", np.int64), ("seq_exc_code", np.uint8)]
+                 ("seq_exc_pos", np.int64), ("seq_exc_code", np.uint8),
+                 ("seg_ref", np.uint16), ("bundle_dict_off", np.int32), ("dict_segs", np.int32), ("dict_phase", np.int8),
+                 ("dict_seq_off", np.int32)]
+# with a segment dictionary (seg_ref) the device library takes the chains from it and never reads these
+_DICT_REPLACES = ("segs", "seg_phase", "seg_seq_off")
 
 
 def _view(ptr, n, dtype):
@@ -155,10 +161,13 @@ class Batch:
         s = _Batch()
         s.n_bundles = max(len(a["bundle_tx_off"]) - 1, 0)
         s.n_tx = len(a["tx_kind"])
-        s.n_segs = a["segs"].shape[0]
+        s.n_segs = a["segs"].shape[0] or a["seg_ref"].size
         s.seq_bytes = int(np.asarray(arrays["seq_bases"]).reshape(-1)[0]) if self.seq_format in (1, 2) else a["seq"].size
         s.seq_format = self.seq_format
         s.n_seq_exc = a["seq_exc_pos"].size
+        if a["dict_segs"].ndim == 1:
+            a["dict_segs"] = a["dict_segs"].reshape(-1, 2)
+        s.n_dict = a["dict_segs"].shape[0]
         for name, _ in _BATCH_ARRAYS:
             arr = a[name]
             setattr(s, name, arr.ctypes.data if arr.size else None)
@@ -188,10 +197,14 @@ class Batch:
             tx_ext_lo=_view(s.tx_ext_lo, nt if s.tx_ext_lo else 0, np.int32), tx_ext_hi=_view(s.tx_ext_hi, nt if s.tx_ext_hi else 0, np.int32),
             tx_ext_flags=_view(s.tx_ext_flags, nt if s.tx_ext_flags else 0, np.uint8),
             seq_exc_pos=_view(s.seq_exc_pos, s.n_seq_exc if s.seq_exc_pos else 0, np.int64),
-            seq_exc_code=_view(s.seq_exc_code, s.n_seq_exc if s.seq_exc_code else 0, np.uint8))
+            seq_exc_code=_view(s.seq_exc_code, s.n_seq_exc if s.seq_exc_code else 0, np.uint8),
+            seg_ref=_view(s.seg_ref, ns if s.seg_ref else 0, np.uint16), bundle_dict_off=_view(s.bundle_dict_off, nb + 1 if s.seg_ref else 0, np.int32),
+            dict_segs=_view(s.dict_segs, s.n_dict * 2 if s.seg_ref else 0, np.int32), dict_phase=_view(s.dict_phase, s.n_dict if s.seg_ref else 0, np.int8),
+            dict_seq_off=_view(s.dict_seq_off, s.n_dict if (s.seg_ref and s.dict_seq_off) else 0, np.int32))
         b = cls.__new__(cls)
         b.arrays = arrays
         b.arrays["segs"] = b.arrays["segs"].reshape(-1, 2)
+        b.arrays["dict_segs"] = b.arrays["dict_segs"].reshape(-1, 2)
         b.owner = owner
         b.seq_format = int(s.seq_format)
         cp = _Batch()
@@ -205,7 +218,16 @@ class Batch:
 
     @property
     def h2d_bytes(self):
-        return int(sum(a.nbytes for a in self.arrays.values()))
+        """Bytes orfx_submit copies to the device (Context.last_upload_bytes() is the library's own count)."""
+        skip = _DICT_REPLACES if self.arrays["seg_ref"].size else ()
+        return int(sum(a.nbytes for k, a in self.arrays.items() if k not in skip))
+
+    def without_segment_arrays(self):
+        """The same batch with segs / seg_phase / seg_seq_off dropped: what a caller that only has the dictionary passes."""
+        assert self.arrays["seg_ref"].size, "no segment dictionary in this batch"
+        a = {k: v for k, v in self.arrays.items() if k not in _DICT_REPLACES}
+        extra = dict(seq_format=np.array([self.seq_format], np.int32), seq_bases=np.array([self.struct.seq_bytes], np.int64)) if self.seq_format else {}
+        return Batch(**a, **extra)
 
     def query_nt(self):
         a = self.arrays
@@ -305,6 +327,9 @@ def load_device_library(path=None):
     lib.orfx_kernel_times.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_char_p), C.POINTER(C.c_float), C.POINTER(C.c_int)]
     lib.orfx_last_run_ms.restype = C.c_float
     lib.orfx_last_run_ms.argtypes = [C.c_void_p]
+    if hasattr(lib, "orfx_last_upload_bytes"):
+        lib.orfx_last_upload_bytes.restype = C.c_int64
+        lib.orfx_last_upload_bytes.argtypes = [C.c_void_p]
     lib.orfx_last_run_launches.restype = C.c_int
     lib.orfx_last_run_launches.argtypes = [C.c_void_p]
     lib.orfx_resident_query_nt.restype = C.c_int64
@@ -388,6 +413,9 @@ class Context:
     def debug_set(self, key, value):
         """orfx_debug_set: test hook that lowers an internal capacity (see include/orfx.h)."""
         self._check(self.lib.orfx_debug_set(self.handle, key.encode(), int(value)))
+
+    def last_upload_bytes(self):
+        return int(self.lib.orfx_last_upload_bytes(self.handle))
 
     def submit(self, batch):
         self._keep = batch
@@ -573,7 +601,7 @@ class Workload:
             dev = load_device_library()
             alloc = C.cast(dev.orfx_host_alloc, C.c_void_p)
             dealloc = C.cast(dev.orfx_host_free, C.c_void_p)
-        rc = self.lib.orfxh_pack(self.handle, shard, n_shards, {"windows": 0, "islands": 1, "islands4": 2, "islands_t": 3, "islands2": 4}[layout], alloc, dealloc, C.byref(s))
+        rc = self.lib.orfxh_pack(self.handle, shard, n_shards, {"windows": 0, "islands": 1, "islands4": 2, "islands_t": 3, "islands2": 4, "islands2d": 5}[layout], alloc, dealloc, C.byref(s))
         if rc != 0:
             raise OrfxError(rc, self.lib.orfxh_last_error().decode())
         return Batch.from_struct(s, owner=self)

@@ -87,7 +87,7 @@ int orfxh_pack(orfxh_workload* w, int shard, int n_shards, int layout, void* (*a
         if (w->packed.size() <= (size_t)shard) w->packed.resize((size_t)shard + 1);
         w->packed[(size_t)shard].reset(new PackedBatch());
         pack_bundles(w->tr, shards[(size_t)shard], w->opt.keep_all_cds, w->tid_classes, *w->packed[(size_t)shard], alloc, dealloc, layout != 0, PACK_EVAL, layout == 2,
-                     w->opt.overhang, w->opt.spliced_overhang, layout == 3, layout == 4);
+                     w->opt.overhang, w->opt.spliced_overhang, layout == 3, layout == 4 || layout == 5, layout == 5);
         *out = w->packed[(size_t)shard]->view();
         return ORFX_OK;
     } catch (const std::exception& e) { g_err = e.what(); return ORFX_E_INVALID; }

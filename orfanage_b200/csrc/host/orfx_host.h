@@ -167,6 +167,14 @@ struct PackedBatch {
     int32_t* tx_ext_lo = nullptr;           // --overhang only: usable flank below / above each query's exon chain
     int32_t* tx_ext_hi = nullptr;
     uint8_t* tx_ext_flags = nullptr;        // ORFX_EXT_* (a flank that re-reads the chromosome's edge base)
+    // segment dictionary (orfx_batch::seg_ref): second arena from the same allocator; NULL when not built
+    void* dict_arena = nullptr;
+    uint16_t* seg_ref = nullptr;
+    int32_t* bundle_dict_off = nullptr;
+    orfx_seg* dict_segs = nullptr;
+    int8_t* dict_phase = nullptr;
+    int32_t* dict_seq_off = nullptr;
+    int64_t n_dict = 0;
     std::vector<int64_t> seq_exc_pos;       // ORFX_SEQ_NT2: the bases that are none of A C G T
     std::vector<uint8_t> seq_exc_code;
     int32_t n_tx = 0;
@@ -194,7 +202,11 @@ void pack_bundles(const Transcriptome& tr, const std::vector<int>& bundle_ids, b
                   bool nt4 = false,    // nt4: islands as 4-bit base codes (ORFX_SEQ_NT4), half the upload
                   int overhang = 0, bool spliced_overhang = false,   // --overhang flanks (TX::extend_seq, Transcriptome.cpp:342-399)
                   bool template_seq = false,    // islands also cover the template CDS segments (orfx_params::align_enabled)
-                  bool nt2 = false);            // islands as 2-bit base codes + exception list (ORFX_SEQ_NT2), a quarter of the raw upload
+                  bool nt2 = false,             // islands as 2-bit base codes + exception list (ORFX_SEQ_NT2), a quarter of the raw upload
+                  bool dict = false);           // also build the segment dictionary (orfx_batch::seg_ref): the upload then skips the per-segment arrays
+// Per bundle, the distinct (segment, phase, sequence offset) records of its transcripts and a 16-bit reference per segment.
+// Returns false (and leaves the batch without a dictionary) when a bundle has more than 65536 distinct records.
+bool build_segment_dictionary(PackedBatch& out, void* (*alloc)(size_t));
 void build_tid_classes(const Transcriptome& tr, TidClasses& out);
 // greedy longest-processing-time split of active bundles over n shards
 void shard_bundles(const Transcriptome& tr, const std::vector<int>& active, int n, std::vector<std::vector<int>>& shards);

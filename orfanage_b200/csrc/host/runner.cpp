@@ -29,6 +29,8 @@ char nt_complement(char c) {   // ntComplement (gclib), IUPAC, case preserving
 
 void PackedBatch::reset() {
     if (arena) { if (dealloc) dealloc(arena); else free(arena); }
+    if (dict_arena) { if (dealloc) dealloc(dict_arena); else free(dict_arena); }
+    dict_arena = nullptr; seg_ref = nullptr; bundle_dict_off = nullptr; dict_segs = nullptr; dict_phase = nullptr; dict_seq_off = nullptr; n_dict = 0;
     arena = nullptr; arena_bytes = 0; dealloc = nullptr;
     bundle_ids.clear(); tx_global.clear();
     n_tx = 0; n_segs = 0; seq_bytes = 0; n_queries = 0; seq_format = ORFX_SEQ_RAW;
@@ -63,6 +65,10 @@ orfx_batch PackedBatch::view() const {
     b.seq_exc_pos = seq_exc_pos.empty() ? nullptr : seq_exc_pos.data();
     b.seq_exc_code = seq_exc_code.empty() ? nullptr : seq_exc_code.data();
     b.n_seq_exc = (int64_t)seq_exc_pos.size();
+    if (seg_ref && n_dict > 0) {
+        b.seg_ref = seg_ref; b.bundle_dict_off = bundle_dict_off; b.dict_segs = dict_segs; b.dict_phase = dict_phase;
+        b.dict_seq_off = b.seg_seq_off ? dict_seq_off : nullptr; b.n_dict = n_dict;
+    }
     return b;
 }
 
@@ -191,7 +197,7 @@ QFlank query_flanks(const Fasta& fa, const Fasta::Seq& chrom, const Bundle& b, c
 void pack_bundles(const Transcriptome& tr, const std::vector<int>& bundle_ids, bool keep_all_cds,
                   const TidClasses& tid_classes, PackedBatch& out,
                   void* (*alloc)(size_t), void (*dealloc)(void*), bool islands, int mode, bool nt4, int overhang, bool spliced_overhang, bool template_seq,
-                  bool nt2) {
+                  bool nt2, bool dict) {
     const bool clean_mode = mode == PACK_CLEAN, compare_mode = mode == PACK_COMPARE;
     template_seq = template_seq && mode == PACK_EVAL;
     if (template_seq) nt4 = nt2 = false;   // the translation needs the letters themselves
@@ -413,6 +419,63 @@ void pack_bundles(const Transcriptome& tr, const std::vector<int>& bundle_ids, b
             out.seq_exc_code.insert(out.seq_exc_code.end(), exc_code_part[k].begin(), exc_code_part[k].end());
         }
     }
+    if (dict && out.n_segs > 0) build_segment_dictionary(out, alloc);
+}
+
+bool build_segment_dictionary(PackedBatch& out, void* (*alloc)(size_t)) {
+    struct Rec {
+        int32_t s, e, off; int8_t ph;
+        bool operator<(const Rec& o) const { return s != o.s ? s < o.s : e != o.e ? e < o.e : ph != o.ph ? ph < o.ph : off < o.off; }
+        bool operator==(const Rec& o) const { return s == o.s && e == o.e && ph == o.ph && off == o.off; }
+    };
+    const size_t nb = out.bundle_ids.size();
+    const bool with_off = out.seq_bytes > 0 && out.seg_seq_off;
+    std::vector<uint16_t> ref((size_t)out.n_segs);
+    const unsigned nthr = nb > 2000 ? std::min(8u, std::max(1u, std::thread::hardware_concurrency())) : 1u;
+    std::vector<std::vector<Rec>> part_recs(nthr);
+    std::vector<int32_t> count(nb + 1, 0);
+    std::atomic<bool> overflow{false};
+    auto work = [&](size_t j0, size_t j1, unsigned part) {
+        std::vector<Rec> all, uniq;
+        for (size_t j = j0; j < j1 && !overflow.load(std::memory_order_relaxed); j++) {
+            const int k0 = out.tx_seg_off[out.bundle_tx_off[j]], k1 = out.tx_seg_off[out.bundle_tx_off[j + 1]];
+            all.clear();
+            for (int k = k0; k < k1; k++) all.push_back(Rec{out.segs[k].start, out.segs[k].end, with_off ? out.seg_seq_off[k] : 0, out.seg_phase[k]});
+            uniq = all;
+            std::sort(uniq.begin(), uniq.end());
+            uniq.erase(std::unique(uniq.begin(), uniq.end()), uniq.end());
+            if (uniq.size() > 65536) { overflow = true; return; }
+            for (int k = k0; k < k1; k++) ref[(size_t)k] = (uint16_t)(std::lower_bound(uniq.begin(), uniq.end(), all[(size_t)(k - k0)]) - uniq.begin());
+            count[j] = (int32_t)uniq.size();
+            part_recs[part].insert(part_recs[part].end(), uniq.begin(), uniq.end());
+        }
+    };
+    if (nthr <= 1) work(0, nb, 0);
+    else {
+        std::vector<std::thread> th;
+        for (unsigned k = 0; k < nthr; k++) th.emplace_back(work, nb * k / nthr, nb * (k + 1) / nthr, k);
+        for (auto& t : th) t.join();
+    }
+    if (overflow) return false;
+    int64_t nd = 0;
+    for (size_t j = 0; j < nb; j++) nd += count[j];
+    auto up = [](size_t x) { return (x + 63) & ~(size_t)63; };
+    const size_t o_ref = 0, o_bdo = o_ref + up((size_t)out.n_segs * 2 + 8), o_ds = o_bdo + up((nb + 1) * 4), o_dp = o_ds + up((size_t)nd * 8 + 8),
+                 o_do = o_dp + up((size_t)nd + 8), o_end = o_do + up((size_t)nd * 4 + 8);
+    void* a = alloc ? alloc(o_end) : malloc(o_end);
+    if (!a) throw std::runtime_error("cannot allocate " + std::to_string(o_end) + " bytes for the segment dictionary");
+    char* base = (char*)a;
+    out.dict_arena = a;
+    out.seg_ref = (uint16_t*)(base + o_ref); out.bundle_dict_off = (int32_t*)(base + o_bdo); out.dict_segs = (orfx_seg*)(base + o_ds);
+    out.dict_phase = (int8_t*)(base + o_dp); out.dict_seq_off = (int32_t*)(base + o_do); out.n_dict = nd;
+    memcpy(out.seg_ref, ref.data(), (size_t)out.n_segs * 2);
+    int32_t at = 0;
+    for (size_t j = 0; j < nb; j++) { out.bundle_dict_off[j] = at; at += count[j]; }
+    out.bundle_dict_off[nb] = at;
+    size_t d = 0;
+    for (const auto& recs : part_recs)   // parts hold consecutive bundle ranges
+        for (const Rec& r : recs) { out.dict_segs[d] = orfx_seg{r.s, r.e}; out.dict_phase[d] = r.ph; out.dict_seq_off[d] = r.off; d++; }
+    return true;
 }
 
 void shard_bundles(const Transcriptome& tr, const std::vector<int>& active, int n, std::vector<std::vector<int>>& shards) {
@@ -643,7 +706,7 @@ int run_orfanage(const Options& opt, const Backend& be) {
             // one batch per process: page-locking the arena would cost more than the one upload saves
             if (!shard_ids[(size_t)k].empty())
                 pack_bundles(tr, shard_ids[(size_t)k], opt.keep_all_cds, tid_classes, s.batch, nullptr, nullptr, true, PACK_EVAL, false, opt.overhang, opt.spliced_overhang,
-                             params.align_enabled != 0, true);
+                             params.align_enabled != 0, true, true);
             auto b = clk::now();
             s.ms_pack = ms(a, b);
             ctx_threads[(size_t)k].join();   // this shard's context (the contexts of one process come up one after the other)

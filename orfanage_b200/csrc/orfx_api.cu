@@ -18,6 +18,8 @@ int launch_prep(const DevBatch& B, int64_t* cnt_q, int64_t* cnt_words, int64_t* 
                 cudaStream_t s);
 int launch_fill_tiles(const DevBatch& B, cudaStream_t s);
 int launch_validate(const DevBatch& B, int has_seq, int allow_empty, int* flag, cudaStream_t s);
+int launch_expand_dict(const DevBatch& B, const uint16_t* ref, const int32_t* bundle_dict_off, const orfx_seg* dict_segs, const int8_t* dict_phase,
+                       const int32_t* dict_seq_off, int64_t n_dict, orfx_seg* segs, int8_t* phase, int32_t* sso, int* flag, cudaStream_t s);
 int launch_count_rows(const DevBatch& B, int64_t* cnt, int64_t* scan_tmp, const int32_t* heavy_list, const unsigned* heavy_count, int n_sm, cudaStream_t s,
                       cudaStream_t side, cudaEvent_t ev_fork, cudaEvent_t ev_join);
 int launch_fill_rows(const DevBatch& B, const DevRows& R, int n_queries, cudaStream_t s);
@@ -83,6 +85,8 @@ struct orfx_ctx {
     DBuf d_clean_keep, d_clean_s, d_clean_e, d_keys;
     DBuf d_xlo, d_xhi, d_xfl;   // --overhang flanks
     DBuf d_flag, d_exc_pos, d_exc_code;
+    DBuf d_ref, d_bdo, d_dsegs, d_dphase, d_dsso;   // segment dictionary (orfx_batch::seg_ref)
+    size_t upload_bytes = 0;
     // alignment stage (params.align_enabled)
     AlnWork aln;
     DBuf d_aa_off, d_aa_pos, d_cnt_aa, d_tables, d_row_pairs, r_aln[6];
@@ -118,14 +122,17 @@ int upload_batch(orfx_ctx* c, const orfx_batch* b, bool overlap = false) {
     if (b->n_bundles < 0 || b->n_tx < 0 || b->n_segs < 0) return fail(ORFX_E_INVALID, "negative batch size");
     if (c->P.has_reference && b->seq_bytes > 0 && !b->seq) return fail(ORFX_E_INVALID, "params.has_reference set but batch.seq is NULL");
     if ((b->n_bundles > 0 || b->n_tx > 0) && (!b->bundle_tx_off || !b->tx_seg_off || !b->tx_kind || !b->tx_strand || !b->tx_cds_start || !b->tx_cds_end || !b->tx_tid_class ||
-                                              !b->bundle_start || (b->n_segs > 0 && (!b->segs || !b->seg_phase)) || (c->P.has_reference && b->seq_bytes > 0 && !b->seq_off)))
+                                              !b->bundle_start || (b->n_segs > 0 && !b->seg_ref && (!b->segs || !b->seg_phase)) || (c->P.has_reference && b->seq_bytes > 0 && !b->seq_off)))
         return fail(ORFX_E_INVALID, "null array in a non-empty batch");
     cudaStream_t s = c->stream;
     const size_t nb = (size_t)b->n_bundles, nt = (size_t)b->n_tx, ns = (size_t)b->n_segs;
     const size_t seqb = c->P.has_reference ? (size_t)b->seq_bytes : 0;                    // bases
     if (b->seq_format != ORFX_SEQ_RAW && b->seq_format != ORFX_SEQ_NT4 && b->seq_format != ORFX_SEQ_NT2) return fail(ORFX_E_INVALID, "unknown batch.seq_format");
+    const bool dict = b->seg_ref != nullptr && b->n_segs > 0;
+    if (dict && (!b->bundle_dict_off || b->n_dict <= 0 || !b->dict_segs || !b->dict_phase)) return fail(ORFX_E_INVALID, "batch.seg_ref without a dictionary (bundle_dict_off, dict_segs, dict_phase, n_dict)");
+    const int32_t* const host_sso = dict ? b->dict_seq_off : b->seg_seq_off;   // non-NULL <=> islands layout
     if (b->seq_format == ORFX_SEQ_NT2 && seqb) {
-        if (!b->seg_seq_off) return fail(ORFX_E_INVALID, "ORFX_SEQ_NT2 is defined for the islands layout (seg_seq_off)");
+        if (!host_sso) return fail(ORFX_E_INVALID, "ORFX_SEQ_NT2 is defined for the islands layout (seg_seq_off)");
         if (b->n_seq_exc < 0 || (b->n_seq_exc > 0 && (!b->seq_exc_pos || !b->seq_exc_code))) return fail(ORFX_E_INVALID, "ORFX_SEQ_NT2: bad exception list");
     }
     const size_t seq_store = b->seq_format == ORFX_SEQ_NT4 ? (seqb + 1) / 2 : (b->seq_format == ORFX_SEQ_NT2 ? (seqb + 3) / 4 : seqb);   // bytes behind batch.seq
@@ -141,8 +148,10 @@ int upload_batch(orfx_ctx* c, const orfx_batch* b, bool overlap = false) {
     CU(c->d_tid.ensure(nt * 4 + 4));
     CU(c->d_segs.ensure(ns * 8 + 8));
     CU(c->d_phase.ensure(ns + 4));
+    c->upload_bytes = 0;
     auto cp = [&](DBuf& d, const void* src, size_t bytes) -> cudaError_t {
         if (bytes == 0) return cudaSuccess;
+        c->upload_bytes += bytes;
         return cudaMemcpyAsync(d.p, src, bytes, cudaMemcpyHostToDevice, s);
     };
     if (seqb && !overlap) {
@@ -158,22 +167,30 @@ int upload_batch(orfx_ctx* c, const orfx_batch* b, bool overlap = false) {
     CU(cp(c->d_cds_s, b->tx_cds_start, nt * 4));
     CU(cp(c->d_cds_e, b->tx_cds_end, nt * 4));
     CU(cp(c->d_tid, b->tx_tid_class, nt * 4));
-    CU(cp(c->d_segs, b->segs, ns * 8));
-    CU(cp(c->d_phase, b->seg_phase, ns));
+    const size_t nd = dict ? (size_t)b->n_dict : 0;
+    if (!dict) {
+        CU(cp(c->d_segs, b->segs, ns * 8));
+        CU(cp(c->d_phase, b->seg_phase, ns));
+    } else {   // 2 bytes per segment + the distinct records; expanded on the device below
+        CU(c->d_ref.ensure(ns * 2 + 4)); CU(c->d_bdo.ensure((nb + 1) * 4)); CU(c->d_dsegs.ensure(nd * 8 + 8)); CU(c->d_dphase.ensure(nd + 4));
+        CU(cp(c->d_ref, b->seg_ref, ns * 2)); CU(cp(c->d_bdo, b->bundle_dict_off, (nb + 1) * 4));
+        CU(cp(c->d_dsegs, b->dict_segs, nd * 8)); CU(cp(c->d_dphase, b->dict_phase, nd));
+        if (b->dict_seq_off) { CU(c->d_dsso.ensure(nd * 4 + 4)); CU(cp(c->d_dsso, b->dict_seq_off, nd * 4)); }
+    }
     const size_t nexc = (seqb && b->seq_format == ORFX_SEQ_NT2) ? (size_t)b->n_seq_exc : 0;
     if (nexc) {
         CU(c->d_exc_pos.ensure(nexc * 8)); CU(c->d_exc_code.ensure(nexc + 4));
         CU(cp(c->d_exc_pos, b->seq_exc_pos, nexc * 8)); CU(cp(c->d_exc_code, b->seq_exc_code, nexc));
     }
-    const bool islands = seqb && b->seg_seq_off;
-    if (islands) { CU(c->d_sso.ensure(ns * 4 + 4)); CU(cp(c->d_sso, b->seg_seq_off, ns * 4)); }
+    const bool islands = seqb && host_sso;
+    if (islands) { CU(c->d_sso.ensure(ns * 4 + 4)); if (!dict) CU(cp(c->d_sso, b->seg_seq_off, ns * 4)); }
     const bool flanks = seqb && c->P.overhang > 0;
     if (flanks) {
         if (nt && (!b->tx_ext_lo || !b->tx_ext_hi)) return fail(ORFX_E_INVALID, "params.overhang > 0 needs batch.tx_ext_lo / tx_ext_hi");
         CU(c->d_xlo.ensure(nt * 4 + 4)); CU(c->d_xhi.ensure(nt * 4 + 4));
         CU(cp(c->d_xlo, b->tx_ext_lo, nt * 4)); CU(cp(c->d_xhi, b->tx_ext_hi, nt * 4));
         if (b->tx_ext_flags) { CU(c->d_xfl.ensure(nt + 4)); CU(cp(c->d_xfl, b->tx_ext_flags, nt)); }
-        if (!b->seg_seq_off)   // a strand '.' query takes its 5' flank from the low side: only a private copy of its bases can hold that
+        if (!host_sso)   // a strand '.' query takes its 5' flank from the low side: only a private copy of its bases can hold that
             for (size_t i = 0; i < nt; i++)
                 if (b->tx_kind[i] == ORFX_TX_QUERY && b->tx_strand[i] != '+' && b->tx_strand[i] != '-' && b->tx_ext_hi[i] > 0)
                     return fail(ORFX_E_UNSUPPORTED, "--overhang with strand '.' query transcripts needs the islands layout (seg_seq_off)");
@@ -184,6 +201,7 @@ int upload_batch(orfx_ctx* c, const orfx_batch* b, bool overlap = false) {
     if (align) { CU(c->d_aa_off.ensure((nt + 1) * 8)); CU(c->d_cnt_aa.ensure(nt * 8 + 8)); }
     c->seq_in_flight = false;
     if (seqb && overlap) {
+        c->upload_bytes += seq_store;
         CU(cudaEventRecord(c->ev_chains, s));
         CU(cudaStreamWaitEvent(c->copy_stream, c->ev_chains, 0));   // after the chains, and after whatever still reads d_seq
         CU(cudaMemcpyAsync(c->d_seq.p, b->seq, seq_store, cudaMemcpyHostToDevice, c->copy_stream));
@@ -234,10 +252,20 @@ int upload_batch(orfx_ctx* c, const orfx_batch* b, bool overlap = false) {
     // range) before anything walks it.  One small kernel and one flag read-back; the sequence bytes are already on their way.
     if (nt || nb) {
         CU(c->d_flag.ensure(16));
+        if (dict)
+            launch_expand_dict(B, c->d_ref.as<uint16_t>(), c->d_bdo.as<int32_t>(), c->d_dsegs.as<orfx_seg>(), c->d_dphase.as<int8_t>(),
+                               b->dict_seq_off && islands ? c->d_dsso.as<int32_t>() : nullptr, (int64_t)nd, c->d_segs.as<orfx_seg>(), c->d_phase.as<int8_t>(),
+                               islands ? c->d_sso.as<int32_t>() : nullptr, c->d_flag.as<int>() + 1, s);
+        else CU(cudaMemsetAsync(c->d_flag.as<int>() + 1, 0, sizeof(int), s));
         launch_validate(B, seqb ? 1 : 0, c->allow_empty_chains ? 1 : 0, c->d_flag.as<int>(), s);
         int* hflag = reinterpret_cast<int*>(c->h_totals.as<int64_t>() + 6);
-        CU(cudaMemcpyAsync(hflag, c->d_flag.p, sizeof(int), cudaMemcpyDeviceToHost, s));
+        CU(cudaMemcpyAsync(hflag, c->d_flag.p, 2 * sizeof(int), cudaMemcpyDeviceToHost, s));
         CU(cudaStreamSynchronize(s));
+        if (hflag[1]) {
+            c->resident = false;
+            if (c->seq_in_flight) { cudaStreamSynchronize(c->copy_stream); c->seq_in_flight = false; }
+            return fail(ORFX_E_INVALID, "malformed batch: a seg_ref outside its bundle's dictionary records, or bundle_dict_off not monotone / beyond n_dict");
+        }
         if (*hflag) {
             c->resident = false;
             if (c->seq_in_flight) { cudaStreamSynchronize(c->copy_stream); c->seq_in_flight = false; }
@@ -579,7 +607,8 @@ void orfx_destroy(orfx_ctx* c) {
                  &c->d_segs, &c->d_phase, &c->d_seg_cum, &c->d_tx_len, &c->d_tx_bundle, &c->d_mask_off, &c->d_tile_off, &c->d_q_off, &c->d_q_list,
                  &c->d_row_off, &c->d_tile_tx, &c->d_stop, &c->d_start, &c->d_need, &c->d_planes, &c->d_heavy, &c->d_heavy_count, &c->d_cnt_q, &c->d_cnt_words, &c->d_cnt_tiles, &c->d_cnt_rows, &c->d_scan_tmp,
                  &c->d_ord, &c->r_order, &c->d_best, &c->d_clean_keep, &c->d_clean_s, &c->d_clean_e, &c->d_keys,
-                 &c->d_xlo, &c->d_xhi, &c->d_xfl, &c->d_flag, &c->d_exc_pos, &c->d_exc_code, &c->r_ext[0], &c->r_ext[1]};
+                 &c->d_xlo, &c->d_xhi, &c->d_xfl, &c->d_flag, &c->d_exc_pos, &c->d_exc_code, &c->r_ext[0], &c->r_ext[1],
+                 &c->d_ref, &c->d_bdo, &c->d_dsegs, &c->d_dphase, &c->d_dsso};
     for (DBuf* b : d) b->free_();
     c->aln.free_();
     c->d_aa_off.free_(); c->d_aa_pos.free_(); c->d_cnt_aa.free_(); c->d_tables.free_(); c->d_row_pairs.free_();
@@ -649,6 +678,7 @@ int orfx_kernel_times(orfx_ctx* c, int max_n, const char** names, float* ms, int
 
 float orfx_last_run_ms(orfx_ctx* c) { return c ? c->run_ms : -1.f; }
 int orfx_last_run_launches(orfx_ctx* c) { return c ? c->n_launches : -1; }
+int64_t orfx_last_upload_bytes(orfx_ctx* c) { return c ? (int64_t)c->upload_bytes : -1; }
 
 int64_t orfx_resident_query_nt(orfx_ctx* c) {
     if (!c || !c->resident) return fail(ORFX_E_STATE, "no resident batch");

@@ -187,6 +187,44 @@ __global__ void __launch_bounds__(256) validate_batch_kernel(DevBatch B, int has
     }
     if (bad) atomicOr(flag, bad);
 }
+// Segment dictionary (orfx_batch::seg_ref, include/orfx.h): every segment of a transcript of bundle b is record
+// bundle_dict_off[b] + seg_ref[k] of the dictionary.  Writes the three per-segment arrays the path reads; runs before the
+// validation, which then checks the expanded chains like uploaded ones.  *flag != 0: a reference outside its bundle's
+// records or dictionary offsets that are not monotone (the segment is written as (0, 0)).  Eight lanes per transcript.
+__global__ void __launch_bounds__(256) expand_dict_kernel(DevBatch B, const uint16_t* __restrict__ ref, const int32_t* __restrict__ bundle_dict_off,
+                                                         const orfx_seg* __restrict__ dict_segs, const int8_t* __restrict__ dict_phase,
+                                                         const int32_t* __restrict__ dict_seq_off, int64_t n_dict, orfx_seg* __restrict__ segs,
+                                                         int8_t* __restrict__ phase, int32_t* __restrict__ sso, int* flag) {
+    const int64_t gt = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int64_t tx = gt >> 3;
+    const int sub = (int)(gt & 7);
+    if (tx >= B.n_tx || B.n_bundles <= 0) return;
+    const int s0 = B.tx_seg_off[tx], s1 = B.tx_seg_off[tx + 1];
+    if (s0 < 0 || s1 < s0 || (int64_t)s1 > B.n_segs) return;   // reported by validate_batch_kernel
+    int lo = 0, hi = B.n_bundles - 1;
+    while (lo < hi) { const int mid = (lo + hi + 1) >> 1; if (B.bundle_tx_off[mid] <= (int)tx) lo = mid; else hi = mid - 1; }
+    int64_t d0 = bundle_dict_off[lo], d1 = bundle_dict_off[lo + 1];
+    bool bad = false;
+    if (d0 < 0 || d1 < d0 || d1 > n_dict || d1 - d0 > 65536) { bad = true; d1 = d0 = 0; }
+    for (int k = s0 + sub; k < s1; k += 8) {
+        const int64_t d = d0 + (int64_t)ref[k];
+        orfx_seg sg{0, 0};
+        int ph = 0, so = 0;
+        if (d < d1) { sg = dict_segs[d]; ph = dict_phase[d]; if (dict_seq_off) so = dict_seq_off[d]; }
+        else bad = true;
+        segs[k] = sg; phase[k] = (int8_t)ph;
+        if (sso) sso[k] = so;
+    }
+    if (bad) atomicOr(flag, 1);
+}
+int launch_expand_dict(const DevBatch& B, const uint16_t* ref, const int32_t* bundle_dict_off, const orfx_seg* dict_segs, const int8_t* dict_phase,
+                       const int32_t* dict_seq_off, int64_t n_dict, orfx_seg* segs, int8_t* phase, int32_t* sso, int* flag, cudaStream_t s) {
+    cudaMemsetAsync(flag, 0, sizeof(int), s);
+    if (B.n_tx <= 0) return 0;
+    const int64_t n = (int64_t)B.n_tx * 8;
+    expand_dict_kernel<<<(unsigned)((n + 255) / 256), 256, 0, s>>>(B, ref, bundle_dict_off, dict_segs, dict_phase, dict_seq_off, n_dict, segs, phase, sso, flag);
+    return 1;
+}
 int launch_validate(const DevBatch& B, int has_seq, int allow_empty, int* flag, cudaStream_t s) {
     cudaMemsetAsync(flag, 0, sizeof(int), s);
     const int64_t n = std::max<int64_t>(std::max<int64_t>((int64_t)B.n_tx * 8, B.n_bundles), 1);

@@ -69,6 +69,13 @@ def test_results_match_oracle_bit_for_bit(synth, oracle_lib, gpu, seed, kw):
             assert nt2.seq_format == 2 and nt2.arrays["seq"].size == (nt2.struct.seq_bytes + 3) // 4
             assert_same_results(got, ox.run(nt2), "windows vs islands2 (oracle)")
             assert_same_results(got, gpu.run(nt2), "windows vs islands2 (kernel)")
+            dct = w.pack(1, 2, layout="islands2d")    # + segment dictionary: the chains are expanded on the device
+            assert dct.arrays["seg_ref"].size == dct.arrays["segs"].shape[0]
+            assert_same_results(got, gpu.run(dct), "windows vs islands2d (kernel)")
+            assert gpu.last_upload_bytes() == dct.h2d_bytes < nt2.h2d_bytes
+            bare = dct.without_segment_arrays()
+            assert_same_results(got, gpu.run(bare), "windows vs islands2d, dictionary only (kernel)")
+            assert_same_results(got, ox.run(bare), "windows vs islands2d, dictionary only (oracle)")
     for pk in PARAM_GRID:
         params = ob.Params.make(**pk)
         gpu.set_params(params)
@@ -83,7 +90,7 @@ def test_results_match_oracle_bit_for_bit(synth, oracle_lib, gpu, seed, kw):
     w.close()
 
 
-@pytest.mark.parametrize("layout", ["islands", "islands4", "islands2"])
+@pytest.mark.parametrize("layout", ["islands", "islands4", "islands2", "islands2d"])
 def test_codon_scan_masks_match_oracle(synth, oracle_lib, gpu, layout):
     """Per-stage check (SURVEY.md §4 iii): stop / ATG masks of every query transcript, soft-masked and
     IUPAC bases included, both strands, against SEQ::translate semantics restated in the oracle."""
@@ -126,7 +133,7 @@ def test_overhang_matches_oracle(synth, oracle_lib, gpu, seed, overhang, spliced
     d = synth(seed, **kw)
     w = ob.Workload(os.path.join(d, "query.gtf"), template_files(d), os.path.join(d, "genome.fa"), overhang=overhang, spliced_overhang=spliced)
     grown = 0
-    for layout in ("islands4", "islands2", "windows"):
+    for layout in ("islands4", "islands2", "islands2d", "windows"):
         batch = w.pack(layout=layout)
         a = batch.arrays
         assert a["tx_ext_lo"].size == a["tx_kind"].size and a["tx_ext_lo"].max() <= overhang and a["tx_ext_hi"].max() > 0
@@ -262,6 +269,15 @@ def test_malformed_batches_are_refused(gpu):
     for patch in bad:
         with pytest.raises(ob.OrfxError) as e:
             gpu.run(ob.Batch(**dict(good, **patch)))
+        assert e.value.code == -1, patch
+    # a segment dictionary whose references or offsets do not fit
+    dct = dict(good, seg_ref=[0, 0, 1], bundle_dict_off=[0, 3], dict_segs=[[101, 120], [140, 180], [150, 170]], dict_phase=[0, 0, 0])
+    dct["seg_ref"] = [2, 0, 1]
+    only = {k: v for k, v in dct.items() if k not in ("segs", "seg_phase")}
+    assert gpu.run(ob.Batch(**only)).n_queries == 1
+    for patch in (dict(seg_ref=[2, 0, 3]), dict(bundle_dict_off=[0, 4]), dict(bundle_dict_off=[2, 1]), dict(seg_ref=[2, 1, 0])):
+        with pytest.raises(ob.OrfxError) as e:
+            gpu.run(ob.Batch(**dict(only, **patch)))
         assert e.value.code == -1, patch
     assert gpu.run(ob.Batch(**good)).n_queries == 1         # the context is still usable
 

@@ -25,7 +25,7 @@ def test_device_library_exports_every_declared_symbol():
     for n in names:
         assert hasattr(lib, n), "liborfx.so does not export %s" % n
     ob.load_device_library()
-    assert lib.orfx_abi_version() == 6
+    assert lib.orfx_abi_version() == 7
 
 
 def test_host_library_exports_every_declared_symbol():
@@ -174,6 +174,51 @@ def test_nt2_islands_decode_to_the_raw_islands(synth, oracle_lib):
     b2.save(path)
     again = ob.Batch.load(path)
     assert again.seq_format == 2 and again.struct.seq_bytes == b2.struct.seq_bytes and again.struct.n_seq_exc == b2.struct.n_seq_exc
+    w.close()
+
+
+def test_segment_dictionary_expands_to_the_segment_arrays(synth, oracle_lib):
+    """orfx_batch::seg_ref (include/orfx.h): per bundle the distinct (segment, phase, sequence offset) records and a 16-bit
+    reference per segment.  Expanded with numpy it gives back segs / seg_phase / seg_seq_off; the oracle, which takes the
+    chains from the dictionary alone, answers the same with and without the per-segment arrays; strand '.' loci with their
+    private island copies (--overhang) and chromosome-edge loci included."""
+    d = synth(8, loci=60, lower=0.3, iupac=0.002, titin=0.1, dot=0.2, edge=True)
+    w = ob.Workload(os.path.join(d, "query.gtf"), template_files(d), os.path.join(d, "genome.fa"), overhang=45)
+    plain = w.pack(1, 2, layout="islands2")
+    ap = {k: v.copy() for k, v in plain.arrays.items()}
+    params = ob.Params.make(mode="ALL", overhang=45)
+    with ob.Context(params, lib=oracle_lib, prefix="orfx_oracle_") as ox:
+        want = ox.run(plain)
+    b = w.pack(1, 2, layout="islands2d")
+    a = b.arrays
+    assert a["seg_ref"].size == a["segs"].shape[0] > 1000 and a["dict_segs"].shape[0] == a["dict_phase"].size == a["dict_seq_off"].size
+    assert a["dict_segs"].shape[0] < a["segs"].shape[0] / 2, "loci share exons: the dictionary is much smaller than the chains"
+    for k in ("segs", "seg_phase", "seg_seq_off", "tx_seg_off", "bundle_tx_off", "seq", "tx_ext_lo", "tx_ext_hi"):
+        assert (a[k] == ap[k]).all(), k
+    seg_tx = np.repeat(np.arange(len(a["tx_kind"])), np.diff(a["tx_seg_off"]))
+    seg_bundle = np.repeat(np.arange(len(a["bundle_tx_off"]) - 1), np.diff(a["bundle_tx_off"]))[seg_tx]
+    n_rec = np.diff(a["bundle_dict_off"])
+    assert (n_rec > 0).all() and n_rec.max() <= 65536 and a["bundle_dict_off"][-1] == a["dict_segs"].shape[0]
+    assert (a["seg_ref"] < n_rec[seg_bundle]).all()
+    at = a["bundle_dict_off"][seg_bundle] + a["seg_ref"].astype(np.int64)
+    assert (a["dict_segs"][at] == a["segs"]).all() and (a["dict_phase"][at] == a["seg_phase"]).all() and (a["dict_seq_off"][at] == a["seg_seq_off"]).all()
+    # records of a bundle are distinct
+    rec = np.stack([np.repeat(np.arange(len(n_rec)), n_rec), a["dict_segs"][:, 0], a["dict_segs"][:, 1], a["dict_phase"], a["dict_seq_off"]], 1)
+    assert len(np.unique(rec, axis=0)) == len(rec)
+    assert b.h2d_bytes < plain.h2d_bytes * 0.9
+    bare = b.without_segment_arrays()
+    assert bare.arrays["segs"].size == 0 and bare.struct.n_segs == b.struct.n_segs and not bare.struct.segs
+    with ob.Context(params, lib=oracle_lib, prefix="orfx_oracle_") as ox:
+        for what, batch in (("with the arrays", b), ("dictionary only", bare)):
+            got = ox.run(batch)
+            assert got.best.tobytes() == want.best.tobytes(), what
+            for k in want.rows:
+                assert got.rows[k].tobytes() == want.rows[k].tobytes(), (what, k)
+        # a reference outside its bundle's records is refused
+        broken = {k: v.copy() for k, v in bare.arrays.items()}
+        broken["seg_ref"][5] = 65535
+        with pytest.raises(ob.OrfxError):
+            ox.run(ob.Batch(**broken, seq_format=np.array([2], np.int32), seq_bases=np.array([b.struct.seq_bytes], np.int64)))
     w.close()
 
 
