@@ -18,6 +18,7 @@ int launch_prep(const DevBatch& B, int64_t* cnt_q, int64_t* cnt_words, int64_t* 
                 cudaStream_t s);
 int launch_fill_tiles(const DevBatch& B, cudaStream_t s);
 int launch_validate(const DevBatch& B, int has_seq, int allow_empty, int* flag, cudaStream_t s);
+int launch_tx_bundle(const DevBatch& B, cudaStream_t s);
 int launch_expand_dict(const DevBatch& B, const uint16_t* ref, const int32_t* bundle_dict_off, const orfx_seg* dict_segs, const int8_t* dict_phase,
                        const int32_t* dict_seq_off, int64_t n_dict, orfx_seg* segs, int8_t* phase, int32_t* sso, int* flag, cudaStream_t s);
 int launch_count_rows(const DevBatch& B, int64_t* cnt, int64_t* scan_tmp, const int32_t* heavy_list, const unsigned* heavy_count, int n_sm, cudaStream_t s,
@@ -252,6 +253,7 @@ int upload_batch(orfx_ctx* c, const orfx_batch* b, bool overlap = false) {
     // range) before anything walks it.  One small kernel and one flag read-back; the sequence bytes are already on their way.
     if (nt || nb) {
         CU(c->d_flag.ensure(16));
+        launch_tx_bundle(B, s);
         if (dict)
             launch_expand_dict(B, c->d_ref.as<uint16_t>(), c->d_bdo.as<int32_t>(), c->d_dsegs.as<orfx_seg>(), c->d_dphase.as<int8_t>(),
                                b->dict_seq_off && islands ? c->d_dsso.as<int32_t>() : nullptr, (int64_t)nd, c->d_segs.as<orfx_seg>(), c->d_phase.as<int8_t>(),

@@ -167,10 +167,9 @@ __global__ void __launch_bounds__(256) validate_batch_kernel(DevBatch B, int has
             if (kind != ORFX_TX_SKIP && s1 == s0 && !allow_empty) bad |= 4;
             int xlo = 0, xhi = 0;
             if (B.tx_ext_lo && kind == ORFX_TX_QUERY) { xlo = B.tx_ext_lo[i]; xhi = B.tx_ext_hi[i]; if (xlo < 0 || xhi < 0) { bad |= 16; xlo = xhi = 0; } }
-            // the transcript's bundle: last b with bundle_tx_off[b] <= i (a broken array is reported by its own threads)
-            int lo = 0, hi = max(B.n_bundles - 1, 0);
-            while (lo < hi) { const int mid = (lo + hi + 1) >> 1; if (B.bundle_tx_off[mid] <= (int)i) lo = mid; else hi = mid - 1; }
+            // the transcript's bundle (a broken bundle_tx_off is reported by its own threads); only the bases of a query are looked up
             const bool check_seq = has_seq && kind == ORFX_TX_QUERY && B.n_bundles > 0;
+            const int lo = check_seq ? B.tx_bundle[i] : 0;   // tx_bundle_kernel: a valid index whatever the batch holds
             const int64_t nbases = check_seq ? B.seq_off[lo + 1] - B.seq_off[lo] : 0;
             const int bstart = check_seq && !B.seg_seq_off ? B.bundle_start[lo] : 0;
             for (int k = s0 + sub; k < s1; k += 8) {
@@ -190,7 +189,11 @@ __global__ void __launch_bounds__(256) validate_batch_kernel(DevBatch B, int has
 // Segment dictionary (orfx_batch::seg_ref, include/orfx.h): every segment of a transcript of bundle b is record
 // bundle_dict_off[b] + seg_ref[k] of the dictionary.  Writes the three per-segment arrays the path reads; runs before the
 // validation, which then checks the expanded chains like uploaded ones.  *flag != 0: a reference outside its bundle's
-// records or dictionary offsets that are not monotone (the segment is written as (0, 0)).  Eight lanes per transcript.
+// records or dictionary offsets that are not monotone (the segment is written as (0, 0)).
+// Eight lanes per transcript; the transcript's bundle comes from tx_bundle (tx_bundle_kernel below, launched first).  Offsets
+// are only trusted as far as staying inside the arrays: the validation that follows reports what is wrong with them.
+// (Measured: one warp per bundle, lanes striding over the bundle's contiguous segments, has the titin-class loci as its
+// tail -- 80 us; a bundle search per lane group 73 us.)
 __global__ void __launch_bounds__(256) expand_dict_kernel(DevBatch B, const uint16_t* __restrict__ ref, const int32_t* __restrict__ bundle_dict_off,
                                                          const orfx_seg* __restrict__ dict_segs, const int8_t* __restrict__ dict_phase,
                                                          const int32_t* __restrict__ dict_seq_off, int64_t n_dict, orfx_seg* __restrict__ segs,
@@ -198,12 +201,11 @@ __global__ void __launch_bounds__(256) expand_dict_kernel(DevBatch B, const uint
     const int64_t gt = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     const int64_t tx = gt >> 3;
     const int sub = (int)(gt & 7);
-    if (tx >= B.n_tx || B.n_bundles <= 0) return;
+    if (tx >= B.n_tx) return;
     const int s0 = B.tx_seg_off[tx], s1 = B.tx_seg_off[tx + 1];
     if (s0 < 0 || s1 < s0 || (int64_t)s1 > B.n_segs) return;   // reported by validate_batch_kernel
-    int lo = 0, hi = B.n_bundles - 1;
-    while (lo < hi) { const int mid = (lo + hi + 1) >> 1; if (B.bundle_tx_off[mid] <= (int)tx) lo = mid; else hi = mid - 1; }
-    int64_t d0 = bundle_dict_off[lo], d1 = bundle_dict_off[lo + 1];
+    const int b = B.tx_bundle[tx];                              // in [0, n_bundles) whatever the batch holds
+    int64_t d0 = bundle_dict_off[b], d1 = bundle_dict_off[b + 1];
     bool bad = false;
     if (d0 < 0 || d1 < d0 || d1 > n_dict || d1 - d0 > 65536) { bad = true; d1 = d0 = 0; }
     for (int k = s0 + sub; k < s1; k += 8) {
@@ -217,10 +219,25 @@ __global__ void __launch_bounds__(256) expand_dict_kernel(DevBatch B, const uint
     }
     if (bad) atomicOr(flag, 1);
 }
+// tx_bundle[x] = the bundle whose [bundle_tx_off[b], bundle_tx_off[b+1]) holds x, for the upload-time kernels (expansion,
+// validation).  Written over a zeroed array and clamped to it, so every entry is a valid bundle index even when the offsets
+// are garbage (which the validation then reports); exact when they are a partition of the transcripts.
+__global__ void tx_bundle_kernel(DevBatch B) {
+    const int b = blockIdx.x * blockDim.x + threadIdx.x;
+    if (b >= B.n_bundles) return;
+    const int x0 = max(B.bundle_tx_off[b], 0), x1 = min(B.bundle_tx_off[b + 1], B.n_tx);
+    for (int x = x0; x < x1; x++) B.tx_bundle[x] = b;
+}
+int launch_tx_bundle(const DevBatch& B, cudaStream_t s) {
+    if (B.n_tx <= 0 || B.n_bundles <= 0) return 0;
+    cudaMemsetAsync(B.tx_bundle, 0, (size_t)B.n_tx * 4, s);
+    tx_bundle_kernel<<<(B.n_bundles + 127) / 128, 128, 0, s>>>(B);
+    return 1;
+}
 int launch_expand_dict(const DevBatch& B, const uint16_t* ref, const int32_t* bundle_dict_off, const orfx_seg* dict_segs, const int8_t* dict_phase,
                        const int32_t* dict_seq_off, int64_t n_dict, orfx_seg* segs, int8_t* phase, int32_t* sso, int* flag, cudaStream_t s) {
     cudaMemsetAsync(flag, 0, sizeof(int), s);
-    if (B.n_tx <= 0) return 0;
+    if (B.n_tx <= 0 || B.n_bundles <= 0 || B.n_segs <= 0) return 0;
     const int64_t n = (int64_t)B.n_tx * 8;
     expand_dict_kernel<<<(unsigned)((n + 255) / 256), 256, 0, s>>>(B, ref, bundle_dict_off, dict_segs, dict_phase, dict_seq_off, n_dict, segs, phase, sso, flag);
     return 1;
