@@ -116,6 +116,7 @@ public:
     const Fasta* fasta = nullptr;
 
     void add(const std::string& gtf_path, bool is_templ, bool coding_only);   // Transcriptome::add, cpp:866-894
+    void add_records(const std::vector<GtfRecord>& recs, bool is_templ, bool coding_only);   // the same from parsed records
     void build_cds_chains();          // cpp:1033-1044
     void correct_chain_len();         // cpp:1045-1051
     void sort(bool use_id);           // Transcriptome.h:904-924

@@ -7,6 +7,7 @@
 #include <chrono>
 #include <cstring>
 #include <functional>
+#include <future>
 #include <thread>
 #include <unordered_map>
 
@@ -613,6 +614,15 @@ void prepare_transcriptome(const Options& opt, Fasta& fasta, Transcriptome& tr, 
             timing += b; last = now;
         }
     };
+    // The query GTF is parsed on the side while the templates are loaded, sorted, cleaned and deduplicated (the two files meet
+    // in bundleup); its records join the transcriptome where the reference loads them, and a parse error of the query surfaces
+    // there too -- after any error of the template stages, as in the reference.
+    struct QueryRecs { std::vector<GtfRecord> recs; std::exception_ptr err; };
+    std::future<QueryRecs> query_parse = std::async(std::launch::async, [&opt]() {
+        QueryRecs q;
+        try { read_gtf(opt.query, q.recs); } catch (...) { q.err = std::current_exception(); }
+        return q;
+    });
     say("loading reference genome");
     if (!opt.reference.empty()) {
         fasta.load(opt.reference);
@@ -633,7 +643,11 @@ void prepare_transcriptome(const Options& opt, Fasta& fasta, Transcriptome& tr, 
     say("start removing duplicates");
     tr.deduplicate(opt.use_id);
     say("loading query transcriptome");
-    tr.add(opt.query, false, false);
+    {
+        QueryRecs q = query_parse.get();
+        if (q.err) std::rethrow_exception(q.err);
+        tr.add_records(q.recs, false, false);
+    }
     say("bundling transcriptome");
     tr.bundleup(opt.use_id, (uint32_t)opt.overhang);
     if (opt.timing) {

@@ -397,9 +397,12 @@ void read_gtf(const std::string& path, std::vector<GtfRecord>& out) {
 
 // ---- Transcriptome -----------------------------------------------------------------------------
 void Transcriptome::add(const std::string& gtf_path, bool is_templ, bool coding_only) {
-    bundles.clear();
     std::vector<GtfRecord> recs;
     read_gtf(gtf_path, recs);
+    add_records(recs, is_templ, coding_only);
+}
+void Transcriptome::add_records(const std::vector<GtfRecord>& recs, bool is_templ, bool coding_only) {
+    bundles.clear();
     for (const GtfRecord& r : recs) {   // Transcriptome::load_seqids, cpp:855-865
         auto ins = seqids_.insert(std::make_pair(r.seqname, (int)seqnames.size()));
         if (ins.second) seqnames.push_back(r.seqname);
