@@ -122,14 +122,19 @@ def evaluated_queries(gtf_path):
 
 
 def source_digest():
-    """SHA-256 over the CUDA sources and the public headers: ties a profile (profiles/r02_traffic.json) to the build."""
+    """SHA-256 over the device code -- every .cu file that defines a kernel, the .cuh headers and the public headers: ties a
+    profile (profiles/r02_traffic.json) to the kernels it measured.  orfx_api.cu (host code only: copies, launches, waits) is
+    left out, so a host-side change does not orphan a kernel profile."""
     import hashlib
     h = hashlib.sha256()
     files = []
     for d in ("orfanage_b200/csrc", "include"):
         for f in sorted(os.listdir(os.path.join(ROOT, d))):
             if f.endswith((".cu", ".cuh", ".h")):
-                files.append(os.path.join(ROOT, d, f))
+                path = os.path.join(ROOT, d, f)
+                if f.endswith(".cu") and b"__global__" not in open(path, "rb").read():
+                    continue
+                files.append(path)
     for f in files:
         h.update(open(f, "rb").read())
     return h.hexdigest()[:16]
@@ -439,6 +444,10 @@ def ours(args):
     if not args.no_pipelined:
         n_ring = max(2, args.stream_contexts)
         ring = [cx] + [ob.Context(params, device=local) for _ in range(n_ring - 1)]
+        # more waiting threads on the box than cores: let them sleep instead of spin (include/orfx.h: blocking_sync)
+        blocking = args.blocking_sync == 1 or (args.blocking_sync < 0 and world * n_ring > (os.cpu_count() or 1))
+        for c_ in ring:
+            c_.debug_set("blocking_sync", 1 if blocking else 0)
         for c_ in ring:
             c_.submit(batch)
         for c_ in ring:
@@ -466,6 +475,7 @@ def ours(args):
         barrier()
         e2e3_ms = (time.perf_counter() - t0) * 1e3
         assert not errs, errs
+        cx.debug_set("blocking_sync", 0)
         for c_ in ring[1:]:
             c_.close()
 
@@ -544,7 +554,7 @@ def ours(args):
         t = time.time()
         align = alignment_leg(cx, args.align_pairs)
         log("alignment leg: %.1f s, %.1f GCUPS" % (time.time() - t, align["gcups"]))
-    return dict(numa=numa, align_path=align_path, stream_contexts=max(2, args.stream_contexts), e2e3_ms=e2e3_ms, stage_ms_alone=stage_ms_alone, alone_ms=alone_ms, c4=c4, digest=digest, nt_all=nt_all, e2e2_ms=e2e2_ms, per_rank=per_rank, align=align, rank=rank, world=world, cfg=cfg, nq=nq, nq_all=nq_all, nt_sum=nt_sum, dev_ms=dev_ms, wall_ms=wall_ms, e2e_ms=e2e_ms,
+    return dict(numa=numa, align_path=align_path, stream_contexts=max(2, args.stream_contexts), stream_blocking=bool(args.blocking_sync == 1 or (args.blocking_sync < 0 and world * max(2, args.stream_contexts) > (os.cpu_count() or 1))), e2e3_ms=e2e3_ms, stage_ms_alone=stage_ms_alone, alone_ms=alone_ms, c4=c4, digest=digest, nt_all=nt_all, e2e2_ms=e2e2_ms, per_rank=per_rank, align=align, rank=rank, world=world, cfg=cfg, nq=nq, nq_all=nq_all, nt_sum=nt_sum, dev_ms=dev_ms, wall_ms=wall_ms, e2e_ms=e2e_ms,
                 e2e_dev=e2e_dev, stage_ms=stage_ms, launches=launches_all, found=found_all, clocks=clocks, h2d=h2d_bytes,
                 d2h=d2h_bytes, windows=seq_bytes, n_templates=w.count("templates"),
                 n_bundles=w.count("active_bundles"))
@@ -715,6 +725,8 @@ def main():
     ap.add_argument("--verbose-shard", action="store_true", help="log the largest loci of this rank's shard")
     ap.add_argument("--seed-offset", type=int, default=0, help="generate the shard rank k of a multi-GPU run would get (k = offset)")
     ap.add_argument("--no-pipelined", action="store_true", help="skip the multi-context end-to-end leg")
+    ap.add_argument("--blocking-sync", type=int, default=-1, help="streamed leg: 1 = waiting threads sleep (blocking_sync), 0 = spin, "
+                    "-1 = sleep when ranks x contexts exceed the host's cores")
     ap.add_argument("--stream-contexts", type=int, default=3, help="contexts (one caller thread each) of the streamed end-to-end leg")
     ap.add_argument("--e2e-contexts", type=int, default=2, help="contexts (locus shards) of the pipelined end-to-end leg")
     ap.add_argument("--align-pairs", type=int, default=-1, help="protein pairs of the alignment leg per GPU (0 = skip; default: BASELINE.json configs[4]'s "
@@ -762,7 +774,7 @@ def main():
             e2e_value, e2e_step_ms = v3, m["e2e3_ms"] / K
             e2e_api = ("orfx_submit + orfx_wait on pinned host batches (include/orfx.h) as a stream of batches over %d contexts, one caller thread each: batch k + 1 is "
                        "uploaded while batch k is evaluated; every batch is uploaded and its results read back inside the timed region") % m.get("stream_contexts", 2)
-        e2e_single["streamed"] = {"contexts": m.get("stream_contexts", 2), "value": v3, "ms_per_step": m["e2e3_ms"] / K}
+        e2e_single["streamed"] = {"contexts": m.get("stream_contexts", 2), "host_wait": "sleep (blocking_sync)" if m.get("stream_blocking") else "spin", "value": v3, "ms_per_step": m["e2e3_ms"] / K}
     peak, peak_src = measured_peak()
     c4 = m["c4"]
     nt_per_launch = m["nt_sum"]          # spliced query nucleotides one rank's codon_scan launch covers

@@ -303,6 +303,9 @@ int64_t orfx_get_masks(orfx_ctx* ctx, int32_t tx, uint32_t* stop_bits, uint32_t*
 /* Test hook: lowers an internal capacity so that small inputs reach the code paths of very large ones.
  * "hb_max_segs" / "hb_max_pairs": segments of a titin-class bundle / (query, transcript) pairs of a bundle slice that
  * the heavy-bundle kernels keep in shared memory (defaults 9216 / 8192); bundles above take their global-memory branches.
+ * "serialize": every kernel on one stream (clean per-kernel times).  "blocking_sync": while the host waits for the stream
+ * (twice inside orfx_submit, once in orfx_wait) the thread sleeps on a cudaEventBlockingSync event instead of spinning in
+ * cudaStreamSynchronize -- for processes in which more threads wait for GPUs than the host has cores.
  * Takes effect at the next orfx_submit / orfx_upload.  Results never depend on these values. */
 int  orfx_debug_set(orfx_ctx* ctx, const char* key, int64_t value);
 

@@ -87,6 +87,8 @@ struct orfx_ctx {
     DBuf d_xlo, d_xhi, d_xfl;   // --overhang flanks
     DBuf d_flag, d_exc_pos, d_exc_code;
     DBuf d_ref, d_bdo, d_dsegs, d_dphase, d_dsso;   // segment dictionary (orfx_batch::seg_ref)
+    bool blocking_sync = false;                      // orfx_debug_set("blocking_sync"): sleep, not spin, while waiting for the stream
+    cudaEvent_t ev_block = nullptr;
     size_t upload_bytes = 0;
     // alignment stage (params.align_enabled)
     AlnWork aln;
@@ -114,6 +116,17 @@ struct orfx_ctx {
 };
 
 namespace {
+
+// Waiting for the stream from the host.  Default: cudaStreamSynchronize (the driver spins, lowest latency).  With
+// blocking_sync the thread sleeps on an event created with cudaEventBlockingSync: what a process wants when more threads wait
+// for GPUs than the host has cores (eight ranks with three contexts each on a 16-core box), where spinning waiters keep the
+// threads that have work to enqueue off the cores.
+cudaError_t sync_stream(orfx_ctx* c, cudaStream_t s) {
+    if (!c->blocking_sync || !c->ev_block) return cudaStreamSynchronize(s);
+    cudaError_t e = cudaEventRecord(c->ev_block, s);
+    if (e != cudaSuccess) return e;
+    return cudaEventSynchronize(c->ev_block);
+}
 
 // overlap = true (orfx_submit): the chain arrays go first on the launch stream, the sequence bytes (two thirds
 // of the upload) follow on the copy stream; prep / candidate-row kernels only need the chains and start while
@@ -262,7 +275,7 @@ int upload_batch(orfx_ctx* c, const orfx_batch* b, bool overlap = false) {
         launch_validate(B, seqb ? 1 : 0, c->allow_empty_chains ? 1 : 0, c->d_flag.as<int>(), s);
         int* hflag = reinterpret_cast<int*>(c->h_totals.as<int64_t>() + 6);
         CU(cudaMemcpyAsync(hflag, c->d_flag.p, 2 * sizeof(int), cudaMemcpyDeviceToHost, s));
-        CU(cudaStreamSynchronize(s));
+        CU(sync_stream(c, s));
         if (hflag[1]) {
             c->resident = false;
             if (c->seq_in_flight) { cudaStreamSynchronize(c->copy_stream); c->seq_in_flight = false; }
@@ -319,7 +332,7 @@ int run_path(orfx_ctx* c) {
     CU(cudaMemcpyAsync(tot + 1, B.tx_mask_off + B.n_tx, 8, cudaMemcpyDeviceToHost, s));
     CU(cudaMemcpyAsync(tot + 2, B.tx_tile_off + B.n_tx, 8, cudaMemcpyDeviceToHost, s));
     CU(cudaMemcpyAsync(tot + 3, B.q_row_off + B.n_tx, 8, cudaMemcpyDeviceToHost, s));
-    CU(cudaStreamSynchronize(s));
+    CU(sync_stream(c, s));
     const int64_t nq = tot[0], words = tot[1], tiles = tot[2], nrows = tot[3];
     c->n_queries = nq; c->n_words = words; c->n_tiles = tiles; c->n_rows = nrows;
     if (c->P.has_reference) {
@@ -529,6 +542,7 @@ int orfx_create(orfx_ctx** out, int device, const orfx_params* params) {
         cudaStreamCreateWithFlags(&c->copy_stream, cudaStreamNonBlocking) != cudaSuccess ||
         cudaStreamCreateWithFlags(&c->side_stream, cudaStreamNonBlocking) != cudaSuccess) { delete c; return fail(ORFX_E_CUDA, "cudaStreamCreate failed"); }
     cudaEventCreateWithFlags(&c->ev_chains, cudaEventDisableTiming);
+    cudaEventCreateWithFlags(&c->ev_block, cudaEventDisableTiming | cudaEventBlockingSync);
     cudaEventCreate(&c->ev_seq);
     for (int i = 0; i < 3; i++) { cudaEventCreateWithFlags(&c->ev_fork[i], cudaEventDisableTiming); cudaEventCreateWithFlags(&c->ev_join[i], cudaEventDisableTiming); }
     for (auto& ev : c->ev) cudaEventCreate(&ev);
@@ -581,7 +595,7 @@ int orfx_wait(orfx_ctx* c, orfx_results* out) {
     if (!c || !out) return fail(ORFX_E_INVALID, "null argument");
     if (!c->pending) return fail(ORFX_E_STATE, "orfx_wait without a pending orfx_submit");
     CU(cudaSetDevice(c->device));
-    CU(cudaStreamSynchronize(c->stream));
+    CU(sync_stream(c, c->stream));
     CU(cudaGetLastError());
     c->pending = false;
     c->have_results = true;
@@ -628,7 +642,7 @@ void orfx_destroy(orfx_ctx* c) {
     for (int i = 0; i < ST_N; i++) { cudaEventDestroy(c->st_ev[i][0]); cudaEventDestroy(c->st_ev[i][1]); }
     cudaEventDestroy(c->run_ev[0]); cudaEventDestroy(c->run_ev[1]);
     cudaStreamSynchronize(c->copy_stream);
-    cudaEventDestroy(c->ev_chains); cudaEventDestroy(c->ev_seq);
+    cudaEventDestroy(c->ev_chains); cudaEventDestroy(c->ev_seq); if (c->ev_block) cudaEventDestroy(c->ev_block);
     cudaStreamDestroy(c->copy_stream);
     cudaStreamSynchronize(c->side_stream);
     for (int i = 0; i < 3; i++) { cudaEventDestroy(c->ev_fork[i]); cudaEventDestroy(c->ev_join[i]); }
@@ -727,6 +741,7 @@ int orfx_debug_set(orfx_ctx* c, const char* key, int64_t value) {
     if (k == "hb_max_segs") { if (value < 0 || value > HB_MAX_SEGS) return fail(ORFX_E_INVALID, "hb_max_segs out of range"); c->hb_max_segs = (int)value; }
     else if (k == "hb_max_pairs") { if (value < 0 || value > HB_MAX_PAIRS) return fail(ORFX_E_INVALID, "hb_max_pairs out of range"); c->hb_max_pairs = (int)value; }
     else if (k == "serialize") c->serialize = value != 0;
+    else if (k == "blocking_sync") c->blocking_sync = value != 0;
     else return fail(ORFX_E_INVALID, "unknown debug key " + k);
     return ORFX_OK;
 }
