@@ -298,7 +298,16 @@ struct Seq {
 struct Bn {   // what a TX needs from its Bundle (Transcriptome.cpp:770-782)
     const uint8_t* seq = nullptr;
     int bstart = 0;
-    std::string nts(int s, int e) const { return std::string((const char*)seq + (s - bstart), (size_t)((e + 1) - s)); }
+    int64_t len = 0;   // bases behind `seq`
+    // Positions outside the stored bases read as 'N'.  The reference has real genome there (its bundle string spans the whole
+    // window) but can only reach them as 5' UTR of an exon that `extend_len - starts[0]` grew past the flank (cpp:461-474):
+    // bases upstream of the start codon it has just chosen, which nothing reads again.
+    std::string nts(int s, int e) const {
+        std::string r((size_t)std::max(e + 1 - s, 0), 'N');
+        const int64_t a = std::max<int64_t>((int64_t)s - bstart, 0), z = std::min<int64_t>((int64_t)e - bstart, len - 1);
+        if (z >= a) memcpy(&r[(size_t)(a - ((int64_t)s - bstart))], seq + a, (size_t)(z - a + 1));
+        return r;
+    }
 };
 
 struct T {
@@ -646,7 +655,7 @@ struct BundleSeq {
         bn.bstart = b->bundle_start[bi];
         if (!b->seq) { bn.seq = nullptr; return; }
         if (b->seq_format != ORFX_SEQ_RAW && !b->seg_seq_off) throw std::runtime_error("ORFX_SEQ_NT4 / ORFX_SEQ_NT2 are defined for the islands layout only");
-        if (!b->seg_seq_off) { bn.seq = b->seq + b->seq_off[bi]; return; }
+        if (!b->seg_seq_off) { bn.seq = b->seq + b->seq_off[bi]; bn.len = b->seq_off[bi + 1] - b->seq_off[bi]; return; }
         int hi = bn.bstart;
         for (int x = b->bundle_tx_off[bi]; x < b->bundle_tx_off[bi + 1]; x++)
             if (b->tx_seg_off[x + 1] > b->tx_seg_off[x]) {
@@ -694,6 +703,7 @@ struct BundleSeq {
             }
         }
         bn.seq = (const uint8_t*)rebuilt.data();
+        bn.len = (int64_t)rebuilt.size();
     }
 };
 

@@ -529,7 +529,9 @@ size_t Transcriptome::clean_short_orfs(int minlen) {
 
 size_t Transcriptome::bundleup(bool use_id, uint32_t overhang) {
     sort(use_id);
-    if (fasta) {
+    bool any_missing = false;
+    if (fasta) for (const std::string& name : seqnames) if (!fasta->find(name)) { any_missing = true; break; }
+    if (fasta && any_missing) {   // (every sequence present: nothing to filter, the transcripts stay where they are)
         std::vector<Tx> valid;
         valid.reserve(txs.size());
         int cur = -1;

@@ -11,6 +11,7 @@ import json
 import os
 import re
 import subprocess
+import sys
 
 import numpy as np
 import pytest
@@ -71,6 +72,17 @@ def test_oracle_cli_matches_reference_binary(synth, seed):
     for args, tpl in SELF_GRID:
         total += compare_clis(ORACLE_CLI, d, args, tpl)
     assert total > 100000   # the runs produced real output
+
+
+@needs_ref_bin
+def test_fuzz_parity_sample():
+    """A slice of the randomised differential campaign (tools/fuzz_parity.py: random generator settings x random option
+    combinations, oracle CLI vs reference binary, bytes and exit codes).  The full campaigns and what they found are in
+    DESIGN.md §4c / profiles/r02_fuzz_parity.txt."""
+    p = subprocess.run([sys.executable, os.path.join(ROOT, "tools", "fuzz_parity.py"), "--seeds", "200:212", "--runs-per-seed", "5"],
+                       capture_output=True, text=True, timeout=900)
+    assert p.returncode == 0, p.stdout[-2000:]
+    assert "60 runs over 12 seeds, 0 failures" in p.stdout
 
 
 @pytest.mark.parametrize("seed", SYNTH_SEEDS)
