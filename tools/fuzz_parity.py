@@ -38,7 +38,7 @@ def random_workload(rng, d, seed):
     return args, tpl
 
 
-def random_options(rng, tpl):
+def random_options(rng, tpl, overhang=True):
     a = []
     query = "query.gtf"
     templates = list(tpl)
@@ -67,7 +67,7 @@ def random_options(rng, tpl):
     if has_ref:
         if rng.random() < 0.35:
             a += ["--cleant"] + (["--rescue"] if rng.random() < 0.6 else [])
-        if rng.random() < 0.45:
+        if overhang and rng.random() < 0.45:
             a += ["--overhang", str(rng.choice([1, 2, 3, 7, 30, 89, 300, 2000, 60000]))]
             if rng.random() < 0.5:
                 a += ["--spliced_overhang"]
@@ -91,16 +91,60 @@ def run(binary, d, args, tag, templates, extra=()):
     return rc, rd(tag + ".gtf"), rd(tag + ".tsv"), err
 
 
+def fuzz_orfcompare(seeds, runs_per_seed):
+    """orfcompare: two annotation files of one workload against each other."""
+    cmp_ref = os.path.join(ROOT, "oracle", "_ref", "orfcompare_ref")
+    fails = runs = 0
+    for seed in seeds:
+        rng = random.Random(seed)
+        d = tempfile.mkdtemp(prefix="orfx_fuzzcmp_%d_" % seed)
+        n_tf = rng.choice([2, 3])
+        synth = [SYNTH, "--out", d, "--seed", str(seed), "--loci", str(rng.choice([20, 60, 150])), "--chroms", str(rng.choice([1, 3])),
+                 "--chrom-len", str(rng.choice([400000, 3000000])), "--queries", str(rng.choice([2, 8])), "--templates", str(rng.choice([2, 5, 9])),
+                 "--template-files", str(n_tf), "--titin-frac", str(rng.choice([0, 0.05])), "--lower-frac", "0.3"]
+        if rng.random() < 0.4:
+            synth += ["--dot-frac", "0.3"]
+        if rng.random() < 0.3:
+            synth += ["--edge-loci"]
+        subprocess.run(synth, check=True, stderr=subprocess.DEVNULL)
+        files = ["template%d.gtf" % (i + 1) for i in range(n_tf)] + ["query.gtf"]
+        for k in range(runs_per_seed):
+            q, t = rng.sample(files, 2) if rng.random() < 0.9 else (files[0], files[0])
+            opts = ["--query", q, "--template", t] + (["--use_id"] if rng.random() < 0.3 else []) + (["--reference", "genome.fa"] if rng.random() < 0.5 else [])
+            pr = subprocess.run([cmp_ref] + opts + ["--threads", "1", "--output", "cmp_ref.tsv"], cwd=d, capture_output=True)
+            po = subprocess.run([ORACLE_CLI, "orfcompare"] + opts + ["--output", "cmp_or.tsv"], cwd=d, capture_output=True)
+            runs += 1
+            if pr.returncode < 0:
+                print("note: reference orfcompare aborted (rc %d) seed %d: %s" % (pr.returncode, seed, " ".join(opts)))
+                continue
+
+            def rd(n):
+                path = os.path.join(d, n)
+                return open(path, "rb").read() if os.path.exists(path) else b""
+            if po.returncode != pr.returncode or (pr.returncode == 0 and rd("cmp_ref.tsv") != rd("cmp_or.tsv")):
+                fails += 1
+                print("FAIL orfcompare seed %d run %d (rc %d vs reference %d)\n  synth: %s\n  opts: %s\n  stderr(ours): %s\n  stderr(ref): %s"
+                      % (seed, k, po.returncode, pr.returncode, " ".join(synth[1:]), " ".join(opts), po.stderr.decode(errors="replace")[-300:],
+                         pr.stderr.decode(errors="replace")[-300:]))
+        shutil.rmtree(d, ignore_errors=True)
+    print("fuzz_parity (orfcompare): %d runs over %d seeds, %d failures" % (runs, len(seeds), fails))
+    return fails
+
+
 def main():
     ap = argparse.ArgumentParser()
+    ap.add_argument("--orfcompare", action="store_true", help="fuzz the orfcompare front-end instead of orfanage")
     ap.add_argument("--seeds", default="200:220")
     ap.add_argument("--runs-per-seed", type=int, default=6)
+    ap.add_argument("--no-overhang", action="store_true", help="never pass --overhang (every other option still varies)")
     ap.add_argument("--keep", action="store_true", help="keep the directories of failing cases")
     args = ap.parse_args()
     lo, _, hi = args.seeds.partition(":")
     seeds = range(int(lo), int(hi or int(lo) + 1))
     if not (os.path.exists(ORACLE_CLI) and os.path.exists(REF_BIN)):
         sys.exit("build first: make oracle (needs /root/reference for oracle/_ref)")
+    if args.orfcompare:
+        sys.exit(1 if fuzz_orfcompare(seeds, args.runs_per_seed) else 0)
     fails = runs = aborted = bytes_cmp = 0
     for seed in seeds:
         rng = random.Random(seed)
@@ -108,7 +152,7 @@ def main():
         synth_args, tpl = random_workload(rng, d, seed)
         bad_here = False
         for k in range(args.runs_per_seed):
-            opts, templates = random_options(rng, tpl)
+            opts, templates = random_options(rng, tpl, not args.no_overhang)
             rc_r, gtf_r, tsv_r, err_r = run(REF_BIN, d, opts, "ref", templates, ["--threads", "1"])
             rc_o, gtf_o, tsv_o, err_o = run(ORACLE_CLI, d, opts, "cand", templates)
             runs += 1
