@@ -785,6 +785,8 @@ def main():
     achieved = alg_bytes / (scan_ms / 1e3) / 1e9 if scan_ms > 0 else 0.0
     stage_achieved = alg_bytes / ((scan_ms + planes_ms) / 1e3) / 1e9 if scan_ms + planes_ms > 0 else 0.0
     traffic, traffic_src = profiled_traffic("codon_scan_kernel")
+    if c4:   # the capture is one configs[1] launch: it says nothing about a launch eight times that size
+        traffic, traffic_src = None, "not captured for this workload (profiles/r02_traffic.json is a configs[1] launch)"
     dominant = max(m["stage_ms"], key=lambda k: m["stage_ms"][k]) if m["stage_ms"] else None
     line = {
         "metric": "query transcripts/sec", "value": value, "unit": "transcripts/s", "n_gpus": m["world"], "steps": K,
