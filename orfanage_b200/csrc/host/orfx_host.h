@@ -65,6 +65,10 @@ struct GtfRecord {   // one transcript as read from a GTF (what the reference ge
     std::vector<std::pair<std::string, std::string>> attrs;   // transcript-line attributes, file order
 };
 void read_gtf(const std::string& path, std::vector<GtfRecord>& out);
+// Records converted to transcripts, not yet part of a Transcriptome: Tx::seqid indexes `seqnames` (the names of all records of
+// the file, first-seen order), Tx::id counts from 0.
+struct ParsedTxs { std::vector<Tx> txs; std::vector<std::string> seqnames; };
+void convert_records(const std::vector<GtfRecord>& recs, bool is_templ, bool coding_only, ParsedTxs& out);
 
 // --- FASTA ------------------------------------------------------------------------------------
 // The FASTA is memory-mapped and read through its samtools-style index (the .fai next to it when present, else
@@ -117,6 +121,7 @@ public:
 
     void add(const std::string& gtf_path, bool is_templ, bool coding_only);   // Transcriptome::add, cpp:866-894
     void add_records(const std::vector<GtfRecord>& recs, bool is_templ, bool coding_only);   // the same from parsed records
+    void append(ParsedTxs&& p);       // converted records join the transcriptome (sequence ids mapped, transcript ids assigned)
     void build_cds_chains();          // cpp:1033-1044
     void correct_chain_len();         // cpp:1045-1051
     void sort(bool use_id);           // Transcriptome.h:904-924

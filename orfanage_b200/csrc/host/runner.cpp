@@ -614,13 +614,17 @@ void prepare_transcriptome(const Options& opt, Fasta& fasta, Transcriptome& tr, 
             timing += b; last = now;
         }
     };
-    // The query GTF is parsed on the side while the templates are loaded, sorted, cleaned and deduplicated (the two files meet
+    // The query GTF is parsed and converted to transcripts on the side while the templates are loaded, sorted, cleaned and deduplicated (the two files meet
     // in bundleup); its records join the transcriptome where the reference loads them, and a parse error of the query surfaces
     // there too -- after any error of the template stages, as in the reference.
-    struct QueryRecs { std::vector<GtfRecord> recs; std::exception_ptr err; };
-    std::future<QueryRecs> query_parse = std::async(std::launch::async, [&opt]() {
-        QueryRecs q;
-        try { read_gtf(opt.query, q.recs); } catch (...) { q.err = std::current_exception(); }
+    struct QueryTxs { ParsedTxs parsed; std::exception_ptr err; };
+    std::future<QueryTxs> query_parse = std::async(std::launch::async, [&opt]() {
+        QueryTxs q;
+        try {
+            std::vector<GtfRecord> recs;
+            read_gtf(opt.query, recs);
+            convert_records(recs, false, false, q.parsed);
+        } catch (...) { q.err = std::current_exception(); }
         return q;
     });
     say("loading reference genome");
@@ -644,9 +648,9 @@ void prepare_transcriptome(const Options& opt, Fasta& fasta, Transcriptome& tr, 
     tr.deduplicate(opt.use_id);
     say("loading query transcriptome");
     {
-        QueryRecs q = query_parse.get();
+        QueryTxs q = query_parse.get();
         if (q.err) std::rethrow_exception(q.err);
-        tr.add_records(q.recs, false, false);
+        tr.append(std::move(q.parsed));
     }
     say("bundling transcriptome");
     tr.bundleup(opt.use_id, (uint32_t)opt.overhang);

@@ -5,6 +5,7 @@
 #include <functional>
 #include <unordered_map>
 #include <algorithm>
+#include <chrono>
 #include <cstring>
 #include <fcntl.h>
 #include <sys/mman.h>
@@ -402,24 +403,31 @@ void Transcriptome::add(const std::string& gtf_path, bool is_templ, bool coding_
     add_records(recs, is_templ, coding_only);
 }
 void Transcriptome::add_records(const std::vector<GtfRecord>& recs, bool is_templ, bool coding_only) {
-    bundles.clear();
-    for (const GtfRecord& r : recs) {   // Transcriptome::load_seqids, cpp:855-865
-        auto ins = seqids_.insert(std::make_pair(r.seqname, (int)seqnames.size()));
-        if (ins.second) seqnames.push_back(r.seqname);
+    ParsedTxs p;
+    convert_records(recs, is_templ, coding_only, p);
+    append(std::move(p));
+}
+// TX::TX(GffObj*), cpp:11-82, for every record that is kept; the conversions are independent of each other.  No Transcriptome
+// state is touched (the query file is converted beside the template stages): Tx::seqid indexes out.seqnames, the names of ALL
+// records in first-seen order (Transcriptome::load_seqids, cpp:855-865, registers them before any record is dropped).
+void convert_records(const std::vector<GtfRecord>& recs, bool is_templ, bool coding_only, ParsedTxs& out) {
+    std::unordered_map<std::string, int> local;
+    std::vector<int> seqid_of(recs.size());
+    for (size_t i = 0; i < recs.size(); i++) {
+        auto ins = local.insert(std::make_pair(recs[i].seqname, (int)out.seqnames.size()));
+        if (ins.second) out.seqnames.push_back(recs[i].seqname);
+        seqid_of[i] = ins.first->second;
     }
-    // TX::TX(GffObj*), cpp:11-82, for every record that is kept; the conversions are independent of each other
     std::vector<size_t> keep;
     keep.reserve(recs.size());
     for (size_t i = 0; i < recs.size(); i++) if (!(coding_only && !recs[i].has_cds) && !recs[i].exons.empty()) keep.push_back(i);
-    const size_t base = txs.size();
-    txs.resize(base + keep.size());
-    std::vector<int> seqid_of(recs.size());
-    for (size_t i : keep) seqid_of[i] = seqids_[recs[i].seqname];
+    std::vector<Tx>& txs = out.txs;
+    txs.resize(keep.size());
     auto convert = [&](size_t k0, size_t k1, std::string* err) {
         try {
             for (size_t k = k0; k < k1; k++) {
                 const GtfRecord& r = recs[keep[k]];
-                Tx& t = txs[base + k];
+                Tx& t = txs[k];
                 if (r.has_cds) {
                     t.is_coding = true;
                     t.cds_start = (int)r.cd_start;
@@ -434,10 +442,10 @@ void Transcriptome::add_records(const std::vector<GtfRecord>& recs, bool is_temp
                     }
                 }
                 t.is_templ = is_templ;
-                t.id = (int)(base + k);
+                t.id = (int)k;                      // Transcriptome::append adds the number of transcripts before it
                 t.tid = r.tid;
                 t.gid = r.has_gid ? r.gid : r.tid;
-                t.seqid = seqid_of[keep[k]];
+                t.seqid = seqid_of[keep[k]];        // local; Transcriptome::append maps it
                 t.strand = r.strand;
                 t.source = r.source;
                 t.cds_source = r.source;
@@ -465,6 +473,19 @@ void Transcriptome::add_records(const std::vector<GtfRecord>& recs, bool is_temp
         for (auto& t : th) t.join();
     }
     for (const std::string& e : errs) if (!e.empty()) throw std::runtime_error(e);   // the first failing slice in file order
+}
+void Transcriptome::append(ParsedTxs&& p) {
+    bundles.clear();
+    std::vector<int> global(p.seqnames.size());
+    for (size_t i = 0; i < p.seqnames.size(); i++) {   // Transcriptome::load_seqids, cpp:855-865
+        auto ins = seqids_.insert(std::make_pair(p.seqnames[i], (int)seqnames.size()));
+        if (ins.second) seqnames.push_back(p.seqnames[i]);
+        global[i] = ins.first->second;
+    }
+    const size_t base = txs.size();
+    if (base == 0) txs = std::move(p.txs);
+    else { txs.reserve(base + p.txs.size()); for (Tx& t : p.txs) txs.emplace_back(std::move(t)); }
+    for (size_t k = base; k < txs.size(); k++) { txs[k].id = (int)k; txs[k].seqid = global[(size_t)txs[k].seqid]; }
 }
 
 void Transcriptome::build_cds_chains() {
@@ -498,10 +519,23 @@ void Transcriptome::sort(bool use_id) {
     } else {
         std::sort(keys.begin(), keys.end(), less);
     }
-    std::vector<Tx> sorted;
-    sorted.reserve(txs.size());
-    for (size_t i = 0; i < keys.size(); i++) sorted.emplace_back(std::move(txs[keys[i].idx]));
-    txs.swap(sorted);
+    // the objects move once, into place: destination i takes source keys[i].idx (a permutation, so every object is read by
+    // one thread and written by one); the copy is bound by the scattered reads, which several threads overlap
+    const size_t n = txs.size();
+    const unsigned nthr = n > 50000 ? std::min(8u, std::max(1u, std::thread::hardware_concurrency())) : 1u;
+    if (nthr <= 1) {
+        std::vector<Tx> sorted;
+        sorted.reserve(n);
+        for (size_t i = 0; i < n; i++) sorted.emplace_back(std::move(txs[keys[i].idx]));
+        txs.swap(sorted);
+    } else {
+        std::vector<Tx> sorted(n);
+        std::vector<std::thread> th;
+        for (unsigned k = 0; k < nthr; k++)
+            th.emplace_back([&, k]() { for (size_t i = n * k / nthr, e = n * (k + 1) / nthr; i < e; i++) sorted[i] = std::move(txs[keys[i].idx]); });
+        for (auto& t : th) t.join();
+        txs.swap(sorted);
+    }
 }
 void Transcriptome::set_cds_as_exons() {
     for (Tx& t : txs) {
