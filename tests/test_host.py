@@ -222,6 +222,16 @@ def test_segment_dictionary_expands_to_the_segment_arrays(synth, oracle_lib):
     w.close()
 
 
+def test_layout_fuzz_sample():
+    """A slice of tools/fuzz_layouts.py: random workloads, parameters and shards; every upload format of the packer gives the
+    oracle the same rows and winners."""
+    import subprocess
+    import sys
+    p = subprocess.run([sys.executable, os.path.join(ROOT, "tools", "fuzz_layouts.py"), "--seeds", "0:12"], capture_output=True, text=True, timeout=600)
+    assert p.returncode == 0, p.stdout[-2000:] + p.stderr[-2000:]
+    assert "0 failures" in p.stdout
+
+
 def test_sharding_is_a_partition(synth, oracle_lib):
     """Shards are disjoint, cover every active bundle, and evaluating them separately gives the same
     per-query answers as one batch (loci are independent: SURVEY.md §8e)."""
